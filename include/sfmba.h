@@ -1,0 +1,191 @@
+/*
+ * sfmba.h -- C ABI of libsfmba.so, the B200 (sm_100a) bundle-adjustment / nonlinear-refinement engine.
+ *
+ * The reference (willSapgreen/structure-from-motion) is pure Python and has NO FFI for this path; its
+ * boundary is the Python class surface.  Each entry point below names the
+ * reference interface it replaces.  The reference-side binding a maintainer would add is the ctypes
+ * stub shown in INTEGRATION.md (and implemented in structure-from-motion_b200/_capi.py).
+ *
+ * Rules of the ABI
+ *   - plain C: pointers, sizes, POD structs; no C++ exceptions cross it; no torch types.
+ *   - every function returns 0 (SFMBA_OK) or a negative sfmba_status; sfmba_last_error() gives text.
+ *   - "device" pointers are CUDA device pointers on the ctx's device (e.g. torch.Tensor.data_ptr());
+ *     "host" pointers are ordinary host memory.  `stream` is a cudaStream_t passed as void*
+ *     (torch.cuda.current_stream().cuda_stream); NULL = the default stream.
+ *   - a ctx owns only its workspace; it is bound to one device and is not thread-safe.
+ *   - *_host entry points take HOST buffers, stage them through pinned memory, run the same device
+ *     path and copy the results back before returning (the end-to-end path bench.py times as `e2e`).
+ *
+ * Conventions (reference: view_processor.py:57, utils.py:58, ba_processor.py:285-294)
+ *   world->camera  p = R^T (X - C);  quaternion order (w,x,y,z);  pose = [Cx,Cy,Cz,qw,qx,qy,qz];
+ *   observations sorted point-major / view-minor (ba_processor.py:304-306).
+ */
+#ifndef SFMBA_H_
+#define SFMBA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SFMBA_API __attribute__((visibility("default")))
+#else
+#define SFMBA_API
+#endif
+
+#define SFMBA_VERSION 100
+#define SFMBA_MAX_COST_HISTORY 64
+
+typedef struct sfmba_ctx sfmba_ctx;
+
+typedef enum {
+  SFMBA_OK = 0,
+  SFMBA_ERR_INVALID_ARG = -1,
+  SFMBA_ERR_CUDA = -2,
+  SFMBA_ERR_NCCL = -3,
+  SFMBA_ERR_NUMERIC = -4,   /* device raised a numeric flag, see sfmba_result.flags              */
+  SFMBA_ERR_UNSUPPORTED = -5,
+  SFMBA_ERR_NO_DEVICE = -6
+} sfmba_status;
+
+/* bits of sfmba_result.flags / refine `flags` outputs (device-side error word)                     */
+#define SFMBA_FLAG_QW_NEAR_ZERO   1u  /* |qw| < 1e-6 when q is re-derived from R (utils.py:49-51)  */
+#define SFMBA_FLAG_DEPTH_ZERO     2u  /* p_w == 0 for some observation                             */
+#define SFMBA_FLAG_NONFINITE      4u  /* NaN/Inf in cost or update                                 */
+#define SFMBA_FLAG_PCG_MAXITER    8u  /* PCG stopped on pcg_max_iter, not on pcg_tol               */
+#define SFMBA_FLAG_SINGULAR      16u  /* a 3x3 / 7x7 block was not positive definite               */
+
+typedef enum { SFMBA_MODE_REFERENCE_FIXED = 0, SFMBA_MODE_ADAPTIVE_LM = 1 } sfmba_mode;
+typedef enum { SFMBA_SOLVER_PCG = 0 } sfmba_solver;
+
+/*
+ * One BA problem (this rank's shard when world_size > 1: cameras replicated, points and their
+ * observations partitioned by point).  Replaces the packing at ba_processor.py:285-294 and the
+ * per-observation gathers at ba_processor.py:309-342.
+ */
+typedef struct {
+  int32_t num_cams;          /* V                                                                   */
+  int32_t num_pts;           /* N (local)                                                           */
+  int32_t num_obs;           /* m (local)                                                           */
+  int32_t reserved0;
+  const float*   obs_uv;     /* f32 [2][m] SoA: all u then all v.  Pixel coordinates when cam_kinv  */
+                             /* is given (cv2.KeyPoint.pt is float32), else already normalised      */
+  const int32_t* obs_cam;    /* i32 [m] camera index of each observation                            */
+  const int32_t* obs_pt;     /* i32 [m] point index, non-decreasing (point-major order)             */
+  const int32_t* pt_rowptr;  /* i32 [N+1] CSR offsets into the observation arrays                   */
+  const double*  cam_kinv;   /* f64 [V][9] row-major K^-1 per camera, or NULL = identity            */
+                             /* (ba_processor.py:339-342: b = K^-1 [u,v,1]^T / z)                   */
+  double*        cams;       /* f64 [V][7] in/out: [C(3), q(w,x,y,z)]                               */
+  double*        pts;        /* f64 [N][3] in/out                                                   */
+} sfmba_problem;
+
+typedef struct {
+  double  lambda;            /* damping factor (ba_processor.py:24 default 5)                       */
+  int32_t iterations;        /* number of (reference mode) / max (adaptive mode) LM iterations      */
+  int32_t mode;              /* sfmba_mode                                                          */
+  int32_t solver;            /* sfmba_solver                                                        */
+  int32_t pcg_max_iter;      /* <= 0: default                                                       */
+  double  pcg_tol;           /* relative residual ||r|| <= tol ||g||;  <= 0: default 1e-12          */
+  int32_t dvdc_sign_quirk;   /* 1 = reproduce campose_processor.py:802-804 (reference), 0 = exact   */
+  int32_t force_slow_path;   /* testing: route every tile through the long-track code path          */
+  int32_t compute_costs;     /* 1 = fill sfmba_result.costs (one extra cost pass at the end)        */
+  int32_t reserved0;
+  double  lm_lambda_min;     /* adaptive mode clamps                                                */
+  double  lm_lambda_max;
+} sfmba_options;
+
+typedef struct {
+  double   initial_cost;     /* sum ||b - f||^2 at entry (normalised camera coordinates)            */
+  double   final_cost;       /* at exit                                                             */
+  double   final_lambda;
+  int32_t  iterations_done;
+  int32_t  iterations_accepted;
+  int32_t  pcg_iterations;   /* total over all LM iterations                                        */
+  uint32_t flags;            /* SFMBA_FLAG_*                                                        */
+  int32_t  num_costs;
+  int32_t  reserved0;
+  double   costs[SFMBA_MAX_COST_HISTORY];  /* cost at the start of iteration k, then the final cost */
+  /* device time of the phases of the last call, milliseconds (CUDA events on `stream`)             */
+  float    ms_total, ms_index, ms_linearize, ms_camreduce, ms_pcg, ms_update;
+  int32_t  kernel_launches;  /* kernels launched by the call                                        */
+  int32_t  reserved1;
+} sfmba_result;
+
+/* ---- lifetime -------------------------------------------------------------------------------- */
+/* nccl_unique_id: NULL when world_size == 1, else the 128-byte ncclUniqueId made by
+ * sfmba_nccl_unique_id() on rank 0 and distributed by the caller (torch.distributed broadcast).   */
+SFMBA_API int sfmba_create(sfmba_ctx** out, int device, int world_size, int rank, const void* nccl_unique_id);
+SFMBA_API int sfmba_destroy(sfmba_ctx* ctx);
+SFMBA_API const char* sfmba_last_error(const sfmba_ctx* ctx);      /* ctx may be NULL: last global error      */
+SFMBA_API int sfmba_version(void);
+SFMBA_API int sfmba_nccl_unique_id(void* out128);
+SFMBA_API void sfmba_default_options(sfmba_options* opt);
+
+/* ---- a1..a17: BaProcessor.__execute_bundle_adjustment  (ba_processor.py:274-440) -------------- */
+SFMBA_API int sfmba_ba_solve(sfmba_ctx* ctx, const sfmba_problem* problem, const sfmba_options* opt,
+                   sfmba_result* result, void* stream);
+/* same with HOST buffers in `problem` (all pointers host); cams/pts updated in place on the host  */
+SFMBA_API int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* problem, const sfmba_options* opt,
+                        sfmba_result* result);
+
+/* ---- a5,a7..a12 alone: residual + Jacobian blocks per observation (K1, for parity tests and for
+ * CamposeProcessor.construct_jacobian_matrix, campose_processor.py:462-482 /
+ * TriangulationProcessor.construct_jacobian_matrix, triangulation_processor.py:237-271) ---------
+ * out_r  f32 [2][m], out_jp f32 [14][m] (row-major 2x7 block, entry e = 7*row+col), out_jx f32
+ * [6][m] (entry e = 3*row+col), all SoA; any of them may be NULL.  out_cost: device f64 [1] or NULL.
+ * out_r64: optional device f64 [2][m] full-precision residuals.                                    */
+SFMBA_API int sfmba_residual_jacobian(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk,
+                            float* out_r, float* out_jp, float* out_jx, double* out_r64,
+                            double* out_cost, void* stream);
+SFMBA_API int sfmba_ba_cost(sfmba_ctx* ctx, const sfmba_problem* problem, double* host_cost, void* stream);
+
+/* ---- a18: TriangulationProcessor.nonlinear_triangulate (triangulation_processor.py:160-234),
+ * batched over points with a CSR of (view, observation) per point.
+ *   projs   f64 [P][12] row-major 3x4 projection matrices (K included by the caller)
+ *   rowptr  i32 [M+1], obs_view i32 [m] index into projs, obs_uv f64 [m][2]
+ *   pts     f64 [M][3] in/out;  X -= inv(J^T J + lambda I3) J^T (proj - obs), `iterations` times    */
+SFMBA_API int sfmba_triangulate_refine_batched(sfmba_ctx* ctx, int32_t num_pts, int32_t num_obs, int32_t num_projs,
+                                     const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                                     const double* obs_uv, double* pts, double lambda, int32_t iterations,
+                                     uint32_t* host_flags, void* stream);
+SFMBA_API int sfmba_triangulate_refine_batched_host(sfmba_ctx* ctx, int32_t num_pts, int32_t num_obs, int32_t num_projs,
+                                          const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                                          const double* obs_uv, double* pts, double lambda, int32_t iterations,
+                                          uint32_t* host_flags);
+
+/* ---- a19: CamposeProcessor.nonlinear_estimate_cam_pose_pnp (campose_processor.py:308-459),
+ * batched over views with a CSR of observations per view.
+ *   rowptr   i32 [P+1];  obs_xy f64 [m][2] normalised observations (K^-1 x / z);  obs_X f64 [m][3]
+ *   world points (homogeneous coordinate 1);  rot f64 [P][9] in/out (row-major, camera-to-world);  loc f64 [P][3]
+ *   in/out.  row_packing_quirk = 1 reproduces campose_processor.py:404-405.                        */
+SFMBA_API int sfmba_pnp_refine_batched(sfmba_ctx* ctx, int32_t num_views, int32_t num_obs, const int32_t* rowptr,
+                             const double* obs_xy, const double* obs_X, double* rot, double* loc,
+                             double lambda, int32_t iterations, int32_t row_packing_quirk,
+                             int32_t dvdc_sign_quirk, uint32_t* host_flags, void* stream);
+SFMBA_API int sfmba_pnp_refine_batched_host(sfmba_ctx* ctx, int32_t num_views, int32_t num_obs, const int32_t* rowptr,
+                                  const double* obs_xy, const double* obs_X, double* rot, double* loc,
+                                  double lambda, int32_t iterations, int32_t row_packing_quirk,
+                                  int32_t dvdc_sign_quirk, uint32_t* host_flags);
+
+/* ---- a3/a4: visibility index from the diagonal rows of KeyTrack.table (key_tracker.py:29-59,
+ * 198-204), bit-exact including the index-0 quirk.  diag i64 [total_keys] is the concatenation of
+ * table[v, :] for v = 0..V-1, key_off i64 [V+1] the offsets.  Outputs (device i32): obs_pt, obs_cam,
+ * obs_key sized >= min(total_keys, V*N); pt_rowptr [N+1]; *host_num_obs receives m.                */
+SFMBA_API int sfmba_build_visibility(sfmba_ctx* ctx, int32_t num_views, int32_t num_pts, const int64_t* diag,
+                           const int64_t* key_off, int32_t* obs_pt, int32_t* obs_cam, int32_t* obs_key,
+                           int32_t* pt_rowptr, int32_t* host_num_obs, void* stream);
+
+/* ---- introspection used by bench.py ---------------------------------------------------------- */
+/* device time (ms) and launch count of named kernels accumulated since the last reset; names:
+ * "linearize", "camreduce", "matvec_a", "matvec_b", "pcg_vec", "k1"                               */
+SFMBA_API int sfmba_profile_reset(sfmba_ctx* ctx);
+SFMBA_API int sfmba_profile_enable(sfmba_ctx* ctx, int enable);    /* per-kernel event timing (adds syncs)    */
+SFMBA_API int sfmba_profile_get(sfmba_ctx* ctx, const char* name, double* ms_total, int64_t* launches);
+SFMBA_API int64_t sfmba_total_launches(const sfmba_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SFMBA_H_ */

@@ -1,0 +1,384 @@
+// Host driver of the BA solve: workspace carving, the LM / PCG launch sequence, collectives.
+//
+// Reference loop: ba_processor.py:297-406 (fixed lambda, `iteration` always-accepted steps).
+// SFMBA_MODE_ADAPTIVE_LM adds cost evaluation, gain ratio and accept/reject, all decided on the
+// device (the reference has none of these).
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "ctx.h"
+
+using namespace sfmba;
+
+std::string g_last_error;
+
+int sfm_set_error(sfmba_ctx* ctx, int code, const std::string& msg) {
+  g_last_error = msg;
+  if (ctx) ctx->err = msg;
+  return code;
+}
+
+int sfm_check_cuda(sfmba_ctx* ctx, cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return SFMBA_OK;
+  return sfm_set_error(ctx, SFMBA_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+cudaError_t DevBuf::reserve(size_t bytes) {
+  if (bytes <= cap) return cudaSuccess;
+  if (ptr) cudaFree(ptr);
+  ptr = nullptr;
+  cap = 0;
+  size_t want = bytes + bytes / 8 + 256;
+  cudaError_t e = cudaMalloc(&ptr, want);
+  if (e != cudaSuccess) {
+    want = bytes;
+    e = cudaMalloc(&ptr, want);
+  }
+  if (e == cudaSuccess) cap = want;
+  return e;
+}
+
+void DevBuf::release() {
+  if (ptr) cudaFree(ptr);
+  ptr = nullptr;
+  cap = 0;
+}
+
+cudaError_t sfmba_ctx::reserve(int slot, size_t bytes, void** out) {
+  if ((int)bufs.size() <= slot) bufs.resize(slot + 1);
+  cudaError_t e = bufs[slot].reserve(bytes ? bytes : 16);
+  *out = bufs[slot].ptr;
+  return e;
+}
+
+namespace {
+
+enum Slot {
+  S_SCALARS = 0, S_TILE_PT, S_CM_PERM, S_PM2CM, S_CAM_ROWPTR, S_CAM_CHUNK_PTR, S_CHUNK_CAM, S_CHUNK_BEG,
+  S_CAMTAB, S_JP_PM, S_JX_PM, S_REC_CM, S_Y_CM, S_DINV, S_VJ, S_TILE_COST, S_CHUNK_ACC, S_CAM_ACC, S_ABLK,
+  S_MINV, S_B_CM, S_CHUNK_Y, S_SVEC, S_X, S_R, S_Z, S_P, S_GVEC, S_CAMS_BAK, S_PTS_BAK, S_SORT_TEMP,
+  S_SORT_KEYS, S_IOTA, S_COUNT
+};
+
+template <typename T>
+int carve(sfmba_ctx* ctx, int slot, size_t count, T** out) {
+  void* p = nullptr;
+  cudaError_t e = ctx->reserve(slot, count * sizeof(T), &p);
+  *out = reinterpret_cast<T*>(p);
+  return sfm_check_cuda(ctx, e, "cudaMalloc(workspace)");
+}
+
+}  // namespace
+
+// Fills the BaDev view.  `full` = false carves only what K1 / cost need.
+int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev* out) {
+  if (!pr || pr->num_cams < 0 || pr->num_pts < 0 || pr->num_obs < 0)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "bad problem sizes");
+  if (pr->num_cams == 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "num_cams == 0");
+  if (!pr->cams || (pr->num_pts > 0 && !pr->pts) || !pr->pt_rowptr ||
+      (pr->num_obs > 0 && (!pr->obs_uv || !pr->obs_cam || !pr->obs_pt)))
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "null pointer in problem");
+  BaDev d;
+  memset(&d, 0, sizeof(d));
+  d.V = pr->num_cams;
+  d.N = pr->num_pts;
+  d.m = pr->num_obs;
+  d.mp = (d.m + 31) / 32 * 32;
+  if (d.mp == 0) d.mp = 32;
+  d.ntiles = std::max(1, (d.m + TILE_OBS - 1) / TILE_OBS);
+  d.nchunk_bound = d.m > 0 ? d.m / CHUNK_OBS + std::min(d.V, d.m) : 0;
+  d.obs_uv = pr->obs_uv;
+  d.obs_cam = pr->obs_cam;
+  d.obs_pt = pr->obs_pt;
+  d.rowptr = pr->pt_rowptr;
+  d.kinv = pr->cam_kinv;
+  d.cams = pr->cams;
+  d.pts = pr->pts;
+  int rc;
+#define CARVE(slot, count, field) \
+  if ((rc = carve(ctx, slot, (size_t)(count), &d.field)) != SFMBA_OK) return rc;
+  CARVE(S_SCALARS, 1, sc);
+  CARVE(S_CAMTAB, (size_t)d.V * CAMTAB_STRIDE, camtab);
+  CARVE(S_TILE_COST, d.ntiles, tile_cost);
+  if (full) {
+    CARVE(S_TILE_PT, d.ntiles + 1, tile_pt);
+    CARVE(S_CM_PERM, std::max(d.m, 1), cm_perm);
+    CARVE(S_PM2CM, std::max(d.m, 1), pm2cm);
+    CARVE(S_CAM_ROWPTR, d.V + 1, cam_rowptr);
+    CARVE(S_CAM_CHUNK_PTR, d.V + 1, cam_chunk_ptr);
+    CARVE(S_CHUNK_CAM, d.nchunk_bound + 1, chunk_cam);
+    CARVE(S_CHUNK_BEG, d.nchunk_bound + 2, chunk_beg);
+    CARVE(S_JP_PM, (size_t)14 * d.mp, jp_pm);
+    CARVE(S_JX_PM, (size_t)6 * d.mp, jx_pm);
+    CARVE(S_REC_CM, (size_t)4 * std::max(d.m, 1), rec_cm);
+    CARVE(S_Y_CM, std::max(d.m, 1), y_cm);
+    CARVE(S_DINV, (size_t)6 * std::max(d.N, 1), dinv);
+    CARVE(S_VJ, (size_t)3 * std::max(d.N, 1), vj);
+    CARVE(S_CHUNK_ACC, (size_t)(d.nchunk_bound + 1) * CAM_ACC, chunk_acc);
+    CARVE(S_CAM_ACC, (size_t)d.V * CAM_ACC + 8, cam_acc);
+    CARVE(S_ABLK, (size_t)d.V * 49, ablk);
+    CARVE(S_MINV, (size_t)d.V * 49, minv);
+    CARVE(S_B_CM, std::max(d.m, 1), b_cm);
+    CARVE(S_CHUNK_Y, (size_t)(d.nchunk_bound + 1) * 8, chunk_y);
+    CARVE(S_SVEC, (size_t)7 * d.V, svec);
+    CARVE(S_X, (size_t)7 * d.V, x);
+    CARVE(S_R, (size_t)7 * d.V, r);
+    CARVE(S_Z, (size_t)7 * d.V, z);
+    CARVE(S_P, (size_t)7 * d.V, p);
+    CARVE(S_GVEC, (size_t)7 * d.V, gvec);
+    CARVE(S_CAMS_BAK, (size_t)7 * d.V, cams_backup);
+    CARVE(S_PTS_BAK, (size_t)3 * std::max(d.N, 1), pts_backup);
+  }
+#undef CARVE
+  *out = d;
+  return SFMBA_OK;
+}
+
+namespace {
+
+struct PhaseTimer {
+  sfmba_ctx* ctx;
+  cudaStream_t st;
+  float acc[6] = {0, 0, 0, 0, 0, 0};
+  // phase timing needs event pairs; to stay asynchronous we record (begin,end) pairs lazily and
+  // resolve them after the final synchronisation
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> spans;
+  std::vector<cudaEvent_t> pool;
+  cudaEvent_t get() {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    pool.push_back(e);
+    return e;
+  }
+  cudaEvent_t begin() {
+    cudaEvent_t e = get();
+    cudaEventRecord(e, st);
+    return e;
+  }
+  void end(int phase, cudaEvent_t b) {
+    cudaEvent_t e = get();
+    cudaEventRecord(e, st);
+    spans.push_back({phase, {b, e}});
+  }
+  // named per-kernel spans, recorded only when ctx->profile is on (sfmba_profile_enable)
+  struct KSpan { const char* name; cudaEvent_t b, e; };
+  std::vector<KSpan> kspans;
+  cudaEvent_t kbegin() { return ctx->profile ? begin() : nullptr; }
+  void kend(const char* name, cudaEvent_t b) {
+    if (!ctx->profile) return;
+    cudaEvent_t e = get();
+    cudaEventRecord(e, st);
+    kspans.push_back({name, b, e});
+  }
+  void resolve() {
+    for (auto& s : spans) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, s.second.first, s.second.second) == cudaSuccess) acc[s.first] += ms;
+    }
+    for (auto& k : kspans) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, k.b, k.e) == cudaSuccess) {
+        ProfileEntry& pe = ctx->prof[k.name];
+        pe.ms += ms;
+        pe.launches += 1;
+      }
+    }
+    kspans.clear();
+    for (auto e : pool) cudaEventDestroy(e);
+    pool.clear();
+    spans.clear();
+  }
+};
+
+enum Phase { PH_INDEX = 0, PH_LINEARIZE, PH_CAMREDUCE, PH_PCG, PH_UPDATE, PH_TOTAL };
+
+}  // namespace
+
+int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_options* opt_in,
+                        sfmba_result* res, cudaStream_t st) {
+  sfmba_options opt;
+  if (opt_in) opt = *opt_in; else sfmba_default_options(&opt);
+  if (opt.iterations < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "iterations < 0");
+  if (opt.solver != SFMBA_SOLVER_PCG) return sfm_set_error(ctx, SFMBA_ERR_UNSUPPORTED, "unknown solver");
+  BaDev d;
+  int rc = sfm_setup_problem(ctx, pr, true, &d);
+  if (rc != SFMBA_OK) return rc;
+  const int n7 = 7 * d.V;
+  const double tol = opt.pcg_tol > 0 ? opt.pcg_tol : 1e-12;
+  const int max_iter = opt.pcg_max_iter > 0 ? opt.pcg_max_iter : std::max(200, std::min(4 * n7, 5000));
+  const bool quirk = opt.dvdc_sign_quirk != 0;
+  const bool slow = opt.force_slow_path != 0;
+  const bool adaptive = opt.mode == SFMBA_MODE_ADAPTIVE_LM;
+  const int64_t launches0 = ctx->lc.launches;
+  LaunchCounter& lc = ctx->lc;
+
+  // sort scratch
+  void* sort_temp = nullptr;
+  int32_t *sort_keys = nullptr, *iota = nullptr;
+  const size_t sort_bytes = index_sort_temp_bytes(d.m, d.V);
+  if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_SORT_TEMP, sort_bytes, &sort_temp), "cudaMalloc(sort)")) != 0) return rc;
+  if ((rc = carve(ctx, S_SORT_KEYS, (size_t)std::max(d.m, 1), &sort_keys)) != 0) return rc;
+  if ((rc = carve(ctx, S_IOTA, (size_t)std::max(d.m, 1), &iota)) != 0) return rc;
+
+  PhaseTimer pt{ctx, st};
+  cudaEvent_t t_total = pt.begin();
+
+  // scalars
+  Scalars h0;
+  memset(&h0, 0, sizeof(h0));
+  h0.lambda = opt.lambda;
+  h0.nu = 2.0;
+  // (pageable source: the copy is staged by the driver before the call returns)
+  if ((rc = sfm_check_cuda(ctx, cudaMemcpyAsync(d.sc, &h0, sizeof(h0), cudaMemcpyHostToDevice, st), "memcpy(scalars)")) != 0)
+    return rc;
+
+  cudaEvent_t t0 = pt.begin();
+  launch_build_index(d, sort_temp, sort_bytes, sort_keys, iota, st, lc);
+  pt.end(PH_INDEX, t0);
+
+  const bool multi = ctx->world > 1;
+  int cost_slot = 0;
+  for (int it = 0; it < opt.iterations; ++it) {
+    t0 = pt.begin();
+    if (adaptive) launch_lm_backup(d, st, lc);
+    launch_cam_prepare(d, st, lc);
+    {
+      cudaEvent_t kb = pt.kbegin();
+      launch_linearize(d, quirk, slow, cost_slot, st, lc);
+      pt.kend("linearize", kb);
+    }
+    pt.end(PH_LINEARIZE, t0);
+
+    t0 = pt.begin();
+    {
+      cudaEvent_t kb = pt.kbegin();
+      launch_camreduce(d, st, lc);
+      pt.kend("camreduce", kb);
+    }
+    launch_cam_finalize(d, st, lc);
+    if (multi) {
+      // one message: the camera accumulators plus this rank's cost in the trailing slot
+      cudaMemcpyAsync(d.cam_acc + (size_t)d.V * CAM_ACC, &d.sc->cost_cur, sizeof(double),
+                      cudaMemcpyDeviceToDevice, st);
+      if ((rc = sfm_nccl_allreduce_f64(ctx, d.cam_acc, (size_t)d.V * CAM_ACC + 1, st)) != 0) return rc;
+      cudaMemcpyAsync(&d.sc->cost_cur, d.cam_acc + (size_t)d.V * CAM_ACC, sizeof(double),
+                      cudaMemcpyDeviceToDevice, st);
+      if (cost_slot < SFMBA_MAX_COST_HISTORY)
+        cudaMemcpyAsync(&d.sc->costs[cost_slot], d.cam_acc + (size_t)d.V * CAM_ACC, sizeof(double),
+                        cudaMemcpyDeviceToDevice, st);
+    }
+    launch_cam_blocks(d, st, lc);
+    launch_pcg_init(d, tol, st, lc);
+    pt.end(PH_CAMREDUCE, t0);
+
+    // ---- PCG: launch in batches; poll the device-side done flag one batch behind so the queue
+    // never drains (kernels of an already-converged solve exit at their first instruction)
+    t0 = pt.begin();
+    {
+      const int batch = 8;
+      int32_t* done_host = reinterpret_cast<int32_t*>(ctx->pinned);
+      cudaEvent_t ev_prev = nullptr;
+      bool have_prev = false;
+      int launched = 0;
+      done_host[0] = 0;
+      done_host[1] = 0;
+      int which = 0;
+      while (launched < max_iter) {
+        const int nb = std::min(batch, max_iter - launched);
+        for (int k = 0; k < nb; ++k) {
+          cudaEvent_t kb = pt.kbegin();
+          launch_matvec_a(d, d.p, false, slow, st, lc);
+          pt.kend("matvec_a", kb);
+          kb = pt.kbegin();
+          launch_matvec_b(d, st, lc);
+          pt.kend("matvec_b", kb);
+          launch_matvec_finalize(d, st, lc);
+          if (multi && (rc = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st)) != 0) return rc;
+          kb = pt.kbegin();
+          launch_pcg_step(d, tol, max_iter, st, lc);
+          pt.kend("pcg_vec", kb);
+        }
+        launched += nb;
+        cudaMemcpyAsync(&done_host[which], &d.sc->pcg_done, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+        cudaEvent_t ev = pt.get();
+        cudaEventRecord(ev, st);
+        if (have_prev) {
+          cudaEventSynchronize(ev_prev);
+          if (done_host[which ^ 1]) break;
+        }
+        ev_prev = ev;
+        have_prev = true;
+        which ^= 1;
+      }
+    }
+    pt.end(PH_PCG, t0);
+
+    t0 = pt.begin();
+    if (adaptive) launch_lm_model_decrease(d, st, lc);
+    launch_matvec_a(d, d.x, true, slow, st, lc);     // back-substitution: pts += v - Dinv B^T dp
+    launch_update_cams(d, st, lc);
+    if (adaptive) {
+      launch_cam_prepare(d, st, lc);
+      launch_cost(d, nullptr, st, lc);               // -> sc->cost_new
+      if (multi) {
+        if ((rc = sfm_nccl_allreduce_f64(ctx, &d.sc->cost_new, 1, st)) != 0) return rc;
+      }
+      launch_lm_decide(d, opt.lm_lambda_min > 0 ? opt.lm_lambda_min : 1e-12,
+                       opt.lm_lambda_max > 0 ? opt.lm_lambda_max : 1e12, st, lc);
+    }
+    pt.end(PH_UPDATE, t0);
+    ++cost_slot;
+  }
+
+  // final cost
+  double* final_cost_dev = d.cam_acc + (size_t)d.V * CAM_ACC + 1;
+  if (opt.compute_costs || adaptive) {
+    launch_cam_prepare(d, st, lc);
+    launch_cost(d, final_cost_dev, st, lc);
+    if (multi && (rc = sfm_nccl_allreduce_f64(ctx, final_cost_dev, 1, st)) != 0) return rc;
+  }
+  pt.end(PH_TOTAL, t_total);
+
+  // results
+  char* pin = reinterpret_cast<char*>(ctx->pinned) + 64;
+  Scalars* hs = reinterpret_cast<Scalars*>(pin);
+  double* hfinal = reinterpret_cast<double*>(pin + sizeof(Scalars));
+  *hfinal = 0.0;
+  cudaMemcpyAsync(hs, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, st);
+  if (opt.compute_costs || adaptive)
+    cudaMemcpyAsync(hfinal, final_cost_dev, sizeof(double), cudaMemcpyDeviceToHost, st);
+  if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "solve sync")) != 0) return rc;
+  if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "solve kernels")) != 0) return rc;
+  pt.resolve();
+
+  if (res) {
+    memset(res, 0, sizeof(*res));
+    res->iterations_done = opt.iterations;
+    res->iterations_accepted = adaptive ? hs->lm_accepted : opt.iterations;
+    res->pcg_iterations = hs->pcg_iters_total;
+    res->flags = hs->flags;
+    res->final_lambda = hs->lambda;
+    const int nc = std::min(opt.iterations, SFMBA_MAX_COST_HISTORY - 1);
+    for (int k = 0; k < nc; ++k) res->costs[k] = hs->costs[k];
+    res->num_costs = nc;
+    res->initial_cost = nc > 0 ? hs->costs[0] : *hfinal;
+    res->final_cost = *hfinal;
+    if (opt.compute_costs || adaptive) res->costs[res->num_costs++] = *hfinal;
+    res->ms_index = pt.acc[PH_INDEX];
+    res->ms_linearize = pt.acc[PH_LINEARIZE];
+    res->ms_camreduce = pt.acc[PH_CAMREDUCE];
+    res->ms_pcg = pt.acc[PH_PCG];
+    res->ms_update = pt.acc[PH_UPDATE];
+    res->ms_total = pt.acc[PH_TOTAL];
+    res->kernel_launches = (int32_t)(ctx->lc.launches - launches0);
+  }
+  if (hs->flags & (SFMBA_FLAG_QW_NEAR_ZERO | SFMBA_FLAG_NONFINITE | SFMBA_FLAG_DEPTH_ZERO | SFMBA_FLAG_SINGULAR)) {
+    char buf[96];
+    snprintf(buf, sizeof(buf), "device numeric flags 0x%x", hs->flags);
+    return sfm_set_error(ctx, SFMBA_ERR_NUMERIC, buf);
+  }
+  return SFMBA_OK;
+}

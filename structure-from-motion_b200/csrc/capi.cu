@@ -1,0 +1,346 @@
+// extern "C" surface of libsfmba (include/sfmba.h).  No exceptions cross this file.
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+
+#include "ctx.h"
+
+using namespace sfmba;
+
+int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev* out);
+int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_options* opt, sfmba_result* res,
+                        cudaStream_t st);
+
+namespace {
+
+constexpr size_t PINNED_BYTES = 1 << 16;
+
+// device copy of a host array in ctx->host_stage[slot]
+template <typename T>
+int stage_in(sfmba_ctx* ctx, int slot, const T* host, size_t count, T** dev, cudaStream_t st) {
+  *dev = nullptr;
+  if (!host || count == 0) {
+    // keep a valid non-null pointer for zero-sized arrays
+    cudaError_t e = ctx->host_stage[slot].reserve(16);
+    if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(stage)");
+    *dev = ctx->host_stage[slot].as<T>();
+    return SFMBA_OK;
+  }
+  cudaError_t e = ctx->host_stage[slot].reserve(count * sizeof(T));
+  if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(stage)");
+  *dev = ctx->host_stage[slot].as<T>();
+  e = cudaMemcpyAsync(*dev, host, count * sizeof(T), cudaMemcpyHostToDevice, st);
+  return sfm_check_cuda(ctx, e, "cudaMemcpyAsync(H2D)");
+}
+
+int read_flags(sfmba_ctx* ctx, uint32_t* dflags, uint32_t* host_flags, cudaStream_t st) {
+  uint32_t* pin = reinterpret_cast<uint32_t*>(ctx->pinned);
+  cudaMemcpyAsync(pin, dflags, sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+  int rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "refine sync");
+  if (rc) return rc;
+  rc = sfm_check_cuda(ctx, cudaGetLastError(), "refine kernels");
+  if (rc) return rc;
+  if (host_flags) *host_flags = *pin;
+  if (*pin & (SFMBA_FLAG_QW_NEAR_ZERO | SFMBA_FLAG_NONFINITE)) {
+    char buf[64];
+    snprintf(buf, sizeof(buf), "device numeric flags 0x%x", *pin);
+    return sfm_set_error(ctx, SFMBA_ERR_NUMERIC, buf);
+  }
+  return SFMBA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sfmba_version(void) { return SFMBA_VERSION; }
+
+void sfmba_default_options(sfmba_options* opt) {
+  if (!opt) return;
+  memset(opt, 0, sizeof(*opt));
+  opt->lambda = 5.0;            // ba_processor.py:24
+  opt->iterations = 3;          // ba_processor.py:24
+  opt->mode = SFMBA_MODE_REFERENCE_FIXED;
+  opt->solver = SFMBA_SOLVER_PCG;
+  opt->pcg_max_iter = 0;
+  opt->pcg_tol = 1e-12;
+  opt->dvdc_sign_quirk = 1;
+  opt->force_slow_path = 0;
+  opt->compute_costs = 1;
+  opt->lm_lambda_min = 1e-12;
+  opt->lm_lambda_max = 1e12;
+}
+
+const char* sfmba_last_error(const sfmba_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
+
+int sfmba_nccl_unique_id(void* out128) {
+  if (!out128) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null id buffer");
+  std::string err;
+  const int rc = sfm_nccl_unique_id(out128, err);
+  if (rc) return sfm_set_error(nullptr, rc, err);
+  return SFMBA_OK;
+}
+
+int sfmba_create(sfmba_ctx** out, int device, int world_size, int rank, const void* nccl_unique_id) {
+  if (!out) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null out");
+  *out = nullptr;
+  if (world_size < 1 || rank < 0 || rank >= world_size)
+    return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "bad world_size / rank");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return sfm_set_error(nullptr, SFMBA_ERR_NO_DEVICE,
+                         "no CUDA device: libsfmba has no CPU fallback (sm_100a kernels only)");
+  }
+  if (device < 0 || device >= ndev) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "bad device index");
+  e = cudaSetDevice(device);
+  if (e != cudaSuccess) return sfm_check_cuda(nullptr, e, "cudaSetDevice");
+  sfmba_ctx* ctx = new (std::nothrow) sfmba_ctx();
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_CUDA, "out of host memory");
+  ctx->device = device;
+  ctx->world = world_size;
+  ctx->rank = rank;
+  e = cudaMallocHost(&ctx->pinned, PINNED_BYTES);
+  if (e != cudaSuccess) {
+    delete ctx;
+    return sfm_check_cuda(nullptr, e, "cudaMallocHost");
+  }
+  ctx->pinned_cap = PINNED_BYTES;
+  memset(ctx->pinned, 0, PINNED_BYTES);
+  cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+  if (world_size > 1) {
+    if (!nccl_unique_id) {
+      sfmba_destroy(ctx);
+      return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "world_size > 1 needs an ncclUniqueId");
+    }
+    const int rc = sfm_nccl_init(ctx, nccl_unique_id);
+    if (rc) {
+      g_last_error = ctx->err;
+      sfmba_destroy(ctx);
+      return rc;
+    }
+  }
+  *out = ctx;
+  return SFMBA_OK;
+}
+
+int sfmba_destroy(sfmba_ctx* ctx) {
+  if (!ctx) return SFMBA_OK;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  sfm_nccl_destroy(ctx);
+  for (auto& b : ctx->bufs) b.release();
+  for (auto& b : ctx->host_stage) b.release();
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+  return SFMBA_OK;
+}
+
+int sfmba_ba_solve(sfmba_ctx* ctx, const sfmba_problem* problem, const sfmba_options* opt, sfmba_result* result,
+                   void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  cudaSetDevice(ctx->device);
+  return sfm_ba_solve_device(ctx, problem, opt, result, (cudaStream_t)stream);
+}
+
+int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_options* opt, sfmba_result* result) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (!pr) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "null problem");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = ctx->own_stream;
+  sfmba_problem dp = *pr;
+  const size_t m = (size_t)std::max(pr->num_obs, 0), N = (size_t)std::max(pr->num_pts, 0),
+               V = (size_t)std::max(pr->num_cams, 0);
+  int rc;
+  float* d_uv;
+  int32_t *d_cam, *d_pt, *d_row;
+  double *d_kinv = nullptr, *d_cams, *d_pts;
+  if ((rc = stage_in(ctx, 0, pr->obs_uv, 2 * m, &d_uv, st))) return rc;
+  if ((rc = stage_in(ctx, 1, pr->obs_cam, m, &d_cam, st))) return rc;
+  if ((rc = stage_in(ctx, 2, pr->obs_pt, m, &d_pt, st))) return rc;
+  if ((rc = stage_in(ctx, 3, pr->pt_rowptr, N + 1, &d_row, st))) return rc;
+  if (pr->cam_kinv && (rc = stage_in(ctx, 4, pr->cam_kinv, 9 * V, &d_kinv, st))) return rc;
+  if ((rc = stage_in(ctx, 5, pr->cams, 7 * V, &d_cams, st))) return rc;
+  if ((rc = stage_in(ctx, 6, pr->pts, 3 * N, &d_pts, st))) return rc;
+  dp.obs_uv = d_uv;
+  dp.obs_cam = d_cam;
+  dp.obs_pt = d_pt;
+  dp.pt_rowptr = d_row;
+  dp.cam_kinv = pr->cam_kinv ? d_kinv : nullptr;
+  dp.cams = d_cams;
+  dp.pts = d_pts;
+  rc = sfm_ba_solve_device(ctx, &dp, opt, result, st);
+  if (rc != SFMBA_OK && rc != SFMBA_ERR_NUMERIC) return rc;
+  cudaMemcpyAsync(pr->cams, d_cams, 7 * V * sizeof(double), cudaMemcpyDeviceToHost, st);
+  if (N) cudaMemcpyAsync(pr->pts, d_pts, 3 * N * sizeof(double), cudaMemcpyDeviceToHost, st);
+  const int rc2 = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "D2H sync");
+  return rc2 ? rc2 : rc;
+}
+
+int sfmba_residual_jacobian(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk, float* out_r,
+                            float* out_jp, float* out_jx, double* out_r64, double* out_cost, void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  BaDev d;
+  int rc = sfm_setup_problem(ctx, problem, false, &d);
+  if (rc) return rc;
+  cudaMemsetAsync(d.sc, 0, sizeof(Scalars), st);
+  launch_cam_prepare(d, st, ctx->lc);
+  launch_k1(d, dvdc_sign_quirk != 0, out_r, out_jp, out_jx, out_r64, out_cost, st, ctx->lc);
+  return sfm_check_cuda(ctx, cudaGetLastError(), "k1 launch");
+}
+
+int sfmba_ba_cost(sfmba_ctx* ctx, const sfmba_problem* problem, double* host_cost, void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  BaDev d;
+  int rc = sfm_setup_problem(ctx, problem, false, &d);
+  if (rc) return rc;
+  cudaMemsetAsync(d.sc, 0, sizeof(Scalars), st);
+  launch_cam_prepare(d, st, ctx->lc);
+  double* dev_cost = d.tile_cost;   // k_sum_cost reads the partials before thread 0 writes slot 0
+  launch_cost(d, dev_cost, st, ctx->lc);
+  double* pin = reinterpret_cast<double*>(ctx->pinned);
+  cudaMemcpyAsync(pin, dev_cost, sizeof(double), cudaMemcpyDeviceToHost, st);
+  rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "cost sync");
+  if (rc) return rc;
+  if (host_cost) *host_cost = *pin;
+  return sfm_check_cuda(ctx, cudaGetLastError(), "cost kernels");
+}
+
+int sfmba_triangulate_refine_batched(sfmba_ctx* ctx, int32_t num_pts, int32_t num_obs, int32_t num_projs,
+                                     const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                                     const double* obs_uv, double* pts, double lambda, int32_t iterations,
+                                     uint32_t* host_flags, void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_pts < 0 || num_obs < 0 || num_projs < 0 || iterations < 0)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  void* fl = nullptr;
+  int rc = sfm_check_cuda(ctx, ctx->reserve(0, sizeof(Scalars), &fl), "cudaMalloc(flags)");
+  if (rc) return rc;
+  uint32_t* dflags = reinterpret_cast<uint32_t*>(fl);
+  cudaMemsetAsync(dflags, 0, sizeof(uint32_t), st);
+  launch_triangulate(num_pts, projs, rowptr, obs_view, obs_uv, pts, lambda, iterations, dflags, st, ctx->lc);
+  return read_flags(ctx, dflags, host_flags, st);
+}
+
+int sfmba_triangulate_refine_batched_host(sfmba_ctx* ctx, int32_t num_pts, int32_t num_obs, int32_t num_projs,
+                                          const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                                          const double* obs_uv, double* pts, double lambda, int32_t iterations,
+                                          uint32_t* host_flags) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_pts < 0 || num_obs < 0 || num_projs < 0)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = ctx->own_stream;
+  double *d_projs, *d_uv, *d_pts;
+  int32_t *d_row, *d_view;
+  int rc;
+  if ((rc = stage_in(ctx, 0, projs, (size_t)12 * num_projs, &d_projs, st))) return rc;
+  if ((rc = stage_in(ctx, 1, rowptr, (size_t)num_pts + 1, &d_row, st))) return rc;
+  if ((rc = stage_in(ctx, 2, obs_view, (size_t)num_obs, &d_view, st))) return rc;
+  if ((rc = stage_in(ctx, 3, obs_uv, (size_t)2 * num_obs, &d_uv, st))) return rc;
+  if ((rc = stage_in(ctx, 4, pts, (size_t)3 * num_pts, &d_pts, st))) return rc;
+  rc = sfmba_triangulate_refine_batched(ctx, num_pts, num_obs, num_projs, d_projs, d_row, d_view, d_uv, d_pts,
+                                        lambda, iterations, host_flags, st);
+  if (rc != SFMBA_OK && rc != SFMBA_ERR_NUMERIC) return rc;
+  if (num_pts) cudaMemcpyAsync(pts, d_pts, (size_t)3 * num_pts * sizeof(double), cudaMemcpyDeviceToHost, st);
+  const int rc2 = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "D2H sync");
+  return rc2 ? rc2 : rc;
+}
+
+int sfmba_pnp_refine_batched(sfmba_ctx* ctx, int32_t num_views, int32_t num_obs, const int32_t* rowptr,
+                             const double* obs_xy, const double* obs_X, double* rot, double* loc, double lambda,
+                             int32_t iterations, int32_t row_packing_quirk, int32_t dvdc_sign_quirk,
+                             uint32_t* host_flags, void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_views < 0 || num_obs < 0 || iterations < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  void* fl = nullptr;
+  int rc = sfm_check_cuda(ctx, ctx->reserve(0, sizeof(Scalars), &fl), "cudaMalloc(flags)");
+  if (rc) return rc;
+  uint32_t* dflags = reinterpret_cast<uint32_t*>(fl);
+  cudaMemsetAsync(dflags, 0, sizeof(uint32_t), st);
+  launch_pnp(num_views, rowptr, obs_xy, obs_X, rot, loc, lambda, iterations, row_packing_quirk != 0,
+             dvdc_sign_quirk != 0, dflags, st, ctx->lc);
+  return read_flags(ctx, dflags, host_flags, st);
+}
+
+int sfmba_pnp_refine_batched_host(sfmba_ctx* ctx, int32_t num_views, int32_t num_obs, const int32_t* rowptr,
+                                  const double* obs_xy, const double* obs_X, double* rot, double* loc,
+                                  double lambda, int32_t iterations, int32_t row_packing_quirk,
+                                  int32_t dvdc_sign_quirk, uint32_t* host_flags) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_views < 0 || num_obs < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = ctx->own_stream;
+  int32_t* d_row;
+  double *d_xy, *d_X, *d_rot, *d_loc;
+  int rc;
+  if ((rc = stage_in(ctx, 0, rowptr, (size_t)num_views + 1, &d_row, st))) return rc;
+  if ((rc = stage_in(ctx, 1, obs_xy, (size_t)2 * num_obs, &d_xy, st))) return rc;
+  if ((rc = stage_in(ctx, 2, obs_X, (size_t)3 * num_obs, &d_X, st))) return rc;
+  if ((rc = stage_in(ctx, 3, rot, (size_t)9 * num_views, &d_rot, st))) return rc;
+  if ((rc = stage_in(ctx, 4, loc, (size_t)3 * num_views, &d_loc, st))) return rc;
+  rc = sfmba_pnp_refine_batched(ctx, num_views, num_obs, d_row, d_xy, d_X, d_rot, d_loc, lambda, iterations,
+                                row_packing_quirk, dvdc_sign_quirk, host_flags, st);
+  if (rc != SFMBA_OK && rc != SFMBA_ERR_NUMERIC) return rc;
+  if (num_views) {
+    cudaMemcpyAsync(rot, d_rot, (size_t)9 * num_views * sizeof(double), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(loc, d_loc, (size_t)3 * num_views * sizeof(double), cudaMemcpyDeviceToHost, st);
+  }
+  const int rc2 = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "D2H sync");
+  return rc2 ? rc2 : rc;
+}
+
+int sfmba_build_visibility(sfmba_ctx* ctx, int32_t num_views, int32_t num_pts, const int64_t* diag,
+                           const int64_t* key_off, int32_t* obs_pt, int32_t* obs_cam, int32_t* obs_key,
+                           int32_t* pt_rowptr, int32_t* host_num_obs, void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (!key_off || num_views <= 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "bad key_off / num_views");
+  cudaSetDevice(ctx->device);
+  std::string err;
+  const int rc = build_visibility_device(num_views, num_pts, diag, key_off, key_off[num_views] - key_off[0], obs_pt,
+                                         obs_cam, obs_key, pt_rowptr, host_num_obs, (cudaStream_t)stream, ctx->lc,
+                                         err);
+  if (rc) return sfm_set_error(ctx, rc, err);
+  return SFMBA_OK;
+}
+
+int sfmba_profile_reset(sfmba_ctx* ctx) {
+  if (!ctx) return SFMBA_ERR_INVALID_ARG;
+  ctx->prof.clear();
+  return SFMBA_OK;
+}
+
+int sfmba_profile_enable(sfmba_ctx* ctx, int enable) {
+  if (!ctx) return SFMBA_ERR_INVALID_ARG;
+  ctx->profile = enable != 0;
+  return SFMBA_OK;
+}
+
+int sfmba_profile_get(sfmba_ctx* ctx, const char* name, double* ms_total, int64_t* launches) {
+  if (!ctx || !name) return SFMBA_ERR_INVALID_ARG;
+  auto it = ctx->prof.find(name);
+  if (it == ctx->prof.end()) {
+    if (ms_total) *ms_total = 0.0;
+    if (launches) *launches = 0;
+    return SFMBA_OK;
+  }
+  if (ms_total) *ms_total = it->second.ms;
+  if (launches) *launches = it->second.launches;
+  return SFMBA_OK;
+}
+
+int64_t sfmba_total_launches(const sfmba_ctx* ctx) { return ctx ? ctx->lc.launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,60 @@
+// Host-side context of libsfmba: device workspace arena, NCCL communicator (dlopen'ed), profiling.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "ba_internal.h"
+
+struct ProfileEntry {
+  double ms = 0.0;
+  int64_t launches = 0;
+};
+
+// Grow-only device buffer.
+struct DevBuf {
+  void* ptr = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes);
+  void release();
+  template <typename T>
+  T* as() const { return reinterpret_cast<T*>(ptr); }
+};
+
+struct sfmba_ctx {
+  int device = 0;
+  int world = 1;
+  int rank = 0;
+  std::string err;
+  sfmba::LaunchCounter lc;
+  // NCCL (only when world > 1)
+  void* nccl_lib = nullptr;
+  void* nccl_comm = nullptr;
+  // profiling
+  bool profile = false;
+  std::map<std::string, ProfileEntry> prof;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t phase_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  // workspace
+  std::vector<DevBuf> bufs;      // indexed by slot
+  DevBuf host_stage[12];         // device copies of host inputs for *_host entry points
+  void* pinned = nullptr;        // pinned staging for results/scalars
+  size_t pinned_cap = 0;
+  cudaStream_t own_stream = nullptr;
+
+  cudaError_t reserve(int slot, size_t bytes, void** out);
+};
+
+extern std::string g_last_error;
+
+int sfm_set_error(sfmba_ctx* ctx, int code, const std::string& msg);
+int sfm_check_cuda(sfmba_ctx* ctx, cudaError_t e, const char* what);
+
+// NCCL helpers (nccl_dl.cu)
+int sfm_nccl_unique_id(void* out128, std::string& err);
+int sfm_nccl_init(sfmba_ctx* ctx, const void* unique_id);
+int sfm_nccl_allreduce_f64(sfmba_ctx* ctx, double* buf, size_t count, cudaStream_t st);
+void sfm_nccl_destroy(sfmba_ctx* ctx);
