@@ -81,6 +81,7 @@ struct BaDev {
   double* cams_backup;                // [V][7]  adaptive mode
   double* pts_backup;                 // [N][3]
   Scalars* sc;
+  unsigned long long* host_sig;       // pinned, device-visible: (epoch << 32) | (pcg_iters << 1) | done
 };
 
 struct LaunchCounter {
@@ -106,12 +107,12 @@ void launch_cam_finalize(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
-void launch_pcg_init(const BaDev& d, double tol, cudaStream_t st, LaunchCounter& lc);
+void launch_pcg_init(const BaDev& d, unsigned epoch, cudaStream_t st, LaunchCounter& lc);
 void launch_matvec_a(const BaDev& d, const double* xvec, bool backsub, bool force_slow, cudaStream_t st,
                      LaunchCounter& lc);
 void launch_matvec_b(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_matvec_finalize(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
-void launch_pcg_step(const BaDev& d, double tol, int max_iter, cudaStream_t st, LaunchCounter& lc);
+void launch_pcg_step(const BaDev& d, double tol, int max_iter, unsigned epoch, cudaStream_t st, LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

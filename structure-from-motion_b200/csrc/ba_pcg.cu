@@ -188,7 +188,7 @@ __device__ __forceinline__ double blk7_row(const double* __restrict__ blk, const
 }
 
 // x = 0, r = g, z = Minv g, p = z, rz = r.z, gg = g.g          (single CTA)
-__global__ void __launch_bounds__(1024) k_pcg_init(BaDev d) {
+__global__ void __launch_bounds__(1024) k_pcg_init(BaDev d, unsigned epoch) {
   __shared__ double red[32];
   const int n = 7 * d.V;
   double rz = 0.0, gg = 0.0;
@@ -210,13 +210,15 @@ __global__ void __launch_bounds__(1024) k_pcg_init(BaDev d) {
     sc->gg = gg;
     sc->rr = gg;
     sc->pcg_iters = 0;
-    sc->pcg_done = (gg == 0.0 || !(gg == gg)) ? 1 : 0;
+    const int done = (gg == 0.0 || !(gg == gg)) ? 1 : 0;
+    sc->pcg_done = done;
     if (!(gg == gg)) atomicOr(&sc->flags, FLAG_NONFINITE);
+    if (d.host_sig) *(volatile unsigned long long*)d.host_sig = ((unsigned long long)epoch << 32) | (unsigned)done;
   }
 }
 
 // one PCG iteration after the matvec: q = A p - svec; alpha; x, r; z = Minv r; beta; p   (single CTA)
-__global__ void __launch_bounds__(1024) k_pcg_step(BaDev d, double tol, int max_iter) {
+__global__ void __launch_bounds__(1024) k_pcg_step(BaDev d, double tol, int max_iter, unsigned epoch) {
   __shared__ double red[32];
   Scalars* sc = d.sc;
   if (sc->pcg_done) return;
@@ -267,6 +269,9 @@ __global__ void __launch_bounds__(1024) k_pcg_step(BaDev d, double tol, int max_
       done = true;
     }
     if (done) sc->pcg_done = 1;
+    if (d.host_sig)
+      *(volatile unsigned long long*)d.host_sig =
+          ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
   }
 }
 
@@ -343,8 +348,8 @@ __global__ void k_lm_decide(BaDev d, double lam_min, double lam_max) {
   }
 }
 
-void launch_pcg_init(const BaDev& d, double, cudaStream_t st, LaunchCounter& lc) {
-  k_pcg_init<<<1, 1024, 0, st>>>(d);
+void launch_pcg_init(const BaDev& d, unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
+  k_pcg_init<<<1, 1024, 0, st>>>(d, epoch);
   lc.launches++;
 }
 
@@ -370,8 +375,8 @@ void launch_matvec_finalize(const BaDev& d, cudaStream_t st, LaunchCounter& lc) 
   lc.launches++;
 }
 
-void launch_pcg_step(const BaDev& d, double tol, int max_iter, cudaStream_t st, LaunchCounter& lc) {
-  k_pcg_step<<<1, 1024, 0, st>>>(d, tol, max_iter);
+void launch_pcg_step(const BaDev& d, double tol, int max_iter, unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
+  k_pcg_step<<<1, 1024, 0, st>>>(d, tol, max_iter, epoch);
   lc.launches++;
 }
 

@@ -97,6 +97,7 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
   d.kinv = pr->cam_kinv;
   d.cams = pr->cams;
   d.pts = pr->pts;
+  d.host_sig = ctx->world == 1 ? reinterpret_cast<unsigned long long*>(ctx->pinned) : nullptr;
   int rc;
 #define CARVE(slot, count, field) \
   if ((rc = carve(ctx, slot, (size_t)(count), &d.field)) != SFMBA_OK) return rc;
@@ -271,36 +272,76 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
                         cudaMemcpyDeviceToDevice, st);
     }
     launch_cam_blocks(d, st, lc);
-    launch_pcg_init(d, tol, st, lc);
+    const unsigned pcg_epoch = ++ctx->pcg_epoch;
+    launch_pcg_init(d, pcg_epoch, st, lc);
     pt.end(PH_CAMREDUCE, t0);
 
-    // ---- PCG: launch in batches; poll the device-side done flag one batch behind so the queue
-    // never drains (kernels of an already-converged solve exit at their first instruction)
+    // ---- PCG.  Kernels of an already-converged solve exit at their first instruction, so launching
+    // past convergence is harmless but not free.  One GPU: k_pcg_step publishes (epoch, iteration,
+    // done) in one 8-byte store to pinned host memory; the host keeps LOOKAHEAD iterations queued
+    // and reads that word without any synchronisation.  Several GPUs: every rank must issue the
+    // same number of collectives, so iterations go out in fixed batches and the (rank-identical)
+    // done flag of batch b is inspected after batch b+1 has been queued.
     t0 = pt.begin();
-    {
-      const int batch = 8;
-      int32_t* done_host = reinterpret_cast<int32_t*>(ctx->pinned);
+    auto launch_iteration = [&](unsigned epoch) -> int {
+      cudaEvent_t kb = pt.kbegin();
+      launch_matvec_a(d, d.p, false, slow, st, lc);
+      pt.kend("matvec_a", kb);
+      kb = pt.kbegin();
+      launch_matvec_b(d, st, lc);
+      pt.kend("matvec_b", kb);
+      launch_matvec_finalize(d, st, lc);
+      if (multi) {
+        const int r2 = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st);
+        if (r2 != 0) return r2;
+      }
+      kb = pt.kbegin();
+      launch_pcg_step(d, tol, max_iter, epoch, st, lc);
+      pt.kend("pcg_vec", kb);
+      return 0;
+    };
+    if (!multi) {
+      const int LOOKAHEAD = 2;
+      volatile unsigned long long* sig = reinterpret_cast<volatile unsigned long long*>(ctx->pinned);
+      int launched = 0;
+      bool done = false;
+      while (launched < max_iter && !done) {
+        if (launched >= LOOKAHEAD) {
+          // wait until iteration (launched - LOOKAHEAD) has finished, or the solve is done
+          long spins = 0;
+          for (;;) {
+            const unsigned long long w = *sig;
+            if ((unsigned)(w >> 32) == pcg_epoch) {
+              if (w & 1ull) { done = true; break; }
+              if ((int)((w & 0xffffffffull) >> 1) >= launched - LOOKAHEAD + 1) break;
+            }
+            if ((++spins & 0x3fff) == 0 && cudaStreamQuery(st) != cudaErrorNotReady) {
+              const unsigned long long w2 = *sig;     // stream drained: final state or an error
+              if ((unsigned)(w2 >> 32) == pcg_epoch && (w2 & 1ull)) done = true;
+              else if (!((unsigned)(w2 >> 32) == pcg_epoch &&
+                         (int)((w2 & 0xffffffffull) >> 1) >= launched - LOOKAHEAD + 1)) {
+                if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "pcg kernels")) != 0) return rc;
+                return sfm_set_error(ctx, SFMBA_ERR_CUDA, "PCG made no progress");
+              }
+              break;
+            }
+          }
+          if (done) break;
+        }
+        if ((rc = launch_iteration(pcg_epoch)) != 0) return rc;
+        ++launched;
+      }
+    } else {
+      const int batch = 4;
+      int32_t* done_host = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ctx->pinned) + 16);
       cudaEvent_t ev_prev = nullptr;
       bool have_prev = false;
-      int launched = 0;
-      done_host[0] = 0;
-      done_host[1] = 0;
-      int which = 0;
+      int launched = 0, which = 0;
+      done_host[0] = done_host[1] = 0;
       while (launched < max_iter) {
         const int nb = std::min(batch, max_iter - launched);
-        for (int k = 0; k < nb; ++k) {
-          cudaEvent_t kb = pt.kbegin();
-          launch_matvec_a(d, d.p, false, slow, st, lc);
-          pt.kend("matvec_a", kb);
-          kb = pt.kbegin();
-          launch_matvec_b(d, st, lc);
-          pt.kend("matvec_b", kb);
-          launch_matvec_finalize(d, st, lc);
-          if (multi && (rc = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st)) != 0) return rc;
-          kb = pt.kbegin();
-          launch_pcg_step(d, tol, max_iter, st, lc);
-          pt.kend("pcg_vec", kb);
-        }
+        for (int k = 0; k < nb; ++k)
+          if ((rc = launch_iteration(pcg_epoch)) != 0) return rc;
         launched += nb;
         cudaMemcpyAsync(&done_host[which], &d.sc->pcg_done, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
         cudaEvent_t ev = pt.get();

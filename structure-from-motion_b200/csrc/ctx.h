@@ -44,6 +44,7 @@ struct sfmba_ctx {
   void* pinned = nullptr;        // pinned staging for results/scalars
   size_t pinned_cap = 0;
   cudaStream_t own_stream = nullptr;
+  unsigned pcg_epoch = 0;        // id of the current PCG solve (see host_sig)
 
   cudaError_t reserve(int slot, size_t bytes, void** out);
 };

@@ -20,6 +20,9 @@ SHAPES = {
 }
 
 
+CAM_SPACING = 0.3      # distance between consecutive camera centres
+
+
 def _quat_mul(a, b):
     w1, x1, y1, z1 = a[..., 0], a[..., 1], a[..., 2], a[..., 3]
     w2, x2, y2, z2 = b[..., 0], b[..., 1], b[..., 2], b[..., 3]
@@ -78,7 +81,7 @@ def make_problem(V: int, N: int, m: int, seed: int = 0, noise_px: float = 0.5, f
         raise ValueError('need 2N <= m <= V*N')
     rng = np.random.default_rng(seed)
     i = np.arange(V, dtype=np.float64)
-    C = np.stack([i, 0.5 * np.sin(i / 50.0), 0.3 * np.cos(i / 70.0)], axis=1)
+    C = np.stack([CAM_SPACING * i, 0.5 * np.sin(i / 50.0), 0.3 * np.cos(i / 70.0)], axis=1)
     yaw = np.deg2rad(25.0) * np.sin(i / 100.0)
     pitch = np.deg2rad(5.0) * np.sin(i / 37.0)
     q = _quat_mul(_axis_angle_quat(np.tile([0.0, 1.0, 0.0], (V, 1)), yaw),
@@ -106,7 +109,7 @@ def make_problem(V: int, N: int, m: int, seed: int = 0, noise_px: float = 0.5, f
     obs_pt = np.repeat(np.arange(N, dtype=np.int64), L)
 
     # points in a slab in front of their centre camera; longer tracks sit farther away
-    local = np.stack([rng.uniform(-4, 4, N), rng.uniform(-3, 3, N), rng.uniform(5, 15, N) + 0.5 * L], axis=1)
+    local = np.stack([rng.uniform(-4, 4, N), rng.uniform(-3, 3, N), rng.uniform(6, 16, N) + 0.3 * L], axis=1)
     X = C[centre] + np.einsum('nij,nj->ni', R[centre], local)
 
     d = X[obs_pt] - C[obs_cam]
