@@ -1,29 +1,205 @@
-// Index construction for one BA problem: point-major tiles, the camera-major permutation and the
-// one-camera-per-chunk table.  Runs once per solve; everything stays on the device (no host sync).
+// Index construction for one BA problem (runs once per solve, on the device).
 //
-// The point-major CSR itself (obs_pt / obs_cam / pt_rowptr) is the bit-exact visibility index of
-// ba_processor.py:304-310 + key_tracker.py:198-204 and is an INPUT here.
+// Input: the point-major CSR (obs_pt / obs_cam / pt_rowptr) -- the bit-exact visibility index of
+// ba_processor.py:304-310 + key_tracker.py:198-204.  Output: groups, chunks, the camera-sorted and
+// lane-transposed observation records, run / segment tables and the camera -> segment-row CSR
+// (layout described in ba_internal.h).  Observations are normalised here once
+// (b = K^-1 [u,v,1]^T / z, ba_processor.py:339-342) and stored as f64 in the records.
 #include <cub/cub.cuh>
 
 #include "ba_internal.h"
+#include "sfmba_device.cuh"
 
 namespace sfmba {
 
-// tile t owns the points whose first observation lies in [t*TILE_OBS, (t+1)*TILE_OBS)
-__global__ void k_tile_bounds(BaDev d) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t > d.ntiles) return;
-  if (t == d.ntiles) {
-    d.tile_pt[t] = d.N;
+// group g owns the points j with rowptr[j] + POINT_WEIGHT * j in [g W, (g+1) W)
+__global__ void k_group_bounds(BaDev d) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g > d.G) return;
+  if (g == d.G) {
+    d.grp_pt[g] = d.N;
     return;
   }
-  const int target = t * TILE_OBS;
-  int lo = 0, hi = d.N;   // first j in [0,N] with rowptr[j] >= target
+  const long long target = (long long)g * GROUP_WEIGHT;
+  int lo = 0, hi = d.N;   // first j in [0,N] with weight prefix >= target
   while (lo < hi) {
     const int mid = (lo + hi) >> 1;
-    if (d.rowptr[mid] < target) lo = mid + 1; else hi = mid;
+    if ((long long)d.rowptr[mid] + (long long)POINT_WEIGHT * mid < target) lo = mid + 1; else hi = mid;
   }
-  d.tile_pt[t] = lo;
+  d.grp_pt[g] = lo;
+}
+
+constexpr int HASH_SLOTS = 4096;
+
+// chunks per group: one chunk unless the group overflows CHUNK_CAP or touches > SEG_CAP cameras
+__global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chunks) {
+  __shared__ int s_hash[HASH_SLOTS];
+  __shared__ int s_distinct;
+  const int g = blockIdx.x;
+  const int pt0 = d.grp_pt[g], pt1 = d.grp_pt[g + 1];
+  const int o0 = d.rowptr[pt0], o1 = d.rowptr[pt1];
+  const int L = o1 - o0;
+  int n;
+  if (L == 0) {
+    n = 0;
+  } else if (fine_chunks || L > CHUNK_CAP) {
+    n = (L + SEG_CAP - 1) / SEG_CAP;
+  } else {
+    for (int i = threadIdx.x; i < HASH_SLOTS; i += blockDim.x) s_hash[i] = -1;
+    if (threadIdx.x == 0) s_distinct = 0;
+    __syncthreads();
+    int mine = 0;
+    for (int i = threadIdx.x; i < L; i += blockDim.x) {
+      const int cam = d.obs_cam[o0 + i];
+      unsigned h = ((unsigned)cam * 2654435761u) >> 20;
+      for (;;) {
+        const int prev = atomicCAS(&s_hash[h & (HASH_SLOTS - 1)], -1, cam);
+        if (prev == -1) {
+          ++mine;
+          break;
+        }
+        if (prev == cam) break;
+        ++h;
+      }
+    }
+    if (mine) atomicAdd(&s_distinct, mine);
+    __syncthreads();
+    n = s_distinct <= SEG_CAP ? 1 : (L + SEG_CAP - 1) / SEG_CAP;
+    if (threadIdx.x == 0 && n == 1) {
+      const int K = (L + RUN_LANES - 1) / RUN_LANES;
+      atomicMax(&d.sc->max_chunk_len, L);
+      atomicMax(&d.sc->max_runs, (L + K - 1) / K + s_distinct);
+    }
+  }
+  if (threadIdx.x == 0) {
+    d.grp_nchunk[g] = n;
+    atomicMax(&d.sc->max_group_pts, pt1 - pt0);
+    if (n > 1) {
+      atomicMax(&d.sc->max_chunk_len, SEG_CAP);
+      atomicMax(&d.sc->max_runs, SEG_CAP);
+    }
+  }
+}
+
+__global__ void k_finish_scan(BaDev d) {
+  // grp_chunk holds the exclusive scan of grp_nchunk over [0, G); close it
+  const int total = d.G > 0 ? d.grp_chunk[d.G - 1] + d.grp_nchunk[d.G - 1] : 0;
+  d.grp_chunk[d.G] = total;
+  d.sc->num_chunks = total;
+}
+
+struct BuildSmem {
+  uint32_t key[CHUNK_CAP];
+  uint16_t seg[CHUNK_CAP];
+  uint16_t run[CHUNK_CAP];
+};
+
+// one CTA per group: sort each chunk by camera, emit records and tables
+__global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits) {
+  using Sort = cub::BlockRadixSort<uint32_t, RUN_LANES, CHUNK_K_MAX>;
+  using Scan = cub::BlockScan<int2, RUN_LANES>;
+  __shared__ union {
+    typename Sort::TempStorage sort;
+    typename Scan::TempStorage scan;
+  } tmp;
+  __shared__ BuildSmem s;
+  const int g = blockIdx.x;
+  const int pt0 = d.grp_pt[g], pt1 = d.grp_pt[g + 1];
+  const int c0 = d.grp_chunk[g], c1 = d.grp_chunk[g + 1];
+  const int o_begin = d.rowptr[pt0], o_end = d.rowptr[pt1];
+  const int tid = threadIdx.x;
+  for (int c = c0; c < c1; ++c) {
+    const int nc = c1 - c0;
+    const int obs0 = nc == 1 ? o_begin : o_begin + (c - c0) * SEG_CAP;
+    const int len = nc == 1 ? (o_end - o_begin) : min(SEG_CAP, o_end - obs0);
+    const int K = (len + RUN_LANES - 1) / RUN_LANES;
+    uint32_t keys[CHUNK_K_MAX];
+#pragma unroll
+    for (int i = 0; i < CHUNK_K_MAX; ++i) {
+      const int idx = tid * CHUNK_K_MAX + i;
+      keys[i] = idx < len ? (((uint32_t)d.obs_cam[obs0 + idx] << 11) | (uint32_t)idx) : 0xffffffffu;
+    }
+    Sort(tmp.sort).Sort(keys, 0, 11 + cam_bits);
+    // heads / run starts of my 10 consecutive sorted items
+    uint32_t prev_cam;
+#pragma unroll
+    for (int i = 0; i < CHUNK_K_MAX; ++i) s.key[tid * CHUNK_K_MAX + i] = keys[i];
+    __syncthreads();
+    prev_cam = tid == 0 ? 0xffffffffu : (s.key[tid * CHUNK_K_MAX - 1] >> 11);
+    int2 cnt = make_int2(0, 0);   // (heads, run starts) among my items
+    uint32_t flags = 0;           // bit i: head, bit 16+i: run start
+#pragma unroll
+    for (int i = 0; i < CHUNK_K_MAX; ++i) {
+      const int idx = tid * CHUNK_K_MAX + i;
+      if (idx < len) {
+        const uint32_t cam = keys[i] >> 11;
+        const bool head = idx == 0 || cam != prev_cam;
+        const bool rs = head || (idx % K) == 0;
+        if (head) {
+          ++cnt.x;
+          flags |= 1u << i;
+        }
+        if (rs) {
+          ++cnt.y;
+          flags |= 1u << (16 + i);
+        }
+        prev_cam = cam;
+      }
+    }
+    int2 excl, total;
+    Scan(tmp.scan).ExclusiveScan(cnt, excl, make_int2(0, 0),
+                                 [](const int2& a, const int2& b) { return make_int2(a.x + b.x, a.y + b.y); }, total);
+    int seg = excl.x - 1, run = excl.y - 1;
+#pragma unroll
+    for (int i = 0; i < CHUNK_K_MAX; ++i) {
+      const int idx = tid * CHUNK_K_MAX + i;
+      if (idx < len) {
+        if (flags & (1u << i)) ++seg;
+        if (flags & (1u << (16 + i))) ++run;
+        s.seg[idx] = (uint16_t)seg;
+        s.run[idx] = (uint16_t)run;
+        if (flags & (1u << i)) {
+          d.seg_cam[(size_t)c * SEG_CAP + seg] = (int32_t)(keys[i] >> 11);
+          d.seg_run0[(size_t)c * (SEG_CAP + 1) + seg] = (uint16_t)run;
+        }
+        if ((idx % K) == 0) d.lane_run0[(size_t)c * RUN_LANES + idx / K] = (uint16_t)run;
+      }
+    }
+    const int nseg = total.x, nruns = total.y;
+    for (int sidx = nseg + tid; sidx < SEG_CAP; sidx += RUN_LANES) d.seg_cam[(size_t)c * SEG_CAP + sidx] = d.V;
+    if (tid == 0) {
+      d.seg_run0[(size_t)c * (SEG_CAP + 1) + nseg] = (uint16_t)nruns;
+      ChunkInfo ci;
+      ci.obs0 = obs0;
+      ci.len = len;
+      ci.nseg = nseg;
+      ci.nruns = nruns;
+      d.chunk_info[c] = ci;
+    }
+    __syncthreads();
+    // records, lane-transposed: slot = k * RUN_LANES + lane  <->  sorted index lane * K + k
+    for (int slot = tid; slot < K * RUN_LANES; slot += RUN_LANES) {
+      const int k = slot / RUN_LANES, lane = slot % RUN_LANES;
+      const int idx = lane * K + k;
+      uint32_t ix = REC_INVALID;
+      double2 b = make_double2(0.0, 0.0);
+      if (k < K && idx < len && idx < (lane + 1) * K) {
+        const uint32_t key = s.key[idx];
+        const int pos = (int)(key & 2047u);
+        const int cam = (int)(key >> 11);
+        const int o = obs0 + pos;
+        const int ptl = d.obs_pt[o] - pt0;
+        const bool rs = idx == 0 || (idx % K) == 0 || s.seg[idx] != s.seg[idx - 1];
+        ix = (uint32_t)ptl | ((uint32_t)pos << 10) | ((uint32_t)s.seg[idx] << 21) | (rs ? REC_RUNSTART : 0u);
+        double bb[2];
+        normalise_obs(d.kinv ? d.kinv + 9 * (size_t)cam : nullptr, d.obs_uv[o], d.obs_uv[d.m + o], bb);
+        b = make_double2(bb[0], bb[1]);
+      }
+      d.rec_ix[(size_t)c * CHUNK_CAP + slot] = ix;
+      d.rec_b[(size_t)c * CHUNK_CAP + slot] = b;
+    }
+    __syncthreads();
+  }
 }
 
 __global__ void k_iota(int32_t* v, int n) {
@@ -31,98 +207,62 @@ __global__ void k_iota(int32_t* v, int n) {
   if (i < n) v[i] = i;
 }
 
-__global__ void k_invert_perm(const int32_t* __restrict__ perm, int32_t* __restrict__ inv, int n) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) inv[perm[i]] = i;
-}
-
-// cam_rowptr[c] = first camera-major slot whose camera is >= c (sorted keys)
-__global__ void k_cam_rowptr(const int32_t* __restrict__ sorted_cam, int m, int V, int32_t* __restrict__ cam_rowptr) {
+// camrow_ptr[c] = first sorted row whose camera is >= c
+__global__ void k_cam_rowptr(const int32_t* __restrict__ sorted_cam, int n, int V, int32_t* __restrict__ out) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c > V) return;
-  int lo = 0, hi = m;
+  int lo = 0, hi = n;
   while (lo < hi) {
     const int mid = (lo + hi) >> 1;
     if (sorted_cam[mid] < c) lo = mid + 1; else hi = mid;
   }
-  cam_rowptr[c] = lo;
+  out[c] = lo;
 }
 
-// Single block: exclusive scan of ceil(count/CHUNK_OBS) over cameras, then every camera writes its
-// chunk rows.  V is small (<= ~1e5), a sequential-by-block scan is plenty.
-__global__ void k_chunk_table(BaDev d) {
-  __shared__ int s_carry;
-  __shared__ int s_scan[1024];
-  if (threadIdx.x == 0) s_carry = 0;
-  __syncthreads();
-  for (int base = 0; base < d.V; base += blockDim.x) {
-    const int c = base + threadIdx.x;
-    int n = 0;
-    if (c < d.V) {
-      const int cnt = d.cam_rowptr[c + 1] - d.cam_rowptr[c];
-      n = (cnt + CHUNK_OBS - 1) / CHUNK_OBS;
-    }
-    s_scan[threadIdx.x] = n;
-    __syncthreads();
-    for (int off = 1; off < blockDim.x; off <<= 1) {   // Hillis-Steele inclusive scan
-      int v = 0;
-      if ((int)threadIdx.x >= off) v = s_scan[threadIdx.x - off];
-      __syncthreads();
-      s_scan[threadIdx.x] += v;
-      __syncthreads();
-    }
-    const int excl = s_carry + s_scan[threadIdx.x] - n;
-    if (c < d.V) {
-      d.cam_chunk_ptr[c] = excl;
-      const int beg = d.cam_rowptr[c], end = d.cam_rowptr[c + 1];
-      for (int k = 0; k < n; ++k) {
-        d.chunk_cam[excl + k] = c;
-        d.chunk_beg[excl + k] = beg + k * CHUNK_OBS;
-      }
-      (void)end;
-    }
-    __syncthreads();
-    if (threadIdx.x == blockDim.x - 1) s_carry += s_scan[threadIdx.x];
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) {
-    d.cam_chunk_ptr[d.V] = s_carry;
-    d.chunk_beg[s_carry] = d.m;
-    d.sc->num_chunks = s_carry;
-  }
-}
-
-static int key_bits(int V) {
+static int bits_for(int n) {   // bits needed to represent values in [0, n]
   int b = 1;
-  while ((1ll << b) < (long long)V) ++b;
+  while ((1ll << b) <= (long long)n) ++b;
   return b;
 }
 
-size_t index_sort_temp_bytes(int m, int V) {
-  size_t bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const int32_t*)nullptr, (int32_t*)nullptr,
-                                  (const int32_t*)nullptr, (int32_t*)nullptr, m > 0 ? m : 1, 0, key_bits(V));
-  return bytes;
+size_t index_temp_bytes(int G, int chunk_bound, int V) {
+  size_t a = 0, b = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, a, (const int32_t*)nullptr, (int32_t*)nullptr, G > 0 ? G : 1);
+  const int n = chunk_bound * SEG_CAP;
+  cub::DeviceRadixSort::SortPairs(nullptr, b, (const int32_t*)nullptr, (int32_t*)nullptr, (const int32_t*)nullptr,
+                                  (int32_t*)nullptr, n > 0 ? n : 1, 0, bits_for(V));
+  return a > b ? a : b;
 }
 
-void launch_build_index(const BaDev& d, void* sort_temp, size_t sort_temp_bytes, int32_t* sort_keys_out,
-                        int32_t* iota, cudaStream_t st, LaunchCounter& lc) {
-  k_tile_bounds<<<(d.ntiles + 1 + 255) / 256, 256, 0, st>>>(d);
+// phase 1: groups and chunk counts (the host then reads sc->num_chunks and the shape statistics)
+void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, cudaStream_t st,
+                        LaunchCounter& lc) {
+  k_group_bounds<<<(d.G + 1 + 255) / 256, 256, 0, st>>>(d);
   lc.launches++;
-  if (d.m > 0) {
-    k_iota<<<(d.m + 255) / 256, 256, 0, st>>>(iota, d.m);
-    lc.launches++;
-    // stable LSD radix sort by camera: ties keep point-major order, so the camera-major order (and
-    // with it every floating-point summation order downstream) is deterministic
-    cub::DeviceRadixSort::SortPairs(sort_temp, sort_temp_bytes, d.obs_cam, sort_keys_out, (const int32_t*)iota,
-                                    d.cm_perm, d.m, 0, key_bits(d.V), st);
-    lc.launches += 4;
-    k_invert_perm<<<(d.m + 255) / 256, 256, 0, st>>>(d.cm_perm, d.pm2cm, d.m);
+  if (d.G > 0) {
+    k_group_count<<<d.G, RUN_LANES, 0, st>>>(d, fine_chunks ? 1 : 0);
+    cub::DeviceScan::ExclusiveSum(temp, temp_bytes, d.grp_nchunk, d.grp_chunk, d.G, st);
+    lc.launches += 2;
+  }
+  k_finish_scan<<<1, 1, 0, st>>>(d);
+  lc.launches++;
+}
+
+// phase 2: records, tables and the camera CSR (chunk arrays allocated for `nchunks`)
+void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_bytes, int32_t* sort_keys_out,
+                        int32_t* iota, cudaStream_t st, LaunchCounter& lc) {
+  if (d.G > 0 && nchunks > 0) {
+    k_chunk_build<<<d.G, RUN_LANES, 0, st>>>(d, bits_for(d.V > 0 ? d.V - 1 : 0));
     lc.launches++;
   }
-  k_cam_rowptr<<<(d.V + 1 + 255) / 256, 256, 0, st>>>(sort_keys_out, d.m, d.V, d.cam_rowptr);
-  lc.launches++;
-  k_chunk_table<<<1, 1024, 0, st>>>(d);
+  const int n = nchunks * SEG_CAP;
+  if (n > 0) {
+    k_iota<<<(n + 255) / 256, 256, 0, st>>>(iota, n);
+    cub::DeviceRadixSort::SortPairs(temp, temp_bytes, (const int32_t*)d.seg_cam, sort_keys_out, (const int32_t*)iota,
+                                    d.camrow_idx, n, 0, bits_for(d.V), st);
+    lc.launches += 4;
+  }
+  k_cam_rowptr<<<(d.V + 1 + 255) / 256, 256, 0, st>>>(sort_keys_out, n, d.V, d.camrow_ptr);
   lc.launches++;
 }
 

@@ -1,4 +1,18 @@
 // Internal (non-ABI) declarations shared by the translation units of libsfmba.
+//
+// Engine layout (v1, matrix-free):
+//   group  = consecutive points whose weight prefix (observations + 2 per point) falls into one
+//            GROUP_WEIGHT bucket; one CTA owns one group in every tile kernel.
+//   chunk  = <= CHUNK_CAP consecutive (point-major) observations of a group.  A group is one chunk
+//            unless it overflows (a very long track) or touches more than SEG_CAP cameras, in which
+//            case it is cut into SEG_CAP-observation chunks.
+//   Inside a chunk the observations are sorted by camera ("segments"); lane r of the CTA walks the
+//   K = ceil(len / RUN_LANES) sorted observations [r K, (r+1) K).  A maximal same-camera stretch of
+//   one lane is a "run": camera constants live in registers for the whole run and the camera-side
+//   sums of a run accumulate in registers, so the per-observation work is pure FP64 arithmetic.
+//   Records are stored lane-transposed ([k][lane]) so every load is coalesced.
+//   Camera-side sums: run -> (shared memory) -> segment row in HBM -> per-camera sum, all in a
+//   fixed order (bitwise reproducible, no atomics on data).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -9,12 +23,25 @@
 
 namespace sfmba {
 
-constexpr int CAMTAB_STRIDE = 16;  // doubles per camera-table row: R[9] row-major, C[3], qj[4]
-constexpr int TILE_OBS = 256;      // observations per point-major tile (by first observation)
-constexpr int TILE_CAP = 512;      // shared-memory slots of the fast path (tile + straddling tail)
-constexpr int TILE_THREADS = 256;
-constexpr int CHUNK_OBS = 256;     // observations per camera-major chunk (one camera per chunk)
-constexpr int CAM_ACC = 64;        // doubles per camera accumulator row: A(28) S(28) g(7) pad(1)
+constexpr int CAMTAB_STRIDE = 16;   // doubles per camera-table row: R[9] row-major, C[3], qj[4]
+constexpr int CAMIT_STRIDE = 16;    // doubles per PCG-iteration camera row: E[9], w[3], wq, pad[3]
+constexpr int RUN_LANES = 128;      // threads per tile CTA = lanes per chunk
+constexpr int CHUNK_K_MAX = 10;     // sorted observations per lane
+constexpr int CHUNK_CAP = RUN_LANES * CHUNK_K_MAX;   // 1280 observations per chunk
+constexpr int GROUP_WEIGHT = 1024;  // bucket width of (rowptr[j] + 2 j)
+constexpr int POINT_WEIGHT = 2;
+constexpr int GROUP_PT_CAP = GROUP_WEIGHT / POINT_WEIGHT;   // <= 512 points per group
+constexpr int SEG_CAP = 128;        // distinct cameras per chunk
+constexpr int RUN_CAP = RUN_LANES + SEG_CAP;            // runs per chunk (< 256)
+constexpr int CAM_ACC = 64;         // doubles per camera accumulator row: A(28) S(28) g(7) pad(1)
+constexpr int MV_ACC = 12;          // doubles per matvec row: T[3][3] (c~ d^T), s[3]
+
+// record index word: ptl[0:10) pos[10:21) seg[21:28) runstart[28]
+constexpr uint32_t REC_INVALID = 0xffffffffu;
+constexpr uint32_t REC_RUNSTART = 1u << 28;
+__host__ __device__ __forceinline__ uint32_t rec_ptl(uint32_t ix) { return ix & 1023u; }
+__host__ __device__ __forceinline__ uint32_t rec_pos(uint32_t ix) { return (ix >> 10) & 2047u; }
+__host__ __device__ __forceinline__ uint32_t rec_seg(uint32_t ix) { return (ix >> 21) & 127u; }
 
 // Device-resident scalars of one solve (one allocation, zeroed per call).
 struct Scalars {
@@ -31,14 +58,26 @@ struct Scalars {
   int32_t lm_accepted;   // number of accepted steps
   int32_t lm_last_accepted;
   uint32_t flags;
-  int32_t pad;
+  int32_t max_chunk_len; // index statistics (read back once per solve to size shared memory)
+  int32_t max_runs;
+  int32_t max_group_pts;
+  uint32_t ticket_a;     // "last block done" tickets of the multi-CTA PCG kernels
+  uint32_t ticket_b;
   double costs[SFMBA_MAX_COST_HISTORY];
+};
+
+struct ChunkInfo {
+  int32_t obs0;          // first (point-major) observation
+  int32_t len;           // observations
+  int32_t nseg;          // distinct cameras
+  int32_t nruns;
 };
 
 // Device view of one BA problem plus its workspace.  Plain pointers so kernels take it by value.
 struct BaDev {
-  int V, N, m, mp;                    // mp: SoA row stride (m rounded up to 32)
-  int ntiles, nchunk_bound;
+  int V, N, m;
+  int G;                              // groups
+  int chunk_bound;                    // allocated chunks
   // inputs
   const float* obs_uv;
   const int32_t* obs_cam;
@@ -48,36 +87,38 @@ struct BaDev {
   double* cams;
   double* pts;
   // index
-  int32_t* tile_pt;                   // [ntiles+1]
-  int32_t* cm_perm;                   // [m] camera-major slot -> point-major observation
-  int32_t* pm2cm;                     // [m] inverse
-  int32_t* cam_rowptr;                // [V+1] offsets into camera-major order
-  int32_t* cam_chunk_ptr;             // [V+1] offsets into the chunk table
-  int32_t* chunk_cam;                 // [nchunk_bound]
-  int32_t* chunk_beg;                 // [nchunk_bound+1] camera-major slot range of each chunk
+  int32_t* grp_pt;                    // [G+1]
+  int32_t* grp_nchunk;                // [G]   chunks per group (scan input)
+  int32_t* grp_chunk;                 // [G+1] first chunk of each group
+  ChunkInfo* chunk_info;              // [chunk_bound]
+  double2* rec_b;                     // [chunk_bound][CHUNK_CAP] normalised observation, lane-transposed
+  uint32_t* rec_ix;                   // [chunk_bound][CHUNK_CAP]
+  int32_t* seg_cam;                   // [chunk_bound][SEG_CAP]   camera of each segment (V = unused)
+  uint16_t* seg_run0;                 // [chunk_bound][SEG_CAP+1] first run of each segment
+  uint16_t* lane_run0;                // [chunk_bound][RUN_LANES] first run of each lane
+  int32_t* camrow_ptr;                // [V+1]  CSR: camera -> segment rows
+  int32_t* camrow_idx;                // [chunk_bound*SEG_CAP] row ids sorted by camera
   // linearisation
   double* camtab;                     // [V][16]
-  float* jp_pm;                       // [14][mp] point-major SoA
-  float* jx_pm;                       // [6][mp]
-  float4* rec_cm;                     // [m][4]: Jp(14) rho(2), camera-major AoS (64 B records)
-  float4* y_cm;                       // [m]: (yuu, yuv, yvv, 0), Y = Jx D^-1 Jx^T
-  float* dinv;                        // [6][N] symmetric packing 00 01 02 11 12 22
-  float* vj;                          // [3][N] D^-1 e_x
-  double* tile_cost;                  // [ntiles]
-  // camera side
-  double* chunk_acc;                  // [nchunk_bound][CAM_ACC]
+  double* dinv;                       // [6][N] symmetric packing 00 01 02 11 12 22
+  double* vj;                         // [3][N] D^-1 e_x
+  double* grp_cost;                   // [max(G, cost grid)]
+  double* part64;                     // [chunk_bound*SEG_CAP][CAM_ACC] segment rows of the Gram sums
   double* cam_acc;                    // [V][CAM_ACC] (+ 8 trailing doubles: local cost at [V*CAM_ACC])
   double* ablk;                       // [V][49] A_i + lambda I
   double* minv;                       // [V][49] block-Jacobi inverse of S_ii
   // PCG
-  double2* b_cm;                      // [m]
-  double* chunk_y;                    // [nchunk_bound][8]
+  double* camit;                      // [V][16]
+  double* part12;                     // [chunk_bound*SEG_CAP][MV_ACC]
   double* svec;                       // [7V] sum_j W D^-1 W^T p (local; allreduced when world > 1)
   double* x;                          // [7V] solution (delta p)
   double* r;
   double* z;
   double* p;
+  double* q;                          // [7V] S p
   double* gvec;                       // [7V] right-hand side
+  double* red_a;                      // [<= 1024] per-block partials of the PCG dot products
+  double* red_b;                      // [<= 2048]
   double* cams_backup;                // [V][7]  adaptive mode
   double* pts_backup;                 // [N][3]
   Scalars* sc;
@@ -88,31 +129,46 @@ struct LaunchCounter {
   int64_t launches = 0;
 };
 
+struct TileShape {                    // from the index statistics; sizes dynamic shared memory
+  int max_chunk_len = CHUNK_CAP;
+  int max_runs = RUN_CAP;
+  int max_group_pts = GROUP_PT_CAP;
+};
+
 // ---- index (ba_index.cu) ------------------------------------------------------------------------
-size_t index_sort_temp_bytes(int m, int V);
-void launch_build_index(const BaDev& d, void* sort_temp, size_t sort_temp_bytes, int32_t* sort_keys_out,
+size_t index_temp_bytes(int G, int chunk_bound, int V);
+// phase 1: groups + chunk counts + shape statistics in sc (host reads them back once)
+void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, cudaStream_t st,
+                        LaunchCounter& lc);
+// phase 2: records, run / segment tables, camera -> segment-row CSR
+void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_bytes, int32_t* sort_keys_out,
                         int32_t* iota, cudaStream_t st, LaunchCounter& lc);
 
 // ---- linearisation (ba_linearize.cu) ------------------------------------------------------------
 void launch_cam_prepare(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
-void launch_linearize(const BaDev& d, bool dvdc_quirk, bool force_slow, int cost_slot, cudaStream_t st,
-                      LaunchCounter& lc);
-void launch_cost(const BaDev& d, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc);
+// per-point Schur elimination: D_j^-1, v_j, cost -> sc->costs[cost_slot] / cost_cur
+void launch_point(const BaDev& d, const TileShape& ts, int cost_slot, cudaStream_t st, LaunchCounter& lc);
+// cost only at the current parameters -> sc->cost_new and (optionally) *out_cost_dev
+void launch_cost_tiles(const BaDev& d, const TileShape& ts, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc);
+void launch_cost(const BaDev& d, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc);   // index-free
 void launch_k1(const BaDev& d, bool dvdc_quirk, float* out_r, float* out_jp, float* out_jx, double* out_r64,
                double* out_cost, cudaStream_t st, LaunchCounter& lc);
 
 // ---- camera-side reduction (ba_schur.cu) --------------------------------------------------------
-void launch_camreduce(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
-void launch_cam_finalize(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // chunk_acc -> cam_acc
+void launch_camgram(const BaDev& d, const TileShape& ts, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
+void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);       // part64 -> cam_acc
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
 void launch_pcg_init(const BaDev& d, unsigned epoch, cudaStream_t st, LaunchCounter& lc);
-void launch_matvec_a(const BaDev& d, const double* xvec, bool backsub, bool force_slow, cudaStream_t st,
+void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool dvdc_quirk, cudaStream_t st,
                      LaunchCounter& lc);
-void launch_matvec_b(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
-void launch_matvec_finalize(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
-void launch_pcg_step(const BaDev& d, double tol, int max_iter, unsigned epoch, cudaStream_t st, LaunchCounter& lc);
+void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
+                   LaunchCounter& lc);
+// part12 -> svec (y); when `fuse_apq`, also q = A p - y and alpha (single GPU)
+void launch_camsum12(const BaDev& d, bool fuse_apq, cudaStream_t st, LaunchCounter& lc);
+void launch_apq(const BaDev& d, cudaStream_t st, LaunchCounter& lc);            // after the allreduce of svec
+void launch_pcg_update(const BaDev& d, double tol, int max_iter, unsigned epoch, cudaStream_t st, LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

@@ -1,17 +1,15 @@
-// Linearisation: camera table, fused residual/Jacobian + per-point Schur elimination (K1+K2a), the
-// stand-alone residual/Jacobian kernel (K1) and the cost pass.
+// Linearisation, point side: camera table, per-point Schur elimination (K2a: D_j, D_j^-1, v_j and the
+// cost), the index-free cost pass and the stand-alone residual/Jacobian kernel (K1).
 //
-// Reference: ba_processor.py:304-363 (per point: gather visible views, J_p, J_x, b, f, D_j += J_x^T J_x,
-// D_j += lambda I, D_j^-1).  Here one CTA owns a point-major tile of ~256 observations:
-//   P1  one lane per observation: r (f64), J_p, J_x; J written point-major (SoA, coalesced)
-//   P2  one thread per point: D_j, e_x,j in f64 from shared memory, closed-form 3x3 inverse,
-//       v_j = D^-1 e_x; per observation rho = r - J_x v_j and Y = J_x D^-1 J_x^T
-//   P3  one lane per observation: the 64-byte camera-major record [J_p | rho] and Y are scattered
-//       to their camera-major slot (full-sector writes)
-// Tiles whose observation range does not fit the shared-memory slots (a track longer than ~256)
-// take a block-cooperative path that handles one point at a time.
+// Reference: ba_processor.py:304-363 (per point: gather visible views, J_x, b, f, D_j += J_x^T J_x,
+// D_j += lambda I, D_j^-1).  k_point walks a group's camera-sorted records (ba_internal.h, tile.cuh):
+// each lane evaluates r and J_x of its observations in f64 with the camera constants in registers,
+// scatters the 9 per-observation terms of (D_j, e_x,j) to shared-memory slots at their point-major
+// position, and one thread per point then sums its slots in order and solves the 3x3 block in
+// closed form.  Nothing per-observation is written to HBM.
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
+#include "tile.cuh"
 
 namespace sfmba {
 
@@ -34,217 +32,113 @@ __global__ void k_cam_prepare(BaDev d) {
   for (int i = 0; i < 4; ++i) t[12 + i] = qj[i];
 }
 
-struct LinSmem {
-  float jx[6][TILE_CAP];
-  double r[2][TILE_CAP];
-  float out[5][TILE_CAP];    // rho0 rho1 yuu yuv yvv
-  float tail[2][TILE_CAP];   // Jp[12], Jp[13] (last float4 of the camera-major record)
-  double red[32];
-  double pt[16];             // slow path broadcast
-};
-
-__device__ __forceinline__ void load_obs(const BaDev& d, int o, int& cam, double X[3], double b[2]) {
-  cam = d.obs_cam[o];
-  const int j = d.obs_pt[o];
-  const double* p = d.pts + 3 * (size_t)j;
-  X[0] = p[0];
-  X[1] = p[1];
-  X[2] = p[2];
-  normalise_obs(d.kinv ? d.kinv + 9 * (size_t)cam : nullptr, d.obs_uv[o], d.obs_uv[d.m + o], b);
-}
-
-__device__ __forceinline__ void store_pm(const BaDev& d, int o, const double Jp[14], const double Jx[6]) {
-#pragma unroll
-  for (int e = 0; e < 14; ++e) d.jp_pm[(size_t)e * d.mp + o] = (float)Jp[e];
-#pragma unroll
-  for (int e = 0; e < 6; ++e) d.jx_pm[(size_t)e * d.mp + o] = (float)Jx[e];
-}
-
-// per-point epilogue shared by both paths: D (with lambda) -> Dinv, v; writes dinv/vj
-__device__ __forceinline__ bool point_solve(const BaDev& d, int j, double D[6], const double ex[3], double lam,
-                                            double Dinv[6], double v[3]) {
-  D[0] += lam;
-  D[3] += lam;
-  D[5] += lam;
-  const bool ok = sym3_inverse(D, Dinv);
-  // the stored (f32) inverse is the one every later kernel uses, so v and rho use it as well
-#pragma unroll
-  for (int e = 0; e < 6; ++e) {
-    const float f = (float)Dinv[e];
-    d.dinv[(size_t)e * d.N + j] = f;
-    Dinv[e] = (double)f;
-  }
-  sym3_mul(Dinv, ex, v);
-#pragma unroll
-  for (int e = 0; e < 3; ++e) {
-    const float f = (float)v[e];
-    d.vj[(size_t)e * d.N + j] = f;
-    v[e] = (double)f;
-  }
-  return ok;
-}
-
-// rho = r - Jx v ; Y = Jx Dinv Jx^T (Jx taken as the stored f32 values)
-__device__ __forceinline__ void obs_schur_terms(const double jx[6], const double r[2], const double Dinv[6],
-                                                const double v[3], float out[5]) {
-  out[0] = (float)(r[0] - (jx[0] * v[0] + jx[1] * v[1] + jx[2] * v[2]));
-  out[1] = (float)(r[1] - (jx[3] * v[0] + jx[4] * v[1] + jx[5] * v[2]));
-  double t0[3], t1[3];
-  sym3_mul(Dinv, jx, t0);
-  sym3_mul(Dinv, jx + 3, t1);
-  out[2] = (float)(jx[0] * t0[0] + jx[1] * t0[1] + jx[2] * t0[2]);
-  out[3] = (float)(jx[0] * t1[0] + jx[1] * t1[1] + jx[2] * t1[2]);
-  out[4] = (float)(jx[3] * t1[0] + jx[4] * t1[1] + jx[5] * t1[2]);
-}
-
-__device__ __forceinline__ void store_cm(const BaDev& d, int o, const float jp[14], const float out[5]) {
-  const int slot = d.pm2cm[o];
-  float4* rec = d.rec_cm + 4 * (size_t)slot;
-  rec[0] = make_float4(jp[0], jp[1], jp[2], jp[3]);
-  rec[1] = make_float4(jp[4], jp[5], jp[6], jp[7]);
-  rec[2] = make_float4(jp[8], jp[9], jp[10], jp[11]);
-  rec[3] = make_float4(jp[12], jp[13], out[0], out[1]);
-  d.y_cm[slot] = make_float4(out[2], out[3], out[4], 0.f);
-}
-
-__global__ void __launch_bounds__(TILE_THREADS) k_linearize(BaDev d, int dvdc_quirk, int force_slow) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  LinSmem& s = *reinterpret_cast<LinSmem*>(smem_raw);
-  const int t = blockIdx.x;
-  const int j0 = d.tile_pt[t], j1 = d.tile_pt[t + 1];
-  const int o0 = d.rowptr[j0], o1 = d.rowptr[j1];
-  const int L = o1 - o0;
-  const double lam = d.sc->lambda;
+// ---- K2a: per-point Schur elimination ------------------------------------------------------------
+// dynamic shared memory: Xs[3][pt_cap] | pacc[9][pt_cap] | slots[9][slot_cap] | red[32]
+template <bool COST_ONLY>
+__global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, int slot_cap, int pt_cap) {
+  extern __shared__ __align__(16) double smem[];
+  double* Xs = smem;
+  double* pacc = Xs + 3 * pt_cap;
+  double* slots = COST_ONLY ? pacc : pacc + 9 * pt_cap;
+  double* red = COST_ONLY ? pacc : slots + 9 * slot_cap;
+  const GroupRange gr = group_range(d, blockIdx.x);
   const int tid = threadIdx.x;
+  stage_points(d, gr, Xs, pt_cap);
+  if (!COST_ONLY) {
+    for (int i = tid; i < 9 * pt_cap; i += RUN_LANES) pacc[i] = 0.0;
+  }
+  __syncthreads();
   double cost = 0.0;
   uint32_t flags = 0;
-
-  if (L <= TILE_CAP && !force_slow) {
-    // ---- P1: one lane per observation; first three float4 of the camera-major record go out now
-    for (int sidx = tid; sidx < L; sidx += TILE_THREADS) {
-      const int o = o0 + sidx;
-      int cam;
-      double X[3], b[2], r[2], Jp[14], Jx[6];
-      load_obs(d, o, cam, X, b);
-      if (!eval_obs<true>(d.camtab + (size_t)CAMTAB_STRIDE * cam, X, b, dvdc_quirk != 0, r, Jp, Jx))
-        flags |= FLAG_DEPTH_ZERO;
-      store_pm(d, o, Jp, Jx);
-      cost += r[0] * r[0] + r[1] * r[1];
-#pragma unroll
-      for (int e = 0; e < 6; ++e) s.jx[e][sidx] = (float)Jx[e];
-      s.r[0][sidx] = r[0];
-      s.r[1][sidx] = r[1];
-      s.tail[0][sidx] = (float)Jp[12];
-      s.tail[1][sidx] = (float)Jp[13];
-      float4* rec = d.rec_cm + 4 * (size_t)d.pm2cm[o];
-      rec[0] = make_float4((float)Jp[0], (float)Jp[1], (float)Jp[2], (float)Jp[3]);
-      rec[1] = make_float4((float)Jp[4], (float)Jp[5], (float)Jp[6], (float)Jp[7]);
-      rec[2] = make_float4((float)Jp[8], (float)Jp[9], (float)Jp[10], (float)Jp[11]);
-    }
-    __syncthreads();
-    // ---- P2: one thread per point
-    for (int j = j0 + tid; j < j1; j += TILE_THREADS) {
-      const int a = d.rowptr[j] - o0, e = d.rowptr[j + 1] - o0;
-      double D[6] = {0, 0, 0, 0, 0, 0}, ex[3] = {0, 0, 0};
-      for (int k = a; k < e; ++k) {
-        const double x0 = s.jx[0][k], x1 = s.jx[1][k], x2 = s.jx[2][k];
-        const double y0 = s.jx[3][k], y1 = s.jx[4][k], y2 = s.jx[5][k];
-        const double r0 = s.r[0][k], r1 = s.r[1][k];
-        D[0] += x0 * x0 + y0 * y0;
-        D[1] += x0 * x1 + y0 * y1;
-        D[2] += x0 * x2 + y0 * y2;
-        D[3] += x1 * x1 + y1 * y1;
-        D[4] += x1 * x2 + y1 * y2;
-        D[5] += x2 * x2 + y2 * y2;
-        ex[0] += x0 * r0 + y0 * r1;
-        ex[1] += x1 * r0 + y1 * r1;
-        ex[2] += x2 * r0 + y2 * r1;
+  for (int c = gr.c0; c < gr.c1; ++c) {
+    const ChunkInfo ci = d.chunk_info[c];
+    const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
+    const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
+    const double2* bp = d.rec_b + (size_t)c * CHUNK_CAP + tid;
+    const int32_t* segcam = d.seg_cam + (size_t)c * SEG_CAP;
+    double R[9], C[3];
+    uint32_t ix = ixp[0];
+    double2 b = bp[0];
+    for (int k = 0; k < K && ix != REC_INVALID; ++k) {
+      const uint32_t ix_cur = ix;
+      const double2 b_cur = b;
+      if (k + 1 < K) {                                   // prefetch the next record
+        ix = ixp[(k + 1) * RUN_LANES];
+        b = bp[(k + 1) * RUN_LANES];
+      } else {
+        ix = REC_INVALID;
       }
-      double Dinv[6], v[3];
-      if (!point_solve(d, j, D, ex, lam, Dinv, v)) flags |= FLAG_SINGULAR;
-      for (int k = a; k < e; ++k) {
-        const double jx[6] = {s.jx[0][k], s.jx[1][k], s.jx[2][k], s.jx[3][k], s.jx[4][k], s.jx[5][k]};
-        const double r[2] = {s.r[0][k], s.r[1][k]};
-        float out[5];
-        obs_schur_terms(jx, r, Dinv, v, out);
-#pragma unroll
-        for (int q = 0; q < 5; ++q) s.out[q][k] = out[q];
+      if (ix_cur & REC_RUNSTART) load_cam_rc(d.camtab, segcam[rec_seg(ix_cur)], R, C);
+      const int ptl = rec_ptl(ix_cur);
+      const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
+      if (!pr.ok) flags |= FLAG_DEPTH_ZERO;
+      const double r0 = b_cur.x - pr.u, r1 = b_cur.y - pr.v;
+      cost += r0 * r0 + r1 * r1;
+      if (!COST_ONLY) {
+        // J_x rows (triangulation_processor.py:259-271 with the K-free projection)
+        const double x0 = (R[0] - pr.u * R[2]) * pr.iw, x1 = (R[3] - pr.u * R[5]) * pr.iw,
+                     x2 = (R[6] - pr.u * R[8]) * pr.iw;
+        const double y0 = (R[1] - pr.v * R[2]) * pr.iw, y1 = (R[4] - pr.v * R[5]) * pr.iw,
+                     y2 = (R[7] - pr.v * R[8]) * pr.iw;
+        double* s = slots + rec_pos(ix_cur);
+        s[0 * slot_cap] = x0 * x0 + y0 * y0;
+        s[1 * slot_cap] = x0 * x1 + y0 * y1;
+        s[2 * slot_cap] = x0 * x2 + y0 * y2;
+        s[3 * slot_cap] = x1 * x1 + y1 * y1;
+        s[4 * slot_cap] = x1 * x2 + y1 * y2;
+        s[5 * slot_cap] = x2 * x2 + y2 * y2;
+        s[6 * slot_cap] = x0 * r0 + y0 * r1;
+        s[7 * slot_cap] = x1 * r0 + y1 * r1;
+        s[8 * slot_cap] = x2 * r0 + y2 * r1;
       }
     }
-    __syncthreads();
-    // ---- P3: finish the camera-major record
-    for (int sidx = tid; sidx < L; sidx += TILE_THREADS) {
-      const int slot = d.pm2cm[o0 + sidx];
-      d.rec_cm[4 * (size_t)slot + 3] = make_float4(s.tail[0][sidx], s.tail[1][sidx], s.out[0][sidx], s.out[1][sidx]);
-      d.y_cm[slot] = make_float4(s.out[2][sidx], s.out[3][sidx], s.out[4][sidx], 0.f);
-    }
-  } else {
-    // ---- long-track path: the block handles one point at a time
-    for (int j = j0; j < j1; ++j) {
-      const int a = d.rowptr[j], e = d.rowptr[j + 1];
-      double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-      for (int o = a + tid; o < e; o += TILE_THREADS) {
-        int cam;
-        double X[3], b[2], r[2], Jp[14], Jx[6];
-        load_obs(d, o, cam, X, b);
-        if (!eval_obs<true>(d.camtab + (size_t)CAMTAB_STRIDE * cam, X, b, dvdc_quirk != 0, r, Jp, Jx))
-          flags |= FLAG_DEPTH_ZERO;
-        cost += r[0] * r[0] + r[1] * r[1];
-        double jx[6];
-#pragma unroll
-        for (int q = 0; q < 6; ++q) jx[q] = (double)(float)Jx[q];
-        acc[0] += jx[0] * jx[0] + jx[3] * jx[3];
-        acc[1] += jx[0] * jx[1] + jx[3] * jx[4];
-        acc[2] += jx[0] * jx[2] + jx[3] * jx[5];
-        acc[3] += jx[1] * jx[1] + jx[4] * jx[4];
-        acc[4] += jx[1] * jx[2] + jx[4] * jx[5];
-        acc[5] += jx[2] * jx[2] + jx[5] * jx[5];
-        acc[6] += jx[0] * r[0] + jx[3] * r[1];
-        acc[7] += jx[1] * r[0] + jx[4] * r[1];
-        acc[8] += jx[2] * r[0] + jx[5] * r[1];
-      }
-#pragma unroll
-      for (int q = 0; q < 9; ++q) acc[q] = block_sum(acc[q], s.red);
-      if (tid == 0) {
-        double D[6] = {acc[0], acc[1], acc[2], acc[3], acc[4], acc[5]};
-        double ex[3] = {acc[6], acc[7], acc[8]};
-        double Dinv[6], v[3];
-        if (!point_solve(d, j, D, ex, lam, Dinv, v)) flags |= FLAG_SINGULAR;
-#pragma unroll
-        for (int q = 0; q < 6; ++q) s.pt[q] = Dinv[q];
-#pragma unroll
-        for (int q = 0; q < 3; ++q) s.pt[6 + q] = v[q];
-      }
+    if (!COST_ONLY) {
       __syncthreads();
-      double Dinv[6], v[3];
+      for (int j = tid; j < gr.np; j += RUN_LANES) {
+        int lo, hi;
+        point_slots(d, gr.pt0 + j, ci, lo, hi);
+        if (lo < hi) {
+          double a[9];
 #pragma unroll
-      for (int q = 0; q < 6; ++q) Dinv[q] = s.pt[q];
+          for (int e = 0; e < 9; ++e) a[e] = pacc[e * pt_cap + j];
+          for (int s = lo; s < hi; ++s) {
 #pragma unroll
-      for (int q = 0; q < 3; ++q) v[q] = s.pt[6 + q];
-      for (int o = a + tid; o < e; o += TILE_THREADS) {
-        int cam;
-        double X[3], b[2], r[2], Jp[14], Jx[6];
-        load_obs(d, o, cam, X, b);
-        eval_obs<true>(d.camtab + (size_t)CAMTAB_STRIDE * cam, X, b, dvdc_quirk != 0, r, Jp, Jx);
-        store_pm(d, o, Jp, Jx);
-        double jx[6];
-        float jpf[14], out[5];
+            for (int e = 0; e < 9; ++e) a[e] += slots[e * slot_cap + s];
+          }
 #pragma unroll
-        for (int q = 0; q < 6; ++q) jx[q] = (double)(float)Jx[q];
-#pragma unroll
-        for (int q = 0; q < 14; ++q) jpf[q] = (float)Jp[q];
-        obs_schur_terms(jx, r, Dinv, v, out);
-        store_cm(d, o, jpf, out);
+          for (int e = 0; e < 9; ++e) pacc[e * pt_cap + j] = a[e];
+        }
       }
       __syncthreads();
     }
   }
-  cost = block_sum(cost, s.red);
-  if (tid == 0) d.tile_cost[t] = cost;
+  if (!COST_ONLY) {
+    const double lam = d.sc->lambda;
+    const size_t N = (size_t)d.N;
+    for (int j = tid; j < gr.np; j += RUN_LANES) {
+      double D[6], ex[3], Dinv[6], v[3];
+#pragma unroll
+      for (int e = 0; e < 6; ++e) D[e] = pacc[e * pt_cap + j];
+#pragma unroll
+      for (int e = 0; e < 3; ++e) ex[e] = pacc[(6 + e) * pt_cap + j];
+      D[0] += lam;                                     // ba_processor.py:359 (every point, observed or not)
+      D[3] += lam;
+      D[5] += lam;
+      if (!sym3_inverse(D, Dinv)) flags |= FLAG_SINGULAR;
+      sym3_mul(Dinv, ex, v);
+      const size_t pt = (size_t)gr.pt0 + j;
+#pragma unroll
+      for (int e = 0; e < 6; ++e) d.dinv[e * N + pt] = Dinv[e];
+#pragma unroll
+      for (int e = 0; e < 3; ++e) d.vj[e * N + pt] = v[e];
+    }
+  }
+  cost = block_sum(cost, red);
+  if (tid == 0) d.grp_cost[blockIdx.x] = cost;
   if (flags) atomicOr(&d.sc->flags, flags);
 }
 
-// deterministic sum of per-tile costs into sc->costs[slot] and sc->cost_cur (slot < 0: cost_new only)
+// deterministic sum of per-block costs into sc->costs[slot] and sc->cost_cur (slot < 0: cost_new only)
 __global__ void k_sum_cost(const double* __restrict__ part, int n, Scalars* sc, int slot, double* out) {
   __shared__ double red[32];
   double a = 0.0;
@@ -264,8 +158,18 @@ __global__ void k_sum_cost(const double* __restrict__ part, int n, Scalars* sc, 
   }
 }
 
-// cost only: one lane per observation, per-block partials (tile_cost is reused as scratch: the
-// grid is capped at ntiles blocks)
+// ---- index-free kernels behind sfmba_ba_cost / sfmba_residual_jacobian ---------------------------
+__device__ __forceinline__ void load_obs(const BaDev& d, int o, int& cam, double X[3], double b[2]) {
+  cam = d.obs_cam[o];
+  const int j = d.obs_pt[o];
+  const double* p = d.pts + 3 * (size_t)j;
+  X[0] = p[0];
+  X[1] = p[1];
+  X[2] = p[2];
+  normalise_obs(d.kinv ? d.kinv + 9 * (size_t)cam : nullptr, d.obs_uv[o], d.obs_uv[d.m + o], b);
+}
+
+// cost only: one lane per observation in point-major order, per-block partials in grp_cost
 __global__ void __launch_bounds__(256) k_cost(BaDev d) {
   __shared__ double red[32];
   double cost = 0.0;
@@ -277,7 +181,7 @@ __global__ void __launch_bounds__(256) k_cost(BaDev d) {
     cost += r[0] * r[0] + r[1] * r[1];
   }
   cost = block_sum(cost, red);
-  if (threadIdx.x == 0) d.tile_cost[blockIdx.x] = cost;
+  if (threadIdx.x == 0) d.grp_cost[blockIdx.x] = cost;
 }
 
 // K1 alone (sfmba_residual_jacobian): SoA outputs, f32 (and optional f64 residuals)
@@ -313,7 +217,7 @@ __global__ void __launch_bounds__(256) k_residual_jacobian(BaDev d, int dvdc_qui
     }
   }
   cost = block_sum(cost, red);
-  if (threadIdx.x == 0) d.tile_cost[blockIdx.x] = cost;
+  if (threadIdx.x == 0) d.grp_cost[blockIdx.x] = cost;
   if (flags) atomicOr(&d.sc->flags, flags);
 }
 
@@ -322,21 +226,30 @@ void launch_cam_prepare(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
   lc.launches++;
 }
 
-void launch_linearize(const BaDev& d, bool dvdc_quirk, bool force_slow, int cost_slot, cudaStream_t st,
-                      LaunchCounter& lc) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(k_linearize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LinSmem));
-    attr_set = true;
-  }
-  k_linearize<<<d.ntiles, TILE_THREADS, sizeof(LinSmem), st>>>(d, dvdc_quirk ? 1 : 0, force_slow ? 1 : 0);
-  k_sum_cost<<<1, 1024, 0, st>>>(d.tile_cost, d.ntiles, d.sc, cost_slot, nullptr);
+static size_t point_smem(const TileShape& ts, bool cost_only) {
+  const size_t pt = (size_t)ts.max_group_pts, sl = (size_t)ts.max_chunk_len;
+  return cost_only ? (3 * pt + 32) * sizeof(double) : (3 * pt + 9 * pt + 9 * sl + 32) * sizeof(double);
+}
+
+void launch_point(const BaDev& d, const TileShape& ts, int cost_slot, cudaStream_t st, LaunchCounter& lc) {
+  const size_t smem = point_smem(ts, false);
+  cudaFuncSetAttribute(k_point<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (d.G > 0) k_point<false><<<d.G, RUN_LANES, smem, st>>>(d, ts.max_chunk_len, ts.max_group_pts);
+  k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, d.G, d.sc, cost_slot, nullptr);
+  lc.launches += 2;
+}
+
+void launch_cost_tiles(const BaDev& d, const TileShape& ts, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc) {
+  const size_t smem = point_smem(ts, true);
+  cudaFuncSetAttribute(k_point<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (d.G > 0) k_point<true><<<d.G, RUN_LANES, smem, st>>>(d, ts.max_chunk_len, ts.max_group_pts);
+  k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, d.G, d.sc, -1, out_cost_dev);
   lc.launches += 2;
 }
 
 static int cost_grid(const BaDev& d) {
   int g = (d.m + 255) / 256;
-  if (g > d.ntiles) g = d.ntiles;
+  if (g > 148 * 8) g = 148 * 8;
   if (g < 1) g = 1;
   return g;
 }
@@ -344,7 +257,7 @@ static int cost_grid(const BaDev& d) {
 void launch_cost(const BaDev& d, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc) {
   const int g = cost_grid(d);
   k_cost<<<g, 256, 0, st>>>(d);
-  k_sum_cost<<<1, 1024, 0, st>>>(d.tile_cost, g, d.sc, -1, out_cost_dev);
+  k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, g, d.sc, -1, out_cost_dev);
   lc.launches += 2;
 }
 
@@ -352,7 +265,7 @@ void launch_k1(const BaDev& d, bool dvdc_quirk, float* out_r, float* out_jp, flo
                double* out_cost, cudaStream_t st, LaunchCounter& lc) {
   const int g = cost_grid(d);
   k_residual_jacobian<<<g, 256, 0, st>>>(d, dvdc_quirk ? 1 : 0, out_r, out_jp, out_jx, out_r64);
-  k_sum_cost<<<1, 1024, 0, st>>>(d.tile_cost, g, nullptr, -1, out_cost);
+  k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, g, nullptr, -1, out_cost);
   lc.launches += 2;
 }
 

@@ -1,274 +1,417 @@
-// Reduced-camera-system solve: implicit-Schur matvec (K3), block-Jacobi PCG, back-substitution and
-// parameter update (K4).
+// Reduced-camera-system solve: matrix-free implicit-Schur matvec (K3), block-Jacobi PCG,
+// back-substitution and parameter update (K4).
 //
 // Reference: ba_processor.py:382 delta_p = inv(A - B D^-1 B^T)(e_p - B D^-1 e_x); 383-392 p += delta_p,
 // quaternion renormalised; 405-406 delta_x = D^-1 (e_x - B^T delta_p), x += delta_x.
 //
-// The matvec q = S p = A p - sum_j W_j D_j^-1 W_j^T p never forms S or B:
-//   pass A (point-major tiles): a_o = J_p,o p_cam(o);  t_j = sum_o J_x,o^T a_o;  u_j = D_j^-1 t_j;
-//                               b_o = J_x,o u_j  -> scattered (16 B) to the camera-major slot
-//   pass B (camera-major chunks, one camera each): y_chunk = sum_o J_p,o^T b_o   (f64, fixed order)
-//   finalize: svec_i = sum of the camera's chunks;   step kernel: q = A p - svec
-// J values are the stored f32 ones; every product and sum is f64, so the operator is exactly linear
-// and symmetric and PCG converges to f64 round-off.
+// q = S p = A p - sum_j W_j D_j^-1 W_j^T p never forms S, B or even J.  With d = X - C, p_c = R^T d,
+// (u, v) = p_uv / p_w, iw = 1 / p_w and M = [[1,0,-u],[0,1,-v]] the blocks factor as
+//     J_x = iw M R^T,   J_pC = -iw M' R^T,   J_pq = iw M [Q_0 d .. Q_3 d],   Q_j = d(R^T)/dq_j
+// (M' = M with the reference's sign quirk in its last column, campose_processor.py:802-804), so
+//   pass 1  a   = J_p p_cam = iw (M (E d - w) - quirk term),  E = sum_j p_q[j] Q_j,  w = R^T p_C
+//           t_j = sum_o J_x^T a = sum_o R (iw M^T a)                      (slots -> per-point sum)
+//   solve   u_j = D_j^-1 t_j
+//   pass 2  b   = J_x u_j = iw M (R^T u_j);   c~ = iw M^T b,  c' = iw M'^T b
+//           y_C = -R sum_o c',   y_q[j] = < Q_j , sum_o c~ d^T >          (12 sums per camera)
+// E and w are per-camera, per-iteration constants (k_cam_iter); the 12 sums of a run stay in
+// registers.  Everything is f64, so the operator is linear and symmetric to round-off and PCG
+// converges to f64 accuracy.  All reductions have a fixed order.
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
+#include "tile.cuh"
 
 namespace sfmba {
 
-struct MatvecSmem {
-  float jx[6][TILE_CAP];
-  double a[2][TILE_CAP];
-  double red[32];
-  double pt[4];
-};
+constexpr int MV_STRIDE = 13;   // doubles per run row in shared memory (odd: conflict-free flushes)
 
-template <bool BACKSUB>
-__global__ void __launch_bounds__(TILE_THREADS) k_matvec_a(BaDev d, const double* __restrict__ xvec, int force_slow) {
-  __shared__ MatvecSmem s;
-  if (!BACKSUB && d.sc->pcg_done) return;
-  const int t = blockIdx.x;
-  const int j0 = d.tile_pt[t], j1 = d.tile_pt[t + 1];
-  const int o0 = d.rowptr[j0], o1 = d.rowptr[j1];
-  const int L = o1 - o0;
-  const int tid = threadIdx.x;
-  const size_t mp = (size_t)d.mp;
+// Q[j][3 c + k] = d R[k][c] / d q_j for q2 = 2 (w,x,y,z)        (campose_processor.py:636-702)
+__device__ __forceinline__ void quat_dRt(const double q2[4], double Q[4][9]) {
+  const double w2 = q2[0], x2 = q2[1], y2 = q2[2], z2 = q2[3];
+  Q[0][0] = 0.0;       Q[0][1] = z2;        Q[0][2] = -y2;
+  Q[0][3] = -z2;       Q[0][4] = 0.0;       Q[0][5] = x2;
+  Q[0][6] = y2;        Q[0][7] = -x2;       Q[0][8] = 0.0;
+  Q[1][0] = 0.0;       Q[1][1] = y2;        Q[1][2] = z2;
+  Q[1][3] = y2;        Q[1][4] = -2.0 * x2; Q[1][5] = w2;
+  Q[1][6] = z2;        Q[1][7] = -w2;       Q[1][8] = -2.0 * x2;
+  Q[2][0] = -2.0 * y2; Q[2][1] = x2;        Q[2][2] = -w2;
+  Q[2][3] = x2;        Q[2][4] = 0.0;       Q[2][5] = z2;
+  Q[2][6] = w2;        Q[2][7] = z2;        Q[2][8] = -2.0 * y2;
+  Q[3][0] = -2.0 * z2; Q[3][1] = w2;        Q[3][2] = x2;
+  Q[3][3] = -w2;       Q[3][4] = -2.0 * z2; Q[3][5] = y2;
+  Q[3][6] = x2;        Q[3][7] = y2;        Q[3][8] = 0.0;
+}
 
-  if (L <= TILE_CAP && !force_slow) {
-    for (int sidx = tid; sidx < L; sidx += TILE_THREADS) {
-      const int o = o0 + sidx;
-      const double* xv = xvec + 7 * (size_t)d.obs_cam[o];
-      double a0 = 0.0, a1 = 0.0;
+// per camera and per matvec: (PCG) p = z + beta p, then E = sum_j p_q[j] Q_j, w = R^T p_C
+__global__ void __launch_bounds__(128) k_cam_iter(BaDev d, const double* __restrict__ vec, int pcg_direction,
+                                                  int dvdc_quirk) {
+  const int cam = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cam >= d.V) return;
+  if (pcg_direction && d.sc->pcg_done) return;
+  double dl[7];
+  if (pcg_direction) {
+    const double beta = d.sc->beta;
 #pragma unroll
-      for (int c = 0; c < 7; ++c) {
-        const double xc = xv[c];
-        a0 += (double)d.jp_pm[c * mp + o] * xc;
-        a1 += (double)d.jp_pm[(7 + c) * mp + o] * xc;
-      }
-      s.a[0][sidx] = a0;
-      s.a[1][sidx] = a1;
-#pragma unroll
-      for (int e = 0; e < 6; ++e) s.jx[e][sidx] = d.jx_pm[e * mp + o];
-    }
-    __syncthreads();
-    for (int j = j0 + tid; j < j1; j += TILE_THREADS) {
-      const int a = d.rowptr[j] - o0, e = d.rowptr[j + 1] - o0;
-      double tv[3] = {0, 0, 0};
-      for (int k = a; k < e; ++k) {
-        const double a0 = s.a[0][k], a1 = s.a[1][k];
-        tv[0] += (double)s.jx[0][k] * a0 + (double)s.jx[3][k] * a1;
-        tv[1] += (double)s.jx[1][k] * a0 + (double)s.jx[4][k] * a1;
-        tv[2] += (double)s.jx[2][k] * a0 + (double)s.jx[5][k] * a1;
-      }
-      double Dinv[6], u[3];
-#pragma unroll
-      for (int q = 0; q < 6; ++q) Dinv[q] = (double)d.dinv[(size_t)q * d.N + j];
-      sym3_mul(Dinv, tv, u);
-      if (BACKSUB) {
-        double* p = d.pts + 3 * (size_t)j;
-#pragma unroll
-        for (int q = 0; q < 3; ++q) p[q] += (double)d.vj[(size_t)q * d.N + j] - u[q];
-      } else {
-        for (int k = a; k < e; ++k) {
-          const double b0 = (double)s.jx[0][k] * u[0] + (double)s.jx[1][k] * u[1] + (double)s.jx[2][k] * u[2];
-          const double b1 = (double)s.jx[3][k] * u[0] + (double)s.jx[4][k] * u[1] + (double)s.jx[5][k] * u[2];
-          s.a[0][k] = b0;
-          s.a[1][k] = b1;
-        }
-      }
-    }
-    if (!BACKSUB) {
-      __syncthreads();
-      for (int sidx = tid; sidx < L; sidx += TILE_THREADS)
-        d.b_cm[d.pm2cm[o0 + sidx]] = make_double2(s.a[0][sidx], s.a[1][sidx]);
+    for (int k = 0; k < 7; ++k) {
+      const double v = d.z[7 * (size_t)cam + k] + beta * d.p[7 * (size_t)cam + k];
+      d.p[7 * (size_t)cam + k] = v;
+      dl[k] = v;
     }
   } else {
-    for (int j = j0; j < j1; ++j) {
-      const int a = d.rowptr[j], e = d.rowptr[j + 1];
-      double tv[3] = {0, 0, 0};
-      for (int o = a + tid; o < e; o += TILE_THREADS) {
-        const double* xv = xvec + 7 * (size_t)d.obs_cam[o];
-        double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-        for (int c = 0; c < 7; ++c) {
-          const double xc = xv[c];
-          a0 += (double)d.jp_pm[c * mp + o] * xc;
-          a1 += (double)d.jp_pm[(7 + c) * mp + o] * xc;
-        }
-        tv[0] += (double)d.jx_pm[0 * mp + o] * a0 + (double)d.jx_pm[3 * mp + o] * a1;
-        tv[1] += (double)d.jx_pm[1 * mp + o] * a0 + (double)d.jx_pm[4 * mp + o] * a1;
-        tv[2] += (double)d.jx_pm[2 * mp + o] * a0 + (double)d.jx_pm[5 * mp + o] * a1;
+    for (int k = 0; k < 7; ++k) dl[k] = vec[7 * (size_t)cam + k];
+  }
+  const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
+  double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
+  double Q[4][9];
+  quat_dRt(q2, Q);
+  double* o = d.camit + (size_t)CAMIT_STRIDE * cam;
+#pragma unroll
+  for (int e = 0; e < 9; ++e) o[e] = dl[3] * Q[0][e] + dl[4] * Q[1][e] + dl[5] * Q[2][e] + dl[6] * Q[3][e];
+  double w[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) w[c] = t[c] * dl[0] + t[3 + c] * dl[1] + t[6 + c] * dl[2];
+  o[9] = w[0];
+  o[10] = w[1];
+  o[11] = w[2];
+  o[12] = dvdc_quirk ? 2.0 * w[2] : 0.0;
+  o[13] = dvdc_quirk ? 1.0 : -1.0;
+  o[14] = 0.0;
+  o[15] = 0.0;
+}
+
+// ---- K3: matrix-free implicit-Schur matvec / back-substitution -----------------------------------
+// dynamic shared memory: Xs[3][pt_cap] | tacc[3][pt_cap] | un[max(3 slot_cap, run_cap MV_STRIDE)]
+// BACKSUB: pass 1 with delta_p, then pts_j += v_j - D_j^-1 t_j        (ba_processor.py:405-406)
+template <bool BACKSUB>
+__global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, int slot_cap, int pt_cap, int dvdc_quirk) {
+  extern __shared__ __align__(16) double smem[];
+  if (!BACKSUB && d.sc->pcg_done) return;
+  double* Xs = smem;
+  double* tacc = Xs + 3 * pt_cap;
+  double* un = tacc + 3 * pt_cap;
+  const GroupRange gr = group_range(d, blockIdx.x);
+  const int tid = threadIdx.x;
+  stage_points(d, gr, Xs, pt_cap);
+  for (int i = tid; i < 3 * pt_cap; i += RUN_LANES) tacc[i] = 0.0;
+  __syncthreads();
+  // ---- pass 1: t_j = sum_o J_x^T (J_p p_cam)
+  for (int c = gr.c0; c < gr.c1; ++c) {
+    const ChunkInfo ci = d.chunk_info[c];
+    const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
+    const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
+    const int32_t* segcam = d.seg_cam + (size_t)c * SEG_CAP;
+    double R[9], C[3], E[9], w[3], wq = 0.0;
+    uint32_t ix = ixp[0];
+    for (int k = 0; k < K && ix != REC_INVALID; ++k) {
+      const uint32_t ix_cur = ix;
+      ix = (k + 1 < K) ? ixp[(k + 1) * RUN_LANES] : REC_INVALID;
+      if (ix_cur & REC_RUNSTART) {
+        const int cam = segcam[rec_seg(ix_cur)];
+        load_cam_rc(d.camtab, cam, R, C);
+        const double2* it = reinterpret_cast<const double2*>(d.camit + (size_t)CAMIT_STRIDE * cam);
+        const double2 a = it[0], b = it[1], cc = it[2], e = it[3], f = it[4], g = it[5], h = it[6];
+        E[0] = a.x; E[1] = a.y; E[2] = b.x; E[3] = b.y; E[4] = cc.x; E[5] = cc.y; E[6] = e.x; E[7] = e.y; E[8] = f.x;
+        w[0] = f.y; w[1] = g.x; w[2] = g.y;
+        wq = h.x;
       }
+      const int ptl = rec_ptl(ix_cur);
+      const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
+      const double g0 = E[0] * pr.d0 + E[1] * pr.d1 + E[2] * pr.d2 - w[0];
+      const double g1 = E[3] * pr.d0 + E[4] * pr.d1 + E[5] * pr.d2 - w[1];
+      const double g2 = E[6] * pr.d0 + E[7] * pr.d1 + E[8] * pr.d2 - w[2];
+      const double a0 = pr.iw * (g0 - pr.u * g2);
+      const double a1 = pr.iw * (g1 - pr.v * (g2 + wq));
+      const double c0 = pr.iw * a0, c1 = pr.iw * a1;
+      const double c2 = -(pr.u * c0 + pr.v * c1);
+      double* s = un + rec_pos(ix_cur);
+      s[0] = R[0] * c0 + R[1] * c1 + R[2] * c2;
+      s[slot_cap] = R[3] * c0 + R[4] * c1 + R[5] * c2;
+      s[2 * slot_cap] = R[6] * c0 + R[7] * c1 + R[8] * c2;
+    }
+    __syncthreads();
+    for (int j = tid; j < gr.np; j += RUN_LANES) {
+      int lo, hi;
+      point_slots(d, gr.pt0 + j, ci, lo, hi);
+      if (lo < hi) {
+        double t0 = tacc[j], t1 = tacc[pt_cap + j], t2 = tacc[2 * pt_cap + j];
+        for (int s = lo; s < hi; ++s) {
+          t0 += un[s];
+          t1 += un[slot_cap + s];
+          t2 += un[2 * slot_cap + s];
+        }
+        tacc[j] = t0;
+        tacc[pt_cap + j] = t1;
+        tacc[2 * pt_cap + j] = t2;
+      }
+    }
+    __syncthreads();
+  }
+  // ---- u_j = D_j^-1 t_j
+  {
+    const size_t N = (size_t)d.N;
+    for (int j = tid; j < gr.np; j += RUN_LANES) {
+      const size_t pt = (size_t)gr.pt0 + j;
+      double Dinv[6], t[3], u[3];
 #pragma unroll
-      for (int q = 0; q < 3; ++q) tv[q] = block_sum(tv[q], s.red);
-      double Dinv[6], u[3];
-#pragma unroll
-      for (int q = 0; q < 6; ++q) Dinv[q] = (double)d.dinv[(size_t)q * d.N + j];
-      sym3_mul(Dinv, tv, u);
+      for (int e = 0; e < 6; ++e) Dinv[e] = d.dinv[e * N + pt];
+      t[0] = tacc[j];
+      t[1] = tacc[pt_cap + j];
+      t[2] = tacc[2 * pt_cap + j];
+      sym3_mul(Dinv, t, u);
       if (BACKSUB) {
-        if (tid == 0) {
-          double* p = d.pts + 3 * (size_t)j;
+        double* p = d.pts + 3 * pt;
 #pragma unroll
-          for (int q = 0; q < 3; ++q) p[q] += (double)d.vj[(size_t)q * d.N + j] - u[q];
-        }
+        for (int e = 0; e < 3; ++e) p[e] += d.vj[e * N + pt] - u[e];
       } else {
-        for (int o = a + tid; o < e; o += TILE_THREADS) {
-          const double b0 = (double)d.jx_pm[0 * mp + o] * u[0] + (double)d.jx_pm[1 * mp + o] * u[1] +
-                            (double)d.jx_pm[2 * mp + o] * u[2];
-          const double b1 = (double)d.jx_pm[3 * mp + o] * u[0] + (double)d.jx_pm[4 * mp + o] * u[1] +
-                            (double)d.jx_pm[5 * mp + o] * u[2];
-          d.b_cm[d.pm2cm[o]] = make_double2(b0, b1);
-        }
+        tacc[j] = u[0];
+        tacc[pt_cap + j] = u[1];
+        tacc[2 * pt_cap + j] = u[2];
       }
     }
   }
+  if (BACKSUB) return;
+  __syncthreads();
+  // ---- pass 2: per camera sums of c~ d^T and c'
+  const double sgn = dvdc_quirk ? 1.0 : -1.0;
+  for (int c = gr.c0; c < gr.c1; ++c) {
+    const ChunkInfo ci = d.chunk_info[c];
+    const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
+    const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
+    const int32_t* segcam = d.seg_cam + (size_t)c * SEG_CAP;
+    double R[9], C[3];
+    double acc[MV_ACC];
+    int run = (int)d.lane_run0[(size_t)c * RUN_LANES + tid] - 1;
+    const uint32_t ix_first = ixp[0];
+    uint32_t ix = ix_first;
+    for (int k = 0; k < K && ix != REC_INVALID; ++k) {
+      const uint32_t ix_cur = ix;
+      ix = (k + 1 < K) ? ixp[(k + 1) * RUN_LANES] : REC_INVALID;
+      if (ix_cur & REC_RUNSTART) {
+        if (k > 0) {
+          double* dst = un + run * MV_STRIDE;
+#pragma unroll
+          for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
+        }
+        ++run;
+#pragma unroll
+        for (int e = 0; e < MV_ACC; ++e) acc[e] = 0.0;
+        load_cam_rc(d.camtab, segcam[rec_seg(ix_cur)], R, C);
+      }
+      const int ptl = rec_ptl(ix_cur);
+      const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
+      const double u0 = tacc[ptl], u1 = tacc[pt_cap + ptl], u2 = tacc[2 * pt_cap + ptl];
+      const double e0 = R[0] * u0 + R[3] * u1 + R[6] * u2;
+      const double e1 = R[1] * u0 + R[4] * u1 + R[7] * u2;
+      const double e2 = R[2] * u0 + R[5] * u1 + R[8] * u2;
+      const double b0 = pr.iw * (e0 - pr.u * e2);
+      const double b1 = pr.iw * (e1 - pr.v * e2);
+      const double ct0 = pr.iw * b0, ct1 = pr.iw * b1;
+      const double ct2 = -(pr.u * ct0 + pr.v * ct1);
+      acc[0] += ct0 * pr.d0; acc[1] += ct0 * pr.d1; acc[2] += ct0 * pr.d2;
+      acc[3] += ct1 * pr.d0; acc[4] += ct1 * pr.d1; acc[5] += ct1 * pr.d2;
+      acc[6] += ct2 * pr.d0; acc[7] += ct2 * pr.d1; acc[8] += ct2 * pr.d2;
+      acc[9] += ct0;
+      acc[10] += ct1;
+      acc[11] += sgn * pr.v * ct1 - pr.u * ct0;
+    }
+    if (ix_first != REC_INVALID) {
+      double* dst = un + run * MV_STRIDE;
+#pragma unroll
+      for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
+    }
+    __syncthreads();
+    const uint16_t* run0 = d.seg_run0 + (size_t)c * (SEG_CAP + 1);
+    for (int idx = tid; idx < ci.nseg * MV_ACC; idx += RUN_LANES) {
+      const int s = idx / MV_ACC, e = idx % MV_ACC;
+      const int ra = run0[s], rb = run0[s + 1];
+      double a = 0.0;
+      for (int rr = ra; rr < rb; ++rr) a += un[rr * MV_STRIDE + e];
+      d.part12[((size_t)c * SEG_CAP + s) * MV_ACC + e] = a;
+    }
+    __syncthreads();
+  }
 }
 
-// pass B: one chunk (one camera) per CTA, one lane per observation
-__global__ void __launch_bounds__(256) k_matvec_b(BaDev d) {
-  __shared__ double s_w[8][8];
-  if (d.sc->pcg_done) return;
-  const int c = blockIdx.x;
-  if (c >= d.sc->num_chunks) return;
-  const int cam = d.chunk_cam[c];
-  const int beg = d.chunk_beg[c];
-  int end = beg + CHUNK_OBS;
-  const int cam_end = d.cam_rowptr[cam + 1];
-  if (end > cam_end) end = cam_end;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  double y[7] = {0, 0, 0, 0, 0, 0, 0};
-  const int slot = beg + tid;
-  if (slot < end) {
-    const float4* rec = d.rec_cm + 4 * (size_t)slot;
-    const float4 a = rec[0], b = rec[1], cc = rec[2], dd = rec[3];
-    const double2 bb = d.b_cm[slot];
-    y[0] = (double)a.x * bb.x + (double)b.w * bb.y;
-    y[1] = (double)a.y * bb.x + (double)cc.x * bb.y;
-    y[2] = (double)a.z * bb.x + (double)cc.y * bb.y;
-    y[3] = (double)a.w * bb.x + (double)cc.z * bb.y;
-    y[4] = (double)b.x * bb.x + (double)cc.w * bb.y;
-    y[5] = (double)b.y * bb.x + (double)dd.x * bb.y;
-    y[6] = (double)b.z * bb.x + (double)dd.y * bb.y;
-  }
+// ---- "last block" finish of a grid-wide sum: per-block partials are summed in block order ----------
+// Returns true in every thread of the block that finished last; `total` is then valid in all of them.
+template <int NV>
+__device__ __forceinline__ bool grid_sum_finish(double (&v)[NV], double* __restrict__ partials, uint32_t* ticket,
+                                                double* red, double (&total)[NV]) {
+  __shared__ bool s_last;
 #pragma unroll
-  for (int q = 0; q < 7; ++q) y[q] = warp_sum(y[q]);
-  if (lane == 0) {
+  for (int i = 0; i < NV; ++i) v[i] = block_sum(v[i], red);
+  if (threadIdx.x == 0) {
 #pragma unroll
-    for (int q = 0; q < 7; ++q) s_w[warp][q] = y[q];
+    for (int i = 0; i < NV; ++i) partials[(size_t)blockIdx.x * NV + i] = v[i];
+    __threadfence();
+    const uint32_t t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1);
   }
   __syncthreads();
-  if (tid < 7) {
+  if (!s_last) return false;
+  __threadfence();
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
     double a = 0.0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) a += s_w[w][tid];
-    d.chunk_y[(size_t)c * 8 + tid] = a;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) a += ((volatile double*)partials)[(size_t)b * NV + i];
+    total[i] = block_sum(a, red);
   }
+  if (threadIdx.x == 0) *ticket = 0u;
+  return true;
 }
 
-__global__ void k_matvec_finalize(BaDev d) {
-  if (d.sc->pcg_done) return;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= 7 * d.V) return;
-  const int cam = idx / 7, e = idx % 7;
-  double a = 0.0;
-  const int c0 = d.cam_chunk_ptr[cam], c1 = d.cam_chunk_ptr[cam + 1];
-  for (int c = c0; c < c1; ++c) a += d.chunk_y[(size_t)c * 8 + e];
-  d.svec[idx] = a;
-}
-
-// z = Minv r for element k (block product over the camera's 7 entries)
-__device__ __forceinline__ double blk7_row(const double* __restrict__ blk, const double* __restrict__ v, int k) {
-  const int cam = k / 7, a = k % 7;
-  const double* row = blk + (size_t)cam * 49 + a * 7;
-  const double* vv = v + 7 * (size_t)cam;
-  double sacc = 0.0;
-#pragma unroll
-  for (int b = 0; b < 7; ++b) sacc += row[b] * vv[b];
-  return sacc;
-}
-
-// x = 0, r = g, z = Minv g, p = z, rz = r.z, gg = g.g          (single CTA)
-__global__ void __launch_bounds__(1024) k_pcg_init(BaDev d, unsigned epoch) {
+// y_i from the camera's segment rows (16 lanes per camera, fixed row order):
+//   y_C = -R s,  y_q[j] = <Q_j, T>;   FUSE: q = A p - y and alpha = rz / (p.q)   (single GPU)
+template <bool FUSE>
+__global__ void __launch_bounds__(256) k_camsum12(BaDev d) {
   __shared__ double red[32];
-  const int n = 7 * d.V;
-  double rz = 0.0, gg = 0.0;
-  for (int k = threadIdx.x; k < n; k += blockDim.x) {
-    const double g = d.gvec[k];
-    const double z = blk7_row(d.minv, d.gvec, k);
-    d.x[k] = 0.0;
-    d.r[k] = g;
-    d.z[k] = z;
-    d.p[k] = z;
-    rz += g * z;
-    gg += g * g;
+  if (d.sc->pcg_done) return;
+  const int sub = threadIdx.x & 15;
+  const int cam = blockIdx.x * 16 + (threadIdx.x >> 4);
+  const bool live = cam < d.V;
+  double a = 0.0;
+  if (live && sub < MV_ACC) {
+    const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
+    for (int k = r0; k < r1; ++k) a += d.part12[(size_t)d.camrow_idx[k] * MV_ACC + sub];
   }
-  rz = block_sum(rz, red);
-  gg = block_sum(gg, red);
-  if (threadIdx.x == 0) {
-    Scalars* sc = d.sc;
-    sc->rz = rz;
-    sc->gg = gg;
-    sc->rr = gg;
-    sc->pcg_iters = 0;
-    const int done = (gg == 0.0 || !(gg == gg)) ? 1 : 0;
-    sc->pcg_done = done;
-    if (!(gg == gg)) atomicOr(&sc->flags, FLAG_NONFINITE);
-    if (d.host_sig) *(volatile unsigned long long*)d.host_sig = ((unsigned long long)epoch << 32) | (unsigned)done;
+  double T[MV_ACC];
+#pragma unroll
+  for (int e = 0; e < MV_ACC; ++e) T[e] = __shfl_sync(0xffffffffu, a, e, 16);
+  double pq = 0.0;
+  if (live && sub < 7) {
+    const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
+    double y;
+    if (sub < 3) {
+      y = -(t[3 * sub] * T[9] + t[3 * sub + 1] * T[10] + t[3 * sub + 2] * T[11]);
+    } else {
+      const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
+      double Q[4][9];
+      quat_dRt(q2, Q);
+      y = 0.0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (j == sub - 3) {
+#pragma unroll
+          for (int e = 0; e < 9; ++e) y += Q[j][e] * T[e];
+        }
+      }
+    }
+    const size_t k = 7 * (size_t)cam + sub;
+    d.svec[k] = y;
+    if (FUSE) {
+      const double* row = d.ablk + (size_t)cam * 49 + sub * 7;
+      const double* pv = d.p + 7 * (size_t)cam;
+      double ap = 0.0;
+#pragma unroll
+      for (int b = 0; b < 7; ++b) ap += row[b] * pv[b];
+      const double qv = ap - y;
+      d.q[k] = qv;
+      pq = pv[sub] * qv;
+    }
+  }
+  if (FUSE) {
+    double v[1] = {pq}, tot[1];
+    if (grid_sum_finish<1>(v, d.red_a, &d.sc->ticket_a, red, tot) && threadIdx.x == 0) {
+      d.sc->pq = tot[0];
+      d.sc->alpha = d.sc->rz / tot[0];
+    }
   }
 }
 
-// one PCG iteration after the matvec: q = A p - svec; alpha; x, r; z = Minv r; beta; p   (single CTA)
-__global__ void __launch_bounds__(1024) k_pcg_step(BaDev d, double tol, int max_iter, unsigned epoch) {
+// q = A p - svec, alpha = rz / (p.q)      (multi-GPU: after the all-reduce of svec)
+__global__ void __launch_bounds__(256) k_apq(BaDev d) {
+  __shared__ double red[32];
+  if (d.sc->pcg_done) return;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  double pq = 0.0;
+  if (k < 7 * d.V) {
+    const int cam = k / 7, a = k % 7;
+    const double* row = d.ablk + (size_t)cam * 49 + a * 7;
+    const double* pv = d.p + 7 * (size_t)cam;
+    double ap = 0.0;
+#pragma unroll
+    for (int b = 0; b < 7; ++b) ap += row[b] * pv[b];
+    const double qv = ap - d.svec[k];
+    d.q[k] = qv;
+    pq = pv[a] * qv;
+  }
+  double v[1] = {pq}, tot[1];
+  if (grid_sum_finish<1>(v, d.red_a, &d.sc->ticket_a, red, tot) && threadIdx.x == 0) {
+    d.sc->pq = tot[0];
+    d.sc->alpha = d.sc->rz / tot[0];
+  }
+}
+
+// One thread per camera (its 7 rows; no cross-thread hazards on r).
+// INIT:  x = 0, p = 0, r = g, z = Minv g, rz = r.z, gg = g.g, beta = 0
+// else:  x += alpha p, r -= alpha q, z = Minv r, beta = rz' / rz, convergence test, host signal
+template <bool INIT>
+__global__ void __launch_bounds__(128) k_pcg_update(BaDev d, double tol, int max_iter, unsigned epoch) {
   __shared__ double red[32];
   Scalars* sc = d.sc;
-  if (sc->pcg_done) return;
-  const int n = 7 * d.V;
-  const double rz = sc->rz;
-  double pq = 0.0;
-  for (int k = threadIdx.x; k < n; k += blockDim.x) {
-    const double q = blk7_row(d.ablk, d.p, k) - d.svec[k];
-    d.z[k] = q;                  // z is free here: reuse it as q
-    pq += d.p[k] * q;
-  }
-  pq = block_sum(pq, red);
-  const double alpha = rz / pq;
-  double rr = 0.0;
-  for (int k = threadIdx.x; k < n; k += blockDim.x) {
-    d.x[k] += alpha * d.p[k];
-    const double r = d.r[k] - alpha * d.z[k];
-    d.r[k] = r;
-    rr += r * r;
-  }
-  rr = block_sum(rr, red);      // also orders the r writes before the block products below
-  double rz_new = 0.0;
-  for (int k = threadIdx.x; k < n; k += blockDim.x) {
-    const double z = blk7_row(d.minv, d.r, k);
-    d.z[k] = z;
-    rz_new += d.r[k] * z;
-  }
-  rz_new = block_sum(rz_new, red);
-  const double beta = rz_new / rz;
-  for (int k = threadIdx.x; k < n; k += blockDim.x) d.p[k] = d.z[k] + beta * d.p[k];
-  if (threadIdx.x == 0) {
-    sc->rz = rz_new;
-    sc->rr = rr;
-    sc->pq = pq;
-    sc->alpha = alpha;
-    sc->beta = beta;
-    const int it = sc->pcg_iters + 1;
-    sc->pcg_iters = it;
-    sc->pcg_iters_total += 1;
-    bool done = false;
-    if (!(pq > 0.0) || !(rr == rr)) {
-      atomicOr(&sc->flags, FLAG_NONFINITE);
-      done = true;
+  if (!INIT && sc->pcg_done) return;
+  const int cam = blockIdx.x * blockDim.x + threadIdx.x;
+  double v[2] = {0.0, 0.0};
+  if (cam < d.V) {
+    const size_t base = 7 * (size_t)cam;
+    double rn[7];
+    if (INIT) {
+#pragma unroll
+      for (int b = 0; b < 7; ++b) {
+        rn[b] = d.gvec[base + b];
+        d.x[base + b] = 0.0;
+        d.p[base + b] = 0.0;
+      }
+    } else {
+      const double alpha = sc->alpha;
+#pragma unroll
+      for (int b = 0; b < 7; ++b) {
+        rn[b] = d.r[base + b] - alpha * d.q[base + b];
+        d.x[base + b] += alpha * d.p[base + b];
+      }
     }
-    if (rr <= tol * tol * sc->gg) done = true;
-    if (!done && it >= max_iter) {
-      atomicOr(&sc->flags, FLAG_PCG_MAXITER);
-      done = true;
+    const double* blk = d.minv + (size_t)cam * 49;
+#pragma unroll
+    for (int a = 0; a < 7; ++a) {
+      double z = 0.0;
+#pragma unroll
+      for (int b = 0; b < 7; ++b) z += blk[a * 7 + b] * rn[b];
+      d.z[base + a] = z;
+      d.r[base + a] = rn[a];
+      v[0] += rn[a] * z;
+      v[1] += rn[a] * rn[a];
     }
-    if (done) sc->pcg_done = 1;
+  }
+  double tot[2];
+  if (grid_sum_finish<2>(v, d.red_b, &sc->ticket_b, red, tot) && threadIdx.x == 0) {
+    const double rz_new = tot[0], rr = tot[1];
+    int done = 0, it = 0;
+    if (INIT) {
+      sc->rz = rz_new;
+      sc->gg = rr;
+      sc->rr = rr;
+      sc->beta = 0.0;
+      sc->pcg_iters = 0;
+      done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
+      if (!(rr == rr)) atomicOr(&sc->flags, FLAG_NONFINITE);
+    } else {
+      sc->beta = rz_new / sc->rz;
+      sc->rz = rz_new;
+      sc->rr = rr;
+      it = sc->pcg_iters + 1;
+      sc->pcg_iters = it;
+      sc->pcg_iters_total += 1;
+      if (!(sc->pq > 0.0) || !(rr == rr)) {
+        atomicOr(&sc->flags, FLAG_NONFINITE);
+        done = 1;
+      }
+      if (rr <= tol * tol * sc->gg) done = 1;
+      if (!done && it >= max_iter) {
+        atomicOr(&sc->flags, FLAG_PCG_MAXITER);
+        done = 1;
+      }
+    }
+    sc->pcg_done = done;
     if (d.host_sig)
       *(volatile unsigned long long*)d.host_sig =
           ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
@@ -348,35 +491,54 @@ __global__ void k_lm_decide(BaDev d, double lam_min, double lam_max) {
   }
 }
 
+
+static size_t matvec_smem(const TileShape& ts) {
+  const size_t un = (size_t)3 * ts.max_chunk_len > (size_t)ts.max_runs * MV_STRIDE ? (size_t)3 * ts.max_chunk_len
+                                                                                   : (size_t)ts.max_runs * MV_STRIDE;
+  return ((size_t)6 * ts.max_group_pts + un) * sizeof(double);
+}
+
 void launch_pcg_init(const BaDev& d, unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
-  k_pcg_init<<<1, 1024, 0, st>>>(d, epoch);
+  k_pcg_update<true><<<(d.V + 127) / 128, 128, 0, st>>>(d, 0.0, 0, epoch);
   lc.launches++;
 }
 
-void launch_matvec_a(const BaDev& d, const double* xvec, bool backsub, bool force_slow, cudaStream_t st,
+void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool dvdc_quirk, cudaStream_t st,
                      LaunchCounter& lc) {
-  if (backsub)
-    k_matvec_a<true><<<d.ntiles, TILE_THREADS, 0, st>>>(d, xvec, force_slow ? 1 : 0);
-  else
-    k_matvec_a<false><<<d.ntiles, TILE_THREADS, 0, st>>>(d, xvec, force_slow ? 1 : 0);
+  k_cam_iter<<<(d.V + 127) / 128, 128, 0, st>>>(d, vec, pcg_direction ? 1 : 0, dvdc_quirk ? 1 : 0);
   lc.launches++;
 }
 
-void launch_matvec_b(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
-  if (d.nchunk_bound > 0) {
-    k_matvec_b<<<d.nchunk_bound, 256, 0, st>>>(d);
-    lc.launches++;
+void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
+                   LaunchCounter& lc) {
+  if (d.G <= 0) return;
+  const size_t smem = matvec_smem(ts);
+  if (backsub) {
+    cudaFuncSetAttribute(k_matvec<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_matvec<true><<<d.G, RUN_LANES, smem, st>>>(d, ts.max_chunk_len, ts.max_group_pts, dvdc_quirk ? 1 : 0);
+  } else {
+    cudaFuncSetAttribute(k_matvec<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_matvec<false><<<d.G, RUN_LANES, smem, st>>>(d, ts.max_chunk_len, ts.max_group_pts, dvdc_quirk ? 1 : 0);
   }
-}
-
-void launch_matvec_finalize(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
-  const int n = 7 * d.V;
-  k_matvec_finalize<<<(n + 255) / 256, 256, 0, st>>>(d);
   lc.launches++;
 }
 
-void launch_pcg_step(const BaDev& d, double tol, int max_iter, unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
-  k_pcg_step<<<1, 1024, 0, st>>>(d, tol, max_iter, epoch);
+void launch_camsum12(const BaDev& d, bool fuse_apq, cudaStream_t st, LaunchCounter& lc) {
+  const int grid = (d.V + 15) / 16;
+  if (fuse_apq)
+    k_camsum12<true><<<grid, 256, 0, st>>>(d);
+  else
+    k_camsum12<false><<<grid, 256, 0, st>>>(d);
+  lc.launches++;
+}
+
+void launch_apq(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
+  k_apq<<<(7 * d.V + 255) / 256, 256, 0, st>>>(d);
+  lc.launches++;
+}
+
+void launch_pcg_update(const BaDev& d, double tol, int max_iter, unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
+  k_pcg_update<false><<<(d.V + 127) / 128, 128, 0, st>>>(d, tol, max_iter, epoch);
   lc.launches++;
 }
 

@@ -1,117 +1,189 @@
-// Camera-side reduction of the normal equations (K2b).
-//
+// Linearisation, camera side (K1 + K2b fused): the 63 numbers per camera the reduced system needs,
+//   A_i   = sum J_p^T J_p                          (28, upper triangle)
+//   Ssub  = sum J_p^T Y J_p,  Y = J_x D^-1 J_x^T    (28)  -> S_ii = A_i + lambda I - Ssub (block-Jacobi)
+//   g_i   = sum J_p^T rho,    rho = r - J_x D^-1 e_x (7)  -> right-hand side e_p - B D^-1 e_x
 // Reference: ba_processor.py:376-382 forms A = J_p^T J_p + lambda I, e_p, B = J_p^T J_x densely and
-// inverts A - B D^-1 B^T.  Here each camera-major chunk (<= 256 observations of ONE camera) reduces,
-// in f64, the 63 numbers the reduced system needs from that camera:
-//   A_i   = sum J_p^T J_p                      (28, upper triangle)
-//   Ssub  = sum J_p^T Y J_p,  Y = J_x D^-1 J_x^T (28)   -> S_ii = A_i + lambda I - Ssub (block-Jacobi)
-//   g_i   = sum J_p^T rho,    rho = r - J_x D^-1 e_x (7) -> right-hand side e_p - B D^-1 e_x
-// The chunk's records are staged in shared memory as doubles; thread (entry, part) then walks 64
-// observations with 4 LDS.64 + 2 DFMA each -- a skinny Gram product, no atomics, fixed order.
+// inverts A - B D^-1 B^T; campose_processor.py:462-482, 636-808 build J_p.
+//
+// k_camgram walks a group's camera-sorted records: a lane keeps the camera constants AND the 63
+// running sums of its current run in registers, so an observation costs ~340 FP64 FMAs and no
+// memory traffic beyond its 20-byte record and shared-memory reads of its point (X, D^-1, v).
+// Runs are flushed to shared memory, summed per segment (camera) in run order and written as one
+// 64-double row per (chunk, camera); k_camsum64 then adds each camera's rows in row order.
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
+#include "tile.cuh"
 
 namespace sfmba {
 
-constexpr int ROW = 30;   // doubles per staged observation: Jp(14) T(14) rho(2)
+constexpr int GRAM = 63;           // A(28) S(28) g(7)
+constexpr int RP_STRIDE = 63;      // odd stride (in doubles): conflict-free simultaneous flushes
 
-struct Cols {
-  unsigned char l0, r0, l1, r1;
-};
-
-__device__ __forceinline__ Cols entry_cols(int e) {
-  // e < 28: A(a,b); e < 56: Ssub(a,b); e < 63: g(a)
-  Cols c;
-  int k = e < 28 ? e : e - 28;
-  if (e < 56) {
-    int a = 0;
-    while (k >= 7 - a) {
-      k -= 7 - a;
-      ++a;
-    }
-    const int b = a + k;
-    c.l0 = a;
-    c.l1 = 7 + a;
-    if (e < 28) {
-      c.r0 = b;
-      c.r1 = 7 + b;
-    } else {
-      c.r0 = 14 + b;
-      c.r1 = 21 + b;
-    }
-  } else {
-    const int a = e - 56;
-    c.l0 = a;
-    c.l1 = 7 + a;
-    c.r0 = 28;
-    c.r1 = 29;
-  }
-  return c;
-}
-
-__global__ void __launch_bounds__(256) k_camreduce(BaDev d) {
-  extern __shared__ __align__(16) double s_rows[];   // [CHUNK_OBS][ROW] + [4][64]
-  double* s_part = s_rows + CHUNK_OBS * ROW;
-  const int c = blockIdx.x;
-  if (c >= d.sc->num_chunks) return;
-  const int cam = d.chunk_cam[c];
-  const int beg = d.chunk_beg[c];
-  int end = beg + CHUNK_OBS;
-  const int cam_end = d.cam_rowptr[cam + 1];
-  if (end > cam_end) end = cam_end;
-  const int len = end - beg;
+// dynamic shared memory: Xs[3][pt_cap] | Dv[9][pt_cap] | runpart[run_cap][RP_STRIDE]
+__global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, int pt_cap, int dvdc_quirk) {
+  extern __shared__ __align__(16) double smem[];
+  double* Xs = smem;
+  double* Dv = Xs + 3 * pt_cap;
+  double* runpart = Dv + 9 * pt_cap;
+  const GroupRange gr = group_range(d, blockIdx.x);
   const int tid = threadIdx.x;
+  stage_points(d, gr, Xs, pt_cap);
   {
-    double* row = s_rows + tid * ROW;
-    if (tid < len) {
-      const float4* rec = d.rec_cm + 4 * (size_t)(beg + tid);
-      const float4 a = rec[0], b = rec[1], cc = rec[2], dd = rec[3];
-      const float4 y = d.y_cm[beg + tid];
-      const double jp[14] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, cc.x, cc.y, cc.z, cc.w, dd.x, dd.y};
-      const double yuu = y.x, yuv = y.y, yvv = y.z;
-#pragma unroll
-      for (int k = 0; k < 7; ++k) {
-        row[k] = jp[k];
-        row[7 + k] = jp[7 + k];
-        row[14 + k] = yuu * jp[k] + yuv * jp[7 + k];
-        row[21 + k] = yuv * jp[k] + yvv * jp[7 + k];
+    const size_t N = (size_t)d.N;
+    for (int i = tid; i < 9 * gr.np; i += RUN_LANES) {
+      const int e = i / gr.np, j = i % gr.np;
+      Dv[e * pt_cap + j] = e < 6 ? d.dinv[e * N + gr.pt0 + j] : d.vj[(e - 6) * N + gr.pt0 + j];
+    }
+  }
+  __syncthreads();
+  for (int c = gr.c0; c < gr.c1; ++c) {
+    const ChunkInfo ci = d.chunk_info[c];
+    const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
+    const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
+    const double2* bp = d.rec_b + (size_t)c * CHUNK_CAP + tid;
+    const int32_t* segcam = d.seg_cam + (size_t)c * SEG_CAP;
+    double R[9], C[3], q2[4];
+    double acc[GRAM];
+    int run = (int)d.lane_run0[(size_t)c * RUN_LANES + tid] - 1;
+    uint32_t ix = ixp[0];
+    double2 b = bp[0];
+    for (int k = 0; k < K && ix != REC_INVALID; ++k) {
+      const uint32_t ix_cur = ix;
+      const double2 b_cur = b;
+      if (k + 1 < K) {
+        ix = ixp[(k + 1) * RUN_LANES];
+        b = bp[(k + 1) * RUN_LANES];
+      } else {
+        ix = REC_INVALID;
       }
-      row[28] = dd.z;
-      row[29] = dd.w;
-    } else {
+      if (ix_cur & REC_RUNSTART) {
+        if (k > 0) {
+          double* dst = runpart + run * RP_STRIDE;
 #pragma unroll
-      for (int k = 0; k < ROW; ++k) row[k] = 0.0;
+          for (int e = 0; e < GRAM; ++e) dst[e] = acc[e];
+        }
+        ++run;
+#pragma unroll
+        for (int e = 0; e < GRAM; ++e) acc[e] = 0.0;
+        const int cam = segcam[rec_seg(ix_cur)];
+        load_cam_rc(d.camtab, cam, R, C);
+        load_cam_q(d.camtab, cam, q2);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) q2[e] *= 2.0;
+      }
+      const int ptl = rec_ptl(ix_cur);
+      const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
+      const double iw = pr.iw, u = pr.u, v = pr.v;
+      const double r0 = b_cur.x - u, r1 = b_cur.y - v;
+      // J_x (2x3)
+      double jx[6];
+      jx[0] = (R[0] - u * R[2]) * iw;
+      jx[1] = (R[3] - u * R[5]) * iw;
+      jx[2] = (R[6] - u * R[8]) * iw;
+      jx[3] = (R[1] - v * R[2]) * iw;
+      jx[4] = (R[4] - v * R[5]) * iw;
+      jx[5] = (R[7] - v * R[8]) * iw;
+      // J_p (2x7): [d/dC | d/dq], u-row in jp[0..6], v-row in jp[7..13]
+      double jp[14];
+      jp[0] = -jx[0];
+      jp[1] = -jx[1];
+      jp[2] = -jx[2];
+      if (dvdc_quirk) {                                   // campose_processor.py:802-804
+        jp[7] = -(R[1] + v * R[2]) * iw;
+        jp[8] = -(R[4] + v * R[5]) * iw;
+        jp[9] = -(R[7] + v * R[8]) * iw;
+      } else {
+        jp[7] = -jx[3];
+        jp[8] = -jx[4];
+        jp[9] = -jx[5];
+      }
+      {
+        const double d0 = pr.d0, d1 = pr.d1, d2 = pr.d2;
+        const double w2 = q2[0], x2 = q2[1], y2 = q2[2], z2 = q2[3];
+        // G_c[j] = sum_k d_k dR[k][c]/dq_j   (campose_processor.py:636-767)
+        const double G00 = d1 * z2 - d2 * y2;
+        const double G01 = d1 * y2 + d2 * z2;
+        const double G02 = -2.0 * d0 * y2 + d1 * x2 - d2 * w2;
+        const double G03 = -2.0 * d0 * z2 + d1 * w2 + d2 * x2;
+        const double G10 = -d0 * z2 + d2 * x2;
+        const double G11 = d0 * y2 - 2.0 * d1 * x2 + d2 * w2;
+        const double G12 = d0 * x2 + d2 * z2;
+        const double G13 = -d0 * w2 - 2.0 * d1 * z2 + d2 * y2;
+        const double G20 = d0 * y2 - d1 * x2;
+        const double G21 = d0 * z2 - d1 * w2 - 2.0 * d2 * x2;
+        const double G22 = d0 * w2 + d1 * z2 - 2.0 * d2 * y2;
+        const double G23 = d0 * x2 + d1 * y2;
+        jp[3] = (G00 - u * G20) * iw;
+        jp[4] = (G01 - u * G21) * iw;
+        jp[5] = (G02 - u * G22) * iw;
+        jp[6] = (G03 - u * G23) * iw;
+        jp[10] = (G10 - v * G20) * iw;
+        jp[11] = (G11 - v * G21) * iw;
+        jp[12] = (G12 - v * G22) * iw;
+        jp[13] = (G13 - v * G23) * iw;
+      }
+      // point terms: Y = J_x D^-1 J_x^T, rho = r - J_x v_j
+      double Dinv[6], vv[3];
+#pragma unroll
+      for (int e = 0; e < 6; ++e) Dinv[e] = Dv[e * pt_cap + ptl];
+#pragma unroll
+      for (int e = 0; e < 3; ++e) vv[e] = Dv[(6 + e) * pt_cap + ptl];
+      double t0[3], t1[3];
+      sym3_mul(Dinv, jx, t0);
+      sym3_mul(Dinv, jx + 3, t1);
+      const double yuu = jx[0] * t0[0] + jx[1] * t0[1] + jx[2] * t0[2];
+      const double yuv = jx[0] * t1[0] + jx[1] * t1[1] + jx[2] * t1[2];
+      const double yvv = jx[3] * t1[0] + jx[4] * t1[1] + jx[5] * t1[2];
+      const double rho0 = r0 - (jx[0] * vv[0] + jx[1] * vv[1] + jx[2] * vv[2]);
+      const double rho1 = r1 - (jx[3] * vv[0] + jx[4] * vv[1] + jx[5] * vv[2]);
+      double tu[7], tv[7];
+#pragma unroll
+      for (int a = 0; a < 7; ++a) {
+        tu[a] = yuu * jp[a] + yuv * jp[7 + a];
+        tv[a] = yuv * jp[a] + yvv * jp[7 + a];
+      }
+      int e = 0;
+#pragma unroll
+      for (int a = 0; a < 7; ++a) {
+#pragma unroll
+        for (int bcol = a; bcol < 7; ++bcol, ++e) {
+          acc[e] += jp[a] * jp[bcol] + jp[7 + a] * jp[7 + bcol];
+          acc[28 + e] += jp[a] * tu[bcol] + jp[7 + a] * tv[bcol];
+        }
+      }
+#pragma unroll
+      for (int a = 0; a < 7; ++a) acc[56 + a] += jp[a] * rho0 + jp[7 + a] * rho1;
     }
-  }
-  __syncthreads();
-  const int part = tid >> 6, e = tid & 63;
-  double acc = 0.0;
-  if (e < 63) {
-    const Cols cl = entry_cols(e);
-    const double* base = s_rows + (part * 64) * ROW;
-#pragma unroll 4
-    for (int o = 0; o < 64; ++o) {
-      const double* row = base + o * ROW;
-      acc += row[cl.l0] * row[cl.r0] + row[cl.l1] * row[cl.r1];
+    if (run >= 0 && ixp[0] != REC_INVALID) {
+      double* dst = runpart + run * RP_STRIDE;
+#pragma unroll
+      for (int e = 0; e < GRAM; ++e) dst[e] = acc[e];
     }
-  }
-  s_part[part * 64 + e] = acc;
-  __syncthreads();
-  if (tid < 64) {
-    const double v = (s_part[tid] + s_part[64 + tid]) + (s_part[128 + tid] + s_part[192 + tid]);
-    d.chunk_acc[(size_t)c * CAM_ACC + tid] = v;
+    __syncthreads();
+    // per segment: sum its runs in run order -> one 64-double row
+    const uint16_t* run0 = d.seg_run0 + (size_t)c * (SEG_CAP + 1);
+    for (int idx = tid; idx < ci.nseg * CAM_ACC; idx += RUN_LANES) {
+      const int s = idx / CAM_ACC, e = idx % CAM_ACC;
+      double a = 0.0;
+      if (e < GRAM) {
+        const int ra = run0[s], rb = run0[s + 1];
+        for (int rr = ra; rr < rb; ++rr) a += runpart[rr * RP_STRIDE + e];
+      }
+      d.part64[((size_t)c * SEG_CAP + s) * CAM_ACC + e] = a;
+    }
+    __syncthreads();
   }
 }
 
-// cam_acc[cam][e] = sum over the camera's chunks, in chunk order
-__global__ void k_cam_finalize(BaDev d) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= d.V * CAM_ACC) return;
-  const int cam = idx / CAM_ACC, e = idx % CAM_ACC;
+// cam_acc[cam][e] = sum over the camera's segment rows, in row order (64 lanes per camera)
+__global__ void __launch_bounds__(256) k_camsum64(BaDev d) {
+  const int cam = blockIdx.x * 4 + (threadIdx.x >> 6);
+  const int e = threadIdx.x & 63;
+  if (cam >= d.V) return;
+  const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
   double a = 0.0;
-  const int c0 = d.cam_chunk_ptr[cam], c1 = d.cam_chunk_ptr[cam + 1];
-  for (int c = c0; c < c1; ++c) a += d.chunk_acc[(size_t)c * CAM_ACC + e];
-  d.cam_acc[idx] = a;
+  for (int k = r0; k < r1; ++k) a += d.part64[(size_t)d.camrow_idx[k] * CAM_ACC + e];
+  d.cam_acc[(size_t)cam * CAM_ACC + e] = a;
 }
 
 // per camera: A_i + lambda I (full 7x7), block-Jacobi inverse of S_ii, right-hand side g_i
@@ -145,22 +217,17 @@ __global__ void k_cam_blocks(BaDev d) {
   for (int a = 0; a < 7; ++a) d.gvec[7 * cam + a] = acc[56 + a];
 }
 
-void launch_camreduce(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
-  const size_t smem = (size_t)(CHUNK_OBS * ROW + 4 * 64) * sizeof(double);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(k_camreduce, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_set = true;
-  }
-  if (d.nchunk_bound > 0) {
-    k_camreduce<<<d.nchunk_bound, 256, smem, st>>>(d);
+void launch_camgram(const BaDev& d, const TileShape& ts, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
+  const size_t smem = ((size_t)12 * ts.max_group_pts + (size_t)ts.max_runs * RP_STRIDE) * sizeof(double);
+  cudaFuncSetAttribute(k_camgram, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (d.G > 0) {
+    k_camgram<<<d.G, RUN_LANES, smem, st>>>(d, ts.max_group_pts, dvdc_quirk ? 1 : 0);
     lc.launches++;
   }
 }
 
-void launch_cam_finalize(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
-  const int n = d.V * CAM_ACC;
-  k_cam_finalize<<<(n + 255) / 256, 256, 0, st>>>(d);
+void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
+  k_camsum64<<<(d.V + 3) / 4, 256, 0, st>>>(d);
   lc.launches++;
 }
 

@@ -57,10 +57,10 @@ cudaError_t sfmba_ctx::reserve(int slot, size_t bytes, void** out) {
 namespace {
 
 enum Slot {
-  S_SCALARS = 0, S_TILE_PT, S_CM_PERM, S_PM2CM, S_CAM_ROWPTR, S_CAM_CHUNK_PTR, S_CHUNK_CAM, S_CHUNK_BEG,
-  S_CAMTAB, S_JP_PM, S_JX_PM, S_REC_CM, S_Y_CM, S_DINV, S_VJ, S_TILE_COST, S_CHUNK_ACC, S_CAM_ACC, S_ABLK,
-  S_MINV, S_B_CM, S_CHUNK_Y, S_SVEC, S_X, S_R, S_Z, S_P, S_GVEC, S_CAMS_BAK, S_PTS_BAK, S_SORT_TEMP,
-  S_SORT_KEYS, S_IOTA, S_COUNT
+  S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_PT, S_GRP_NCHUNK, S_GRP_CHUNK, S_DINV, S_VJ, S_CAM_ACC, S_ABLK, S_MINV,
+  S_CAMIT, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
+  S_CHUNK_INFO, S_REC_B, S_REC_IX, S_SEG_CAM, S_SEG_RUN0, S_LANE_RUN0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
+  S_TEMP, S_SORT_KEYS, S_IOTA, S_COUNT
 };
 
 template <typename T>
@@ -73,7 +73,10 @@ int carve(sfmba_ctx* ctx, int slot, size_t count, T** out) {
 
 }  // namespace
 
-// Fills the BaDev view.  `full` = false carves only what K1 / cost need.
+#define CARVE(slot, count, field) \
+  if ((rc = carve(ctx, slot, (size_t)(count), &d.field)) != SFMBA_OK) return rc;
+
+// Fills the BaDev view.  `full` = false carves only what K1 / the index-free cost need.
 int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev* out) {
   if (!pr || pr->num_cams < 0 || pr->num_pts < 0 || pr->num_obs < 0)
     return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "bad problem sizes");
@@ -86,10 +89,7 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
   d.V = pr->num_cams;
   d.N = pr->num_pts;
   d.m = pr->num_obs;
-  d.mp = (d.m + 31) / 32 * 32;
-  if (d.mp == 0) d.mp = 32;
-  d.ntiles = std::max(1, (d.m + TILE_OBS - 1) / TILE_OBS);
-  d.nchunk_bound = d.m > 0 ? d.m / CHUNK_OBS + std::min(d.V, d.m) : 0;
+  d.G = (int)(((long long)d.m + (long long)POINT_WEIGHT * d.N + GROUP_WEIGHT - 1) / GROUP_WEIGHT);
   d.obs_uv = pr->obs_uv;
   d.obs_cam = pr->obs_cam;
   d.obs_pt = pr->obs_pt;
@@ -99,44 +99,55 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
   d.pts = pr->pts;
   d.host_sig = ctx->world == 1 ? reinterpret_cast<unsigned long long*>(ctx->pinned) : nullptr;
   int rc;
-#define CARVE(slot, count, field) \
-  if ((rc = carve(ctx, slot, (size_t)(count), &d.field)) != SFMBA_OK) return rc;
+  const size_t V = (size_t)d.V, N = (size_t)std::max(d.N, 1);
   CARVE(S_SCALARS, 1, sc);
-  CARVE(S_CAMTAB, (size_t)d.V * CAMTAB_STRIDE, camtab);
-  CARVE(S_TILE_COST, d.ntiles, tile_cost);
+  CARVE(S_CAMTAB, V * CAMTAB_STRIDE, camtab);
+  CARVE(S_GRP_COST, std::max(d.G, 148 * 8) + 1, grp_cost);
   if (full) {
-    CARVE(S_TILE_PT, d.ntiles + 1, tile_pt);
-    CARVE(S_CM_PERM, std::max(d.m, 1), cm_perm);
-    CARVE(S_PM2CM, std::max(d.m, 1), pm2cm);
-    CARVE(S_CAM_ROWPTR, d.V + 1, cam_rowptr);
-    CARVE(S_CAM_CHUNK_PTR, d.V + 1, cam_chunk_ptr);
-    CARVE(S_CHUNK_CAM, d.nchunk_bound + 1, chunk_cam);
-    CARVE(S_CHUNK_BEG, d.nchunk_bound + 2, chunk_beg);
-    CARVE(S_JP_PM, (size_t)14 * d.mp, jp_pm);
-    CARVE(S_JX_PM, (size_t)6 * d.mp, jx_pm);
-    CARVE(S_REC_CM, (size_t)4 * std::max(d.m, 1), rec_cm);
-    CARVE(S_Y_CM, std::max(d.m, 1), y_cm);
-    CARVE(S_DINV, (size_t)6 * std::max(d.N, 1), dinv);
-    CARVE(S_VJ, (size_t)3 * std::max(d.N, 1), vj);
-    CARVE(S_CHUNK_ACC, (size_t)(d.nchunk_bound + 1) * CAM_ACC, chunk_acc);
-    CARVE(S_CAM_ACC, (size_t)d.V * CAM_ACC + 8, cam_acc);
-    CARVE(S_ABLK, (size_t)d.V * 49, ablk);
-    CARVE(S_MINV, (size_t)d.V * 49, minv);
-    CARVE(S_B_CM, std::max(d.m, 1), b_cm);
-    CARVE(S_CHUNK_Y, (size_t)(d.nchunk_bound + 1) * 8, chunk_y);
-    CARVE(S_SVEC, (size_t)7 * d.V, svec);
-    CARVE(S_X, (size_t)7 * d.V, x);
-    CARVE(S_R, (size_t)7 * d.V, r);
-    CARVE(S_Z, (size_t)7 * d.V, z);
-    CARVE(S_P, (size_t)7 * d.V, p);
-    CARVE(S_GVEC, (size_t)7 * d.V, gvec);
-    CARVE(S_CAMS_BAK, (size_t)7 * d.V, cams_backup);
-    CARVE(S_PTS_BAK, (size_t)3 * std::max(d.N, 1), pts_backup);
+    CARVE(S_GRP_PT, d.G + 1, grp_pt);
+    CARVE(S_GRP_NCHUNK, d.G + 1, grp_nchunk);
+    CARVE(S_GRP_CHUNK, d.G + 1, grp_chunk);
+    CARVE(S_DINV, 6 * N, dinv);
+    CARVE(S_VJ, 3 * N, vj);
+    CARVE(S_CAM_ACC, V * CAM_ACC + 8, cam_acc);
+    CARVE(S_ABLK, V * 49, ablk);
+    CARVE(S_MINV, V * 49, minv);
+    CARVE(S_CAMIT, V * CAMIT_STRIDE, camit);
+    CARVE(S_SVEC, 7 * V, svec);
+    CARVE(S_X, 7 * V, x);
+    CARVE(S_R, 7 * V, r);
+    CARVE(S_Z, 7 * V, z);
+    CARVE(S_P, 7 * V, p);
+    CARVE(S_Q, 7 * V, q);
+    CARVE(S_GVEC, 7 * V, gvec);
+    CARVE(S_RED_A, 7 * V / 256 + V / 16 + 8, red_a);
+    CARVE(S_RED_B, 2 * (V / 128 + 2), red_b);
+    CARVE(S_CAMS_BAK, 7 * V, cams_backup);
+    CARVE(S_PTS_BAK, 3 * N, pts_backup);
+    CARVE(S_CAMROW_PTR, V + 1, camrow_ptr);
   }
-#undef CARVE
   *out = d;
   return SFMBA_OK;
 }
+
+// chunk-sized arrays, once the number of chunks is known
+static int sfm_setup_chunks(sfmba_ctx* ctx, int nchunks, BaDev* io) {
+  BaDev& d = *io;
+  int rc;
+  const size_t nc = (size_t)std::max(nchunks, 1);
+  d.chunk_bound = (int)nc;
+  CARVE(S_CHUNK_INFO, nc, chunk_info);
+  CARVE(S_REC_B, nc * CHUNK_CAP, rec_b);
+  CARVE(S_REC_IX, nc * CHUNK_CAP, rec_ix);
+  CARVE(S_SEG_CAM, nc * SEG_CAP, seg_cam);
+  CARVE(S_SEG_RUN0, nc * (SEG_CAP + 1), seg_run0);
+  CARVE(S_LANE_RUN0, nc * RUN_LANES, lane_run0);
+  CARVE(S_CAMROW_IDX, nc * SEG_CAP, camrow_idx);
+  CARVE(S_PART64, nc * SEG_CAP * CAM_ACC, part64);
+  CARVE(S_PART12, nc * SEG_CAP * MV_ACC, part12);
+  return SFMBA_OK;
+}
+#undef CARVE
 
 namespace {
 
@@ -198,6 +209,7 @@ enum Phase { PH_INDEX = 0, PH_LINEARIZE, PH_CAMREDUCE, PH_PCG, PH_UPDATE, PH_TOT
 
 }  // namespace
 
+
 int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_options* opt_in,
                         sfmba_result* res, cudaStream_t st) {
   sfmba_options opt;
@@ -211,36 +223,50 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   const double tol = opt.pcg_tol > 0 ? opt.pcg_tol : 1e-12;
   const int max_iter = opt.pcg_max_iter > 0 ? opt.pcg_max_iter : std::max(200, std::min(4 * n7, 5000));
   const bool quirk = opt.dvdc_sign_quirk != 0;
-  const bool slow = opt.force_slow_path != 0;
+  const bool fine = opt.force_slow_path != 0;
   const bool adaptive = opt.mode == SFMBA_MODE_ADAPTIVE_LM;
+  const bool multi = ctx->world > 1;
   const int64_t launches0 = ctx->lc.launches;
   LaunchCounter& lc = ctx->lc;
-
-  // sort scratch
-  void* sort_temp = nullptr;
-  int32_t *sort_keys = nullptr, *iota = nullptr;
-  const size_t sort_bytes = index_sort_temp_bytes(d.m, d.V);
-  if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_SORT_TEMP, sort_bytes, &sort_temp), "cudaMalloc(sort)")) != 0) return rc;
-  if ((rc = carve(ctx, S_SORT_KEYS, (size_t)std::max(d.m, 1), &sort_keys)) != 0) return rc;
-  if ((rc = carve(ctx, S_IOTA, (size_t)std::max(d.m, 1), &iota)) != 0) return rc;
 
   PhaseTimer pt{ctx, st};
   cudaEvent_t t_total = pt.begin();
 
-  // scalars
+  // scalars (pageable source: the copy is staged by the driver before the call returns)
   Scalars h0;
   memset(&h0, 0, sizeof(h0));
   h0.lambda = opt.lambda;
   h0.nu = 2.0;
-  // (pageable source: the copy is staged by the driver before the call returns)
   if ((rc = sfm_check_cuda(ctx, cudaMemcpyAsync(d.sc, &h0, sizeof(h0), cudaMemcpyHostToDevice, st), "memcpy(scalars)")) != 0)
     return rc;
 
+  // ---- index: count chunks (one host round trip), then build
+  char* pin = reinterpret_cast<char*>(ctx->pinned) + 64;
+  Scalars* hs = reinterpret_cast<Scalars*>(pin);
+  double* hfinal = reinterpret_cast<double*>(pin + sizeof(Scalars));
   cudaEvent_t t0 = pt.begin();
-  launch_build_index(d, sort_temp, sort_bytes, sort_keys, iota, st, lc);
+  const int chunk_upper = d.G + d.m / SEG_CAP + 1;
+  void* temp = nullptr;
+  size_t temp_bytes = index_temp_bytes(d.G, 1, d.V);
+  if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_TEMP, temp_bytes, &temp), "cudaMalloc(temp)")) != 0) return rc;
+  launch_index_count(d, fine, temp, temp_bytes, st, lc);
+  cudaMemcpyAsync(hs, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, st);
+  if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "index count")) != 0) return rc;
+  const int nchunks = hs->num_chunks;
+  if (nchunks < 0 || nchunks > chunk_upper) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "pt_rowptr is not a CSR");
+  TileShape ts;
+  ts.max_chunk_len = std::max(hs->max_chunk_len, 1);
+  ts.max_runs = std::max(hs->max_runs, 1);
+  ts.max_group_pts = std::max(hs->max_group_pts, 1);
+  if ((rc = sfm_setup_chunks(ctx, nchunks, &d)) != 0) return rc;
+  int32_t *sort_keys = nullptr, *iota = nullptr;
+  temp_bytes = index_temp_bytes(d.G, d.chunk_bound, d.V);
+  if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_TEMP, temp_bytes, &temp), "cudaMalloc(temp)")) != 0) return rc;
+  if ((rc = carve(ctx, S_SORT_KEYS, (size_t)d.chunk_bound * SEG_CAP, &sort_keys)) != 0) return rc;
+  if ((rc = carve(ctx, S_IOTA, (size_t)d.chunk_bound * SEG_CAP, &iota)) != 0) return rc;
+  launch_index_build(d, nchunks, temp, temp_bytes, sort_keys, iota, st, lc);
   pt.end(PH_INDEX, t0);
 
-  const bool multi = ctx->world > 1;
   int cost_slot = 0;
   for (int it = 0; it < opt.iterations; ++it) {
     t0 = pt.begin();
@@ -248,18 +274,18 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     launch_cam_prepare(d, st, lc);
     {
       cudaEvent_t kb = pt.kbegin();
-      launch_linearize(d, quirk, slow, cost_slot, st, lc);
-      pt.kend("linearize", kb);
+      launch_point(d, ts, cost_slot, st, lc);
+      pt.kend("point", kb);
     }
     pt.end(PH_LINEARIZE, t0);
 
     t0 = pt.begin();
     {
       cudaEvent_t kb = pt.kbegin();
-      launch_camreduce(d, st, lc);
-      pt.kend("camreduce", kb);
+      launch_camgram(d, ts, quirk, st, lc);
+      pt.kend("camgram", kb);
     }
-    launch_cam_finalize(d, st, lc);
+    launch_camsum64(d, st, lc);
     if (multi) {
       // one message: the camera accumulators plus this rank's cost in the trailing slot
       cudaMemcpyAsync(d.cam_acc + (size_t)d.V * CAM_ACC, &d.sc->cost_cur, sizeof(double),
@@ -277,27 +303,28 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     pt.end(PH_CAMREDUCE, t0);
 
     // ---- PCG.  Kernels of an already-converged solve exit at their first instruction, so launching
-    // past convergence is harmless but not free.  One GPU: k_pcg_step publishes (epoch, iteration,
+    // past convergence is harmless but not free.  One GPU: k_pcg_update publishes (epoch, iteration,
     // done) in one 8-byte store to pinned host memory; the host keeps LOOKAHEAD iterations queued
     // and reads that word without any synchronisation.  Several GPUs: every rank must issue the
     // same number of collectives, so iterations go out in fixed batches and the (rank-identical)
     // done flag of batch b is inspected after batch b+1 has been queued.
     t0 = pt.begin();
     auto launch_iteration = [&](unsigned epoch) -> int {
+      launch_cam_iter(d, nullptr, true, quirk, st, lc);
       cudaEvent_t kb = pt.kbegin();
-      launch_matvec_a(d, d.p, false, slow, st, lc);
-      pt.kend("matvec_a", kb);
+      launch_matvec(d, ts, false, quirk, st, lc);
+      pt.kend("matvec", kb);
       kb = pt.kbegin();
-      launch_matvec_b(d, st, lc);
-      pt.kend("matvec_b", kb);
-      launch_matvec_finalize(d, st, lc);
+      launch_camsum12(d, !multi, st, lc);
+      pt.kend("camsum12", kb);
       if (multi) {
         const int r2 = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st);
         if (r2 != 0) return r2;
+        launch_apq(d, st, lc);
       }
       kb = pt.kbegin();
-      launch_pcg_step(d, tol, max_iter, epoch, st, lc);
-      pt.kend("pcg_vec", kb);
+      launch_pcg_update(d, tol, max_iter, epoch, st, lc);
+      pt.kend("pcg_update", kb);
       return 0;
     };
     if (!multi) {
@@ -359,11 +386,16 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
 
     t0 = pt.begin();
     if (adaptive) launch_lm_model_decrease(d, st, lc);
-    launch_matvec_a(d, d.x, true, slow, st, lc);     // back-substitution: pts += v - Dinv B^T dp
+    launch_cam_iter(d, d.x, false, quirk, st, lc);
+    {
+      cudaEvent_t kb = pt.kbegin();
+      launch_matvec(d, ts, true, quirk, st, lc);        // back-substitution: pts += v - Dinv B^T dp
+      pt.kend("backsub", kb);
+    }
     launch_update_cams(d, st, lc);
     if (adaptive) {
       launch_cam_prepare(d, st, lc);
-      launch_cost(d, nullptr, st, lc);               // -> sc->cost_new
+      launch_cost_tiles(d, ts, nullptr, st, lc);       // -> sc->cost_new
       if (multi) {
         if ((rc = sfm_nccl_allreduce_f64(ctx, &d.sc->cost_new, 1, st)) != 0) return rc;
       }
@@ -378,15 +410,14 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   double* final_cost_dev = d.cam_acc + (size_t)d.V * CAM_ACC + 1;
   if (opt.compute_costs || adaptive) {
     launch_cam_prepare(d, st, lc);
-    launch_cost(d, final_cost_dev, st, lc);
+    cudaEvent_t kb = pt.kbegin();
+    launch_cost_tiles(d, ts, final_cost_dev, st, lc);
+    pt.kend("cost", kb);
     if (multi && (rc = sfm_nccl_allreduce_f64(ctx, final_cost_dev, 1, st)) != 0) return rc;
   }
   pt.end(PH_TOTAL, t_total);
 
   // results
-  char* pin = reinterpret_cast<char*>(ctx->pinned) + 64;
-  Scalars* hs = reinterpret_cast<Scalars*>(pin);
-  double* hfinal = reinterpret_cast<double*>(pin + sizeof(Scalars));
   *hfinal = 0.0;
   cudaMemcpyAsync(hs, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, st);
   if (opt.compute_costs || adaptive)

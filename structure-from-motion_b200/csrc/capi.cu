@@ -204,7 +204,7 @@ int sfmba_ba_cost(sfmba_ctx* ctx, const sfmba_problem* problem, double* host_cos
   if (rc) return rc;
   cudaMemsetAsync(d.sc, 0, sizeof(Scalars), st);
   launch_cam_prepare(d, st, ctx->lc);
-  double* dev_cost = d.tile_cost;   // k_sum_cost reads the partials before thread 0 writes slot 0
+  double* dev_cost = d.grp_cost;    // k_sum_cost reads the partials before thread 0 writes slot 0
   launch_cost(d, dev_cost, st, ctx->lc);
   double* pin = reinterpret_cast<double*>(ctx->pinned);
   cudaMemcpyAsync(pin, dev_cost, sizeof(double), cudaMemcpyDeviceToHost, st);

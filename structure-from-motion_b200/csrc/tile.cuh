@@ -1,0 +1,70 @@
+// Helpers shared by the tile kernels (one CTA per group, one lane per K sorted observations):
+// staging of a group's points, camera-constant loads, per-point reduction of scattered slots.
+#pragma once
+#include "ba_internal.h"
+#include "sfmba_device.cuh"
+
+namespace sfmba {
+
+struct GroupRange {
+  int pt0, np, c0, c1;
+};
+
+__device__ __forceinline__ GroupRange group_range(const BaDev& d, int g) {
+  GroupRange r;
+  r.pt0 = d.grp_pt[g];
+  r.np = d.grp_pt[g + 1] - r.pt0;
+  r.c0 = d.grp_chunk[g];
+  r.c1 = d.grp_chunk[g + 1];
+  return r;
+}
+
+// Xs[e * cap + j] = pts[pt0 + j][e]  (coalesced global read, SoA in shared memory)
+__device__ __forceinline__ void stage_points(const BaDev& d, const GroupRange& gr, double* Xs, int cap) {
+  const double* src = d.pts + 3 * (size_t)gr.pt0;
+  for (int i = threadIdx.x; i < 3 * gr.np; i += blockDim.x) Xs[(i % 3) * cap + i / 3] = src[i];
+}
+
+// R (9, row-major, camera-to-world) and C (3) of one camera: six 16-byte loads of its table row
+__device__ __forceinline__ void load_cam_rc(const double* __restrict__ camtab, int cam, double R[9], double C[3]) {
+  const double2* row = reinterpret_cast<const double2*>(camtab + (size_t)CAMTAB_STRIDE * cam);
+  const double2 a = row[0], b = row[1], c = row[2], e = row[3], f = row[4], g = row[5];
+  R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = c.x; R[5] = c.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
+  C[0] = f.y; C[1] = g.x; C[2] = g.y;
+}
+
+__device__ __forceinline__ void load_cam_q(const double* __restrict__ camtab, int cam, double q[4]) {
+  const double2* row = reinterpret_cast<const double2*>(camtab + (size_t)CAMTAB_STRIDE * cam);
+  const double2 a = row[6], b = row[7];
+  q[0] = a.x; q[1] = a.y; q[2] = b.x; q[3] = b.y;
+}
+
+// projection of one point: d = X - C, p = R^T d, iw = 1 / p_w, (u, v) = p_uv * iw
+struct Proj {
+  double d0, d1, d2, iw, u, v;
+  bool ok;
+};
+
+__device__ __forceinline__ Proj project(const double R[9], const double C[3], double x0, double x1, double x2) {
+  Proj p;
+  p.d0 = x0 - C[0];
+  p.d1 = x1 - C[1];
+  p.d2 = x2 - C[2];
+  const double pu = R[0] * p.d0 + R[3] * p.d1 + R[6] * p.d2;
+  const double pv = R[1] * p.d0 + R[4] * p.d1 + R[7] * p.d2;
+  const double pw = R[2] * p.d0 + R[5] * p.d1 + R[8] * p.d2;
+  p.iw = 1.0 / pw;
+  p.u = pu * p.iw;
+  p.v = pv * p.iw;
+  p.ok = pw != 0.0;
+  return p;
+}
+
+// observation range of point j (group-local) inside chunk [obs0, obs0 + len), as slot positions
+__device__ __forceinline__ void point_slots(const BaDev& d, int pt, const ChunkInfo& ci, int& lo, int& hi) {
+  const int a = d.rowptr[pt], b = d.rowptr[pt + 1];
+  lo = max(a, ci.obs0) - ci.obs0;
+  hi = min(b, ci.obs0 + ci.len) - ci.obs0;
+}
+
+}  // namespace sfmba
