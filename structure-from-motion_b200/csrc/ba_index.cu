@@ -69,6 +69,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chu
       const int K = (L + RUN_LANES - 1) / RUN_LANES;
       atomicMax(&d.sc->max_chunk_len, L);
       atomicMax(&d.sc->max_runs, (L + K - 1) / K + s_distinct);
+      atomicMax(&d.sc->max_nseg, s_distinct);
     }
   }
   if (threadIdx.x == 0) {
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chu
     if (n > 1) {
       atomicMax(&d.sc->max_chunk_len, SEG_CAP);
       atomicMax(&d.sc->max_runs, SEG_CAP);
+      atomicMax(&d.sc->max_nseg, SEG_CAP);
     }
   }
 }
@@ -108,6 +110,15 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
   const int c0 = d.grp_chunk[g], c1 = d.grp_chunk[g + 1];
   const int o_begin = d.rowptr[pt0], o_end = d.rowptr[pt1];
   const int tid = threadIdx.x;
+  if (tid == 0) {
+    GroupMeta gm;
+    gm.pt0 = pt0;
+    gm.np = pt1 - pt0;
+    gm.c0 = c0;
+    gm.nc = c1 - c0;
+    gm.len0 = gm.nseg0 = gm.obs0 = gm.nruns0 = 0;
+    d.grp_meta[g] = gm;
+  }
   for (int c = c0; c < c1; ++c) {
     const int nc = c1 - c0;
     const int obs0 = nc == 1 ? o_begin : o_begin + (c - c0) * SEG_CAP;
@@ -160,7 +171,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
         s.run[idx] = (uint16_t)run;
         if (flags & (1u << i)) {
           d.seg_cam[(size_t)c * SEG_CAP + seg] = (int32_t)(keys[i] >> 11);
-          d.seg_run0[(size_t)c * (SEG_CAP + 1) + seg] = (uint16_t)run;
+          d.seg_run0[(size_t)c * SEG_RUN_STRIDE + seg] = (uint16_t)run;
         }
         if ((idx % K) == 0) d.lane_run0[(size_t)c * RUN_LANES + idx / K] = (uint16_t)run;
       }
@@ -168,13 +179,20 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
     const int nseg = total.x, nruns = total.y;
     for (int sidx = nseg + tid; sidx < SEG_CAP; sidx += RUN_LANES) d.seg_cam[(size_t)c * SEG_CAP + sidx] = d.V;
     if (tid == 0) {
-      d.seg_run0[(size_t)c * (SEG_CAP + 1) + nseg] = (uint16_t)nruns;
+      d.seg_run0[(size_t)c * SEG_RUN_STRIDE + nseg] = (uint16_t)nruns;
       ChunkInfo ci;
       ci.obs0 = obs0;
       ci.len = len;
       ci.nseg = nseg;
       ci.nruns = nruns;
       d.chunk_info[c] = ci;
+      if (c == c0) {
+        GroupMeta* gm = d.grp_meta + g;
+        gm->len0 = len;
+        gm->nseg0 = nseg;
+        gm->obs0 = obs0;
+        gm->nruns0 = nruns;
+      }
     }
     __syncthreads();
     // records, lane-transposed: slot = k * RUN_LANES + lane  <->  sorted index lane * K + k
@@ -251,7 +269,7 @@ void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t tem
 // phase 2: records, tables and the camera CSR (chunk arrays allocated for `nchunks`)
 void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_bytes, int32_t* sort_keys_out,
                         int32_t* iota, cudaStream_t st, LaunchCounter& lc) {
-  if (d.G > 0 && nchunks > 0) {
+  if (d.G > 0) {
     k_chunk_build<<<d.G, RUN_LANES, 0, st>>>(d, bits_for(d.V > 0 ? d.V - 1 : 0));
     lc.launches++;
   }

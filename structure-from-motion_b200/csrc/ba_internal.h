@@ -33,6 +33,7 @@ constexpr int POINT_WEIGHT = 2;
 constexpr int GROUP_PT_CAP = GROUP_WEIGHT / POINT_WEIGHT;   // <= 512 points per group
 constexpr int SEG_CAP = 128;        // distinct cameras per chunk
 constexpr int RUN_CAP = RUN_LANES + SEG_CAP;            // runs per chunk (< 256)
+constexpr int SEG_RUN_STRIDE = SEG_CAP + 2;             // u16 entries per chunk in seg_run0 (4-byte aligned rows)
 constexpr int CAM_ACC = 64;         // doubles per camera accumulator row: A(28) S(28) g(7) pad(1)
 constexpr int MV_ACC = 12;          // doubles per matvec row: T[3][3] (c~ d^T), s[3]
 
@@ -61,9 +62,18 @@ struct Scalars {
   int32_t max_chunk_len; // index statistics (read back once per solve to size shared memory)
   int32_t max_runs;
   int32_t max_group_pts;
+  int32_t max_nseg;
   uint32_t ticket_a;     // "last block done" tickets of the multi-CTA PCG kernels
   uint32_t ticket_b;
   double costs[SFMBA_MAX_COST_HISTORY];
+};
+
+// One 32-byte load tells a tile CTA everything it needs to start staging its group.
+struct GroupMeta {
+  int32_t pt0, np;       // points [pt0, pt0 + np)
+  int32_t c0, nc;        // chunks [c0, c0 + nc)
+  int32_t len0, nseg0;   // first chunk: observations, distinct cameras
+  int32_t obs0, nruns0;  // first chunk: first observation, runs
 };
 
 struct ChunkInfo {
@@ -90,11 +100,12 @@ struct BaDev {
   int32_t* grp_pt;                    // [G+1]
   int32_t* grp_nchunk;                // [G]   chunks per group (scan input)
   int32_t* grp_chunk;                 // [G+1] first chunk of each group
+  GroupMeta* grp_meta;                // [G]
   ChunkInfo* chunk_info;              // [chunk_bound]
   double2* rec_b;                     // [chunk_bound][CHUNK_CAP] normalised observation, lane-transposed
   uint32_t* rec_ix;                   // [chunk_bound][CHUNK_CAP]
   int32_t* seg_cam;                   // [chunk_bound][SEG_CAP]   camera of each segment (V = unused)
-  uint16_t* seg_run0;                 // [chunk_bound][SEG_CAP+1] first run of each segment
+  uint16_t* seg_run0;                 // [chunk_bound][SEG_RUN_STRIDE] first run of each segment (+ end)
   uint16_t* lane_run0;                // [chunk_bound][RUN_LANES] first run of each lane
   int32_t* camrow_ptr;                // [V+1]  CSR: camera -> segment rows
   int32_t* camrow_idx;                // [chunk_bound*SEG_CAP] row ids sorted by camera
@@ -133,6 +144,7 @@ struct TileShape {                    // from the index statistics; sizes dynami
   int max_chunk_len = CHUNK_CAP;
   int max_runs = RUN_CAP;
   int max_group_pts = GROUP_PT_CAP;
+  int max_nseg = SEG_CAP;
 };
 
 // ---- index (ba_index.cu) ------------------------------------------------------------------------

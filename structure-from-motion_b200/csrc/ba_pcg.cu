@@ -80,58 +80,113 @@ __global__ void __launch_bounds__(128) k_cam_iter(BaDev d, const double* __restr
 }
 
 // ---- K3: matrix-free implicit-Schur matvec / back-substitution -----------------------------------
-// dynamic shared memory: Xs[3][pt_cap] | tacc[3][pt_cap] | un[max(3 slot_cap, run_cap MV_STRIDE)]
+// Everything a group needs is staged into shared memory up front with cp.async (points, D^-1, row
+// pointers, record words, segment cameras, run tables), then the camera constants of the chunk's
+// segments are gathered; the two passes touch global memory only to write their results.
 // BACKSUB: pass 1 with delta_p, then pts_j += v_j - D_j^-1 t_j        (ba_processor.py:405-406)
+struct MvShape {
+  int slot_cap, pt_cap, seg_cap, k_cap, un_doubles;
+};
+constexpr int CAMC = 26;   // doubles per staged camera row: R[9] C[3] E[9] w[3] wq pad
+
+__host__ __device__ inline size_t mv_smem_bytes(const MvShape& s) {
+  size_t dbl = (size_t)3 * s.pt_cap + 3 * s.pt_cap + 6 * s.pt_cap + s.un_doubles + (size_t)CAMC * s.seg_cap;
+  size_t b = dbl * 8;
+  b += (size_t)4 * (s.pt_cap + 4);                 // rowp
+  b += (size_t)4 * s.k_cap * RUN_LANES;            // ixs
+  b += (size_t)4 * ((s.seg_cap + 3) / 4 * 4);      // segc
+  b += (size_t)2 * (SEG_RUN_STRIDE + 6);           // srun (padded to 16 B)
+  b += (size_t)2 * RUN_LANES;                      // lrun
+  return b;
+}
+
 template <bool BACKSUB>
-__global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, int slot_cap, int pt_cap, int dvdc_quirk) {
+__global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, int dvdc_quirk) {
   extern __shared__ __align__(16) double smem[];
   if (!BACKSUB && d.sc->pcg_done) return;
-  double* Xs = smem;
-  double* tacc = Xs + 3 * pt_cap;
-  double* un = tacc + 3 * pt_cap;
-  const GroupRange gr = group_range(d, blockIdx.x);
+  const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
+  double* Xa = smem;                               // AoS [np][3]
+  double* tacc = Xa + 3 * pt_cap;                  // SoA [3][pt_cap]
+  double* Dn = tacc + 3 * pt_cap;                  // SoA [6][pt_cap]
+  double* un = Dn + 6 * pt_cap;
+  double* camc = un + sh.un_doubles;
+  ChunkStage cs;
+  cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * sh.seg_cap);
+  cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
+  cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (sh.seg_cap + 3) / 4 * 4);
+  cs.lrun = cs.srun + SEG_RUN_STRIDE + 6;
+  int32_t* rowp = reinterpret_cast<int32_t*>(cs.lrun + RUN_LANES);
   const int tid = threadIdx.x;
-  stage_points(d, gr, Xs, pt_cap);
-  for (int i = tid; i < 3 * pt_cap; i += RUN_LANES) tacc[i] = 0.0;
-  __syncthreads();
+  const GroupMeta gm = d.grp_meta[blockIdx.x];
+  const int np = gm.np, pt0 = gm.pt0, c0 = gm.c0, c1 = gm.c0 + gm.nc;
+  {
+    const size_t N = (size_t)d.N;
+    const double* src = d.pts + 3 * (size_t)pt0;
+    for (int i = tid; i < 3 * np; i += RUN_LANES) cp_async8(Xa + i, src + i);
+    for (int i = tid; i <= np; i += RUN_LANES) cp_async4(rowp + i, d.rowptr + pt0 + i);
+    for (int i = tid; i < 6 * np; i += RUN_LANES) {
+      const int e = i / np, j = i - e * np;
+      cp_async8(Dn + e * pt_cap + j, d.dinv + e * N + pt0 + j);
+    }
+    for (int i = tid; i < 3 * pt_cap; i += RUN_LANES) tacc[i] = 0.0;
+  }
+  ChunkInfo ci;
+  ci.obs0 = gm.obs0;
+  ci.len = gm.len0;
+  ci.nseg = gm.nseg0;
+  ci.nruns = gm.nruns0;
+  // stage one chunk: async tables, then gather the camera constants of its segments
+  auto stage = [&](int c, bool with_iter) {
+    stage_chunk_async(d, c, ci, cs);
+    cp_async_wait_all();
+    __syncthreads();
+    const int parts = with_iter ? 13 : 6;
+    for (int i = tid; i < ci.nseg * parts; i += RUN_LANES) {
+      const int s = i / parts, part = i - s * parts;
+      const int cam = cs.segc[s];
+      const double2 v = part < 6 ? reinterpret_cast<const double2*>(d.camtab + (size_t)CAMTAB_STRIDE * cam)[part]
+                                 : reinterpret_cast<const double2*>(d.camit + (size_t)CAMIT_STRIDE * cam)[part - 6];
+      reinterpret_cast<double2*>(camc + (size_t)CAMC * s)[part] = v;
+    }
+    __syncthreads();
+  };
   // ---- pass 1: t_j = sum_o J_x^T (J_p p_cam)
-  for (int c = gr.c0; c < gr.c1; ++c) {
-    const ChunkInfo ci = d.chunk_info[c];
+  for (int c = c0; c < c1; ++c) {
+    if (c > c0) ci = d.chunk_info[c];
+    stage(c, true);
     const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
-    const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
-    const int32_t* segcam = d.seg_cam + (size_t)c * SEG_CAP;
     double R[9], C[3], E[9], w[3], wq = 0.0;
-    uint32_t ix = ixp[0];
-    for (int k = 0; k < K && ix != REC_INVALID; ++k) {
-      const uint32_t ix_cur = ix;
-      ix = (k + 1 < K) ? ixp[(k + 1) * RUN_LANES] : REC_INVALID;
-      if (ix_cur & REC_RUNSTART) {
-        const int cam = segcam[rec_seg(ix_cur)];
-        load_cam_rc(d.camtab, cam, R, C);
-        const double2* it = reinterpret_cast<const double2*>(d.camit + (size_t)CAMIT_STRIDE * cam);
-        const double2 a = it[0], b = it[1], cc = it[2], e = it[3], f = it[4], g = it[5], h = it[6];
-        E[0] = a.x; E[1] = a.y; E[2] = b.x; E[3] = b.y; E[4] = cc.x; E[5] = cc.y; E[6] = e.x; E[7] = e.y; E[8] = f.x;
-        w[0] = f.y; w[1] = g.x; w[2] = g.y;
-        wq = h.x;
+    for (int k = 0; k < K; ++k) {
+      const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
+      if (ix == REC_INVALID) break;
+      if (ix & REC_RUNSTART) {
+        const double2* row = reinterpret_cast<const double2*>(camc + (size_t)CAMC * rec_seg(ix));
+        const double2 a = row[0], b = row[1], cc = row[2], e = row[3], f = row[4], g = row[5];
+        R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = cc.x; R[5] = cc.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
+        C[0] = f.y; C[1] = g.x; C[2] = g.y;
+        const double2 h = row[6], i2 = row[7], j2 = row[8], k2 = row[9], l2 = row[10], m2 = row[11], n2 = row[12];
+        E[0] = h.x; E[1] = h.y; E[2] = i2.x; E[3] = i2.y; E[4] = j2.x; E[5] = j2.y; E[6] = k2.x; E[7] = k2.y; E[8] = l2.x;
+        w[0] = l2.y; w[1] = m2.x; w[2] = m2.y;
+        wq = n2.x;
       }
-      const int ptl = rec_ptl(ix_cur);
-      const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
+      const int ptl = rec_ptl(ix);
+      const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double g0 = E[0] * pr.d0 + E[1] * pr.d1 + E[2] * pr.d2 - w[0];
       const double g1 = E[3] * pr.d0 + E[4] * pr.d1 + E[5] * pr.d2 - w[1];
       const double g2 = E[6] * pr.d0 + E[7] * pr.d1 + E[8] * pr.d2 - w[2];
       const double a0 = pr.iw * (g0 - pr.u * g2);
       const double a1 = pr.iw * (g1 - pr.v * (g2 + wq));
-      const double c0 = pr.iw * a0, c1 = pr.iw * a1;
-      const double c2 = -(pr.u * c0 + pr.v * c1);
-      double* s = un + rec_pos(ix_cur);
-      s[0] = R[0] * c0 + R[1] * c1 + R[2] * c2;
-      s[slot_cap] = R[3] * c0 + R[4] * c1 + R[5] * c2;
-      s[2 * slot_cap] = R[6] * c0 + R[7] * c1 + R[8] * c2;
+      const double q0 = pr.iw * a0, q1 = pr.iw * a1;
+      const double q2 = -(pr.u * q0 + pr.v * q1);
+      double* s = un + rec_pos(ix);
+      s[0] = R[0] * q0 + R[1] * q1 + R[2] * q2;
+      s[slot_cap] = R[3] * q0 + R[4] * q1 + R[5] * q2;
+      s[2 * slot_cap] = R[6] * q0 + R[7] * q1 + R[8] * q2;
     }
     __syncthreads();
-    for (int j = tid; j < gr.np; j += RUN_LANES) {
-      int lo, hi;
-      point_slots(d, gr.pt0 + j, ci, lo, hi);
+    for (int j = tid; j < np; j += RUN_LANES) {
+      const int lo = max(rowp[j], ci.obs0) - ci.obs0;
+      const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
       if (lo < hi) {
         double t0 = tacc[j], t1 = tacc[pt_cap + j], t2 = tacc[2 * pt_cap + j];
         for (int s = lo; s < hi; ++s) {
@@ -147,47 +202,46 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, int slot_cap, 
     __syncthreads();
   }
   // ---- u_j = D_j^-1 t_j
-  {
-    const size_t N = (size_t)d.N;
-    for (int j = tid; j < gr.np; j += RUN_LANES) {
-      const size_t pt = (size_t)gr.pt0 + j;
-      double Dinv[6], t[3], u[3];
+  cp_async_wait_all();
+  __syncthreads();
+  for (int j = tid; j < np; j += RUN_LANES) {
+    double Dinv[6], t[3], u[3];
 #pragma unroll
-      for (int e = 0; e < 6; ++e) Dinv[e] = d.dinv[e * N + pt];
-      t[0] = tacc[j];
-      t[1] = tacc[pt_cap + j];
-      t[2] = tacc[2 * pt_cap + j];
-      sym3_mul(Dinv, t, u);
-      if (BACKSUB) {
-        double* p = d.pts + 3 * pt;
+    for (int e = 0; e < 6; ++e) Dinv[e] = Dn[e * pt_cap + j];
+    t[0] = tacc[j];
+    t[1] = tacc[pt_cap + j];
+    t[2] = tacc[2 * pt_cap + j];
+    sym3_mul(Dinv, t, u);
+    if (BACKSUB) {
+      const size_t N = (size_t)d.N, pt = (size_t)pt0 + j;
+      double* p = d.pts + 3 * pt;
 #pragma unroll
-        for (int e = 0; e < 3; ++e) p[e] += d.vj[e * N + pt] - u[e];
-      } else {
-        tacc[j] = u[0];
-        tacc[pt_cap + j] = u[1];
-        tacc[2 * pt_cap + j] = u[2];
-      }
+      for (int e = 0; e < 3; ++e) p[e] = Xa[3 * j + e] + (d.vj[e * N + pt] - u[e]);
+    } else {
+      tacc[j] = u[0];
+      tacc[pt_cap + j] = u[1];
+      tacc[2 * pt_cap + j] = u[2];
     }
   }
   if (BACKSUB) return;
   __syncthreads();
   // ---- pass 2: per camera sums of c~ d^T and c'
   const double sgn = dvdc_quirk ? 1.0 : -1.0;
-  for (int c = gr.c0; c < gr.c1; ++c) {
-    const ChunkInfo ci = d.chunk_info[c];
+  for (int c = c0; c < c1; ++c) {
+    if (gm.nc > 1) {                       // single-chunk groups still hold their chunk from pass 1
+      ci = d.chunk_info[c];
+      stage(c, false);
+    }
     const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
-    const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
-    const int32_t* segcam = d.seg_cam + (size_t)c * SEG_CAP;
     double R[9], C[3];
     double acc[MV_ACC];
-    int run = (int)d.lane_run0[(size_t)c * RUN_LANES + tid] - 1;
-    const uint32_t ix_first = ixp[0];
-    uint32_t ix = ix_first;
-    for (int k = 0; k < K && ix != REC_INVALID; ++k) {
-      const uint32_t ix_cur = ix;
-      ix = (k + 1 < K) ? ixp[(k + 1) * RUN_LANES] : REC_INVALID;
-      if (ix_cur & REC_RUNSTART) {
-        if (k > 0) {
+    int run = (int)cs.lrun[tid] - 1;
+    bool any = false;
+    for (int k = 0; k < K; ++k) {
+      const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
+      if (ix == REC_INVALID) break;
+      if (ix & REC_RUNSTART) {
+        if (any) {
           double* dst = un + run * MV_STRIDE;
 #pragma unroll
           for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
@@ -195,10 +249,14 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, int slot_cap, 
         ++run;
 #pragma unroll
         for (int e = 0; e < MV_ACC; ++e) acc[e] = 0.0;
-        load_cam_rc(d.camtab, segcam[rec_seg(ix_cur)], R, C);
+        const double2* row = reinterpret_cast<const double2*>(camc + (size_t)CAMC * rec_seg(ix));
+        const double2 a = row[0], b = row[1], cc = row[2], e = row[3], f = row[4], g = row[5];
+        R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = cc.x; R[5] = cc.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
+        C[0] = f.y; C[1] = g.x; C[2] = g.y;
       }
-      const int ptl = rec_ptl(ix_cur);
-      const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
+      any = true;
+      const int ptl = rec_ptl(ix);
+      const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double u0 = tacc[ptl], u1 = tacc[pt_cap + ptl], u2 = tacc[2 * pt_cap + ptl];
       const double e0 = R[0] * u0 + R[3] * u1 + R[6] * u2;
       const double e1 = R[1] * u0 + R[4] * u1 + R[7] * u2;
@@ -214,16 +272,15 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, int slot_cap, 
       acc[10] += ct1;
       acc[11] += sgn * pr.v * ct1 - pr.u * ct0;
     }
-    if (ix_first != REC_INVALID) {
+    if (any) {
       double* dst = un + run * MV_STRIDE;
 #pragma unroll
       for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
     }
     __syncthreads();
-    const uint16_t* run0 = d.seg_run0 + (size_t)c * (SEG_CAP + 1);
     for (int idx = tid; idx < ci.nseg * MV_ACC; idx += RUN_LANES) {
-      const int s = idx / MV_ACC, e = idx % MV_ACC;
-      const int ra = run0[s], rb = run0[s + 1];
+      const int s = idx / MV_ACC, e = idx - s * MV_ACC;
+      const int ra = cs.srun[s], rb = cs.srun[s + 1];
       double a = 0.0;
       for (int rr = ra; rr < rb; ++rr) a += un[rr * MV_STRIDE + e];
       d.part12[((size_t)c * SEG_CAP + s) * MV_ACC + e] = a;
@@ -492,10 +549,15 @@ __global__ void k_lm_decide(BaDev d, double lam_min, double lam_max) {
 }
 
 
-static size_t matvec_smem(const TileShape& ts) {
-  const size_t un = (size_t)3 * ts.max_chunk_len > (size_t)ts.max_runs * MV_STRIDE ? (size_t)3 * ts.max_chunk_len
-                                                                                   : (size_t)ts.max_runs * MV_STRIDE;
-  return ((size_t)6 * ts.max_group_pts + un) * sizeof(double);
+static MvShape matvec_shape(const TileShape& ts) {
+  MvShape sh;
+  sh.slot_cap = ts.max_chunk_len;
+  sh.pt_cap = (ts.max_group_pts + 1) & ~1;
+  sh.seg_cap = ts.max_nseg;
+  sh.k_cap = (ts.max_chunk_len + RUN_LANES - 1) / RUN_LANES;
+  const int a = 3 * ts.max_chunk_len, bb = ts.max_runs * MV_STRIDE;
+  sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
+  return sh;
 }
 
 void launch_pcg_init(const BaDev& d, unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
@@ -512,13 +574,14 @@ void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc) {
   if (d.G <= 0) return;
-  const size_t smem = matvec_smem(ts);
+  const MvShape sh = matvec_shape(ts);
+  const size_t smem = mv_smem_bytes(sh);
   if (backsub) {
     cudaFuncSetAttribute(k_matvec<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_matvec<true><<<d.G, RUN_LANES, smem, st>>>(d, ts.max_chunk_len, ts.max_group_pts, dvdc_quirk ? 1 : 0);
+    k_matvec<true><<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
   } else {
     cudaFuncSetAttribute(k_matvec<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_matvec<false><<<d.G, RUN_LANES, smem, st>>>(d, ts.max_chunk_len, ts.max_group_pts, dvdc_quirk ? 1 : 0);
+    k_matvec<false><<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
   }
   lc.launches++;
 }

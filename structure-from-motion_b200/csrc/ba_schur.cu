@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, int pt_cap, i
     }
     __syncthreads();
     // per segment: sum its runs in run order -> one 64-double row
-    const uint16_t* run0 = d.seg_run0 + (size_t)c * (SEG_CAP + 1);
+    const uint16_t* run0 = d.seg_run0 + (size_t)c * SEG_RUN_STRIDE;
     for (int idx = tid; idx < ci.nseg * CAM_ACC; idx += RUN_LANES) {
       const int s = idx / CAM_ACC, e = idx % CAM_ACC;
       double a = 0.0;
