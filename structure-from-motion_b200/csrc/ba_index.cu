@@ -31,21 +31,38 @@ __global__ void k_group_bounds(BaDev d) {
 
 constexpr int HASH_SLOTS = 4096;
 
-// chunks per group: one chunk unless the group overflows CHUNK_CAP or touches > SEG_CAP cameras
+// lanes a chunk needs when every camera's observations are cut into runs of K
+__device__ __forceinline__ int lanes_needed(const int* cnt, int K, int* s_sum) {
+  int mine = 0;
+  for (int i = threadIdx.x; i < HASH_SLOTS; i += blockDim.x) mine += (cnt[i] + K - 1) / K;
+  __syncthreads();
+  if (threadIdx.x == 0) *s_sum = 0;
+  __syncthreads();
+  if (mine) atomicAdd(s_sum, mine);
+  __syncthreads();
+  return *s_sum;
+}
+
+// chunks per group: one chunk when some K <= CHUNK_K_MAX fits the group into RUN_LANES lanes and
+// SEG_CAP cameras, otherwise SEG_CAP-observation chunks with one observation per lane
 __global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chunks) {
-  __shared__ int s_hash[HASH_SLOTS];
-  __shared__ int s_distinct;
+  __shared__ int s_key[HASH_SLOTS];
+  __shared__ int s_cnt[HASH_SLOTS];
+  __shared__ int s_distinct, s_sum;
   const int g = blockIdx.x;
   const int pt0 = d.grp_pt[g], pt1 = d.grp_pt[g + 1];
   const int o0 = d.rowptr[pt0], o1 = d.rowptr[pt1];
   const int L = o1 - o0;
-  int n;
+  int n, K = 1;
   if (L == 0) {
     n = 0;
   } else if (fine_chunks || L > CHUNK_CAP) {
     n = (L + SEG_CAP - 1) / SEG_CAP;
   } else {
-    for (int i = threadIdx.x; i < HASH_SLOTS; i += blockDim.x) s_hash[i] = -1;
+    for (int i = threadIdx.x; i < HASH_SLOTS; i += blockDim.x) {
+      s_key[i] = -1;
+      s_cnt[i] = 0;
+    }
     if (threadIdx.x == 0) s_distinct = 0;
     __syncthreads();
     int mine = 0;
@@ -53,32 +70,42 @@ __global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chu
       const int cam = d.obs_cam[o0 + i];
       unsigned h = ((unsigned)cam * 2654435761u) >> 20;
       for (;;) {
-        const int prev = atomicCAS(&s_hash[h & (HASH_SLOTS - 1)], -1, cam);
-        if (prev == -1) {
-          ++mine;
+        const int slot = h & (HASH_SLOTS - 1);
+        const int prev = atomicCAS(&s_key[slot], -1, cam);
+        if (prev == -1 || prev == cam) {
+          if (prev == -1) ++mine;
+          atomicAdd(&s_cnt[slot], 1);
           break;
         }
-        if (prev == cam) break;
         ++h;
       }
     }
     if (mine) atomicAdd(&s_distinct, mine);
     __syncthreads();
-    n = s_distinct <= SEG_CAP ? 1 : (L + SEG_CAP - 1) / SEG_CAP;
+    n = (L + SEG_CAP - 1) / SEG_CAP;
+    if (s_distinct <= SEG_CAP) {
+      for (K = (L + RUN_LANES - 1) / RUN_LANES; K <= CHUNK_K_MAX; ++K) {
+        if (lanes_needed(s_cnt, K, &s_sum) <= RUN_LANES) {
+          n = 1;
+          break;
+        }
+      }
+    }
+    if (n != 1) K = 1;
     if (threadIdx.x == 0 && n == 1) {
-      const int K = (L + RUN_LANES - 1) / RUN_LANES;
       atomicMax(&d.sc->max_chunk_len, L);
-      atomicMax(&d.sc->max_runs, (L + K - 1) / K + s_distinct);
       atomicMax(&d.sc->max_nseg, s_distinct);
+      atomicMax(&d.sc->max_k, K);
     }
   }
   if (threadIdx.x == 0) {
     d.grp_nchunk[g] = n;
+    d.grp_K[g] = K;
     atomicMax(&d.sc->max_group_pts, pt1 - pt0);
-    if (n > 1) {
-      atomicMax(&d.sc->max_chunk_len, SEG_CAP);
-      atomicMax(&d.sc->max_runs, SEG_CAP);
-      atomicMax(&d.sc->max_nseg, SEG_CAP);
+    if (n > 1 || (n == 1 && K == 1 && L <= SEG_CAP)) {
+      atomicMax(&d.sc->max_chunk_len, L < SEG_CAP ? L : SEG_CAP);
+      atomicMax(&d.sc->max_nseg, L < SEG_CAP ? L : SEG_CAP);
+      atomicMax(&d.sc->max_k, 1);
     }
   }
 }
@@ -92,14 +119,16 @@ __global__ void k_finish_scan(BaDev d) {
 
 struct BuildSmem {
   uint32_t key[CHUNK_CAP];
-  uint16_t seg[CHUNK_CAP];
-  uint16_t run[CHUNK_CAP];
+  uint16_t seg[CHUNK_CAP];          // segment of each sorted position
+  int seg_start[SEG_CAP + 1];       // first sorted position of each segment (+ end)
+  int seg_lane0[SEG_CAP + 1];       // first lane of each segment (+ end)
+  uint16_t lane_seg[RUN_LANES];
 };
 
-// one CTA per group: sort each chunk by camera, emit records and tables
+// one CTA per group: sort each chunk by camera, cut segments into runs of K, emit records and tables
 __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits) {
   using Sort = cub::BlockRadixSort<uint32_t, RUN_LANES, CHUNK_K_MAX>;
-  using Scan = cub::BlockScan<int2, RUN_LANES>;
+  using Scan = cub::BlockScan<int, RUN_LANES>;
   __shared__ union {
     typename Sort::TempStorage sort;
     typename Scan::TempStorage scan;
@@ -109,21 +138,22 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
   const int pt0 = d.grp_pt[g], pt1 = d.grp_pt[g + 1];
   const int c0 = d.grp_chunk[g], c1 = d.grp_chunk[g + 1];
   const int o_begin = d.rowptr[pt0], o_end = d.rowptr[pt1];
+  const int nc = c1 - c0;
+  const int K = nc == 1 ? d.grp_K[g] : 1;
   const int tid = threadIdx.x;
   if (tid == 0) {
     GroupMeta gm;
     gm.pt0 = pt0;
     gm.np = pt1 - pt0;
     gm.c0 = c0;
-    gm.nc = c1 - c0;
-    gm.len0 = gm.nseg0 = gm.obs0 = gm.nruns0 = 0;
+    gm.nc = nc;
+    gm.len0 = gm.nseg0 = gm.obs0 = 0;
+    gm.K0 = 1;
     d.grp_meta[g] = gm;
   }
   for (int c = c0; c < c1; ++c) {
-    const int nc = c1 - c0;
     const int obs0 = nc == 1 ? o_begin : o_begin + (c - c0) * SEG_CAP;
     const int len = nc == 1 ? (o_end - o_begin) : min(SEG_CAP, o_end - obs0);
-    const int K = (len + RUN_LANES - 1) / RUN_LANES;
     uint32_t keys[CHUNK_K_MAX];
 #pragma unroll
     for (int i = 0; i < CHUNK_K_MAX; ++i) {
@@ -131,87 +161,90 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
       keys[i] = idx < len ? (((uint32_t)d.obs_cam[obs0 + idx] << 11) | (uint32_t)idx) : 0xffffffffu;
     }
     Sort(tmp.sort).Sort(keys, 0, 11 + cam_bits);
-    // heads / run starts of my 10 consecutive sorted items
-    uint32_t prev_cam;
 #pragma unroll
     for (int i = 0; i < CHUNK_K_MAX; ++i) s.key[tid * CHUNK_K_MAX + i] = keys[i];
     __syncthreads();
-    prev_cam = tid == 0 ? 0xffffffffu : (s.key[tid * CHUNK_K_MAX - 1] >> 11);
-    int2 cnt = make_int2(0, 0);   // (heads, run starts) among my items
-    uint32_t flags = 0;           // bit i: head, bit 16+i: run start
+    // segment heads among my consecutive sorted items
+    uint32_t prev_cam = tid == 0 ? 0xffffffffu : (s.key[tid * CHUNK_K_MAX - 1] >> 11);
+    int heads = 0;
+    uint32_t flags = 0;
 #pragma unroll
     for (int i = 0; i < CHUNK_K_MAX; ++i) {
       const int idx = tid * CHUNK_K_MAX + i;
       if (idx < len) {
         const uint32_t cam = keys[i] >> 11;
-        const bool head = idx == 0 || cam != prev_cam;
-        const bool rs = head || (idx % K) == 0;
-        if (head) {
-          ++cnt.x;
+        if (idx == 0 || cam != prev_cam) {
+          ++heads;
           flags |= 1u << i;
-        }
-        if (rs) {
-          ++cnt.y;
-          flags |= 1u << (16 + i);
         }
         prev_cam = cam;
       }
     }
-    int2 excl, total;
-    Scan(tmp.scan).ExclusiveScan(cnt, excl, make_int2(0, 0),
-                                 [](const int2& a, const int2& b) { return make_int2(a.x + b.x, a.y + b.y); }, total);
-    int seg = excl.x - 1, run = excl.y - 1;
+    int excl, nseg;
+    Scan(tmp.scan).ExclusiveSum(heads, excl, nseg);
+    int seg = excl - 1;
 #pragma unroll
     for (int i = 0; i < CHUNK_K_MAX; ++i) {
       const int idx = tid * CHUNK_K_MAX + i;
       if (idx < len) {
-        if (flags & (1u << i)) ++seg;
-        if (flags & (1u << (16 + i))) ++run;
-        s.seg[idx] = (uint16_t)seg;
-        s.run[idx] = (uint16_t)run;
         if (flags & (1u << i)) {
+          ++seg;
+          s.seg_start[seg] = idx;
           d.seg_cam[(size_t)c * SEG_CAP + seg] = (int32_t)(keys[i] >> 11);
-          d.seg_run0[(size_t)c * SEG_RUN_STRIDE + seg] = (uint16_t)run;
         }
-        if ((idx % K) == 0) d.lane_run0[(size_t)c * RUN_LANES + idx / K] = (uint16_t)run;
+        s.seg[idx] = (uint16_t)seg;
       }
     }
-    const int nseg = total.x, nruns = total.y;
+    if (tid == 0) s.seg_start[nseg] = len;
     for (int sidx = nseg + tid; sidx < SEG_CAP; sidx += RUN_LANES) d.seg_cam[(size_t)c * SEG_CAP + sidx] = d.V;
+    __syncthreads();
+    // lanes per segment -> first lane of each segment
+    const int nl = tid < nseg ? (s.seg_start[tid + 1] - s.seg_start[tid] + K - 1) / K : 0;
+    int lane0, nlanes;
+    __syncthreads();
+    Scan(tmp.scan).ExclusiveSum(nl, lane0, nlanes);
+    if (tid < nseg) {
+      s.seg_lane0[tid] = lane0;
+      d.seg_lane0[(size_t)c * SEG_RUN_STRIDE + tid] = (uint16_t)lane0;
+      for (int j = 0; j < nl; ++j) s.lane_seg[lane0 + j] = (uint16_t)tid;
+    }
     if (tid == 0) {
-      d.seg_run0[(size_t)c * SEG_RUN_STRIDE + nseg] = (uint16_t)nruns;
+      s.seg_lane0[nseg] = nlanes;
+      d.seg_lane0[(size_t)c * SEG_RUN_STRIDE + nseg] = (uint16_t)nlanes;
       ChunkInfo ci;
       ci.obs0 = obs0;
       ci.len = len;
       ci.nseg = nseg;
-      ci.nruns = nruns;
+      ci.K = K;
       d.chunk_info[c] = ci;
       if (c == c0) {
         GroupMeta* gm = d.grp_meta + g;
         gm->len0 = len;
         gm->nseg0 = nseg;
         gm->obs0 = obs0;
-        gm->nruns0 = nruns;
+        gm->K0 = K;
       }
     }
     __syncthreads();
-    // records, lane-transposed: slot = k * RUN_LANES + lane  <->  sorted index lane * K + k
+    // records, lane-transposed: slot = k * RUN_LANES + lane; lane = run (K sorted observations of ONE camera)
     for (int slot = tid; slot < K * RUN_LANES; slot += RUN_LANES) {
       const int k = slot / RUN_LANES, lane = slot % RUN_LANES;
-      const int idx = lane * K + k;
       uint32_t ix = REC_INVALID;
       double2 b = make_double2(0.0, 0.0);
-      if (k < K && idx < len && idx < (lane + 1) * K) {
-        const uint32_t key = s.key[idx];
-        const int pos = (int)(key & 2047u);
-        const int cam = (int)(key >> 11);
-        const int o = obs0 + pos;
-        const int ptl = d.obs_pt[o] - pt0;
-        const bool rs = idx == 0 || (idx % K) == 0 || s.seg[idx] != s.seg[idx - 1];
-        ix = (uint32_t)ptl | ((uint32_t)pos << 10) | ((uint32_t)s.seg[idx] << 21) | (rs ? REC_RUNSTART : 0u);
-        double bb[2];
-        normalise_obs(d.kinv ? d.kinv + 9 * (size_t)cam : nullptr, d.obs_uv[o], d.obs_uv[d.m + o], bb);
-        b = make_double2(bb[0], bb[1]);
+      if (lane < nlanes) {
+        const int sg = s.lane_seg[lane];
+        const int idx = s.seg_start[sg] + (lane - s.seg_lane0[sg]) * K + k;
+        if (idx < s.seg_start[sg + 1]) {
+          const uint32_t key = s.key[idx];
+          const int pos = (int)(key & 2047u);
+          const int cam = (int)(key >> 11);
+          const int o = obs0 + pos;
+          const int ptl = d.obs_pt[o] - pt0;
+          ix = (uint32_t)ptl | ((uint32_t)pos << 10) | ((uint32_t)sg << 21);
+          double bb[2];
+          normalise_obs(d.kinv ? d.kinv + 9 * (size_t)cam : nullptr, d.obs_uv[o], d.obs_uv[d.m + o], bb);
+          b = make_double2(bb[0], bb[1]);
+        }
       }
       d.rec_ix[(size_t)c * CHUNK_CAP + slot] = ix;
       d.rec_b[(size_t)c * CHUNK_CAP + slot] = b;

@@ -6,12 +6,14 @@
 //   chunk  = <= CHUNK_CAP consecutive (point-major) observations of a group.  A group is one chunk
 //            unless it overflows (a very long track) or touches more than SEG_CAP cameras, in which
 //            case it is cut into SEG_CAP-observation chunks.
-//   Inside a chunk the observations are sorted by camera ("segments"); lane r of the CTA walks the
-//   K = ceil(len / RUN_LANES) sorted observations [r K, (r+1) K).  A maximal same-camera stretch of
-//   one lane is a "run": camera constants live in registers for the whole run and the camera-side
-//   sums of a run accumulate in registers, so the per-observation work is pure FP64 arithmetic.
-//   Records are stored lane-transposed ([k][lane]) so every load is coalesced.
-//   Camera-side sums: run -> (shared memory) -> segment row in HBM -> per-camera sum, all in a
+//   Inside a chunk the observations are sorted by camera ("segments").  Every segment is cut into
+//   runs of K consecutive sorted observations (the last run of a segment may be shorter) and every
+//   run belongs to exactly one lane of the CTA; K is the smallest value for which the chunk needs at
+//   most RUN_LANES lanes.  A lane therefore sees ONE camera: its constants are loaded once into
+//   registers, the camera-side sums of the run accumulate in registers, and the per-observation work
+//   is pure FP64 arithmetic without divergence.  Records are stored lane-transposed ([k][lane]) so
+//   every load is coalesced.
+//   Camera-side sums: lane -> (shared memory) -> segment row in HBM -> per-camera sum, all in a
 //   fixed order (bitwise reproducible, no atomics on data).
 #pragma once
 #include <cuda_runtime.h>
@@ -26,20 +28,18 @@ namespace sfmba {
 constexpr int CAMTAB_STRIDE = 16;   // doubles per camera-table row: R[9] row-major, C[3], qj[4]
 constexpr int CAMIT_STRIDE = 16;    // doubles per PCG-iteration camera row: E[9], w[3], wq, pad[3]
 constexpr int RUN_LANES = 128;      // threads per tile CTA = lanes per chunk
-constexpr int CHUNK_K_MAX = 10;     // sorted observations per lane
-constexpr int CHUNK_CAP = RUN_LANES * CHUNK_K_MAX;   // 1280 observations per chunk
+constexpr int CHUNK_K_MAX = 12;     // sorted observations per lane
+constexpr int CHUNK_CAP = RUN_LANES * CHUNK_K_MAX;   // 1536 record slots per chunk
 constexpr int GROUP_WEIGHT = 1024;  // bucket width of (rowptr[j] + 2 j)
 constexpr int POINT_WEIGHT = 2;
 constexpr int GROUP_PT_CAP = GROUP_WEIGHT / POINT_WEIGHT;   // <= 512 points per group
 constexpr int SEG_CAP = 128;        // distinct cameras per chunk
-constexpr int RUN_CAP = RUN_LANES + SEG_CAP;            // runs per chunk (< 256)
-constexpr int SEG_RUN_STRIDE = SEG_CAP + 2;             // u16 entries per chunk in seg_run0 (4-byte aligned rows)
+constexpr int SEG_RUN_STRIDE = SEG_CAP + 2;             // u16 entries per chunk in seg_lane0 (4-byte aligned rows)
 constexpr int CAM_ACC = 64;         // doubles per camera accumulator row: A(28) S(28) g(7) pad(1)
 constexpr int MV_ACC = 12;          // doubles per matvec row: T[3][3] (c~ d^T), s[3]
 
-// record index word: ptl[0:10) pos[10:21) seg[21:28) runstart[28]
+// record index word: ptl[0:10) pos[10:21) seg[21:28)
 constexpr uint32_t REC_INVALID = 0xffffffffu;
-constexpr uint32_t REC_RUNSTART = 1u << 28;
 __host__ __device__ __forceinline__ uint32_t rec_ptl(uint32_t ix) { return ix & 1023u; }
 __host__ __device__ __forceinline__ uint32_t rec_pos(uint32_t ix) { return (ix >> 10) & 2047u; }
 __host__ __device__ __forceinline__ uint32_t rec_seg(uint32_t ix) { return (ix >> 21) & 127u; }
@@ -60,9 +60,9 @@ struct Scalars {
   int32_t lm_last_accepted;
   uint32_t flags;
   int32_t max_chunk_len; // index statistics (read back once per solve to size shared memory)
-  int32_t max_runs;
   int32_t max_group_pts;
   int32_t max_nseg;
+  int32_t max_k;
   uint32_t ticket_a;     // "last block done" tickets of the multi-CTA PCG kernels
   uint32_t ticket_b;
   double costs[SFMBA_MAX_COST_HISTORY];
@@ -73,14 +73,14 @@ struct GroupMeta {
   int32_t pt0, np;       // points [pt0, pt0 + np)
   int32_t c0, nc;        // chunks [c0, c0 + nc)
   int32_t len0, nseg0;   // first chunk: observations, distinct cameras
-  int32_t obs0, nruns0;  // first chunk: first observation, runs
+  int32_t obs0, K0;      // first chunk: first observation, observations per lane
 };
 
 struct ChunkInfo {
   int32_t obs0;          // first (point-major) observation
   int32_t len;           // observations
   int32_t nseg;          // distinct cameras
-  int32_t nruns;
+  int32_t K;             // observations per lane
 };
 
 // Device view of one BA problem plus its workspace.  Plain pointers so kernels take it by value.
@@ -99,14 +99,14 @@ struct BaDev {
   // index
   int32_t* grp_pt;                    // [G+1]
   int32_t* grp_nchunk;                // [G]   chunks per group (scan input)
+  int32_t* grp_K;                     // [G]   observations per lane of a single-chunk group
   int32_t* grp_chunk;                 // [G+1] first chunk of each group
   GroupMeta* grp_meta;                // [G]
   ChunkInfo* chunk_info;              // [chunk_bound]
   double2* rec_b;                     // [chunk_bound][CHUNK_CAP] normalised observation, lane-transposed
   uint32_t* rec_ix;                   // [chunk_bound][CHUNK_CAP]
   int32_t* seg_cam;                   // [chunk_bound][SEG_CAP]   camera of each segment (V = unused)
-  uint16_t* seg_run0;                 // [chunk_bound][SEG_RUN_STRIDE] first run of each segment (+ end)
-  uint16_t* lane_run0;                // [chunk_bound][RUN_LANES] first run of each lane
+  uint16_t* seg_lane0;                // [chunk_bound][SEG_RUN_STRIDE] first lane of each segment (+ end)
   int32_t* camrow_ptr;                // [V+1]  CSR: camera -> segment rows
   int32_t* camrow_idx;                // [chunk_bound*SEG_CAP] row ids sorted by camera
   // linearisation
@@ -142,9 +142,9 @@ struct LaunchCounter {
 
 struct TileShape {                    // from the index statistics; sizes dynamic shared memory
   int max_chunk_len = CHUNK_CAP;
-  int max_runs = RUN_CAP;
   int max_group_pts = GROUP_PT_CAP;
   int max_nseg = SEG_CAP;
+  int max_k = CHUNK_K_MAX;
 };
 
 // ---- index (ba_index.cu) ------------------------------------------------------------------------

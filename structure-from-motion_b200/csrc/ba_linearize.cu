@@ -52,13 +52,13 @@ __global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, int slot_cap, int 
   uint32_t flags = 0;
   for (int c = gr.c0; c < gr.c1; ++c) {
     const ChunkInfo ci = d.chunk_info[c];
-    const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
+    const int K = ci.K;
     const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
     const double2* bp = d.rec_b + (size_t)c * CHUNK_CAP + tid;
-    const int32_t* segcam = d.seg_cam + (size_t)c * SEG_CAP;
     double R[9], C[3];
     uint32_t ix = ixp[0];
     double2 b = bp[0];
+    if (ix != REC_INVALID) load_cam_rc(d.camtab, d.seg_cam[(size_t)c * SEG_CAP + rec_seg(ix)], R, C);   // one camera per lane
     for (int k = 0; k < K && ix != REC_INVALID; ++k) {
       const uint32_t ix_cur = ix;
       const double2 b_cur = b;
@@ -68,7 +68,6 @@ __global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, int slot_cap, int 
       } else {
         ix = REC_INVALID;
       }
-      if (ix_cur & REC_RUNSTART) load_cam_rc(d.camtab, segcam[rec_seg(ix_cur)], R, C);
       const int ptl = rec_ptl(ix_cur);
       const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
       if (!pr.ok) flags |= FLAG_DEPTH_ZERO;

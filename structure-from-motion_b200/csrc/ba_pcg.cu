@@ -96,7 +96,6 @@ __host__ __device__ inline size_t mv_smem_bytes(const MvShape& s) {
   b += (size_t)4 * s.k_cap * RUN_LANES;            // ixs
   b += (size_t)4 * ((s.seg_cap + 3) / 4 * 4);      // segc
   b += (size_t)2 * (SEG_RUN_STRIDE + 6);           // srun (padded to 16 B)
-  b += (size_t)2 * RUN_LANES;                      // lrun
   return b;
 }
 
@@ -114,8 +113,7 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
   cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * sh.seg_cap);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
   cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (sh.seg_cap + 3) / 4 * 4);
-  cs.lrun = cs.srun + SEG_RUN_STRIDE + 6;
-  int32_t* rowp = reinterpret_cast<int32_t*>(cs.lrun + RUN_LANES);
+  int32_t* rowp = reinterpret_cast<int32_t*>(cs.srun + SEG_RUN_STRIDE + 6);
   const int tid = threadIdx.x;
   const GroupMeta gm = d.grp_meta[blockIdx.x];
   const int np = gm.np, pt0 = gm.pt0, c0 = gm.c0, c1 = gm.c0 + gm.nc;
@@ -134,7 +132,7 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
   ci.obs0 = gm.obs0;
   ci.len = gm.len0;
   ci.nseg = gm.nseg0;
-  ci.nruns = gm.nruns0;
+  ci.K = gm.K0;
   // stage one chunk: async tables, then gather the camera constants of its segments
   auto stage = [&](int c, bool with_iter) {
     stage_chunk_async(d, c, ci, cs);
@@ -154,21 +152,22 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
   for (int c = c0; c < c1; ++c) {
     if (c > c0) ci = d.chunk_info[c];
     stage(c, true);
-    const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
+    const int K = ci.K;
     double R[9], C[3], E[9], w[3], wq = 0.0;
+    const uint32_t ix_first = cs.ixs[tid];
+    if (ix_first != REC_INVALID) {                         // one camera per lane
+      const double2* row = reinterpret_cast<const double2*>(camc + (size_t)CAMC * rec_seg(ix_first));
+      const double2 a = row[0], b = row[1], cc = row[2], e = row[3], f = row[4], g = row[5];
+      R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = cc.x; R[5] = cc.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
+      C[0] = f.y; C[1] = g.x; C[2] = g.y;
+      const double2 h = row[6], i2 = row[7], j2 = row[8], k2 = row[9], l2 = row[10], m2 = row[11], n2 = row[12];
+      E[0] = h.x; E[1] = h.y; E[2] = i2.x; E[3] = i2.y; E[4] = j2.x; E[5] = j2.y; E[6] = k2.x; E[7] = k2.y; E[8] = l2.x;
+      w[0] = l2.y; w[1] = m2.x; w[2] = m2.y;
+      wq = n2.x;
+    }
     for (int k = 0; k < K; ++k) {
       const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
       if (ix == REC_INVALID) break;
-      if (ix & REC_RUNSTART) {
-        const double2* row = reinterpret_cast<const double2*>(camc + (size_t)CAMC * rec_seg(ix));
-        const double2 a = row[0], b = row[1], cc = row[2], e = row[3], f = row[4], g = row[5];
-        R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = cc.x; R[5] = cc.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
-        C[0] = f.y; C[1] = g.x; C[2] = g.y;
-        const double2 h = row[6], i2 = row[7], j2 = row[8], k2 = row[9], l2 = row[10], m2 = row[11], n2 = row[12];
-        E[0] = h.x; E[1] = h.y; E[2] = i2.x; E[3] = i2.y; E[4] = j2.x; E[5] = j2.y; E[6] = k2.x; E[7] = k2.y; E[8] = l2.x;
-        w[0] = l2.y; w[1] = m2.x; w[2] = m2.y;
-        wq = n2.x;
-      }
       const int ptl = rec_ptl(ix);
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double g0 = E[0] * pr.d0 + E[1] * pr.d1 + E[2] * pr.d2 - w[0];
@@ -232,29 +231,22 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
       ci = d.chunk_info[c];
       stage(c, false);
     }
-    const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
+    const int K = ci.K;
     double R[9], C[3];
     double acc[MV_ACC];
-    int run = (int)cs.lrun[tid] - 1;
-    bool any = false;
+#pragma unroll
+    for (int e = 0; e < MV_ACC; ++e) acc[e] = 0.0;
+    const uint32_t ix_first = cs.ixs[tid];
+    const bool any = ix_first != REC_INVALID;
+    if (any) {
+      const double2* row = reinterpret_cast<const double2*>(camc + (size_t)CAMC * rec_seg(ix_first));
+      const double2 a = row[0], b = row[1], cc = row[2], e = row[3], f = row[4], g = row[5];
+      R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = cc.x; R[5] = cc.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
+      C[0] = f.y; C[1] = g.x; C[2] = g.y;
+    }
     for (int k = 0; k < K; ++k) {
       const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
       if (ix == REC_INVALID) break;
-      if (ix & REC_RUNSTART) {
-        if (any) {
-          double* dst = un + run * MV_STRIDE;
-#pragma unroll
-          for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
-        }
-        ++run;
-#pragma unroll
-        for (int e = 0; e < MV_ACC; ++e) acc[e] = 0.0;
-        const double2* row = reinterpret_cast<const double2*>(camc + (size_t)CAMC * rec_seg(ix));
-        const double2 a = row[0], b = row[1], cc = row[2], e = row[3], f = row[4], g = row[5];
-        R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = cc.x; R[5] = cc.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
-        C[0] = f.y; C[1] = g.x; C[2] = g.y;
-      }
-      any = true;
       const int ptl = rec_ptl(ix);
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double u0 = tacc[ptl], u1 = tacc[pt_cap + ptl], u2 = tacc[2 * pt_cap + ptl];
@@ -273,7 +265,7 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
       acc[11] += sgn * pr.v * ct1 - pr.u * ct0;
     }
     if (any) {
-      double* dst = un + run * MV_STRIDE;
+      double* dst = un + tid * MV_STRIDE;
 #pragma unroll
       for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
     }
@@ -554,8 +546,8 @@ static MvShape matvec_shape(const TileShape& ts) {
   sh.slot_cap = ts.max_chunk_len;
   sh.pt_cap = (ts.max_group_pts + 1) & ~1;
   sh.seg_cap = ts.max_nseg;
-  sh.k_cap = (ts.max_chunk_len + RUN_LANES - 1) / RUN_LANES;
-  const int a = 3 * ts.max_chunk_len, bb = ts.max_runs * MV_STRIDE;
+  sh.k_cap = ts.max_k;
+  const int a = 3 * ts.max_chunk_len, bb = RUN_LANES * MV_STRIDE;
   sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
   return sh;
 }

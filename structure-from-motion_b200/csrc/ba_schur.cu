@@ -8,7 +8,7 @@
 // k_camgram walks a group's camera-sorted records: a lane keeps the camera constants AND the 63
 // running sums of its current run in registers, so an observation costs ~340 FP64 FMAs and no
 // memory traffic beyond its 20-byte record and shared-memory reads of its point (X, D^-1, v).
-// Runs are flushed to shared memory, summed per segment (camera) in run order and written as one
+// Lanes flush once to shared memory, are summed per segment (camera) in lane order and written as one
 // 64-double row per (chunk, camera); k_camsum64 then adds each camera's rows in row order.
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
@@ -19,7 +19,7 @@ namespace sfmba {
 constexpr int GRAM = 63;           // A(28) S(28) g(7)
 constexpr int RP_STRIDE = 63;      // odd stride (in doubles): conflict-free simultaneous flushes
 
-// dynamic shared memory: Xs[3][pt_cap] | Dv[9][pt_cap] | runpart[run_cap][RP_STRIDE]
+// dynamic shared memory: Xs[3][pt_cap] | Dv[9][pt_cap] | runpart[RUN_LANES][RP_STRIDE]
 __global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, int pt_cap, int dvdc_quirk) {
   extern __shared__ __align__(16) double smem[];
   double* Xs = smem;
@@ -38,15 +38,23 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, int pt_cap, i
   __syncthreads();
   for (int c = gr.c0; c < gr.c1; ++c) {
     const ChunkInfo ci = d.chunk_info[c];
-    const int K = (ci.len + RUN_LANES - 1) / RUN_LANES;
+    const int K = ci.K;
     const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
     const double2* bp = d.rec_b + (size_t)c * CHUNK_CAP + tid;
-    const int32_t* segcam = d.seg_cam + (size_t)c * SEG_CAP;
     double R[9], C[3], q2[4];
     double acc[GRAM];
-    int run = (int)d.lane_run0[(size_t)c * RUN_LANES + tid] - 1;
+#pragma unroll
+    for (int e = 0; e < GRAM; ++e) acc[e] = 0.0;
     uint32_t ix = ixp[0];
     double2 b = bp[0];
+    const bool live = ix != REC_INVALID;
+    if (live) {                                            // one camera per lane
+      const int cam = d.seg_cam[(size_t)c * SEG_CAP + rec_seg(ix)];
+      load_cam_rc(d.camtab, cam, R, C);
+      load_cam_q(d.camtab, cam, q2);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) q2[e] *= 2.0;
+    }
     for (int k = 0; k < K && ix != REC_INVALID; ++k) {
       const uint32_t ix_cur = ix;
       const double2 b_cur = b;
@@ -55,21 +63,6 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, int pt_cap, i
         b = bp[(k + 1) * RUN_LANES];
       } else {
         ix = REC_INVALID;
-      }
-      if (ix_cur & REC_RUNSTART) {
-        if (k > 0) {
-          double* dst = runpart + run * RP_STRIDE;
-#pragma unroll
-          for (int e = 0; e < GRAM; ++e) dst[e] = acc[e];
-        }
-        ++run;
-#pragma unroll
-        for (int e = 0; e < GRAM; ++e) acc[e] = 0.0;
-        const int cam = segcam[rec_seg(ix_cur)];
-        load_cam_rc(d.camtab, cam, R, C);
-        load_cam_q(d.camtab, cam, q2);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) q2[e] *= 2.0;
       }
       const int ptl = rec_ptl(ix_cur);
       const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
@@ -154,14 +147,14 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, int pt_cap, i
 #pragma unroll
       for (int a = 0; a < 7; ++a) acc[56 + a] += jp[a] * rho0 + jp[7 + a] * rho1;
     }
-    if (run >= 0 && ixp[0] != REC_INVALID) {
-      double* dst = runpart + run * RP_STRIDE;
+    if (live) {
+      double* dst = runpart + tid * RP_STRIDE;
 #pragma unroll
       for (int e = 0; e < GRAM; ++e) dst[e] = acc[e];
     }
     __syncthreads();
-    // per segment: sum its runs in run order -> one 64-double row
-    const uint16_t* run0 = d.seg_run0 + (size_t)c * SEG_RUN_STRIDE;
+    // per segment: sum its lanes in lane order -> one 64-double row
+    const uint16_t* run0 = d.seg_lane0 + (size_t)c * SEG_RUN_STRIDE;
     for (int idx = tid; idx < ci.nseg * CAM_ACC; idx += RUN_LANES) {
       const int s = idx / CAM_ACC, e = idx % CAM_ACC;
       double a = 0.0;
@@ -218,7 +211,7 @@ __global__ void k_cam_blocks(BaDev d) {
 }
 
 void launch_camgram(const BaDev& d, const TileShape& ts, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
-  const size_t smem = ((size_t)12 * ts.max_group_pts + (size_t)ts.max_runs * RP_STRIDE) * sizeof(double);
+  const size_t smem = ((size_t)12 * ts.max_group_pts + (size_t)RUN_LANES * RP_STRIDE) * sizeof(double);
   cudaFuncSetAttribute(k_camgram, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (d.G > 0) {
     k_camgram<<<d.G, RUN_LANES, smem, st>>>(d, ts.max_group_pts, dvdc_quirk ? 1 : 0);

@@ -57,9 +57,9 @@ cudaError_t sfmba_ctx::reserve(int slot, size_t bytes, void** out) {
 namespace {
 
 enum Slot {
-  S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_PT, S_GRP_NCHUNK, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_CAM_ACC, S_ABLK, S_MINV,
+  S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_CAM_ACC, S_ABLK, S_MINV,
   S_CAMIT, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
-  S_CHUNK_INFO, S_REC_B, S_REC_IX, S_SEG_CAM, S_SEG_RUN0, S_LANE_RUN0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
+  S_CHUNK_INFO, S_REC_B, S_REC_IX, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_COUNT
 };
 
@@ -106,6 +106,7 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
   if (full) {
     CARVE(S_GRP_PT, d.G + 1, grp_pt);
     CARVE(S_GRP_NCHUNK, d.G + 1, grp_nchunk);
+    CARVE(S_GRP_K, d.G + 1, grp_K);
     CARVE(S_GRP_CHUNK, d.G + 1, grp_chunk);
     CARVE(S_GRP_META, d.G + 1, grp_meta);
     CARVE(S_DINV, 6 * N, dinv);
@@ -141,8 +142,7 @@ static int sfm_setup_chunks(sfmba_ctx* ctx, int nchunks, BaDev* io) {
   CARVE(S_REC_B, nc * CHUNK_CAP, rec_b);
   CARVE(S_REC_IX, nc * CHUNK_CAP, rec_ix);
   CARVE(S_SEG_CAM, nc * SEG_CAP, seg_cam);
-  CARVE(S_SEG_RUN0, nc * SEG_RUN_STRIDE, seg_run0);
-  CARVE(S_LANE_RUN0, nc * RUN_LANES, lane_run0);
+  CARVE(S_SEG_LANE0, nc * SEG_RUN_STRIDE, seg_lane0);
   CARVE(S_CAMROW_IDX, nc * SEG_CAP, camrow_idx);
   CARVE(S_PART64, nc * SEG_CAP * CAM_ACC, part64);
   CARVE(S_PART12, nc * SEG_CAP * MV_ACC, part12);
@@ -257,9 +257,9 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if (nchunks < 0 || nchunks > chunk_upper) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "pt_rowptr is not a CSR");
   TileShape ts;
   ts.max_chunk_len = std::max(hs->max_chunk_len, 1);
-  ts.max_runs = std::max(hs->max_runs, 1);
   ts.max_group_pts = std::max(hs->max_group_pts, 1);
   ts.max_nseg = std::max(hs->max_nseg, 1);
+  ts.max_k = std::max(hs->max_k, 1);
   if ((rc = sfm_setup_chunks(ctx, nchunks, &d)) != 0) return rc;
   int32_t *sort_keys = nullptr, *iota = nullptr;
   temp_bytes = index_temp_bytes(d.G, d.chunk_bound, d.V);
