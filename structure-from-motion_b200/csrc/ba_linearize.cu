@@ -33,45 +33,72 @@ __global__ void k_cam_prepare(BaDev d) {
 }
 
 // ---- K2a: per-point Schur elimination ------------------------------------------------------------
-// dynamic shared memory: Xs[3][pt_cap] | pacc[9][pt_cap] | slots[9][slot_cap] | red[32]
+// The group's points, row pointers and records are staged with cp.async; the passes read shared
+// memory only.  dynamic shared memory (doubles, then 16-byte, then 4-byte items):
+//   Xa[3 pt_cap] | pacc[9][pt_cap] | slots[9][slot_cap] | red[32] | bs[k_cap 128] | ixs | segc | rowp
+struct PtShape {
+  int slot_cap, pt_cap, seg_cap, k_cap;
+};
+
+__host__ __device__ inline size_t pt_smem_bytes(const PtShape& s, bool cost_only) {
+  size_t dbl = (size_t)3 * s.pt_cap + 32 + (cost_only ? 0 : (size_t)9 * s.pt_cap + (size_t)9 * s.slot_cap);
+  size_t b = dbl * 8;
+  b += (size_t)16 * s.k_cap * RUN_LANES;           // bs
+  b += (size_t)4 * s.k_cap * RUN_LANES;            // ixs
+  b += (size_t)4 * ((s.seg_cap + 3) / 4 * 4);      // segc
+  b += (size_t)4 * (s.pt_cap + 4);                 // rowp
+  return b;
+}
+
 template <bool COST_ONLY>
-__global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, int slot_cap, int pt_cap) {
+__global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, PtShape sh) {
   extern __shared__ __align__(16) double smem[];
-  double* Xs = smem;
-  double* pacc = Xs + 3 * pt_cap;
+  const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
+  double* Xa = smem;
+  double* pacc = Xa + 3 * pt_cap;
   double* slots = COST_ONLY ? pacc : pacc + 9 * pt_cap;
   double* red = COST_ONLY ? pacc : slots + 9 * slot_cap;
-  const GroupRange gr = group_range(d, blockIdx.x);
+  ChunkStage cs;
+  cs.bs = reinterpret_cast<double2*>(red + 32);
+  cs.ixs = reinterpret_cast<uint32_t*>(cs.bs + (size_t)sh.k_cap * RUN_LANES);
+  cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
+  cs.srun = nullptr;
+  int32_t* rowp = cs.segc + (sh.seg_cap + 3) / 4 * 4;
   const int tid = threadIdx.x;
-  stage_points(d, gr, Xs, pt_cap);
-  if (!COST_ONLY) {
-    for (int i = tid; i < 9 * pt_cap; i += RUN_LANES) pacc[i] = 0.0;
+  const GroupMeta gm = d.grp_meta[blockIdx.x];
+  const int np = gm.np, pt0 = gm.pt0, c0 = gm.c0, c1 = gm.c0 + gm.nc;
+  {
+    const double* src = d.pts + 3 * (size_t)pt0;
+    for (int i = tid; i < 3 * np; i += RUN_LANES) cp_async8(Xa + i, src + i);
+    if (!COST_ONLY) {
+      for (int i = tid; i <= np; i += RUN_LANES) cp_async4(rowp + i, d.rowptr + pt0 + i);
+      for (int i = tid; i < 9 * pt_cap; i += RUN_LANES) pacc[i] = 0.0;
+    }
   }
-  __syncthreads();
+  ChunkInfo ci;
+  ci.obs0 = gm.obs0;
+  ci.len = gm.len0;
+  ci.nseg = gm.nseg0;
+  ci.K = gm.K0;
   double cost = 0.0;
   uint32_t flags = 0;
-  for (int c = gr.c0; c < gr.c1; ++c) {
-    const ChunkInfo ci = d.chunk_info[c];
+  for (int c = c0; c < c1; ++c) {
+    if (c > c0) ci = d.chunk_info[c];
+    stage_chunk_async(d, c, ci, cs);
+    cp_async_wait_all();
+    __syncthreads();
     const int K = ci.K;
-    const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
-    const double2* bp = d.rec_b + (size_t)c * CHUNK_CAP + tid;
     double R[9], C[3];
-    uint32_t ix = ixp[0];
-    double2 b = bp[0];
-    if (ix != REC_INVALID) load_cam_rc(d.camtab, d.seg_cam[(size_t)c * SEG_CAP + rec_seg(ix)], R, C);   // one camera per lane
-    for (int k = 0; k < K && ix != REC_INVALID; ++k) {
-      const uint32_t ix_cur = ix;
-      const double2 b_cur = b;
-      if (k + 1 < K) {                                   // prefetch the next record
-        ix = ixp[(k + 1) * RUN_LANES];
-        b = bp[(k + 1) * RUN_LANES];
-      } else {
-        ix = REC_INVALID;
-      }
-      const int ptl = rec_ptl(ix_cur);
-      const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
+    const uint32_t ix_first = cs.ixs[tid];
+    if (ix_first != REC_INVALID) load_cam_rc(d.camtab, cs.segc[rec_seg(ix_first)], R, C);   // one camera per lane
+    for (int k = 0; k < K; ++k) {
+      const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
+      if (ix == REC_INVALID) break;
+      const double2 b = cs.bs[k * RUN_LANES + tid];
+      const int ptl = rec_ptl(ix);
+      const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       if (!pr.ok) flags |= FLAG_DEPTH_ZERO;
-      const double r0 = b_cur.x - pr.u, r1 = b_cur.y - pr.v;
+      const double r0 = b.x - pr.u, r1 = b.y - pr.v;
       cost += r0 * r0 + r1 * r1;
       if (!COST_ONLY) {
         // J_x rows (triangulation_processor.py:259-271 with the K-free projection)
@@ -79,7 +106,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, int slot_cap, int 
                      x2 = (R[6] - pr.u * R[8]) * pr.iw;
         const double y0 = (R[1] - pr.v * R[2]) * pr.iw, y1 = (R[4] - pr.v * R[5]) * pr.iw,
                      y2 = (R[7] - pr.v * R[8]) * pr.iw;
-        double* s = slots + rec_pos(ix_cur);
+        double* s = slots + rec_pos(ix);
         s[0 * slot_cap] = x0 * x0 + y0 * y0;
         s[1 * slot_cap] = x0 * x1 + y0 * y1;
         s[2 * slot_cap] = x0 * x2 + y0 * y2;
@@ -91,11 +118,11 @@ __global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, int slot_cap, int 
         s[8 * slot_cap] = x2 * r0 + y2 * r1;
       }
     }
+    __syncthreads();
     if (!COST_ONLY) {
-      __syncthreads();
-      for (int j = tid; j < gr.np; j += RUN_LANES) {
-        int lo, hi;
-        point_slots(d, gr.pt0 + j, ci, lo, hi);
+      for (int j = tid; j < np; j += RUN_LANES) {
+        const int lo = max(rowp[j], ci.obs0) - ci.obs0;
+        const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
         if (lo < hi) {
           double a[9];
 #pragma unroll
@@ -114,7 +141,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, int slot_cap, int 
   if (!COST_ONLY) {
     const double lam = d.sc->lambda;
     const size_t N = (size_t)d.N;
-    for (int j = tid; j < gr.np; j += RUN_LANES) {
+    for (int j = tid; j < np; j += RUN_LANES) {
       double D[6], ex[3], Dinv[6], v[3];
 #pragma unroll
       for (int e = 0; e < 6; ++e) D[e] = pacc[e * pt_cap + j];
@@ -125,13 +152,14 @@ __global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, int slot_cap, int 
       D[5] += lam;
       if (!sym3_inverse(D, Dinv)) flags |= FLAG_SINGULAR;
       sym3_mul(Dinv, ex, v);
-      const size_t pt = (size_t)gr.pt0 + j;
+      const size_t pt = (size_t)pt0 + j;
 #pragma unroll
       for (int e = 0; e < 6; ++e) d.dinv[e * N + pt] = Dinv[e];
 #pragma unroll
       for (int e = 0; e < 3; ++e) d.vj[e * N + pt] = v[e];
     }
   }
+  cp_async_wait_all();
   cost = block_sum(cost, red);
   if (tid == 0) d.grp_cost[blockIdx.x] = cost;
   if (flags) atomicOr(&d.sc->flags, flags);
@@ -225,23 +253,29 @@ void launch_cam_prepare(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
   lc.launches++;
 }
 
-static size_t point_smem(const TileShape& ts, bool cost_only) {
-  const size_t pt = (size_t)ts.max_group_pts, sl = (size_t)ts.max_chunk_len;
-  return cost_only ? (3 * pt + 32) * sizeof(double) : (3 * pt + 9 * pt + 9 * sl + 32) * sizeof(double);
+static PtShape point_shape(const TileShape& ts) {
+  PtShape sh;
+  sh.slot_cap = (ts.max_chunk_len + 1) & ~1;
+  sh.pt_cap = (ts.max_group_pts + 1) & ~1;
+  sh.seg_cap = ts.max_nseg;
+  sh.k_cap = ts.max_k;
+  return sh;
 }
 
 void launch_point(const BaDev& d, const TileShape& ts, int cost_slot, cudaStream_t st, LaunchCounter& lc) {
-  const size_t smem = point_smem(ts, false);
+  const PtShape sh = point_shape(ts);
+  const size_t smem = pt_smem_bytes(sh, false);
   cudaFuncSetAttribute(k_point<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (d.G > 0) k_point<false><<<d.G, RUN_LANES, smem, st>>>(d, ts.max_chunk_len, ts.max_group_pts);
+  if (d.G > 0) k_point<false><<<d.G, RUN_LANES, smem, st>>>(d, sh);
   k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, d.G, d.sc, cost_slot, nullptr);
   lc.launches += 2;
 }
 
 void launch_cost_tiles(const BaDev& d, const TileShape& ts, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc) {
-  const size_t smem = point_smem(ts, true);
+  const PtShape sh = point_shape(ts);
+  const size_t smem = pt_smem_bytes(sh, true);
   cudaFuncSetAttribute(k_point<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (d.G > 0) k_point<true><<<d.G, RUN_LANES, smem, st>>>(d, ts.max_chunk_len, ts.max_group_pts);
+  if (d.G > 0) k_point<true><<<d.G, RUN_LANES, smem, st>>>(d, sh);
   k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, d.G, d.sc, -1, out_cost_dev);
   lc.launches += 2;
 }

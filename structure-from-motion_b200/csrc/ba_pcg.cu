@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
   cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * sh.seg_cap);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
   cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (sh.seg_cap + 3) / 4 * 4);
+  cs.bs = nullptr;
   int32_t* rowp = reinterpret_cast<int32_t*>(cs.srun + SEG_RUN_STRIDE + 6);
   const int tid = threadIdx.x;
   const GroupMeta gm = d.grp_meta[blockIdx.x];

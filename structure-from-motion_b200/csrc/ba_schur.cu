@@ -19,53 +19,72 @@ namespace sfmba {
 constexpr int GRAM = 63;           // A(28) S(28) g(7)
 constexpr int RP_STRIDE = 63;      // odd stride (in doubles): conflict-free simultaneous flushes
 
-// dynamic shared memory: Xs[3][pt_cap] | Dv[9][pt_cap] | runpart[RUN_LANES][RP_STRIDE]
-__global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, int pt_cap, int dvdc_quirk) {
+// dynamic shared memory: Xa[3 pt_cap] | Dv[9][pt_cap] | runpart[RUN_LANES][RP_STRIDE] | bs | ixs | segc | srun
+struct GramShape {
+  int pt_cap, seg_cap, k_cap;
+};
+
+__host__ __device__ inline size_t gram_smem_bytes(const GramShape& s) {
+  size_t b = ((size_t)12 * s.pt_cap + (size_t)RUN_LANES * RP_STRIDE) * 8;
+  b += (size_t)20 * s.k_cap * RUN_LANES;           // bs + ixs
+  b += (size_t)4 * ((s.seg_cap + 3) / 4 * 4);      // segc
+  b += (size_t)2 * (SEG_RUN_STRIDE + 6);           // srun
+  return b;
+}
+
+__global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, GramShape sh, int dvdc_quirk) {
   extern __shared__ __align__(16) double smem[];
-  double* Xs = smem;
-  double* Dv = Xs + 3 * pt_cap;
+  const int pt_cap = sh.pt_cap;
+  double* Xa = smem;
+  double* Dv = Xa + 3 * pt_cap;
   double* runpart = Dv + 9 * pt_cap;
-  const GroupRange gr = group_range(d, blockIdx.x);
+  ChunkStage cs;
+  cs.bs = reinterpret_cast<double2*>(runpart + RUN_LANES * RP_STRIDE);
+  cs.ixs = reinterpret_cast<uint32_t*>(cs.bs + (size_t)sh.k_cap * RUN_LANES);
+  cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
+  cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (sh.seg_cap + 3) / 4 * 4);
   const int tid = threadIdx.x;
-  stage_points(d, gr, Xs, pt_cap);
+  const GroupMeta gm = d.grp_meta[blockIdx.x];
+  const int np = gm.np, pt0 = gm.pt0, c0 = gm.c0, c1 = gm.c0 + gm.nc;
   {
     const size_t N = (size_t)d.N;
-    for (int i = tid; i < 9 * gr.np; i += RUN_LANES) {
-      const int e = i / gr.np, j = i % gr.np;
-      Dv[e * pt_cap + j] = e < 6 ? d.dinv[e * N + gr.pt0 + j] : d.vj[(e - 6) * N + gr.pt0 + j];
+    const double* src = d.pts + 3 * (size_t)pt0;
+    for (int i = tid; i < 3 * np; i += RUN_LANES) cp_async8(Xa + i, src + i);
+    for (int i = tid; i < 9 * np; i += RUN_LANES) {
+      const int e = i / np, j = i - e * np;
+      cp_async8(Dv + e * pt_cap + j, e < 6 ? d.dinv + e * N + pt0 + j : d.vj + (e - 6) * N + pt0 + j);
     }
   }
-  __syncthreads();
-  for (int c = gr.c0; c < gr.c1; ++c) {
-    const ChunkInfo ci = d.chunk_info[c];
+  ChunkInfo ci;
+  ci.obs0 = gm.obs0;
+  ci.len = gm.len0;
+  ci.nseg = gm.nseg0;
+  ci.K = gm.K0;
+  for (int c = c0; c < c1; ++c) {
+    if (c > c0) ci = d.chunk_info[c];
+    stage_chunk_async(d, c, ci, cs);
+    cp_async_wait_all();
+    __syncthreads();
     const int K = ci.K;
-    const uint32_t* ixp = d.rec_ix + (size_t)c * CHUNK_CAP + tid;
-    const double2* bp = d.rec_b + (size_t)c * CHUNK_CAP + tid;
     double R[9], C[3], q2[4];
     double acc[GRAM];
 #pragma unroll
     for (int e = 0; e < GRAM; ++e) acc[e] = 0.0;
-    uint32_t ix = ixp[0];
-    double2 b = bp[0];
-    const bool live = ix != REC_INVALID;
+    const uint32_t ix_first = cs.ixs[tid];
+    const bool live = ix_first != REC_INVALID;
     if (live) {                                            // one camera per lane
-      const int cam = d.seg_cam[(size_t)c * SEG_CAP + rec_seg(ix)];
+      const int cam = cs.segc[rec_seg(ix_first)];
       load_cam_rc(d.camtab, cam, R, C);
       load_cam_q(d.camtab, cam, q2);
 #pragma unroll
       for (int e = 0; e < 4; ++e) q2[e] *= 2.0;
     }
-    for (int k = 0; k < K && ix != REC_INVALID; ++k) {
-      const uint32_t ix_cur = ix;
-      const double2 b_cur = b;
-      if (k + 1 < K) {
-        ix = ixp[(k + 1) * RUN_LANES];
-        b = bp[(k + 1) * RUN_LANES];
-      } else {
-        ix = REC_INVALID;
-      }
+    for (int k = 0; k < K; ++k) {
+      const uint32_t ix_cur = cs.ixs[k * RUN_LANES + tid];
+      if (ix_cur == REC_INVALID) break;
+      const double2 b_cur = cs.bs[k * RUN_LANES + tid];
       const int ptl = rec_ptl(ix_cur);
-      const Proj pr = project(R, C, Xs[ptl], Xs[pt_cap + ptl], Xs[2 * pt_cap + ptl]);
+      const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double iw = pr.iw, u = pr.u, v = pr.v;
       const double r0 = b_cur.x - u, r1 = b_cur.y - v;
       // J_x (2x3)
@@ -154,7 +173,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, int pt_cap, i
     }
     __syncthreads();
     // per segment: sum its lanes in lane order -> one 64-double row
-    const uint16_t* run0 = d.seg_lane0 + (size_t)c * SEG_RUN_STRIDE;
+    const uint16_t* run0 = cs.srun;
     for (int idx = tid; idx < ci.nseg * CAM_ACC; idx += RUN_LANES) {
       const int s = idx / CAM_ACC, e = idx % CAM_ACC;
       double a = 0.0;
@@ -211,10 +230,14 @@ __global__ void k_cam_blocks(BaDev d) {
 }
 
 void launch_camgram(const BaDev& d, const TileShape& ts, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
-  const size_t smem = ((size_t)12 * ts.max_group_pts + (size_t)RUN_LANES * RP_STRIDE) * sizeof(double);
+  GramShape sh;
+  sh.pt_cap = (ts.max_group_pts + 1) & ~1;
+  sh.seg_cap = ts.max_nseg;
+  sh.k_cap = ts.max_k;
+  const size_t smem = gram_smem_bytes(sh);
   cudaFuncSetAttribute(k_camgram, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (d.G > 0) {
-    k_camgram<<<d.G, RUN_LANES, smem, st>>>(d, ts.max_group_pts, dvdc_quirk ? 1 : 0);
+    k_camgram<<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
     lc.launches++;
   }
 }

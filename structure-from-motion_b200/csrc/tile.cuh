@@ -89,7 +89,8 @@ __device__ __forceinline__ void cp_async_wait_all() {
 struct ChunkStage {
   uint32_t* ixs;     // [k_cap * RUN_LANES]
   int32_t* segc;     // [seg_cap rounded to 4]
-  uint16_t* srun;    // [SEG_RUN_STRIDE] first lane of each segment (+ end)
+  uint16_t* srun;    // [SEG_RUN_STRIDE] first lane of each segment (+ end), or nullptr
+  double2* bs;       // [k_cap * RUN_LANES] normalised observations, or nullptr
 };
 
 __device__ __forceinline__ void stage_chunk_async(const BaDev& d, int c, const ChunkInfo& ci, const ChunkStage& cs) {
@@ -98,8 +99,14 @@ __device__ __forceinline__ void stage_chunk_async(const BaDev& d, int c, const C
   for (int i = threadIdx.x; i < K * (RUN_LANES / 4); i += blockDim.x) cp_async16(cs.ixs + 4 * i, ix + 4 * i);
   const int32_t* sc = d.seg_cam + (size_t)c * SEG_CAP;
   for (int i = threadIdx.x; i < (ci.nseg + 3) / 4; i += blockDim.x) cp_async16(cs.segc + 4 * i, sc + 4 * i);
-  const uint16_t* sr = d.seg_lane0 + (size_t)c * SEG_RUN_STRIDE;
-  for (int i = threadIdx.x; i < (ci.nseg + 2) / 2; i += blockDim.x) cp_async4(cs.srun + 2 * i, sr + 2 * i);
+  if (cs.srun) {
+    const uint16_t* sr = d.seg_lane0 + (size_t)c * SEG_RUN_STRIDE;
+    for (int i = threadIdx.x; i < (ci.nseg + 2) / 2; i += blockDim.x) cp_async4(cs.srun + 2 * i, sr + 2 * i);
+  }
+  if (cs.bs) {
+    const double2* b = d.rec_b + (size_t)c * CHUNK_CAP;
+    for (int i = threadIdx.x; i < K * RUN_LANES; i += blockDim.x) cp_async16(cs.bs + i, b + i);
+  }
 }
 
 }  // namespace sfmba
