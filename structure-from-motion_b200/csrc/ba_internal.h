@@ -167,7 +167,10 @@ void launch_k1(const BaDev& d, bool dvdc_quirk, float* out_r, float* out_jp, flo
                double* out_cost, cudaStream_t st, LaunchCounter& lc);
 
 // ---- camera-side reduction (ba_schur.cu) --------------------------------------------------------
-void launch_camgram(const BaDev& d, const TileShape& ts, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
+// fused linearisation: point blocks (D^-1, v, cost -> sc->costs[cost_slot]) + camera-side Gram rows
+void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int cost_slot, cudaStream_t st,
+                      LaunchCounter& lc);
+void launch_sum_cost(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc);
 void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);       // part64 -> cam_acc
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 

@@ -253,6 +253,11 @@ void launch_cam_prepare(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
   lc.launches++;
 }
 
+void launch_sum_cost(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc) {
+  k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, d.G, d.sc, cost_slot, nullptr);
+  lc.launches++;
+}
+
 static PtShape point_shape(const TileShape& ts) {
   PtShape sh;
   sh.slot_cap = (ts.max_chunk_len + 1) & ~1;

@@ -19,52 +19,145 @@ namespace sfmba {
 constexpr int GRAM = 63;           // A(28) S(28) g(7)
 constexpr int RP_STRIDE = 63;      // odd stride (in doubles): conflict-free simultaneous flushes
 
-// dynamic shared memory: Xa[3 pt_cap] | Dv[9][pt_cap] | runpart[RUN_LANES][RP_STRIDE] | bs | ixs | segc | srun
+// dynamic shared memory (doubles): Xa[3 pt_cap] | Dv[9][pt_cap] | red[32] | un[max(9 slot_cap, RUN_LANES RP_STRIDE)]
+// then bs | ixs | segc | srun | rowp.   `un` holds the point-pass slots, later the lane sums.
 struct GramShape {
-  int pt_cap, seg_cap, k_cap;
+  int pt_cap, seg_cap, k_cap, slot_cap, un_doubles;
 };
 
 __host__ __device__ inline size_t gram_smem_bytes(const GramShape& s) {
-  size_t b = ((size_t)12 * s.pt_cap + (size_t)RUN_LANES * RP_STRIDE) * 8;
+  size_t b = ((size_t)12 * s.pt_cap + 32 + (size_t)s.un_doubles) * 8;
   b += (size_t)20 * s.k_cap * RUN_LANES;           // bs + ixs
   b += (size_t)4 * ((s.seg_cap + 3) / 4 * 4);      // segc
   b += (size_t)2 * (SEG_RUN_STRIDE + 6);           // srun
+  b += (size_t)4 * (s.pt_cap + 4);                 // rowp
   return b;
 }
 
-__global__ void __launch_bounds__(RUN_LANES, 2) k_camgram(BaDev d, GramShape sh, int dvdc_quirk) {
+// Phase A (K2a, ba_processor.py:355-363): per point D_j = sum J_x^T J_x + lambda I, D_j^-1, v_j = D_j^-1 e_x
+// and the cost; phase B: the camera-side Gram sums.  One launch linearises the whole problem.
+__global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape sh, int dvdc_quirk) {
   extern __shared__ __align__(16) double smem[];
-  const int pt_cap = sh.pt_cap;
+  const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
   double* Xa = smem;
   double* Dv = Xa + 3 * pt_cap;
-  double* runpart = Dv + 9 * pt_cap;
+  double* red = Dv + 9 * pt_cap;
+  double* runpart = red + 32;
+  double* slots = runpart;
   ChunkStage cs;
-  cs.bs = reinterpret_cast<double2*>(runpart + RUN_LANES * RP_STRIDE);
+  cs.bs = reinterpret_cast<double2*>(runpart + sh.un_doubles);
   cs.ixs = reinterpret_cast<uint32_t*>(cs.bs + (size_t)sh.k_cap * RUN_LANES);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
   cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (sh.seg_cap + 3) / 4 * 4);
+  int32_t* rowp = reinterpret_cast<int32_t*>(cs.srun + SEG_RUN_STRIDE + 6);
   const int tid = threadIdx.x;
   const GroupMeta gm = d.grp_meta[blockIdx.x];
   const int np = gm.np, pt0 = gm.pt0, c0 = gm.c0, c1 = gm.c0 + gm.nc;
   {
-    const size_t N = (size_t)d.N;
     const double* src = d.pts + 3 * (size_t)pt0;
     for (int i = tid; i < 3 * np; i += RUN_LANES) cp_async8(Xa + i, src + i);
-    for (int i = tid; i < 9 * np; i += RUN_LANES) {
-      const int e = i / np, j = i - e * np;
-      cp_async8(Dv + e * pt_cap + j, e < 6 ? d.dinv + e * N + pt0 + j : d.vj + (e - 6) * N + pt0 + j);
-    }
+    for (int i = tid; i <= np; i += RUN_LANES) cp_async4(rowp + i, d.rowptr + pt0 + i);
+    for (int i = tid; i < 9 * pt_cap; i += RUN_LANES) Dv[i] = 0.0;
   }
   ChunkInfo ci;
   ci.obs0 = gm.obs0;
   ci.len = gm.len0;
   ci.nseg = gm.nseg0;
   ci.K = gm.K0;
+  double cost = 0.0;
+  uint32_t flags = 0;
+  // ---- phase A: point blocks
   for (int c = c0; c < c1; ++c) {
     if (c > c0) ci = d.chunk_info[c];
     stage_chunk_async(d, c, ci, cs);
     cp_async_wait_all();
     __syncthreads();
+    const int K = ci.K;
+    double R[9], C[3];
+    const uint32_t ix_first = cs.ixs[tid];
+    if (ix_first != REC_INVALID) load_cam_rc(d.camtab, cs.segc[rec_seg(ix_first)], R, C);
+    for (int k = 0; k < K; ++k) {
+      const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
+      if (ix == REC_INVALID) break;
+      const double2 b = cs.bs[k * RUN_LANES + tid];
+      const int ptl = rec_ptl(ix);
+      const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
+      if (!pr.ok) flags |= FLAG_DEPTH_ZERO;
+      const double r0 = b.x - pr.u, r1 = b.y - pr.v;
+      cost += r0 * r0 + r1 * r1;
+      const double x0 = (R[0] - pr.u * R[2]) * pr.iw, x1 = (R[3] - pr.u * R[5]) * pr.iw,
+                   x2 = (R[6] - pr.u * R[8]) * pr.iw;
+      const double y0 = (R[1] - pr.v * R[2]) * pr.iw, y1 = (R[4] - pr.v * R[5]) * pr.iw,
+                   y2 = (R[7] - pr.v * R[8]) * pr.iw;
+      double* s = slots + rec_pos(ix);
+      s[0 * slot_cap] = x0 * x0 + y0 * y0;
+      s[1 * slot_cap] = x0 * x1 + y0 * y1;
+      s[2 * slot_cap] = x0 * x2 + y0 * y2;
+      s[3 * slot_cap] = x1 * x1 + y1 * y1;
+      s[4 * slot_cap] = x1 * x2 + y1 * y2;
+      s[5 * slot_cap] = x2 * x2 + y2 * y2;
+      s[6 * slot_cap] = x0 * r0 + y0 * r1;
+      s[7 * slot_cap] = x1 * r0 + y1 * r1;
+      s[8 * slot_cap] = x2 * r0 + y2 * r1;
+    }
+    __syncthreads();
+    for (int j = tid; j < np; j += RUN_LANES) {
+      const int lo = max(rowp[j], ci.obs0) - ci.obs0;
+      const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
+      if (lo < hi) {
+        double a[9];
+#pragma unroll
+        for (int e = 0; e < 9; ++e) a[e] = Dv[e * pt_cap + j];
+        for (int sidx = lo; sidx < hi; ++sidx) {
+#pragma unroll
+          for (int e = 0; e < 9; ++e) a[e] += slots[e * slot_cap + sidx];
+        }
+#pragma unroll
+        for (int e = 0; e < 9; ++e) Dv[e * pt_cap + j] = a[e];
+      }
+    }
+    __syncthreads();
+  }
+  cp_async_wait_all();
+  __syncthreads();
+  {
+    const double lam = d.sc->lambda;
+    const size_t N = (size_t)d.N;
+    for (int j = tid; j < np; j += RUN_LANES) {
+      double D[6], ex[3], Dinv[6], v[3];
+#pragma unroll
+      for (int e = 0; e < 6; ++e) D[e] = Dv[e * pt_cap + j];
+#pragma unroll
+      for (int e = 0; e < 3; ++e) ex[e] = Dv[(6 + e) * pt_cap + j];
+      D[0] += lam;                                     // ba_processor.py:359 (every point, observed or not)
+      D[3] += lam;
+      D[5] += lam;
+      if (!sym3_inverse(D, Dinv)) flags |= FLAG_SINGULAR;
+      sym3_mul(Dinv, ex, v);
+      const size_t pt = (size_t)pt0 + j;
+#pragma unroll
+      for (int e = 0; e < 6; ++e) {
+        Dv[e * pt_cap + j] = Dinv[e];
+        d.dinv[e * N + pt] = Dinv[e];
+      }
+#pragma unroll
+      for (int e = 0; e < 3; ++e) {
+        Dv[(6 + e) * pt_cap + j] = v[e];
+        d.vj[e * N + pt] = v[e];
+      }
+    }
+  }
+  cost = block_sum(cost, red);     // (contains the barrier that publishes Dv)
+  if (tid == 0) d.grp_cost[blockIdx.x] = cost;
+  if (flags) atomicOr(&d.sc->flags, flags);
+  // ---- phase B: camera-side Gram sums
+  for (int c = c0; c < c1; ++c) {
+    if (gm.nc > 1) {                       // single-chunk groups still hold their chunk from phase A
+      ci = d.chunk_info[c];
+      stage_chunk_async(d, c, ci, cs);
+      cp_async_wait_all();
+      __syncthreads();
+    }
     const int K = ci.K;
     double R[9], C[3], q2[4];
     double acc[GRAM];
@@ -229,17 +322,22 @@ __global__ void k_cam_blocks(BaDev d) {
   for (int a = 0; a < 7; ++a) d.gvec[7 * cam + a] = acc[56 + a];
 }
 
-void launch_camgram(const BaDev& d, const TileShape& ts, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
+void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int cost_slot, cudaStream_t st,
+                      LaunchCounter& lc) {
   GramShape sh;
   sh.pt_cap = (ts.max_group_pts + 1) & ~1;
   sh.seg_cap = ts.max_nseg;
   sh.k_cap = ts.max_k;
+  sh.slot_cap = (ts.max_chunk_len + 1) & ~1;
+  const int a = 9 * sh.slot_cap, bb = RUN_LANES * RP_STRIDE;
+  sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
   const size_t smem = gram_smem_bytes(sh);
-  cudaFuncSetAttribute(k_camgram, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(k_linearize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (d.G > 0) {
-    k_camgram<<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
+    k_linearize<<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
     lc.launches++;
   }
+  launch_sum_cost(d, cost_slot, st, lc);
 }
 
 void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {

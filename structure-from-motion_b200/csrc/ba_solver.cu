@@ -276,17 +276,12 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     launch_cam_prepare(d, st, lc);
     {
       cudaEvent_t kb = pt.kbegin();
-      launch_point(d, ts, cost_slot, st, lc);
-      pt.kend("point", kb);
+      launch_linearize(d, ts, quirk, cost_slot, st, lc);
+      pt.kend("linearize", kb);
     }
     pt.end(PH_LINEARIZE, t0);
 
     t0 = pt.begin();
-    {
-      cudaEvent_t kb = pt.kbegin();
-      launch_camgram(d, ts, quirk, st, lc);
-      pt.kend("camgram", kb);
-    }
     launch_camsum64(d, st, lc);
     if (multi) {
       // one message: the camera accumulators plus this rank's cost in the trailing slot
