@@ -123,9 +123,9 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
     const double* src = d.pts + 3 * (size_t)pt0;
     for (int i = tid; i < 3 * np; i += RUN_LANES) cp_async8(Xa + i, src + i);
     for (int i = tid; i <= np; i += RUN_LANES) cp_async4(rowp + i, d.rowptr + pt0 + i);
-    for (int i = tid; i < 6 * np; i += RUN_LANES) {
-      const int e = i / np, j = i - e * np;
-      cp_async8(Dn + e * pt_cap + j, d.dinv + e * N + pt0 + j);
+#pragma unroll
+    for (int e = 0; e < 6; ++e) {
+      for (int j = tid; j < np; j += RUN_LANES) cp_async8(Dn + e * pt_cap + j, d.dinv + e * N + pt0 + j);
     }
     for (int i = tid; i < 3 * pt_cap; i += RUN_LANES) tacc[i] = 0.0;
   }
@@ -166,9 +166,8 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
       w[0] = l2.y; w[1] = m2.x; w[2] = m2.y;
       wq = n2.x;
     }
-    for (int k = 0; k < K; ++k) {
-      const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
-      if (ix == REC_INVALID) break;
+    // two observations per trip: their dependency chains are independent and interleave
+    auto pass1 = [&](uint32_t ix, double t[3]) {
       const int ptl = rec_ptl(ix);
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double g0 = E[0] * pr.d0 + E[1] * pr.d1 + E[2] * pr.d2 - w[0];
@@ -178,10 +177,29 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
       const double a1 = pr.iw * (g1 - pr.v * (g2 + wq));
       const double q0 = pr.iw * a0, q1 = pr.iw * a1;
       const double q2 = -(pr.u * q0 + pr.v * q1);
-      double* s = un + rec_pos(ix);
-      s[0] = R[0] * q0 + R[1] * q1 + R[2] * q2;
-      s[slot_cap] = R[3] * q0 + R[4] * q1 + R[5] * q2;
-      s[2 * slot_cap] = R[6] * q0 + R[7] * q1 + R[8] * q2;
+      t[0] = R[0] * q0 + R[1] * q1 + R[2] * q2;
+      t[1] = R[3] * q0 + R[4] * q1 + R[5] * q2;
+      t[2] = R[6] * q0 + R[7] * q1 + R[8] * q2;
+    };
+    for (int k = 0; k < K; k += 2) {
+      const uint32_t ixa = cs.ixs[k * RUN_LANES + tid];
+      if (ixa == REC_INVALID) break;
+      uint32_t ixb = (k + 1 < K) ? cs.ixs[(k + 1) * RUN_LANES + tid] : REC_INVALID;
+      const bool vb = ixb != REC_INVALID;
+      if (!vb) ixb = ixa;
+      double ta[3], tb[3];
+      pass1(ixa, ta);
+      pass1(ixb, tb);
+      double* sa = un + rec_pos(ixa);
+      sa[0] = ta[0];
+      sa[slot_cap] = ta[1];
+      sa[2 * slot_cap] = ta[2];
+      if (vb) {
+        double* sb = un + rec_pos(ixb);
+        sb[0] = tb[0];
+        sb[slot_cap] = tb[1];
+        sb[2 * slot_cap] = tb[2];
+      }
     }
     __syncthreads();
     for (int j = tid; j < np; j += RUN_LANES) {
@@ -245,18 +263,17 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
       R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = cc.x; R[5] = cc.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
       C[0] = f.y; C[1] = g.x; C[2] = g.y;
     }
-    for (int k = 0; k < K; ++k) {
-      const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
-      if (ix == REC_INVALID) break;
+    auto pass2 = [&](uint32_t ix, double scale) {
       const int ptl = rec_ptl(ix);
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double u0 = tacc[ptl], u1 = tacc[pt_cap + ptl], u2 = tacc[2 * pt_cap + ptl];
       const double e0 = R[0] * u0 + R[3] * u1 + R[6] * u2;
       const double e1 = R[1] * u0 + R[4] * u1 + R[7] * u2;
       const double e2 = R[2] * u0 + R[5] * u1 + R[8] * u2;
+      const double iws = pr.iw * scale;
       const double b0 = pr.iw * (e0 - pr.u * e2);
       const double b1 = pr.iw * (e1 - pr.v * e2);
-      const double ct0 = pr.iw * b0, ct1 = pr.iw * b1;
+      const double ct0 = iws * b0, ct1 = iws * b1;
       const double ct2 = -(pr.u * ct0 + pr.v * ct1);
       acc[0] += ct0 * pr.d0; acc[1] += ct0 * pr.d1; acc[2] += ct0 * pr.d2;
       acc[3] += ct1 * pr.d0; acc[4] += ct1 * pr.d1; acc[5] += ct1 * pr.d2;
@@ -264,6 +281,15 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
       acc[9] += ct0;
       acc[10] += ct1;
       acc[11] += sgn * pr.v * ct1 - pr.u * ct0;
+    };
+    for (int k = 0; k < K; k += 2) {
+      const uint32_t ixa = cs.ixs[k * RUN_LANES + tid];
+      if (ixa == REC_INVALID) break;
+      uint32_t ixb = (k + 1 < K) ? cs.ixs[(k + 1) * RUN_LANES + tid] : REC_INVALID;
+      const bool vb = ixb != REC_INVALID;
+      if (!vb) ixb = ixa;
+      pass2(ixa, 1.0);
+      pass2(ixb, vb ? 1.0 : 0.0);
     }
     if (any) {
       double* dst = un + tid * MV_STRIDE;

@@ -39,6 +39,17 @@ __device__ __forceinline__ void load_cam_q(const double* __restrict__ camtab, in
   q[0] = a.x; q[1] = a.y; q[2] = b.x; q[3] = b.y;
 }
 
+// 1 / x: MUFU.RCP64H seed (rcp.approx.ftz.f64, ~20 bits) + two Newton steps = full f64 accuracy to
+// ~1 ulp in 5 instructions, no slow path (x == 0 gives inf and is flagged by the caller).
+__device__ __forceinline__ double fast_rcp(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+}
+
 // projection of one point: d = X - C, p = R^T d, iw = 1 / p_w, (u, v) = p_uv * iw
 struct Proj {
   double d0, d1, d2, iw, u, v;
@@ -53,7 +64,7 @@ __device__ __forceinline__ Proj project(const double R[9], const double C[3], do
   const double pu = R[0] * p.d0 + R[3] * p.d1 + R[6] * p.d2;
   const double pv = R[1] * p.d0 + R[4] * p.d1 + R[7] * p.d2;
   const double pw = R[2] * p.d0 + R[5] * p.d1 + R[8] * p.d2;
-  p.iw = 1.0 / pw;
+  p.iw = fast_rcp(pw);
   p.u = pu * p.iw;
   p.v = pv * p.iw;
   p.ok = pw != 0.0;
