@@ -85,12 +85,12 @@ __global__ void __launch_bounds__(128) k_cam_iter(BaDev d, const double* __restr
 // segments are gathered; the two passes touch global memory only to write their results.
 // BACKSUB: pass 1 with delta_p, then pts_j += v_j - D_j^-1 t_j        (ba_processor.py:405-406)
 struct MvShape {
-  int slot_cap, pt_cap, seg_cap, k_cap, un_doubles;
+  int slot_cap, pt_cap, seg_cap, k_cap, un_doubles, vn_doubles;
 };
 constexpr int CAMC = 26;   // doubles per staged camera row: R[9] C[3] E[9] w[3] wq pad
 
 __host__ __device__ inline size_t mv_smem_bytes(const MvShape& s) {
-  size_t dbl = (size_t)3 * s.pt_cap + 3 * s.pt_cap + 6 * s.pt_cap + s.un_doubles + (size_t)CAMC * s.seg_cap;
+  size_t dbl = (size_t)3 * s.pt_cap + 3 * s.pt_cap + 6 * s.pt_cap + s.vn_doubles + s.un_doubles + (size_t)CAMC * s.seg_cap;
   size_t b = dbl * 8;
   b += (size_t)4 * (s.pt_cap + 4);                 // rowp
   b += (size_t)4 * s.k_cap * RUN_LANES;            // ixs
@@ -107,7 +107,8 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
   double* Xa = smem;                               // AoS [np][3]
   double* tacc = Xa + 3 * pt_cap;                  // SoA [3][pt_cap]
   double* Dn = tacc + 3 * pt_cap;                  // SoA [6][pt_cap]
-  double* un = Dn + 6 * pt_cap;
+  double* Vn = Dn + 6 * pt_cap;                    // SoA [3][pt_cap] v_j (back-substitution only)
+  double* un = Vn + sh.vn_doubles;
   double* camc = un + sh.un_doubles;
   ChunkStage cs;
   cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * sh.seg_cap);
@@ -126,6 +127,12 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
 #pragma unroll
     for (int e = 0; e < 6; ++e) {
       for (int j = tid; j < np; j += RUN_LANES) cp_async8(Dn + e * pt_cap + j, d.dinv + e * N + pt0 + j);
+    }
+    if (BACKSUB) {
+#pragma unroll
+      for (int e = 0; e < 3; ++e) {
+        for (int j = tid; j < np; j += RUN_LANES) cp_async8(Vn + e * pt_cap + j, d.vj + e * N + pt0 + j);
+      }
     }
     for (int i = tid; i < 3 * pt_cap; i += RUN_LANES) tacc[i] = 0.0;
   }
@@ -202,19 +209,15 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
       }
     }
     __syncthreads();
-    for (int j = tid; j < np; j += RUN_LANES) {
+    for (int idx = tid; idx < 3 * np; idx += RUN_LANES) {
+      const int j = idx / 3, e = idx - 3 * j;
       const int lo = max(rowp[j], ci.obs0) - ci.obs0;
       const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
       if (lo < hi) {
-        double t0 = tacc[j], t1 = tacc[pt_cap + j], t2 = tacc[2 * pt_cap + j];
-        for (int s = lo; s < hi; ++s) {
-          t0 += un[s];
-          t1 += un[slot_cap + s];
-          t2 += un[2 * slot_cap + s];
-        }
-        tacc[j] = t0;
-        tacc[pt_cap + j] = t1;
-        tacc[2 * pt_cap + j] = t2;
+        const double* sl = un + e * slot_cap;
+        double a = tacc[e * pt_cap + j];
+        for (int s = lo; s < hi; ++s) a += sl[s];
+        tacc[e * pt_cap + j] = a;
       }
     }
     __syncthreads();
@@ -231,10 +234,9 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
     t[2] = tacc[2 * pt_cap + j];
     sym3_mul(Dinv, t, u);
     if (BACKSUB) {
-      const size_t N = (size_t)d.N, pt = (size_t)pt0 + j;
-      double* p = d.pts + 3 * pt;
+      double* p = d.pts + 3 * ((size_t)pt0 + j);
 #pragma unroll
-      for (int e = 0; e < 3; ++e) p[e] = Xa[3 * j + e] + (d.vj[e * N + pt] - u[e]);
+      for (int e = 0; e < 3; ++e) p[e] = Xa[3 * j + e] + (Vn[e * pt_cap + j] - u[e]);
     } else {
       tacc[j] = u[0];
       tacc[pt_cap + j] = u[1];
@@ -568,14 +570,15 @@ __global__ void k_lm_decide(BaDev d, double lam_min, double lam_max) {
 }
 
 
-static MvShape matvec_shape(const TileShape& ts) {
+static MvShape matvec_shape(const TileShape& ts, bool backsub) {
   MvShape sh;
-  sh.slot_cap = ts.max_chunk_len;
+  sh.slot_cap = ((ts.max_chunk_len + 15) & ~15) + 1;
   sh.pt_cap = (ts.max_group_pts + 1) & ~1;
   sh.seg_cap = ts.max_nseg;
   sh.k_cap = ts.max_k;
-  const int a = 3 * ts.max_chunk_len, bb = RUN_LANES * MV_STRIDE;
+  const int a = 3 * sh.slot_cap, bb = RUN_LANES * MV_STRIDE;
   sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
+  sh.vn_doubles = backsub ? 3 * sh.pt_cap : 0;
   return sh;
 }
 
@@ -593,7 +596,7 @@ void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc) {
   if (d.G <= 0) return;
-  const MvShape sh = matvec_shape(ts);
+  const MvShape sh = matvec_shape(ts, backsub);
   const size_t smem = mv_smem_bytes(sh);
   if (backsub) {
     cudaFuncSetAttribute(k_matvec<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -101,19 +101,16 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
       s[8 * slot_cap] = x2 * r0 + y2 * r1;
     }
     __syncthreads();
-    for (int j = tid; j < np; j += RUN_LANES) {
+    // one work item per (point, component): the slots of a point are summed in observation order
+    for (int idx = tid; idx < 9 * np; idx += RUN_LANES) {
+      const int j = idx / 9, e = idx - 9 * j;
       const int lo = max(rowp[j], ci.obs0) - ci.obs0;
       const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
       if (lo < hi) {
-        double a[9];
-#pragma unroll
-        for (int e = 0; e < 9; ++e) a[e] = Dv[e * pt_cap + j];
-        for (int sidx = lo; sidx < hi; ++sidx) {
-#pragma unroll
-          for (int e = 0; e < 9; ++e) a[e] += slots[e * slot_cap + sidx];
-        }
-#pragma unroll
-        for (int e = 0; e < 9; ++e) Dv[e * pt_cap + j] = a[e];
+        const double* sl = slots + e * slot_cap;
+        double a = Dv[e * pt_cap + j];
+        for (int sidx = lo; sidx < hi; ++sidx) a += sl[sidx];
+        Dv[e * pt_cap + j] = a;
       }
     }
     __syncthreads();
@@ -247,17 +244,31 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
         tu[a] = yuu * jp[a] + yuv * jp[7 + a];
         tv[a] = yuv * jp[a] + yvv * jp[7 + a];
       }
-      int e = 0;
+      // two FMA sweeps (u-row products, then v-row products): 2 instructions per sum, all independent
+      {
+        int e = 0;
 #pragma unroll
-      for (int a = 0; a < 7; ++a) {
+        for (int a = 0; a < 7; ++a) {
 #pragma unroll
-        for (int bcol = a; bcol < 7; ++bcol, ++e) {
-          acc[e] += jp[a] * jp[bcol] + jp[7 + a] * jp[7 + bcol];
-          acc[28 + e] += jp[a] * tu[bcol] + jp[7 + a] * tv[bcol];
+          for (int bcol = a; bcol < 7; ++bcol, ++e) {
+            acc[e] = fma(jp[a], jp[bcol], acc[e]);
+            acc[28 + e] = fma(jp[a], tu[bcol], acc[28 + e]);
+          }
         }
-      }
 #pragma unroll
-      for (int a = 0; a < 7; ++a) acc[56 + a] += jp[a] * rho0 + jp[7 + a] * rho1;
+        for (int a = 0; a < 7; ++a) acc[56 + a] = fma(jp[a], rho0, acc[56 + a]);
+        e = 0;
+#pragma unroll
+        for (int a = 0; a < 7; ++a) {
+#pragma unroll
+          for (int bcol = a; bcol < 7; ++bcol, ++e) {
+            acc[e] = fma(jp[7 + a], jp[7 + bcol], acc[e]);
+            acc[28 + e] = fma(jp[7 + a], tv[bcol], acc[28 + e]);
+          }
+        }
+#pragma unroll
+        for (int a = 0; a < 7; ++a) acc[56 + a] = fma(jp[7 + a], rho1, acc[56 + a]);
+      }
     }
     if (live) {
       double* dst = runpart + tid * RP_STRIDE;
@@ -328,7 +339,7 @@ void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int 
   sh.pt_cap = (ts.max_group_pts + 1) & ~1;
   sh.seg_cap = ts.max_nseg;
   sh.k_cap = ts.max_k;
-  sh.slot_cap = (ts.max_chunk_len + 1) & ~1;
+  sh.slot_cap = ((ts.max_chunk_len + 15) & ~15) + 1;   // = 1 mod 16: the 9 slot planes start in different banks
   const int a = 9 * sh.slot_cap, bb = RUN_LANES * RP_STRIDE;
   sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
   const size_t smem = gram_smem_bytes(sh);
