@@ -175,15 +175,14 @@ void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);       
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
-void launch_pcg_init(const BaDev& d, unsigned epoch, cudaStream_t st, LaunchCounter& lc);
+void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool dvdc_quirk, cudaStream_t st,
                      LaunchCounter& lc);
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc);
-// part12 -> svec (y); when `fuse_apq`, also q = A p - y and alpha (single GPU)
-void launch_camsum12(const BaDev& d, bool fuse_apq, cudaStream_t st, LaunchCounter& lc);
-void launch_apq(const BaDev& d, cudaStream_t st, LaunchCounter& lc);            // after the allreduce of svec
-void launch_pcg_update(const BaDev& d, double tol, int max_iter, unsigned epoch, cudaStream_t st, LaunchCounter& lc);
+void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // part12 -> svec (multi-GPU)
+void launch_pcg_tail(const BaDev& d, bool from_rows, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
+                     cudaStream_t st, LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

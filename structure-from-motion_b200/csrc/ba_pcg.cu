@@ -18,7 +18,11 @@
 // converges to f64 accuracy.  All reductions have a fixed order.
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
+#include <cooperative_groups.h>
+
 #include "tile.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace sfmba {
 
@@ -316,6 +320,7 @@ template <int NV>
 __device__ __forceinline__ bool grid_sum_finish(double (&v)[NV], double* __restrict__ partials, uint32_t* ticket,
                                                 double* red, double (&total)[NV]) {
   __shared__ bool s_last;
+  __threadfence();   // this block's earlier global writes (q) must be visible to the block that finishes last
 #pragma unroll
   for (int i = 0; i < NV; ++i) v[i] = block_sum(v[i], red);
   if (threadIdx.x == 0) {
@@ -338,157 +343,216 @@ __device__ __forceinline__ bool grid_sum_finish(double (&v)[NV], double* __restr
   return true;
 }
 
-// y_i from the camera's segment rows (16 lanes per camera, fixed row order):
-//   y_C = -R s,  y_q[j] = <Q_j, T>;   FUSE: q = A p - y and alpha = rz / (p.q)   (single GPU)
-template <bool FUSE>
-__global__ void __launch_bounds__(256) k_camsum12(BaDev d) {
-  __shared__ double red[32];
-  if (d.sc->pcg_done) return;
-  const int sub = threadIdx.x & 15;
-  const int cam = blockIdx.x * 16 + (threadIdx.x >> 4);
-  const bool live = cam < d.V;
+// camit row of one camera for direction dl = (dC, dq): E = sum_j dq[j] Q_j, w = R^T dC, quirk term
+__device__ __forceinline__ void write_camit(const BaDev& d, int cam, const double dl[7], int dvdc_quirk) {
+  const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
+  const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
+  double Q[4][9];
+  quat_dRt(q2, Q);
+  double* o = d.camit + (size_t)CAMIT_STRIDE * cam;
+#pragma unroll
+  for (int e = 0; e < 9; ++e) o[e] = dl[3] * Q[0][e] + dl[4] * Q[1][e] + dl[5] * Q[2][e] + dl[6] * Q[3][e];
+  double w[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) w[c] = t[c] * dl[0] + t[3 + c] * dl[1] + t[6 + c] * dl[2];
+  o[9] = w[0];
+  o[10] = w[1];
+  o[11] = w[2];
+  o[12] = dvdc_quirk ? 2.0 * w[2] : 0.0;
+  o[13] = 0.0;
+  o[14] = 0.0;
+  o[15] = 0.0;
+}
+
+// y_i from the camera's segment rows, one warp per camera: lane = (row slot, component), two row slots
+// of 16 lanes each take alternate rows with eight loads in flight, slot sums are combined in fixed
+// order.  y_C = -R s, y_q[j] = <Q_j, T>.  Returns y in lanes 0..6 (0 elsewhere).
+__device__ __forceinline__ double cam_y_from_rows(const BaDev& d, int cam, int lane, bool live) {
+  const int sub = lane & 15, slot = lane >> 4;
   double a = 0.0;
   if (live && sub < MV_ACC) {
     const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
-    for (int k = r0; k < r1; ++k) a += d.part12[(size_t)d.camrow_idx[k] * MV_ACC + sub];
+    int k = r0 + slot;
+    for (; k + 14 < r1; k += 16) {                     // rows k, k+2, ..., k+14 of this slot
+      int idx[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) idx[u] = d.camrow_idx[k + 2 * u];
+      double v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = d.part12[(size_t)idx[u] * MV_ACC + sub];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) a += v[u];
+    }
+    for (; k < r1; k += 2) a += d.part12[(size_t)d.camrow_idx[k] * MV_ACC + sub];
   }
+  a += __shfl_down_sync(0xffffffffu, a, 16);           // slot 0 + slot 1
   double T[MV_ACC];
 #pragma unroll
-  for (int e = 0; e < MV_ACC; ++e) T[e] = __shfl_sync(0xffffffffu, a, e, 16);
-  double pq = 0.0;
-  if (live && sub < 7) {
+  for (int e = 0; e < MV_ACC; ++e) T[e] = __shfl_sync(0xffffffffu, a, e);
+  double y = 0.0;
+  if (live && lane < 7) {
     const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
-    double y;
-    if (sub < 3) {
-      y = -(t[3 * sub] * T[9] + t[3 * sub + 1] * T[10] + t[3 * sub + 2] * T[11]);
+    if (lane < 3) {
+      y = -(t[3 * lane] * T[9] + t[3 * lane + 1] * T[10] + t[3 * lane + 2] * T[11]);
     } else {
       const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
       double Q[4][9];
       quat_dRt(q2, Q);
-      y = 0.0;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (j == sub - 3) {
+        if (j == lane - 3) {
 #pragma unroll
           for (int e = 0; e < 9; ++e) y += Q[j][e] * T[e];
         }
       }
     }
-    const size_t k = 7 * (size_t)cam + sub;
-    d.svec[k] = y;
-    if (FUSE) {
-      const double* row = d.ablk + (size_t)cam * 49 + sub * 7;
-      const double* pv = d.p + 7 * (size_t)cam;
-      double ap = 0.0;
-#pragma unroll
-      for (int b = 0; b < 7; ++b) ap += row[b] * pv[b];
-      const double qv = ap - y;
-      d.q[k] = qv;
-      pq = pv[sub] * qv;
-    }
   }
-  if (FUSE) {
-    double v[1] = {pq}, tot[1];
-    if (grid_sum_finish<1>(v, d.red_a, &d.sc->ticket_a, red, tot) && threadIdx.x == 0) {
-      d.sc->pq = tot[0];
-      d.sc->alpha = d.sc->rz / tot[0];
-    }
-  }
+  return y;
 }
 
-// q = A p - svec, alpha = rz / (p.q)      (multi-GPU: after the all-reduce of svec)
-__global__ void __launch_bounds__(256) k_apq(BaDev d) {
-  __shared__ double red[32];
+// svec = y only (multi-GPU: all-reduced before k_pcg_tail<2>)
+__global__ void __launch_bounds__(256) k_camsum12(BaDev d) {
   if (d.sc->pcg_done) return;
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  double pq = 0.0;
-  if (k < 7 * d.V) {
-    const int cam = k / 7, a = k % 7;
-    const double* row = d.ablk + (size_t)cam * 49 + a * 7;
-    const double* pv = d.p + 7 * (size_t)cam;
-    double ap = 0.0;
-#pragma unroll
-    for (int b = 0; b < 7; ++b) ap += row[b] * pv[b];
-    const double qv = ap - d.svec[k];
-    d.q[k] = qv;
-    pq = pv[a] * qv;
-  }
-  double v[1] = {pq}, tot[1];
-  if (grid_sum_finish<1>(v, d.red_a, &d.sc->ticket_a, red, tot) && threadIdx.x == 0) {
-    d.sc->pq = tot[0];
-    d.sc->alpha = d.sc->rz / tot[0];
-  }
+  const int sub = threadIdx.x & 31;
+  const int cam = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const bool live = cam < d.V;
+  const double y = cam_y_from_rows(d, cam, sub, live);
+  if (live && sub < 7) d.svec[7 * (size_t)cam + sub] = y;
 }
 
-// One thread per camera (its 7 rows; no cross-thread hazards on r).
-// INIT:  x = 0, p = 0, r = g, z = Minv g, rz = r.z, gg = g.g, beta = 0
-// else:  x += alpha p, r -= alpha q, z = Minv r, beta = rz' / rz, convergence test, host signal
-template <bool INIT>
-__global__ void __launch_bounds__(128) k_pcg_update(BaDev d, double tol, int max_iter, unsigned epoch) {
+// The vector part of one PCG iteration in ONE cooperative launch (grid-wide barriers between phases).
+//   MODE 0  init: x = 0, r = g, z = Minv g, rz, gg, p = z, camit(p)
+//   MODE 1  phase 1: y from the segment rows, q = A p - y, p.q            (single GPU)
+//   MODE 2  phase 1: y = svec (already all-reduced), q = A p - y, p.q     (several GPUs)
+//   phase 2: alpha = rz / p.q;  x += alpha p;  r' = r - alpha q;  z = Minv r';  r'.z, r'.r
+//   phase 3: beta = rz' / rz;  convergence test and host signal;  r = r';  p = z + beta p;  camit(p)
+// Every block sums the per-block partials itself, in block order, so all blocks hold identical scalars.
+__device__ __forceinline__ double all_blocks_sum(const double* __restrict__ partials, int stride, int which,
+                                                 double* red) {
+  double a = 0.0;
+  for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) a += __ldcg(partials + (size_t)b * stride + which);
+  return block_sum(a, red);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) k_pcg_tail(BaDev d, double tol, int max_iter, unsigned epoch, int dvdc_quirk) {
   __shared__ double red[32];
+  cg::grid_group grid = cg::this_grid();
   Scalars* sc = d.sc;
-  if (!INIT && sc->pcg_done) return;
-  const int cam = blockIdx.x * blockDim.x + threadIdx.x;
-  double v[2] = {0.0, 0.0};
-  if (cam < d.V) {
+  if (MODE != 0 && sc->pcg_done) return;            // uniform over the grid: nobody reaches a barrier
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int gsize = gridDim.x * blockDim.x;
+  const int n7 = 7 * d.V;
+  double alpha = 0.0;
+  const double rz_old = sc->rz;
+  if (MODE != 0) {
+    double pq = 0.0;
+    const int sub = threadIdx.x & 31;
+    const int ngroups = gsize >> 5;
+    for (int c0 = 0; c0 < d.V; c0 += ngroups) {     // uniform trip count (shuffles inside)
+      const int cam = c0 + (gtid >> 5);
+      const bool live = cam < d.V;
+      double y = 0.0;
+      if (MODE == 1) y = cam_y_from_rows(d, cam, sub, live);
+      if (live && sub < 7) {
+        const size_t k = 7 * (size_t)cam + sub;
+        if (MODE == 2) y = d.svec[k];
+        const double* row = d.ablk + (size_t)cam * 49 + sub * 7;
+        const double* pv = d.p + 7 * (size_t)cam;
+        double ap = 0.0;
+#pragma unroll
+        for (int b = 0; b < 7; ++b) ap += row[b] * pv[b];
+        const double qv = ap - y;
+        d.q[k] = qv;
+        pq += pv[sub] * qv;
+      }
+    }
+    pq = block_sum(pq, red);
+    if (threadIdx.x == 0) d.red_a[blockIdx.x] = pq;
+    grid.sync();
+    const double pq_all = all_blocks_sum(d.red_a, 1, 0, red);
+    alpha = rz_old / pq_all;
+    if (gtid == 0) {
+      sc->pq = pq_all;
+      sc->alpha = alpha;
+    }
+  }
+  // ---- phase 2: one thread per (camera, row); r' goes to svec (r is still being read by the row's peers)
+  double v0 = 0.0, v1 = 0.0;
+  for (int k = gtid; k < n7; k += gsize) {
+    const int cam = k / 7, a = k - 7 * cam;
     const size_t base = 7 * (size_t)cam;
     double rn[7];
-    if (INIT) {
+    if (MODE == 0) {
 #pragma unroll
-      for (int b = 0; b < 7; ++b) {
-        rn[b] = d.gvec[base + b];
-        d.x[base + b] = 0.0;
-        d.p[base + b] = 0.0;
-      }
+      for (int b = 0; b < 7; ++b) rn[b] = d.gvec[base + b];
+      d.x[k] = 0.0;
     } else {
-      const double alpha = sc->alpha;
 #pragma unroll
-      for (int b = 0; b < 7; ++b) {
-        rn[b] = d.r[base + b] - alpha * d.q[base + b];
-        d.x[base + b] += alpha * d.p[base + b];
-      }
+      for (int b = 0; b < 7; ++b) rn[b] = d.r[base + b] - alpha * __ldcg(d.q + base + b);
+      d.x[k] += alpha * d.p[k];
     }
-    const double* blk = d.minv + (size_t)cam * 49;
+    const double* row = d.minv + (size_t)cam * 49 + a * 7;
+    double z = 0.0;
 #pragma unroll
-    for (int a = 0; a < 7; ++a) {
-      double z = 0.0;
-#pragma unroll
-      for (int b = 0; b < 7; ++b) z += blk[a * 7 + b] * rn[b];
-      d.z[base + a] = z;
-      d.r[base + a] = rn[a];
-      v[0] += rn[a] * z;
-      v[1] += rn[a] * rn[a];
+    for (int b = 0; b < 7; ++b) z += row[b] * rn[b];
+    d.z[k] = z;
+    d.svec[k] = rn[a];
+    v0 += rn[a] * z;
+    v1 += rn[a] * rn[a];
+  }
+  v0 = block_sum(v0, red);
+  v1 = block_sum(v1, red);
+  if (threadIdx.x == 0) {
+    d.red_b[2 * blockIdx.x] = v0;
+    d.red_b[2 * blockIdx.x + 1] = v1;
+  }
+  grid.sync();
+  const double rz_new = all_blocks_sum(d.red_b, 2, 0, red);
+  const double rr = all_blocks_sum(d.red_b, 2, 1, red);
+  const double beta = MODE == 0 ? 0.0 : rz_new / rz_old;
+  // convergence: every thread evaluates the same scalars; thread 0 of the grid publishes them
+  int done = 0, it = 0;
+  const double gg = MODE == 0 ? rr : sc->gg;
+  uint32_t newflags = 0;
+  if (MODE == 0) {
+    done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
+    if (!(rr == rr)) newflags |= FLAG_NONFINITE;
+  } else {
+    it = sc->pcg_iters + 1;
+    if (!(rz_old / alpha > 0.0) || !(rr == rr)) {    // p.q <= 0 or NaN
+      newflags |= FLAG_NONFINITE;
+      done = 1;
+    }
+    if (rr <= tol * tol * gg) done = 1;
+    if (!done && it >= max_iter) {
+      newflags |= FLAG_PCG_MAXITER;
+      done = 1;
     }
   }
-  double tot[2];
-  if (grid_sum_finish<2>(v, d.red_b, &sc->ticket_b, red, tot) && threadIdx.x == 0) {
-    const double rz_new = tot[0], rr = tot[1];
-    int done = 0, it = 0;
-    if (INIT) {
-      sc->rz = rz_new;
-      sc->gg = rr;
-      sc->rr = rr;
-      sc->beta = 0.0;
-      sc->pcg_iters = 0;
-      done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
-      if (!(rr == rr)) atomicOr(&sc->flags, FLAG_NONFINITE);
-    } else {
-      sc->beta = rz_new / sc->rz;
-      sc->rz = rz_new;
-      sc->rr = rr;
-      it = sc->pcg_iters + 1;
-      sc->pcg_iters = it;
-      sc->pcg_iters_total += 1;
-      if (!(sc->pq > 0.0) || !(rr == rr)) {
-        atomicOr(&sc->flags, FLAG_NONFINITE);
-        done = 1;
-      }
-      if (rr <= tol * tol * sc->gg) done = 1;
-      if (!done && it >= max_iter) {
-        atomicOr(&sc->flags, FLAG_PCG_MAXITER);
-        done = 1;
-      }
+  // ---- phase 3
+  for (int k = gtid; k < n7; k += gsize) {
+    const double pn = __ldcg(d.z + k) + beta * (MODE == 0 ? 0.0 : d.p[k]);
+    d.r[k] = __ldcg(d.svec + k);
+    d.p[k] = pn;
+  }
+  grid.sync();   // p complete (camit needs the 7 entries of a camera), pcg_iters read by everyone
+  if (!done) {
+    for (int cam = gtid; cam < d.V; cam += gsize) {
+      double dl[7];
+#pragma unroll
+      for (int k = 0; k < 7; ++k) dl[k] = __ldcg(d.p + 7 * (size_t)cam + k);
+      write_camit(d, cam, dl, dvdc_quirk);
     }
+  }
+  if (gtid == 0) {
+    if (MODE == 0) sc->gg = rr;
+    if (MODE != 0) sc->pcg_iters_total += 1;
+    sc->pcg_iters = it;
+    if (newflags) atomicOr(&sc->flags, newflags);
+    sc->beta = beta;
+    sc->rz = rz_new;
+    sc->rr = rr;
     sc->pcg_done = done;
     if (d.host_sig)
       *(volatile unsigned long long*)d.host_sig =
@@ -582,8 +646,29 @@ static MvShape matvec_shape(const TileShape& ts, bool backsub) {
   return sh;
 }
 
-void launch_pcg_init(const BaDev& d, unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
-  k_pcg_update<true><<<(d.V + 127) / 128, 128, 0, st>>>(d, 0.0, 0, epoch);
+static int tail_grid(const BaDev& d) {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 1;
+  }
+  int g = (d.V + 7) / 8;                  // phase 1 wants one warp per camera
+  if (g < 1) g = 1;
+  return g < sms ? g : sms;               // cooperative launch: every block must be resident
+}
+
+template <int MODE>
+static void launch_tail(const BaDev& d, double tol, int max_iter, unsigned epoch, bool dvdc_quirk, cudaStream_t st) {
+  BaDev dd = d;
+  int quirk = dvdc_quirk ? 1 : 0;
+  void* args[] = {&dd, &tol, &max_iter, &epoch, &quirk};
+  cudaLaunchCooperativeKernel((const void*)k_pcg_tail<MODE>, dim3(tail_grid(d)), dim3(256), args, 0, st);
+}
+
+void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
+  launch_tail<0>(d, 0.0, 0, epoch, dvdc_quirk, st);
   lc.launches++;
 }
 
@@ -608,22 +693,18 @@ void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_
   lc.launches++;
 }
 
-void launch_camsum12(const BaDev& d, bool fuse_apq, cudaStream_t st, LaunchCounter& lc) {
-  const int grid = (d.V + 15) / 16;
-  if (fuse_apq)
-    k_camsum12<true><<<grid, 256, 0, st>>>(d);
+void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
+  k_camsum12<<<(d.V + 7) / 8, 256, 0, st>>>(d);
+  lc.launches++;
+}
+
+// the vector part of a PCG iteration; from_rows: y from the segment rows (one GPU), else from svec
+void launch_pcg_tail(const BaDev& d, bool from_rows, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
+                     cudaStream_t st, LaunchCounter& lc) {
+  if (from_rows)
+    launch_tail<1>(d, tol, max_iter, epoch, dvdc_quirk, st);
   else
-    k_camsum12<false><<<grid, 256, 0, st>>>(d);
-  lc.launches++;
-}
-
-void launch_apq(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
-  k_apq<<<(7 * d.V + 255) / 256, 256, 0, st>>>(d);
-  lc.launches++;
-}
-
-void launch_pcg_update(const BaDev& d, double tol, int max_iter, unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
-  k_pcg_update<false><<<(d.V + 127) / 128, 128, 0, st>>>(d, tol, max_iter, epoch);
+    launch_tail<2>(d, tol, max_iter, epoch, dvdc_quirk, st);
   lc.launches++;
 }
 

@@ -122,8 +122,8 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
     CARVE(S_P, 7 * V, p);
     CARVE(S_Q, 7 * V, q);
     CARVE(S_GVEC, 7 * V, gvec);
-    CARVE(S_RED_A, 7 * V / 256 + V / 16 + 8, red_a);
-    CARVE(S_RED_B, 2 * (V / 128 + 2), red_b);
+    CARVE(S_RED_A, 1024, red_a);
+    CARVE(S_RED_B, 2048, red_b);
     CARVE(S_CAMS_BAK, 7 * V, cams_backup);
     CARVE(S_PTS_BAK, 3 * N, pts_backup);
     CARVE(S_CAMROW_PTR, V + 1, camrow_ptr);
@@ -296,7 +296,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     }
     launch_cam_blocks(d, st, lc);
     const unsigned pcg_epoch = ++ctx->pcg_epoch;
-    launch_pcg_init(d, pcg_epoch, st, lc);
+    launch_pcg_init(d, pcg_epoch, quirk, st, lc);
     pt.end(PH_CAMREDUCE, t0);
 
     // ---- PCG.  Kernels of an already-converged solve exit at their first instruction, so launching
@@ -307,21 +307,17 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     // done flag of batch b is inspected after batch b+1 has been queued.
     t0 = pt.begin();
     auto launch_iteration = [&](unsigned epoch) -> int {
-      launch_cam_iter(d, nullptr, true, quirk, st, lc);
       cudaEvent_t kb = pt.kbegin();
       launch_matvec(d, ts, false, quirk, st, lc);
       pt.kend("matvec", kb);
-      kb = pt.kbegin();
-      launch_camsum12(d, !multi, st, lc);
-      pt.kend("camsum12", kb);
       if (multi) {
+        launch_camsum12(d, st, lc);
         const int r2 = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st);
         if (r2 != 0) return r2;
-        launch_apq(d, st, lc);
       }
       kb = pt.kbegin();
-      launch_pcg_update(d, tol, max_iter, epoch, st, lc);
-      pt.kend("pcg_update", kb);
+      launch_pcg_tail(d, !multi, tol, max_iter, epoch, quirk, st, lc);
+      pt.kend("pcg_tail", kb);
       return 0;
     };
     if (!multi) {
