@@ -211,7 +211,7 @@ def run_ours(args):
                             obs_cam=pin['obs_cam'].numpy(), obs_pt=pin['obs_pt'].numpy(), rowptr=pin['rowptr'].numpy())
     assert hp.cams.ctypes.data == pin['cams'].data_ptr()
     cams_h0, pts_h0 = prob.cams.copy(), prob.pts.copy()
-    h2d = sum(getattr(hp, k).nbytes for k in ('cams', 'pts', 'obs_uv', 'obs_cam', 'obs_pt', 'rowptr'))
+    h2d = sum(getattr(hp, k).nbytes for k in ('cams', 'pts', 'obs_uv', 'obs_cam', 'rowptr'))   # obs_pt is not uploaded
     d2h = hp.cams.nbytes + hp.pts.nbytes
     e2e_steps = max(1, min(args.steps, 5))
     for _ in range(min(args.warmup, 2)):
@@ -219,14 +219,17 @@ def run_ours(args):
         hp.pts[...] = pts_h0
         eng.ba_solve_host(hp, opt)
     barrier()
-    t0 = time.perf_counter()
+    e2e_sum = 0.0
     for _ in range(e2e_steps):
-        hp.cams[...] = cams_h0
+        hp.cams[...] = cams_h0                   # harness: restore the inputs (the solve is in place); not timed
         hp.pts[...] = pts_h0
-        r2 = eng.ba_solve_host(hp, opt)          # returns after the D2H copies have completed
+        barrier()
+        t0 = time.perf_counter()
+        r2 = eng.ba_solve_host(hp, opt)          # H2D of every input, solve, D2H of cameras and points
+        e2e_sum += time.perf_counter() - t0
         launches_e2e = r2.kernel_launches
     barrier()
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
+    e2e_s = torch.tensor([e2e_sum], dtype=torch.float64, device='cuda')
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_s = float(e2e_s.item())

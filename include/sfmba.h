@@ -73,7 +73,9 @@ typedef struct {
   const float*   obs_uv;     /* f32 [2][m] SoA: all u then all v.  Pixel coordinates when cam_kinv  */
                              /* is given (cv2.KeyPoint.pt is float32), else already normalised      */
   const int32_t* obs_cam;    /* i32 [m] camera index of each observation                            */
-  const int32_t* obs_pt;     /* i32 [m] point index, non-decreasing (point-major order)             */
+  const int32_t* obs_pt;     /* i32 [m] point index, non-decreasing (point-major order).  Read only */
+                             /* by sfmba_residual_jacobian / sfmba_ba_cost; the solve derives it   */
+                             /* from pt_rowptr and accepts NULL                                    */
   const int32_t* pt_rowptr;  /* i32 [N+1] CSR offsets into the observation arrays                   */
   const double*  cam_kinv;   /* f64 [V][9] row-major K^-1 per camera, or NULL = identity            */
                              /* (ba_processor.py:339-342: b = K^-1 [u,v,1]^T / z)                   */

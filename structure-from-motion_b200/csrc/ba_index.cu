@@ -123,6 +123,7 @@ struct BuildSmem {
   int seg_start[SEG_CAP + 1];       // first sorted position of each segment (+ end)
   int seg_lane0[SEG_CAP + 1];       // first lane of each segment (+ end)
   uint16_t lane_seg[RUN_LANES];
+  int rowp[GROUP_PT_CAP + 1];       // pt_rowptr of the group's points (observation -> point by bisection)
 };
 
 // one CTA per group: sort each chunk by camera, cut segments into runs of K, emit records and tables
@@ -141,6 +142,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
   const int nc = c1 - c0;
   const int K = nc == 1 ? d.grp_K[g] : 1;
   const int tid = threadIdx.x;
+  for (int i = tid; i <= pt1 - pt0; i += RUN_LANES) s.rowp[i] = d.rowptr[pt0 + i];
   if (tid == 0) {
     GroupMeta gm;
     gm.pt0 = pt0;
@@ -239,7 +241,12 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
           const int pos = (int)(key & 2047u);
           const int cam = (int)(key >> 11);
           const int o = obs0 + pos;
-          const int ptl = d.obs_pt[o] - pt0;
+          int lo = 0, hi = pt1 - pt0;                       // last point j with rowp[j] <= o
+          while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (s.rowp[mid] <= o) lo = mid; else hi = mid;
+          }
+          const int ptl = lo;
           ix = (uint32_t)ptl | ((uint32_t)pos << 10) | ((uint32_t)sg << 21);
           double bb[2];
           normalise_obs(d.kinv ? d.kinv + 9 * (size_t)cam : nullptr, d.obs_uv[o], d.obs_uv[d.m + o], bb);

@@ -82,7 +82,7 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
     return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "bad problem sizes");
   if (pr->num_cams == 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "num_cams == 0");
   if (!pr->cams || (pr->num_pts > 0 && !pr->pts) || !pr->pt_rowptr ||
-      (pr->num_obs > 0 && (!pr->obs_uv || !pr->obs_cam || !pr->obs_pt)))
+      (pr->num_obs > 0 && (!pr->obs_uv || !pr->obs_cam || (!full && !pr->obs_pt))))
     return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "null pointer in problem");
   BaDev d;
   memset(&d, 0, sizeof(d));

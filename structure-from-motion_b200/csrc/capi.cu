@@ -157,18 +157,17 @@ int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
                V = (size_t)std::max(pr->num_cams, 0);
   int rc;
   float* d_uv;
-  int32_t *d_cam, *d_pt, *d_row;
+  int32_t *d_cam, *d_row;
   double *d_kinv = nullptr, *d_cams, *d_pts;
   if ((rc = stage_in(ctx, 0, pr->obs_uv, 2 * m, &d_uv, st))) return rc;
   if ((rc = stage_in(ctx, 1, pr->obs_cam, m, &d_cam, st))) return rc;
-  if ((rc = stage_in(ctx, 2, pr->obs_pt, m, &d_pt, st))) return rc;
   if ((rc = stage_in(ctx, 3, pr->pt_rowptr, N + 1, &d_row, st))) return rc;
   if (pr->cam_kinv && (rc = stage_in(ctx, 4, pr->cam_kinv, 9 * V, &d_kinv, st))) return rc;
   if ((rc = stage_in(ctx, 5, pr->cams, 7 * V, &d_cams, st))) return rc;
   if ((rc = stage_in(ctx, 6, pr->pts, 3 * N, &d_pts, st))) return rc;
   dp.obs_uv = d_uv;
   dp.obs_cam = d_cam;
-  dp.obs_pt = d_pt;
+  dp.obs_pt = nullptr;   // the solve derives the point of an observation from pt_rowptr
   dp.pt_rowptr = d_row;
   dp.cam_kinv = pr->cam_kinv ? d_kinv : nullptr;
   dp.cams = d_cams;
