@@ -1,0 +1,56 @@
+"""Two-rank NCCL run of the point-sharded solve (needs 2 GPUs; skipped otherwise): every rank must end
+with the cameras of the single-GPU solve and its own shard of the points."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+sys.path.insert(0, %(root)r)
+import sfm_b200
+from sfm_b200 import synthetic
+rank, world = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
+torch.cuda.set_device(rank)
+dist.init_process_group('nccl', device_id=torch.device('cuda', rank))
+buf = torch.zeros(128, dtype=torch.uint8, device='cuda')
+if rank == 0:
+    buf.copy_(torch.frombuffer(bytearray(sfm_b200.Engine.nccl_unique_id()), dtype=torch.uint8))
+dist.broadcast(buf, 0)
+eng = sfm_b200.Engine(device=rank, world_size=world, rank=rank, nccl_unique_id=bytes(buf.cpu().numpy().tobytes()))
+full, _ = synthetic.make_shape('ladybug')
+sh = synthetic.shard_problem(full, world, rank)
+res = eng.ba_solve_host(sh, lam=5.0, iterations=3)
+np.savez(os.path.join(%(out)r, 'rank%%d.npz' %% rank), cams=sh.cams, pts=sh.pts, cost=res.final_cost, c0=res.costs[0])
+eng.close()
+dist.destroy_process_group()
+'''
+
+
+def test_two_rank_solve_matches_single_gpu(engine, tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs 2 GPUs')
+    from sfm_b200 import synthetic
+    script = tmp_path / 'worker.py'
+    script.write_text(WORKER % dict(root=ROOT, out=str(tmp_path)))
+    env = dict(os.environ, MASTER_ADDR='127.0.0.1')
+    subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2',
+                    '--master-addr', '127.0.0.1', '--master-port', '29533', str(script)], check=True, env=env,
+                   timeout=600)
+    full, _ = synthetic.make_shape('ladybug')
+    res = engine.ba_solve_host(full, lam=5.0, iterations=3)
+    out = [np.load(tmp_path / ('rank%d.npz' % r)) for r in range(2)]
+    for o in out:
+        assert np.max(np.abs(o['cams'] - full.cams)) < 1e-9
+        assert abs(float(o['cost']) - res.final_cost) <= 1e-9 * res.final_cost
+        assert abs(float(o['c0']) - res.costs[0]) <= 1e-9 * res.costs[0]
+    assert np.max(np.abs(np.concatenate([o['pts'] for o in out]) - full.pts)) < 1e-8
