@@ -122,7 +122,7 @@ def run_reference(args):
         'e2e': {'value': base['value'], 'unit': 'LM iterations/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'jacobian_schur_obs_per_sec': base['obs_per_s'],
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -281,13 +281,22 @@ def run_ours(args):
         if world == 1 and not args.no_cpu:
             base = cpu_baseline(steps=1, warmup=0, shape=args.shape)
             line['cpu_baseline'] = {k: base[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
-        print(json.dumps(line))
+        emit(line)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
 
 
 def main():
+    # Libraries (NCCL_DEBUG=VERSION, torchrun banners) may print to stdout; the contract is ONE JSON line there.
+    # Everything else goes to stderr: fd 1 is pointed at stderr and the JSON line is written to the saved fd.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(real_stdout, (json.dumps(obj) + '\n').encode())
+    globals()['emit'] = emit
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=5)
