@@ -181,7 +181,8 @@ SFMBA_API int sfmba_build_visibility(sfmba_ctx* ctx, int32_t num_views, int32_t 
 
 /* ---- introspection used by bench.py ---------------------------------------------------------- */
 /* device time (ms) and launch count of named kernels accumulated since the last reset; names:
- * "linearize", "matvec", "pcg_tail", "backsub", "cost"                               */
+ * "linearize", "pcg_solve" (every PCG iteration of one LM iteration, one launch), "backsub",
+ * "cost"; and "matvec", "pcg_tail" on the multi-GPU NCCL fallback path                           */
 SFMBA_API int sfmba_profile_reset(sfmba_ctx* ctx);
 SFMBA_API int sfmba_profile_enable(sfmba_ctx* ctx, int enable);    /* per-kernel event timing (adds syncs)    */
 SFMBA_API int sfmba_profile_get(sfmba_ctx* ctx, const char* name, double* ms_total, int64_t* launches);

@@ -66,6 +66,9 @@ struct Scalars {
   uint32_t ticket_a;     // "last block done" tickets of the multi-CTA PCG kernels
   uint32_t ticket_b;
   double costs[SFMBA_MAX_COST_HISTORY];
+  // k_pcg_solve phase clocks (ns, summed over the solve, seen from CTA 0): matvec, peer exchange,
+  // q = Ap - y, x/r/z update, direction update
+  unsigned long long pcg_ns[5];
 };
 
 // One 32-byte load tells a tile CTA everything it needs to start staging its group.
@@ -84,6 +87,25 @@ struct ChunkInfo {
 };
 
 // Device view of one BA problem plus its workspace.  Plain pointers so kernels take it by value.
+// Peer exchange window, one per rank, every rank maps every other rank's window (CUDA IPC over
+// NVLink / NVSwitch).  Layout of a window: 256-byte header = flags[2][MAX_PEERS] (u64, written by the
+// peers) + this rank's exchange counter; then data[2][world][cap] doubles: slot (parity, r) is
+// written by rank r only.  An exchange with counter value s uses parity s & 1; a rank can enter
+// exchange s + 1 only after every peer has signalled s, and a peer signals s only after it has left
+// exchange s - 1 (stream order), so two parities suffice.
+constexpr int MAX_PEERS = 8;
+constexpr int PEER_HEADER_BYTES = 256;
+struct PeerWindow {
+  int world, rank;
+  unsigned long long cap;             // doubles per (parity, rank) slot
+  char* base[MAX_PEERS];              // window of every rank in this rank's address space
+  __host__ __device__ unsigned long long* flags(int r) const { return reinterpret_cast<unsigned long long*>(base[r]); }
+  __host__ __device__ unsigned long long* counter() const { return flags(rank) + 2 * MAX_PEERS; }
+  __host__ __device__ double* slot(int window, int parity, int writer) const {
+    return reinterpret_cast<double*>(base[window] + PEER_HEADER_BYTES) + ((size_t)parity * world + writer) * cap;
+  }
+};
+
 struct BaDev {
   int V, N, m;
   int G;                              // groups
@@ -133,7 +155,7 @@ struct BaDev {
   double* cams_backup;                // [V][7]  adaptive mode
   double* pts_backup;                 // [N][3]
   Scalars* sc;
-  unsigned long long* host_sig;       // pinned, device-visible: (epoch << 32) | (pcg_iters << 1) | done
+  PeerWindow xw;                      // NVLink peer exchange window (world > 1 and peers mapped), else world = 0
 };
 
 struct LaunchCounter {
@@ -175,14 +197,18 @@ void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);       
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
-void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
+void launch_pcg_init(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool dvdc_quirk, cudaStream_t st,
                      LaunchCounter& lc);
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc);
+// whole PCG solve in one persistent cooperative launch (one GPU, or several with peer windows);
+// leaves camit = rows of x for the back-substitution.  false: cannot launch (no resident CTA)
+bool launch_pcg_solve(const BaDev& d, const TileShape& ts, bool peer, double tol, int max_iter, bool dvdc_quirk,
+                      cudaStream_t st, LaunchCounter& lc);
 void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // part12 -> svec (multi-GPU)
-void launch_pcg_tail(const BaDev& d, bool from_rows, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
-                     cudaStream_t st, LaunchCounter& lc);
+// NCCL fallback path (several GPUs without peer windows): one PCG iteration's vector part, y = svec
+void launch_pcg_tail(const BaDev& d, double tol, int max_iter, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

@@ -20,6 +20,9 @@
 #include "sfmba_device.cuh"
 #include <cooperative_groups.h>
 
+#include <stdio.h>
+#include <stdlib.h>
+
 #include "tile.cuh"
 
 namespace cg = cooperative_groups;
@@ -103,25 +106,31 @@ __host__ __device__ inline size_t mv_smem_bytes(const MvShape& s) {
   return b;
 }
 
+// One group (blockIdx-independent, so a persistent kernel can walk over groups).  Ends with a
+// block-wide barrier unless BACKSUB, so the shared memory can be restaged right away.
 template <bool BACKSUB>
-__global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, int dvdc_quirk) {
-  extern __shared__ __align__(16) double smem[];
-  if (!BACKSUB && d.sc->pcg_done) return;
-  const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
+__device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, int dvdc_quirk, int grp, double* smem) {
+  // The shape words and the lane id pass through an empty asm: when this body sits inside a persistent
+  // kernel's group loop, the compiler would otherwise hoist every address derived from them out of the
+  // loop and keep them live across it, which costs the inner loops their registers.
+  int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap, seg_cap = sh.seg_cap, k_cap = sh.k_cap;
+  int un_doubles = sh.un_doubles, vn_doubles = sh.vn_doubles;
+  int tid = threadIdx.x;
+  asm volatile("" : "+r"(pt_cap), "+r"(slot_cap), "+r"(seg_cap), "+r"(k_cap), "+r"(un_doubles), "+r"(vn_doubles),
+               "+r"(tid));
   double* Xa = smem;                               // AoS [np][3]
   double* tacc = Xa + 3 * pt_cap;                  // SoA [3][pt_cap]
   double* Dn = tacc + 3 * pt_cap;                  // SoA [6][pt_cap]
   double* Vn = Dn + 6 * pt_cap;                    // SoA [3][pt_cap] v_j (back-substitution only)
-  double* un = Vn + sh.vn_doubles;
-  double* camc = un + sh.un_doubles;
+  double* un = Vn + vn_doubles;
+  double* camc = un + un_doubles;
   ChunkStage cs;
-  cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * sh.seg_cap);
-  cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
-  cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (sh.seg_cap + 3) / 4 * 4);
+  cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * seg_cap);
+  cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)k_cap * RUN_LANES);
+  cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (seg_cap + 3) / 4 * 4);
   cs.bs = nullptr;
   int32_t* rowp = reinterpret_cast<int32_t*>(cs.srun + SEG_RUN_STRIDE + 6);
-  const int tid = threadIdx.x;
-  const GroupMeta gm = d.grp_meta[blockIdx.x];
+  const GroupMeta gm = d.grp_meta[grp];
   const int np = gm.np, pt0 = gm.pt0, c0 = gm.c0, c1 = gm.c0 + gm.nc;
   {
     const size_t N = (size_t)d.N;
@@ -314,6 +323,13 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
   }
 }
 
+template <bool BACKSUB>
+__global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, int dvdc_quirk) {
+  extern __shared__ __align__(16) double smem[];
+  if (!BACKSUB && d.sc->pcg_done) return;
+  matvec_group<BACKSUB>(d, sh, dvdc_quirk, blockIdx.x, smem);
+}
+
 // ---- "last block" finish of a grid-wide sum: per-block partials are summed in block order ----------
 // Returns true in every thread of the block that finished last; `total` is then valid in all of them.
 template <int NV>
@@ -423,7 +439,9 @@ __global__ void __launch_bounds__(256) k_camsum12(BaDev d) {
 // The vector part of one PCG iteration in ONE cooperative launch (grid-wide barriers between phases).
 //   MODE 0  init: x = 0, r = g, z = Minv g, rz, gg, p = z, camit(p)
 //   MODE 1  phase 1: y from the segment rows, q = A p - y, p.q            (single GPU)
-//   MODE 2  phase 1: y = svec (already all-reduced), q = A p - y, p.q     (several GPUs)
+//   MODE 2  phase 1: y = svec (already all-reduced), q = A p - y, p.q     (several GPUs, NCCL)
+//   MODE 3  phase 0: this rank's partial y from its rows, stored into every rank's peer window
+//           over NVLink; flags; phase 1: y = sum over ranks in rank order (several GPUs, fused)
 //   phase 2: alpha = rz / p.q;  x += alpha p;  r' = r - alpha q;  z = Minv r';  r'.z, r'.r
 //   phase 3: beta = rz' / rz;  convergence test and host signal;  r = r';  p = z + beta p;  camit(p)
 // Every block sums the per-block partials itself, in block order, so all blocks hold identical scalars.
@@ -434,8 +452,45 @@ __device__ __forceinline__ double all_blocks_sum(const double* __restrict__ part
   return block_sum(a, red);
 }
 
+// ---- system-scope flag accesses for the peer exchange (flags live in peer HBM, reached over NVLink)
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+constexpr unsigned long long PEER_TIMEOUT_NS = 20ull * 1000ull * 1000ull * 1000ull;
+
+// Signal "this rank's slot of exchange `seq` is complete" to every rank, then wait for all ranks.
+// Call after a grid-wide barrier that follows the (system-fenced) slot stores; every block waits
+// for itself.  A peer that never arrives (crashed rank) raises FLAG_PEER_TIMEOUT instead of hanging.
+__device__ __forceinline__ void peer_signal_and_wait(const PeerWindow& xw, unsigned long long seq, Scalars* sc) {
+  const int par = (int)(seq & 1ull);
+  if (blockIdx.x == 0 && (int)threadIdx.x < xw.world)
+    st_release_sys(xw.flags(threadIdx.x) + par * MAX_PEERS + xw.rank, seq);
+  if ((int)threadIdx.x < xw.world) {
+    const unsigned long long* f = xw.flags(xw.rank) + par * MAX_PEERS + threadIdx.x;
+    const unsigned long long t0 = global_timer_ns();
+    unsigned spins = 0;
+    while (ld_acquire_sys(f) < seq) {
+      if ((++spins & 0x3ffu) == 0 && global_timer_ns() - t0 > PEER_TIMEOUT_NS) {
+        atomicOr(&sc->flags, FLAG_PEER_TIMEOUT);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
 template <int MODE>
-__global__ void __launch_bounds__(256) k_pcg_tail(BaDev d, double tol, int max_iter, unsigned epoch, int dvdc_quirk) {
+__global__ void __launch_bounds__(256) k_pcg_tail(BaDev d, double tol, int max_iter, int dvdc_quirk) {
   __shared__ double red[32];
   cg::grid_group grid = cg::this_grid();
   Scalars* sc = d.sc;
@@ -453,7 +508,6 @@ __global__ void __launch_bounds__(256) k_pcg_tail(BaDev d, double tol, int max_i
       const int cam = c0 + (gtid >> 5);
       const bool live = cam < d.V;
       double y = 0.0;
-      if (MODE == 1) y = cam_y_from_rows(d, cam, sub, live);
       if (live && sub < 7) {
         const size_t k = 7 * (size_t)cam + sub;
         if (MODE == 2) y = d.svec[k];
@@ -554,9 +608,271 @@ __global__ void __launch_bounds__(256) k_pcg_tail(BaDev d, double tol, int max_i
     sc->rz = rz_new;
     sc->rr = rr;
     sc->pcg_done = done;
-    if (d.host_sig)
-      *(volatile unsigned long long*)d.host_sig =
-          ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
+  }
+}
+
+// ---- the whole PCG solve of one LM iteration in ONE persistent cooperative launch -------------------
+// Grid = as many CTAs as are co-resident (4 per SM); a CTA walks over groups g = blockIdx, + gridDim, ...
+// for the matvec, then the grid meets at a barrier and runs the vector part with one warp per camera
+// (lane a < 7 owns entry a of the camera's 7-vectors; x, r, z, p, q are touched by their owner only,
+// so only camit, the segment rows and the dot-product partials cross a grid barrier).
+//   init      x = 0, r = g, z = Minv g, p = z, camit(p); rz, gg
+//   A         matvec over the groups -> segment rows (part12)
+//   [PEER]    partial y of this rank -> every rank's window over NVLink; flags
+//   B         y per camera, q = A p - y, p.q
+//   C         alpha; x += alpha p; r -= alpha q; z = Minv r; r.z, r.r
+//   D         beta; convergence; p = z + beta p; camit(p)
+// At exit camit holds the rows of x (the back-substitution direction), so k_matvec<true> follows directly.
+__device__ __forceinline__ double row7_dot(const double* __restrict__ M49, int lane, double v_lane) {
+  double a = 0.0;
+#pragma unroll
+  for (int b = 0; b < 7; ++b) {
+    const double vb = __shfl_sync(0xffffffffu, v_lane, b);
+    if (lane < 7) a += M49[lane * 7 + b] * vb;
+  }
+  return a;
+}
+
+// lanes 0..6 hold a direction (dC, dq) of camera `cam`: lane 0 writes its camit row
+__device__ __forceinline__ void camit_from_lanes(const BaDev& d, int cam, int lane, double v_lane, int dvdc_quirk) {
+  double dl[7];
+#pragma unroll
+  for (int b = 0; b < 7; ++b) dl[b] = __shfl_sync(0xffffffffu, v_lane, b);
+  if (lane == 0) write_camit(d, cam, dl, dvdc_quirk);
+}
+
+// Loop-carried state of the solve lives in shared memory (every CTA holds the same values): nothing
+// but addresses stays live in registers across the matvec, whose inner loops need all 128 of them.
+struct SolveCarry {
+  double rz, gg, rr, alpha, beta;
+  unsigned long long xseq, stamp, ns[5];
+  int it, done, grp;
+  uint32_t newflags;
+};
+
+#ifndef SOLVE_CTAS
+#define SOLVE_CTAS 3
+#endif
+template <bool PEER>
+__global__ void __launch_bounds__(RUN_LANES, SOLVE_CTAS)
+k_pcg_solve(BaDev d, MvShape sh, double tol, int max_iter, int dvdc_quirk) {
+  extern __shared__ __align__(16) double smem[];
+  __shared__ double red[32];
+  __shared__ SolveCarry cy;
+  cg::grid_group grid = cg::this_grid();
+  const int tid = threadIdx.x;
+  const bool clock_thread = blockIdx.x == 0 && tid == 0;
+  auto lap = [&](int which) {
+    if (clock_thread) {
+      const unsigned long long now = global_timer_ns();
+      cy.ns[which] += now - cy.stamp;
+      cy.stamp = now;
+    }
+  };
+  // ---- init
+  {
+    const int lane = tid & 31;
+    const int gwarp = (blockIdx.x * RUN_LANES + tid) >> 5, nwarps = gridDim.x * (RUN_LANES / 32);
+    const bool l7 = lane < 7;
+    double v0 = 0.0, v1 = 0.0;
+    for (int cam = gwarp; cam < d.V; cam += nwarps) {
+      const size_t k = 7 * (size_t)cam + lane;
+      const double g = l7 ? d.gvec[k] : 0.0;
+      const double z = row7_dot(d.minv + 49 * (size_t)cam, lane, g);
+      if (l7) {
+        d.x[k] = 0.0;
+        d.r[k] = g;
+        d.p[k] = z;
+        v0 += g * z;
+        v1 += g * g;
+      }
+      camit_from_lanes(d, cam, lane, z, dvdc_quirk);
+    }
+    v0 = block_sum(v0, red);
+    v1 = block_sum(v1, red);
+    if (tid == 0) {
+      d.red_b[2 * blockIdx.x] = v0;
+      d.red_b[2 * blockIdx.x + 1] = v1;
+    }
+    grid.sync();
+    const double rz = all_blocks_sum(d.red_b, 2, 0, red);
+    const double gg = all_blocks_sum(d.red_b, 2, 1, red);
+    if (tid == 0) {
+      cy.rz = rz;
+      cy.gg = gg;
+      cy.rr = gg;
+      cy.alpha = 0.0;
+      cy.beta = 0.0;
+      cy.it = 0;
+      cy.newflags = !(gg == gg) ? FLAG_NONFINITE : 0u;
+      cy.done = (gg == 0.0 || !(gg == gg)) ? 1 : 0;
+      cy.xseq = PEER ? *d.xw.counter() : 0ull;       // rewritten by one thread at the very end
+#pragma unroll
+      for (int k = 0; k < 5; ++k) cy.ns[k] = 0ull;
+      cy.stamp = global_timer_ns();
+    }
+    __syncthreads();
+  }
+  while (!cy.done) {
+    // ---- A: matvec.  Groups are handed out by a ticket counter (one per iteration parity; the idle
+    // one is re-armed in phase C), fetched one group ahead so the atomic's latency hides behind work.
+    {
+      uint32_t* ctr = (cy.it & 1) ? &d.sc->ticket_b : &d.sc->ticket_a;
+      if (tid == 0) cy.grp = (int)atomicAdd(ctr, 1u);
+      __syncthreads();
+      int g = cy.grp;
+      while (g < d.G) {
+        unsigned nxt = 0;
+        if (tid == 0) nxt = atomicAdd(ctr, 1u);
+        matvec_group<false>(d, sh, dvdc_quirk, g, smem);
+        if (tid == 0) cy.grp = (int)nxt;
+        __syncthreads();
+        g = cy.grp;
+      }
+    }
+    grid.sync();
+    lap(0);
+    // ---- vector part: one warp per camera
+    const int lane = tid & 31;
+    const int gwarp = (blockIdx.x * RUN_LANES + tid) >> 5, nwarps = gridDim.x * (RUN_LANES / 32);
+    const bool l7 = lane < 7;
+    const int V = d.V;
+    Scalars* sc = d.sc;
+    unsigned long long xseq = cy.xseq;
+    if (PEER) {
+      const PeerWindow& xw = d.xw;
+      ++xseq;
+      const int par = (int)(xseq & 1ull);
+      for (int cam = gwarp; cam < V; cam += nwarps) {
+        const double y = cam_y_from_rows(d, cam, lane, true);
+        if (l7) {
+          const size_t k = 7 * (size_t)cam + lane;
+          for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
+        }
+      }
+      __threadfence_system();
+      grid.sync();
+      peer_signal_and_wait(xw, xseq, sc);
+      lap(1);
+    }
+    // ---- B: q = A p - y, p.q
+    double pq = 0.0;
+    for (int cam = gwarp; cam < V; cam += nwarps) {
+      const size_t k = 7 * (size_t)cam + lane;
+      double y = 0.0;
+      if (PEER) {
+        if (l7) {
+          const int par = (int)(xseq & 1ull);
+          for (int w = 0; w < d.xw.world; ++w) y += __ldcg(d.xw.slot(d.xw.rank, par, w) + k);
+        }
+      } else {
+        y = cam_y_from_rows(d, cam, lane, true);
+      }
+      const double pv = l7 ? d.p[k] : 0.0;
+      const double ap = row7_dot(d.ablk + 49 * (size_t)cam, lane, pv);
+      if (l7) {
+        const double qv = ap - y;
+        d.q[k] = qv;
+        pq += pv * qv;
+      }
+    }
+    pq = block_sum(pq, red);
+    if (tid == 0) d.red_a[blockIdx.x] = pq;
+    grid.sync();
+    lap(2);
+    int it = cy.it;
+    if (clock_thread) *((it & 1) ? &sc->ticket_a : &sc->ticket_b) = 0u;   // the next iteration's counter
+    const double rz = cy.rz, gg = cy.gg;
+    const double pq_all = all_blocks_sum(d.red_a, 1, 0, red);
+    const double alpha = rz / pq_all;
+    // ---- C: x += alpha p, r -= alpha q, z = Minv r
+    double v0 = 0.0, v1 = 0.0;
+    for (int cam = gwarp; cam < V; cam += nwarps) {
+      const size_t k = 7 * (size_t)cam + lane;
+      double rn = 0.0;
+      if (l7) {
+        d.x[k] += alpha * d.p[k];
+        rn = d.r[k] - alpha * d.q[k];
+      }
+      const double z = row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
+      if (l7) {
+        d.r[k] = rn;
+        d.z[k] = z;
+        v0 += rn * z;
+        v1 += rn * rn;
+      }
+    }
+    v0 = block_sum(v0, red);
+    v1 = block_sum(v1, red);
+    if (tid == 0) {
+      d.red_b[2 * blockIdx.x] = v0;
+      d.red_b[2 * blockIdx.x + 1] = v1;
+    }
+    grid.sync();
+    lap(3);
+    const double rz_new = all_blocks_sum(d.red_b, 2, 0, red);
+    const double rr = all_blocks_sum(d.red_b, 2, 1, red);
+    const double beta = rz_new / rz;
+    ++it;
+    uint32_t newflags = cy.newflags;
+    int done = 0;
+    if (!(pq_all > 0.0) || !(rr == rr)) {            // p.q <= 0 or NaN
+      newflags |= FLAG_NONFINITE;
+      done = 1;
+    }
+    if (rr <= tol * tol * gg) done = 1;
+    if (PEER && (*(volatile uint32_t*)&sc->flags & FLAG_PEER_TIMEOUT)) done = 1;
+    if (!done && it >= max_iter) {
+      newflags |= FLAG_PCG_MAXITER;
+      done = 1;
+    }
+    // ---- D: next direction (or, when done, the camit rows of x for the back-substitution)
+    for (int cam = gwarp; cam < V; cam += nwarps) {
+      const size_t k = 7 * (size_t)cam + lane;
+      double pn = 0.0;
+      if (l7) {
+        pn = d.z[k] + beta * d.p[k];
+        d.p[k] = pn;
+      }
+      const double dir = done ? (l7 ? d.x[k] : 0.0) : pn;
+      camit_from_lanes(d, cam, lane, dir, dvdc_quirk);
+    }
+    __syncthreads();                                  // every thread has read the carry of this iteration
+    if (tid == 0) {
+      cy.rz = rz_new;
+      cy.rr = rr;
+      cy.alpha = alpha;
+      cy.beta = beta;
+      cy.it = it;
+      cy.done = done;
+      cy.newflags = newflags;
+      cy.xseq = xseq;
+    }
+    if (!done) grid.sync();
+    else __syncthreads();
+    lap(4);
+  }
+  if (cy.it == 0) {                                   // zero right-hand side: x = 0
+    const int lane = tid & 31;
+    const int gwarp = (blockIdx.x * RUN_LANES + tid) >> 5, nwarps = gridDim.x * (RUN_LANES / 32);
+    for (int cam = gwarp; cam < d.V; cam += nwarps) camit_from_lanes(d, cam, lane, 0.0, dvdc_quirk);
+  }
+  if (clock_thread) {
+    Scalars* sc = d.sc;
+    if (PEER) *d.xw.counter() = cy.xseq;
+    sc->ticket_a = 0u;
+    sc->ticket_b = 0u;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) sc->pcg_ns[k] += cy.ns[k];
+    sc->gg = cy.gg;
+    sc->pcg_iters = cy.it;
+    sc->pcg_iters_total += cy.it;
+    if (cy.newflags) atomicOr(&sc->flags, cy.newflags);
+    sc->alpha = cy.alpha;
+    sc->beta = cy.beta;
+    sc->rz = cy.rz;
+    sc->rr = cy.rr;
+    sc->pcg_done = 1;
   }
 }
 
@@ -660,15 +976,15 @@ static int tail_grid(const BaDev& d) {
 }
 
 template <int MODE>
-static void launch_tail(const BaDev& d, double tol, int max_iter, unsigned epoch, bool dvdc_quirk, cudaStream_t st) {
+static void launch_tail(const BaDev& d, double tol, int max_iter, bool dvdc_quirk, cudaStream_t st) {
   BaDev dd = d;
   int quirk = dvdc_quirk ? 1 : 0;
-  void* args[] = {&dd, &tol, &max_iter, &epoch, &quirk};
+  void* args[] = {&dd, &tol, &max_iter, &quirk};
   cudaLaunchCooperativeKernel((const void*)k_pcg_tail<MODE>, dim3(tail_grid(d)), dim3(256), args, 0, st);
 }
 
-void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
-  launch_tail<0>(d, 0.0, 0, epoch, dvdc_quirk, st);
+void launch_pcg_init(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
+  launch_tail<0>(d, 0.0, 0, dvdc_quirk, st);
   lc.launches++;
 }
 
@@ -693,18 +1009,57 @@ void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_
   lc.launches++;
 }
 
+// persistent PCG solve: grid = co-resident CTAs (cooperative launch)
+template <bool PEER>
+static int launch_solve_t(const BaDev& d, const MvShape& sh, size_t smem, double tol, int max_iter, int quirk,
+                          cudaStream_t st) {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  cudaFuncSetAttribute(k_pcg_solve<PEER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int per_sm = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_solve<PEER>, RUN_LANES, smem);
+  if (per_sm < 1) return 0;
+  int grid = per_sm * sms;
+  if (grid > d.G) grid = d.G;
+  if (grid > 1024) grid = 1024;                     // red_a / red_b hold one partial per CTA
+  static bool told = false;
+  if (!told && getenv("SFMBA_DEBUG")) {
+    told = true;
+    fprintf(stderr, "[sfmba] k_pcg_solve: %d CTAs/SM x %d SMs, grid %d for %d groups, %zu B dynamic smem "
+            "(slot_cap %d pt_cap %d seg_cap %d k_cap %d)\n", per_sm, sms, grid, d.G, smem, sh.slot_cap, sh.pt_cap,
+            sh.seg_cap, sh.k_cap);
+  }
+  BaDev dd = d;
+  MvShape s2 = sh;
+  void* args[] = {&dd, &s2, &tol, &max_iter, &quirk};
+  cudaLaunchCooperativeKernel((const void*)k_pcg_solve<PEER>, dim3(grid), dim3(RUN_LANES), args, smem, st);
+  return grid;
+}
+
+bool launch_pcg_solve(const BaDev& d, const TileShape& ts, bool peer, double tol, int max_iter, bool dvdc_quirk,
+                      cudaStream_t st, LaunchCounter& lc) {
+  if (d.G <= 0) return false;
+  const MvShape sh = matvec_shape(ts, false);
+  const size_t smem = mv_smem_bytes(sh);
+  const int grid = peer ? launch_solve_t<true>(d, sh, smem, tol, max_iter, dvdc_quirk ? 1 : 0, st)
+                        : launch_solve_t<false>(d, sh, smem, tol, max_iter, dvdc_quirk ? 1 : 0, st);
+  if (grid <= 0) return false;
+  lc.launches++;
+  return true;
+}
+
 void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
   k_camsum12<<<(d.V + 7) / 8, 256, 0, st>>>(d);
   lc.launches++;
 }
 
 // the vector part of a PCG iteration; from_rows: y from the segment rows (one GPU), else from svec
-void launch_pcg_tail(const BaDev& d, bool from_rows, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
-                     cudaStream_t st, LaunchCounter& lc) {
-  if (from_rows)
-    launch_tail<1>(d, tol, max_iter, epoch, dvdc_quirk, st);
-  else
-    launch_tail<2>(d, tol, max_iter, epoch, dvdc_quirk, st);
+void launch_pcg_tail(const BaDev& d, double tol, int max_iter, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
+  launch_tail<2>(d, tol, max_iter, dvdc_quirk, st);
   lc.launches++;
 }
 

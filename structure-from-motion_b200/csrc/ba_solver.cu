@@ -97,7 +97,6 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
   d.kinv = pr->cam_kinv;
   d.cams = pr->cams;
   d.pts = pr->pts;
-  d.host_sig = ctx->world == 1 ? reinterpret_cast<unsigned long long*>(ctx->pinned) : nullptr;
   int rc;
   const size_t V = (size_t)d.V, N = (size_t)std::max(d.N, 1);
   CARVE(S_SCALARS, 1, sc);
@@ -230,6 +229,14 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   const int64_t launches0 = ctx->lc.launches;
   LaunchCounter& lc = ctx->lc;
 
+  // several GPUs: map the peer windows (first solve, or more cameras than before); NCCL otherwise
+  memset(&d.xw, 0, sizeof(d.xw));
+  if (multi) {
+    if ((rc = sfm_peer_setup(ctx, (size_t)d.V * CAM_ACC + 64, st)) != 0) return rc;
+    d.xw = ctx->peer;
+  }
+  const bool peer = multi && d.xw.world == ctx->world;
+
   PhaseTimer pt{ctx, st};
   cudaEvent_t t_total = pt.begin();
 
@@ -295,62 +302,33 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
                         cudaMemcpyDeviceToDevice, st);
     }
     launch_cam_blocks(d, st, lc);
-    const unsigned pcg_epoch = ++ctx->pcg_epoch;
-    launch_pcg_init(d, pcg_epoch, quirk, st, lc);
+    const bool persistent = !multi || peer;
+    if (!persistent) launch_pcg_init(d, quirk, st, lc);
     pt.end(PH_CAMREDUCE, t0);
 
-    // ---- PCG.  Kernels of an already-converged solve exit at their first instruction, so launching
-    // past convergence is harmless but not free.  One GPU: k_pcg_update publishes (epoch, iteration,
-    // done) in one 8-byte store to pinned host memory; the host keeps LOOKAHEAD iterations queued
-    // and reads that word without any synchronisation.  Several GPUs: every rank must issue the
-    // same number of collectives, so iterations go out in fixed batches and the (rank-identical)
-    // done flag of batch b is inspected after batch b+1 has been queued.
+    // ---- PCG.  One GPU, or several with peer windows: the whole solve is one persistent cooperative
+    // launch.  NCCL fallback: every rank must issue the same number of collectives, so iterations go
+    // out in fixed batches and the (rank-identical) done flag of batch b is inspected after batch
+    // b+1 has been queued; kernels of an already-converged solve exit at their first instruction.
     t0 = pt.begin();
-    auto launch_iteration = [&](unsigned epoch) -> int {
+    auto launch_iteration = [&]() -> int {
       cudaEvent_t kb = pt.kbegin();
       launch_matvec(d, ts, false, quirk, st, lc);
       pt.kend("matvec", kb);
-      if (multi) {
-        launch_camsum12(d, st, lc);
-        const int r2 = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st);
-        if (r2 != 0) return r2;
-      }
+      launch_camsum12(d, st, lc);
+      const int r2 = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st);
+      if (r2 != 0) return r2;
       kb = pt.kbegin();
-      launch_pcg_tail(d, !multi, tol, max_iter, epoch, quirk, st, lc);
+      launch_pcg_tail(d, tol, max_iter, quirk, st, lc);
       pt.kend("pcg_tail", kb);
       return 0;
     };
-    if (!multi) {
-      const int LOOKAHEAD = 2;
-      volatile unsigned long long* sig = reinterpret_cast<volatile unsigned long long*>(ctx->pinned);
-      int launched = 0;
-      bool done = false;
-      while (launched < max_iter && !done) {
-        if (launched >= LOOKAHEAD) {
-          // wait until iteration (launched - LOOKAHEAD) has finished, or the solve is done
-          long spins = 0;
-          for (;;) {
-            const unsigned long long w = *sig;
-            if ((unsigned)(w >> 32) == pcg_epoch) {
-              if (w & 1ull) { done = true; break; }
-              if ((int)((w & 0xffffffffull) >> 1) >= launched - LOOKAHEAD + 1) break;
-            }
-            if ((++spins & 0x3fff) == 0 && cudaStreamQuery(st) != cudaErrorNotReady) {
-              const unsigned long long w2 = *sig;     // stream drained: final state or an error
-              if ((unsigned)(w2 >> 32) == pcg_epoch && (w2 & 1ull)) done = true;
-              else if (!((unsigned)(w2 >> 32) == pcg_epoch &&
-                         (int)((w2 & 0xffffffffull) >> 1) >= launched - LOOKAHEAD + 1)) {
-                if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "pcg kernels")) != 0) return rc;
-                return sfm_set_error(ctx, SFMBA_ERR_CUDA, "PCG made no progress");
-              }
-              break;
-            }
-          }
-          if (done) break;
-        }
-        if ((rc = launch_iteration(pcg_epoch)) != 0) return rc;
-        ++launched;
-      }
+    if (persistent) {
+      // one cooperative launch runs every PCG iteration: no host round trips, no launch gaps
+      cudaEvent_t kb = pt.kbegin();
+      if (!launch_pcg_solve(d, ts, peer, tol, max_iter, quirk, st, lc))
+        return sfm_set_error(ctx, SFMBA_ERR_CUDA, "k_pcg_solve: no resident CTA (shared memory)");
+      pt.kend("pcg_solve", kb);
     } else {
       const int batch = 4;
       int32_t* done_host = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ctx->pinned) + 16);
@@ -361,7 +339,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       while (launched < max_iter) {
         const int nb = std::min(batch, max_iter - launched);
         for (int k = 0; k < nb; ++k)
-          if ((rc = launch_iteration(pcg_epoch)) != 0) return rc;
+          if ((rc = launch_iteration()) != 0) return rc;
         launched += nb;
         cudaMemcpyAsync(&done_host[which], &d.sc->pcg_done, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
         cudaEvent_t ev = pt.get();
@@ -379,7 +357,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
 
     t0 = pt.begin();
     if (adaptive) launch_lm_model_decrease(d, st, lc);
-    launch_cam_iter(d, d.x, false, quirk, st, lc);
+    if (!persistent) launch_cam_iter(d, d.x, false, quirk, st, lc);   // (k_pcg_solve leaves camit = rows of x)
     {
       cudaEvent_t kb = pt.kbegin();
       launch_matvec(d, ts, true, quirk, st, lc);        // back-substitution: pts += v - Dinv B^T dp
@@ -418,6 +396,15 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "solve sync")) != 0) return rc;
   if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "solve kernels")) != 0) return rc;
   pt.resolve();
+  if (ctx->profile && hs->pcg_iters_total > 0) {
+    // phase clocks of the persistent PCG kernel, per PCG iteration
+    static const char* names[5] = {"pcg.matvec", "pcg.peer", "pcg.q", "pcg.update", "pcg.direction"};
+    for (int k = 0; k < 5; ++k) {
+      ProfileEntry& pe = ctx->prof[names[k]];
+      pe.ms += (double)hs->pcg_ns[k] * 1e-6;
+      pe.launches += hs->pcg_iters_total;
+    }
+  }
 
   if (res) {
     memset(res, 0, sizeof(*res));

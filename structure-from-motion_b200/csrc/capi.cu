@@ -131,7 +131,9 @@ int sfmba_destroy(sfmba_ctx* ctx) {
   if (!ctx) return SFMBA_OK;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  sfm_peer_destroy(ctx);
   sfm_nccl_destroy(ctx);
+  ctx->misc.release();
   for (auto& b : ctx->bufs) b.release();
   for (auto& b : ctx->host_stage) b.release();
   if (ctx->pinned) cudaFreeHost(ctx->pinned);

@@ -33,6 +33,17 @@ struct sfmba_ctx {
   // NCCL (only when world > 1)
   void* nccl_lib = nullptr;
   void* nccl_comm = nullptr;
+  // NVLink peer exchange windows (peer_window.cu); peer.world == 0 until mapped
+  void* peer_local = nullptr;
+  void* peer_mapped[sfmba::MAX_PEERS] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  sfmba::PeerWindow peer = {};
+  bool peer_disabled = false;
+  DevBuf misc;
+  cudaError_t reserve_misc(size_t bytes, void** out) {
+    const cudaError_t e = misc.reserve(bytes);
+    *out = misc.ptr;
+    return e;
+  }
   // profiling
   bool profile = false;
   std::map<std::string, ProfileEntry> prof;
@@ -44,7 +55,6 @@ struct sfmba_ctx {
   void* pinned = nullptr;        // pinned staging for results/scalars
   size_t pinned_cap = 0;
   cudaStream_t own_stream = nullptr;
-  unsigned pcg_epoch = 0;        // id of the current PCG solve (see host_sig)
 
   cudaError_t reserve(int slot, size_t bytes, void** out);
 };
@@ -58,4 +68,10 @@ int sfm_check_cuda(sfmba_ctx* ctx, cudaError_t e, const char* what);
 int sfm_nccl_unique_id(void* out128, std::string& err);
 int sfm_nccl_init(sfmba_ctx* ctx, const void* unique_id);
 int sfm_nccl_allreduce_f64(sfmba_ctx* ctx, double* buf, size_t count, cudaStream_t st);
+int sfm_nccl_allgather_bytes(sfmba_ctx* ctx, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
+int sfm_nccl_barrier(sfmba_ctx* ctx, cudaStream_t st);
 void sfm_nccl_destroy(sfmba_ctx* ctx);
+
+// peer windows (peer_window.cu)
+int sfm_peer_setup(sfmba_ctx* ctx, size_t doubles_cap, cudaStream_t st);
+void sfm_peer_destroy(sfmba_ctx* ctx);

@@ -13,8 +13,10 @@ typedef int (*fn_comm_init_rank)(void**, int, NcclUniqueId, int);
 typedef int (*fn_comm_destroy)(void*);
 typedef int (*fn_all_reduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
 typedef const char* (*fn_get_error_string)(int);
+typedef int (*fn_all_gather)(const void*, void*, size_t, int, void*, cudaStream_t);
 
 constexpr int NCCL_FLOAT64 = 8;   // ncclDataType_t ncclFloat64 / ncclDouble
+constexpr int NCCL_INT8 = 0;      // ncclDataType_t ncclInt8 / ncclChar
 constexpr int NCCL_SUM = 0;       // ncclRedOp_t ncclSum
 
 void* open_nccl(std::string& err) {
@@ -72,6 +74,26 @@ int sfm_nccl_allreduce_f64(sfmba_ctx* ctx, double* buf, size_t count, cudaStream
   const int rc = f(buf, buf, count, NCCL_FLOAT64, NCCL_SUM, ctx->nccl_comm, st);
   if (rc != 0) return sfm_set_error(ctx, SFMBA_ERR_NCCL, "ncclAllReduce failed");
   return SFMBA_OK;
+}
+
+int sfm_nccl_allgather_bytes(sfmba_ctx* ctx, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st) {
+  static fn_all_gather f = nullptr;
+  if (!f) f = (fn_all_gather)dlsym(ctx->nccl_lib, "ncclAllGather");
+  if (!f) return sfm_set_error(ctx, SFMBA_ERR_NCCL, "ncclAllGather not found");
+  const int rc = f(send, recv, bytes_per_rank, NCCL_INT8, ctx->nccl_comm, st);
+  if (rc != 0) return sfm_set_error(ctx, SFMBA_ERR_NCCL, "ncclAllGather failed");
+  return SFMBA_OK;
+}
+
+// all ranks have reached this point of `st` when the call returns
+int sfm_nccl_barrier(sfmba_ctx* ctx, cudaStream_t st) {
+  void* w = nullptr;
+  int rc = sfm_check_cuda(ctx, ctx->reserve_misc(4096, &w), "cudaMalloc(barrier word)");
+  if (rc != 0) return rc;
+  double* word = reinterpret_cast<double*>(reinterpret_cast<char*>(w) + 2048);
+  cudaMemsetAsync(word, 0, sizeof(double), st);
+  if ((rc = sfm_nccl_allreduce_f64(ctx, word, 1, st)) != 0) return rc;
+  return sfm_check_cuda(ctx, cudaStreamSynchronize(st), "nccl barrier");
 }
 
 void sfm_nccl_destroy(sfmba_ctx* ctx) {

@@ -16,6 +16,7 @@ constexpr uint32_t FLAG_DEPTH_ZERO = 2u;
 constexpr uint32_t FLAG_NONFINITE = 4u;
 constexpr uint32_t FLAG_PCG_MAXITER = 8u;
 constexpr uint32_t FLAG_SINGULAR = 16u;
+constexpr uint32_t FLAG_PEER_TIMEOUT = 32u;
 
 // q (w,x,y,z) -> R row-major, utils.py:64-97
 __device__ __forceinline__ void quat_to_rot(const double q[4], double R[9]) {
