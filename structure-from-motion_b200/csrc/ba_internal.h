@@ -66,9 +66,6 @@ struct Scalars {
   uint32_t ticket_a;     // "last block done" tickets of the multi-CTA PCG kernels
   uint32_t ticket_b;
   double costs[SFMBA_MAX_COST_HISTORY];
-  // k_pcg_solve phase clocks (ns, summed over the solve, seen from CTA 0): matvec, peer exchange,
-  // q = Ap - y, x/r/z update, direction update
-  unsigned long long pcg_ns[5];
 };
 
 // One 32-byte load tells a tile CTA everything it needs to start staging its group.
@@ -155,6 +152,7 @@ struct BaDev {
   double* cams_backup;                // [V][7]  adaptive mode
   double* pts_backup;                 // [N][3]
   Scalars* sc;
+  unsigned long long* host_sig;       // pinned, device-visible: (epoch << 32) | (pcg_iters << 1) | done; or null
   PeerWindow xw;                      // NVLink peer exchange window (world > 1 and peers mapped), else world = 0
 };
 
@@ -197,18 +195,16 @@ void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);       
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
-void launch_pcg_init(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
+void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool dvdc_quirk, cudaStream_t st,
                      LaunchCounter& lc);
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc);
-// whole PCG solve in one persistent cooperative launch (one GPU, or several with peer windows);
-// leaves camit = rows of x for the back-substitution.  false: cannot launch (no resident CTA)
-bool launch_pcg_solve(const BaDev& d, const TileShape& ts, bool peer, double tol, int max_iter, bool dvdc_quirk,
-                      cudaStream_t st, LaunchCounter& lc);
 void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // part12 -> svec (multi-GPU)
-// NCCL fallback path (several GPUs without peer windows): one PCG iteration's vector part, y = svec
-void launch_pcg_tail(const BaDev& d, double tol, int max_iter, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
+// vector part of one PCG iteration.  mode 1: y from this GPU's rows; 2: y = svec (NCCL all-reduced);
+// 3: partial y exchanged through the peer windows over NVLink inside the kernel
+void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
+                     cudaStream_t st, LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

@@ -18,14 +18,12 @@
 // converges to f64 accuracy.  All reductions have a fixed order.
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
-#include <cooperative_groups.h>
 
 #include <stdio.h>
 #include <stdlib.h>
 
+#include "launch.cuh"
 #include "tile.cuh"
-
-namespace cg = cooperative_groups;
 
 namespace sfmba {
 
@@ -51,11 +49,15 @@ __device__ __forceinline__ void quat_dRt(const double q2[4], double Q[4][9]) {
 // per camera and per matvec: (PCG) p = z + beta p, then E = sum_j p_q[j] Q_j, w = R^T p_C
 __global__ void __launch_bounds__(128) k_cam_iter(BaDev d, const double* __restrict__ vec, int pcg_direction,
                                                   int dvdc_quirk) {
+  pdl_wait();
+  pdl_trigger();
   const int cam = blockIdx.x * blockDim.x + threadIdx.x;
   if (cam >= d.V) return;
-  if (pcg_direction && d.sc->pcg_done) return;
   double dl[7];
-  if (pcg_direction) {
+  if (pcg_direction && d.sc->pcg_done) {            // converged: the rows of x, for the back-substitution
+#pragma unroll
+    for (int k = 0; k < 7; ++k) dl[k] = d.x[7 * (size_t)cam + k];
+  } else if (pcg_direction) {
     const double beta = d.sc->beta;
 #pragma unroll
     for (int k = 0; k < 7; ++k) {
@@ -154,6 +156,13 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
   ci.len = gm.len0;
   ci.nseg = gm.nseg0;
   ci.K = gm.K0;
+  // Everything staged so far is constant during the PCG solve, so under a programmatic dependent launch
+  // it overlaps the previous kernel's tail; camit and the done flag are that kernel's results.
+  pdl_wait();
+  if (!BACKSUB && d.sc->pcg_done) {
+    cp_async_wait_all();
+    return;
+  }
   // stage one chunk: async tables, then gather the camera constants of its segments
   auto stage = [&](int c, bool with_iter) {
     stage_chunk_async(d, c, ci, cs);
@@ -222,15 +231,20 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       }
     }
     __syncthreads();
-    for (int idx = tid; idx < 3 * np; idx += RUN_LANES) {
-      const int j = idx / 3, e = idx - 3 * j;
+    // one thread per point: its slots are summed in observation order, three components side by side
+    for (int j = tid; j < np; j += RUN_LANES) {
       const int lo = max(rowp[j], ci.obs0) - ci.obs0;
       const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
       if (lo < hi) {
-        const double* sl = un + e * slot_cap;
-        double a = tacc[e * pt_cap + j];
-        for (int s = lo; s < hi; ++s) a += sl[s];
-        tacc[e * pt_cap + j] = a;
+        double a0 = tacc[j], a1 = tacc[pt_cap + j], a2 = tacc[2 * pt_cap + j];
+        for (int s = lo; s < hi; ++s) {
+          a0 += un[s];
+          a1 += un[slot_cap + s];
+          a2 += un[2 * slot_cap + s];
+        }
+        tacc[j] = a0;
+        tacc[pt_cap + j] = a1;
+        tacc[2 * pt_cap + j] = a2;
       }
     }
     __syncthreads();
@@ -312,12 +326,17 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
     }
     __syncthreads();
-    for (int idx = tid; idx < ci.nseg * MV_ACC; idx += RUN_LANES) {
-      const int s = idx / MV_ACC, e = idx - s * MV_ACC;
-      const int ra = cs.srun[s], rb = cs.srun[s + 1];
-      double a = 0.0;
-      for (int rr = ra; rr < rb; ++rr) a += un[rr * MV_STRIDE + e];
-      d.part12[((size_t)c * SEG_CAP + s) * MV_ACC + e] = a;
+    // half a warp per segment (lane = component): no index arithmetic per element, coalesced rows
+    {
+      const int e = tid & 15;
+      for (int s = tid >> 4; s < ci.nseg; s += RUN_LANES / 16) {
+        if (e < MV_ACC) {
+          const int ra = cs.srun[s], rb = cs.srun[s + 1];
+          double a = 0.0;
+          for (int rr = ra; rr < rb; ++rr) a += un[rr * MV_STRIDE + e];
+          d.part12[((size_t)c * SEG_CAP + s) * MV_ACC + e] = a;
+        }
+      }
     }
     __syncthreads();
   }
@@ -326,58 +345,8 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
 template <bool BACKSUB>
 __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, int dvdc_quirk) {
   extern __shared__ __align__(16) double smem[];
-  if (!BACKSUB && d.sc->pcg_done) return;
+  pdl_trigger();                                   // the next kernel may queue up behind this one's last wave
   matvec_group<BACKSUB>(d, sh, dvdc_quirk, blockIdx.x, smem);
-}
-
-// ---- "last block" finish of a grid-wide sum: per-block partials are summed in block order ----------
-// Returns true in every thread of the block that finished last; `total` is then valid in all of them.
-template <int NV>
-__device__ __forceinline__ bool grid_sum_finish(double (&v)[NV], double* __restrict__ partials, uint32_t* ticket,
-                                                double* red, double (&total)[NV]) {
-  __shared__ bool s_last;
-  __threadfence();   // this block's earlier global writes (q) must be visible to the block that finishes last
-#pragma unroll
-  for (int i = 0; i < NV; ++i) v[i] = block_sum(v[i], red);
-  if (threadIdx.x == 0) {
-#pragma unroll
-    for (int i = 0; i < NV; ++i) partials[(size_t)blockIdx.x * NV + i] = v[i];
-    __threadfence();
-    const uint32_t t = atomicAdd(ticket, 1u);
-    s_last = (t == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!s_last) return false;
-  __threadfence();
-#pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    double a = 0.0;
-    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) a += ((volatile double*)partials)[(size_t)b * NV + i];
-    total[i] = block_sum(a, red);
-  }
-  if (threadIdx.x == 0) *ticket = 0u;
-  return true;
-}
-
-// camit row of one camera for direction dl = (dC, dq): E = sum_j dq[j] Q_j, w = R^T dC, quirk term
-__device__ __forceinline__ void write_camit(const BaDev& d, int cam, const double dl[7], int dvdc_quirk) {
-  const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
-  const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
-  double Q[4][9];
-  quat_dRt(q2, Q);
-  double* o = d.camit + (size_t)CAMIT_STRIDE * cam;
-#pragma unroll
-  for (int e = 0; e < 9; ++e) o[e] = dl[3] * Q[0][e] + dl[4] * Q[1][e] + dl[5] * Q[2][e] + dl[6] * Q[3][e];
-  double w[3];
-#pragma unroll
-  for (int c = 0; c < 3; ++c) w[c] = t[c] * dl[0] + t[3 + c] * dl[1] + t[6 + c] * dl[2];
-  o[9] = w[0];
-  o[10] = w[1];
-  o[11] = w[2];
-  o[12] = dvdc_quirk ? 2.0 * w[2] : 0.0;
-  o[13] = 0.0;
-  o[14] = 0.0;
-  o[15] = 0.0;
 }
 
 // y_i from the camera's segment rows, one warp per camera: lane = (row slot, component), two row slots
@@ -468,13 +437,72 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 }
 constexpr unsigned long long PEER_TIMEOUT_NS = 20ull * 1000ull * 1000ull * 1000ull;
 
-// Signal "this rank's slot of exchange `seq` is complete" to every rank, then wait for all ranks.
-// Call after a grid-wide barrier that follows the (system-fenced) slot stores; every block waits
-// for itself.  A peer that never arrives (crashed rank) raises FLAG_PEER_TIMEOUT instead of hanging.
-__device__ __forceinline__ void peer_signal_and_wait(const PeerWindow& xw, unsigned long long seq, Scalars* sc) {
+// ---- the vector part of one PCG iteration: three ordinary launches, no grid-wide barrier --------------
+//   k_pcg_q<MODE>     y per camera, q = A p - y, per-CTA partials of p.q
+//        MODE 1  y from this GPU's segment rows                                   (one GPU)
+//        MODE 2  y = svec, already all-reduced by NCCL                            (fallback)
+//        MODE 3  y = sum over ranks of the peer-window slots, in rank order       (NVLink peers)
+//   k_pcg_ypeer       (MODE 3 only, before k_pcg_q) this rank's partial y -> its slot in every rank's
+//                     window; the CTA that finishes last raises the flags
+//   k_pcg_update<INIT> alpha = rz / p.q; x += alpha p; r -= alpha q; z = Minv r; partials of r.z, r.r;
+//                     the CTA that finishes last sums them: beta, convergence test, host signal
+//   k_cam_iter        p = z + beta p and its camit rows (or, once converged, the rows of x)
+// One warp per camera: lane a < 7 owns entry a of the camera's 7-vectors.  Every CTA sums the per-CTA
+// partials itself, in CTA order, so all CTAs hold identical scalars; nothing spins on this GPU.
+__device__ __forceinline__ double row7_dot(const double* __restrict__ M49, int lane, double v_lane) {
+  double a = 0.0;
+#pragma unroll
+  for (int b = 0; b < 7; ++b) {
+    const double vb = __shfl_sync(0xffffffffu, v_lane, b);
+    if (lane < 7) a += M49[lane * 7 + b] * vb;
+  }
+  return a;
+}
+
+// true in every thread of the CTA that arrives last (its view of the other CTAs' writes is complete)
+__device__ __forceinline__ bool last_cta_arrives(uint32_t* ticket) {
+  __shared__ bool s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *ticket = 0u;
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last;
+}
+
+__global__ void __launch_bounds__(256) k_pcg_ypeer(BaDev d) {
+  pdl_wait();
+  pdl_trigger();
+  Scalars* sc = d.sc;
+  if (sc->pcg_done) return;
+  const PeerWindow& xw = d.xw;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int gwarp = (blockIdx.x * blockDim.x + tid) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const unsigned long long seq = *xw.counter() + 1ull;    // advanced by k_pcg_update
   const int par = (int)(seq & 1ull);
-  if (blockIdx.x == 0 && (int)threadIdx.x < xw.world)
-    st_release_sys(xw.flags(threadIdx.x) + par * MAX_PEERS + xw.rank, seq);
+  for (int cam = gwarp; cam < d.V; cam += nwarps) {
+    const double y = cam_y_from_rows(d, cam, lane, true);
+    if (lane < 7) {
+      const size_t k = 7 * (size_t)cam + lane;
+      for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
+    }
+  }
+  __threadfence_system();
+  if (last_cta_arrives(&sc->ticket_a)) {
+    __threadfence_system();
+    if (tid < xw.world) st_release_sys(xw.flags(tid) + par * MAX_PEERS + xw.rank, seq);
+  }
+}
+
+// every CTA waits until all ranks have raised the flag of exchange `seq` (peers run on other GPUs;
+// a peer that never arrives raises FLAG_PEER_TIMEOUT instead of hanging this GPU)
+__device__ __forceinline__ void peer_wait(const PeerWindow& xw, unsigned long long seq, Scalars* sc) {
+  const int par = (int)(seq & 1ull);
   if ((int)threadIdx.x < xw.world) {
     const unsigned long long* f = xw.flags(xw.rank) + par * MAX_PEERS + threadIdx.x;
     const unsigned long long t0 = global_timer_ns();
@@ -490,333 +518,106 @@ __device__ __forceinline__ void peer_signal_and_wait(const PeerWindow& xw, unsig
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(256) k_pcg_tail(BaDev d, double tol, int max_iter, int dvdc_quirk) {
+__global__ void __launch_bounds__(256) k_pcg_q(BaDev d) {
   __shared__ double red[32];
-  cg::grid_group grid = cg::this_grid();
+  pdl_wait();
+  pdl_trigger();
   Scalars* sc = d.sc;
-  if (MODE != 0 && sc->pcg_done) return;            // uniform over the grid: nobody reaches a barrier
-  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int gsize = gridDim.x * blockDim.x;
-  const int n7 = 7 * d.V;
-  double alpha = 0.0;
-  const double rz_old = sc->rz;
-  if (MODE != 0) {
-    double pq = 0.0;
-    const int sub = threadIdx.x & 31;
-    const int ngroups = gsize >> 5;
-    for (int c0 = 0; c0 < d.V; c0 += ngroups) {     // uniform trip count (shuffles inside)
-      const int cam = c0 + (gtid >> 5);
-      const bool live = cam < d.V;
-      double y = 0.0;
-      if (live && sub < 7) {
-        const size_t k = 7 * (size_t)cam + sub;
-        if (MODE == 2) y = d.svec[k];
-        const double* row = d.ablk + (size_t)cam * 49 + sub * 7;
-        const double* pv = d.p + 7 * (size_t)cam;
-        double ap = 0.0;
-#pragma unroll
-        for (int b = 0; b < 7; ++b) ap += row[b] * pv[b];
-        const double qv = ap - y;
-        d.q[k] = qv;
-        pq += pv[sub] * qv;
-      }
+  if (sc->pcg_done) return;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int gwarp = (blockIdx.x * blockDim.x + tid) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const bool l7 = lane < 7;
+  int par = 0;
+  if (MODE == 3) {
+    const unsigned long long seq = *d.xw.counter() + 1ull;
+    par = (int)(seq & 1ull);
+    peer_wait(d.xw, seq, sc);
+  }
+  double pq = 0.0;
+  for (int cam = gwarp; cam < d.V; cam += nwarps) {
+    const size_t k = 7 * (size_t)cam + lane;
+    double y = 0.0;
+    if (MODE == 1) y = cam_y_from_rows(d, cam, lane, true);
+    if (MODE == 2 && l7) y = d.svec[k];
+    if (MODE == 3 && l7) {
+      for (int w = 0; w < d.xw.world; ++w) y += __ldcg(d.xw.slot(d.xw.rank, par, w) + k);
     }
-    pq = block_sum(pq, red);
-    if (threadIdx.x == 0) d.red_a[blockIdx.x] = pq;
-    grid.sync();
-    const double pq_all = all_blocks_sum(d.red_a, 1, 0, red);
-    alpha = rz_old / pq_all;
-    if (gtid == 0) {
-      sc->pq = pq_all;
-      sc->alpha = alpha;
+    const double pv = l7 ? d.p[k] : 0.0;
+    const double ap = row7_dot(d.ablk + 49 * (size_t)cam, lane, pv);
+    if (l7) {
+      const double qv = ap - y;
+      d.q[k] = qv;
+      pq += pv * qv;
     }
   }
-  // ---- phase 2: one thread per (camera, row); r' goes to svec (r is still being read by the row's peers)
-  double v0 = 0.0, v1 = 0.0;
-  for (int k = gtid; k < n7; k += gsize) {
-    const int cam = k / 7, a = k - 7 * cam;
-    const size_t base = 7 * (size_t)cam;
-    double rn[7];
-    if (MODE == 0) {
-#pragma unroll
-      for (int b = 0; b < 7; ++b) rn[b] = d.gvec[base + b];
-      d.x[k] = 0.0;
-    } else {
-#pragma unroll
-      for (int b = 0; b < 7; ++b) rn[b] = d.r[base + b] - alpha * __ldcg(d.q + base + b);
-      d.x[k] += alpha * d.p[k];
-    }
-    const double* row = d.minv + (size_t)cam * 49 + a * 7;
-    double z = 0.0;
-#pragma unroll
-    for (int b = 0; b < 7; ++b) z += row[b] * rn[b];
-    d.z[k] = z;
-    d.svec[k] = rn[a];
-    v0 += rn[a] * z;
-    v1 += rn[a] * rn[a];
-  }
-  v0 = block_sum(v0, red);
-  v1 = block_sum(v1, red);
-  if (threadIdx.x == 0) {
-    d.red_b[2 * blockIdx.x] = v0;
-    d.red_b[2 * blockIdx.x + 1] = v1;
-  }
-  grid.sync();
-  const double rz_new = all_blocks_sum(d.red_b, 2, 0, red);
-  const double rr = all_blocks_sum(d.red_b, 2, 1, red);
-  const double beta = MODE == 0 ? 0.0 : rz_new / rz_old;
-  // convergence: every thread evaluates the same scalars; thread 0 of the grid publishes them
-  int done = 0, it = 0;
-  const double gg = MODE == 0 ? rr : sc->gg;
-  uint32_t newflags = 0;
-  if (MODE == 0) {
-    done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
-    if (!(rr == rr)) newflags |= FLAG_NONFINITE;
-  } else {
-    it = sc->pcg_iters + 1;
-    if (!(rz_old / alpha > 0.0) || !(rr == rr)) {    // p.q <= 0 or NaN
-      newflags |= FLAG_NONFINITE;
-      done = 1;
-    }
-    if (rr <= tol * tol * gg) done = 1;
-    if (!done && it >= max_iter) {
-      newflags |= FLAG_PCG_MAXITER;
-      done = 1;
-    }
-  }
-  // ---- phase 3
-  for (int k = gtid; k < n7; k += gsize) {
-    const double pn = __ldcg(d.z + k) + beta * (MODE == 0 ? 0.0 : d.p[k]);
-    d.r[k] = __ldcg(d.svec + k);
-    d.p[k] = pn;
-  }
-  grid.sync();   // p complete (camit needs the 7 entries of a camera), pcg_iters read by everyone
-  if (!done) {
-    for (int cam = gtid; cam < d.V; cam += gsize) {
-      double dl[7];
-#pragma unroll
-      for (int k = 0; k < 7; ++k) dl[k] = __ldcg(d.p + 7 * (size_t)cam + k);
-      write_camit(d, cam, dl, dvdc_quirk);
-    }
-  }
-  if (gtid == 0) {
-    if (MODE == 0) sc->gg = rr;
-    if (MODE != 0) sc->pcg_iters_total += 1;
-    sc->pcg_iters = it;
-    if (newflags) atomicOr(&sc->flags, newflags);
-    sc->beta = beta;
-    sc->rz = rz_new;
-    sc->rr = rr;
-    sc->pcg_done = done;
-  }
+  pq = block_sum(pq, red);
+  if (tid == 0) d.red_a[blockIdx.x] = pq;
 }
 
-// ---- the whole PCG solve of one LM iteration in ONE persistent cooperative launch -------------------
-// Grid = as many CTAs as are co-resident (4 per SM); a CTA walks over groups g = blockIdx, + gridDim, ...
-// for the matvec, then the grid meets at a barrier and runs the vector part with one warp per camera
-// (lane a < 7 owns entry a of the camera's 7-vectors; x, r, z, p, q are touched by their owner only,
-// so only camit, the segment rows and the dot-product partials cross a grid barrier).
-//   init      x = 0, r = g, z = Minv g, p = z, camit(p); rz, gg
-//   A         matvec over the groups -> segment rows (part12)
-//   [PEER]    partial y of this rank -> every rank's window over NVLink; flags
-//   B         y per camera, q = A p - y, p.q
-//   C         alpha; x += alpha p; r -= alpha q; z = Minv r; r.z, r.r
-//   D         beta; convergence; p = z + beta p; camit(p)
-// At exit camit holds the rows of x (the back-substitution direction), so k_matvec<true> follows directly.
-__device__ __forceinline__ double row7_dot(const double* __restrict__ M49, int lane, double v_lane) {
-  double a = 0.0;
-#pragma unroll
-  for (int b = 0; b < 7; ++b) {
-    const double vb = __shfl_sync(0xffffffffu, v_lane, b);
-    if (lane < 7) a += M49[lane * 7 + b] * vb;
-  }
-  return a;
-}
-
-// lanes 0..6 hold a direction (dC, dq) of camera `cam`: lane 0 writes its camit row
-__device__ __forceinline__ void camit_from_lanes(const BaDev& d, int cam, int lane, double v_lane, int dvdc_quirk) {
-  double dl[7];
-#pragma unroll
-  for (int b = 0; b < 7; ++b) dl[b] = __shfl_sync(0xffffffffu, v_lane, b);
-  if (lane == 0) write_camit(d, cam, dl, dvdc_quirk);
-}
-
-// Loop-carried state of the solve lives in shared memory (every CTA holds the same values): nothing
-// but addresses stays live in registers across the matvec, whose inner loops need all 128 of them.
-struct SolveCarry {
-  double rz, gg, rr, alpha, beta;
-  unsigned long long xseq, stamp, ns[5];
-  int it, done, grp;
-  uint32_t newflags;
-};
-
-#ifndef SOLVE_CTAS
-#define SOLVE_CTAS 3
-#endif
-template <bool PEER>
-__global__ void __launch_bounds__(RUN_LANES, SOLVE_CTAS)
-k_pcg_solve(BaDev d, MvShape sh, double tol, int max_iter, int dvdc_quirk) {
-  extern __shared__ __align__(16) double smem[];
+// INIT: x = 0, r = g, z = Minv g (then k_cam_iter with beta = 0 makes p = z)
+template <bool INIT, bool PEER>
+__global__ void __launch_bounds__(256) k_pcg_update(BaDev d, int q_grid, double tol, int max_iter, unsigned epoch) {
   __shared__ double red[32];
-  __shared__ SolveCarry cy;
-  cg::grid_group grid = cg::this_grid();
-  const int tid = threadIdx.x;
-  const bool clock_thread = blockIdx.x == 0 && tid == 0;
-  auto lap = [&](int which) {
-    if (clock_thread) {
-      const unsigned long long now = global_timer_ns();
-      cy.ns[which] += now - cy.stamp;
-      cy.stamp = now;
-    }
-  };
-  // ---- init
-  {
-    const int lane = tid & 31;
-    const int gwarp = (blockIdx.x * RUN_LANES + tid) >> 5, nwarps = gridDim.x * (RUN_LANES / 32);
-    const bool l7 = lane < 7;
-    double v0 = 0.0, v1 = 0.0;
-    for (int cam = gwarp; cam < d.V; cam += nwarps) {
-      const size_t k = 7 * (size_t)cam + lane;
-      const double g = l7 ? d.gvec[k] : 0.0;
-      const double z = row7_dot(d.minv + 49 * (size_t)cam, lane, g);
-      if (l7) {
-        d.x[k] = 0.0;
-        d.r[k] = g;
-        d.p[k] = z;
-        v0 += g * z;
-        v1 += g * g;
-      }
-      camit_from_lanes(d, cam, lane, z, dvdc_quirk);
-    }
-    v0 = block_sum(v0, red);
-    v1 = block_sum(v1, red);
-    if (tid == 0) {
-      d.red_b[2 * blockIdx.x] = v0;
-      d.red_b[2 * blockIdx.x + 1] = v1;
-    }
-    grid.sync();
-    const double rz = all_blocks_sum(d.red_b, 2, 0, red);
-    const double gg = all_blocks_sum(d.red_b, 2, 1, red);
-    if (tid == 0) {
-      cy.rz = rz;
-      cy.gg = gg;
-      cy.rr = gg;
-      cy.alpha = 0.0;
-      cy.beta = 0.0;
-      cy.it = 0;
-      cy.newflags = !(gg == gg) ? FLAG_NONFINITE : 0u;
-      cy.done = (gg == 0.0 || !(gg == gg)) ? 1 : 0;
-      cy.xseq = PEER ? *d.xw.counter() : 0ull;       // rewritten by one thread at the very end
-#pragma unroll
-      for (int k = 0; k < 5; ++k) cy.ns[k] = 0ull;
-      cy.stamp = global_timer_ns();
-    }
-    __syncthreads();
+  pdl_wait();
+  pdl_trigger();
+  Scalars* sc = d.sc;
+  if (!INIT && sc->pcg_done) return;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int gwarp = (blockIdx.x * blockDim.x + tid) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const bool l7 = lane < 7;
+  const double rz_old = sc->rz, gg_old = sc->gg;          // rewritten by the last CTA only
+  const int it_old = sc->pcg_iters;
+  double alpha = 0.0, pq_all = 1.0;
+  if (!INIT) {
+    double a = 0.0;
+    for (int b = tid; b < q_grid; b += blockDim.x) a += d.red_a[b];
+    pq_all = block_sum(a, red);
+    alpha = rz_old / pq_all;
   }
-  while (!cy.done) {
-    // ---- A: matvec.  Groups are handed out by a ticket counter (one per iteration parity; the idle
-    // one is re-armed in phase C), fetched one group ahead so the atomic's latency hides behind work.
-    {
-      uint32_t* ctr = (cy.it & 1) ? &d.sc->ticket_b : &d.sc->ticket_a;
-      if (tid == 0) cy.grp = (int)atomicAdd(ctr, 1u);
-      __syncthreads();
-      int g = cy.grp;
-      while (g < d.G) {
-        unsigned nxt = 0;
-        if (tid == 0) nxt = atomicAdd(ctr, 1u);
-        matvec_group<false>(d, sh, dvdc_quirk, g, smem);
-        if (tid == 0) cy.grp = (int)nxt;
-        __syncthreads();
-        g = cy.grp;
-      }
-    }
-    grid.sync();
-    lap(0);
-    // ---- vector part: one warp per camera
-    const int lane = tid & 31;
-    const int gwarp = (blockIdx.x * RUN_LANES + tid) >> 5, nwarps = gridDim.x * (RUN_LANES / 32);
-    const bool l7 = lane < 7;
-    const int V = d.V;
-    Scalars* sc = d.sc;
-    unsigned long long xseq = cy.xseq;
-    if (PEER) {
-      const PeerWindow& xw = d.xw;
-      ++xseq;
-      const int par = (int)(xseq & 1ull);
-      for (int cam = gwarp; cam < V; cam += nwarps) {
-        const double y = cam_y_from_rows(d, cam, lane, true);
-        if (l7) {
-          const size_t k = 7 * (size_t)cam + lane;
-          for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
-        }
-      }
-      __threadfence_system();
-      grid.sync();
-      peer_signal_and_wait(xw, xseq, sc);
-      lap(1);
-    }
-    // ---- B: q = A p - y, p.q
-    double pq = 0.0;
-    for (int cam = gwarp; cam < V; cam += nwarps) {
-      const size_t k = 7 * (size_t)cam + lane;
-      double y = 0.0;
-      if (PEER) {
-        if (l7) {
-          const int par = (int)(xseq & 1ull);
-          for (int w = 0; w < d.xw.world; ++w) y += __ldcg(d.xw.slot(d.xw.rank, par, w) + k);
-        }
+  double v0 = 0.0, v1 = 0.0;
+  for (int cam = gwarp; cam < d.V; cam += nwarps) {
+    const size_t k = 7 * (size_t)cam + lane;
+    double rn = 0.0;
+    if (l7) {
+      if (INIT) {
+        rn = d.gvec[k];
+        d.x[k] = 0.0;
+        d.p[k] = 0.0;
       } else {
-        y = cam_y_from_rows(d, cam, lane, true);
-      }
-      const double pv = l7 ? d.p[k] : 0.0;
-      const double ap = row7_dot(d.ablk + 49 * (size_t)cam, lane, pv);
-      if (l7) {
-        const double qv = ap - y;
-        d.q[k] = qv;
-        pq += pv * qv;
-      }
-    }
-    pq = block_sum(pq, red);
-    if (tid == 0) d.red_a[blockIdx.x] = pq;
-    grid.sync();
-    lap(2);
-    int it = cy.it;
-    if (clock_thread) *((it & 1) ? &sc->ticket_a : &sc->ticket_b) = 0u;   // the next iteration's counter
-    const double rz = cy.rz, gg = cy.gg;
-    const double pq_all = all_blocks_sum(d.red_a, 1, 0, red);
-    const double alpha = rz / pq_all;
-    // ---- C: x += alpha p, r -= alpha q, z = Minv r
-    double v0 = 0.0, v1 = 0.0;
-    for (int cam = gwarp; cam < V; cam += nwarps) {
-      const size_t k = 7 * (size_t)cam + lane;
-      double rn = 0.0;
-      if (l7) {
         d.x[k] += alpha * d.p[k];
         rn = d.r[k] - alpha * d.q[k];
       }
-      const double z = row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
-      if (l7) {
-        d.r[k] = rn;
-        d.z[k] = z;
-        v0 += rn * z;
-        v1 += rn * rn;
-      }
     }
-    v0 = block_sum(v0, red);
-    v1 = block_sum(v1, red);
-    if (tid == 0) {
-      d.red_b[2 * blockIdx.x] = v0;
-      d.red_b[2 * blockIdx.x + 1] = v1;
+    const double z = row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
+    if (l7) {
+      d.r[k] = rn;
+      d.z[k] = z;
+      v0 += rn * z;
+      v1 += rn * rn;
     }
-    grid.sync();
-    lap(3);
-    const double rz_new = all_blocks_sum(d.red_b, 2, 0, red);
-    const double rr = all_blocks_sum(d.red_b, 2, 1, red);
-    const double beta = rz_new / rz;
-    ++it;
-    uint32_t newflags = cy.newflags;
-    int done = 0;
-    if (!(pq_all > 0.0) || !(rr == rr)) {            // p.q <= 0 or NaN
+  }
+  v0 = block_sum(v0, red);
+  v1 = block_sum(v1, red);
+  if (tid == 0) {
+    d.red_b[2 * blockIdx.x] = v0;
+    d.red_b[2 * blockIdx.x + 1] = v1;
+  }
+  if (!last_cta_arrives(&sc->ticket_b)) return;
+  // ---- the last CTA: scalars of the iteration
+  const double rz_new = all_blocks_sum(d.red_b, 2, 0, red);
+  const double rr = all_blocks_sum(d.red_b, 2, 1, red);
+  if (tid != 0) return;
+  const double gg = INIT ? rr : gg_old;
+  int done = 0, it = 0;
+  uint32_t newflags = 0;
+  if (INIT) {
+    done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
+    if (!(rr == rr)) newflags |= FLAG_NONFINITE;
+  } else {
+    it = it_old + 1;
+    if (!(pq_all > 0.0) || !(rr == rr)) {              // p.q <= 0 or NaN
       newflags |= FLAG_NONFINITE;
       done = 1;
     }
@@ -826,54 +627,21 @@ k_pcg_solve(BaDev d, MvShape sh, double tol, int max_iter, int dvdc_quirk) {
       newflags |= FLAG_PCG_MAXITER;
       done = 1;
     }
-    // ---- D: next direction (or, when done, the camit rows of x for the back-substitution)
-    for (int cam = gwarp; cam < V; cam += nwarps) {
-      const size_t k = 7 * (size_t)cam + lane;
-      double pn = 0.0;
-      if (l7) {
-        pn = d.z[k] + beta * d.p[k];
-        d.p[k] = pn;
-      }
-      const double dir = done ? (l7 ? d.x[k] : 0.0) : pn;
-      camit_from_lanes(d, cam, lane, dir, dvdc_quirk);
-    }
-    __syncthreads();                                  // every thread has read the carry of this iteration
-    if (tid == 0) {
-      cy.rz = rz_new;
-      cy.rr = rr;
-      cy.alpha = alpha;
-      cy.beta = beta;
-      cy.it = it;
-      cy.done = done;
-      cy.newflags = newflags;
-      cy.xseq = xseq;
-    }
-    if (!done) grid.sync();
-    else __syncthreads();
-    lap(4);
+    sc->pcg_iters_total += 1;
+    if (PEER) *d.xw.counter() += 1ull;                  // this exchange is finished on this rank
   }
-  if (cy.it == 0) {                                   // zero right-hand side: x = 0
-    const int lane = tid & 31;
-    const int gwarp = (blockIdx.x * RUN_LANES + tid) >> 5, nwarps = gridDim.x * (RUN_LANES / 32);
-    for (int cam = gwarp; cam < d.V; cam += nwarps) camit_from_lanes(d, cam, lane, 0.0, dvdc_quirk);
-  }
-  if (clock_thread) {
-    Scalars* sc = d.sc;
-    if (PEER) *d.xw.counter() = cy.xseq;
-    sc->ticket_a = 0u;
-    sc->ticket_b = 0u;
-#pragma unroll
-    for (int k = 0; k < 5; ++k) sc->pcg_ns[k] += cy.ns[k];
-    sc->gg = cy.gg;
-    sc->pcg_iters = cy.it;
-    sc->pcg_iters_total += cy.it;
-    if (cy.newflags) atomicOr(&sc->flags, cy.newflags);
-    sc->alpha = cy.alpha;
-    sc->beta = cy.beta;
-    sc->rz = cy.rz;
-    sc->rr = cy.rr;
-    sc->pcg_done = 1;
-  }
+  sc->gg = gg;
+  sc->pcg_iters = it;
+  if (newflags) atomicOr(&sc->flags, newflags);
+  sc->pq = pq_all;
+  sc->alpha = alpha;
+  sc->beta = INIT ? 0.0 : rz_new / rz_old;
+  sc->rz = rz_new;
+  sc->rr = rr;
+  sc->pcg_done = done;
+  if (d.host_sig)
+    *(volatile unsigned long long*)d.host_sig =
+        ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
 }
 
 // cams += delta_p; q /= |q|                      (ba_processor.py:383-392)
@@ -962,30 +730,16 @@ static MvShape matvec_shape(const TileShape& ts, bool backsub) {
   return sh;
 }
 
-static int tail_grid(const BaDev& d) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 1;
-  }
-  int g = (d.V + 7) / 8;                  // phase 1 wants one warp per camera
+static int vec_grid(const BaDev& d) {
+  int g = (d.V + 7) / 8;                  // one warp per camera
   if (g < 1) g = 1;
-  return g < sms ? g : sms;               // cooperative launch: every block must be resident
+  return g < 1024 ? g : 1024;             // red_a / red_b hold one partial per CTA
 }
 
-template <int MODE>
-static void launch_tail(const BaDev& d, double tol, int max_iter, bool dvdc_quirk, cudaStream_t st) {
-  BaDev dd = d;
-  int quirk = dvdc_quirk ? 1 : 0;
-  void* args[] = {&dd, &tol, &max_iter, &quirk};
-  cudaLaunchCooperativeKernel((const void*)k_pcg_tail<MODE>, dim3(tail_grid(d)), dim3(256), args, 0, st);
-}
-
-void launch_pcg_init(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
-  launch_tail<0>(d, 0.0, 0, dvdc_quirk, st);
-  lc.launches++;
+void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
+  launch_pdl(k_pcg_update<true, false>, dim3(vec_grid(d)), dim3(256), 0, st, d, 0, 0.0, 0, epoch);
+  launch_pdl(k_cam_iter, dim3((d.V + 127) / 128), dim3(128), 0, st, d, (const double*)nullptr, 1, dvdc_quirk ? 1 : 0);
+  lc.launches += 2;
 }
 
 void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool dvdc_quirk, cudaStream_t st,
@@ -999,57 +753,25 @@ void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_
   if (d.G <= 0) return;
   const MvShape sh = matvec_shape(ts, backsub);
   const size_t smem = mv_smem_bytes(sh);
+  // the opt-in shared memory size is sticky per function and device: raise it only when needed
+  static size_t granted[2][64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  size_t& g = granted[backsub ? 1 : 0][dev & 63];
   if (backsub) {
-    cudaFuncSetAttribute(k_matvec<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_matvec<true><<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
+    if (smem > g) {
+      cudaFuncSetAttribute(k_matvec<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      g = smem;
+    }
+    launch_pdl(k_matvec<true>, dim3(d.G), dim3(RUN_LANES), smem, st, d, sh, dvdc_quirk ? 1 : 0);
   } else {
-    cudaFuncSetAttribute(k_matvec<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_matvec<false><<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
+    if (smem > g) {
+      cudaFuncSetAttribute(k_matvec<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      g = smem;
+    }
+    launch_pdl(k_matvec<false>, dim3(d.G), dim3(RUN_LANES), smem, st, d, sh, dvdc_quirk ? 1 : 0);
   }
   lc.launches++;
-}
-
-// persistent PCG solve: grid = co-resident CTAs (cooperative launch)
-template <bool PEER>
-static int launch_solve_t(const BaDev& d, const MvShape& sh, size_t smem, double tol, int max_iter, int quirk,
-                          cudaStream_t st) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  }
-  cudaFuncSetAttribute(k_pcg_solve<PEER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  int per_sm = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_solve<PEER>, RUN_LANES, smem);
-  if (per_sm < 1) return 0;
-  int grid = per_sm * sms;
-  if (grid > d.G) grid = d.G;
-  if (grid > 1024) grid = 1024;                     // red_a / red_b hold one partial per CTA
-  static bool told = false;
-  if (!told && getenv("SFMBA_DEBUG")) {
-    told = true;
-    fprintf(stderr, "[sfmba] k_pcg_solve: %d CTAs/SM x %d SMs, grid %d for %d groups, %zu B dynamic smem "
-            "(slot_cap %d pt_cap %d seg_cap %d k_cap %d)\n", per_sm, sms, grid, d.G, smem, sh.slot_cap, sh.pt_cap,
-            sh.seg_cap, sh.k_cap);
-  }
-  BaDev dd = d;
-  MvShape s2 = sh;
-  void* args[] = {&dd, &s2, &tol, &max_iter, &quirk};
-  cudaLaunchCooperativeKernel((const void*)k_pcg_solve<PEER>, dim3(grid), dim3(RUN_LANES), args, smem, st);
-  return grid;
-}
-
-bool launch_pcg_solve(const BaDev& d, const TileShape& ts, bool peer, double tol, int max_iter, bool dvdc_quirk,
-                      cudaStream_t st, LaunchCounter& lc) {
-  if (d.G <= 0) return false;
-  const MvShape sh = matvec_shape(ts, false);
-  const size_t smem = mv_smem_bytes(sh);
-  const int grid = peer ? launch_solve_t<true>(d, sh, smem, tol, max_iter, dvdc_quirk ? 1 : 0, st)
-                        : launch_solve_t<false>(d, sh, smem, tol, max_iter, dvdc_quirk ? 1 : 0, st);
-  if (grid <= 0) return false;
-  lc.launches++;
-  return true;
 }
 
 void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
@@ -1058,9 +780,24 @@ void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
 }
 
 // the vector part of a PCG iteration; from_rows: y from the segment rows (one GPU), else from svec
-void launch_pcg_tail(const BaDev& d, double tol, int max_iter, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
-  launch_tail<2>(d, tol, max_iter, dvdc_quirk, st);
-  lc.launches++;
+void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
+                     cudaStream_t st, LaunchCounter& lc) {
+  const int g = vec_grid(d);
+  if (mode == 1) {
+    launch_pdl(k_pcg_q<1>, dim3(g), dim3(256), 0, st, d);
+  } else if (mode == 2) {
+    launch_pdl(k_pcg_q<2>, dim3(g), dim3(256), 0, st, d);
+  } else {
+    launch_pdl(k_pcg_ypeer, dim3(g), dim3(256), 0, st, d);
+    launch_pdl(k_pcg_q<3>, dim3(g), dim3(256), 0, st, d);
+    lc.launches++;
+  }
+  if (mode == 3)
+    launch_pdl(k_pcg_update<false, true>, dim3(g), dim3(256), 0, st, d, g, tol, max_iter, epoch);
+  else
+    launch_pdl(k_pcg_update<false, false>, dim3(g), dim3(256), 0, st, d, g, tol, max_iter, epoch);
+  launch_pdl(k_cam_iter, dim3((d.V + 127) / 128), dim3(128), 0, st, d, (const double*)nullptr, 1, dvdc_quirk ? 1 : 0);
+  lc.launches += 3;
 }
 
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {

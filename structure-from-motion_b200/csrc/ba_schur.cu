@@ -102,15 +102,22 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
     }
     __syncthreads();
     // one work item per (point, component): the slots of a point are summed in observation order
-    for (int idx = tid; idx < 9 * np; idx += RUN_LANES) {
-      const int j = idx / 9, e = idx - 9 * j;
+    // (three components side by side per work item: the row-pointer lookups are paid once for three sums)
+    for (int idx = tid; idx < 3 * np; idx += RUN_LANES) {
+      const int j = idx / 3, e = 3 * (idx - 3 * j);
       const int lo = max(rowp[j], ci.obs0) - ci.obs0;
       const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
       if (lo < hi) {
         const double* sl = slots + e * slot_cap;
-        double a = Dv[e * pt_cap + j];
-        for (int sidx = lo; sidx < hi; ++sidx) a += sl[sidx];
-        Dv[e * pt_cap + j] = a;
+        double a0 = Dv[e * pt_cap + j], a1 = Dv[(e + 1) * pt_cap + j], a2 = Dv[(e + 2) * pt_cap + j];
+        for (int sidx = lo; sidx < hi; ++sidx) {
+          a0 += sl[sidx];
+          a1 += sl[slot_cap + sidx];
+          a2 += sl[2 * slot_cap + sidx];
+        }
+        Dv[e * pt_cap + j] = a0;
+        Dv[(e + 1) * pt_cap + j] = a1;
+        Dv[(e + 2) * pt_cap + j] = a2;
       }
     }
     __syncthreads();
@@ -278,14 +285,20 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
     __syncthreads();
     // per segment: sum its lanes in lane order -> one 64-double row
     const uint16_t* run0 = cs.srun;
-    for (int idx = tid; idx < ci.nseg * CAM_ACC; idx += RUN_LANES) {
-      const int s = idx / CAM_ACC, e = idx % CAM_ACC;
-      double a = 0.0;
-      if (e < GRAM) {
+    // one warp per segment, two components per lane: no index arithmetic per element, coalesced rows
+    {
+      const int lane = tid & 31;
+      for (int s = tid >> 5; s < ci.nseg; s += RUN_LANES / 32) {
         const int ra = run0[s], rb = run0[s + 1];
-        for (int rr = ra; rr < rb; ++rr) a += runpart[rr * RP_STRIDE + e];
+        double a0 = 0.0, a1 = 0.0;
+        for (int rr = ra; rr < rb; ++rr) {
+          a0 += runpart[rr * RP_STRIDE + lane];
+          if (lane + 32 < GRAM) a1 += runpart[rr * RP_STRIDE + 32 + lane];
+        }
+        double* row = d.part64 + ((size_t)c * SEG_CAP + s) * CAM_ACC;
+        row[lane] = a0;
+        row[32 + lane] = a1;
       }
-      d.part64[((size_t)c * SEG_CAP + s) * CAM_ACC + e] = a;
     }
     __syncthreads();
   }

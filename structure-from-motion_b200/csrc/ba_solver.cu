@@ -5,6 +5,7 @@
 // device (the reference has none of these).
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -220,7 +221,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   int rc = sfm_setup_problem(ctx, pr, true, &d);
   if (rc != SFMBA_OK) return rc;
   const int n7 = 7 * d.V;
-  const double tol = opt.pcg_tol > 0 ? opt.pcg_tol : 1e-12;
+  const double tol = opt.pcg_tol > 0 ? opt.pcg_tol : 1e-10;
   const int max_iter = opt.pcg_max_iter > 0 ? opt.pcg_max_iter : std::max(200, std::min(4 * n7, 5000));
   const bool quirk = opt.dvdc_sign_quirk != 0;
   const bool fine = opt.force_slow_path != 0;
@@ -236,6 +237,8 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     d.xw = ctx->peer;
   }
   const bool peer = multi && d.xw.world == ctx->world;
+  // PCG progress word in pinned memory: polled by the host when the ranks need no matched collectives
+  d.host_sig = (!multi || peer) ? reinterpret_cast<unsigned long long*>(ctx->pinned) : nullptr;
 
   PhaseTimer pt{ctx, st};
   cudaEvent_t t_total = pt.begin();
@@ -302,33 +305,79 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
                         cudaMemcpyDeviceToDevice, st);
     }
     launch_cam_blocks(d, st, lc);
-    const bool persistent = !multi || peer;
-    if (!persistent) launch_pcg_init(d, quirk, st, lc);
+    const unsigned pcg_epoch = ++ctx->pcg_epoch;
+    launch_pcg_init(d, pcg_epoch, quirk, st, lc);
     pt.end(PH_CAMREDUCE, t0);
 
-    // ---- PCG.  One GPU, or several with peer windows: the whole solve is one persistent cooperative
-    // launch.  NCCL fallback: every rank must issue the same number of collectives, so iterations go
-    // out in fixed batches and the (rank-identical) done flag of batch b is inspected after batch
-    // b+1 has been queued; kernels of an already-converged solve exit at their first instruction.
+    // ---- PCG.  Kernels of an already-converged solve exit at their first instruction, so launching
+    // past convergence is harmless but not free.  One GPU, or several with peer windows (the exchange
+    // happens inside k_pcg_tail, and launches past convergence exit before it, so the ranks need not
+    // agree on their number): k_pcg_tail publishes (epoch, iteration, done) in one 8-byte store to
+    // pinned host memory; the host keeps LOOKAHEAD iterations queued and reads that word without any
+    // synchronisation.  NCCL fallback: every rank must issue the same number of collectives, so
+    // iterations go out in fixed batches and the (rank-identical) done flag of batch b is inspected
+    // after batch b+1 has been queued.
     t0 = pt.begin();
+    const int tail_mode = !multi ? 1 : (peer ? 3 : 2);
     auto launch_iteration = [&]() -> int {
       cudaEvent_t kb = pt.kbegin();
       launch_matvec(d, ts, false, quirk, st, lc);
       pt.kend("matvec", kb);
-      launch_camsum12(d, st, lc);
-      const int r2 = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st);
-      if (r2 != 0) return r2;
+      if (tail_mode == 2) {
+        launch_camsum12(d, st, lc);
+        const int r2 = sfm_nccl_allreduce_f64(ctx, d.svec, (size_t)n7, st);
+        if (r2 != 0) return r2;
+      }
       kb = pt.kbegin();
-      launch_pcg_tail(d, tol, max_iter, quirk, st, lc);
+      launch_pcg_tail(d, tail_mode, tol, max_iter, pcg_epoch, quirk, st, lc);
       pt.kend("pcg_tail", kb);
       return 0;
     };
-    if (persistent) {
-      // one cooperative launch runs every PCG iteration: no host round trips, no launch gaps
-      cudaEvent_t kb = pt.kbegin();
-      if (!launch_pcg_solve(d, ts, peer, tol, max_iter, quirk, st, lc))
-        return sfm_set_error(ctx, SFMBA_ERR_CUDA, "k_pcg_solve: no resident CTA (shared memory)");
-      pt.kend("pcg_solve", kb);
+    if (tail_mode != 2) {
+      // The iteration count of the previous solve is the hint: that many iterations are queued without
+      // looking at the flag (consecutive LM iterations need the same count almost always), then the host
+      // waits for the last of them; only if the solve is not done does it fall back to keeping LOOKAHEAD
+      // iterations in flight.  A right hint costs no no-op launches and no GPU idle time.
+      static const int LOOKAHEAD = getenv("SFMBA_LOOKAHEAD") ? std::max(1, atoi(getenv("SFMBA_LOOKAHEAD"))) : 2;
+      volatile unsigned long long* sig = reinterpret_cast<volatile unsigned long long*>(ctx->pinned);
+      int launched = 0, finished = 0;
+      bool done = false;
+      // wait until iteration `want` (1-based) has finished or the solve is done; updates finished/done
+      auto wait_for = [&](int want) -> int {
+        long spins = 0;
+        for (;;) {
+          const unsigned long long w = *sig;
+          if ((unsigned)(w >> 32) == pcg_epoch) {
+            finished = (int)((w & 0xffffffffull) >> 1);
+            if (w & 1ull) { done = true; return 0; }
+            if (finished >= want) return 0;
+          }
+          if ((++spins & 0x3fff) == 0 && cudaStreamQuery(st) != cudaErrorNotReady) {
+            const unsigned long long w2 = *sig;       // stream drained: final state or an error
+            if ((unsigned)(w2 >> 32) == pcg_epoch) {
+              finished = (int)((w2 & 0xffffffffull) >> 1);
+              if (w2 & 1ull) { done = true; return 0; }
+              if (finished >= want) return 0;
+            }
+            int r2 = sfm_check_cuda(ctx, cudaGetLastError(), "pcg kernels");
+            return r2 ? r2 : sfm_set_error(ctx, SFMBA_ERR_CUDA, "PCG made no progress");
+          }
+        }
+      };
+      const int hint = std::min(ctx->pcg_hint, max_iter);
+      for (; launched < hint; ++launched)
+        if ((rc = launch_iteration()) != 0) return rc;
+      if (hint > 0 && (rc = wait_for(hint)) != 0) return rc;
+      while (launched < max_iter && !done) {
+        if (launched >= LOOKAHEAD + finished) {
+          if ((rc = wait_for(launched - LOOKAHEAD + 1)) != 0) return rc;
+          if (done) break;
+        }
+        if ((rc = launch_iteration()) != 0) return rc;
+        ++launched;
+      }
+      if (!done && (rc = wait_for(launched)) != 0) return rc;   // max_iter reached: the kernel sets done itself
+      ctx->pcg_hint = finished;
     } else {
       const int batch = 4;
       int32_t* done_host = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ctx->pinned) + 16);
@@ -357,7 +406,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
 
     t0 = pt.begin();
     if (adaptive) launch_lm_model_decrease(d, st, lc);
-    if (!persistent) launch_cam_iter(d, d.x, false, quirk, st, lc);   // (k_pcg_solve leaves camit = rows of x)
+    // (the last k_pcg_tail of the solve left camit = rows of x, the back-substitution direction)
     {
       cudaEvent_t kb = pt.kbegin();
       launch_matvec(d, ts, true, quirk, st, lc);        // back-substitution: pts += v - Dinv B^T dp
@@ -396,16 +445,6 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "solve sync")) != 0) return rc;
   if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "solve kernels")) != 0) return rc;
   pt.resolve();
-  if (ctx->profile && hs->pcg_iters_total > 0) {
-    // phase clocks of the persistent PCG kernel, per PCG iteration
-    static const char* names[5] = {"pcg.matvec", "pcg.peer", "pcg.q", "pcg.update", "pcg.direction"};
-    for (int k = 0; k < 5; ++k) {
-      ProfileEntry& pe = ctx->prof[names[k]];
-      pe.ms += (double)hs->pcg_ns[k] * 1e-6;
-      pe.launches += hs->pcg_iters_total;
-    }
-  }
-
   if (res) {
     memset(res, 0, sizeof(*res));
     res->iterations_done = opt.iterations;

@@ -55,6 +55,8 @@ struct sfmba_ctx {
   void* pinned = nullptr;        // pinned staging for results/scalars
   size_t pinned_cap = 0;
   cudaStream_t own_stream = nullptr;
+  unsigned pcg_epoch = 0;        // id of the current PCG solve (see host_sig)
+  int pcg_hint = 0;              // iterations the previous PCG solve needed
 
   cudaError_t reserve(int slot, size_t bytes, void** out);
 };
