@@ -191,7 +191,9 @@ void launch_k1(const BaDev& d, bool dvdc_quirk, float* out_r, float* out_jp, flo
 void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int cost_slot, cudaStream_t st,
                       LaunchCounter& lc);
 void launch_sum_cost(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc);
-void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);       // part64 -> cam_acc
+void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
+// several GPUs with peer windows: segment rows -> every rank's window -> cam_acc and cost summed over ranks
+void launch_camsum64_peer(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc);       // part64 -> cam_acc
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------

@@ -23,6 +23,7 @@
 #include <stdlib.h>
 
 #include "launch.cuh"
+#include "peer.cuh"
 #include "tile.cuh"
 
 namespace sfmba {
@@ -421,21 +422,6 @@ __device__ __forceinline__ double all_blocks_sum(const double* __restrict__ part
   return block_sum(a, red);
 }
 
-// ---- system-scope flag accesses for the peer exchange (flags live in peer HBM, reached over NVLink)
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
-constexpr unsigned long long PEER_TIMEOUT_NS = 20ull * 1000ull * 1000ull * 1000ull;
 
 // ---- the vector part of one PCG iteration: three ordinary launches, no grid-wide barrier --------------
 //   k_pcg_q<MODE>     y per camera, q = A p - y, per-CTA partials of p.q
@@ -459,21 +445,6 @@ __device__ __forceinline__ double row7_dot(const double* __restrict__ M49, int l
   return a;
 }
 
-// true in every thread of the CTA that arrives last (its view of the other CTAs' writes is complete)
-__device__ __forceinline__ bool last_cta_arrives(uint32_t* ticket) {
-  __shared__ bool s_last;
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t t = atomicAdd(ticket, 1u);
-    s_last = (t == gridDim.x - 1);
-    if (s_last) *ticket = 0u;
-  }
-  __syncthreads();
-  if (s_last) __threadfence();
-  return s_last;
-}
-
 __global__ void __launch_bounds__(256) k_pcg_ypeer(BaDev d) {
   pdl_wait();
   pdl_trigger();
@@ -492,29 +463,7 @@ __global__ void __launch_bounds__(256) k_pcg_ypeer(BaDev d) {
       for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
     }
   }
-  __threadfence_system();
-  if (last_cta_arrives(&sc->ticket_a)) {
-    __threadfence_system();
-    if (tid < xw.world) st_release_sys(xw.flags(tid) + par * MAX_PEERS + xw.rank, seq);
-  }
-}
-
-// every CTA waits until all ranks have raised the flag of exchange `seq` (peers run on other GPUs;
-// a peer that never arrives raises FLAG_PEER_TIMEOUT instead of hanging this GPU)
-__device__ __forceinline__ void peer_wait(const PeerWindow& xw, unsigned long long seq, Scalars* sc) {
-  const int par = (int)(seq & 1ull);
-  if ((int)threadIdx.x < xw.world) {
-    const unsigned long long* f = xw.flags(xw.rank) + par * MAX_PEERS + threadIdx.x;
-    const unsigned long long t0 = global_timer_ns();
-    unsigned spins = 0;
-    while (ld_acquire_sys(f) < seq) {
-      if ((++spins & 0x3ffu) == 0 && global_timer_ns() - t0 > PEER_TIMEOUT_NS) {
-        atomicOr(&sc->flags, FLAG_PEER_TIMEOUT);
-        break;
-      }
-    }
-  }
-  __syncthreads();
+  peer_publish(xw, seq, &sc->ticket_a);
 }
 
 template <int MODE>

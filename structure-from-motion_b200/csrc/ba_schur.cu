@@ -12,6 +12,7 @@
 // 64-double row per (chunk, camera); k_camsum64 then adds each camera's rows in row order.
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
+#include "peer.cuh"
 #include "tile.cuh"
 
 namespace sfmba {
@@ -362,6 +363,55 @@ void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int 
     lc.launches++;
   }
   launch_sum_cost(d, cost_slot, st, lc);
+}
+
+// Several GPUs with peer windows: this rank's sums (and its cost, in the trailing entry) go straight into
+// every rank's window over NVLink; k_cam_gather_peers then adds the ranks' slots in rank order.
+__global__ void __launch_bounds__(256) k_camsum64_peer(BaDev d) {
+  const PeerWindow& xw = d.xw;
+  const unsigned long long seq = *xw.counter() + 1ull;      // advanced by k_cam_gather_peers
+  const int par = (int)(seq & 1ull);
+  const int cam = blockIdx.x * 4 + (threadIdx.x >> 6);
+  const int e = threadIdx.x & 63;
+  if (cam < d.V) {
+    const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
+    double a = 0.0;
+    for (int k = r0; k < r1; ++k) a += d.part64[(size_t)d.camrow_idx[k] * CAM_ACC + e];
+    for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)cam * CAM_ACC + e] = a;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const double c = d.sc->cost_cur;
+    for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)d.V * CAM_ACC] = c;
+  }
+  peer_publish(xw, seq, &d.sc->ticket_a);
+}
+
+__global__ void __launch_bounds__(256) k_cam_gather_peers(BaDev d, int cost_slot) {
+  const PeerWindow& xw = d.xw;
+  Scalars* sc = d.sc;
+  const unsigned long long seq = *xw.counter() + 1ull;
+  const int par = (int)(seq & 1ull);
+  peer_wait(xw, seq, sc);
+  const size_t n = (size_t)d.V * CAM_ACC + 1;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    double a = 0.0;
+    for (int w = 0; w < xw.world; ++w) a += __ldcg(xw.slot(xw.rank, par, w) + i);
+    if (i + 1 < n) {
+      d.cam_acc[i] = a;
+    } else {
+      sc->cost_cur = a;
+      if (cost_slot < SFMBA_MAX_COST_HISTORY) sc->costs[cost_slot] = a;
+    }
+  }
+  if (last_cta_arrives(&sc->ticket_b) && threadIdx.x == 0) *xw.counter() = seq;   // every CTA has read it
+}
+
+void launch_camsum64_peer(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc) {
+  k_camsum64_peer<<<(d.V + 3) / 4, 256, 0, st>>>(d);
+  int g = (int)(((size_t)d.V * CAM_ACC + 256) / 256);
+  if (g > 592) g = 592;
+  k_cam_gather_peers<<<g, 256, 0, st>>>(d, cost_slot);
+  lc.launches += 2;
 }
 
 void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {

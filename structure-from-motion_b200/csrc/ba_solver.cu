@@ -212,7 +212,7 @@ enum Phase { PH_INDEX = 0, PH_LINEARIZE, PH_CAMREDUCE, PH_PCG, PH_UPDATE, PH_TOT
 
 
 int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_options* opt_in,
-                        sfmba_result* res, cudaStream_t st) {
+                        sfmba_result* res, cudaStream_t st, const SolveIo* io) {
   sfmba_options opt;
   if (opt_in) opt = *opt_in; else sfmba_default_options(&opt);
   if (opt.iterations < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "iterations < 0");
@@ -260,6 +260,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   void* temp = nullptr;
   size_t temp_bytes = index_temp_bytes(d.G, 1, d.V);
   if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_TEMP, temp_bytes, &temp), "cudaMalloc(temp)")) != 0) return rc;
+  if (io) cudaStreamWaitEvent(st, io->ev_index, 0);
   launch_index_count(d, fine, temp, temp_bytes, st, lc);
   cudaMemcpyAsync(hs, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, st);
   if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "index count")) != 0) return rc;
@@ -276,8 +277,10 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_TEMP, temp_bytes, &temp), "cudaMalloc(temp)")) != 0) return rc;
   if ((rc = carve(ctx, S_SORT_KEYS, (size_t)d.chunk_bound * SEG_CAP, &sort_keys)) != 0) return rc;
   if ((rc = carve(ctx, S_IOTA, (size_t)d.chunk_bound * SEG_CAP, &iota)) != 0) return rc;
+  if (io) cudaStreamWaitEvent(st, io->ev_obs, 0);
   launch_index_build(d, nchunks, temp, temp_bytes, sort_keys, iota, st, lc);
   pt.end(PH_INDEX, t0);
+  if (io) cudaStreamWaitEvent(st, io->ev_params, 0);
 
   int cost_slot = 0;
   for (int it = 0; it < opt.iterations; ++it) {
@@ -292,8 +295,12 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     pt.end(PH_LINEARIZE, t0);
 
     t0 = pt.begin();
-    launch_camsum64(d, st, lc);
-    if (multi) {
+    if (peer) {
+      launch_camsum64_peer(d, cost_slot, st, lc);
+    } else {
+      launch_camsum64(d, st, lc);
+    }
+    if (multi && !peer) {
       // one message: the camera accumulators plus this rank's cost in the trailing slot
       cudaMemcpyAsync(d.cam_acc + (size_t)d.V * CAM_ACC, &d.sc->cost_cur, sizeof(double),
                       cudaMemcpyDeviceToDevice, st);
@@ -426,6 +433,13 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     ++cost_slot;
   }
 
+  if (io) {
+    // parameters are final: their download runs on the copy stream beside the final cost pass
+    cudaEventRecord(io->ev_final, st);
+    cudaStreamWaitEvent(io->copy, io->ev_final, 0);
+    cudaMemcpyAsync(io->host_cams, d.cams, (size_t)7 * d.V * sizeof(double), cudaMemcpyDeviceToHost, io->copy);
+    if (d.N) cudaMemcpyAsync(io->host_pts, d.pts, (size_t)3 * d.N * sizeof(double), cudaMemcpyDeviceToHost, io->copy);
+  }
   // final cost
   double* final_cost_dev = d.cam_acc + (size_t)d.V * CAM_ACC + 1;
   if (opt.compute_costs || adaptive) {
@@ -443,6 +457,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if (opt.compute_costs || adaptive)
     cudaMemcpyAsync(hfinal, final_cost_dev, sizeof(double), cudaMemcpyDeviceToHost, st);
   if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "solve sync")) != 0) return rc;
+  if (io && (rc = sfm_check_cuda(ctx, cudaStreamSynchronize(io->copy), "D2H sync")) != 0) return rc;
   if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "solve kernels")) != 0) return rc;
   pt.resolve();
   if (res) {

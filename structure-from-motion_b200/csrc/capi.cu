@@ -11,7 +11,7 @@ using namespace sfmba;
 
 int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev* out);
 int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_options* opt, sfmba_result* res,
-                        cudaStream_t st);
+                        cudaStream_t st, const SolveIo* io);
 
 namespace {
 
@@ -138,6 +138,13 @@ int sfmba_destroy(sfmba_ctx* ctx) {
   for (auto& b : ctx->host_stage) b.release();
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  if (ctx->io.copy) {
+    cudaStreamDestroy(ctx->io.copy);
+    cudaEventDestroy(ctx->io.ev_index);
+    cudaEventDestroy(ctx->io.ev_obs);
+    cudaEventDestroy(ctx->io.ev_params);
+    cudaEventDestroy(ctx->io.ev_final);
+  }
   delete ctx;
   return SFMBA_OK;
 }
@@ -146,7 +153,7 @@ int sfmba_ba_solve(sfmba_ctx* ctx, const sfmba_problem* problem, const sfmba_opt
                    void* stream) {
   if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
   cudaSetDevice(ctx->device);
-  return sfm_ba_solve_device(ctx, problem, opt, result, (cudaStream_t)stream);
+  return sfm_ba_solve_device(ctx, problem, opt, result, (cudaStream_t)stream, nullptr);
 }
 
 int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_options* opt, sfmba_result* result) {
@@ -154,6 +161,14 @@ int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if (!pr) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "null problem");
   cudaSetDevice(ctx->device);
   cudaStream_t st = ctx->own_stream;
+  SolveIo& io = ctx->io;
+  if (!io.copy) {
+    cudaStreamCreateWithFlags(&io.copy, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&io.ev_index, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&io.ev_obs, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&io.ev_params, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&io.ev_final, cudaEventDisableTiming);
+  }
   sfmba_problem dp = *pr;
   const size_t m = (size_t)std::max(pr->num_obs, 0), N = (size_t)std::max(pr->num_pts, 0),
                V = (size_t)std::max(pr->num_cams, 0);
@@ -161,12 +176,16 @@ int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   float* d_uv;
   int32_t *d_cam, *d_row;
   double *d_kinv = nullptr, *d_cams, *d_pts;
-  if ((rc = stage_in(ctx, 0, pr->obs_uv, 2 * m, &d_uv, st))) return rc;
-  if ((rc = stage_in(ctx, 1, pr->obs_cam, m, &d_cam, st))) return rc;
-  if ((rc = stage_in(ctx, 3, pr->pt_rowptr, N + 1, &d_row, st))) return rc;
-  if (pr->cam_kinv && (rc = stage_in(ctx, 4, pr->cam_kinv, 9 * V, &d_kinv, st))) return rc;
-  if ((rc = stage_in(ctx, 5, pr->cams, 7 * V, &d_cams, st))) return rc;
-  if ((rc = stage_in(ctx, 6, pr->pts, 3 * N, &d_pts, st))) return rc;
+  // uploads in the order of first use: index inputs, observations, parameters
+  if ((rc = stage_in(ctx, 3, pr->pt_rowptr, N + 1, &d_row, io.copy))) return rc;
+  if ((rc = stage_in(ctx, 1, pr->obs_cam, m, &d_cam, io.copy))) return rc;
+  cudaEventRecord(io.ev_index, io.copy);
+  if ((rc = stage_in(ctx, 0, pr->obs_uv, 2 * m, &d_uv, io.copy))) return rc;
+  if (pr->cam_kinv && (rc = stage_in(ctx, 4, pr->cam_kinv, 9 * V, &d_kinv, io.copy))) return rc;
+  cudaEventRecord(io.ev_obs, io.copy);
+  if ((rc = stage_in(ctx, 5, pr->cams, 7 * V, &d_cams, io.copy))) return rc;
+  if ((rc = stage_in(ctx, 6, pr->pts, 3 * N, &d_pts, io.copy))) return rc;
+  cudaEventRecord(io.ev_params, io.copy);
   dp.obs_uv = d_uv;
   dp.obs_cam = d_cam;
   dp.obs_pt = nullptr;   // the solve derives the point of an observation from pt_rowptr
@@ -174,12 +193,14 @@ int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   dp.cam_kinv = pr->cam_kinv ? d_kinv : nullptr;
   dp.cams = d_cams;
   dp.pts = d_pts;
-  rc = sfm_ba_solve_device(ctx, &dp, opt, result, st);
-  if (rc != SFMBA_OK && rc != SFMBA_ERR_NUMERIC) return rc;
-  cudaMemcpyAsync(pr->cams, d_cams, 7 * V * sizeof(double), cudaMemcpyDeviceToHost, st);
-  if (N) cudaMemcpyAsync(pr->pts, d_pts, 3 * N * sizeof(double), cudaMemcpyDeviceToHost, st);
-  const int rc2 = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "D2H sync");
-  return rc2 ? rc2 : rc;
+  io.host_cams = pr->cams;
+  io.host_pts = pr->pts;
+  rc = sfm_ba_solve_device(ctx, &dp, opt, result, st, &io);   // downloads cams / pts and waits for both streams
+  if (rc != SFMBA_OK && rc != SFMBA_ERR_NUMERIC) {
+    cudaStreamSynchronize(io.copy);                           // nothing of this call stays in flight
+    cudaStreamSynchronize(st);
+  }
+  return rc;
 }
 
 int sfmba_residual_jacobian(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk, float* out_r,

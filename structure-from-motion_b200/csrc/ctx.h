@@ -24,6 +24,19 @@ struct DevBuf {
   T* as() const { return reinterpret_cast<T*>(ptr); }
 };
 
+// Host-buffer solves (sfmba_ba_solve_host): the uploads run on a copy stream in the order the solve
+// needs them and the solve waits for each group at its first use, so the index build overlaps the
+// uploads; the downloads start as soon as the parameters are final, beside the final cost pass.
+struct SolveIo {
+  cudaStream_t copy = nullptr;
+  cudaEvent_t ev_index = nullptr;    // pt_rowptr, obs_cam resident
+  cudaEvent_t ev_obs = nullptr;      // obs_uv, cam_kinv resident
+  cudaEvent_t ev_params = nullptr;   // cams, pts resident
+  cudaEvent_t ev_final = nullptr;    // recorded by the solve when cams / pts are final
+  double* host_cams = nullptr;
+  double* host_pts = nullptr;
+};
+
 struct sfmba_ctx {
   int device = 0;
   int world = 1;
@@ -55,6 +68,7 @@ struct sfmba_ctx {
   void* pinned = nullptr;        // pinned staging for results/scalars
   size_t pinned_cap = 0;
   cudaStream_t own_stream = nullptr;
+  SolveIo io;                    // copy stream and events of the host-buffer entry point
   unsigned pcg_epoch = 0;        // id of the current PCG solve (see host_sig)
   int pcg_hint = 0;              // iterations the previous PCG solve needed
 

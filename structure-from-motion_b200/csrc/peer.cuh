@@ -1,0 +1,74 @@
+// Device side of the NVLink peer exchange (PeerWindow in ba_internal.h, host side in peer_window.cu).
+// An exchange with sequence number `seq` (the window's counter + 1) goes
+//   1. every CTA stores this rank's partial values into slot (seq & 1, rank) of EVERY rank's window,
+//   2. peer_publish: the CTA that finishes last raises this rank's flag in every window,
+//   3. (next kernel) peer_wait: every CTA waits for all ranks' flags, then sums the slots of its own
+//      window in rank order, so all ranks obtain bit-identical sums,
+//   4. one thread advances the counter once every CTA of step 3 has read it.
+// The only waiting is on flags written by OTHER GPUs; it is bounded by PEER_TIMEOUT_NS.
+#pragma once
+#include "ba_internal.h"
+#include "sfmba_device.cuh"
+
+namespace sfmba {
+
+// system-scope flag accesses (flags live in peer HBM, reached over NVLink)
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+constexpr unsigned long long PEER_TIMEOUT_NS = 20ull * 1000ull * 1000ull * 1000ull;
+
+// true in every thread of the CTA that arrives last (its view of the other CTAs' writes is complete)
+__device__ __forceinline__ bool last_cta_arrives(uint32_t* ticket) {
+  __shared__ bool s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) *ticket = 0u;
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last;
+}
+
+// call after the slot stores of this CTA: the last CTA to arrive raises the flags
+__device__ __forceinline__ void peer_publish(const PeerWindow& xw, unsigned long long seq, uint32_t* ticket) {
+  __threadfence_system();
+  if (last_cta_arrives(ticket)) {
+    __threadfence_system();
+    const int par = (int)(seq & 1ull);
+    if ((int)threadIdx.x < xw.world) st_release_sys(xw.flags(threadIdx.x) + par * MAX_PEERS + xw.rank, seq);
+  }
+}
+
+// every CTA waits until all ranks have raised the flag of exchange `seq` (peers run on other GPUs;
+// a peer that never arrives raises FLAG_PEER_TIMEOUT instead of hanging this GPU)
+__device__ __forceinline__ void peer_wait(const PeerWindow& xw, unsigned long long seq, Scalars* sc) {
+  const int par = (int)(seq & 1ull);
+  if ((int)threadIdx.x < xw.world) {
+    const unsigned long long* f = xw.flags(xw.rank) + par * MAX_PEERS + threadIdx.x;
+    const unsigned long long t0 = global_timer_ns();
+    unsigned spins = 0;
+    while (ld_acquire_sys(f) < seq) {
+      if ((++spins & 0x3ffu) == 0 && global_timer_ns() - t0 > PEER_TIMEOUT_NS) {
+        atomicOr(&sc->flags, FLAG_PEER_TIMEOUT);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+}  // namespace sfmba
