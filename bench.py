@@ -33,6 +33,9 @@ sys.path.insert(0, ROOT)
 LM_ITERS = 3
 LAMBDA = 5.0
 CPU_SAMPLE_SCALE = 0.25
+# ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of ONE k_matvec<0> launch at the full Venice
+# shape on one GPU (profiles/r1_ncu_full_v16_summary.txt: 103.35 MB read + 9.79 MB written)
+NCU_DRAM_BYTES_PER_MATVEC = {('venice', 1.0, 1): 113.14e6}
 
 
 def _peaks():
@@ -62,7 +65,7 @@ class ClockSampler(threading.Thread):
                     self.samples.append(parts)
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.02)
 
     def summary(self):
         if not self.samples:
@@ -278,7 +281,9 @@ def run_ours(args):
                           for k, v in prof.items() if v[1] > 0},
             'roofline': {'kernel': k3_name,
                          'bound': 'hbm', 'achieved': k3_gbs, 'peak': peak, 'unit': 'GB/s', 'frac': k3_gbs / peak,
-                         'peak_kind': peak_kind, 'traffic': None, 'algorithmic_bytes': k3_bytes, 'ms': k3_ms},
+                         'peak_kind': peak_kind, 'traffic': NCU_DRAM_BYTES_PER_MATVEC.get((args.shape, args.scale, world)),
+                         'traffic_source': 'profiles/r1_ncu_full_v16_summary.txt (k_matvec<0>, one launch)',
+                         'algorithmic_bytes': k3_bytes, 'ms': k3_ms},
             'roofline_jacobian_schur': {'kernel': 'K1+K2 = k_linearize (residuals, Jacobians, point Schur blocks and camera Gram rows in one launch; J never stored)', 'bound': 'hbm',
                                         'achieved': k12_gbs, 'peak': peak, 'unit': 'GB/s', 'frac': k12_gbs / peak,
                                         'algorithmic_bytes': k12_bytes, 'ms': k12_ms, 'traffic': None},
