@@ -1,0 +1,125 @@
+#!/usr/bin/env python3
+"""Config C3 of SURVEY.md section 8 (batched refiners) and the other BA shapes, one JSON line each.
+
+    python profiles/bench_refiners.py [--points 1000000] [--views 10000]
+
+* a18 batched: M points with 2..6 observations each out of 200 projections, `iterations` damped steps
+  (reference defaults: lambda 0.5, 100 iterations, triangulation_processor.py:12)
+* a19 batched: P views with ~100 observations each (reference pipeline: lambda 5, 300 iterations)
+* BA at the Ladybug and Final shapes (device-resident, reference mode), as sanity lines next to the
+  Venice headline of bench.py.
+Times are wall-clock around the host-buffer entry points (uploads and downloads included) and, for the
+BA shapes, CUDA-event device time as reported by the library.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import sfm_b200                      # noqa: E402
+from sfm_b200 import synthetic       # noqa: E402
+
+
+def tri_problem(M, rng):
+    P = 200
+    K = np.array([[569.0, 0, 640.0], [0, 569.0, 480.0], [0, 0, 1.0]])
+    projs = np.zeros((P, 3, 4))
+    for i in range(P):
+        ang = 0.2 * np.sin(i / 30.0)
+        R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+        C = np.array([[i * 0.2], [0.0], [0.0]])
+        projs[i] = K @ np.hstack((R.T, -R.T @ C))
+    n = rng.integers(2, 7, M)
+    rowptr = np.zeros(M + 1, dtype=np.int32)
+    rowptr[1:] = np.cumsum(n)
+    first = rng.integers(0, P - 6, M)
+    obs_view = (np.repeat(first, n) + (np.arange(rowptr[-1]) - np.repeat(rowptr[:-1], n))).astype(np.int32)
+    obs_pt = np.repeat(np.arange(M), n)
+    X = np.stack([first * 0.2 + rng.uniform(-2, 2, M), rng.uniform(-2, 2, M), rng.uniform(6, 14, M)], 1)
+    ph = np.einsum('mck,mk->mc', projs[obs_view][:, :, 0:3], X[obs_pt]) + projs[obs_view][:, :, 3]
+    uv = ph[:, 0:2] / ph[:, 2:3] + rng.normal(0, 0.5, (rowptr[-1], 2))
+    return projs, rowptr, obs_view, uv, X + rng.normal(0, 0.05, X.shape)
+
+
+def pnp_problem(P, rng):
+    from scipy.spatial.transform import Rotation
+    n = rng.integers(80, 121, P)
+    rowptr = np.zeros(P + 1, dtype=np.int32)
+    rowptr[1:] = np.cumsum(n)
+    m = int(rowptr[-1])
+    R = Rotation.from_rotvec(rng.normal(0, 0.2, (P, 3))).as_matrix()
+    C = rng.normal(0, 1, (P, 3))
+    pc = np.stack([rng.uniform(-3, 3, m), rng.uniform(-2, 2, m), rng.uniform(5, 15, m)], 1)
+    view = np.repeat(np.arange(P), n)
+    X = np.einsum('mij,mj->mi', R[view], pc) + C[view]
+    xy = pc[:, 0:2] / pc[:, 2:3] + rng.normal(0, 1e-3, (m, 2))
+    rots = np.einsum('pij,pjk->pik', Rotation.from_rotvec(rng.normal(0, 0.01, (P, 3))).as_matrix(), R)
+    locs = C + rng.normal(0, 0.05, (P, 3))
+    return rowptr, xy, X, rots, locs
+
+
+def timed(fn, reps=3):
+    fn()
+    best = 1e30
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        out = fn()
+        best = min(best, time.perf_counter() - t0)
+    return best, out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--points', type=int, default=1000000)
+    ap.add_argument('--views', type=int, default=10000)
+    ap.add_argument('--tri-iterations', type=int, default=100)
+    ap.add_argument('--pnp-iterations', type=int, default=300)
+    ap.add_argument('--skip-ba', action='store_true')
+    args = ap.parse_args()
+    eng = sfm_b200.Engine(device=0)
+    rng = np.random.default_rng(3)
+
+    projs, rowptr, obs_view, uv, X0 = tri_problem(args.points, rng)
+    dt, out = timed(lambda: eng.triangulate_refine(projs, rowptr, obs_view, uv, X0, 0.5, args.tri_iterations))
+    print(json.dumps({'workload': 'C3 a18 batched nonlinear triangulation', 'points': args.points,
+                      'observations': int(rowptr[-1]), 'iterations': args.tri_iterations, 'seconds': dt,
+                      'point_iterations_per_sec': args.points * args.tri_iterations / dt,
+                      'mean_abs_move': float(np.mean(np.abs(out - X0)))}))
+
+    rowptr, xy, X, rots, locs = pnp_problem(args.views, rng)
+    dt, (rot, loc) = timed(lambda: eng.pnp_refine(rowptr, xy, X, rots, locs, 5.0, args.pnp_iterations))
+    print(json.dumps({'workload': 'C3 a19 batched nonlinear PnP', 'views': args.views, 'observations': int(rowptr[-1]),
+                      'iterations': args.pnp_iterations, 'seconds': dt,
+                      'observation_iterations_per_sec': int(rowptr[-1]) * args.pnp_iterations / dt,
+                      'mean_abs_loc_move': float(np.mean(np.abs(loc - locs)))}))
+
+    if not args.skip_ba:
+        import torch
+        for shape in ('ladybug', 'final'):
+            prob, _ = synthetic.make_shape(shape)
+            t = eng.to_device(prob)
+            c0, p0 = t['cams'].clone(), t['pts'].clone()
+            best, res = 1e30, None
+            for _ in range(4):
+                t['cams'].copy_(c0)
+                t['pts'].copy_(p0)
+                torch.cuda.synchronize()
+                res = eng.ba_solve_device(t, lam=5.0, iterations=3)
+                best = min(best, res.ms['total'])
+            print(json.dumps({'workload': 'BA %s shape (reference mode, 3 LM iterations)' % shape, 'cams': prob.num_cams,
+                              'pts': prob.num_pts, 'obs': prob.num_obs, 'device_ms': best,
+                              'lm_iterations_per_sec': 3e3 / best, 'pcg_iterations': res.pcg_iterations,
+                              'initial_cost': res.initial_cost, 'final_cost': res.final_cost,
+                              'phase_ms': res.ms}))
+            del t, c0, p0
+            torch.cuda.empty_cache()
+    eng.close()
+
+
+if __name__ == '__main__':
+    main()

@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libsfmba.so')
+# SFMBA_LIB: another build of the same library (A/B measurements); default = the in-tree build
+LIB_PATH = os.environ.get('SFMBA_LIB') or os.path.join(_HERE, 'libsfmba.so')
 
 SFMBA_MAX_COST_HISTORY = 64
 
