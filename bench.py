@@ -108,6 +108,11 @@ def cpu_baseline(steps=1, warmup=0, shape='venice'):
     }
 
 
+def workload_name(shape, V, N, m, pcg_tol):
+    return ('%s-shaped BA: %d cams / %d pts / %d obs; reference mode: lambda=%g, %d LM iterations per step, PCG to %.0e'
+            % (shape, V, N, m, LAMBDA, LM_ITERS, pcg_tol))
+
+
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
@@ -119,7 +124,10 @@ def run_reference(args):
         'impl': 'reference', 'metric': 'ba_lm_iterations_per_sec', 'value': base['value'], 'unit': 'LM iterations/s',
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': base['ms_per_step'],
         'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': '%s-shaped BA (%d cams / %d pts / %d obs), reference mode lambda=%g' % (args.shape, V, N, m, LAMBDA),
+        'config': {'workload': workload_name(args.shape, V, N, m, args.pcg_tol),
+                   'note': 'CPU arm: each timed step is ONE LM iteration of the oracle port (exact reduced solve instead '
+                           'of PCG) on a %.2f-scale sample of the workload; value = LM iterations/s scaled linearly in '
+                           'observations to the full shape' % CPU_SAMPLE_SCALE,
                    'sample_scale': CPU_SAMPLE_SCALE},
         'cpu_baseline': {k: base[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
         'e2e': {'value': base['value'], 'unit': 'LM iterations/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
@@ -269,8 +277,7 @@ def run_ours(args):
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_total / args.steps,
             'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64',
             'data': 'synthetic',
-            'config': {'workload': '%s-shaped BA: %d cams / %d pts / %d obs; reference mode: lambda=%g, %d LM iterations '
-                                   'per step, PCG to %.0e' % (args.shape, V, N, m, LAMBDA, LM_ITERS, args.pcg_tol),
+            'config': {'workload': workload_name(args.shape, V, N, m, args.pcg_tol),
                        'parallelism': 'points sharded over %d GPU(s), cameras replicated' % world,
                        'pcg_iterations_per_lm_iteration': pcg_iters / max(1, LM_ITERS * args.steps),
                        'l2': 'inputs larger than L2 (>1 GB streamed per matvec)'},
