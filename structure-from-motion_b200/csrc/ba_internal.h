@@ -179,7 +179,6 @@ void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_byt
 // ---- linearisation (ba_linearize.cu) ------------------------------------------------------------
 void launch_cam_prepare(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 // per-point Schur elimination: D_j^-1, v_j, cost -> sc->costs[cost_slot] / cost_cur
-void launch_point(const BaDev& d, const TileShape& ts, int cost_slot, cudaStream_t st, LaunchCounter& lc);
 // cost only at the current parameters -> sc->cost_new and (optionally) *out_cost_dev
 void launch_cost_tiles(const BaDev& d, const TileShape& ts, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc);
 void launch_cost(const BaDev& d, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc);   // index-free
@@ -198,8 +197,6 @@ void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
 void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
-void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool dvdc_quirk, cudaStream_t st,
-                     LaunchCounter& lc);
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc);
 void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // part12 -> svec (multi-GPU)

@@ -1,12 +1,10 @@
-// Linearisation, point side: camera table, per-point Schur elimination (K2a: D_j, D_j^-1, v_j and the
-// cost), the index-free cost pass and the stand-alone residual/Jacobian kernel (K1).
+// Camera table (k_cam_prepare), the cost pass over the solve's index (k_cost_tiles), the index-free
+// cost pass and the stand-alone residual/Jacobian kernel (K1) behind sfmba_ba_cost /
+// sfmba_residual_jacobian.  The linearisation itself (point blocks and camera Gram rows) is k_linearize
+// in ba_schur.cu.
 //
-// Reference: ba_processor.py:304-363 (per point: gather visible views, J_x, b, f, D_j += J_x^T J_x,
-// D_j += lambda I, D_j^-1).  k_point walks a group's camera-sorted records (ba_internal.h, tile.cuh):
-// each lane evaluates r and J_x of its observations in f64 with the camera constants in registers,
-// scatters the 9 per-observation terms of (D_j, e_x,j) to shared-memory slots at their point-major
-// position, and one thread per point then sums its slots in order and solves the 3x3 block in
-// closed form.  Nothing per-observation is written to HBM.
+// Reference: ba_processor.py:323 (R from q per observation -> once per camera here), 339-349 (b, f,
+// r = b - f), campose_processor.py:462-482 and triangulation_processor.py:237-271 (Jacobian blocks).
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
 #include "tile.cuh"
@@ -32,48 +30,36 @@ __global__ void k_cam_prepare(BaDev d) {
   for (int i = 0; i < 4; ++i) t[12 + i] = qj[i];
 }
 
-// ---- K2a: per-point Schur elimination ------------------------------------------------------------
-// The group's points, row pointers and records are staged with cp.async; the passes read shared
-// memory only.  dynamic shared memory (doubles, then 16-byte, then 4-byte items):
-//   Xa[3 pt_cap] | pacc[9][pt_cap] | slots[9][slot_cap] | red[32] | bs[k_cap 128] | ixs | segc | rowp
+// ---- cost over the solve's index: sum ||b - f||^2 per group (ba_processor.py:346-349,376) ------------
+// The group's points and records are staged with cp.async; one lane walks its K observations of one
+// camera.  dynamic shared memory: Xa[3 pt_cap] | red[32] | bs[k_cap 128] | ixs | segc
 struct PtShape {
-  int slot_cap, pt_cap, seg_cap, k_cap;
+  int pt_cap, seg_cap, k_cap;
 };
 
-__host__ __device__ inline size_t pt_smem_bytes(const PtShape& s, bool cost_only) {
-  size_t dbl = (size_t)3 * s.pt_cap + 32 + (cost_only ? 0 : (size_t)9 * s.pt_cap + (size_t)9 * s.slot_cap);
-  size_t b = dbl * 8;
+__host__ __device__ inline size_t pt_smem_bytes(const PtShape& s) {
+  size_t b = ((size_t)3 * s.pt_cap + 32) * 8;
   b += (size_t)16 * s.k_cap * RUN_LANES;           // bs
   b += (size_t)4 * s.k_cap * RUN_LANES;            // ixs
   b += (size_t)4 * ((s.seg_cap + 3) / 4 * 4);      // segc
-  b += (size_t)4 * (s.pt_cap + 4);                 // rowp
   return b;
 }
 
-template <bool COST_ONLY>
-__global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, PtShape sh) {
+__global__ void __launch_bounds__(RUN_LANES) k_cost_tiles(BaDev d, PtShape sh) {
   extern __shared__ __align__(16) double smem[];
-  const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
   double* Xa = smem;
-  double* pacc = Xa + 3 * pt_cap;
-  double* slots = COST_ONLY ? pacc : pacc + 9 * pt_cap;
-  double* red = COST_ONLY ? pacc : slots + 9 * slot_cap;
+  double* red = Xa + 3 * sh.pt_cap;
   ChunkStage cs;
   cs.bs = reinterpret_cast<double2*>(red + 32);
   cs.ixs = reinterpret_cast<uint32_t*>(cs.bs + (size_t)sh.k_cap * RUN_LANES);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
   cs.srun = nullptr;
-  int32_t* rowp = cs.segc + (sh.seg_cap + 3) / 4 * 4;
   const int tid = threadIdx.x;
   const GroupMeta gm = d.grp_meta[blockIdx.x];
-  const int np = gm.np, pt0 = gm.pt0, c0 = gm.c0, c1 = gm.c0 + gm.nc;
+  const int np = gm.np, c0 = gm.c0, c1 = gm.c0 + gm.nc;
   {
-    const double* src = d.pts + 3 * (size_t)pt0;
+    const double* src = d.pts + 3 * (size_t)gm.pt0;
     for (int i = tid; i < 3 * np; i += RUN_LANES) cp_async8(Xa + i, src + i);
-    if (!COST_ONLY) {
-      for (int i = tid; i <= np; i += RUN_LANES) cp_async4(rowp + i, d.rowptr + pt0 + i);
-      for (int i = tid; i < 9 * pt_cap; i += RUN_LANES) pacc[i] = 0.0;
-    }
   }
   ChunkInfo ci;
   ci.obs0 = gm.obs0;
@@ -100,64 +86,8 @@ __global__ void __launch_bounds__(RUN_LANES) k_point(BaDev d, PtShape sh) {
       if (!pr.ok) flags |= FLAG_DEPTH_ZERO;
       const double r0 = b.x - pr.u, r1 = b.y - pr.v;
       cost += r0 * r0 + r1 * r1;
-      if (!COST_ONLY) {
-        // J_x rows (triangulation_processor.py:259-271 with the K-free projection)
-        const double x0 = (R[0] - pr.u * R[2]) * pr.iw, x1 = (R[3] - pr.u * R[5]) * pr.iw,
-                     x2 = (R[6] - pr.u * R[8]) * pr.iw;
-        const double y0 = (R[1] - pr.v * R[2]) * pr.iw, y1 = (R[4] - pr.v * R[5]) * pr.iw,
-                     y2 = (R[7] - pr.v * R[8]) * pr.iw;
-        double* s = slots + rec_pos(ix);
-        s[0 * slot_cap] = x0 * x0 + y0 * y0;
-        s[1 * slot_cap] = x0 * x1 + y0 * y1;
-        s[2 * slot_cap] = x0 * x2 + y0 * y2;
-        s[3 * slot_cap] = x1 * x1 + y1 * y1;
-        s[4 * slot_cap] = x1 * x2 + y1 * y2;
-        s[5 * slot_cap] = x2 * x2 + y2 * y2;
-        s[6 * slot_cap] = x0 * r0 + y0 * r1;
-        s[7 * slot_cap] = x1 * r0 + y1 * r1;
-        s[8 * slot_cap] = x2 * r0 + y2 * r1;
-      }
     }
     __syncthreads();
-    if (!COST_ONLY) {
-      for (int j = tid; j < np; j += RUN_LANES) {
-        const int lo = max(rowp[j], ci.obs0) - ci.obs0;
-        const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
-        if (lo < hi) {
-          double a[9];
-#pragma unroll
-          for (int e = 0; e < 9; ++e) a[e] = pacc[e * pt_cap + j];
-          for (int s = lo; s < hi; ++s) {
-#pragma unroll
-            for (int e = 0; e < 9; ++e) a[e] += slots[e * slot_cap + s];
-          }
-#pragma unroll
-          for (int e = 0; e < 9; ++e) pacc[e * pt_cap + j] = a[e];
-        }
-      }
-      __syncthreads();
-    }
-  }
-  if (!COST_ONLY) {
-    const double lam = d.sc->lambda;
-    const size_t N = (size_t)d.N;
-    for (int j = tid; j < np; j += RUN_LANES) {
-      double D[6], ex[3], Dinv[6], v[3];
-#pragma unroll
-      for (int e = 0; e < 6; ++e) D[e] = pacc[e * pt_cap + j];
-#pragma unroll
-      for (int e = 0; e < 3; ++e) ex[e] = pacc[(6 + e) * pt_cap + j];
-      D[0] += lam;                                     // ba_processor.py:359 (every point, observed or not)
-      D[3] += lam;
-      D[5] += lam;
-      if (!sym3_inverse(D, Dinv)) flags |= FLAG_SINGULAR;
-      sym3_mul(Dinv, ex, v);
-      const size_t pt = (size_t)pt0 + j;
-#pragma unroll
-      for (int e = 0; e < 6; ++e) d.dinv[e * N + pt] = Dinv[e];
-#pragma unroll
-      for (int e = 0; e < 3; ++e) d.vj[e * N + pt] = v[e];
-    }
   }
   cp_async_wait_all();
   cost = block_sum(cost, red);
@@ -258,29 +188,14 @@ void launch_sum_cost(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCount
   lc.launches++;
 }
 
-static PtShape point_shape(const TileShape& ts) {
+void launch_cost_tiles(const BaDev& d, const TileShape& ts, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc) {
   PtShape sh;
-  sh.slot_cap = (ts.max_chunk_len + 1) & ~1;
   sh.pt_cap = (ts.max_group_pts + 1) & ~1;
   sh.seg_cap = ts.max_nseg;
   sh.k_cap = ts.max_k;
-  return sh;
-}
-
-void launch_point(const BaDev& d, const TileShape& ts, int cost_slot, cudaStream_t st, LaunchCounter& lc) {
-  const PtShape sh = point_shape(ts);
-  const size_t smem = pt_smem_bytes(sh, false);
-  cudaFuncSetAttribute(k_point<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (d.G > 0) k_point<false><<<d.G, RUN_LANES, smem, st>>>(d, sh);
-  k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, d.G, d.sc, cost_slot, nullptr);
-  lc.launches += 2;
-}
-
-void launch_cost_tiles(const BaDev& d, const TileShape& ts, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc) {
-  const PtShape sh = point_shape(ts);
-  const size_t smem = pt_smem_bytes(sh, true);
-  cudaFuncSetAttribute(k_point<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (d.G > 0) k_point<true><<<d.G, RUN_LANES, smem, st>>>(d, sh);
+  const size_t smem = pt_smem_bytes(sh);
+  cudaFuncSetAttribute(k_cost_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (d.G > 0) k_cost_tiles<<<d.G, RUN_LANES, smem, st>>>(d, sh);
   k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, d.G, d.sc, -1, out_cost_dev);
   lc.launches += 2;
 }

@@ -691,12 +691,6 @@ void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream
   lc.launches += 2;
 }
 
-void launch_cam_iter(const BaDev& d, const double* vec, bool pcg_direction, bool dvdc_quirk, cudaStream_t st,
-                     LaunchCounter& lc) {
-  k_cam_iter<<<(d.V + 127) / 128, 128, 0, st>>>(d, vec, pcg_direction ? 1 : 0, dvdc_quirk ? 1 : 0);
-  lc.launches++;
-}
-
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc) {
   if (d.G <= 0) return;

@@ -1,29 +1,10 @@
 // Helpers shared by the tile kernels (one CTA per group, one lane per K sorted observations):
-// staging of a group's points, camera-constant loads, per-point reduction of scattered slots.
+// camera-constant loads, the projection, asynchronous staging of a chunk's tables.
 #pragma once
 #include "ba_internal.h"
 #include "sfmba_device.cuh"
 
 namespace sfmba {
-
-struct GroupRange {
-  int pt0, np, c0, c1;
-};
-
-__device__ __forceinline__ GroupRange group_range(const BaDev& d, int g) {
-  GroupRange r;
-  r.pt0 = d.grp_pt[g];
-  r.np = d.grp_pt[g + 1] - r.pt0;
-  r.c0 = d.grp_chunk[g];
-  r.c1 = d.grp_chunk[g + 1];
-  return r;
-}
-
-// Xs[e * cap + j] = pts[pt0 + j][e]  (coalesced global read, SoA in shared memory)
-__device__ __forceinline__ void stage_points(const BaDev& d, const GroupRange& gr, double* Xs, int cap) {
-  const double* src = d.pts + 3 * (size_t)gr.pt0;
-  for (int i = threadIdx.x; i < 3 * gr.np; i += blockDim.x) Xs[(i % 3) * cap + i / 3] = src[i];
-}
 
 // R (9, row-major, camera-to-world) and C (3) of one camera: six 16-byte loads of its table row
 __device__ __forceinline__ void load_cam_rc(const double* __restrict__ camtab, int cam, double R[9], double C[3]) {
@@ -69,13 +50,6 @@ __device__ __forceinline__ Proj project(const double R[9], const double C[3], do
   p.v = pv * p.iw;
   p.ok = pw != 0.0;
   return p;
-}
-
-// observation range of point j (group-local) inside chunk [obs0, obs0 + len), as slot positions
-__device__ __forceinline__ void point_slots(const BaDev& d, int pt, const ChunkInfo& ci, int& lo, int& hi) {
-  const int a = d.rowptr[pt], b = d.rowptr[pt + 1];
-  lo = max(a, ci.obs0) - ci.obs0;
-  hi = min(b, ci.obs0 + ci.len) - ci.obs0;
 }
 
 }  // namespace sfmba
