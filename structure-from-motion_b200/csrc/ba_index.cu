@@ -162,7 +162,9 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
       const int idx = tid * CHUNK_K_MAX + i;
       keys[i] = idx < len ? (((uint32_t)d.obs_cam[obs0 + idx] << 11) | (uint32_t)idx) : 0xffffffffu;
     }
-    Sort(tmp.sort).Sort(keys, 0, 11 + cam_bits);
+    // the keys arrive in position order (blocked arrangement) and the radix sort is stable, so sorting on
+    // the camera bits alone leaves equal cameras in position order; padding keys (all ones) stay last
+    Sort(tmp.sort).Sort(keys, 11, 11 + cam_bits);
 #pragma unroll
     for (int i = 0; i < CHUNK_K_MAX; ++i) s.key[tid * CHUNK_K_MAX + i] = keys[i];
     __syncthreads();
