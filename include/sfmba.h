@@ -158,6 +158,22 @@ SFMBA_API int sfmba_triangulate_refine_batched_host(sfmba_ctx* ctx, int32_t num_
                                           const double* obs_uv, double* pts, double lambda, int32_t iterations,
                                           uint32_t* host_flags);
 
+/* ---- f2: TriangulationProcessor.linear_triangulate (triangulation_processor.py:91-157)
+ * and the depth test of CamposeProcessor.evalulate_cam_pose_cheirality (campose_processor.py:139-189),
+ * batched over points with the same CSR as above (the reference takes exactly two views per point; any
+ * number >= 2 is accepted here).
+ *   pts    f64 [M][3] out: right singular vector of the smallest singular value of the 2n x 4 DLT system,
+ *          divided by its last entry
+ *   front  i32 [M] out or NULL: 1 when the point has positive depth (third projected coordinate) in every one
+ *          of its views, else 0                                                                          */
+SFMBA_API int sfmba_triangulate_linear_batched(sfmba_ctx* ctx, int32_t num_pts, int32_t num_obs, int32_t num_projs,
+                                     const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                                     const double* obs_uv, double* pts, int32_t* front, uint32_t* host_flags,
+                                     void* stream);
+SFMBA_API int sfmba_triangulate_linear_batched_host(sfmba_ctx* ctx, int32_t num_pts, int32_t num_obs, int32_t num_projs,
+                                          const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                                          const double* obs_uv, double* pts, int32_t* front, uint32_t* host_flags);
+
 /* ---- a19: CamposeProcessor.nonlinear_estimate_cam_pose_pnp (campose_processor.py:308-459),
  * batched over views with a CSR of observations per view.
  *   rowptr   i32 [P+1];  obs_xy f64 [m][2] normalised observations (K^-1 x / z);  obs_X f64 [m][3]

@@ -398,6 +398,35 @@ def nonlinear_triangulate(init_3d_pts, projs, matched_pairs, damping_factor: flo
 
 
 # ----------------------------------------------------------------------------------------------
+# f2: linear triangulation + cheirality, the step before a18
+#                                triangulation_processor.py:91-157, campose_processor.py:139-189
+# ----------------------------------------------------------------------------------------------
+def linear_triangulate(projs, matched_pairs):
+    """TriangulationProcessor.linear_triangulate (triangulation_processor.py:136-155) for a batch:
+    rows u P[2] - P[0] and v P[2] - P[1] per view, the right singular vector of the smallest singular
+    value, divided by its last entry.  projs list of n (3,4); matched_pairs list of n (3,M).
+    Returns (4,M).  (The reference accepts exactly two views, :122-134; n views follow the same rows.)"""
+    projs = np.stack([np.asarray(p, dtype=np.float64) for p in projs])                       # (n,3,4)
+    uv = np.stack([np.asarray(mp, dtype=np.float64)[0:2, :].T for mp in matched_pairs], axis=1)  # (M,n,2)
+    M, n = uv.shape[0], uv.shape[1]
+    a = np.empty((M, 2 * n, 4))
+    a[:, 0::2, :] = uv[:, :, 0, None] * projs[None, :, 2, :] - projs[None, :, 0, :]
+    a[:, 1::2, :] = uv[:, :, 1, None] * projs[None, :, 2, :] - projs[None, :, 1, :]
+    _, _, vh = np.linalg.svd(a)
+    x = vh[:, -1, :]
+    return (x / x[:, 3:4]).T
+
+
+def cheirality_indices(p1, p2, tri_3d_pts):
+    """CamposeProcessor.evalulate_cam_pose_cheirality (campose_processor.py:181-189): indices of the
+    points whose third projected coordinate is positive in both views."""
+    X = np.asarray(tri_3d_pts, dtype=np.float64)
+    d1 = (np.asarray(p1, dtype=np.float64) @ X)[2]
+    d2 = (np.asarray(p2, dtype=np.float64) @ X)[2]
+    return [int(i) for i in np.flatnonzero((d1 > 0) & (d2 > 0))]
+
+
+# ----------------------------------------------------------------------------------------------
 # a19: nonlinear PnP                                           campose_processor.py:308-459
 # ----------------------------------------------------------------------------------------------
 def nonlinear_pnp(key_2d_pts, tri_3d_pts, intrinsic_mat, init_rot, init_loc, damping_factor: float,

@@ -91,6 +91,11 @@ def main():
                       'point_iterations_per_sec': args.points * args.tri_iterations / dt,
                       'mean_abs_move': float(np.mean(np.abs(out - X0)))}))
 
+    dt, (lin, front) = timed(lambda: eng.triangulate_linear(projs, rowptr, obs_view, uv))
+    print(json.dumps({'workload': 'f2 batched linear (DLT) triangulation + cheirality', 'points': args.points,
+                      'observations': int(rowptr[-1]), 'seconds': dt, 'points_per_sec': args.points / dt,
+                      'front_fraction': float(np.mean(front)), 'mean_abs_diff_to_refined': float(np.mean(np.abs(lin - out)))}))
+
     rowptr, xy, X, rots, locs = pnp_problem(args.views, rng)
     dt, (rot, loc) = timed(lambda: eng.pnp_refine(rowptr, xy, X, rots, locs, 5.0, args.pnp_iterations))
     print(json.dumps({'workload': 'C3 a19 batched nonlinear PnP', 'views': args.views, 'observations': int(rowptr[-1]),

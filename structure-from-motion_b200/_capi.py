@@ -68,6 +68,10 @@ SYMBOLS = {
                                                    C.POINTER(C.c_uint32), _vp]),
     'sfmba_triangulate_refine_batched_host': (C.c_int, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _i32,
                                                         C.POINTER(C.c_uint32)]),
+    'sfmba_triangulate_linear_batched': (C.c_int, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
+                                                   C.POINTER(C.c_uint32), _vp]),
+    'sfmba_triangulate_linear_batched_host': (C.c_int, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
+                                                        C.POINTER(C.c_uint32)]),
     'sfmba_pnp_refine_batched': (C.c_int, [_vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _i32, _i32, _i32,
                                            C.POINTER(C.c_uint32), _vp]),
     'sfmba_pnp_refine_batched_host': (C.c_int, [_vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _i32, _i32, _i32,

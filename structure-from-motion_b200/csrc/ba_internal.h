@@ -213,6 +213,9 @@ void launch_lm_model_decrease(const BaDev& d, cudaStream_t st, LaunchCounter& lc
 void launch_triangulate(int num_pts, const double* projs, const int32_t* rowptr, const int32_t* obs_view,
                         const double* obs_uv, double* pts, double lambda, int iterations, uint32_t* flags,
                         cudaStream_t st, LaunchCounter& lc);
+void launch_triangulate_linear(int num_pts, const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                               const double* obs_uv, double* pts, int32_t* front, uint32_t* flags, cudaStream_t st,
+                               LaunchCounter& lc);
 void launch_pnp(int num_views, const int32_t* rowptr, const double* obs_xy, const double* obs_X, double* rot,
                 double* loc, double lambda, int iterations, bool row_packing_quirk, bool dvdc_quirk,
                 uint32_t* flags, cudaStream_t st, LaunchCounter& lc);

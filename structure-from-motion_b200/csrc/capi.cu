@@ -279,6 +279,60 @@ int sfmba_triangulate_refine_batched_host(sfmba_ctx* ctx, int32_t num_pts, int32
   return rc2 ? rc2 : rc;
 }
 
+int sfmba_triangulate_linear_batched(sfmba_ctx* ctx, int32_t num_pts, int32_t num_obs, int32_t num_projs,
+                                     const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                                     const double* obs_uv, double* pts, int32_t* front, uint32_t* host_flags,
+                                     void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_pts < 0 || num_obs < 0 || num_projs < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  void* fl = nullptr;
+  int rc = sfm_check_cuda(ctx, ctx->reserve(0, sizeof(Scalars), &fl), "cudaMalloc(flags)");
+  if (rc) return rc;
+  uint32_t* dflags = reinterpret_cast<uint32_t*>(fl);
+  cudaMemsetAsync(dflags, 0, sizeof(uint32_t), st);
+  launch_triangulate_linear(num_pts, projs, rowptr, obs_view, obs_uv, pts, front, dflags, st, ctx->lc);
+  uint32_t* pin = reinterpret_cast<uint32_t*>(ctx->pinned);
+  cudaMemcpyAsync(pin, dflags, sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+  if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "triangulate sync")) != 0) return rc;
+  if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "triangulate kernel")) != 0) return rc;
+  if (host_flags) *host_flags = *pin;
+  if (*pin & SFMBA_FLAG_NONFINITE) return sfm_set_error(ctx, SFMBA_ERR_NUMERIC, "linear triangulation: point at infinity");
+  return SFMBA_OK;
+}
+
+int sfmba_triangulate_linear_batched_host(sfmba_ctx* ctx, int32_t num_pts, int32_t num_obs, int32_t num_projs,
+                                          const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                                          const double* obs_uv, double* pts, int32_t* front, uint32_t* host_flags) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_pts < 0 || num_obs < 0 || num_projs < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = ctx->own_stream;
+  double *d_projs, *d_uv;
+  int32_t *d_row, *d_view;
+  int rc;
+  if ((rc = stage_in(ctx, 0, projs, (size_t)12 * num_projs, &d_projs, st))) return rc;
+  if ((rc = stage_in(ctx, 1, rowptr, (size_t)num_pts + 1, &d_row, st))) return rc;
+  if ((rc = stage_in(ctx, 2, obs_view, (size_t)num_obs, &d_view, st))) return rc;
+  if ((rc = stage_in(ctx, 3, obs_uv, (size_t)2 * num_obs, &d_uv, st))) return rc;
+  cudaError_t e = ctx->host_stage[4].reserve(std::max<size_t>(16, (size_t)3 * num_pts * sizeof(double)));
+  if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(stage)");
+  e = ctx->host_stage[7].reserve(std::max<size_t>(16, (size_t)num_pts * sizeof(int32_t)));
+  if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(stage)");
+  double* d_pts = ctx->host_stage[4].as<double>();
+  int32_t* d_front = front ? ctx->host_stage[7].as<int32_t>() : nullptr;
+  rc = sfmba_triangulate_linear_batched(ctx, num_pts, num_obs, num_projs, d_projs, d_row, d_view, d_uv, d_pts, d_front,
+                                        host_flags, st);
+  if (rc != SFMBA_OK && rc != SFMBA_ERR_NUMERIC) return rc;
+  if (num_pts) {
+    cudaMemcpyAsync(pts, d_pts, (size_t)3 * num_pts * sizeof(double), cudaMemcpyDeviceToHost, st);
+    if (front) cudaMemcpyAsync(front, d_front, (size_t)num_pts * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+  }
+  const int rc2 = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "D2H sync");
+  return rc2 ? rc2 : rc;
+}
+
 int sfmba_pnp_refine_batched(sfmba_ctx* ctx, int32_t num_views, int32_t num_obs, const int32_t* rowptr,
                              const double* obs_xy, const double* obs_X, double* rot, double* loc, double lambda,
                              int32_t iterations, int32_t row_packing_quirk, int32_t dvdc_sign_quirk,

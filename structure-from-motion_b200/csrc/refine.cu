@@ -174,6 +174,140 @@ __global__ void __launch_bounds__(32 * PNP_WARPS) k_pnp(int num_views, const int
   if (lane == 0 && f) atomicOr(flags, f);
 }
 
+// ---- f2: linear (DLT) triangulation + cheirality, one thread per point --------
+// triangulation_processor.py:136-155: rows u P[2] - P[0] and v P[2] - P[1] of every view of the point,
+// the right singular vector of the smallest singular value, divided by its last entry.  The 2n x 4
+// system is never stored: each row is rotated into a 4 x 4 upper-triangular factor (Givens QR, which has
+// the same right singular vectors and no squaring of the condition number), and the factor's SVD comes
+// from one-sided Jacobi rotations of its columns.  front[j] = 1 when the point has positive depth in
+// every one of its views (campose_processor.py:181-189 for the two-view case).
+__device__ __forceinline__ void givens_row_into_r(double R[4][4], double r[4]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (r[i] != 0.0) {
+      const double h = hypot(R[i][i], r[i]);
+      const double c = R[i][i] / h, s = r[i] / h;
+      R[i][i] = h;
+#pragma unroll
+      for (int k = i + 1; k < 4; ++k) {
+        const double t = c * R[i][k] + s * r[k];
+        r[k] = c * r[k] - s * R[i][k];
+        R[i][k] = t;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128) k_triangulate_linear(int num_pts, const double* __restrict__ projs,
+                                                            const int32_t* __restrict__ rowptr,
+                                                            const int32_t* __restrict__ obs_view,
+                                                            const double* __restrict__ obs_uv,
+                                                            double* __restrict__ pts, int32_t* __restrict__ front,
+                                                            uint32_t* flags) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= num_pts) return;
+  const int a = rowptr[j], e = rowptr[j + 1];
+  double U[4][4], V[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      U[i][k] = 0.0;
+      V[i][k] = i == k ? 1.0 : 0.0;
+    }
+  }
+  for (int o = a; o < e; ++o) {
+    const double* P = projs + 12 * (size_t)obs_view[o];
+    const double u = obs_uv[2 * (size_t)o], v = obs_uv[2 * (size_t)o + 1];
+    double ru[4], rv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      ru[k] = u * P[8 + k] - P[k];
+      rv[k] = v * P[8 + k] - P[4 + k];
+    }
+    givens_row_into_r(U, ru);
+    givens_row_into_r(U, rv);
+  }
+  // one-sided Jacobi: rotate column pairs of U (and of V) until all columns are mutually orthogonal
+  for (int sweep = 0; sweep < 12; ++sweep) {
+    double off = 0.0;
+#pragma unroll
+    for (int p = 0; p < 3; ++p) {
+#pragma unroll
+      for (int q = p + 1; q < 4; ++q) {
+        double al = 0.0, be = 0.0, ga = 0.0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          al += U[k][p] * U[k][p];
+          be += U[k][q] * U[k][q];
+          ga += U[k][p] * U[k][q];
+        }
+        if (ga != 0.0 && fabs(ga) > 1e-17 * sqrt(al * be)) {
+          off = fmax(off, fabs(ga) / sqrt(al * be));
+          const double zeta = (be - al) / (2.0 * ga);
+          const double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+          const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const double up = U[k][p], uq = U[k][q];
+            U[k][p] = c * up - sn * uq;
+            U[k][q] = sn * up + c * uq;
+            const double vp = V[k][p], vq = V[k][q];
+            V[k][p] = c * vp - sn * vq;
+            V[k][q] = sn * vp + c * vq;
+          }
+        }
+      }
+    }
+    if (off < 1e-15) break;
+  }
+  int best = 0;
+  double smin = 0.0;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    double n2 = 0.0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) n2 += U[k][q] * U[k][q];
+    if (q == 0 || n2 < smin) {
+      smin = n2;
+      best = q;
+    }
+  }
+  double x[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    x[k] = V[k][0];
+#pragma unroll
+    for (int q = 1; q < 4; ++q)
+      if (q == best) x[k] = V[k][q];
+  }
+  uint32_t f = 0;
+  if (x[3] == 0.0) f |= FLAG_DEPTH_ZERO;
+  const double X0 = x[0] / x[3], X1 = x[1] / x[3], X2 = x[2] / x[3];
+  if (!(X0 == X0) || !(X1 == X1) || !(X2 == X2) || isinf(X0) || isinf(X1) || isinf(X2)) f |= FLAG_NONFINITE;
+  pts[3 * (size_t)j] = X0;
+  pts[3 * (size_t)j + 1] = X1;
+  pts[3 * (size_t)j + 2] = X2;
+  if (front) {
+    int ok = 1;
+    for (int o = a; o < e; ++o) {
+      const double* P = projs + 12 * (size_t)obs_view[o];
+      if (!(P[8] * X0 + P[9] * X1 + P[10] * X2 + P[11] > 0.0)) ok = 0;
+    }
+    front[j] = ok;
+  }
+  if (f) atomicOr(flags, f);
+}
+
+void launch_triangulate_linear(int num_pts, const double* projs, const int32_t* rowptr, const int32_t* obs_view,
+                               const double* obs_uv, double* pts, int32_t* front, uint32_t* flags, cudaStream_t st,
+                               LaunchCounter& lc) {
+  if (num_pts <= 0) return;
+  k_triangulate_linear<<<(num_pts + 127) / 128, 128, 0, st>>>(num_pts, projs, rowptr, obs_view, obs_uv, pts, front,
+                                                              flags);
+  lc.launches++;
+}
+
 void launch_triangulate(int num_pts, const double* projs, const int32_t* rowptr, const int32_t* obs_view,
                         const double* obs_uv, double* pts, double lambda, int iterations, uint32_t* flags,
                         cudaStream_t st, LaunchCounter& lc) {

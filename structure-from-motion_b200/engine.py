@@ -264,6 +264,26 @@ class Engine:
         _capi.check(rc, self.ctx)
         return out
 
+    def triangulate_linear(self, projs, rowptr, obs_view, obs_uv):
+        """f2 batched (triangulation_processor.py:136-155, campose_processor.py:181-189).  projs (P,3,4); rowptr
+        (M+1,); obs_view (m,); obs_uv (m,2).  Returns (pts (M,3) f64, front (M,) bool: positive depth in
+        every view of the point)."""
+        projs = np.ascontiguousarray(projs, dtype=np.float64).reshape(-1, 12)
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int32)
+        obs_view = np.ascontiguousarray(obs_view, dtype=np.int32)
+        obs_uv = np.ascontiguousarray(obs_uv, dtype=np.float64).reshape(-1, 2)
+        M = rowptr.shape[0] - 1
+        out = np.zeros((M, 3), dtype=np.float64)
+        front = np.zeros(M, dtype=np.int32)
+        flags = C.c_uint32(0)
+        rc = self.lib.sfmba_triangulate_linear_batched_host(
+            self.ctx, M, obs_view.shape[0], projs.shape[0], _ptr(projs), _ptr(rowptr), _ptr(obs_view), _ptr(obs_uv),
+            _ptr(out), _ptr(front), C.byref(flags))
+        if rc == _capi.ERR_NUMERIC:
+            raise FloatingPointError('linear triangulation produced a point at infinity (flags 0x%x)' % flags.value)
+        _capi.check(rc, self.ctx)
+        return out, front.astype(bool)
+
     def pnp_refine(self, rowptr, obs_xy, obs_X, rot, loc, lam, iterations, row_packing_quirk=True,
                    dvdc_sign_quirk=True):
         """a19 batched.  rowptr (P+1,); obs_xy (m,2) normalised; obs_X (m,3); rot (P,3,3); loc (P,3).

@@ -58,9 +58,8 @@ class TriangulationProcessor:
 
     # ------------------------------------------------------------------------------------------
     def linear_triangulate(self, projs, matched_pairs):
-        """DLT triangulation, one 2n x 4 SVD per point (triangulation_processor.py:91-157), here as
-        one batched SVD over all points.  Host code: the initialiser is outside the accelerated
-        path."""
+        """DLT triangulation, one 2n x 4 SVD per point (triangulation_processor.py:91-157), here one GPU
+        thread per point."""
         if len(matched_pairs) != len(projs) != 2:
             print('{}:{} - num of projs {} and matched pairs {} need to be 2'.format(
                 self.__class__.__name__, 'linear_triangulate', len(projs), len(matched_pairs)))
@@ -71,18 +70,16 @@ class TriangulationProcessor:
             return None
         num_views = len(matched_pairs)
         num_pts = matched_pairs[0].shape[1]
-        a = np.zeros((num_pts, 2 * num_views, 4))
-        for v in range(num_views):
-            proj = np.asarray(projs[v], dtype=float)
-            u = np.asarray(matched_pairs[v])[0, :]
-            w = np.asarray(matched_pairs[v])[1, :]
-            a[:, 2 * v, :] = u[:, None] * proj[2:3, :] - proj[0:1, :]
-            a[:, 2 * v + 1, :] = w[:, None] * proj[2:3, :] - proj[1:2, :]
         tri_pts = TriPt(num_pts)
         if num_pts:
-            _, _, vh = np.linalg.svd(a)
-            x = vh[:, -1, :]
-            tri_pts[:, :] = (x / x[:, 3:4]).T
+            # one thread per point on the GPU (sfmba_triangulate_linear_batched): CSR with num_views entries per point
+            rowptr = np.arange(num_pts + 1, dtype=np.int32) * num_views
+            obs_view = np.tile(np.arange(num_views, dtype=np.int32), num_pts)
+            uv = np.stack([np.asarray(mp, dtype=np.float64)[0:2, :].T for mp in matched_pairs], axis=1)   # (M,n,2)
+            pts, _ = self.engine.triangulate_linear(np.stack([np.asarray(p, dtype=np.float64) for p in projs]),
+                                                    rowptr, obs_view, uv.reshape(-1, 2))
+            tri_pts[0:3, :] = pts.T
+            tri_pts[3, :] = 1.0
         return tri_pts
 
     # ------------------------------------------------------------------------------------------

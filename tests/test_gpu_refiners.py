@@ -207,3 +207,65 @@ def test_visibility_on_device_is_bit_exact(engine, oracle):
     # empty tables
     op, oc, ok, rp = engine.build_visibility([np.full(5, -1), np.full(3, -1)], 4)
     assert op.size == 0 and np.array_equal(rp, np.zeros(5, dtype=np.int32))
+
+
+# ---- f2: linear triangulation + cheirality on the GPU ------------------------
+def test_linear_triangulation_pipeline_calls(engine, oracle):
+    """Every linear_triangulate result of the upenn pipeline, recorded from the unmodified reference."""
+    import sfm_b200
+    z = load_golden('upenn_tri_calls.npz')
+    tp = sfm_b200.TriangulationProcessor(engine=engine)
+    cp = sfm_b200.CamposeProcessor(None, 5, 10, engine=engine)
+    for c in range(5):
+        projs, pairs, ref = list(z['c%d_projs' % c]), list(z['c%d_pairs' % c]), z['c%d_init' % c]
+        lin = tp.linear_triangulate(projs, pairs)
+        assert lin.shape == ref.shape and np.all(lin[3] == 1.0)
+        assert np.max(np.abs(lin - ref) / np.maximum(1.0, np.abs(ref))) < 1e-10
+        assert cp.evalulate_cam_pose_cheirality(projs[0], projs[1], lin) == oracle.cheirality_indices(projs[0], projs[1], ref)
+
+
+def test_linear_triangulation_ragged_batch_and_front_flags(engine, oracle):
+    """2..6 views per point out of 200 projections, some points behind a camera; vs the oracle's SVD."""
+    rng = np.random.default_rng(7)
+    P, M = 200, 20000
+    K = np.array([[569.0, 0, 640.0], [0, 569.0, 480.0], [0, 0, 1.0]])
+    projs = np.zeros((P, 3, 4))
+    for i in range(P):
+        ang = 0.2 * np.sin(i / 30.0)
+        R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+        C = np.array([[i * 0.2], [0.0], [0.0]])
+        projs[i] = K @ np.hstack((R.T, -R.T @ C))
+    n = rng.integers(2, 7, M)
+    rowptr = np.zeros(M + 1, dtype=np.int32)
+    rowptr[1:] = np.cumsum(n)
+    first = rng.integers(0, P - 6, M)
+    obs_view = (np.repeat(first, n) + (np.arange(rowptr[-1]) - np.repeat(rowptr[:-1], n))).astype(np.int32)
+    obs_pt = np.repeat(np.arange(M), n)
+    depth = np.where(rng.random(M) < 0.1, rng.uniform(-14, -6, M), rng.uniform(6, 14, M))   # 10 % behind the cameras
+    X = np.stack([first * 0.2 + rng.uniform(-2, 2, M), rng.uniform(-2, 2, M), depth], 1)
+    ph = np.einsum('mck,mk->mc', projs[obs_view][:, :, 0:3], X[obs_pt]) + projs[obs_view][:, :, 3]
+    uv = ph[:, 0:2] / ph[:, 2:3] + rng.normal(0, 0.5, (rowptr[-1], 2))
+    pts, front = engine.triangulate_linear(projs, rowptr, obs_view, uv)
+    assert np.array_equal(front, depth > 0)
+    for k in range(2, 7):
+        sel = np.flatnonzero(n == k)[:200]
+        a = rowptr[sel][:, None] + np.arange(k)[None, :]                                      # (S,k) observation ids
+        pairs = [np.vstack((uv[a[:, v]].T, np.ones(len(sel)))) for v in range(k)]
+        for j, jj in enumerate(sel[:40]):
+            ref = oracle.linear_triangulate(list(projs[obs_view[a[j]]]), [p[:, j:j + 1] for p in pairs])
+            assert close(pts[jj], ref[0:3, 0], 1e-9), (pts[jj], ref[0:3, 0])
+
+
+def test_linear_triangulation_matches_opencv(engine):
+    """The reference's own check (triangulation_processor.py:456-468): cv2.triangulatePoints."""
+    cv2 = pytest.importorskip('cv2')
+    z = load_golden('upenn_tri_calls.npz')
+    projs, pairs = z['c0_projs'], z['c0_pairs']
+    M = pairs.shape[2]
+    rowptr = np.arange(M + 1, dtype=np.int32) * 2
+    obs_view = np.tile(np.arange(2, dtype=np.int32), M)
+    uv = np.stack([pairs[0][0:2].T, pairs[1][0:2].T], axis=1).reshape(-1, 2)
+    pts, _ = engine.triangulate_linear(projs, rowptr, obs_view, uv)
+    ref = cv2.triangulatePoints(projs[0], projs[1], pairs[0][0:2], pairs[1][0:2])
+    ref = (ref[0:3] / ref[3]).T
+    assert np.max(np.abs(pts - ref) / np.maximum(1.0, np.abs(ref))) < 1e-8

@@ -114,6 +114,25 @@ def test_oracle_triangulation_known_answers(oracle):
         assert np.max(np.abs(out - ref) / np.maximum(1.0, np.abs(ref))) < 1e-9
 
 
+def test_oracle_linear_triangulation_reproduces_reference(oracle):
+    """f2: every linear_triangulate result of the upenn pipeline (the `init` argument the reference passed on
+    to nonlinear_triangulate) and the inline known answer (triangulation_processor.py:415-473)."""
+    z = load_golden('upenn_tri_calls.npz')
+    for c in range(5):
+        lin = oracle.linear_triangulate(list(z['c%d_projs' % c]), list(z['c%d_pairs' % c]))
+        ref = z['c%d_init' % c]
+        assert lin.shape == ref.shape
+        assert np.max(np.abs(lin - ref) / np.maximum(1.0, np.abs(ref))) < 1e-12
+        front = oracle.cheirality_indices(z['c%d_projs' % c][0], z['c%d_projs' % c][1], ref)
+        d1 = (z['c%d_projs' % c][0] @ ref)[2]
+        d2 = (z['c%d_projs' % c][1] @ ref)[2]
+        assert front == [i for i in range(ref.shape[1]) if d1[i] > 0 and d2[i] > 0]      # campose_processor.py:181-189
+    t = load_golden('tri_inline.npz')
+    lin = oracle.linear_triangulate(list(t['projs'][:2]), list(t['pairs'][:2]))
+    assert np.max(np.abs(lin - t['linear'])) < 1e-12
+    assert np.allclose(lin[0:3, 0], [-0.0347069, -0.00593501, 2.02198105], atol=5e-9)
+
+
 def test_oracle_pnp_known_answers(oracle):
     z = load_golden('opencv_pnp.npz')
     rot, loc = oracle.nonlinear_pnp(z['key_2d'], z['tri_3d'], z['k'], z['init_rot'], z['init_loc'],
