@@ -267,6 +267,12 @@ __global__ void k_iota(int32_t* v, int n) {
   if (i < n) v[i] = i;
 }
 
+// rowpos[slot] = position of (chunk, segment) slot in the camera-sorted order
+__global__ void k_rowpos(const int32_t* __restrict__ sorted_slot, int n, int32_t* __restrict__ rowpos) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) rowpos[sorted_slot[k]] = k;
+}
+
 // camrow_ptr[c] = first sorted row whose camera is >= c
 __global__ void k_cam_rowptr(const int32_t* __restrict__ sorted_cam, int n, int V, int32_t* __restrict__ out) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -320,7 +326,8 @@ void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_byt
     k_iota<<<(n + 255) / 256, 256, 0, st>>>(iota, n);
     cub::DeviceRadixSort::SortPairs(temp, temp_bytes, (const int32_t*)d.seg_cam, sort_keys_out, (const int32_t*)iota,
                                     d.camrow_idx, n, 0, bits_for(d.V), st);
-    lc.launches += 4;
+    k_rowpos<<<(n + 255) / 256, 256, 0, st>>>(d.camrow_idx, n, d.rowpos);     // (iota's buffer: free after the sort)
+    lc.launches += 5;
   }
   k_cam_rowptr<<<(d.V + 1 + 255) / 256, 256, 0, st>>>(sort_keys_out, n, d.V, d.camrow_ptr);
   lc.launches++;

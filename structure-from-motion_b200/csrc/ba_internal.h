@@ -127,7 +127,9 @@ struct BaDev {
   int32_t* seg_cam;                   // [chunk_bound][SEG_CAP]   camera of each segment (V = unused)
   uint16_t* seg_lane0;                // [chunk_bound][SEG_RUN_STRIDE] first lane of each segment (+ end)
   int32_t* camrow_ptr;                // [V+1]  CSR: camera -> segment rows
-  int32_t* camrow_idx;                // [chunk_bound*SEG_CAP] row ids sorted by camera
+  int32_t* camrow_idx;                // [chunk_bound*SEG_CAP] (chunk, segment) slots sorted by camera (index build only)
+  int32_t* rowpos;                    // [chunk_bound*SEG_CAP] inverse: row of slot (chunk, segment) in part12 / part64,
+                                      // so that the rows of one camera are contiguous (camrow_ptr[cam] .. camrow_ptr[cam+1])
   // linearisation
   double* camtab;                     // [V][16]
   double* dinv;                       // [6][N] symmetric packing 00 01 02 11 12 22

@@ -54,6 +54,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_cost_tiles(BaDev d, PtShape sh) {
   cs.ixs = reinterpret_cast<uint32_t*>(cs.bs + (size_t)sh.k_cap * RUN_LANES);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
   cs.srun = nullptr;
+  cs.rpos = nullptr;
   const int tid = threadIdx.x;
   const GroupMeta gm = d.grp_meta[blockIdx.x];
   const int np = gm.np, c0 = gm.c0, c1 = gm.c0 + gm.nc;

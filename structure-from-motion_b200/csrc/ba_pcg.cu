@@ -104,7 +104,7 @@ __host__ __device__ inline size_t mv_smem_bytes(const MvShape& s) {
   size_t b = dbl * 8;
   b += (size_t)4 * (s.pt_cap + 4);                 // rowp
   b += (size_t)4 * s.k_cap * RUN_LANES;            // ixs
-  b += (size_t)4 * ((s.seg_cap + 3) / 4 * 4);      // segc
+  b += (size_t)8 * ((s.seg_cap + 3) / 4 * 4);      // segc, rpos
   b += (size_t)2 * (SEG_RUN_STRIDE + 6);           // srun (padded to 16 B)
   return b;
 }
@@ -130,7 +130,8 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
   ChunkStage cs;
   cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * seg_cap);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)k_cap * RUN_LANES);
-  cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (seg_cap + 3) / 4 * 4);
+  cs.rpos = cs.segc + (seg_cap + 3) / 4 * 4;
+  cs.srun = reinterpret_cast<uint16_t*>(cs.rpos + (seg_cap + 3) / 4 * 4);
   cs.bs = nullptr;
   int32_t* rowp = reinterpret_cast<int32_t*>(cs.srun + SEG_RUN_STRIDE + 6);
   const GroupMeta gm = d.grp_meta[grp];
@@ -335,7 +336,7 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
           const int ra = cs.srun[s], rb = cs.srun[s + 1];
           double a = 0.0;
           for (int rr = ra; rr < rb; ++rr) a += un[rr * MV_STRIDE + e];
-          d.part12[((size_t)c * SEG_CAP + s) * MV_ACC + e] = a;
+          d.part12[(size_t)cs.rpos[s] * MV_ACC + e] = a;
         }
       }
     }
@@ -359,17 +360,14 @@ __device__ __forceinline__ double cam_y_from_rows(const BaDev& d, int cam, int l
   if (live && sub < MV_ACC) {
     const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
     int k = r0 + slot;
-    for (; k + 14 < r1; k += 16) {                     // rows k, k+2, ..., k+14 of this slot
-      int idx[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) idx[u] = d.camrow_idx[k + 2 * u];
+    for (; k + 14 < r1; k += 16) {                     // rows k, k+2, ..., k+14 of this slot (contiguous rows)
       double v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = d.part12[(size_t)idx[u] * MV_ACC + sub];
+      for (int u = 0; u < 8; ++u) v[u] = d.part12[(size_t)(k + 2 * u) * MV_ACC + sub];
 #pragma unroll
       for (int u = 0; u < 8; ++u) a += v[u];
     }
-    for (; k < r1; k += 2) a += d.part12[(size_t)d.camrow_idx[k] * MV_ACC + sub];
+    for (; k < r1; k += 2) a += d.part12[(size_t)k * MV_ACC + sub];
   }
   a += __shfl_down_sync(0xffffffffu, a, 16);           // slot 0 + slot 1
   double T[MV_ACC];

@@ -29,7 +29,7 @@ struct GramShape {
 __host__ __device__ inline size_t gram_smem_bytes(const GramShape& s) {
   size_t b = ((size_t)12 * s.pt_cap + 32 + (size_t)s.un_doubles) * 8;
   b += (size_t)20 * s.k_cap * RUN_LANES;           // bs + ixs
-  b += (size_t)4 * ((s.seg_cap + 3) / 4 * 4);      // segc
+  b += (size_t)8 * ((s.seg_cap + 3) / 4 * 4);      // segc, rpos
   b += (size_t)2 * (SEG_RUN_STRIDE + 6);           // srun
   b += (size_t)4 * (s.pt_cap + 4);                 // rowp
   return b;
@@ -49,7 +49,8 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
   cs.bs = reinterpret_cast<double2*>(runpart + sh.un_doubles);
   cs.ixs = reinterpret_cast<uint32_t*>(cs.bs + (size_t)sh.k_cap * RUN_LANES);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
-  cs.srun = reinterpret_cast<uint16_t*>(cs.segc + (sh.seg_cap + 3) / 4 * 4);
+  cs.rpos = cs.segc + (sh.seg_cap + 3) / 4 * 4;
+  cs.srun = reinterpret_cast<uint16_t*>(cs.rpos + (sh.seg_cap + 3) / 4 * 4);
   int32_t* rowp = reinterpret_cast<int32_t*>(cs.srun + SEG_RUN_STRIDE + 6);
   const int tid = threadIdx.x;
   const GroupMeta gm = d.grp_meta[blockIdx.x];
@@ -296,7 +297,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
           a0 += runpart[rr * RP_STRIDE + lane];
           if (lane + 32 < GRAM) a1 += runpart[rr * RP_STRIDE + 32 + lane];
         }
-        double* row = d.part64 + ((size_t)c * SEG_CAP + s) * CAM_ACC;
+        double* row = d.part64 + (size_t)cs.rpos[s] * CAM_ACC;
         row[lane] = a0;
         row[32 + lane] = a1;
       }
@@ -305,15 +306,35 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
   }
 }
 
-// cam_acc[cam][e] = sum over the camera's segment rows, in row order (64 lanes per camera)
-__global__ void __launch_bounds__(256) k_camsum64(BaDev d) {
-  const int cam = blockIdx.x * 4 + (threadIdx.x >> 6);
-  const int e = threadIdx.x & 63;
-  if (cam >= d.V) return;
+// Sum of one camera's (contiguous) segment rows, element e: four row slots (slot = tid >> 6) take rows
+// r0+slot, r0+slot+4, ... with eight loads in flight each and are combined in slot order through shared
+// memory.  One CTA of 256 threads per camera; the result is valid in the threads of slot 0.
+__device__ __forceinline__ double cam_rows_sum64(const BaDev& d, int cam, double (*sh)[CAM_ACC]) {
+  const int e = threadIdx.x & 63, slot = threadIdx.x >> 6;
   const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
+  const double* p = d.part64 + e;
   double a = 0.0;
-  for (int k = r0; k < r1; ++k) a += d.part64[(size_t)d.camrow_idx[k] * CAM_ACC + e];
-  d.cam_acc[(size_t)cam * CAM_ACC + e] = a;
+  int k = r0 + slot;
+  for (; k + 28 < r1; k += 32) {
+    double v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(k + 4 * u) * CAM_ACC];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) a += v[u];
+  }
+  for (; k < r1; k += 4) a += p[(size_t)k * CAM_ACC];
+  if (slot) sh[slot - 1][e] = a;
+  __syncthreads();
+  if (slot == 0) a = ((a + sh[0][e]) + sh[1][e]) + sh[2][e];
+  return a;
+}
+
+// cam_acc[cam][e] = sum over the camera's segment rows
+__global__ void __launch_bounds__(256) k_camsum64(BaDev d) {
+  __shared__ double sh[3][CAM_ACC];
+  const int cam = blockIdx.x;
+  const double a = cam_rows_sum64(d, cam, sh);
+  if (threadIdx.x < CAM_ACC) d.cam_acc[(size_t)cam * CAM_ACC + threadIdx.x] = a;
 }
 
 // per camera: A_i + lambda I (full 7x7), block-Jacobi inverse of S_ii, right-hand side g_i
@@ -371,14 +392,11 @@ __global__ void __launch_bounds__(256) k_camsum64_peer(BaDev d) {
   const PeerWindow& xw = d.xw;
   const unsigned long long seq = *xw.counter() + 1ull;      // advanced by k_cam_gather_peers
   const int par = (int)(seq & 1ull);
-  const int cam = blockIdx.x * 4 + (threadIdx.x >> 6);
-  const int e = threadIdx.x & 63;
-  if (cam < d.V) {
-    const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
-    double a = 0.0;
-    for (int k = r0; k < r1; ++k) a += d.part64[(size_t)d.camrow_idx[k] * CAM_ACC + e];
-    for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)cam * CAM_ACC + e] = a;
-  }
+  __shared__ double sh[3][CAM_ACC];
+  const int cam = blockIdx.x;
+  const double a = cam_rows_sum64(d, cam, sh);
+  if (threadIdx.x < CAM_ACC)
+    for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)cam * CAM_ACC + threadIdx.x] = a;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     const double c = d.sc->cost_cur;
     for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)d.V * CAM_ACC] = c;
@@ -407,7 +425,7 @@ __global__ void __launch_bounds__(256) k_cam_gather_peers(BaDev d, int cost_slot
 }
 
 void launch_camsum64_peer(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc) {
-  k_camsum64_peer<<<(d.V + 3) / 4, 256, 0, st>>>(d);
+  k_camsum64_peer<<<d.V, 256, 0, st>>>(d);
   int g = (int)(((size_t)d.V * CAM_ACC + 256) / 256);
   if (g > 592) g = 592;
   k_cam_gather_peers<<<g, 256, 0, st>>>(d, cost_slot);
@@ -415,7 +433,7 @@ void launch_camsum64_peer(const BaDev& d, int cost_slot, cudaStream_t st, Launch
 }
 
 void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
-  k_camsum64<<<(d.V + 3) / 4, 256, 0, st>>>(d);
+  k_camsum64<<<d.V, 256, 0, st>>>(d);
   lc.launches++;
 }
 

@@ -278,6 +278,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if ((rc = carve(ctx, S_SORT_KEYS, (size_t)d.chunk_bound * SEG_CAP, &sort_keys)) != 0) return rc;
   if ((rc = carve(ctx, S_IOTA, (size_t)d.chunk_bound * SEG_CAP, &iota)) != 0) return rc;
   if (io) cudaStreamWaitEvent(st, io->ev_obs, 0);
+  d.rowpos = iota;   // the identity permutation fed to the sort; overwritten with the inverse permutation after it
   launch_index_build(d, nchunks, temp, temp_bytes, sort_keys, iota, st, lc);
   pt.end(PH_INDEX, t0);
   if (io) cudaStreamWaitEvent(st, io->ev_params, 0);

@@ -74,6 +74,7 @@ __device__ __forceinline__ void cp_async_wait_all() {
 struct ChunkStage {
   uint32_t* ixs;     // [k_cap * RUN_LANES]
   int32_t* segc;     // [seg_cap rounded to 4]
+  int32_t* rpos;     // [seg_cap rounded to 4] row of each segment in the camera-sorted row arrays, or nullptr
   uint16_t* srun;    // [SEG_RUN_STRIDE] first lane of each segment (+ end), or nullptr
   double2* bs;       // [k_cap * RUN_LANES] normalised observations, or nullptr
 };
@@ -84,6 +85,10 @@ __device__ __forceinline__ void stage_chunk_async(const BaDev& d, int c, const C
   for (int i = threadIdx.x; i < K * (RUN_LANES / 4); i += blockDim.x) cp_async16(cs.ixs + 4 * i, ix + 4 * i);
   const int32_t* sc = d.seg_cam + (size_t)c * SEG_CAP;
   for (int i = threadIdx.x; i < (ci.nseg + 3) / 4; i += blockDim.x) cp_async16(cs.segc + 4 * i, sc + 4 * i);
+  if (cs.rpos) {
+    const int32_t* rp = d.rowpos + (size_t)c * SEG_CAP;
+    for (int i = threadIdx.x; i < (ci.nseg + 3) / 4; i += blockDim.x) cp_async16(cs.rpos + 4 * i, rp + 4 * i);
+  }
   if (cs.srun) {
     const uint16_t* sr = d.seg_lane0 + (size_t)c * SEG_RUN_STRIDE;
     for (int i = threadIdx.x; i < (ci.nseg + 2) / 2; i += blockDim.x) cp_async4(cs.srun + 2 * i, sr + 2 * i);
