@@ -58,7 +58,10 @@ typedef enum {
 #define SFMBA_FLAG_SINGULAR      16u  /* a 3x3 / 7x7 block was not positive definite               */
 
 typedef enum { SFMBA_MODE_REFERENCE_FIXED = 0, SFMBA_MODE_ADAPTIVE_LM = 1 } sfmba_mode;
-typedef enum { SFMBA_SOLVER_PCG = 0 } sfmba_solver;
+/* PCG: matrix-free block-Jacobi preconditioned conjugate gradients on the implicit Schur complement.
+ * DENSE_CHOLESKY: the reduced camera matrix (7V x 7V, f64) is assembled and factored on the FP64 tensor
+ * cores -- the direct solve of ba_processor.py:382; needs 8 (7V)^2 bytes, replicated on every rank.     */
+typedef enum { SFMBA_SOLVER_PCG = 0, SFMBA_SOLVER_DENSE_CHOLESKY = 1 } sfmba_solver;
 
 /*
  * One BA problem (this rank's shard when world_size > 1: cameras replicated, points and their

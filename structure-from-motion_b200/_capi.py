@@ -19,6 +19,7 @@ OK = 0
 ERR_INVALID_ARG, ERR_CUDA, ERR_NCCL, ERR_NUMERIC, ERR_UNSUPPORTED, ERR_NO_DEVICE = -1, -2, -3, -4, -5, -6
 FLAG_QW_NEAR_ZERO, FLAG_DEPTH_ZERO, FLAG_NONFINITE, FLAG_PCG_MAXITER, FLAG_SINGULAR = 1, 2, 4, 8, 16
 MODE_REFERENCE_FIXED, MODE_ADAPTIVE_LM = 0, 1
+SOLVER_PCG, SOLVER_DENSE_CHOLESKY = 0, 1
 SOLVER_PCG = 0
 
 

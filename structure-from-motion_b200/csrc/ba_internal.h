@@ -211,6 +211,22 @@ void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_model_decrease(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 
+// ---- dense direct solve of the reduced system (dense.cu) -------------------------------------------
+struct DenseWork {
+  double* S;        // [npad][ld] column-major, lower triangle used
+  size_t ld;        // = npad
+  int n, npad;      // 7 V and its padding to a multiple of 128
+  double* linv;     // [npad / 128][128][128] inverses of the diagonal factor tiles
+  double* vec;      // [3][npad] rhs | y | x
+};
+size_t dense_padded_dim(int V);
+// S = -(off-diagonal blocks) of this rank's points (zeroed first); all-reduced by the caller when world > 1
+void launch_dense_assemble(const BaDev& d, const DenseWork& w, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
+// adds the diagonal blocks (cam_acc, lambda), factors, solves S x = gvec -> d.x
+void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, cudaStream_t st, LaunchCounter& lc);
+// camit rows of an arbitrary 7V-vector (the back-substitution direction)
+void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
+
 // ---- refiners (refine.cu) ------------------------------------------------------------------------
 void launch_triangulate(int num_pts, const double* projs, const int32_t* rowptr, const int32_t* obs_view,
                         const double* obs_uv, double* pts, double lambda, int iterations, uint32_t* flags,

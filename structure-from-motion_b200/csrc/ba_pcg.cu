@@ -741,6 +741,11 @@ void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigne
   lc.launches += 3;
 }
 
+void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
+  k_cam_iter<<<(d.V + 127) / 128, 128, 0, st>>>(d, vec, 0, dvdc_quirk ? 1 : 0);
+  lc.launches++;
+}
+
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
   k_update_cams<<<(d.V + 127) / 128, 128, 0, st>>>(d);
   lc.launches++;

@@ -61,7 +61,7 @@ enum Slot {
   S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_CAM_ACC, S_ABLK, S_MINV,
   S_CAMIT, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
   S_CHUNK_INFO, S_REC_B, S_REC_IX, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
-  S_TEMP, S_SORT_KEYS, S_IOTA, S_COUNT
+  S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
 };
 
 template <typename T>
@@ -216,11 +216,29 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   sfmba_options opt;
   if (opt_in) opt = *opt_in; else sfmba_default_options(&opt);
   if (opt.iterations < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "iterations < 0");
-  if (opt.solver != SFMBA_SOLVER_PCG) return sfm_set_error(ctx, SFMBA_ERR_UNSUPPORTED, "unknown solver");
+  if (opt.solver != SFMBA_SOLVER_PCG && opt.solver != SFMBA_SOLVER_DENSE_CHOLESKY)
+    return sfm_set_error(ctx, SFMBA_ERR_UNSUPPORTED, "unknown solver");
+  const bool dense = opt.solver == SFMBA_SOLVER_DENSE_CHOLESKY;
   BaDev d;
   int rc = sfm_setup_problem(ctx, pr, true, &d);
   if (rc != SFMBA_OK) return rc;
   const int n7 = 7 * d.V;
+  DenseWork dw;
+  memset(&dw, 0, sizeof(dw));
+  if (dense) {
+    dw.n = n7;
+    dw.npad = (int)dense_padded_dim(d.V);
+    dw.ld = (size_t)dw.npad;
+    const size_t bytes = dw.ld * (size_t)dw.npad * sizeof(double);
+    if (bytes > ((size_t)96 << 30)) {
+      char buf[128];
+      snprintf(buf, sizeof(buf), "dense solver: the %d x %d reduced matrix needs %.1f GB", n7, n7, bytes / 1e9);
+      return sfm_set_error(ctx, SFMBA_ERR_UNSUPPORTED, buf);
+    }
+    if ((rc = carve(ctx, S_DENSE, dw.ld * (size_t)dw.npad, &dw.S)) != 0) return rc;
+    if ((rc = carve(ctx, S_DENSE_LINV, (size_t)dw.npad * 128, &dw.linv)) != 0) return rc;
+    if ((rc = carve(ctx, S_DENSE_VEC, (size_t)3 * dw.npad, &dw.vec)) != 0) return rc;
+  }
   const double tol = opt.pcg_tol > 0 ? opt.pcg_tol : 1e-10;
   const int max_iter = opt.pcg_max_iter > 0 ? opt.pcg_max_iter : std::max(200, std::min(4 * n7, 5000));
   const bool quirk = opt.dvdc_sign_quirk != 0;
@@ -314,7 +332,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     }
     launch_cam_blocks(d, st, lc);
     const unsigned pcg_epoch = ++ctx->pcg_epoch;
-    launch_pcg_init(d, pcg_epoch, quirk, st, lc);
+    if (!dense) launch_pcg_init(d, pcg_epoch, quirk, st, lc);
     pt.end(PH_CAMREDUCE, t0);
 
     // ---- PCG.  Kernels of an already-converged solve exit at their first instruction, so launching
@@ -326,6 +344,17 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     // iterations go out in fixed batches and the (rank-identical) done flag of batch b is inspected
     // after batch b+1 has been queued.
     t0 = pt.begin();
+    if (dense) {
+      // direct solve: explicit S (this rank's off-diagonal blocks, summed over ranks), Cholesky, substitution
+      cudaEvent_t kb = pt.kbegin();
+      launch_dense_assemble(d, dw, quirk, st, lc);
+      if (multi && (rc = sfm_nccl_allreduce_f64(ctx, dw.S, dw.ld * (size_t)dw.npad, st)) != 0) return rc;
+      pt.kend("dense_assemble", kb);
+      kb = pt.kbegin();
+      launch_dense_factor_solve(d, dw, st, lc);
+      pt.kend("dense_factor_solve", kb);
+      launch_cam_rows(d, d.x, quirk, st, lc);
+    }
     const int tail_mode = !multi ? 1 : (peer ? 3 : 2);
     auto launch_iteration = [&]() -> int {
       cudaEvent_t kb = pt.kbegin();
@@ -341,7 +370,8 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       pt.kend("pcg_tail", kb);
       return 0;
     };
-    if (tail_mode != 2) {
+    if (dense) {
+    } else if (tail_mode != 2) {
       // The iteration count of the previous solve is the hint: that many iterations are queued without
       // looking at the flag (consecutive LM iterations need the same count almost always), then the host
       // waits for the last of them; only if the solve is not done does it fall back to keeping LOOKAHEAD

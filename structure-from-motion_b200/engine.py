@@ -128,8 +128,9 @@ class Engine:
 
     # -- options ----------------------------------------------------------------------------------
     def make_options(self, lam=5.0, iterations=3, mode=_capi.MODE_REFERENCE_FIXED, pcg_tol=1e-10, pcg_max_iter=0,
-                     dvdc_sign_quirk=True, force_slow_path=False, compute_costs=True):
+                     dvdc_sign_quirk=True, force_slow_path=False, compute_costs=True, solver=_capi.SOLVER_PCG):
         opt = _capi.default_options()
+        opt.solver = int(solver)
         opt.lambda_ = float(lam)
         opt.iterations = int(iterations)
         opt.mode = int(mode)
