@@ -191,6 +191,48 @@ SFMBA_API int sfmba_pnp_refine_batched_host(sfmba_ctx* ctx, int32_t num_views, i
                                   double lambda, int32_t iterations, int32_t row_packing_quirk,
                                   int32_t dvdc_sign_quirk, uint32_t* host_flags);
 
+/* ---- f3: RANSAC hypotheses evaluated in parallel.  The sample indices are drawn
+ * by the caller (the Python layer uses random.sample exactly as the reference does), the library evaluates
+ * all H minimal-sample models, counts inliers over all n points per hypothesis and returns the first
+ * hypothesis with the strictly largest count (the reference's update rule) together with its inlier mask.
+ *
+ * sfmba_pnp_ransac: CamposeProcessor.__linear_determine_cam_pos / __estimate_six_pts
+ * (campose_processor.py:485-633).
+ *   key      f64 [n][3] homogeneous image points (rows of key_2d_pts^T)
+ *   X        f64 [n][4] homogeneous world points (rows of tri_3d_pts^T)
+ *   K        f64 [9] intrinsic matrix, row-major (host pointer in both variants)
+ *   samples  i32 [H][6] point indices of every hypothesis
+ *   loc_sign i32 [H] or NULL: +1 / -1 per hypothesis.  campose_processor.py:620-631 returns (R, C) when LAPACK
+ *            hands back the last right singular vector with det(rot_t_noise) > 0 and (R, -C) otherwise; that
+ *            sign is an implementation detail of the host's LAPACK, so the caller passes it when it wants
+ *            the reference's outcome bit for bit.  NULL = +1 everywhere (the geometrically consistent pose).
+ *   out_rot f64 [9] (row-major, camera-to-world), out_loc f64 [3]: winner's pose (host pointers; identity / 0
+ *            when no hypothesis has an inlier, like the reference's initial best_rot / best_loc)
+ *   out_best i32 [2] host: {winning hypothesis or -1, its inlier count}
+ *   out_mask u8 [n]: 1 for the winner's inliers;  out_counts i32 [H] or NULL;  out_models f64 [H][12] or NULL
+ *            (rot | loc of every hypothesis)
+ * sfmba_fund_ransac: EpipolarProcessor.__estimate_ransac / __estimate_eight_pts (epipolar_processor.py:140-247)
+ *   pairs    f64 [n][4] normalised matched pairs [xl, yl, xr, yr];  samples i32 [H][8]
+ *   out_F    f64 [9] host: winner's fundamental matrix (f__ / f__[2][2]); zeros when best = -1
+ *   out_models f64 [H][9] or NULL.  host_flags carries SFMBA_FLAG_SINGULAR when some hypothesis's f__ does not
+ *   have rank 2 (the reference raises ValueError there, epipolar_processor.py:179-183).
+ * The plain variants take device pointers for key / X / pairs / samples / loc_sign / out_mask / out_counts /
+ * out_models; the _host variants take host pointers for everything.  Both synchronise before returning.   */
+SFMBA_API int sfmba_pnp_ransac(sfmba_ctx* ctx, int32_t num_pts, int32_t num_hyp, const double* key, const double* X,
+                     const double* K, const int32_t* samples, const int32_t* loc_sign, double inlier_threshold,
+                     double* out_rot, double* out_loc, int32_t* out_best, uint8_t* out_mask, int32_t* out_counts,
+                     double* out_models, uint32_t* host_flags, void* stream);
+SFMBA_API int sfmba_pnp_ransac_host(sfmba_ctx* ctx, int32_t num_pts, int32_t num_hyp, const double* key, const double* X,
+                          const double* K, const int32_t* samples, const int32_t* loc_sign, double inlier_threshold,
+                          double* out_rot, double* out_loc, int32_t* out_best, uint8_t* out_mask,
+                          int32_t* out_counts, double* out_models, uint32_t* host_flags);
+SFMBA_API int sfmba_fund_ransac(sfmba_ctx* ctx, int32_t num_pairs, int32_t num_hyp, const double* pairs,
+                      const int32_t* samples, double inlier_threshold, double* out_F, int32_t* out_best,
+                      uint8_t* out_mask, int32_t* out_counts, double* out_models, uint32_t* host_flags, void* stream);
+SFMBA_API int sfmba_fund_ransac_host(sfmba_ctx* ctx, int32_t num_pairs, int32_t num_hyp, const double* pairs,
+                           const int32_t* samples, double inlier_threshold, double* out_F, int32_t* out_best,
+                           uint8_t* out_mask, int32_t* out_counts, double* out_models, uint32_t* host_flags);
+
 /* ---- a3/a4: visibility index from the diagonal rows of KeyTrack.table (key_tracker.py:29-59,
  * 198-204), bit-exact including the index-0 quirk.  diag i64 [total_keys] is the concatenation of
  * table[v, :] for v = 0..V-1, key_off i64 [V+1] the offsets.  Outputs (device i32): obs_pt, obs_cam,

@@ -32,6 +32,7 @@ __all__ = [
     'is_visible_literal', 'build_visibility', 'normalise_observations',
     'quaternion_jacobian', 'residual_jacobian', 'ba_cost', 'ba_solve', 'ba_normal_equations',
     'nonlinear_triangulate', 'triangulation_jacobian', 'nonlinear_pnp', 'pose_jacobian',
+    'pnp_dlt_six', 'pnp_ransac', 'fund_eight', 'fund_ransac', 'fund_normalize', 'fund_denormalize',
 ]
 
 
@@ -484,3 +485,124 @@ def nonlinear_pnp(key_2d_pts, tri_3d_pts, intrinsic_mat, init_rot, init_loc, dam
         rot = quaternion_to_rotation(q, check=True)
     rot = quaternion_to_rotation(q, check=True)
     return rot, loc.reshape(3, 1)
+
+
+# ----------------------------------------------------------------------------------------------
+# f3: RANSAC initialisers        campose_processor.py:485-633, epipolar_processor.py:96-265
+# The sample index table is an input (the reference draws it with random.sample, one draw of 6 / 8
+# indices per hypothesis, campose_processor.py:531 / epipolar_processor.py:222), so the oracle and
+# the device code see the reference's draws.
+# ----------------------------------------------------------------------------------------------
+def pnp_dlt_six(p2d: np.ndarray, p3d: np.ndarray):
+    """Pose from six correspondences (campose_processor.py:565-633).  p2d (3,6) camera coordinates,
+    p3d (4,6).  Returns (rot (3,3), loc (3,1), lapack_sign) where lapack_sign = +1 when numpy's SVD
+    returned the last right singular vector with det(rot_t_noise) > 0, else -1: in the second case
+    lines 628-631 flip rot AND loc, which leaves (R, -C) instead of (R, C)."""
+    w = np.zeros((12, 12))
+    for i in range(6):
+        x, y, z = p2d[0, i], p2d[1, i], p2d[2, i]
+        X = p3d[0:3, i]
+        w[2 * i, 0:3] = z * X
+        w[2 * i, 3] = z                                    # :592 (4th column is p2d_z, not p2d_z * W)
+        w[2 * i, 8:11] = -x * X
+        w[2 * i, 11] = -x
+        w[2 * i + 1, 4:7] = z * X
+        w[2 * i + 1, 7] = z
+        w[2 * i + 1, 8:11] = -y * X
+        w[2 * i + 1, 11] = -y
+    _, _, vh = np.linalg.svd(w)                            # :616
+    cam_mat = vh[-1, :].reshape(3, 4)
+    uu, ss, vvh = np.linalg.svd(cam_mat[:, 0:3])           # :621
+    rot = (uu @ vvh).T
+    loc = (rot @ -cam_mat[:, 3:4]) / ss[0]                 # :625
+    sign = 1
+    if np.linalg.det(rot) < 0:                             # :628-631
+        rot = -rot
+        loc = -loc
+        sign = -1
+    return rot, loc, sign
+
+
+def pnp_ransac(key_2d_pts, tri_3d_pts, intrinsic_mat, samples, inlier_threshold: float):
+    """campose_processor.py:485-563 for a given sample table (H,6).  Returns a dict with the per-hypothesis
+    models (H,12: rot row-major | loc), LAPACK signs, inlier counts, the winner, its inlier list and pose."""
+    key = np.asarray(key_2d_pts, dtype=float)
+    tri = np.asarray(tri_3d_pts, dtype=float)
+    k = np.asarray(intrinsic_mat, dtype=float)
+    kinv = np.linalg.inv(k)
+    H = len(samples)
+    models = np.zeros((H, 12))
+    signs = np.zeros(H, dtype=np.int32)
+    counts = np.zeros(H, dtype=np.int32)
+    best = dict(hyp=-1, count=0, inliers=[], rot=np.identity(3), loc=np.zeros((3, 1)))
+    for h in range(H):
+        idx = list(samples[h])
+        rot, loc, sg = pnp_dlt_six(kinv @ key[:, idx], tri[:, idx])
+        proj = k @ np.hstack((rot.T, rot.T @ -loc))                      # :540
+        p = proj @ tri
+        with np.errstate(all='ignore'):
+            p = p / p[2]
+            err = np.sqrt(np.sum((key - p) ** 2, axis=0))                # :551
+        inl = np.flatnonzero(err < inlier_threshold)
+        models[h, 0:9] = rot.reshape(9)
+        models[h, 9:12] = loc.reshape(3)
+        signs[h] = sg
+        counts[h] = inl.size
+        if inl.size > best['count']:                                     # :558
+            best = dict(hyp=h, count=int(inl.size), inliers=[int(i) for i in inl], rot=rot, loc=loc)
+    best.update(models=models, signs=signs, counts=counts)
+    return best
+
+
+def fund_normalize(left_xy: np.ndarray, right_xy: np.ndarray):
+    """epipolar_processor.py:96-137.  left_xy / right_xy (n,2).  Returns (pairs (n,4), T_left, T_right)."""
+    n = left_xy.shape[0]
+    lm, rm = np.average(left_xy, axis=0), np.average(right_xy, axis=0)
+    ls = (2 * n) ** 0.5 / np.sum(np.sum((left_xy - lm) ** 2, axis=1) ** 0.5)
+    rs = (2 * n) ** 0.5 / np.sum(np.sum((right_xy - rm) ** 2, axis=1) ** 0.5)
+    tl = np.array([[ls, 0, -lm[0] * ls], [0, ls, -lm[1] * ls], [0, 0, 1]])
+    tr = np.array([[rs, 0, -rm[0] * rs], [0, rs, -rm[1] * rs], [0, 0, 1]])
+    one = np.ones((n, 1))
+    ln = (tl @ np.column_stack((left_xy, one)).T).T
+    rn = (tr @ np.column_stack((right_xy, one)).T).T
+    return np.column_stack((ln[:, 0:2], rn[:, 0:2])), tl, tr
+
+
+def fund_denormalize(fund_mat, t_left, t_right):
+    """epipolar_processor.py:250-265."""
+    f = t_right.T @ fund_mat @ t_left
+    return f / f[2][2]
+
+
+def fund_eight(pairs8: np.ndarray) -> np.ndarray:
+    """Eight-point fundamental matrix with the rank-2 projection (epipolar_processor.py:140-191)."""
+    x1, y1, x1_, y1_ = pairs8[:, 0], pairs8[:, 1], pairs8[:, 2], pairs8[:, 3]
+    w = np.column_stack((x1 * x1_, y1 * x1_, x1_, x1 * y1_, y1 * y1_, y1_, x1, y1, np.ones(8)))
+    _, _, vh = np.linalg.svd(w)
+    f_ = vh[8, :].reshape(3, 3)
+    u, s, vh2 = np.linalg.svd(f_)
+    f2 = u @ np.diag([s[0], s[1], 0.0]) @ vh2
+    if np.linalg.matrix_rank(f2) != 2:                                    # :179-183
+        raise ValueError('f__ rank is not equal to 2')
+    return f2 / f2[2][2]
+
+
+def fund_ransac(pairs: np.ndarray, samples, inlier_threshold: float):
+    """epipolar_processor.py:194-247 (the rows > 8 branch) for a given sample table (H,8)."""
+    pairs = np.asarray(pairs, dtype=float)
+    H = len(samples)
+    models = np.zeros((H, 9))
+    counts = np.zeros(H, dtype=np.int32)
+    best = dict(hyp=-1, count=0, inliers=None, F=np.zeros((3, 3)))
+    xl = np.column_stack((pairs[:, 0:2], np.ones(pairs.shape[0])))
+    xr = np.column_stack((pairs[:, 2:4], np.ones(pairs.shape[0])))
+    for h in range(H):
+        f = fund_eight(pairs[list(samples[h]), :])
+        val = np.abs(np.sum(xr * (f @ xl.T).T, axis=1))                   # :235
+        inl = np.flatnonzero(val < inlier_threshold)
+        models[h] = f.reshape(9)
+        counts[h] = inl.size
+        if inl.size > best['count']:                                      # :239
+            best = dict(hyp=h, count=int(inl.size), inliers=[int(i) for i in inl], F=f)
+    best.update(models=models, counts=counts)
+    return best

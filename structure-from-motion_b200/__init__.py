@@ -12,6 +12,7 @@ from .utils import (KeyPt, TriPt, convert_rotation_to_quaternion,          # noq
 from .index import build_visibility_host, problem_from_tracks               # noqa: F401
 from .triangulation_processor import TriangulationProcessor                 # noqa: F401
 from .campose_processor import CamposeProcessor                             # noqa: F401
+from .epipolar_processor import EpipolarProcessor                           # noqa: F401
 from .ba_processor import BaProcessor                                       # noqa: F401
 
 __version__ = '0.1.0'

@@ -77,6 +77,14 @@ SYMBOLS = {
                                            C.POINTER(C.c_uint32), _vp]),
     'sfmba_pnp_refine_batched_host': (C.c_int, [_vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _i32, _i32, _i32,
                                                 C.POINTER(C.c_uint32)]),
+    'sfmba_pnp_ransac': (C.c_int, [_vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _vp, _vp, _vp, _vp, _vp, _vp,
+                                   C.POINTER(C.c_uint32), _vp]),
+    'sfmba_pnp_ransac_host': (C.c_int, [_vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _vp, _vp, _vp, _vp, _vp, _vp,
+                                        C.POINTER(C.c_uint32)]),
+    'sfmba_fund_ransac': (C.c_int, [_vp, _i32, _i32, _vp, _vp, _f64, _vp, _vp, _vp, _vp, _vp,
+                                    C.POINTER(C.c_uint32), _vp]),
+    'sfmba_fund_ransac_host': (C.c_int, [_vp, _i32, _i32, _vp, _vp, _f64, _vp, _vp, _vp, _vp, _vp,
+                                         C.POINTER(C.c_uint32)]),
     'sfmba_build_visibility': (C.c_int, [_vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_i32), _vp]),
     'sfmba_profile_reset': (C.c_int, [_vp]),
     'sfmba_profile_enable': (C.c_int, [_vp, C.c_int]),

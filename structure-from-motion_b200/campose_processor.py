@@ -1,10 +1,11 @@
 """CamposeProcessor with the reference's interface (campose_processor.py:11-808).
 
 The nonlinear PnP refinement (campose_processor.py:308-459) runs on the GPU through
-sfmba_pnp_refine_batched, including the reference's row-packing and dv/dC quirks.  The linear
-initialisers (essential-matrix decomposition, cheirality vote, RANSAC-DLT PnP) are host code outside
-the accelerated path; they are restated here in vectorised NumPy
-and consume Python's `random.sample` stream exactly like the reference so RANSAC draws agree.
+sfmba_pnp_refine_batched, including the reference's row-packing and dv/dC quirks.  The RANSAC-DLT
+initialiser (campose_processor.py:485-633) evaluates all its hypotheses on the GPU (sfmba_pnp_ransac,
+SURVEY.md section 8(f) row 3) from sample indices drawn with Python's `random.sample` exactly like
+the reference.  Essential-matrix decomposition and the cheirality vote are a handful of 3x3
+operations and stay host code.
 """
 from __future__ import annotations
 
@@ -86,8 +87,20 @@ class CamposeProcessor:
         return inlier_indices, ref_rot, ref_loc
 
     # ------------------------------------------------------------------------------------------
-    def linear_estimate_cam_pose_pnp(self, key_2d_pts, tri_3d_pts, intrinsic_mat, ransac_config=None):
-        """RANSAC over 6-point DLT poses (campose_processor.py:249-305, 485-633)."""
+    def linear_estimate_cam_pose_pnp(self, key_2d_pts, tri_3d_pts, intrinsic_mat, ransac_config=None,
+                                     lapack_sign_quirk=True):
+        """RANSAC over 6-point DLT poses (campose_processor.py:249-305, 485-633).
+
+        The six indices of every hypothesis are drawn here with random.sample, one draw per iteration in the
+        reference's order (campose_processor.py:531), so Python's global random stream is consumed exactly as
+        the reference consumes it.  All hypotheses are then evaluated at once on the GPU (sfmba_pnp_ransac:
+        12x12 null vector, rotation re-orthogonalisation, inlier count over every point, first strict maximum).
+
+        lapack_sign_quirk: campose_processor.py:620-631 returns (R, C) or (R, -C) depending on the sign LAPACK
+        happens to give the last right singular vector (about half of the hypotheses each).  True (default)
+        reproduces that outcome hypothesis by hypothesis -- the sign, and only the sign, is read off a batched
+        numpy.linalg.svd of the same 12x12 systems on the host; False uses the geometrically consistent sign
+        everywhere (pure device path, usually a better winner than the reference finds)."""
         if not ransac_config:
             ransac_config = self.ransac_config
         if key_2d_pts.shape[1] != tri_3d_pts.shape[1]:
@@ -102,44 +115,36 @@ class CamposeProcessor:
         key = np.asarray(key_2d_pts, dtype=float)
         tri = np.asarray(tri_3d_pts, dtype=float)
         k = np.asarray(intrinsic_mat, dtype=float)
-        kinv = np.linalg.inv(k)
-        best = (np.identity(3), np.zeros((3, 1)), 0, [])
-        for _ in range(ransac_config.iteration):
-            idx = random.sample(range(num_pts), 6)
-            rot, loc = self._dlt_six(kinv @ key[:, idx], tri[:, idx])
-            proj = k @ np.hstack((rot.T, rot.T @ -loc))
-            p = proj @ tri
-            p = p / p[2]
-            err = np.sqrt(np.sum((key - p) ** 2, axis=0))
-            inliers = np.flatnonzero(err < ransac_config.inlier_threshold)
-            if inliers.size > best[2]:
-                best = (rot, loc, int(inliers.size), [int(i) for i in inliers])
-        return best[3], best[0], best[1]
+        samples = np.array([random.sample(range(num_pts), 6) for _ in range(ransac_config.iteration)],
+                           dtype=np.int32).reshape(-1, 6)
+        sign = self._lapack_loc_signs(key, tri, k, samples) if lapack_sign_quirk else None
+        res = self.engine.pnp_ransac(key.T, tri.T, k, samples, ransac_config.inlier_threshold, sign)
+        inliers = [int(i) for i in np.flatnonzero(res['mask'])]
+        return inliers, res['rot'], res['loc']
 
     @staticmethod
-    def _dlt_six(p2d, p3d):
-        """Pose from six correspondences: 12x12 DLT, rotation re-orthogonalised
-        (campose_processor.py:565-633)."""
-        w = np.zeros((12, 12))
-        x3 = p3d.T * p2d[2][:, None]                 # rows: p2d_z * (X, Y, Z, W)
-        w[0::2, 0:4] = x3
-        w[0::2, 8:12] = -p3d.T * p2d[0][:, None]
-        w[1::2, 4:8] = x3
-        w[1::2, 8:12] = -p3d.T * p2d[1][:, None]
-        # the reference writes p2d_z for the 4th column (campose_processor.py:592, 609), i.e. W == 1
-        w[0::2, 3] = p2d[2]
-        w[1::2, 7] = p2d[2]
-        w[0::2, 11] = -p2d[0]
-        w[1::2, 11] = -p2d[1]
-        _, _, vh = np.linalg.svd(w)
-        cam_mat = np.reshape(vh[-1, :], (3, 4))
-        uu, ss, vvh = np.linalg.svd(cam_mat[:, 0:3])
-        rot = (uu @ vvh).T
-        loc = (rot @ -cam_mat[:, 3:4]) / ss[0]
-        if np.linalg.det(rot) < 0:
-            rot = -rot
-            loc = -loc
-        return rot, loc
+    def _lapack_loc_signs(key, tri, k, samples):
+        """+1 / -1 per hypothesis: the sign of det(rot_t_noise) for the last right singular vector as the host's
+        LAPACK returns it (campose_processor.py:616-631).  One batched SVD; nothing else of the model is used."""
+        if samples.shape[0] == 0:
+            return np.zeros(0, dtype=np.int32)
+        p2 = np.linalg.inv(k) @ key                                   # (3, n)
+        a = p2[:, samples]                                            # (3, H, 6)
+        x = tri[0:3][:, samples]                                      # (3, H, 6)
+        H = samples.shape[0]
+        w = np.zeros((H, 12, 12))
+        zx = (a[2][None] * x).transpose(1, 2, 0)                      # (H, 6, 3)
+        w[:, 0::2, 0:3] = zx
+        w[:, 0::2, 3] = a[2]
+        w[:, 0::2, 8:11] = -(a[0][None] * x).transpose(1, 2, 0)
+        w[:, 0::2, 11] = -a[0]
+        w[:, 1::2, 4:7] = zx
+        w[:, 1::2, 7] = a[2]
+        w[:, 1::2, 8:11] = -(a[1][None] * x).transpose(1, 2, 0)
+        w[:, 1::2, 11] = -a[1]
+        vh = np.linalg.svd(w)[2]
+        m = vh[:, -1, :].reshape(H, 3, 4)[:, :, 0:3]
+        return np.where(np.linalg.det(m) < 0, -1, 1).astype(np.int32)
 
     # ------------------------------------------------------------------------------------------
     def nonlinear_estimate_cam_pose_pnp(self, key_2d_pts, tri_3d_pts, intrinsic_mat, init_rot, init_loc,

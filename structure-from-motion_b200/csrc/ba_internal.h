@@ -238,6 +238,15 @@ void launch_pnp(int num_views, const int32_t* rowptr, const double* obs_xy, cons
                 double* loc, double lambda, int iterations, bool row_packing_quirk, bool dvdc_quirk,
                 uint32_t* flags, cudaStream_t st, LaunchCounter& lc);
 
+// ---- RANSAC hypotheses (ransac.cu) -----------------------------------------------------------------
+void launch_pnp_ransac(int n, int H, const double* key, const double* X, const double* Kmat, const double* Kinv,
+                       const int32_t* samples, const int32_t* loc_sign, double thr, double* models, double* projs,
+                       int32_t* counts, int32_t* best, uint8_t* mask, uint32_t* flags, cudaStream_t st,
+                       LaunchCounter& lc);
+void launch_fund_ransac(int n, int H, const double* pairs, const int32_t* samples, double thr, double* models,
+                        int32_t* counts, int32_t* best, uint8_t* mask, uint32_t* flags, cudaStream_t st,
+                        LaunchCounter& lc);
+
 // ---- visibility (visibility.cu) ------------------------------------------------------------------
 int build_visibility_device(int num_views, int num_pts, const int64_t* diag, const int64_t* key_off_host,
                             int64_t total_keys, int32_t* obs_pt, int32_t* obs_cam, int32_t* obs_key,

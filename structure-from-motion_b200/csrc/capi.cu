@@ -378,6 +378,212 @@ int sfmba_pnp_refine_batched_host(sfmba_ctx* ctx, int32_t num_views, int32_t num
   return rc2 ? rc2 : rc;
 }
 
+// ---- f3: RANSAC hypotheses ---------------------------------------------------------------------------
+namespace {
+bool inv3_host(const double* a, double* o) {
+  const double c00 = a[4] * a[8] - a[5] * a[7], c01 = a[5] * a[6] - a[3] * a[8], c02 = a[3] * a[7] - a[4] * a[6];
+  const double det = a[0] * c00 + a[1] * c01 + a[2] * c02;
+  if (det == 0.0 || det != det) return false;
+  o[0] = c00 / det;
+  o[1] = (a[2] * a[7] - a[1] * a[8]) / det;
+  o[2] = (a[1] * a[5] - a[2] * a[4]) / det;
+  o[3] = c01 / det;
+  o[4] = (a[0] * a[8] - a[2] * a[6]) / det;
+  o[5] = (a[2] * a[3] - a[0] * a[5]) / det;
+  o[6] = c02 / det;
+  o[7] = (a[1] * a[6] - a[0] * a[7]) / det;
+  o[8] = (a[0] * a[4] - a[1] * a[3]) / det;
+  return true;
+}
+
+// scratch layout inside ctx->host_stage[11]: flags(16 B) | best i32[2] (16 B) | K, Kinv (18 doubles) | counts[H] |
+// models[H][stride] | projs[H][12]
+struct RansacScratch {
+  uint32_t* flags;
+  int32_t* best;
+  double* kk;
+  int32_t* counts;
+  double* models;
+  double* projs;
+};
+int ransac_scratch(sfmba_ctx* ctx, int H, int stride, bool want_projs, RansacScratch* r) {
+  const size_t hc = ((size_t)H * sizeof(int32_t) + 15) & ~(size_t)15;
+  const size_t bytes = 32 + 18 * sizeof(double) + hc + (size_t)H * stride * sizeof(double) +
+                       (want_projs ? (size_t)H * 12 * sizeof(double) : 0) + 64;
+  cudaError_t e = ctx->host_stage[11].reserve(bytes);
+  if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(ransac scratch)");
+  char* b = ctx->host_stage[11].as<char>();
+  r->flags = reinterpret_cast<uint32_t*>(b);
+  r->best = reinterpret_cast<int32_t*>(b + 16);
+  r->kk = reinterpret_cast<double*>(b + 32);
+  r->counts = reinterpret_cast<int32_t*>(b + 32 + 18 * sizeof(double));
+  r->models = reinterpret_cast<double*>(b + 32 + 18 * sizeof(double) + hc);
+  r->projs = r->models + (size_t)H * stride;
+  return SFMBA_OK;
+}
+}  // namespace
+
+int sfmba_pnp_ransac(sfmba_ctx* ctx, int32_t num_pts, int32_t num_hyp, const double* key, const double* X,
+                     const double* K, const int32_t* samples, const int32_t* loc_sign, double inlier_threshold,
+                     double* out_rot, double* out_loc, int32_t* out_best, uint8_t* out_mask, int32_t* out_counts,
+                     double* out_models, uint32_t* host_flags, void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_pts < 0 || num_hyp < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  if (!K || !out_best || (num_pts > 0 && (!key || !X || !out_mask)) || (num_hyp > 0 && !samples))
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "null pointer in pnp_ransac");
+  if (num_hyp > 0 && num_pts < 6) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "pnp_ransac needs >= 6 points");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  double kk[18];
+  for (int i = 0; i < 9; ++i) kk[i] = K[i];
+  if (!inv3_host(K, kk + 9)) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "singular intrinsic matrix");
+  RansacScratch rs;
+  int rc = ransac_scratch(ctx, std::max(num_hyp, 1), 12, true, &rs);
+  if (rc) return rc;
+  cudaMemsetAsync(rs.flags, 0, 32, st);
+  cudaMemcpyAsync(rs.kk, kk, sizeof(kk), cudaMemcpyHostToDevice, st);
+  launch_pnp_ransac(num_pts, num_hyp, key, X, rs.kk, rs.kk + 9, samples, loc_sign, inlier_threshold, rs.models,
+                    rs.projs, rs.counts, rs.best, out_mask, rs.flags, st, ctx->lc);
+  // pinned read-back: flags | best[2] | winner's model
+  char* pin = reinterpret_cast<char*>(ctx->pinned);
+  cudaMemcpyAsync(pin, rs.flags, 32, cudaMemcpyDeviceToHost, st);
+  if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "pnp_ransac sync")) != 0) return rc;
+  if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "pnp_ransac kernels")) != 0) return rc;
+  const uint32_t fl = *reinterpret_cast<uint32_t*>(pin);
+  int32_t best[2] = {-1, 0};
+  if (num_hyp > 0) {
+    best[0] = reinterpret_cast<int32_t*>(pin + 16)[0];
+    best[1] = reinterpret_cast<int32_t*>(pin + 16)[1];
+  }
+  out_best[0] = best[0];
+  out_best[1] = best[1];
+  if (host_flags) *host_flags = fl;
+  double model[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0};       // campose_processor.py:526-527
+  if (best[0] >= 0) {
+    cudaMemcpyAsync(pin + 64, rs.models + 12 * (size_t)best[0], sizeof(model), cudaMemcpyDeviceToHost, st);
+    if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "pnp_ransac model")) != 0) return rc;
+    memcpy(model, pin + 64, sizeof(model));
+  } else if (num_hyp <= 0 && num_pts > 0) {
+    cudaMemsetAsync(out_mask, 0, (size_t)num_pts, st);
+  }
+  if (out_rot) memcpy(out_rot, model, 9 * sizeof(double));
+  if (out_loc) memcpy(out_loc, model + 9, 3 * sizeof(double));
+  if (num_hyp > 0 && out_counts)
+    cudaMemcpyAsync(out_counts, rs.counts, (size_t)num_hyp * sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
+  if (num_hyp > 0 && out_models)
+    cudaMemcpyAsync(out_models, rs.models, (size_t)num_hyp * 12 * sizeof(double), cudaMemcpyDeviceToDevice, st);
+  return sfm_check_cuda(ctx, cudaStreamSynchronize(st), "pnp_ransac outputs");
+}
+
+int sfmba_pnp_ransac_host(sfmba_ctx* ctx, int32_t num_pts, int32_t num_hyp, const double* key, const double* X,
+                          const double* K, const int32_t* samples, const int32_t* loc_sign, double inlier_threshold,
+                          double* out_rot, double* out_loc, int32_t* out_best, uint8_t* out_mask,
+                          int32_t* out_counts, double* out_models, uint32_t* host_flags) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_pts < 0 || num_hyp < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = ctx->own_stream;
+  double *d_key, *d_X;
+  int32_t *d_s, *d_sign = nullptr;
+  int rc;
+  if ((rc = stage_in(ctx, 0, key, (size_t)3 * num_pts, &d_key, st))) return rc;
+  if ((rc = stage_in(ctx, 1, X, (size_t)4 * num_pts, &d_X, st))) return rc;
+  if ((rc = stage_in(ctx, 2, samples, (size_t)6 * num_hyp, &d_s, st))) return rc;
+  if (loc_sign && (rc = stage_in(ctx, 3, loc_sign, (size_t)num_hyp, &d_sign, st))) return rc;
+  cudaError_t e = ctx->host_stage[4].reserve(std::max<size_t>(16, (size_t)num_pts));
+  if (e == cudaSuccess) e = ctx->host_stage[5].reserve(std::max<size_t>(16, (size_t)num_hyp * sizeof(int32_t)));
+  if (e == cudaSuccess) e = ctx->host_stage[6].reserve(std::max<size_t>(16, (size_t)num_hyp * 12 * sizeof(double)));
+  if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(stage)");
+  uint8_t* d_mask = ctx->host_stage[4].as<uint8_t>();
+  int32_t* d_counts = out_counts ? ctx->host_stage[5].as<int32_t>() : nullptr;
+  double* d_models = out_models ? ctx->host_stage[6].as<double>() : nullptr;
+  rc = sfmba_pnp_ransac(ctx, num_pts, num_hyp, d_key, d_X, K, d_s, loc_sign ? d_sign : nullptr, inlier_threshold,
+                        out_rot, out_loc, out_best, d_mask, d_counts, d_models, host_flags, st);
+  if (rc != SFMBA_OK) return rc;
+  if (num_pts && out_mask) cudaMemcpyAsync(out_mask, d_mask, (size_t)num_pts, cudaMemcpyDeviceToHost, st);
+  if (num_hyp && out_counts)
+    cudaMemcpyAsync(out_counts, d_counts, (size_t)num_hyp * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+  if (num_hyp && out_models)
+    cudaMemcpyAsync(out_models, d_models, (size_t)num_hyp * 12 * sizeof(double), cudaMemcpyDeviceToHost, st);
+  return sfm_check_cuda(ctx, cudaStreamSynchronize(st), "D2H sync");
+}
+
+int sfmba_fund_ransac(sfmba_ctx* ctx, int32_t num_pairs, int32_t num_hyp, const double* pairs,
+                      const int32_t* samples, double inlier_threshold, double* out_F, int32_t* out_best,
+                      uint8_t* out_mask, int32_t* out_counts, double* out_models, uint32_t* host_flags,
+                      void* stream) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_pairs < 0 || num_hyp < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  if (!out_best || (num_pairs > 0 && (!pairs || !out_mask)) || (num_hyp > 0 && !samples))
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "null pointer in fund_ransac");
+  if (num_hyp > 0 && num_pairs < 8) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "fund_ransac needs >= 8 pairs");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  RansacScratch rs;
+  int rc = ransac_scratch(ctx, std::max(num_hyp, 1), 9, false, &rs);
+  if (rc) return rc;
+  cudaMemsetAsync(rs.flags, 0, 32, st);
+  launch_fund_ransac(num_pairs, num_hyp, pairs, samples, inlier_threshold, rs.models, rs.counts, rs.best, out_mask,
+                     rs.flags, st, ctx->lc);
+  char* pin = reinterpret_cast<char*>(ctx->pinned);
+  cudaMemcpyAsync(pin, rs.flags, 32, cudaMemcpyDeviceToHost, st);
+  if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "fund_ransac sync")) != 0) return rc;
+  if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "fund_ransac kernels")) != 0) return rc;
+  const uint32_t fl = *reinterpret_cast<uint32_t*>(pin);
+  int32_t best[2] = {-1, 0};
+  if (num_hyp > 0) {
+    best[0] = reinterpret_cast<int32_t*>(pin + 16)[0];
+    best[1] = reinterpret_cast<int32_t*>(pin + 16)[1];
+  }
+  out_best[0] = best[0];
+  out_best[1] = best[1];
+  if (host_flags) *host_flags = fl;
+  double model[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};                  // epipolar_processor.py:213
+  if (best[0] >= 0) {
+    cudaMemcpyAsync(pin + 64, rs.models + 9 * (size_t)best[0], sizeof(model), cudaMemcpyDeviceToHost, st);
+    if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "fund_ransac model")) != 0) return rc;
+    memcpy(model, pin + 64, sizeof(model));
+  } else if (num_hyp <= 0 && num_pairs > 0) {
+    cudaMemsetAsync(out_mask, 0, (size_t)num_pairs, st);
+  }
+  if (out_F) memcpy(out_F, model, sizeof(model));
+  if (num_hyp > 0 && out_counts)
+    cudaMemcpyAsync(out_counts, rs.counts, (size_t)num_hyp * sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
+  if (num_hyp > 0 && out_models)
+    cudaMemcpyAsync(out_models, rs.models, (size_t)num_hyp * 9 * sizeof(double), cudaMemcpyDeviceToDevice, st);
+  return sfm_check_cuda(ctx, cudaStreamSynchronize(st), "fund_ransac outputs");
+}
+
+int sfmba_fund_ransac_host(sfmba_ctx* ctx, int32_t num_pairs, int32_t num_hyp, const double* pairs,
+                           const int32_t* samples, double inlier_threshold, double* out_F, int32_t* out_best,
+                           uint8_t* out_mask, int32_t* out_counts, double* out_models, uint32_t* host_flags) {
+  if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (num_pairs < 0 || num_hyp < 0) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "negative size");
+  cudaSetDevice(ctx->device);
+  cudaStream_t st = ctx->own_stream;
+  double* d_pairs;
+  int32_t* d_s;
+  int rc;
+  if ((rc = stage_in(ctx, 0, pairs, (size_t)4 * num_pairs, &d_pairs, st))) return rc;
+  if ((rc = stage_in(ctx, 2, samples, (size_t)8 * num_hyp, &d_s, st))) return rc;
+  cudaError_t e = ctx->host_stage[4].reserve(std::max<size_t>(16, (size_t)num_pairs));
+  if (e == cudaSuccess) e = ctx->host_stage[5].reserve(std::max<size_t>(16, (size_t)num_hyp * sizeof(int32_t)));
+  if (e == cudaSuccess) e = ctx->host_stage[6].reserve(std::max<size_t>(16, (size_t)num_hyp * 9 * sizeof(double)));
+  if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(stage)");
+  uint8_t* d_mask = ctx->host_stage[4].as<uint8_t>();
+  int32_t* d_counts = out_counts ? ctx->host_stage[5].as<int32_t>() : nullptr;
+  double* d_models = out_models ? ctx->host_stage[6].as<double>() : nullptr;
+  rc = sfmba_fund_ransac(ctx, num_pairs, num_hyp, d_pairs, d_s, inlier_threshold, out_F, out_best, d_mask, d_counts,
+                         d_models, host_flags, st);
+  if (rc != SFMBA_OK) return rc;
+  if (num_pairs && out_mask) cudaMemcpyAsync(out_mask, d_mask, (size_t)num_pairs, cudaMemcpyDeviceToHost, st);
+  if (num_hyp && out_counts)
+    cudaMemcpyAsync(out_counts, d_counts, (size_t)num_hyp * sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+  if (num_hyp && out_models)
+    cudaMemcpyAsync(out_models, d_models, (size_t)num_hyp * 9 * sizeof(double), cudaMemcpyDeviceToHost, st);
+  return sfm_check_cuda(ctx, cudaStreamSynchronize(st), "D2H sync");
+}
+
 int sfmba_build_visibility(sfmba_ctx* ctx, int32_t num_views, int32_t num_pts, const int64_t* diag,
                            const int64_t* key_off, int32_t* obs_pt, int32_t* obs_cam, int32_t* obs_key,
                            int32_t* pt_rowptr, int32_t* host_num_obs, void* stream) {

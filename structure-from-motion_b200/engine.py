@@ -307,6 +307,62 @@ class Engine:
         return rot_o.reshape(-1, 3, 3), loc_o
 
     # -- visibility index on the device ------------------------------------------------------------
+    def pnp_ransac(self, key, X, k_mat, samples, inlier_threshold, loc_sign=None, want_all=False):
+        """f3: every 6-point DLT hypothesis of campose_processor.py:485-633 on the device.  key (n,3), X (n,4),
+        samples (H,6) int, loc_sign (H,) of +-1 or None.  Returns dict(hyp, count, mask (n,) bool, rot (3,3),
+        loc (3,1), flags[, counts (H,), models (H,12)])."""
+        key = np.ascontiguousarray(key, dtype=np.float64).reshape(-1, 3)
+        X = np.ascontiguousarray(X, dtype=np.float64).reshape(-1, 4)
+        k_mat = np.ascontiguousarray(k_mat, dtype=np.float64).reshape(9)
+        samples = np.ascontiguousarray(samples, dtype=np.int32).reshape(-1, 6)
+        n, H = key.shape[0], samples.shape[0]
+        if X.shape[0] != n:
+            raise ValueError('key / X size mismatch')
+        if H and (samples.min() < 0 or samples.max() >= n):
+            raise ValueError('sample index out of range')
+        sign = None if loc_sign is None else np.ascontiguousarray(loc_sign, dtype=np.int32).reshape(H)
+        rot = np.zeros(9)
+        loc = np.zeros(3)
+        best = np.zeros(2, dtype=np.int32)
+        mask = np.zeros(max(n, 1), dtype=np.uint8)
+        counts = np.zeros(max(H, 1), dtype=np.int32) if want_all else None
+        models = np.zeros((max(H, 1), 12)) if want_all else None
+        flags = C.c_uint32(0)
+        rc = self.lib.sfmba_pnp_ransac_host(
+            self.ctx, n, H, _ptr(key), _ptr(X), _ptr(k_mat), _ptr(samples), None if sign is None else _ptr(sign),
+            float(inlier_threshold), _ptr(rot), _ptr(loc), _ptr(best), _ptr(mask),
+            None if counts is None else _ptr(counts), None if models is None else _ptr(models), C.byref(flags))
+        _capi.check(rc, self.ctx)
+        out = dict(hyp=int(best[0]), count=int(best[1]), mask=mask[:n].astype(bool), rot=rot.reshape(3, 3),
+                   loc=loc.reshape(3, 1), flags=int(flags.value))
+        if want_all:
+            out.update(counts=counts[:H], models=models[:H])
+        return out
+
+    def fund_ransac(self, pairs, samples, inlier_threshold, want_all=False):
+        """f3: every 8-point hypothesis of epipolar_processor.py:140-247 on the device.  pairs (n,4) normalised
+        [xl, yl, xr, yr], samples (H,8).  Returns dict(hyp, count, mask, F (3,3), flags[, counts, models (H,9)])."""
+        pairs = np.ascontiguousarray(pairs, dtype=np.float64).reshape(-1, 4)
+        samples = np.ascontiguousarray(samples, dtype=np.int32).reshape(-1, 8)
+        n, H = pairs.shape[0], samples.shape[0]
+        if H and (samples.min() < 0 or samples.max() >= n):
+            raise ValueError('sample index out of range')
+        F = np.zeros(9)
+        best = np.zeros(2, dtype=np.int32)
+        mask = np.zeros(max(n, 1), dtype=np.uint8)
+        counts = np.zeros(max(H, 1), dtype=np.int32) if want_all else None
+        models = np.zeros((max(H, 1), 9)) if want_all else None
+        flags = C.c_uint32(0)
+        rc = self.lib.sfmba_fund_ransac_host(
+            self.ctx, n, H, _ptr(pairs), _ptr(samples), float(inlier_threshold), _ptr(F), _ptr(best), _ptr(mask),
+            None if counts is None else _ptr(counts), None if models is None else _ptr(models), C.byref(flags))
+        _capi.check(rc, self.ctx)
+        out = dict(hyp=int(best[0]), count=int(best[1]), mask=mask[:n].astype(bool), F=F.reshape(3, 3),
+                   flags=int(flags.value))
+        if want_all:
+            out.update(counts=counts[:H], models=models[:H])
+        return out
+
     def build_visibility(self, diag_rows, num_pts: int):
         """a3/a4 on the GPU: returns int32 (obs_pt, obs_cam, obs_key, rowptr), bit-exact with
         KeyTracker.is_visible in the loop order of ba_processor.py:304-310."""

@@ -19,6 +19,9 @@ Fixtures written (all float64 unless noted):
   opencv_pnp.npz            campose_processor.py:1070-1090 nonlinear PnP known answer
   tri_inline.npz            triangulation_processor.py:415-473 inline known answer
   synth_ba_small.npz        random small BA problems pushed through the literal reference
+  ransac.npz                f3: linear_estimate_cam_pose_pnp and determine_fundamental_mat on the OpenCV test
+                            data with the sample tables the reference drew (campose_processor.py:485-633,
+                            epipolar_processor.py:23-265)
 """
 import argparse
 import os
@@ -268,6 +271,84 @@ def run_opencv_pnp(ref):
     print('opencv_pnp: loc_diff %.6f' % np.sqrt(np.sum(np.square(loc_truth - out_loc))))
 
 
+def run_ransac(ref):
+    """f3: the two RANSAC initialisers on the reference's own OpenCV test data, with the sample table the
+    reference drew (random.sample replayed from the same generator state)."""
+    import random
+    d = os.path.join(REF, 'test_dataset', 'opencv')
+    # ---- 6-point DLT PnP (campose_processor.py:249-305, 485-633)
+    ref_k = np.load(d + '/ess_intrinsic_mat.npy')
+    pts3 = np.load(d + '/pnp_points_3d.npy').T
+    ones = np.ones((1, pts3.shape[1]))
+    pts3h = np.vstack((pts3, ones))
+    pts2h = np.vstack((np.load(d + '/pnp_points_2d.npy').T, ones))
+    # a perturbed copy: every 5th point is an outlier, so the inlier sets differ between hypotheses
+    rng = np.random.default_rng(7)
+    pts2o = pts2h.copy()
+    out = np.arange(0, pts2o.shape[1], 5)
+    pts2o[0:2, out] += rng.normal(0, 60.0, size=(2, out.size))
+    res = {}
+    for tag, key, thr, iters in (('clean', pts2h, 8.0, 120), ('outliers', pts2o, 30.0, 120)):
+        cfg = ref.utils.RansacConfig(inlier_threshold=thr, subset_confidence=0.99, sample_confidence=0.75,
+                                     sample_num=6, iteration=iters)
+        state = random.getstate()
+        cp = ref.cp.CamposeProcessor(cfg, 5, 200)
+        inl, rot, loc = cp.linear_estimate_cam_pose_pnp(key, pts3h, ref_k, cfg)
+        random.setstate(state)
+        samples = np.array([random.sample(range(key.shape[1]), 6) for _ in range(cfg.iteration)], dtype=np.int32)
+        res['pnp_%s_key' % tag] = key
+        res['pnp_%s_samples' % tag] = samples
+        res['pnp_%s_inliers' % tag] = np.array(inl, dtype=np.int32)
+        res['pnp_%s_rot' % tag] = rot
+        res['pnp_%s_loc' % tag] = loc
+        res['pnp_%s_thr' % tag] = np.float64(thr)
+        print('pnp_ransac %s: %d hypotheses, %d inliers' % (tag, cfg.iteration, len(inl)))
+    res['pnp_tri'] = pts3h
+    res['pnp_k'] = ref_k
+    # ---- 8-point fundamental matrix (epipolar_processor.py:23-56, 96-265)
+    p1 = np.load(d + '/ess_pixel_pt1.npy')[:, 0:2]
+    p2 = np.load(d + '/ess_pixel_pt2.npy')[:, 0:2]
+    p2o = p2.copy()
+    out = np.arange(0, p2o.shape[0], 4)
+    p2o[out] += rng.normal(0, 25.0, size=(out.size, 2))
+    ep_mod = ref.ep
+    for tag, right, thr, iters in (('clean', p2, 1e-3, 60), ('outliers', p2o, 1e-1, 60)):
+        left_pts = ref.utils.KeyPt(p1.shape[0])
+        right_pts = ref.utils.KeyPt(p1.shape[0])
+        left_pts[0:2, :] = p1.T
+        right_pts[0:2, :] = right.T
+        cfg = ref.utils.RansacConfig(inlier_threshold=thr, subset_confidence=0.99, sample_confidence=0.75,
+                                     sample_num=8, iteration=iters)
+        state = random.getstate()
+        ep = ep_mod.EpipolarProcessor(cfg)
+        inl = ep.determine_fundamental_mat([left_pts, right_pts], cfg)
+        random.setstate(state)
+        samples = np.array([random.sample(range(p1.shape[0]), 8) for _ in range(cfg.iteration)], dtype=np.int32)
+        res['fund_%s_left' % tag] = p1
+        res['fund_%s_right' % tag] = right
+        res['fund_%s_samples' % tag] = samples
+        res['fund_%s_inliers' % tag] = np.array(inl, dtype=np.int32)
+        res['fund_%s_F' % tag] = ep.fund_mat
+        res['fund_%s_thr' % tag] = np.float64(thr)
+        print('fund_ransac %s: %d hypotheses, %d inliers' % (tag, cfg.iteration, len(inl)))
+    # the 8-pair known answer of epipolar_processor.py:274-299 (rows == 8: no RANSAC)
+    data8 = np.array([[580, 2362, 492, 1803], [2050, 2097, 1381, 1956], [2558, 2174, 1544, 2115],
+                      [1395, 1970, 1166, 1752], [2490, 3003, 466, 2440], [3368, 1622, 3320, 2011],
+                      [2183, 1500, 2471, 1621], [1972, 1775, 1674, 1736]], dtype=float)
+    left_pts = ref.utils.KeyPt(8)
+    right_pts = ref.utils.KeyPt(8)
+    left_pts[0:2, :] = data8[:, 0:2].T
+    right_pts[0:2, :] = data8[:, 2:4].T
+    cfg = ref.utils.RansacConfig(inlier_threshold=1e-3, subset_confidence=0.99, sample_confidence=0.75,
+                                 sample_num=8, iteration=200)
+    ep = ep_mod.EpipolarProcessor(cfg)
+    inl = ep.determine_fundamental_mat([left_pts, right_pts], cfg)
+    res['fund_eight_data'] = data8
+    res['fund_eight_F'] = ep.fund_mat
+    res['fund_eight_inliers'] = np.array(inl, dtype=np.int32)
+    np.savez_compressed(os.path.join(HERE, 'ransac.npz'), **res)
+
+
 def run_tri_inline(ref):
     p1 = np.array([[5.010e+03, 0.000e+00, 3.600e+02, 0.000e+00],
                    [0.000e+00, 5.010e+03, 6.400e+02, 0.000e+00],
@@ -413,8 +494,12 @@ def main():
     ap.add_argument('--skip-pipeline', action='store_true')
     ap.add_argument('--skip-pnp', action='store_true')
     ap.add_argument('--skip-synth', action='store_true')
+    ap.add_argument('--only-ransac', action='store_true')
     args = ap.parse_args()
     ref = _import_reference()
+    run_ransac(ref)
+    if args.only_ransac:
+        return
     run_tri_inline(ref)
     if not args.skip_synth:
         run_synth_small(ref)

@@ -164,3 +164,28 @@ def test_synthetic_shapes_and_sharding():
         assert max(s.num_obs for s in shards) - min(s.num_obs for s in shards) <= 2 * int(np.diff(p1.rowptr).max())
         for s in shards:
             assert s.rowptr[0] == 0 and s.rowptr[-1] == s.num_obs and s.num_cams == V
+
+
+def test_lapack_sign_helper_matches_oracle(oracle):
+    """CamposeProcessor._lapack_loc_signs (host, batched SVD) reads the same sign per hypothesis as the oracle's
+    hypothesis-by-hypothesis restatement of campose_processor.py:616-631."""
+    import sfm_b200
+    from helpers import load_golden
+    g = load_golden('ransac.npz')
+    key, tri, k, samples = g['pnp_outliers_key'], g['pnp_tri'], g['pnp_k'], g['pnp_outliers_samples']
+    ora = oracle.pnp_ransac(key, tri, k, samples[:40], 30.0)
+    sg = sfm_b200.CamposeProcessor._lapack_loc_signs(key, tri, k, samples[:40])
+    assert np.array_equal(sg, ora['signs'])
+
+
+def test_epipolar_normalize_matches_oracle(oracle):
+    import sfm_b200
+    from helpers import load_golden
+    g = load_golden('ransac.npz')
+    left, right = g['fund_clean_left'], g['fund_clean_right']
+    kl, kr = sfm_b200.KeyPt(left.shape[0]), sfm_b200.KeyPt(left.shape[0])
+    kl[0:2, :] = left.T
+    kr[0:2, :] = right.T
+    pairs, tl, tr = sfm_b200.EpipolarProcessor._normalize([kl, kr])
+    p2, tl2, tr2 = oracle.fund_normalize(left, right)
+    assert np.array_equal(pairs, p2) and np.array_equal(tl, tl2) and np.array_equal(tr, tr2)

@@ -175,3 +175,37 @@ def test_jacobian_quirk_vs_finite_differences(oracle):
     assert np.max(np.abs(jp_fix[0] - num)) < 1e-6
     diff = np.abs(jp_q[0] - jp_fix[0]) > 1e-12
     assert not diff[0].any() and not diff[1, 3:].any() and diff[1, 0:3].any()
+
+
+# ---- f3: RANSAC initialisers ---------------------------------------------------------------------------
+@pytest.mark.parametrize('tag', ['clean', 'outliers'])
+def test_oracle_pnp_ransac_matches_reference(oracle, tag):
+    """oracle.pnp_ransac on the sample table the reference drew == linear_estimate_cam_pose_pnp's own result
+    (campose_processor.py:485-633), including the LAPACK-sign dependent (R, -C) hypotheses."""
+    g = load_golden('ransac.npz')
+    r = oracle.pnp_ransac(g['pnp_%s_key' % tag], g['pnp_tri'], g['pnp_k'], g['pnp_%s_samples' % tag],
+                          float(g['pnp_%s_thr' % tag]))
+    assert r['inliers'] == list(g['pnp_%s_inliers' % tag])
+    assert np.max(np.abs(r['rot'] - g['pnp_%s_rot' % tag])) < 1e-12
+    assert np.max(np.abs(r['loc'] - g['pnp_%s_loc' % tag])) < 1e-9
+    frac = float(np.mean(r['signs'] > 0))
+    assert 0.2 < frac < 0.8            # both signs occur: the quirk is real on this host's LAPACK
+
+
+@pytest.mark.parametrize('tag', ['clean', 'outliers'])
+def test_oracle_fund_ransac_matches_reference(oracle, tag):
+    g = load_golden('ransac.npz')
+    pairs, tl, tr = oracle.fund_normalize(g['fund_%s_left' % tag], g['fund_%s_right' % tag])
+    r = oracle.fund_ransac(pairs, g['fund_%s_samples' % tag], float(g['fund_%s_thr' % tag]))
+    assert r['inliers'] == list(g['fund_%s_inliers' % tag])
+    f = oracle.fund_denormalize(r['F'], tl, tr)
+    assert np.max(np.abs(f - g['fund_%s_F' % tag])) < 1e-10 * np.max(np.abs(f))
+
+
+def test_oracle_fund_eight_known_answer(oracle):
+    """epipolar_processor.py:274-299: eight pairs, no RANSAC."""
+    g = load_golden('ransac.npz')
+    d8 = g['fund_eight_data']
+    pairs, tl, tr = oracle.fund_normalize(d8[:, 0:2], d8[:, 2:4])
+    f = oracle.fund_denormalize(oracle.fund_eight(pairs), tl, tr)
+    assert np.max(np.abs(f - g['fund_eight_F'])) < 1e-9 * np.max(np.abs(f))
