@@ -6,6 +6,7 @@
 * a18 batched: M points with 2..6 observations each out of 200 projections, `iterations` damped steps
   (reference defaults: lambda 0.5, 100 iterations, triangulation_processor.py:12)
 * a19 batched: P views with ~100 observations each (reference pipeline: lambda 5, 300 iterations)
+* f3: both RANSAC initialisers, 100 000 points x 2 000 hypotheses
 * BA at the Ladybug and Final shapes (device-resident, reference mode), as sanity lines next to the
   Venice headline of bench.py.
 Times are wall-clock around the host-buffer entry points (uploads and downloads included) and, for the
@@ -102,6 +103,36 @@ def main():
                       'iterations': args.pnp_iterations, 'seconds': dt,
                       'observation_iterations_per_sec': int(rowptr[-1]) * args.pnp_iterations / dt,
                       'mean_abs_loc_move': float(np.mean(np.abs(loc - locs)))}))
+
+    # f3: RANSAC hypotheses in parallel (host buffers; the reference loops over hypotheses and, inside, over points)
+    n, H = 100000, 2000
+    k = np.array([[800.0, 0, 320], [0, 800, 240], [0, 0, 1]])
+    ang = 0.3
+    rot0 = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+    loc0 = np.array([[0.5], [-0.2], [0.1]])
+    Xh = np.vstack([rng.uniform(-2, 2, (2, n)), rng.uniform(4, 9, (1, n)), np.ones((1, n))])
+    pp = k @ np.hstack((rot0.T, rot0.T @ -loc0)) @ Xh
+    key = pp / pp[2]
+    bad = rng.random(n) < 0.3
+    key[0:2, bad] += rng.normal(0, 40, (2, int(bad.sum())))
+    samples = np.array([rng.choice(n, 6, replace=False) for _ in range(H)], dtype=np.int32)
+    keyT, XT = np.ascontiguousarray(key.T), np.ascontiguousarray(Xh.T)
+    dt, res = timed(lambda: eng.pnp_ransac(keyT, XT, k, samples, 1.0))
+    print(json.dumps({'workload': 'f3 PnP RANSAC (6-point DLT), all hypotheses at once', 'points': n, 'hypotheses': H,
+                      'seconds': dt, 'hypothesis_point_tests_per_sec': n * H / dt, 'inliers': res['count'],
+                      'true_inliers': int((~bad).sum())}))
+    left = rng.uniform(-1, 1, (n, 2))
+    Ftrue = np.array([[0.0, -0.3, 0.2], [0.3, 0.0, -1.0], [-0.2, 1.0, 0.0]]) @ rot0
+    ln = (Ftrue @ np.column_stack((left, np.ones(n))).T).T                 # epipolar lines in the right image
+    xr = rng.uniform(-1, 1, n)
+    yr = -(ln[:, 0] * xr + ln[:, 2]) / ln[:, 1]
+    pairs = np.column_stack((left, xr, yr))
+    pairs[bad, 3] += rng.normal(0, 0.2, int(bad.sum()))
+    samples8 = np.array([rng.choice(n, 8, replace=False) for _ in range(H)], dtype=np.int32)
+    dt, res = timed(lambda: eng.fund_ransac(pairs, samples8, 1e-6))
+    print(json.dumps({'workload': 'f3 fundamental-matrix RANSAC (8-point), all hypotheses at once', 'pairs': n,
+                      'hypotheses': H, 'seconds': dt, 'hypothesis_pair_tests_per_sec': n * H / dt,
+                      'inliers': res['count'], 'true_inliers': int((~bad).sum())}))
 
     if not args.skip_ba:
         import torch
