@@ -100,6 +100,12 @@ typedef struct {
   int32_t reserved0;
   double  lm_lambda_min;     /* adaptive mode clamps                                                */
   double  lm_lambda_max;
+  double  huber_delta;       /* > 0: Huber loss on every observation's residual norm, in the units of the */
+                             /* residual (normalised camera coordinates): rho(s) = s for s = |r|^2 <=      */
+                             /* delta^2, 2 delta sqrt(s) - delta^2 beyond.  Each linearisation re-weights   */
+                             /* the observation by rho'(s) (IRLS); costs reported are sum rho.  0 = plain   */
+                             /* least squares (the reference has no robust loss). */
+                             /* PCG solver only.                                                          */
 } sfmba_options;
 
 typedef struct {

@@ -32,7 +32,7 @@ __all__ = [
     'is_visible_literal', 'build_visibility', 'normalise_observations',
     'quaternion_jacobian', 'residual_jacobian', 'ba_cost', 'ba_solve', 'ba_normal_equations',
     'nonlinear_triangulate', 'triangulation_jacobian', 'nonlinear_pnp', 'pose_jacobian',
-    'pnp_dlt_six', 'pnp_ransac', 'fund_eight', 'fund_ransac', 'fund_normalize', 'fund_denormalize',
+    'huber_rho', 'huber_weight', 'pnp_dlt_six', 'pnp_ransac', 'fund_eight', 'fund_ransac', 'fund_normalize', 'fund_denormalize',
 ]
 
 
@@ -267,18 +267,42 @@ def _segment_sum(values: np.ndarray, seg: np.ndarray, nseg: int) -> np.ndarray:
     return out.reshape((nseg,) + values.shape[1:])
 
 
-def ba_normal_equations(cams, pts, obs_cam, obs_pt, obs_b, lam: float, dvdc_quirk: bool = True):
+def huber_rho(s: np.ndarray, delta: float) -> np.ndarray:
+    """Huber loss of the squared residual norm s = |r|^2: s inside delta, 2 delta sqrt(s) - delta^2 outside
+    (not in the reference: SURVEY.md section 8(f) row 4)."""
+    s = np.asarray(s, dtype=np.float64)
+    return np.where(s <= delta * delta, s, 2.0 * delta * np.sqrt(np.maximum(s, 1e-300)) - delta * delta)
+
+
+def huber_weight(s: np.ndarray, delta: float) -> np.ndarray:
+    """rho'(s): 1 inside delta, delta / sqrt(s) outside -- the IRLS weight of one observation."""
+    s = np.asarray(s, dtype=np.float64)
+    return np.where(s <= delta * delta, 1.0, delta / np.sqrt(np.maximum(s, 1e-300)))
+
+
+def ba_normal_equations(cams, pts, obs_cam, obs_pt, obs_b, lam: float, dvdc_quirk: bool = True,
+                        huber_delta: float = 0.0):
     """One linearisation: returns dict with r, Jp, Jx, A (V,7,7), e_p (V,7), D (N,3,3), Dinv,
-    e_x (N,3), W (m,7,3) following ba_processor.py:355-379 block by block."""
+    e_x (N,3), W (m,7,3) following ba_processor.py:355-379 block by block.  huber_delta > 0: every
+    observation's residual and Jacobian rows are scaled by sqrt(rho'(|r|^2)) first (iteratively
+    re-weighted least squares; r in the result stays unweighted, `cost` is sum rho)."""
     V, N = cams.shape[0], pts.shape[0]
     r, jp, jx = residual_jacobian(cams, pts, obs_cam, obs_pt, obs_b, dvdc_quirk)
+    r_raw = r
+    if huber_delta > 0:
+        sw = np.sqrt(huber_weight(np.sum(r * r, axis=1), huber_delta))
+        r = r * sw[:, None]
+        jp = jp * sw[:, None, None]
+        jx = jx * sw[:, None, None]
     D = _segment_sum(np.einsum('mai,maj->mij', jx, jx), obs_pt, N) + lam * np.eye(3)      # a13
     e_x = _segment_sum(np.einsum('mai,ma->mi', jx, r), obs_pt, N)
     A = _segment_sum(np.einsum('mai,maj->mij', jp, jp), obs_cam, V) + lam * np.eye(7)     # a14
     e_p = _segment_sum(np.einsum('mai,ma->mi', jp, r), obs_cam, V)
     W = np.einsum('mai,maj->mij', jp, jx)                                                  # B blocks
     Dinv = np.linalg.inv(D)
-    return dict(r=r, jp=jp, jx=jx, A=A, e_p=e_p, D=D, Dinv=Dinv, e_x=e_x, W=W)
+    s_raw = np.sum(r_raw * r_raw, axis=1)
+    cost = float(np.sum(huber_rho(s_raw, huber_delta))) if huber_delta > 0 else float(np.sum(s_raw))
+    return dict(r=r_raw, jp=jp, jx=jx, A=A, e_p=e_p, D=D, Dinv=Dinv, e_x=e_x, W=W, cost=cost)
 
 
 def _reduced_system_dense(ne, obs_cam, obs_pt, V):
@@ -326,7 +350,8 @@ def _reduced_system_sparse(ne, obs_cam, obs_pt, V, N):
 
 
 def ba_solve(cams, pts, obs_cam, obs_pt, obs_b, lam: float = 5.0, iterations: int = 3,
-             dvdc_quirk: bool = True, sparse: bool | None = None, return_costs: bool = True):
+             dvdc_quirk: bool = True, sparse: bool | None = None, return_costs: bool = True,
+             huber_delta: float = 0.0):
     """BaProcessor.__execute_bundle_adjustment in reference mode (ba_processor.py:297-406):
     fixed damping `lam`, `iterations` always-accepted steps, reduced system solved exactly,
     additive quaternion update followed by normalisation (383-392), dx back-substitution (405-406).
@@ -342,8 +367,8 @@ def ba_solve(cams, pts, obs_cam, obs_pt, obs_b, lam: float = 5.0, iterations: in
         sparse = obs_cam.shape[0] > 20000
     costs = []
     for _ in range(iterations):
-        ne = ba_normal_equations(cams, pts, obs_cam, obs_pt, obs_b, lam, dvdc_quirk)
-        costs.append(float(np.sum(np.square(ne['r']))))
+        ne = ba_normal_equations(cams, pts, obs_cam, obs_pt, obs_b, lam, dvdc_quirk, huber_delta)
+        costs.append(ne['cost'])
         if sparse:
             S, g, _ = _reduced_system_sparse(ne, obs_cam, obs_pt, V, N)
             dp = np.linalg.solve(S.toarray(), g)
@@ -358,7 +383,11 @@ def ba_solve(cams, pts, obs_cam, obs_pt, obs_b, lam: float = 5.0, iterations: in
         cams[:, 3:7] /= np.sqrt(np.sum(np.square(cams[:, 3:7]), axis=1, keepdims=True))
         pts += dx
     if return_costs:
-        costs.append(ba_cost(cams, pts, obs_cam, obs_pt, obs_b))
+        if huber_delta > 0:
+            rr, _, _ = residual_jacobian(cams, pts, obs_cam, obs_pt, obs_b, want_jac=False)
+            costs.append(float(np.sum(huber_rho(np.sum(rr * rr, axis=1), huber_delta))))
+        else:
+            costs.append(ba_cost(cams, pts, obs_cam, obs_pt, obs_b))
     return cams, pts, costs
 
 

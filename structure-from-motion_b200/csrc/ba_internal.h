@@ -124,6 +124,9 @@ struct BaDev {
   ChunkInfo* chunk_info;              // [chunk_bound]
   double2* rec_b;                     // [chunk_bound][CHUNK_CAP] normalised observation, lane-transposed
   uint32_t* rec_ix;                   // [chunk_bound][CHUNK_CAP]
+  double* rec_w;                      // [chunk_bound][CHUNK_CAP] Huber weight of each record at the linearisation
+                                      // point (robust solves only: written by k_linearize, read by the matvec)
+  double huber_delta;                 // 0 = plain least squares
   int32_t* seg_cam;                   // [chunk_bound][SEG_CAP]   camera of each segment (V = unused)
   uint16_t* seg_lane0;                // [chunk_bound][SEG_RUN_STRIDE] first lane of each segment (+ end)
   int32_t* camrow_ptr;                // [V+1]  CSR: camera -> segment rows

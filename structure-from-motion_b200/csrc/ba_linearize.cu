@@ -45,6 +45,7 @@ __host__ __device__ inline size_t pt_smem_bytes(const PtShape& s) {
   return b;
 }
 
+template <bool ROBUST>
 __global__ void __launch_bounds__(RUN_LANES) k_cost_tiles(BaDev d, PtShape sh) {
   extern __shared__ __align__(16) double smem[];
   double* Xa = smem;
@@ -86,7 +87,13 @@ __global__ void __launch_bounds__(RUN_LANES) k_cost_tiles(BaDev d, PtShape sh) {
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       if (!pr.ok) flags |= FLAG_DEPTH_ZERO;
       const double r0 = b.x - pr.u, r1 = b.y - pr.v;
-      cost += r0 * r0 + r1 * r1;
+      if (ROBUST) {
+        double rho;
+        huber_weight(r0 * r0 + r1 * r1, d.huber_delta, rho);
+        cost += rho;
+      } else {
+        cost += r0 * r0 + r1 * r1;
+      }
     }
     __syncthreads();
   }
@@ -195,8 +202,13 @@ void launch_cost_tiles(const BaDev& d, const TileShape& ts, double* out_cost_dev
   sh.seg_cap = ts.max_nseg;
   sh.k_cap = ts.max_k;
   const size_t smem = pt_smem_bytes(sh);
-  cudaFuncSetAttribute(k_cost_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (d.G > 0) k_cost_tiles<<<d.G, RUN_LANES, smem, st>>>(d, sh);
+  if (d.huber_delta > 0.0) {
+    cudaFuncSetAttribute(k_cost_tiles<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (d.G > 0) k_cost_tiles<true><<<d.G, RUN_LANES, smem, st>>>(d, sh);
+  } else {
+    cudaFuncSetAttribute(k_cost_tiles<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (d.G > 0) k_cost_tiles<false><<<d.G, RUN_LANES, smem, st>>>(d, sh);
+  }
   k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, d.G, d.sc, -1, out_cost_dev);
   lc.launches += 2;
 }

@@ -96,11 +96,13 @@ __global__ void __launch_bounds__(128) k_cam_iter(BaDev d, const double* __restr
 // BACKSUB: pass 1 with delta_p, then pts_j += v_j - D_j^-1 t_j        (ba_processor.py:405-406)
 struct MvShape {
   int slot_cap, pt_cap, seg_cap, k_cap, un_doubles, vn_doubles;
+  int ws_doubles;            // Huber weights of the chunk's records (robust solves), else 0
 };
 constexpr int CAMC = 26;   // doubles per staged camera row: R[9] C[3] E[9] w[3] wq pad
 
 __host__ __device__ inline size_t mv_smem_bytes(const MvShape& s) {
-  size_t dbl = (size_t)3 * s.pt_cap + 3 * s.pt_cap + 6 * s.pt_cap + s.vn_doubles + s.un_doubles + (size_t)CAMC * s.seg_cap;
+  size_t dbl = (size_t)3 * s.pt_cap + 3 * s.pt_cap + 6 * s.pt_cap + s.vn_doubles + s.un_doubles + (size_t)CAMC * s.seg_cap +
+               s.ws_doubles;
   size_t b = dbl * 8;
   b += (size_t)4 * (s.pt_cap + 4);                 // rowp
   b += (size_t)4 * s.k_cap * RUN_LANES;            // ixs
@@ -111,16 +113,16 @@ __host__ __device__ inline size_t mv_smem_bytes(const MvShape& s) {
 
 // One group (blockIdx-independent, so a persistent kernel can walk over groups).  Ends with a
 // block-wide barrier unless BACKSUB, so the shared memory can be restaged right away.
-template <bool BACKSUB>
+template <bool BACKSUB, bool ROBUST>
 __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, int dvdc_quirk, int grp, double* smem) {
   // The shape words and the lane id pass through an empty asm: when this body sits inside a persistent
   // kernel's group loop, the compiler would otherwise hoist every address derived from them out of the
   // loop and keep them live across it, which costs the inner loops their registers.
   int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap, seg_cap = sh.seg_cap, k_cap = sh.k_cap;
-  int un_doubles = sh.un_doubles, vn_doubles = sh.vn_doubles;
+  int un_doubles = sh.un_doubles, vn_doubles = sh.vn_doubles, ws_doubles = sh.ws_doubles;
   int tid = threadIdx.x;
   asm volatile("" : "+r"(pt_cap), "+r"(slot_cap), "+r"(seg_cap), "+r"(k_cap), "+r"(un_doubles), "+r"(vn_doubles),
-               "+r"(tid));
+               "+r"(tid), "+r"(ws_doubles));
   double* Xa = smem;                               // AoS [np][3]
   double* tacc = Xa + 3 * pt_cap;                  // SoA [3][pt_cap]
   double* Dn = tacc + 3 * pt_cap;                  // SoA [6][pt_cap]
@@ -128,7 +130,8 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
   double* un = Vn + vn_doubles;
   double* camc = un + un_doubles;
   ChunkStage cs;
-  cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * seg_cap);
+  cs.ws = ROBUST ? camc + (size_t)CAMC * seg_cap : nullptr;
+  cs.ixs = reinterpret_cast<uint32_t*>(camc + (size_t)CAMC * seg_cap + ws_doubles);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)k_cap * RUN_LANES);
   cs.rpos = cs.segc + (seg_cap + 3) / 4 * 4;
   cs.srun = reinterpret_cast<uint16_t*>(cs.rpos + (seg_cap + 3) / 4 * 4);
@@ -198,7 +201,7 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       wq = n2.x;
     }
     // two observations per trip: their dependency chains are independent and interleave
-    auto pass1 = [&](uint32_t ix, double t[3]) {
+    auto pass1 = [&](uint32_t ix, double wgt, double t[3]) {
       const int ptl = rec_ptl(ix);
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double g0 = E[0] * pr.d0 + E[1] * pr.d1 + E[2] * pr.d2 - w[0];
@@ -206,7 +209,8 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       const double g2 = E[6] * pr.d0 + E[7] * pr.d1 + E[8] * pr.d2 - w[2];
       const double a0 = pr.iw * (g0 - pr.u * g2);
       const double a1 = pr.iw * (g1 - pr.v * (g2 + wq));
-      const double q0 = pr.iw * a0, q1 = pr.iw * a1;
+      const double iww = ROBUST ? pr.iw * wgt : pr.iw;        // J_x^T W (J_p p)
+      const double q0 = iww * a0, q1 = iww * a1;
       const double q2 = -(pr.u * q0 + pr.v * q1);
       t[0] = R[0] * q0 + R[1] * q1 + R[2] * q2;
       t[1] = R[3] * q0 + R[4] * q1 + R[5] * q2;
@@ -219,8 +223,10 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       const bool vb = ixb != REC_INVALID;
       if (!vb) ixb = ixa;
       double ta[3], tb[3];
-      pass1(ixa, ta);
-      pass1(ixb, tb);
+      const double wa = ROBUST ? cs.ws[k * RUN_LANES + tid] : 1.0;
+      const double wb = ROBUST && vb ? cs.ws[(k + 1) * RUN_LANES + tid] : 1.0;
+      pass1(ixa, wa, ta);
+      pass1(ixb, wb, tb);
       double* sa = un + rec_pos(ixa);
       sa[0] = ta[0];
       sa[slot_cap] = ta[1];
@@ -319,8 +325,10 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       uint32_t ixb = (k + 1 < K) ? cs.ixs[(k + 1) * RUN_LANES + tid] : REC_INVALID;
       const bool vb = ixb != REC_INVALID;
       if (!vb) ixb = ixa;
-      pass2(ixa, 1.0);
-      pass2(ixb, vb ? 1.0 : 0.0);
+      const double wa = ROBUST ? cs.ws[k * RUN_LANES + tid] : 1.0;
+      const double wb = ROBUST && vb ? cs.ws[(k + 1) * RUN_LANES + tid] : 1.0;
+      pass2(ixa, wa);
+      pass2(ixb, vb ? wb : 0.0);
     }
     if (any) {
       double* dst = un + tid * MV_STRIDE;
@@ -344,11 +352,11 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
   }
 }
 
-template <bool BACKSUB>
+template <bool BACKSUB, bool ROBUST>
 __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, int dvdc_quirk) {
   extern __shared__ __align__(16) double smem[];
   pdl_trigger();                                   // the next kernel may queue up behind this one's last wave
-  matvec_group<BACKSUB>(d, sh, dvdc_quirk, blockIdx.x, smem);
+  matvec_group<BACKSUB, ROBUST>(d, sh, dvdc_quirk, blockIdx.x, smem);
 }
 
 // y_i from the camera's segment rows, one warp per camera: lane = (row slot, component), two row slots
@@ -665,7 +673,7 @@ __global__ void k_lm_decide(BaDev d, double lam_min, double lam_max) {
 }
 
 
-static MvShape matvec_shape(const TileShape& ts, bool backsub) {
+static MvShape matvec_shape(const TileShape& ts, bool backsub, bool robust) {
   MvShape sh;
   sh.slot_cap = ((ts.max_chunk_len + 15) & ~15) + 1;
   sh.pt_cap = (ts.max_group_pts + 1) & ~1;
@@ -674,6 +682,7 @@ static MvShape matvec_shape(const TileShape& ts, bool backsub) {
   const int a = 3 * sh.slot_cap, bb = RUN_LANES * MV_STRIDE;
   sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
   sh.vn_doubles = backsub ? 3 * sh.pt_cap : 0;
+  sh.ws_doubles = robust ? sh.k_cap * RUN_LANES : 0;
   return sh;
 }
 
@@ -692,25 +701,25 @@ void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc) {
   if (d.G <= 0) return;
-  const MvShape sh = matvec_shape(ts, backsub);
+  const bool robust = d.huber_delta > 0.0;
+  const MvShape sh = matvec_shape(ts, backsub, robust);
   const size_t smem = mv_smem_bytes(sh);
   // the opt-in shared memory size is sticky per function and device: raise it only when needed
-  static size_t granted[2][64] = {};
+  static size_t granted[4][64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
-  size_t& g = granted[backsub ? 1 : 0][dev & 63];
+  size_t& g = granted[(backsub ? 1 : 0) + (robust ? 2 : 0)][dev & 63];
+  auto go = [&](auto kernel) {
+    if (smem > g) {
+      cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      g = smem;
+    }
+    launch_pdl(kernel, dim3(d.G), dim3(RUN_LANES), smem, st, d, sh, dvdc_quirk ? 1 : 0);
+  };
   if (backsub) {
-    if (smem > g) {
-      cudaFuncSetAttribute(k_matvec<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      g = smem;
-    }
-    launch_pdl(k_matvec<true>, dim3(d.G), dim3(RUN_LANES), smem, st, d, sh, dvdc_quirk ? 1 : 0);
+    if (robust) go(k_matvec<true, true>); else go(k_matvec<true, false>);
   } else {
-    if (smem > g) {
-      cudaFuncSetAttribute(k_matvec<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      g = smem;
-    }
-    launch_pdl(k_matvec<false>, dim3(d.G), dim3(RUN_LANES), smem, st, d, sh, dvdc_quirk ? 1 : 0);
+    if (robust) go(k_matvec<false, true>); else go(k_matvec<false, false>);
   }
   lc.launches++;
 }

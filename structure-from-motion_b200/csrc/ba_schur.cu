@@ -37,6 +37,8 @@ __host__ __device__ inline size_t gram_smem_bytes(const GramShape& s) {
 
 // Phase A (K2a, ba_processor.py:355-363): per point D_j = sum J_x^T J_x + lambda I, D_j^-1, v_j = D_j^-1 e_x
 // and the cost; phase B: the camera-side Gram sums.  One launch linearises the whole problem.
+// ROBUST: every observation enters with its Huber weight w = rho'(|r|^2) (J^T W J, J^T W r); the cost is sum rho
+template <bool ROBUST>
 __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape sh, int dvdc_quirk) {
   extern __shared__ __align__(16) double smem[];
   const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
@@ -86,21 +88,29 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       if (!pr.ok) flags |= FLAG_DEPTH_ZERO;
       const double r0 = b.x - pr.u, r1 = b.y - pr.v;
-      cost += r0 * r0 + r1 * r1;
       const double x0 = (R[0] - pr.u * R[2]) * pr.iw, x1 = (R[3] - pr.u * R[5]) * pr.iw,
                    x2 = (R[6] - pr.u * R[8]) * pr.iw;
       const double y0 = (R[1] - pr.v * R[2]) * pr.iw, y1 = (R[4] - pr.v * R[5]) * pr.iw,
                    y2 = (R[7] - pr.v * R[8]) * pr.iw;
+      double wx0 = x0, wx1 = x1, wx2 = x2, wy0 = y0, wy1 = y1, wy2 = y2;
+      if (ROBUST) {
+        double rho;
+        const double w = huber_weight(r0 * r0 + r1 * r1, d.huber_delta, rho);
+        cost += rho;
+        wx0 *= w; wx1 *= w; wx2 *= w; wy0 *= w; wy1 *= w; wy2 *= w;
+      } else {
+        cost += r0 * r0 + r1 * r1;
+      }
       double* s = slots + rec_pos(ix);
-      s[0 * slot_cap] = x0 * x0 + y0 * y0;
-      s[1 * slot_cap] = x0 * x1 + y0 * y1;
-      s[2 * slot_cap] = x0 * x2 + y0 * y2;
-      s[3 * slot_cap] = x1 * x1 + y1 * y1;
-      s[4 * slot_cap] = x1 * x2 + y1 * y2;
-      s[5 * slot_cap] = x2 * x2 + y2 * y2;
-      s[6 * slot_cap] = x0 * r0 + y0 * r1;
-      s[7 * slot_cap] = x1 * r0 + y1 * r1;
-      s[8 * slot_cap] = x2 * r0 + y2 * r1;
+      s[0 * slot_cap] = wx0 * x0 + wy0 * y0;
+      s[1 * slot_cap] = wx0 * x1 + wy0 * y1;
+      s[2 * slot_cap] = wx0 * x2 + wy0 * y2;
+      s[3 * slot_cap] = wx1 * x1 + wy1 * y1;
+      s[4 * slot_cap] = wx1 * x2 + wy1 * y2;
+      s[5 * slot_cap] = wx2 * x2 + wy2 * y2;
+      s[6 * slot_cap] = wx0 * r0 + wy0 * r1;
+      s[7 * slot_cap] = wx1 * r0 + wy1 * r1;
+      s[8 * slot_cap] = wx2 * r0 + wy2 * r1;
     }
     __syncthreads();
     // one work item per (point, component): the slots of a point are summed in observation order
@@ -242,11 +252,25 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
       double t0[3], t1[3];
       sym3_mul(Dinv, jx, t0);
       sym3_mul(Dinv, jx + 3, t1);
-      const double yuu = jx[0] * t0[0] + jx[1] * t0[1] + jx[2] * t0[2];
-      const double yuv = jx[0] * t1[0] + jx[1] * t1[1] + jx[2] * t1[2];
-      const double yvv = jx[3] * t1[0] + jx[4] * t1[1] + jx[5] * t1[2];
+      double yuu = jx[0] * t0[0] + jx[1] * t0[1] + jx[2] * t0[2];
+      double yuv = jx[0] * t1[0] + jx[1] * t1[1] + jx[2] * t1[2];
+      double yvv = jx[3] * t1[0] + jx[4] * t1[1] + jx[5] * t1[2];
       const double rho0 = r0 - (jx[0] * vv[0] + jx[1] * vv[1] + jx[2] * vv[2]);
       const double rho1 = r1 - (jx[3] * vv[0] + jx[4] * vv[1] + jx[5] * vv[2]);
+      // weighted sums: the left factor of every product below is w J_p, Y carries the second w of J_p^T (w Y w) J_p
+      double jw[14];
+#pragma unroll
+      for (int a = 0; a < 14; ++a) jw[a] = jp[a];
+      if (ROBUST) {
+        double rho_unused;
+        const double w = huber_weight(r0 * r0 + r1 * r1, d.huber_delta, rho_unused);
+        d.rec_w[(size_t)c * CHUNK_CAP + k * RUN_LANES + tid] = w;
+#pragma unroll
+        for (int a = 0; a < 14; ++a) jw[a] *= w;
+        yuu *= w;
+        yuv *= w;
+        yvv *= w;
+      }
       double tu[7], tv[7];
 #pragma unroll
       for (int a = 0; a < 7; ++a) {
@@ -260,23 +284,23 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
         for (int a = 0; a < 7; ++a) {
 #pragma unroll
           for (int bcol = a; bcol < 7; ++bcol, ++e) {
-            acc[e] = fma(jp[a], jp[bcol], acc[e]);
-            acc[28 + e] = fma(jp[a], tu[bcol], acc[28 + e]);
+            acc[e] = fma(jw[a], jp[bcol], acc[e]);
+            acc[28 + e] = fma(jw[a], tu[bcol], acc[28 + e]);
           }
         }
 #pragma unroll
-        for (int a = 0; a < 7; ++a) acc[56 + a] = fma(jp[a], rho0, acc[56 + a]);
+        for (int a = 0; a < 7; ++a) acc[56 + a] = fma(jw[a], rho0, acc[56 + a]);
         e = 0;
 #pragma unroll
         for (int a = 0; a < 7; ++a) {
 #pragma unroll
           for (int bcol = a; bcol < 7; ++bcol, ++e) {
-            acc[e] = fma(jp[7 + a], jp[7 + bcol], acc[e]);
-            acc[28 + e] = fma(jp[7 + a], tv[bcol], acc[28 + e]);
+            acc[e] = fma(jw[7 + a], jp[7 + bcol], acc[e]);
+            acc[28 + e] = fma(jw[7 + a], tv[bcol], acc[28 + e]);
           }
         }
 #pragma unroll
-        for (int a = 0; a < 7; ++a) acc[56 + a] = fma(jp[7 + a], rho1, acc[56 + a]);
+        for (int a = 0; a < 7; ++a) acc[56 + a] = fma(jw[7 + a], rho1, acc[56 + a]);
       }
     }
     if (live) {
@@ -378,9 +402,14 @@ void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int 
   const int a = 9 * sh.slot_cap, bb = RUN_LANES * RP_STRIDE;
   sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
   const size_t smem = gram_smem_bytes(sh);
-  cudaFuncSetAttribute(k_linearize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (d.G > 0) {
-    k_linearize<<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
+    if (d.huber_delta > 0.0) {
+      cudaFuncSetAttribute(k_linearize<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      k_linearize<true><<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
+    } else {
+      cudaFuncSetAttribute(k_linearize<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      k_linearize<false><<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
+    }
     lc.launches++;
   }
   launch_sum_cost(d, cost_slot, st, lc);

@@ -60,7 +60,7 @@ namespace {
 enum Slot {
   S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_CAM_ACC, S_ABLK, S_MINV,
   S_CAMIT, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
-  S_CHUNK_INFO, S_REC_B, S_REC_IX, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
+  S_CHUNK_INFO, S_REC_B, S_REC_IX, S_REC_W, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
 };
 
@@ -141,6 +141,7 @@ static int sfm_setup_chunks(sfmba_ctx* ctx, int nchunks, BaDev* io) {
   CARVE(S_CHUNK_INFO, nc, chunk_info);
   CARVE(S_REC_B, nc * CHUNK_CAP, rec_b);
   CARVE(S_REC_IX, nc * CHUNK_CAP, rec_ix);
+  if (d.huber_delta > 0.0) CARVE(S_REC_W, nc * CHUNK_CAP, rec_w);
   CARVE(S_SEG_CAM, nc * SEG_CAP, seg_cam);
   CARVE(S_SEG_LANE0, nc * SEG_RUN_STRIDE, seg_lane0);
   CARVE(S_CAMROW_IDX, nc * SEG_CAP, camrow_idx);
@@ -219,9 +220,13 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if (opt.solver != SFMBA_SOLVER_PCG && opt.solver != SFMBA_SOLVER_DENSE_CHOLESKY)
     return sfm_set_error(ctx, SFMBA_ERR_UNSUPPORTED, "unknown solver");
   const bool dense = opt.solver == SFMBA_SOLVER_DENSE_CHOLESKY;
+  if (!(opt.huber_delta >= 0.0)) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "huber_delta < 0");
+  if (dense && opt.huber_delta > 0.0)
+    return sfm_set_error(ctx, SFMBA_ERR_UNSUPPORTED, "the Huber loss is implemented for the PCG solver only");
   BaDev d;
   int rc = sfm_setup_problem(ctx, pr, true, &d);
   if (rc != SFMBA_OK) return rc;
+  d.huber_delta = opt.huber_delta;
   const int n7 = 7 * d.V;
   DenseWork dw;
   memset(&dw, 0, sizeof(dw));

@@ -111,6 +111,17 @@ __device__ __forceinline__ bool eval_obs(const double* __restrict__ ct, const do
   return pw != 0.0;
 }
 
+// Huber loss of the squared residual norm s: returns the IRLS weight rho'(s) and rho(s) itself.
+__device__ __forceinline__ double huber_weight(double s, double delta, double& rho) {
+  if (s <= delta * delta) {
+    rho = s;
+    return 1.0;
+  }
+  const double rs = sqrt(s);
+  rho = 2.0 * delta * rs - delta * delta;
+  return delta / rs;
+}
+
 // b = (K^-1 [u,v,1]^T) / z, ba_processor.py:339-342.  kinv NULL: (u,v) already normalised.
 __device__ __forceinline__ void normalise_obs(const double* __restrict__ kinv, float u, float v, double b[2]) {
   if (kinv == nullptr) {

@@ -77,6 +77,7 @@ struct ChunkStage {
   int32_t* rpos;     // [seg_cap rounded to 4] row of each segment in the camera-sorted row arrays, or nullptr
   uint16_t* srun;    // [SEG_RUN_STRIDE] first lane of each segment (+ end), or nullptr
   double2* bs;       // [k_cap * RUN_LANES] normalised observations, or nullptr
+  double* ws = nullptr;   // [k_cap * RUN_LANES] Huber weights (robust matvec), or nullptr
 };
 
 __device__ __forceinline__ void stage_chunk_async(const BaDev& d, int c, const ChunkInfo& ci, const ChunkStage& cs) {
@@ -96,6 +97,10 @@ __device__ __forceinline__ void stage_chunk_async(const BaDev& d, int c, const C
   if (cs.bs) {
     const double2* b = d.rec_b + (size_t)c * CHUNK_CAP;
     for (int i = threadIdx.x; i < K * RUN_LANES; i += blockDim.x) cp_async16(cs.bs + i, b + i);
+  }
+  if (cs.ws) {
+    const double* w = d.rec_w + (size_t)c * CHUNK_CAP;
+    for (int i = threadIdx.x; i < K * (RUN_LANES / 2); i += blockDim.x) cp_async16(cs.ws + 2 * i, w + 2 * i);
   }
 }
 
