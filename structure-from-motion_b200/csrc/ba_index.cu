@@ -127,7 +127,7 @@ struct BuildSmem {
 };
 
 // one CTA per group: sort each chunk by camera, cut segments into runs of K, emit records and tables
-__global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits) {
+__global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits, int g0) {
   using Sort = cub::BlockRadixSort<uint32_t, RUN_LANES, CHUNK_K_MAX>;
   using Scan = cub::BlockScan<int, RUN_LANES>;
   __shared__ union {
@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
     typename Scan::TempStorage scan;
   } tmp;
   __shared__ BuildSmem s;
-  const int g = blockIdx.x;
+  const int g = g0 + blockIdx.x;
   const int pt0 = d.grp_pt[g], pt1 = d.grp_pt[g + 1];
   const int c0 = d.grp_chunk[g], c1 = d.grp_chunk[g + 1];
   const int o_begin = d.rowptr[pt0], o_end = d.rowptr[pt1];
@@ -315,12 +315,15 @@ void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t tem
 }
 
 // phase 2: records, tables and the camera CSR (chunk arrays allocated for `nchunks`)
-void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_bytes, int32_t* sort_keys_out,
-                        int32_t* iota, cudaStream_t st, LaunchCounter& lc) {
-  if (d.G > 0) {
-    k_chunk_build<<<d.G, RUN_LANES, 0, st>>>(d, bits_for(d.V > 0 ? d.V - 1 : 0));
+void launch_chunk_build(const BaDev& d, int g0, int g1, cudaStream_t st, LaunchCounter& lc) {
+  if (g1 > g0) {
+    k_chunk_build<<<g1 - g0, RUN_LANES, 0, st>>>(d, bits_for(d.V > 0 ? d.V - 1 : 0), g0);
     lc.launches++;
   }
+}
+
+void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_bytes, int32_t* sort_keys_out,
+                        int32_t* iota, cudaStream_t st, LaunchCounter& lc) {
   const int n = nchunks * SEG_CAP;
   if (n > 0) {
     k_iota<<<(n + 255) / 256, 256, 0, st>>>(iota, n);

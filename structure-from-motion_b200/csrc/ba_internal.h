@@ -177,7 +177,9 @@ size_t index_temp_bytes(int G, int chunk_bound, int V);
 // phase 1: groups + chunk counts + shape statistics in sc (host reads them back once)
 void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, cudaStream_t st,
                         LaunchCounter& lc);
-// phase 2: records, run / segment tables, camera -> segment-row CSR
+// phase 2a: records and run / segment tables of the groups [g0, g1) (needs obs_uv of their observations only)
+void launch_chunk_build(const BaDev& d, int g0, int g1, cudaStream_t st, LaunchCounter& lc);
+// phase 2b: camera -> segment-row CSR over all chunks
 void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_bytes, int32_t* sort_keys_out,
                         int32_t* iota, cudaStream_t st, LaunchCounter& lc);
 
@@ -193,7 +195,7 @@ void launch_k1(const BaDev& d, bool dvdc_quirk, float* out_r, float* out_jp, flo
 // ---- camera-side reduction (ba_schur.cu) --------------------------------------------------------
 // fused linearisation: point blocks (D^-1, v, cost -> sc->costs[cost_slot]) + camera-side Gram rows
 void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int cost_slot, cudaStream_t st,
-                      LaunchCounter& lc);
+                      LaunchCounter& lc, int g0 = 0, int g1 = -1, bool sum_cost = true);
 void launch_sum_cost(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc);
 void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 // several GPUs with peer windows: segment rows -> every rank's window -> cam_acc and cost summed over ranks

@@ -39,7 +39,7 @@ __host__ __device__ inline size_t gram_smem_bytes(const GramShape& s) {
 // and the cost; phase B: the camera-side Gram sums.  One launch linearises the whole problem.
 // ROBUST: every observation enters with its Huber weight w = rho'(|r|^2) (J^T W J, J^T W r); the cost is sum rho
 template <bool ROBUST>
-__global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape sh, int dvdc_quirk) {
+__global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape sh, int dvdc_quirk, int g0) {
   extern __shared__ __align__(16) double smem[];
   const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
   double* Xa = smem;
@@ -55,7 +55,8 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
   cs.srun = reinterpret_cast<uint16_t*>(cs.rpos + (sh.seg_cap + 3) / 4 * 4);
   int32_t* rowp = reinterpret_cast<int32_t*>(cs.srun + SEG_RUN_STRIDE + 6);
   const int tid = threadIdx.x;
-  const GroupMeta gm = d.grp_meta[blockIdx.x];
+  const int grp = g0 + blockIdx.x;
+  const GroupMeta gm = d.grp_meta[grp];
   const int np = gm.np, pt0 = gm.pt0, c0 = gm.c0, c1 = gm.c0 + gm.nc;
   {
     const double* src = d.pts + 3 * (size_t)pt0;
@@ -164,7 +165,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
     }
   }
   cost = block_sum(cost, red);     // (contains the barrier that publishes Dv)
-  if (tid == 0) d.grp_cost[blockIdx.x] = cost;
+  if (tid == 0) d.grp_cost[grp] = cost;
   if (flags) atomicOr(&d.sc->flags, flags);
   // ---- phase B: camera-side Gram sums
   for (int c = c0; c < c1; ++c) {
@@ -392,8 +393,10 @@ __global__ void k_cam_blocks(BaDev d) {
   for (int a = 0; a < 7; ++a) d.gvec[7 * cam + a] = acc[56 + a];
 }
 
+// Linearises the groups [g0, g1) (g1 < 0: all).  The host-buffer solve calls it once per upload range, so the
+// first linearisation overlaps the arrival of the later points; sum_cost closes the last range.
 void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int cost_slot, cudaStream_t st,
-                      LaunchCounter& lc) {
+                      LaunchCounter& lc, int g0, int g1, bool sum_cost) {
   GramShape sh;
   sh.pt_cap = (ts.max_group_pts + 1) & ~1;
   sh.seg_cap = ts.max_nseg;
@@ -402,17 +405,21 @@ void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int 
   const int a = 9 * sh.slot_cap, bb = RUN_LANES * RP_STRIDE;
   sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
   const size_t smem = gram_smem_bytes(sh);
-  if (d.G > 0) {
+  if (g1 < 0) {
+    g0 = 0;
+    g1 = d.G;
+  }
+  if (g1 > g0) {
     if (d.huber_delta > 0.0) {
       cudaFuncSetAttribute(k_linearize<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      k_linearize<true><<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
+      k_linearize<true><<<g1 - g0, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0, g0);
     } else {
       cudaFuncSetAttribute(k_linearize<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      k_linearize<false><<<d.G, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0);
+      k_linearize<false><<<g1 - g0, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0, g0);
     }
     lc.launches++;
   }
-  launch_sum_cost(d, cost_slot, st, lc);
+  if (sum_cost) launch_sum_cost(d, cost_slot, st, lc);
 }
 
 // Several GPUs with peer windows: this rank's sums (and its cost, in the trailing entry) go straight into

@@ -300,18 +300,38 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_TEMP, temp_bytes, &temp), "cudaMalloc(temp)")) != 0) return rc;
   if ((rc = carve(ctx, S_SORT_KEYS, (size_t)d.chunk_bound * SEG_CAP, &sort_keys)) != 0) return rc;
   if ((rc = carve(ctx, S_IOTA, (size_t)d.chunk_bound * SEG_CAP, &iota)) != 0) return rc;
-  if (io) cudaStreamWaitEvent(st, io->ev_obs, 0);
   d.rowpos = iota;   // the identity permutation fed to the sort; overwritten with the inverse permutation after it
+  const bool ranged = io && io->num_ranges > 1 && io->range_grp[io->num_ranges] == d.G;
+  if (ranged) {
+    // records of a range are built as soon as its observations have arrived
+    for (int r = 0; r < io->num_ranges; ++r) {
+      cudaStreamWaitEvent(st, io->ev_range_obs[r], 0);
+      launch_chunk_build(d, io->range_grp[r], io->range_grp[r + 1], st, lc);
+    }
+  } else {
+    if (io) cudaStreamWaitEvent(st, io->ev_obs, 0);
+    launch_chunk_build(d, 0, d.G, st, lc);
+  }
   launch_index_build(d, nchunks, temp, temp_bytes, sort_keys, iota, st, lc);
   pt.end(PH_INDEX, t0);
-  if (io) cudaStreamWaitEvent(st, io->ev_params, 0);
+  if (io) cudaStreamWaitEvent(st, io->ev_params, 0);      // ranged: the cameras; otherwise cameras and points
+  if (ranged && adaptive) {
+    for (int r = 0; r < io->num_ranges; ++r) cudaStreamWaitEvent(st, io->ev_range_pts[r], 0);   // (the backup reads every point)
+  }
 
   int cost_slot = 0;
   for (int it = 0; it < opt.iterations; ++it) {
     t0 = pt.begin();
     if (adaptive) launch_lm_backup(d, st, lc);
     launch_cam_prepare(d, st, lc);
-    {
+    if (it == 0 && ranged) {
+      // first linearisation of a host-buffer solve: range by range, behind the upload of the points
+      for (int r = 0; r < io->num_ranges; ++r) {
+        cudaStreamWaitEvent(st, io->ev_range_pts[r], 0);
+        launch_linearize(d, ts, quirk, cost_slot, st, lc, io->range_grp[r], io->range_grp[r + 1],
+                         r + 1 == io->num_ranges);
+      }
+    } else {
       cudaEvent_t kb = pt.kbegin();
       launch_linearize(d, ts, quirk, cost_slot, st, lc);
       pt.kend("linearize", kb);

@@ -1,5 +1,6 @@
 // extern "C" surface of libsfmba (include/sfmba.h).  No exceptions cross this file.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -144,6 +145,10 @@ int sfmba_destroy(sfmba_ctx* ctx) {
     cudaEventDestroy(ctx->io.ev_obs);
     cudaEventDestroy(ctx->io.ev_params);
     cudaEventDestroy(ctx->io.ev_final);
+    for (int r = 0; r < SolveIo::MAX_RANGES; ++r) {
+      if (ctx->io.ev_range_obs[r]) cudaEventDestroy(ctx->io.ev_range_obs[r]);
+      if (ctx->io.ev_range_pts[r]) cudaEventDestroy(ctx->io.ev_range_pts[r]);
+    }
   }
   delete ctx;
   return SFMBA_OK;
@@ -176,16 +181,83 @@ int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   float* d_uv;
   int32_t *d_cam, *d_row;
   double *d_kinv = nullptr, *d_cams, *d_pts;
-  // uploads in the order of first use: index inputs, observations, parameters
+  // uploads in the order of first use: index inputs, cameras, observations, points.  Large problems are cut into
+  // ranges of whole groups (the solver's own partition: group g starts at the first point j with
+  // pt_rowptr[j] + 2 j >= 1024 g, ba_index.cu) so that the record build and the first linearisation of a range run
+  // while the later ranges are still on the bus.
   if ((rc = stage_in(ctx, 3, pr->pt_rowptr, N + 1, &d_row, io.copy))) return rc;
   if ((rc = stage_in(ctx, 1, pr->obs_cam, m, &d_cam, io.copy))) return rc;
   cudaEventRecord(io.ev_index, io.copy);
-  if ((rc = stage_in(ctx, 0, pr->obs_uv, 2 * m, &d_uv, io.copy))) return rc;
   if (pr->cam_kinv && (rc = stage_in(ctx, 4, pr->cam_kinv, 9 * V, &d_kinv, io.copy))) return rc;
-  cudaEventRecord(io.ev_obs, io.copy);
   if ((rc = stage_in(ctx, 5, pr->cams, 7 * V, &d_cams, io.copy))) return rc;
-  if ((rc = stage_in(ctx, 6, pr->pts, 3 * N, &d_pts, io.copy))) return rc;
-  cudaEventRecord(io.ev_params, io.copy);
+  io.num_ranges = 0;
+  const long long G = ((long long)m + 2ll * (long long)N + 1023) / 1024;
+  // (measured at the Venice shape: 5.87 ms per call in one piece, 5.64 ms in two ranges, 5.67 in four, 5.78 in eight:
+  // profiles/prof_e2e.py)
+  int R = (m >= ((size_t)1 << 20) && pr->pt_rowptr && pr->obs_uv && pr->pts) ? 2 : 1;
+  if (G < 64) R = 1;
+  if (const char* ev = getenv("SFMBA_UPLOAD_RANGES")) R = std::max(1, std::min(atoi(ev), (int)SolveIo::MAX_RANGES));
+  if (R > 1) {
+    // range boundaries in groups, points and observations; clamped and monotone whatever pt_rowptr holds
+    size_t rp[SolveIo::MAX_RANGES + 1], ro[SolveIo::MAX_RANGES + 1];
+    for (int r = 0; r <= R; ++r) {
+      const long long g = r == R ? G : G * r / R;
+      io.range_grp[r] = (int)g;
+      size_t lo = 0, hi = N;
+      if (r == R) {
+        lo = N;
+      } else {
+        const long long target = g * 1024;
+        while (lo < hi) {
+          const size_t mid = (lo + hi) >> 1;
+          if ((long long)pr->pt_rowptr[mid] + 2ll * (long long)mid < target) lo = mid + 1; else hi = mid;
+        }
+      }
+      rp[r] = lo;
+      long long o = r == R ? (long long)m : (long long)pr->pt_rowptr[lo];
+      if (o < 0) o = 0;
+      if (o > (long long)m) o = (long long)m;
+      ro[r] = (size_t)o;
+      if (r > 0 && ro[r] < ro[r - 1]) ro[r] = ro[r - 1];
+      if (r > 0 && rp[r] < rp[r - 1]) rp[r] = rp[r - 1];
+    }
+    ro[0] = 0;
+    rp[0] = 0;
+    for (int r = 0; r < R; ++r) {
+      if (!io.ev_range_obs[r]) {
+        cudaEventCreateWithFlags(&io.ev_range_obs[r], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&io.ev_range_pts[r], cudaEventDisableTiming);
+      }
+    }
+    cudaError_t e = ctx->host_stage[0].reserve(std::max<size_t>(16, 2 * m * sizeof(float)));
+    if (e == cudaSuccess) e = ctx->host_stage[6].reserve(std::max<size_t>(16, 3 * N * sizeof(double)));
+    if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(stage)");
+    d_uv = ctx->host_stage[0].as<float>();
+    d_pts = ctx->host_stage[6].as<double>();
+    cudaEventRecord(io.ev_params, io.copy);                   // ranged: "cameras resident"
+    for (int r = 0; r < R; ++r) {
+      const size_t o0 = ro[r], cnt = ro[r + 1] - ro[r];
+      if (cnt) {
+        cudaMemcpyAsync(d_uv + o0, pr->obs_uv + o0, cnt * sizeof(float), cudaMemcpyHostToDevice, io.copy);
+        cudaMemcpyAsync(d_uv + m + o0, pr->obs_uv + m + o0, cnt * sizeof(float), cudaMemcpyHostToDevice, io.copy);
+      }
+      cudaEventRecord(io.ev_range_obs[r], io.copy);
+    }
+    cudaEventRecord(io.ev_obs, io.copy);
+    for (int r = 0; r < R; ++r) {
+      const size_t p0 = rp[r], cnt = rp[r + 1] - rp[r];
+      if (cnt)
+        cudaMemcpyAsync(d_pts + 3 * p0, pr->pts + 3 * p0, 3 * cnt * sizeof(double), cudaMemcpyHostToDevice, io.copy);
+      cudaEventRecord(io.ev_range_pts[r], io.copy);
+    }
+    if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "ranged upload")) != 0) return rc;
+    io.num_ranges = R;
+  } else {
+    if ((rc = stage_in(ctx, 0, pr->obs_uv, 2 * m, &d_uv, io.copy))) return rc;
+    cudaEventRecord(io.ev_obs, io.copy);
+    if ((rc = stage_in(ctx, 6, pr->pts, 3 * N, &d_pts, io.copy))) return rc;
+    cudaEventRecord(io.ev_params, io.copy);
+  }
   dp.obs_uv = d_uv;
   dp.obs_cam = d_cam;
   dp.obs_pt = nullptr;   // the solve derives the point of an observation from pt_rowptr

@@ -35,6 +35,13 @@ struct SolveIo {
   cudaEvent_t ev_final = nullptr;    // recorded by the solve when cams / pts are final
   double* host_cams = nullptr;
   double* host_pts = nullptr;
+  // upload ranges of the host-buffer solve: range r = groups [range_grp[r], range_grp[r+1]); ev_range_obs[r] /
+  // ev_range_pts[r] fire when the observations / the points of the range are resident
+  static constexpr int MAX_RANGES = 8;
+  int num_ranges = 0;
+  int range_grp[MAX_RANGES + 1] = {};
+  cudaEvent_t ev_range_obs[MAX_RANGES] = {};
+  cudaEvent_t ev_range_pts[MAX_RANGES] = {};
 };
 
 struct sfmba_ctx {
