@@ -183,12 +183,18 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
     }
     __syncthreads();
   };
+  // R and C of the lane's camera stay in registers from pass 1 to pass 2 when the group is a single chunk
+  // (the lane owns the same run in both passes): the middle phases need few registers
+  double R[9], C[3];
+#pragma unroll
+  for (int e = 0; e < 9; ++e) R[e] = 0.0;
+  C[0] = C[1] = C[2] = 0.0;
   // ---- pass 1: t_j = sum_o J_x^T (J_p p_cam)
   for (int c = c0; c < c1; ++c) {
     if (c > c0) ci = d.chunk_info[c];
     stage(c, true);
     const int K = ci.K;
-    double R[9], C[3], E[9], w[3], wq = 0.0;
+    double E[9], w[3], wq = 0.0;
     const uint32_t ix_first = cs.ixs[tid];
     if (ix_first != REC_INVALID) {                         // one camera per lane
       const double2* row = reinterpret_cast<const double2*>(camc + (size_t)CAMC * rec_seg(ix_first));
@@ -288,13 +294,12 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       stage(c, false);
     }
     const int K = ci.K;
-    double R[9], C[3];
     double acc[MV_ACC];
 #pragma unroll
     for (int e = 0; e < MV_ACC; ++e) acc[e] = 0.0;
     const uint32_t ix_first = cs.ixs[tid];
     const bool any = ix_first != REC_INVALID;
-    if (any) {
+    if (any && gm.nc > 1) {
       const double2* row = reinterpret_cast<const double2*>(camc + (size_t)CAMC * rec_seg(ix_first));
       const double2 a = row[0], b = row[1], cc = row[2], e = row[3], f = row[4], g = row[5];
       R[0] = a.x; R[1] = a.y; R[2] = b.x; R[3] = b.y; R[4] = cc.x; R[5] = cc.y; R[6] = e.x; R[7] = e.y; R[8] = f.x;
