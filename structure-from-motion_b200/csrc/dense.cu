@@ -24,6 +24,7 @@
 #include "tile.cuh"
 
 #include <algorithm>
+#include <vector>
 
 namespace sfmba {
 
@@ -240,28 +241,36 @@ __device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, do
 }
 
 // MODE 0 (trailing update): tile (ti, tj), i >= j > k:  S_ij -= S_ik S_jk^T
+//        part 0: every such tile;  part 1: only the next panel's column j = k + 1 (what the next diagonal
+//        factor and panel solve wait for);  part 2: the columns j >= k + 2 (runs beside them: look-ahead)
 // MODE 1 (panel solve):     tile (ti, k),  i > k:       S_ik  = S_ik Linv_k^T
+// CTA b takes tiles b, b + gridDim.x, ... (the K chunks of consecutive tiles form one stream through the two
+// shared-memory stages); the launches below use one tile per CTA.
 template <int MODE>
 __global__ void __launch_bounds__(512) k_dense_gemm(double* __restrict__ S, size_t ld, int k,
-                                                    const double* __restrict__ linv_all) {
+                                                    const double* __restrict__ linv_all, int part, int ntiles) {
   extern __shared__ __align__(16) double sm[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  int ti, tj;
-  if (MODE == 0) {
-    const int b = blockIdx.x;
-    int i = (int)((sqrt(8.0 * (double)b + 1.0) - 1.0) * 0.5);
-    while ((long long)(i + 1) * (i + 2) / 2 <= b) ++i;
-    while ((long long)i * (i + 1) / 2 > b) --i;
-    ti = k + 1 + i;
-    tj = k + 1 + (b - (int)((long long)i * (i + 1) / 2));
-  } else {
-    ti = k + 1 + blockIdx.x;
-    tj = k;
-  }
-  const double* X = S + (size_t)k * DT * ld + (size_t)ti * DT;
-  const double* Y = MODE == 0 ? S + (size_t)k * DT * ld + (size_t)tj * DT : linv_all + (size_t)k * DT * DT;
+  auto decode = [&](int b, int& ti, int& tj) {
+    if (MODE == 0 && part == 1) {
+      ti = k + 1 + b;
+      tj = k + 1;
+    } else if (MODE == 0) {
+      int i = (int)((sqrt(8.0 * (double)b + 1.0) - 1.0) * 0.5);
+      while ((long long)(i + 1) * (i + 2) / 2 <= b) ++i;
+      while ((long long)i * (i + 1) / 2 > b) --i;
+      const int base = part == 2 ? k + 2 : k + 1;      // part 2: the triangle without its first column
+      ti = base + i;
+      tj = base + (b - (int)((long long)i * (i + 1) / 2));
+    } else {
+      ti = k + 1 + b;
+      tj = k;
+    }
+  };
   const size_t ldy = MODE == 0 ? ld : (size_t)DT;
-  auto load = [&](int stage, int kc) {
+  auto load = [&](int stage, int ti, int tj, int kc) {
+    const double* X = S + (size_t)k * DT * ld + (size_t)ti * DT;
+    const double* Y = MODE == 0 ? S + (size_t)k * DT * ld + (size_t)tj * DT : linv_all + (size_t)k * DT * DT;
     double* xs = sm + (size_t)stage * 2 * GK * GS;
     double* ys = xs + GK * GS;
     for (int p = tid; p < GK * (DT / 2); p += 512) {
@@ -271,56 +280,75 @@ __global__ void __launch_bounds__(512) k_dense_gemm(double* __restrict__ S, size
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  double acc[4][4][2];
-#pragma unroll
-  for (int mi = 0; mi < 4; ++mi)
-#pragma unroll
-    for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
   const int r0 = (warp & 3) * 32 + (lane >> 2), c0 = (warp >> 2) * 32 + (lane >> 2), kl = lane & 3;
-  load(0, 0);
   constexpr int NCH = DT / GK;
-  for (int kc = 0; kc < NCH; ++kc) {
-    if (kc + 1 < NCH) {
-      load((kc + 1) & 1, kc + 1);
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-    } else {
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-    }
-    __syncthreads();
-    const double* xs = sm + (size_t)(kc & 1) * 2 * GK * GS;
-    const double* ys = xs + GK * GS;
+  int t = blockIdx.x;
+  if (t >= ntiles) return;
+  int ti, tj;
+  decode(t, ti, tj);
+  int seq = 0;                                           // chunks consumed so far: stage = seq & 1
+  load(0, ti, tj, 0);
+  for (; t < ntiles; t += gridDim.x) {
+    const int tn = t + gridDim.x;
+    int tin = 0, tjn = 0;
+    if (tn < ntiles) decode(tn, tin, tjn);
+    double acc[4][4][2];
 #pragma unroll
-    for (int k0 = 0; k0 < GK; k0 += 4) {
-      double a[4], b[4];
+    for (int mi = 0; mi < 4; ++mi)
 #pragma unroll
-      for (int mi = 0; mi < 4; ++mi) a[mi] = xs[(k0 + kl) * GS + r0 + 8 * mi];
-#pragma unroll
-      for (int ni = 0; ni < 4; ++ni) b[ni] = ys[(k0 + kl) * GS + c0 + 8 * ni];
-#pragma unroll
-      for (int mi = 0; mi < 4; ++mi)
-#pragma unroll
-        for (int ni = 0; ni < 4; ++ni) dmma_m8n8k4(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
-    }
-    __syncthreads();                                     // the stage is refilled by the next iteration's load
-  }
-  // epilogue: lane holds D[row][col], D[row][col + 1], row = lane / 4, col = 2 (lane % 4) of each 8 x 8 tile
-  double* C = MODE == 0 ? S + (size_t)tj * DT * ld + (size_t)ti * DT : S + (size_t)k * DT * ld + (size_t)ti * DT;
-#pragma unroll
-  for (int mi = 0; mi < 4; ++mi) {
-#pragma unroll
-    for (int ni = 0; ni < 4; ++ni) {
-      const int row = (warp & 3) * 32 + 8 * mi + (lane >> 2);
-      const int col = (warp >> 2) * 32 + 8 * ni + 2 * (lane & 3);
-      double* p0 = C + (size_t)col * ld + row;
-      double* p1 = p0 + ld;
-      if (MODE == 0) {
-        *p0 -= acc[mi][ni][0];
-        *p1 -= acc[mi][ni][1];
+      for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+    for (int kc = 0; kc < NCH; ++kc, ++seq) {
+      bool more = true;
+      if (kc + 1 < NCH) {
+        load((seq + 1) & 1, ti, tj, kc + 1);
+      } else if (tn < ntiles) {
+        load((seq + 1) & 1, tin, tjn, 0);
       } else {
-        *p0 = acc[mi][ni][0];
-        *p1 = acc[mi][ni][1];
+        more = false;
+      }
+      if (more) {
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+      } else {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+      }
+      __syncthreads();
+      const double* xs = sm + (size_t)(seq & 1) * 2 * GK * GS;
+      const double* ys = xs + GK * GS;
+#pragma unroll
+      for (int k0 = 0; k0 < GK; k0 += 4) {
+        double a[4], b[4];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi) a[mi] = xs[(k0 + kl) * GS + r0 + 8 * mi];
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) b[ni] = ys[(k0 + kl) * GS + c0 + 8 * ni];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+          for (int ni = 0; ni < 4; ++ni) dmma_m8n8k4(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+      }
+      __syncthreads();                                   // the stage is refilled by the next iteration's load
+    }
+    // epilogue: lane holds D[row][col], D[row][col + 1], row = lane / 4, col = 2 (lane % 4) of each 8 x 8 tile
+    double* C = MODE == 0 ? S + (size_t)tj * DT * ld + (size_t)ti * DT : S + (size_t)k * DT * ld + (size_t)ti * DT;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi) {
+#pragma unroll
+      for (int ni = 0; ni < 4; ++ni) {
+        const int row = (warp & 3) * 32 + 8 * mi + (lane >> 2);
+        const int col = (warp >> 2) * 32 + 8 * ni + 2 * (lane & 3);
+        double* p0 = C + (size_t)col * ld + row;
+        double* p1 = p0 + ld;
+        if (MODE == 0) {
+          *p0 -= acc[mi][ni][0];
+          *p1 -= acc[mi][ni][1];
+        } else {
+          *p0 = acc[mi][ni][0];
+          *p1 = acc[mi][ni][1];
+        }
       }
     }
+    ti = tin;
+    tj = tjn;
   }
 }
 
@@ -417,14 +445,59 @@ void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, cudaStream_t 
   const int cover = std::max(d.V * 49, w.npad);
   k_dense_diag<<<(cover + 255) / 256, 256, 0, st>>>(d, w.S, w.ld, w.n, w.npad, rhs);
   lc.launches++;
+  // Right-looking factorisation with one panel of look-ahead: the diagonal factor and the panel solve of
+  // panel k + 1 only need column k + 1 of update k, so the rest of update k (columns >= k + 2: the bulk of the
+  // flops) stays on the caller's stream while the critical path (column update, diagonal factor, panel solve)
+  // runs on an internal high-priority stream -- its few CTAs must not queue behind the thousands of the bulk
+  // update.  Without the look-ahead the one-CTA diagonal factor (0.2 ms) sits between any two updates.
+  static cudaStream_t crit[64] = {};
+  static std::vector<cudaEvent_t> ev_panel[64], ev_upd[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  if (!crit[dev]) {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    cudaStreamCreateWithPriority(&crit[dev], cudaStreamNonBlocking, hi);
+  }
+  while ((int)ev_panel[dev].size() < T + 1) {
+    cudaEvent_t e1, e2;
+    cudaEventCreateWithFlags(&e1, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&e2, cudaEventDisableTiming);
+    ev_panel[dev].push_back(e1);
+    ev_upd[dev].push_back(e2);
+  }
+  cudaStream_t sc = crit[dev];
+  // (the critical stream starts after everything queued on st so far: the assembly and the diagonal blocks)
+  cudaEventRecord(ev_panel[dev][T], st);
+  cudaStreamWaitEvent(sc, ev_panel[dev][T], 0);
   for (int k = 0; k < T; ++k) {
-    k_dense_potrf<<<1, 1024, POTRF_SMEM, st>>>(w.S, w.ld, k, w.linv, d.sc);
-    lc.launches++;
     const int R = T - k - 1;
+    if (k > 0) {
+      // column k of update k - 1, after the bulk stream has finished update k - 2 on it
+      if (k > 1) cudaStreamWaitEvent(sc, ev_upd[dev][k - 2], 0);
+      k_dense_gemm<0><<<(unsigned)(R + 1), 512, GEMM_SMEM, sc>>>(w.S, w.ld, k - 1, w.linv, 1, R + 1);
+      lc.launches++;
+    }
+    k_dense_potrf<<<1, 1024, POTRF_SMEM, sc>>>(w.S, w.ld, k, w.linv, d.sc);
+    lc.launches++;
     if (R > 0) {
-      k_dense_gemm<1><<<R, 512, GEMM_SMEM, st>>>(w.S, w.ld, k, w.linv);
-      k_dense_gemm<0><<<(unsigned)((long long)R * (R + 1) / 2), 512, GEMM_SMEM, st>>>(w.S, w.ld, k, w.linv);
-      lc.launches += 2;
+      k_dense_gemm<1><<<(unsigned)R, 512, GEMM_SMEM, sc>>>(w.S, w.ld, k, w.linv, 0, R);
+      lc.launches++;
+      cudaEventRecord(ev_panel[dev][k], sc);
+      cudaStreamWaitEvent(st, ev_panel[dev][k], 0);
+      if (R > 1) {
+        // columns >= k + 2 of update k (ordered after update k - 1 on the same stream)
+        const int nt = (int)((long long)(R - 1) * R / 2);
+        // (one tile per CTA: CTAs that hold their SM for the whole update -- grid = SM count -- leave the critical
+        // stream nothing to run on and were not faster, 56.2 ms against 54.9 ms per factorisation at Venice)
+        k_dense_gemm<0><<<(unsigned)nt, 512, GEMM_SMEM, st>>>(w.S, w.ld, k, w.linv, 2, nt);
+        lc.launches++;
+      }
+      cudaEventRecord(ev_upd[dev][k], st);
+    } else {
+      cudaEventRecord(ev_panel[dev][k], sc);
+      cudaStreamWaitEvent(st, ev_panel[dev][k], 0);      // the last diagonal factor joins the caller's stream
     }
   }
   for (int k = 0; k < T; ++k) k_dense_fwd<<<T - k, DT, 0, st>>>(w.S, w.ld, k, w.linv, rhs, y);
