@@ -138,3 +138,30 @@ def test_ransac_large_synthetic(engine, oracle):
     want[:, 9:12] *= ora['signs'][:, None]
     ok = np.all(np.isfinite(want), axis=1)
     assert np.max(np.abs(res['models'][sub][ok] - want[ok])) < 1e-6
+
+
+def test_ransac_edge_cases(engine):
+    """No hypotheses, no inliers, bad indices, degenerate samples."""
+    import sfm_b200
+    g = load_golden('ransac.npz')
+    key, tri, k = g['pnp_clean_key'], g['pnp_tri'], g['pnp_k']
+    # no hypotheses: the reference's initial best (identity, zero, no inliers), campose_processor.py:524-527
+    res = engine.pnp_ransac(key.T, tri.T, k, np.zeros((0, 6), dtype=np.int32), 8.0)
+    assert res['hyp'] == -1 and res['count'] == 0 and not res['mask'].any()
+    assert np.array_equal(res['rot'], np.identity(3)) and np.array_equal(res['loc'], np.zeros((3, 1)))
+    # a threshold nothing passes: same outcome with hypotheses present
+    res = engine.pnp_ransac(key.T, tri.T, k, g['pnp_clean_samples'][:10], 1e-12)
+    assert res['hyp'] == -1 and res['count'] == 0 and not res['mask'].any()
+    with pytest.raises(ValueError):
+        engine.pnp_ransac(key.T, tri.T, k, np.full((1, 6), key.shape[1], dtype=np.int32), 8.0)
+    with pytest.raises(ValueError):
+        engine.fund_ransac(np.zeros((10, 4)), np.full((1, 8), 10, dtype=np.int32), 1.0)
+    # eight identical pairs: f__ cannot have rank 2 -> the reference raises (epipolar_processor.py:179-183)
+    pairs = np.tile(np.array([[0.1, 0.2, 0.3, 0.4]]), (12, 1))
+    res = engine.fund_ransac(pairs, np.arange(8, dtype=np.int32).reshape(1, 8), 1.0)
+    assert res['flags'] & 16 or not np.all(np.isfinite(res['F']))
+    cfg = sfm_b200.RansacConfig(1e-3, 0.99, 0.75, 8, 1, is_use_seed=False)
+    ep = sfm_b200.EpipolarProcessor(cfg, engine=engine)
+    with pytest.raises(ValueError):
+        ep._check_rank(engine.fund_ransac(np.tile(np.array([[0.1, 0.2, 0.3, 0.4]]), (9, 1)),
+                                          np.arange(8, dtype=np.int32).reshape(1, 8), 1.0, want_all=True))
