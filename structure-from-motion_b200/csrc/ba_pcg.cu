@@ -144,14 +144,16 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
     const double* src = d.pts + 3 * (size_t)pt0;
     for (int i = tid; i < 3 * np; i += RUN_LANES) cp_async8(Xa + i, src + i);
     for (int i = tid; i <= np; i += RUN_LANES) cp_async4(rowp + i, d.rowptr + pt0 + i);
+    for (int j = tid; j < np; j += RUN_LANES) {             // one trip stages all planes of a point
+      const double* gd = d.dinv + pt0 + j;
+      double* sd = Dn + j;
 #pragma unroll
-    for (int e = 0; e < 6; ++e) {
-      for (int j = tid; j < np; j += RUN_LANES) cp_async8(Dn + e * pt_cap + j, d.dinv + e * N + pt0 + j);
-    }
-    if (BACKSUB) {
+      for (int e = 0; e < 6; ++e) cp_async8(sd + e * pt_cap, gd + e * N);
+      if (BACKSUB) {
+        const double* gv = d.vj + pt0 + j;
+        double* sv = Vn + j;
 #pragma unroll
-      for (int e = 0; e < 3; ++e) {
-        for (int j = tid; j < np; j += RUN_LANES) cp_async8(Vn + e * pt_cap + j, d.vj + e * N + pt0 + j);
+        for (int e = 0; e < 3; ++e) cp_async8(sv + e * pt_cap, gv + e * N);
       }
     }
     for (int i = tid; i < 3 * pt_cap; i += RUN_LANES) tacc[i] = 0.0;
@@ -174,12 +176,29 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
     cp_async_wait_all();
     __syncthreads();
     const int parts = with_iter ? 13 : 6;
-    for (int i = tid; i < ci.nseg * parts; i += RUN_LANES) {
-      const int s = i / parts, part = i - s * parts;
+    const int total = ci.nseg * parts;
+    auto fetch = [&](int i, int& s, int& part) -> double2 {
+      s = i / parts;
+      part = i - s * parts;
       const int cam = cs.segc[s];
-      const double2 v = part < 6 ? reinterpret_cast<const double2*>(d.camtab + (size_t)CAMTAB_STRIDE * cam)[part]
-                                 : reinterpret_cast<const double2*>(d.camit + (size_t)CAMIT_STRIDE * cam)[part - 6];
-      reinterpret_cast<double2*>(camc + (size_t)CAMC * s)[part] = v;
+      return part < 6 ? reinterpret_cast<const double2*>(d.camtab + (size_t)CAMTAB_STRIDE * cam)[part]
+                      : reinterpret_cast<const double2*>(d.camit + (size_t)CAMIT_STRIDE * cam)[part - 6];
+    };
+    // four rounds of loads in flight before the first store: a round-by-round loop would pay the L2 latency
+    // once per round (a typical chunk has ~30 cameras = 3 to 4 rounds)
+    for (int i0 = tid; i0 < total; i0 += 4 * RUN_LANES) {
+      double2 v[4];
+      int sg[4], pa[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * RUN_LANES;
+        sg[u] = -1;
+        if (i < total) v[u] = fetch(i, sg[u], pa[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (sg[u] >= 0) reinterpret_cast<double2*>(camc + (size_t)CAMC * sg[u])[pa[u]] = v[u];
+      }
     }
     __syncthreads();
   };
@@ -341,17 +360,20 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
     }
     __syncthreads();
-    // half a warp per segment (lane = component): no index arithmetic per element, coalesced rows
-    {
-      const int e = tid & 15;
-      for (int s = tid >> 4; s < ci.nseg; s += RUN_LANES / 16) {
-        if (e < MV_ACC) {
-          const int ra = cs.srun[s], rb = cs.srun[s + 1];
-          double a = 0.0;
-          for (int rr = ra; rr < rb; ++rr) a += un[rr * MV_STRIDE + e];
-          d.part12[(size_t)cs.rpos[s] * MV_ACC + e] = a;
-        }
+    // one thread per (segment, component): its runs are added in lane order; consecutive threads write
+    // consecutive doubles of a row
+    for (int i = tid; i < ci.nseg * MV_ACC; i += RUN_LANES) {
+      const int s = i / MV_ACC, e = i - s * MV_ACC;
+      const int ra = cs.srun[s], rb = cs.srun[s + 1];
+      const double* src = un + ra * MV_STRIDE + e;
+      double a = 0.0;
+      int rr = ra;
+      for (; rr + 4 <= rb; rr += 4, src += 4 * MV_STRIDE) {
+        const double v0 = src[0], v1 = src[MV_STRIDE], v2 = src[2 * MV_STRIDE], v3 = src[3 * MV_STRIDE];
+        a = (((a + v0) + v1) + v2) + v3;
       }
+      for (; rr < rb; ++rr, src += MV_STRIDE) a += src[0];
+      d.part12[(size_t)cs.rpos[s] * MV_ACC + e] = a;
     }
     __syncthreads();
   }
