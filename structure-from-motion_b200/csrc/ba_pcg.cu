@@ -202,6 +202,7 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
     }
     __syncthreads();
   };
+  const bool single = gm.nc == 1;
   // R and C of the lane's camera stay in registers from pass 1 to pass 2 when the group is a single chunk
   // (the lane owns the same run in both passes): the middle phases need few registers
   double R[9], C[3];
@@ -264,17 +265,35 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       }
     }
     __syncthreads();
-    // one thread per point: its slots are summed in observation order, three components side by side
+    // one thread per point: its slots are summed in observation order, three components side by side.  A
+    // single-chunk group has the whole t_j here, so the same thread goes on to u_j = D_j^-1 t_j (and, in the
+    // back-substitution, to the point update): no second pass over the points, no barrier in between.
     for (int j = tid; j < np; j += RUN_LANES) {
       const int lo = max(rowp[j], ci.obs0) - ci.obs0;
       const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
-      if (lo < hi) {
-        double a0 = tacc[j], a1 = tacc[pt_cap + j], a2 = tacc[2 * pt_cap + j];
-        for (int s = lo; s < hi; ++s) {
-          a0 += un[s];
-          a1 += un[slot_cap + s];
-          a2 += un[2 * slot_cap + s];
+      double a0 = tacc[j], a1 = tacc[pt_cap + j], a2 = tacc[2 * pt_cap + j];
+      for (int s = lo; s < hi; ++s) {
+        a0 += un[s];
+        a1 += un[slot_cap + s];
+        a2 += un[2 * slot_cap + s];
+      }
+      if (single) {
+        double Dinv[6], u[3];
+        const double t[3] = {a0, a1, a2};
+#pragma unroll
+        for (int e = 0; e < 6; ++e) Dinv[e] = Dn[e * pt_cap + j];
+        sym3_mul(Dinv, t, u);
+        if (BACKSUB) {
+          double* p = d.pts + 3 * ((size_t)pt0 + j);
+#pragma unroll
+          for (int e = 0; e < 3; ++e) p[e] = Xa[3 * j + e] + (Vn[e * pt_cap + j] - u[e]);
+        } else {
+          a0 = u[0];
+          a1 = u[1];
+          a2 = u[2];
         }
+      }
+      if (!(BACKSUB && single)) {
         tacc[j] = a0;
         tacc[pt_cap + j] = a1;
         tacc[2 * pt_cap + j] = a2;
@@ -282,29 +301,29 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
     }
     __syncthreads();
   }
-  // ---- u_j = D_j^-1 t_j
-  cp_async_wait_all();
-  __syncthreads();
-  for (int j = tid; j < np; j += RUN_LANES) {
-    double Dinv[6], t[3], u[3];
+  if (!single) {
+    // ---- u_j = D_j^-1 t_j once every chunk has added its part
+    for (int j = tid; j < np; j += RUN_LANES) {
+      double Dinv[6], t[3], u[3];
 #pragma unroll
-    for (int e = 0; e < 6; ++e) Dinv[e] = Dn[e * pt_cap + j];
-    t[0] = tacc[j];
-    t[1] = tacc[pt_cap + j];
-    t[2] = tacc[2 * pt_cap + j];
-    sym3_mul(Dinv, t, u);
-    if (BACKSUB) {
-      double* p = d.pts + 3 * ((size_t)pt0 + j);
+      for (int e = 0; e < 6; ++e) Dinv[e] = Dn[e * pt_cap + j];
+      t[0] = tacc[j];
+      t[1] = tacc[pt_cap + j];
+      t[2] = tacc[2 * pt_cap + j];
+      sym3_mul(Dinv, t, u);
+      if (BACKSUB) {
+        double* p = d.pts + 3 * ((size_t)pt0 + j);
 #pragma unroll
-      for (int e = 0; e < 3; ++e) p[e] = Xa[3 * j + e] + (Vn[e * pt_cap + j] - u[e]);
-    } else {
-      tacc[j] = u[0];
-      tacc[pt_cap + j] = u[1];
-      tacc[2 * pt_cap + j] = u[2];
+        for (int e = 0; e < 3; ++e) p[e] = Xa[3 * j + e] + (Vn[e * pt_cap + j] - u[e]);
+      } else {
+        tacc[j] = u[0];
+        tacc[pt_cap + j] = u[1];
+        tacc[2 * pt_cap + j] = u[2];
+      }
     }
+    if (!BACKSUB) __syncthreads();
   }
   if (BACKSUB) return;
-  __syncthreads();
   // ---- pass 2: per camera sums of c~ d^T and c'
   const double sgn = dvdc_quirk ? 1.0 : -1.0;
   for (int c = c0; c < c1; ++c) {
