@@ -272,10 +272,25 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       const int lo = max(rowp[j], ci.obs0) - ci.obs0;
       const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
       double a0 = tacc[j], a1 = tacc[pt_cap + j], a2 = tacc[2 * pt_cap + j];
-      for (int s = lo; s < hi; ++s) {
-        a0 += un[s];
-        a1 += un[slot_cap + s];
-        a2 += un[2 * slot_cap + s];
+      for (int s = lo; s < hi; s += 3) {                 // up to nine loads in flight, sums in observation order
+        const int n = hi - s;
+        const double* q = un + s;
+        const double v00 = q[0], v10 = q[slot_cap], v20 = q[2 * slot_cap];
+        const double v01 = n > 1 ? q[1] : 0.0, v11 = n > 1 ? q[slot_cap + 1] : 0.0, v21 = n > 1 ? q[2 * slot_cap + 1] : 0.0;
+        const double v02 = n > 2 ? q[2] : 0.0, v12 = n > 2 ? q[slot_cap + 2] : 0.0, v22 = n > 2 ? q[2 * slot_cap + 2] : 0.0;
+        a0 += v00;
+        a1 += v10;
+        a2 += v20;
+        if (n > 1) {
+          a0 += v01;
+          a1 += v11;
+          a2 += v21;
+        }
+        if (n > 2) {
+          a0 += v02;
+          a1 += v12;
+          a2 += v22;
+        }
       }
       if (single) {
         double Dinv[6], u[3];
@@ -302,7 +317,10 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
     __syncthreads();
   }
   if (!single) {
-    // ---- u_j = D_j^-1 t_j once every chunk has added its part
+    // ---- u_j = D_j^-1 t_j once every chunk has added its part (a group of unobserved points has no chunk at
+    // all: nothing has waited for the staged points yet)
+    cp_async_wait_all();
+    __syncthreads();
     for (int j = tid; j < np; j += RUN_LANES) {
       double Dinv[6], t[3], u[3];
 #pragma unroll
@@ -386,12 +404,17 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
       const int ra = cs.srun[s], rb = cs.srun[s + 1];
       const double* src = un + ra * MV_STRIDE + e;
       double a = 0.0;
-      int rr = ra;
-      for (; rr + 4 <= rb; rr += 4, src += 4 * MV_STRIDE) {
-        const double v0 = src[0], v1 = src[MV_STRIDE], v2 = src[2 * MV_STRIDE], v3 = src[3 * MV_STRIDE];
-        a = (((a + v0) + v1) + v2) + v3;
+      for (int rr = ra; rr < rb; rr += 4, src += 4 * MV_STRIDE) {   // up to four loads in flight, sums in run order
+        const int n = rb - rr;
+        const double v0 = src[0];
+        const double v1 = n > 1 ? src[MV_STRIDE] : 0.0;
+        const double v2 = n > 2 ? src[2 * MV_STRIDE] : 0.0;
+        const double v3 = n > 3 ? src[3 * MV_STRIDE] : 0.0;
+        a += v0;
+        if (n > 1) a += v1;
+        if (n > 2) a += v2;
+        if (n > 3) a += v3;
       }
-      for (; rr < rb; ++rr, src += MV_STRIDE) a += src[0];
       d.part12[(size_t)cs.rpos[s] * MV_ACC + e] = a;
     }
     __syncthreads();
