@@ -34,8 +34,8 @@ LM_ITERS = 3
 LAMBDA = 5.0
 CPU_SAMPLE_SCALE = 0.25
 # ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of ONE k_matvec<0> launch at the full Venice
-# shape on one GPU (profiles/r1_ncu_full_v25_summary.txt, mean of three launches: 104.53 MB read + 10.85 MB written)
-NCU_DRAM_BYTES_PER_MATVEC = {('venice', 1.0, 1): 115.38e6}
+# shape on one GPU (profiles/r1_ncu_full_v36_summary.txt, mean of two launches: 104.52 MB read + 10.60 MB written)
+NCU_DRAM_BYTES_PER_MATVEC = {('venice', 1.0, 1): 115.13e6}
 
 
 def _peaks():
@@ -289,7 +289,7 @@ def run_ours(args):
             'roofline': {'kernel': k3_name,
                          'bound': 'hbm', 'achieved': k3_gbs, 'peak': peak, 'unit': 'GB/s', 'frac': k3_gbs / peak,
                          'peak_kind': peak_kind, 'traffic': NCU_DRAM_BYTES_PER_MATVEC.get((args.shape, args.scale, world)),
-                         'traffic_source': 'profiles/r1_ncu_full_v25_summary.txt (k_matvec<0>, one launch)',
+                         'traffic_source': 'profiles/r1_ncu_full_v36_summary.txt (k_matvec<0, 0>, one launch)',
                          'algorithmic_bytes': k3_bytes, 'ms': k3_ms},
             'roofline_jacobian_schur': {'kernel': 'K1+K2 = k_linearize (residuals, Jacobians, point Schur blocks and camera Gram rows in one launch; J never stored)', 'bound': 'hbm',
                                         'achieved': k12_gbs, 'peak': peak, 'unit': 'GB/s', 'frac': k12_gbs / peak,
