@@ -56,6 +56,7 @@ typedef enum {
 #define SFMBA_FLAG_NONFINITE      4u  /* NaN/Inf in cost or update                                 */
 #define SFMBA_FLAG_PCG_MAXITER    8u  /* PCG stopped on pcg_max_iter, not on pcg_tol               */
 #define SFMBA_FLAG_SINGULAR      16u  /* a 3x3 / 7x7 block was not positive definite               */
+#define SFMBA_FLAG_BAD_INDEX     64u  /* a RANSAC sample index outside [0, n): the call returns INVALID_ARG */
 
 typedef enum { SFMBA_MODE_REFERENCE_FIXED = 0, SFMBA_MODE_ADAPTIVE_LM = 1 } sfmba_mode;
 /* PCG: matrix-free block-Jacobi preconditioned conjugate gradients on the implicit Schur complement.

@@ -81,13 +81,11 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
     double R[9], C[3];
     const uint32_t ix_first = cs.ixs[tid];
     if (ix_first != REC_INVALID) load_cam_rc(d.camtab, cs.segc[rec_seg(ix_first)], R, C);
-    for (int k = 0; k < K; ++k) {
-      const uint32_t ix = cs.ixs[k * RUN_LANES + tid];
-      if (ix == REC_INVALID) break;
-      const double2 b = cs.bs[k * RUN_LANES + tid];
+    // two observations of the lane per trip: their dependent chains (projection, reciprocal, products) interleave
+    auto point_terms = [&](uint32_t ix, double2 b, double out[9], double& cterm, bool& ok) {
       const int ptl = rec_ptl(ix);
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
-      if (!pr.ok) flags |= FLAG_DEPTH_ZERO;
+      ok = pr.ok;
       const double r0 = b.x - pr.u, r1 = b.y - pr.v;
       const double x0 = (R[0] - pr.u * R[2]) * pr.iw, x1 = (R[3] - pr.u * R[5]) * pr.iw,
                    x2 = (R[6] - pr.u * R[8]) * pr.iw;
@@ -97,21 +95,44 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
       if (ROBUST) {
         double rho;
         const double w = huber_weight(r0 * r0 + r1 * r1, d.huber_delta, rho);
-        cost += rho;
+        cterm = rho;
         wx0 *= w; wx1 *= w; wx2 *= w; wy0 *= w; wy1 *= w; wy2 *= w;
       } else {
-        cost += r0 * r0 + r1 * r1;
+        cterm = r0 * r0 + r1 * r1;
       }
-      double* s = slots + rec_pos(ix);
-      s[0 * slot_cap] = wx0 * x0 + wy0 * y0;
-      s[1 * slot_cap] = wx0 * x1 + wy0 * y1;
-      s[2 * slot_cap] = wx0 * x2 + wy0 * y2;
-      s[3 * slot_cap] = wx1 * x1 + wy1 * y1;
-      s[4 * slot_cap] = wx1 * x2 + wy1 * y2;
-      s[5 * slot_cap] = wx2 * x2 + wy2 * y2;
-      s[6 * slot_cap] = wx0 * r0 + wy0 * r1;
-      s[7 * slot_cap] = wx1 * r0 + wy1 * r1;
-      s[8 * slot_cap] = wx2 * r0 + wy2 * r1;
+      out[0] = wx0 * x0 + wy0 * y0;
+      out[1] = wx0 * x1 + wy0 * y1;
+      out[2] = wx0 * x2 + wy0 * y2;
+      out[3] = wx1 * x1 + wy1 * y1;
+      out[4] = wx1 * x2 + wy1 * y2;
+      out[5] = wx2 * x2 + wy2 * y2;
+      out[6] = wx0 * r0 + wy0 * r1;
+      out[7] = wx1 * r0 + wy1 * r1;
+      out[8] = wx2 * r0 + wy2 * r1;
+    };
+    for (int k = 0; k < K; k += 2) {
+      const uint32_t ix_a = cs.ixs[k * RUN_LANES + tid];
+      if (ix_a == REC_INVALID) break;
+      const double2 b_a = cs.bs[k * RUN_LANES + tid];
+      uint32_t ix_b = k + 1 < K ? cs.ixs[(k + 1) * RUN_LANES + tid] : REC_INVALID;
+      const bool two = ix_b != REC_INVALID;
+      const double2 b_b = two ? cs.bs[(k + 1) * RUN_LANES + tid] : b_a;
+      if (!two) ix_b = ix_a;
+      double oa[9], ob[9], ca, cb;
+      bool ok_a, ok_b;
+      point_terms(ix_a, b_a, oa, ca, ok_a);
+      point_terms(ix_b, b_b, ob, cb, ok_b);
+      if (!ok_a || !ok_b) flags |= FLAG_DEPTH_ZERO;
+      cost += ca;
+      double* sa = slots + rec_pos(ix_a);
+#pragma unroll
+      for (int e = 0; e < 9; ++e) sa[e * slot_cap] = oa[e];
+      if (two) {
+        cost += cb;
+        double* sb = slots + rec_pos(ix_b);
+#pragma unroll
+        for (int e = 0; e < 9; ++e) sb[e * slot_cap] = ob[e];
+      }
     }
     __syncthreads();
     // one work item per (point, component): the slots of a point are summed in observation order

@@ -522,6 +522,7 @@ int sfmba_pnp_ransac(sfmba_ctx* ctx, int32_t num_pts, int32_t num_hyp, const dou
   if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "pnp_ransac sync")) != 0) return rc;
   if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "pnp_ransac kernels")) != 0) return rc;
   const uint32_t fl = *reinterpret_cast<uint32_t*>(pin);
+  if (fl & SFMBA_FLAG_BAD_INDEX) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "sample index out of range");
   int32_t best[2] = {-1, 0};
   if (num_hyp > 0) {
     best[0] = reinterpret_cast<int32_t*>(pin + 16)[0];
@@ -602,6 +603,7 @@ int sfmba_fund_ransac(sfmba_ctx* ctx, int32_t num_pairs, int32_t num_hyp, const 
   if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "fund_ransac sync")) != 0) return rc;
   if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "fund_ransac kernels")) != 0) return rc;
   const uint32_t fl = *reinterpret_cast<uint32_t*>(pin);
+  if (fl & SFMBA_FLAG_BAD_INDEX) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "sample index out of range");
   int32_t best[2] = {-1, 0};
   if (num_hyp > 0) {
     best[0] = reinterpret_cast<int32_t*>(pin + 16)[0];

@@ -92,7 +92,7 @@ __device__ __forceinline__ double det3(const double a[9]) {
 
 // ---- 6-point DLT pose (campose_processor.py:565-633) -----------------------------------------------
 // models[h] = rot[9] (row-major, camera-to-world) | loc[3];  projs[h] = K [rot^T | -rot^T loc] (3x4)
-__global__ void __launch_bounds__(32) k_pnp_models(int H, const double* __restrict__ key, const double* __restrict__ X,
+__global__ void __launch_bounds__(32) k_pnp_models(int H, int n, const double* __restrict__ key, const double* __restrict__ X,
                                                    const double* __restrict__ Kmat, const double* __restrict__ Kinv,
                                                    const int32_t* __restrict__ samples,
                                                    const int32_t* __restrict__ loc_sign, double* __restrict__ models,
@@ -102,7 +102,11 @@ __global__ void __launch_bounds__(32) k_pnp_models(int H, const double* __restri
   double W[144], V[144], v[12];
   for (int i = 0; i < 144; ++i) W[i] = 0.0;
   for (int i = 0; i < 6; ++i) {
-    const int s = samples[6 * (size_t)h + i];
+    int s = samples[6 * (size_t)h + i];
+    if (s < 0 || s >= n) {                       // reported to the caller as SFMBA_ERR_INVALID_ARG
+      atomicOr(flags, FLAG_BAD_INDEX);
+      s = 0;
+    }
     const double kx = key[3 * (size_t)s], ky = key[3 * (size_t)s + 1], kz = key[3 * (size_t)s + 2];
     // campose_processor.py:537: key points of the sample in camera coordinates
     const double px = Kinv[0] * kx + Kinv[1] * ky + Kinv[2] * kz;
@@ -251,14 +255,18 @@ __global__ void __launch_bounds__(256) k_ransac_mask(int n, const double* __rest
 }
 
 // ---- 8-point fundamental matrix (epipolar_processor.py:140-191) ------------------------------------
-__global__ void __launch_bounds__(32) k_fund_models(int H, const double* __restrict__ pairs,
+__global__ void __launch_bounds__(32) k_fund_models(int H, int n, const double* __restrict__ pairs,
                                                     const int32_t* __restrict__ samples, double* __restrict__ models,
                                                     uint32_t* flags) {
   const int h = blockIdx.x * blockDim.x + threadIdx.x;
   if (h >= H) return;
   double W[72], V[81], f[9];
   for (int i = 0; i < 8; ++i) {
-    const int s = samples[8 * (size_t)h + i];
+    int s = samples[8 * (size_t)h + i];
+    if (s < 0 || s >= n) {
+      atomicOr(flags, FLAG_BAD_INDEX);
+      s = 0;
+    }
     const double x1 = pairs[4 * (size_t)s], y1 = pairs[4 * (size_t)s + 1];
     const double x1_ = pairs[4 * (size_t)s + 2], y1_ = pairs[4 * (size_t)s + 3];
     double* r = W + 9 * i;
@@ -298,7 +306,7 @@ void launch_pnp_ransac(int n, int H, const double* key, const double* X, const d
                        int32_t* counts, int32_t* best, uint8_t* mask, uint32_t* flags, cudaStream_t st,
                        LaunchCounter& lc) {
   if (H <= 0) return;
-  k_pnp_models<<<(H + 31) / 32, 32, 0, st>>>(H, key, X, Kmat, Kinv, samples, loc_sign, models, projs, flags);
+  k_pnp_models<<<(H + 31) / 32, 32, 0, st>>>(H, n, key, X, Kmat, Kinv, samples, loc_sign, models, projs, flags);
   k_ransac_score<true><<<H, 256, 0, st>>>(n, projs, 12, key, X, thr, counts);
   k_ransac_pick<<<1, 1024, 0, st>>>(H, counts, best);
   lc.launches += 3;
@@ -312,7 +320,7 @@ void launch_fund_ransac(int n, int H, const double* pairs, const int32_t* sample
                         int32_t* counts, int32_t* best, uint8_t* mask, uint32_t* flags, cudaStream_t st,
                         LaunchCounter& lc) {
   if (H <= 0) return;
-  k_fund_models<<<(H + 31) / 32, 32, 0, st>>>(H, pairs, samples, models, flags);
+  k_fund_models<<<(H + 31) / 32, 32, 0, st>>>(H, n, pairs, samples, models, flags);
   k_ransac_score<false><<<H, 256, 0, st>>>(n, models, 9, pairs, nullptr, thr, counts);
   k_ransac_pick<<<1, 1024, 0, st>>>(H, counts, best);
   lc.launches += 3;

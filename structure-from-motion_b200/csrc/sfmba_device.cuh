@@ -17,6 +17,7 @@ constexpr uint32_t FLAG_NONFINITE = 4u;
 constexpr uint32_t FLAG_PCG_MAXITER = 8u;
 constexpr uint32_t FLAG_SINGULAR = 16u;
 constexpr uint32_t FLAG_PEER_TIMEOUT = 32u;
+constexpr uint32_t FLAG_BAD_INDEX = 64u;      // a caller-supplied index outside its array (RANSAC sample tables)
 
 // q (w,x,y,z) -> R row-major, utils.py:64-97
 __device__ __forceinline__ void quat_to_rot(const double q[4], double R[9]) {

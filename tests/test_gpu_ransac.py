@@ -165,3 +165,31 @@ def test_ransac_edge_cases(engine):
     with pytest.raises(ValueError):
         ep._check_rank(engine.fund_ransac(np.tile(np.array([[0.1, 0.2, 0.3, 0.4]]), (9, 1)),
                                           np.arange(8, dtype=np.int32).reshape(1, 8), 1.0, want_all=True))
+
+
+def test_ransac_c_abi_rejects_bad_sample_index(engine, oracle):
+    """The C-ABI itself (not only the Python wrapper) refuses a sample index outside [0, n)."""
+    import ctypes as C
+    from sfm_b200 import _capi
+    from sfm_b200.engine import _ptr
+    g = load_golden('ransac.npz')
+    key = np.ascontiguousarray(g['pnp_clean_key'].T)
+    tri = np.ascontiguousarray(g['pnp_tri'].T)
+    k = np.ascontiguousarray(g['pnp_k'], dtype=np.float64)
+    n = key.shape[0]
+    for bad in (n, -1):
+        samples = np.ascontiguousarray(g['pnp_clean_samples'][:4], dtype=np.int32).copy()
+        samples[2, 3] = bad
+        rot, loc, best = np.zeros(9), np.zeros(3), np.zeros(2, dtype=np.int32)
+        mask, flags = np.zeros(n, dtype=np.uint8), C.c_uint32(0)
+        rc = engine.lib.sfmba_pnp_ransac_host(engine.ctx, n, 4, _ptr(key), _ptr(tri), _ptr(k), _ptr(samples), None, 8.0,
+                                              _ptr(rot), _ptr(loc), _ptr(best), _ptr(mask), None, None, C.byref(flags))
+        assert rc == _capi.ERR_INVALID_ARG
+        pairs = np.ascontiguousarray(oracle.fund_normalize(g['fund_clean_left'], g['fund_clean_right'])[0], dtype=np.float64)
+        fs = np.ascontiguousarray(g['fund_clean_samples'][:4], dtype=np.int32).copy()
+        fs[1, 7] = bad if bad < 0 else pairs.shape[0]
+        fm = np.zeros(9)
+        fmask = np.zeros(pairs.shape[0], dtype=np.uint8)
+        rc = engine.lib.sfmba_fund_ransac_host(engine.ctx, pairs.shape[0], 4, _ptr(pairs), _ptr(fs), 1e-3,
+                                               _ptr(fm), _ptr(best), _ptr(fmask), None, None, C.byref(flags))
+        assert rc == _capi.ERR_INVALID_ARG
