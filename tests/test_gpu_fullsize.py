@@ -118,3 +118,27 @@ def test_venice_host_and_device_paths_are_bit_identical(engine, venice):
         assert np.array_equal(ph.pts, t['pts'].cpu().numpy())
         assert rh.final_cost == rd.final_cost and rh.initial_cost == rd.initial_cost
         assert rh.costs == rd.costs
+
+
+def test_final_shape_properties(engine):
+    """The largest configuration (Final shape: 13 682 cameras / 4 456 117 points / 28 987 644 observations) on one GPU,
+    through the same size-independent properties: the two cost paths agree, the host-buffer (ranged upload) and the
+    device-resident solves give identical bits, and the reference-mode step solves the normal equations."""
+    from sfm_b200 import synthetic
+    final, _ = synthetic.make_shape('final')
+    direct = engine.ba_cost(final)
+    ph = _copy(final)
+    rh = engine.ba_solve_host(ph, lam=5.0, iterations=2)
+    assert abs(rh.initial_cost - direct) <= 1e-11 * direct
+    assert abs(rh.final_cost - engine.ba_cost(ph)) <= 1e-11 * rh.final_cost
+    t = engine.to_device(final)
+    rd = engine.ba_solve_device(t, lam=5.0, iterations=2)
+    assert np.array_equal(ph.cams, t['cams'].cpu().numpy())
+    assert np.array_equal(ph.pts, t['pts'].cpu().numpy())
+    assert rh.costs == rd.costs and rh.pcg_iterations == rd.pcg_iterations
+    p1, p2 = _copy(final), _copy(final)
+    engine.ba_solve_host(p1, lam=5.0, iterations=1, pcg_tol=1e-13)
+    engine.ba_solve_host(p2, lam=5.0, iterations=1, pcg_tol=1e-8)
+    scale = np.max(np.abs(p1.cams - final.cams))
+    assert np.max(np.abs(p1.cams - p2.cams)) <= 1e-6 * scale
+    assert np.max(np.abs(p1.pts - p2.pts)) <= 1e-6 * max(1.0, np.max(np.abs(p1.pts - final.pts)))
