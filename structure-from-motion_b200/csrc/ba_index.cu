@@ -12,6 +12,24 @@
 
 namespace sfmba {
 
+// pt_rowptr must be a CSR over [0, m] and obs_cam must lie in [0, V): everything below indexes the observation
+// arrays and the camera tables through them.  The host reads the flag after the counting phase.
+__global__ void k_validate_index(BaDev d) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  bool bad = false;
+  if (j <= d.N) {
+    const int a = d.rowptr[j];
+    bad = a < 0 || a > d.m;
+    if (j == 0 && a != 0) bad = true;
+    if (j == d.N && a != d.m) bad = true;
+    if (j < d.N && a > d.rowptr[j + 1]) bad = true;
+  }
+  const int stride = gridDim.x * blockDim.x;
+  for (int o = j; o < d.m; o += stride)
+    if ((uint32_t)d.obs_cam[o] >= (uint32_t)d.V) bad = true;
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(&d.sc->flags, FLAG_BAD_INDEX);
+}
+
 // group g owns the points j with rowptr[j] + POINT_WEIGHT * j in [g W, (g+1) W)
 __global__ void k_group_bounds(BaDev d) {
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -50,6 +68,13 @@ __global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chu
   __shared__ int s_cnt[HASH_SLOTS];
   __shared__ int s_distinct, s_sum;
   const int g = blockIdx.x;
+  if (d.sc->flags & FLAG_BAD_INDEX) {               // k_validate_index: the host rejects the problem after this phase
+    if (threadIdx.x == 0) {
+      d.grp_nchunk[g] = 0;
+      d.grp_K[g] = 1;
+    }
+    return;
+  }
   const int pt0 = d.grp_pt[g], pt1 = d.grp_pt[g + 1];
   const int o0 = d.rowptr[pt0], o1 = d.rowptr[pt1];
   const int L = o1 - o0;
@@ -157,11 +182,18 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
     const int obs0 = nc == 1 ? o_begin : o_begin + (c - c0) * SEG_CAP;
     const int len = nc == 1 ? (o_end - o_begin) : min(SEG_CAP, o_end - obs0);
     uint32_t keys[CHUNK_K_MAX];
+    bool bad_cam = false;
 #pragma unroll
     for (int i = 0; i < CHUNK_K_MAX; ++i) {
       const int idx = tid * CHUNK_K_MAX + i;
-      keys[i] = idx < len ? (((uint32_t)d.obs_cam[obs0 + idx] << 11) | (uint32_t)idx) : 0xffffffffu;
+      uint32_t cam = idx < len ? (uint32_t)d.obs_cam[obs0 + idx] : 0u;
+      if (cam >= (uint32_t)d.V) {                    // (k_validate_index has flagged it; stay inside the tables)
+        bad_cam = true;
+        cam = 0u;
+      }
+      keys[i] = idx < len ? ((cam << 11) | (uint32_t)idx) : 0xffffffffu;
     }
+    if (bad_cam) atomicOr(&d.sc->flags, FLAG_BAD_INDEX);
     // the keys arrive in position order (blocked arrangement) and the radix sort is stable, so sorting on
     // the camera bits alone leaves equal cameras in position order; padding keys (all ones) stay last
     Sort(tmp.sort).Sort(keys, 11, 11 + cam_bits);
@@ -303,8 +335,9 @@ size_t index_temp_bytes(int G, int chunk_bound, int V) {
 // phase 1: groups and chunk counts (the host then reads sc->num_chunks and the shape statistics)
 void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, cudaStream_t st,
                         LaunchCounter& lc) {
+  k_validate_index<<<(d.N + 1 + 255) / 256, 256, 0, st>>>(d);
   k_group_bounds<<<(d.G + 1 + 255) / 256, 256, 0, st>>>(d);
-  lc.launches++;
+  lc.launches += 2;
   if (d.G > 0) {
     k_group_count<<<d.G, RUN_LANES, 0, st>>>(d, fine_chunks ? 1 : 0);
     cub::DeviceScan::ExclusiveSum(temp, temp_bytes, d.grp_nchunk, d.grp_chunk, d.G, st);

@@ -20,6 +20,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/sfmba.h"
 
@@ -224,11 +225,25 @@ struct DenseWork {
   double* linv;     // [npad / 128][128][128] inverses of the diagonal factor tiles
   double* vec;      // [3][npad] rhs | y | x
 };
+// the look-ahead of the factorisation: a high-priority stream for the critical path and the events that order it
+// against the caller's stream.  Owned by the context (created on first use, destroyed with it).
+struct DenseStreams {
+  cudaStream_t crit = nullptr;
+  std::vector<cudaEvent_t> ev_panel, ev_upd;
+  void release() {
+    for (cudaEvent_t e : ev_panel) cudaEventDestroy(e);
+    for (cudaEvent_t e : ev_upd) cudaEventDestroy(e);
+    ev_panel.clear();
+    ev_upd.clear();
+    if (crit) cudaStreamDestroy(crit);
+    crit = nullptr;
+  }
+};
 size_t dense_padded_dim(int V);
 // S = -(off-diagonal blocks) of this rank's points (zeroed first); all-reduced by the caller when world > 1
 void launch_dense_assemble(const BaDev& d, const DenseWork& w, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 // adds the diagonal blocks (cam_acc, lambda), factors, solves S x = gvec -> d.x
-void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, cudaStream_t st, LaunchCounter& lc);
+void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, DenseStreams& ds, cudaStream_t st, LaunchCounter& lc);
 // camit rows of an arbitrary 7V-vector (the back-substitution direction)
 void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 

@@ -22,6 +22,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "launch.cuh"
 #include "peer.cuh"
 #include "tile.cuh"
@@ -774,14 +776,18 @@ void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_
   const MvShape sh = matvec_shape(ts, backsub, robust);
   const size_t smem = mv_smem_bytes(sh);
   // the opt-in shared memory size is sticky per function and device: raise it only when needed
+  static std::mutex granted_mu;                       // contexts of different host threads share this table
   static size_t granted[4][64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   size_t& g = granted[(backsub ? 1 : 0) + (robust ? 2 : 0)][dev & 63];
   auto go = [&](auto kernel) {
-    if (smem > g) {
-      cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      g = smem;
+    {
+      std::lock_guard<std::mutex> lock(granted_mu);
+      if (smem > g) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        g = smem;
+      }
     }
     launch_pdl(kernel, dim3(d.G), dim3(RUN_LANES), smem, st, d, sh, dvdc_quirk ? 1 : 0);
   };

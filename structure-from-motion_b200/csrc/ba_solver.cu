@@ -288,7 +288,9 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   cudaMemcpyAsync(hs, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, st);
   if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "index count")) != 0) return rc;
   const int nchunks = hs->num_chunks;
-  if (nchunks < 0 || nchunks > chunk_upper) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "pt_rowptr is not a CSR");
+  if ((hs->flags & SFMBA_FLAG_BAD_INDEX) || nchunks < 0 || nchunks > chunk_upper)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG,
+                         "pt_rowptr is not a CSR over [0, num_obs] or obs_cam has an index outside [0, num_cams)");
   TileShape ts;
   ts.max_chunk_len = std::max(hs->max_chunk_len, 1);
   ts.max_group_pts = std::max(hs->max_group_pts, 1);
@@ -376,7 +378,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       if (multi && (rc = sfm_nccl_allreduce_f64(ctx, dw.S, dw.ld * (size_t)dw.npad, st)) != 0) return rc;
       pt.kend("dense_assemble", kb);
       kb = pt.kbegin();
-      launch_dense_factor_solve(d, dw, st, lc);
+      launch_dense_factor_solve(d, dw, ctx->dense_streams, st, lc);
       pt.kend("dense_factor_solve", kb);
       launch_cam_rows(d, d.x, quirk, st, lc);
     }

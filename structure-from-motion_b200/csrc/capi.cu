@@ -138,6 +138,7 @@ int sfmba_destroy(sfmba_ctx* ctx) {
   for (auto& b : ctx->bufs) b.release();
   for (auto& b : ctx->host_stage) b.release();
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  ctx->dense_streams.release();
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   if (ctx->io.copy) {
     cudaStreamDestroy(ctx->io.copy);

@@ -76,6 +76,7 @@ struct sfmba_ctx {
   size_t pinned_cap = 0;
   cudaStream_t own_stream = nullptr;
   SolveIo io;                    // copy stream and events of the host-buffer entry point
+  sfmba::DenseStreams dense_streams;   // dense-Cholesky look-ahead (dense.cu)
   unsigned pcg_epoch = 0;        // id of the current PCG solve (see host_sig)
   int pcg_hint = 0;              // iterations the previous PCG solve needed
 

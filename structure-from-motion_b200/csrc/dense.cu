@@ -430,14 +430,12 @@ void launch_dense_assemble(const BaDev& d, const DenseWork& w, bool dvdc_quirk, 
   }
 }
 
-void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, cudaStream_t st, LaunchCounter& lc) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaFuncSetAttribute(k_dense_potrf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)POTRF_SMEM);
-    cudaFuncSetAttribute(k_dense_gemm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
-    cudaFuncSetAttribute(k_dense_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
-    attr_done = true;
-  }
+void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, DenseStreams& ds, cudaStream_t st,
+                               LaunchCounter& lc) {
+  // (the opt-in shared memory size is per function and per device; setting it again is cheap next to a factorisation)
+  cudaFuncSetAttribute(k_dense_potrf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)POTRF_SMEM);
+  cudaFuncSetAttribute(k_dense_gemm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
+  cudaFuncSetAttribute(k_dense_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_SMEM);
   const int T = w.npad / DT;
   double* rhs = w.vec;
   double* y = w.vec + w.npad;
@@ -450,32 +448,29 @@ void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, cudaStream_t 
   // flops) stays on the caller's stream while the critical path (column update, diagonal factor, panel solve)
   // runs on an internal high-priority stream -- its few CTAs must not queue behind the thousands of the bulk
   // update.  Without the look-ahead the one-CTA diagonal factor (0.2 ms) sits between any two updates.
-  static cudaStream_t crit[64] = {};
-  static std::vector<cudaEvent_t> ev_panel[64], ev_upd[64];
-  int dev = 0;
-  cudaGetDevice(&dev);
-  dev &= 63;
-  if (!crit[dev]) {
+  if (!ds.crit) {
     int lo = 0, hi = 0;
     cudaDeviceGetStreamPriorityRange(&lo, &hi);
-    cudaStreamCreateWithPriority(&crit[dev], cudaStreamNonBlocking, hi);
+    cudaStreamCreateWithPriority(&ds.crit, cudaStreamNonBlocking, hi);
   }
-  while ((int)ev_panel[dev].size() < T + 1) {
+  while ((int)ds.ev_panel.size() < T + 1) {
     cudaEvent_t e1, e2;
     cudaEventCreateWithFlags(&e1, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&e2, cudaEventDisableTiming);
-    ev_panel[dev].push_back(e1);
-    ev_upd[dev].push_back(e2);
+    ds.ev_panel.push_back(e1);
+    ds.ev_upd.push_back(e2);
   }
-  cudaStream_t sc = crit[dev];
+  const std::vector<cudaEvent_t>& ev_panel_ = ds.ev_panel;
+  const std::vector<cudaEvent_t>& ev_upd_ = ds.ev_upd;
+  cudaStream_t sc = ds.crit;
   // (the critical stream starts after everything queued on st so far: the assembly and the diagonal blocks)
-  cudaEventRecord(ev_panel[dev][T], st);
-  cudaStreamWaitEvent(sc, ev_panel[dev][T], 0);
+  cudaEventRecord(ev_panel_[T], st);
+  cudaStreamWaitEvent(sc, ev_panel_[T], 0);
   for (int k = 0; k < T; ++k) {
     const int R = T - k - 1;
     if (k > 0) {
       // column k of update k - 1, after the bulk stream has finished update k - 2 on it
-      if (k > 1) cudaStreamWaitEvent(sc, ev_upd[dev][k - 2], 0);
+      if (k > 1) cudaStreamWaitEvent(sc, ev_upd_[k - 2], 0);
       k_dense_gemm<0><<<(unsigned)(R + 1), 512, GEMM_SMEM, sc>>>(w.S, w.ld, k - 1, w.linv, 1, R + 1);
       lc.launches++;
     }
@@ -484,8 +479,8 @@ void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, cudaStream_t 
     if (R > 0) {
       k_dense_gemm<1><<<(unsigned)R, 512, GEMM_SMEM, sc>>>(w.S, w.ld, k, w.linv, 0, R);
       lc.launches++;
-      cudaEventRecord(ev_panel[dev][k], sc);
-      cudaStreamWaitEvent(st, ev_panel[dev][k], 0);
+      cudaEventRecord(ev_panel_[k], sc);
+      cudaStreamWaitEvent(st, ev_panel_[k], 0);
       if (R > 1) {
         // columns >= k + 2 of update k (ordered after update k - 1 on the same stream)
         const int nt = (int)((long long)(R - 1) * R / 2);
@@ -494,10 +489,10 @@ void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, cudaStream_t 
         k_dense_gemm<0><<<(unsigned)nt, 512, GEMM_SMEM, st>>>(w.S, w.ld, k, w.linv, 2, nt);
         lc.launches++;
       }
-      cudaEventRecord(ev_upd[dev][k], st);
+      cudaEventRecord(ev_upd_[k], st);
     } else {
-      cudaEventRecord(ev_panel[dev][k], sc);
-      cudaStreamWaitEvent(st, ev_panel[dev][k], 0);      // the last diagonal factor joins the caller's stream
+      cudaEventRecord(ev_panel_[k], sc);
+      cudaStreamWaitEvent(st, ev_panel_[k], 0);      // the last diagonal factor joins the caller's stream
     }
   }
   for (int k = 0; k < T; ++k) k_dense_fwd<<<T - k, DT, 0, st>>>(w.S, w.ld, k, w.linv, rhs, y);

@@ -138,3 +138,39 @@ def test_device_resident_solve_equals_host_solve(engine):
     engine.ba_solve_device(t, lam=5.0, iterations=2)
     assert np.array_equal(t['cams'].cpu().numpy(), p1.cams)
     assert np.array_equal(t['pts'].cpu().numpy(), p1.pts)
+
+
+def test_c_abi_rejects_bad_indices(engine):
+    """The C-ABI validates the index arrays on the device (the Python wrapper's own checks are bypassed here by
+    corrupting the arrays after construction): INVALID_ARG, parameters untouched, and the context still works."""
+    from sfm_b200 import _capi, synthetic
+
+    def corrupt_cam_high(p):
+        p.obs_cam[p.num_obs // 2] = p.num_cams
+
+    def corrupt_cam_negative(p):
+        p.obs_cam[3] = -1
+
+    def corrupt_rowptr_order(p):
+        p.rowptr[5], p.rowptr[6] = p.rowptr[6] + 1, p.rowptr[5]
+
+    def corrupt_rowptr_end(p):
+        p.rowptr[-1] += 7
+
+    def corrupt_rowptr_start(p):
+        p.rowptr[0] = -4
+
+    for shape, scale in (('small', 1.0), ('venice', 0.3)):       # (the second one takes the ranged-upload path)
+        for corrupt in (corrupt_cam_high, corrupt_cam_negative, corrupt_rowptr_order, corrupt_rowptr_end,
+                        corrupt_rowptr_start):
+            p, _ = synthetic.make_shape(shape, scale)
+            corrupt(p)
+            cams0, pts0 = p.cams.copy(), p.pts.copy()
+            with pytest.raises(_capi.SfmbaError) as err:
+                engine.ba_solve_host(p, lam=5.0, iterations=1)
+            assert err.value.code == _capi.ERR_INVALID_ARG, corrupt.__name__
+            assert np.array_equal(p.cams, cams0) and np.array_equal(p.pts, pts0)
+    good, _ = synthetic.make_shape('small')
+    ref, _ = synthetic.make_shape('small')
+    res = engine.ba_solve_host(good, lam=5.0, iterations=1)
+    assert res.final_cost > 0.0 and not np.array_equal(good.cams, ref.cams)
