@@ -248,6 +248,8 @@ void launch_dense_factor_solve(const BaDev& d, const DenseWork& w, DenseStreams&
 void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 
 // ---- refiners (refine.cu) ------------------------------------------------------------------------
+void launch_validate_csr(int n_items, int num_obs, const int32_t* rowptr, const int32_t* idx, int bound,
+                         uint32_t* flags, cudaStream_t st, LaunchCounter& lc);
 void launch_triangulate(int num_pts, const double* projs, const int32_t* rowptr, const int32_t* obs_view,
                         const double* obs_uv, double* pts, double lambda, int iterations, uint32_t* flags,
                         cudaStream_t st, LaunchCounter& lc);

@@ -124,29 +124,37 @@ __global__ void k_sum_cost(const double* __restrict__ part, int n, Scalars* sc, 
 }
 
 // ---- index-free kernels behind sfmba_ba_cost / sfmba_residual_jacobian ---------------------------
-__device__ __forceinline__ void load_obs(const BaDev& d, int o, int& cam, double X[3], double b[2]) {
+// false (nothing loaded) when the observation's camera or point index lies outside the arrays
+__device__ __forceinline__ bool load_obs(const BaDev& d, int o, int& cam, double X[3], double b[2]) {
   cam = d.obs_cam[o];
   const int j = d.obs_pt[o];
+  if ((uint32_t)cam >= (uint32_t)d.V || (uint32_t)j >= (uint32_t)d.N) return false;
   const double* p = d.pts + 3 * (size_t)j;
   X[0] = p[0];
   X[1] = p[1];
   X[2] = p[2];
   normalise_obs(d.kinv ? d.kinv + 9 * (size_t)cam : nullptr, d.obs_uv[o], d.obs_uv[d.m + o], b);
+  return true;
 }
 
 // cost only: one lane per observation in point-major order, per-block partials in grp_cost
 __global__ void __launch_bounds__(256) k_cost(BaDev d) {
   __shared__ double red[32];
   double cost = 0.0;
+  bool bad = false;
   for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < d.m; o += gridDim.x * blockDim.x) {
     int cam;
     double X[3], b[2], r[2];
-    load_obs(d, o, cam, X, b);
+    if (!load_obs(d, o, cam, X, b)) {
+      bad = true;
+      continue;
+    }
     eval_obs<false>(d.camtab + (size_t)CAMTAB_STRIDE * cam, X, b, false, r, nullptr, nullptr);
     cost += r[0] * r[0] + r[1] * r[1];
   }
   cost = block_sum(cost, red);
   if (threadIdx.x == 0) d.grp_cost[blockIdx.x] = cost;
+  if (bad) atomicOr(&d.sc->flags, FLAG_BAD_INDEX);
 }
 
 // K1 alone (sfmba_residual_jacobian): SoA outputs, f32 (and optional f64 residuals)
@@ -160,7 +168,10 @@ __global__ void __launch_bounds__(256) k_residual_jacobian(BaDev d, int dvdc_qui
   for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < d.m; o += gridDim.x * blockDim.x) {
     int cam;
     double X[3], b[2], r[2], Jp[14], Jx[6];
-    load_obs(d, o, cam, X, b);
+    if (!load_obs(d, o, cam, X, b)) {               // outputs of this observation stay as they were
+      flags |= FLAG_BAD_INDEX;
+      continue;
+    }
     if (!eval_obs<true>(d.camtab + (size_t)CAMTAB_STRIDE * cam, X, b, dvdc_quirk != 0, r, Jp, Jx))
       flags |= FLAG_DEPTH_ZERO;
     cost += r[0] * r[0] + r[1] * r[1];

@@ -44,6 +44,8 @@ int read_flags(sfmba_ctx* ctx, uint32_t* dflags, uint32_t* host_flags, cudaStrea
   rc = sfm_check_cuda(ctx, cudaGetLastError(), "refine kernels");
   if (rc) return rc;
   if (host_flags) *host_flags = *pin;
+  if (*pin & SFMBA_FLAG_BAD_INDEX)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "rowptr is not a CSR over [0, num_obs] or an index is out of range");
   if (*pin & (SFMBA_FLAG_QW_NEAR_ZERO | SFMBA_FLAG_NONFINITE)) {
     char buf[64];
     snprintf(buf, sizeof(buf), "device numeric flags 0x%x", *pin);
@@ -302,9 +304,13 @@ int sfmba_ba_cost(sfmba_ctx* ctx, const sfmba_problem* problem, double* host_cos
   double* dev_cost = d.grp_cost;    // k_sum_cost reads the partials before thread 0 writes slot 0
   launch_cost(d, dev_cost, st, ctx->lc);
   double* pin = reinterpret_cast<double*>(ctx->pinned);
+  uint32_t* pin_flags = reinterpret_cast<uint32_t*>(pin + 1);
   cudaMemcpyAsync(pin, dev_cost, sizeof(double), cudaMemcpyDeviceToHost, st);
+  cudaMemcpyAsync(pin_flags, &d.sc->flags, sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
   rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "cost sync");
   if (rc) return rc;
+  if (*pin_flags & SFMBA_FLAG_BAD_INDEX)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "obs_cam / obs_pt has an index outside its array");
   if (host_cost) *host_cost = *pin;
   return sfm_check_cuda(ctx, cudaGetLastError(), "cost kernels");
 }
@@ -323,6 +329,7 @@ int sfmba_triangulate_refine_batched(sfmba_ctx* ctx, int32_t num_pts, int32_t nu
   if (rc) return rc;
   uint32_t* dflags = reinterpret_cast<uint32_t*>(fl);
   cudaMemsetAsync(dflags, 0, sizeof(uint32_t), st);
+  launch_validate_csr(num_pts, num_obs, rowptr, obs_view, num_projs, dflags, st, ctx->lc);
   launch_triangulate(num_pts, projs, rowptr, obs_view, obs_uv, pts, lambda, iterations, dflags, st, ctx->lc);
   return read_flags(ctx, dflags, host_flags, st);
 }
@@ -365,12 +372,15 @@ int sfmba_triangulate_linear_batched(sfmba_ctx* ctx, int32_t num_pts, int32_t nu
   if (rc) return rc;
   uint32_t* dflags = reinterpret_cast<uint32_t*>(fl);
   cudaMemsetAsync(dflags, 0, sizeof(uint32_t), st);
+  launch_validate_csr(num_pts, num_obs, rowptr, obs_view, num_projs, dflags, st, ctx->lc);
   launch_triangulate_linear(num_pts, projs, rowptr, obs_view, obs_uv, pts, front, dflags, st, ctx->lc);
   uint32_t* pin = reinterpret_cast<uint32_t*>(ctx->pinned);
   cudaMemcpyAsync(pin, dflags, sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
   if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "triangulate sync")) != 0) return rc;
   if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "triangulate kernel")) != 0) return rc;
   if (host_flags) *host_flags = *pin;
+  if (*pin & SFMBA_FLAG_BAD_INDEX)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "rowptr is not a CSR over [0, num_obs] or an index is out of range");
   if (*pin & SFMBA_FLAG_NONFINITE) return sfm_set_error(ctx, SFMBA_ERR_NUMERIC, "linear triangulation: point at infinity");
   return SFMBA_OK;
 }
@@ -419,6 +429,7 @@ int sfmba_pnp_refine_batched(sfmba_ctx* ctx, int32_t num_views, int32_t num_obs,
   if (rc) return rc;
   uint32_t* dflags = reinterpret_cast<uint32_t*>(fl);
   cudaMemsetAsync(dflags, 0, sizeof(uint32_t), st);
+  launch_validate_csr(num_views, num_obs, rowptr, nullptr, 0, dflags, st, ctx->lc);
   launch_pnp(num_views, rowptr, obs_xy, obs_X, rot, loc, lambda, iterations, row_packing_quirk != 0,
              dvdc_sign_quirk != 0, dflags, st, ctx->lc);
   return read_flags(ctx, dflags, host_flags, st);

@@ -9,6 +9,33 @@
 
 namespace sfmba {
 
+// rowptr must be a CSR over [0, num_obs] and idx (when given) must lie in [0, bound): the refiners index their
+// observation and projection arrays through them.  They return at once when this kernel has raised the flag.
+__global__ void k_validate_csr(int n_items, int num_obs, const int32_t* __restrict__ rowptr,
+                               const int32_t* __restrict__ idx, int bound, uint32_t* flags) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  bool bad = false;
+  if (j <= n_items) {
+    const int a = rowptr[j];
+    bad = a < 0 || a > num_obs;
+    if (j == 0 && a != 0) bad = true;
+    if (j == n_items && a != num_obs) bad = true;
+    if (j < n_items && a > rowptr[j + 1]) bad = true;
+  }
+  if (idx) {
+    const int stride = gridDim.x * blockDim.x;
+    for (int o = j; o < num_obs; o += stride)
+      if ((uint32_t)idx[o] >= (uint32_t)bound) bad = true;
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flags, FLAG_BAD_INDEX);
+}
+
+void launch_validate_csr(int n_items, int num_obs, const int32_t* rowptr, const int32_t* idx, int bound,
+                         uint32_t* flags, cudaStream_t st, LaunchCounter& lc) {
+  k_validate_csr<<<(n_items + 1 + 255) / 256, 256, 0, st>>>(n_items, num_obs, rowptr, idx, bound, flags);
+  lc.launches++;
+}
+
 // X -= inv(J^T J + lambda I3) J^T (proj - obs)     triangulation_processor.py:220-228
 __global__ void __launch_bounds__(128) k_triangulate(int num_pts, const double* __restrict__ projs,
                                                      const int32_t* __restrict__ rowptr,
@@ -16,7 +43,7 @@ __global__ void __launch_bounds__(128) k_triangulate(int num_pts, const double* 
                                                      const double* __restrict__ obs_uv, double* __restrict__ pts,
                                                      double lambda, int iterations, uint32_t* flags) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= num_pts) return;
+  if (j >= num_pts || (*flags & FLAG_BAD_INDEX)) return;
   const int a = rowptr[j], e = rowptr[j + 1];
   double X[3] = {pts[3 * (size_t)j], pts[3 * (size_t)j + 1], pts[3 * (size_t)j + 2]};
   uint32_t f = 0;
@@ -75,7 +102,7 @@ __global__ void __launch_bounds__(32 * PNP_WARPS) k_pnp(int num_views, const int
   __shared__ double s_par[PNP_WARPS][8];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int view = blockIdx.x * PNP_WARPS + w;
-  if (view >= num_views) return;   // whole warp exits together; no block-level barrier below
+  if (view >= num_views || (*flags & FLAG_BAD_INDEX)) return;   // whole warp exits together; no block-level barrier below
   const int a = rowptr[view], e = rowptr[view + 1];
   uint32_t f = 0;
   if (lane == 0) {
@@ -205,7 +232,7 @@ __global__ void __launch_bounds__(128) k_triangulate_linear(int num_pts, const d
                                                             double* __restrict__ pts, int32_t* __restrict__ front,
                                                             uint32_t* flags) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= num_pts) return;
+  if (j >= num_pts || (*flags & FLAG_BAD_INDEX)) return;
   const int a = rowptr[j], e = rowptr[j + 1];
   double U[4][4], V[4][4];
 #pragma unroll

@@ -170,7 +170,15 @@ def test_c_abi_rejects_bad_indices(engine):
                 engine.ba_solve_host(p, lam=5.0, iterations=1)
             assert err.value.code == _capi.ERR_INVALID_ARG, corrupt.__name__
             assert np.array_equal(p.cams, cams0) and np.array_equal(p.pts, pts0)
+    # the index-free cost pass reads obs_pt / obs_cam directly
+    for field, value in (('obs_pt', 3000), ('obs_pt', -1), ('obs_cam', 24)):
+        p, _ = synthetic.make_shape('small')
+        getattr(p, field)[100] = value
+        with pytest.raises(_capi.SfmbaError) as err:
+            engine.ba_cost(p)
+        assert err.value.code == _capi.ERR_INVALID_ARG, field
     good, _ = synthetic.make_shape('small')
     ref, _ = synthetic.make_shape('small')
+    assert engine.ba_cost(good) > 0.0
     res = engine.ba_solve_host(good, lam=5.0, iterations=1)
     assert res.final_cost > 0.0 and not np.array_equal(good.cams, ref.cams)

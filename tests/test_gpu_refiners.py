@@ -269,3 +269,44 @@ def test_linear_triangulation_matches_opencv(engine):
     ref = cv2.triangulatePoints(projs[0], projs[1], pairs[0][0:2], pairs[1][0:2])
     ref = (ref[0:3] / ref[3]).T
     assert np.max(np.abs(pts - ref) / np.maximum(1.0, np.abs(ref))) < 1e-8
+
+
+def test_refiners_reject_bad_indices(engine):
+    """rowptr / obs_view are validated on the device: INVALID_ARG instead of an out-of-bounds read."""
+    from sfm_b200 import _capi
+    rng = np.random.default_rng(11)
+    P, M = 5, 40
+    projs = np.tile(np.hstack((np.identity(3), np.zeros((3, 1)))), (P, 1, 1))
+    rowptr = (2 * np.arange(M + 1)).astype(np.int32)
+    obs_view = np.tile(np.array([0, 1], dtype=np.int32), M)
+    uv = rng.normal(0, 0.1, (2 * M, 2))
+    X0 = np.column_stack([rng.normal(0, 1, M), rng.normal(0, 1, M), rng.uniform(5, 9, M)])
+
+    def variants():
+        v = obs_view.copy(); v[17] = P
+        yield rowptr, v
+        v = obs_view.copy(); v[0] = -2
+        yield rowptr, v
+        r = rowptr.copy(); r[9], r[10] = r[10], r[9]
+        yield r, obs_view
+        r = rowptr.copy(); r[-1] += 1
+        yield r, obs_view
+        r = rowptr.copy(); r[0] = 1
+        yield r, obs_view
+
+    for r, v in variants():
+        with pytest.raises(_capi.SfmbaError) as err:
+            engine.triangulate_refine(projs, r, v, uv, X0, 0.5, 3)
+        assert err.value.code == _capi.ERR_INVALID_ARG
+        with pytest.raises(_capi.SfmbaError) as err:
+            engine.triangulate_linear(projs, r, v, uv)
+        assert err.value.code == _capi.ERR_INVALID_ARG
+    rot = np.tile(np.identity(3), (M, 1, 1))
+    loc = np.zeros((M, 3))
+    for r in (rowptr[::-1].copy(), np.where(np.arange(M + 1) == M, 2 * M + 3, rowptr).astype(np.int32)):
+        with pytest.raises(_capi.SfmbaError) as err:
+            engine.pnp_refine(r, uv, np.column_stack([uv, np.full(2 * M, 6.0)]), rot, loc, 0.5, 2)
+        assert err.value.code == _capi.ERR_INVALID_ARG
+    # and the valid inputs still run on the same context
+    out = engine.triangulate_refine(projs, rowptr, obs_view, uv, X0, 0.5, 3)
+    assert out.shape == (M, 3) and np.all(np.isfinite(out))
