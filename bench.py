@@ -326,7 +326,7 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--shape', default='venice')
     ap.add_argument('--scale', type=float, default=1.0)
-    ap.add_argument('--pcg-tol', type=float, default=1e-10)
+    ap.add_argument('--pcg-tol', type=float, default=1e-8)
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--pcg-max-iter', type=int, default=0, help='diagnostic: cap PCG iterations (0 = library default)')
     ap.add_argument('--profile-timed', action='store_true', help='keep per-kernel event timing on inside the timed region')

@@ -93,8 +93,9 @@ typedef struct {
   int32_t mode;              /* sfmba_mode                                                          */
   int32_t solver;            /* sfmba_solver                                                        */
   int32_t pcg_max_iter;      /* <= 0: default                                                       */
-  double  pcg_tol;           /* relative residual ||r|| <= tol ||g||;  <= 0: default 1e-10 (the step  */
-                             /* error this leaves is ~1e5 below the 1e-5 parity bar on poses/points) */
+  double  pcg_tol;           /* relative residual ||r|| <= tol ||g||;  <= 0: default 1e-8 (at Venice the */
+                             /* final cost then lies 2e-9 and the poses 9e-9 from a 1e-13 solve, three   */
+                             /* orders inside the parity bar: profiles/r1_sweep_pcg_tol.jsonl)           */
   int32_t dvdc_sign_quirk;   /* 1 = reproduce campose_processor.py:802-804 (reference), 0 = exact   */
   int32_t force_slow_path;   /* testing: route every tile through the long-track code path          */
   int32_t compute_costs;     /* 1 = fill sfmba_result.costs (one extra cost pass at the end)        */

@@ -40,7 +40,7 @@ class BaProcessor:
         self.last_result = None                  # SolveResult of the most recent BA call
         # engine knobs (reference behaviour by default)
         self.dvdc_sign_quirk = True
-        self.pcg_tol = 1e-10
+        self.pcg_tol = 1e-8
         self.use_gpu_index = False
 
     @property

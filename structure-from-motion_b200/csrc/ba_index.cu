@@ -47,7 +47,11 @@ __global__ void k_group_bounds(BaDev d) {
   d.grp_pt[g] = lo;
 }
 
-constexpr int HASH_SLOTS = 4096;
+// Cameras of one group are counted in a small open-addressing table: only groups with <= SEG_CAP distinct
+// cameras become a single chunk, so the insertion stops as soon as more have been seen (every thread can
+// add at most one more camera before it notices, which keeps the table below half full).
+constexpr int HASH_SLOTS = 512;
+static_assert(HASH_SLOTS >= 2 * (SEG_CAP + RUN_LANES), "table must hold SEG_CAP cameras plus one per thread");
 
 // lanes a chunk needs when every camera's observations are cut into runs of K
 __device__ __forceinline__ int lanes_needed(const int* cnt, int K, int* s_sum) {
@@ -90,22 +94,33 @@ __global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chu
     }
     if (threadIdx.x == 0) s_distinct = 0;
     __syncthreads();
-    int mine = 0;
-    for (int i = threadIdx.x; i < L; i += blockDim.x) {
-      const int cam = d.obs_cam[o0 + i];
-      unsigned h = ((unsigned)cam * 2654435761u) >> 20;
-      for (;;) {
-        const int slot = h & (HASH_SLOTS - 1);
-        const int prev = atomicCAS(&s_key[slot], -1, cam);
-        if (prev == -1 || prev == cam) {
-          if (prev == -1) ++mine;
-          atomicAdd(&s_cnt[slot], 1);
-          break;
+    // the loads of a thread's cameras are issued together, the table work follows
+    for (int i0 = threadIdx.x; i0 < L; i0 += 4 * RUN_LANES) {
+      int cams[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * RUN_LANES;
+        cams[u] = i < L ? d.obs_cam[o0 + i] : -1;
+      }
+      if (*(volatile int*)&s_distinct > SEG_CAP) break;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int cam = cams[u];
+        if (cam < 0) continue;
+        unsigned h = ((unsigned)cam * 2654435761u) >> 20;
+        for (;;) {
+          const int slot = h & (HASH_SLOTS - 1);
+          const int prev = atomicCAS(&s_key[slot], -1, cam);
+          if (prev == -1 || prev == cam) {
+            if (prev == -1) atomicAdd(&s_distinct, 1);
+            atomicAdd(&s_cnt[slot], 1);
+            break;
+          }
+          ++h;
         }
-        ++h;
+        if (*(volatile int*)&s_distinct > SEG_CAP) break;
       }
     }
-    if (mine) atomicAdd(&s_distinct, mine);
     __syncthreads();
     n = (L + SEG_CAP - 1) / SEG_CAP;
     if (s_distinct <= SEG_CAP) {

@@ -244,7 +244,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     if ((rc = carve(ctx, S_DENSE_LINV, (size_t)dw.npad * 128, &dw.linv)) != 0) return rc;
     if ((rc = carve(ctx, S_DENSE_VEC, (size_t)3 * dw.npad, &dw.vec)) != 0) return rc;
   }
-  const double tol = opt.pcg_tol > 0 ? opt.pcg_tol : 1e-10;
+  const double tol = opt.pcg_tol > 0 ? opt.pcg_tol : 1e-8;
   const int max_iter = opt.pcg_max_iter > 0 ? opt.pcg_max_iter : std::max(200, std::min(4 * n7, 5000));
   const bool quirk = opt.dvdc_sign_quirk != 0;
   const bool fine = opt.force_slow_path != 0;

@@ -68,7 +68,7 @@ void sfmba_default_options(sfmba_options* opt) {
   opt->mode = SFMBA_MODE_REFERENCE_FIXED;
   opt->solver = SFMBA_SOLVER_PCG;
   opt->pcg_max_iter = 0;
-  opt->pcg_tol = 1e-10;
+  opt->pcg_tol = 1e-8;
   opt->dvdc_sign_quirk = 1;
   opt->force_slow_path = 0;
   opt->compute_costs = 1;

@@ -127,7 +127,7 @@ class Engine:
         return buf.raw
 
     # -- options ----------------------------------------------------------------------------------
-    def make_options(self, lam=5.0, iterations=3, mode=_capi.MODE_REFERENCE_FIXED, pcg_tol=1e-10, pcg_max_iter=0,
+    def make_options(self, lam=5.0, iterations=3, mode=_capi.MODE_REFERENCE_FIXED, pcg_tol=1e-8, pcg_max_iter=0,
                      dvdc_sign_quirk=True, force_slow_path=False, compute_costs=True, solver=_capi.SOLVER_PCG,
                      huber_delta=0.0):
         opt = _capi.default_options()
