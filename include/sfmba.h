@@ -63,6 +63,12 @@ typedef enum { SFMBA_MODE_REFERENCE_FIXED = 0, SFMBA_MODE_ADAPTIVE_LM = 1 } sfmb
  * DENSE_CHOLESKY: the reduced camera matrix (7V x 7V, f64) is assembled and factored on the FP64 tensor
  * cores -- the direct solve of ba_processor.py:382; needs 8 (7V)^2 bytes, replicated on every rank.     */
 typedef enum { SFMBA_SOLVER_PCG = 0, SFMBA_SOLVER_DENSE_CHOLESKY = 1 } sfmba_solver;
+/* Block-Jacobi preconditioner of the PCG solve.  JACOBI: the 7x7 blocks of A + lambda I (the sums the matvec needs
+ * anyway).  SCHUR_JACOBI: the 7x7 diagonal blocks of the Schur complement S itself; costs 28 more running sums and the
+ * 2x2 point term Y = J_x D^-1 J_x^T per observation in the linearisation.  On the BAL-shaped problems both need the
+ * same number of iterations at every damping tried, so JACOBI is the default.  The solution is
+ * the same to the PCG tolerance either way.                                                                        */
+typedef enum { SFMBA_PRECOND_JACOBI = 0, SFMBA_PRECOND_SCHUR_JACOBI = 1 } sfmba_precond;
 
 /*
  * One BA problem (this rank's shard when world_size > 1: cameras replicated, points and their
@@ -99,7 +105,7 @@ typedef struct {
   int32_t dvdc_sign_quirk;   /* 1 = reproduce campose_processor.py:802-804 (reference), 0 = exact   */
   int32_t force_slow_path;   /* testing: route every tile through the long-track code path          */
   int32_t compute_costs;     /* 1 = fill sfmba_result.costs (one extra cost pass at the end)        */
-  int32_t reserved0;
+  int32_t precond;           /* sfmba_precond (PCG solver)                                          */
   double  lm_lambda_min;     /* adaptive mode clamps                                                */
   double  lm_lambda_max;
   double  huber_delta;       /* > 0: Huber loss on every observation's residual norm, in the units of the */

@@ -20,6 +20,7 @@ ERR_INVALID_ARG, ERR_CUDA, ERR_NCCL, ERR_NUMERIC, ERR_UNSUPPORTED, ERR_NO_DEVICE
 FLAG_QW_NEAR_ZERO, FLAG_DEPTH_ZERO, FLAG_NONFINITE, FLAG_PCG_MAXITER, FLAG_SINGULAR = 1, 2, 4, 8, 16
 MODE_REFERENCE_FIXED, MODE_ADAPTIVE_LM = 0, 1
 SOLVER_PCG, SOLVER_DENSE_CHOLESKY = 0, 1
+PRECOND_JACOBI, PRECOND_SCHUR_JACOBI = 0, 1
 SOLVER_PCG = 0
 
 
@@ -38,7 +39,7 @@ class Problem(C.Structure):
 class Options(C.Structure):
     _fields_ = [('lambda_', C.c_double), ('iterations', C.c_int32), ('mode', C.c_int32), ('solver', C.c_int32),
                 ('pcg_max_iter', C.c_int32), ('pcg_tol', C.c_double), ('dvdc_sign_quirk', C.c_int32),
-                ('force_slow_path', C.c_int32), ('compute_costs', C.c_int32), ('reserved0', C.c_int32),
+                ('force_slow_path', C.c_int32), ('compute_costs', C.c_int32), ('precond', C.c_int32),
                 ('lm_lambda_min', C.c_double), ('lm_lambda_max', C.c_double), ('huber_delta', C.c_double)]
 
 

@@ -128,6 +128,8 @@ struct BaDev {
   double* rec_w;                      // [chunk_bound][CHUNK_CAP] Huber weight of each record at the linearisation
                                       // point (robust solves only: written by k_linearize, read by the matvec)
   double huber_delta;                 // 0 = plain least squares
+  int schur_diag;                     // 1 = the linearisation also sums the diagonal blocks of B D^-1 B^T (Schur-Jacobi
+                                      // preconditioner, dense solver); 0 = those 28 entries of every row are zero
   int32_t* seg_cam;                   // [chunk_bound][SEG_CAP]   camera of each segment (V = unused)
   uint16_t* seg_lane0;                // [chunk_bound][SEG_RUN_STRIDE] first lane of each segment (+ end)
   int32_t* camrow_ptr;                // [V+1]  CSR: camera -> segment rows

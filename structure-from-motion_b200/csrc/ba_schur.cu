@@ -38,7 +38,8 @@ __host__ __device__ inline size_t gram_smem_bytes(const GramShape& s) {
 // Phase A (K2a, ba_processor.py:355-363): per point D_j = sum J_x^T J_x + lambda I, D_j^-1, v_j = D_j^-1 e_x
 // and the cost; phase B: the camera-side Gram sums.  One launch linearises the whole problem.
 // ROBUST: every observation enters with its Huber weight w = rho'(|r|^2) (J^T W J, J^T W r); the cost is sum rho
-template <bool ROBUST>
+// SCHUR: also the 28 sums of J_p^T Y J_p (diagonal blocks of B D^-1 B^T); without it those entries stay zero
+template <bool ROBUST, bool SCHUR>
 __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape sh, int dvdc_quirk, int g0) {
   extern __shared__ __align__(16) double smem[];
   const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
@@ -266,17 +267,21 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
         jp[13] = (G13 - v * G23) * iw;
       }
       // point terms: Y = J_x D^-1 J_x^T, rho = r - J_x v_j
-      double Dinv[6], vv[3];
-#pragma unroll
-      for (int e = 0; e < 6; ++e) Dinv[e] = Dv[e * pt_cap + ptl];
+      double vv[3];
 #pragma unroll
       for (int e = 0; e < 3; ++e) vv[e] = Dv[(6 + e) * pt_cap + ptl];
-      double t0[3], t1[3];
-      sym3_mul(Dinv, jx, t0);
-      sym3_mul(Dinv, jx + 3, t1);
-      double yuu = jx[0] * t0[0] + jx[1] * t0[1] + jx[2] * t0[2];
-      double yuv = jx[0] * t1[0] + jx[1] * t1[1] + jx[2] * t1[2];
-      double yvv = jx[3] * t1[0] + jx[4] * t1[1] + jx[5] * t1[2];
+      double yuu = 0.0, yuv = 0.0, yvv = 0.0;
+      if (SCHUR) {
+        double Dinv[6];
+#pragma unroll
+        for (int e = 0; e < 6; ++e) Dinv[e] = Dv[e * pt_cap + ptl];
+        double t0[3], t1[3];
+        sym3_mul(Dinv, jx, t0);
+        sym3_mul(Dinv, jx + 3, t1);
+        yuu = jx[0] * t0[0] + jx[1] * t0[1] + jx[2] * t0[2];
+        yuv = jx[0] * t1[0] + jx[1] * t1[1] + jx[2] * t1[2];
+        yvv = jx[3] * t1[0] + jx[4] * t1[1] + jx[5] * t1[2];
+      }
       const double rho0 = r0 - (jx[0] * vv[0] + jx[1] * vv[1] + jx[2] * vv[2]);
       const double rho1 = r1 - (jx[3] * vv[0] + jx[4] * vv[1] + jx[5] * vv[2]);
       // weighted sums: the left factor of every product below is w J_p, Y carries the second w of J_p^T (w Y w) J_p
@@ -296,8 +301,8 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
       double tu[7], tv[7];
 #pragma unroll
       for (int a = 0; a < 7; ++a) {
-        tu[a] = yuu * jp[a] + yuv * jp[7 + a];
-        tv[a] = yuv * jp[a] + yvv * jp[7 + a];
+        tu[a] = SCHUR ? yuu * jp[a] + yuv * jp[7 + a] : 0.0;
+        tv[a] = SCHUR ? yuv * jp[a] + yvv * jp[7 + a] : 0.0;
       }
       // two FMA sweeps (u-row products, then v-row products): 2 instructions per sum, all independent
       {
@@ -307,7 +312,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
 #pragma unroll
           for (int bcol = a; bcol < 7; ++bcol, ++e) {
             acc[e] = fma(jw[a], jp[bcol], acc[e]);
-            acc[28 + e] = fma(jw[a], tu[bcol], acc[28 + e]);
+            if (SCHUR) acc[28 + e] = fma(jw[a], tu[bcol], acc[28 + e]);
           }
         }
 #pragma unroll
@@ -318,7 +323,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
 #pragma unroll
           for (int bcol = a; bcol < 7; ++bcol, ++e) {
             acc[e] = fma(jw[7 + a], jp[7 + bcol], acc[e]);
-            acc[28 + e] = fma(jw[7 + a], tv[bcol], acc[28 + e]);
+            if (SCHUR) acc[28 + e] = fma(jw[7 + a], tv[bcol], acc[28 + e]);
           }
         }
 #pragma unroll
@@ -431,12 +436,14 @@ void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int 
     g1 = d.G;
   }
   if (g1 > g0) {
+    auto go = [&](auto kernel) {
+      cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      kernel<<<g1 - g0, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0, g0);
+    };
     if (d.huber_delta > 0.0) {
-      cudaFuncSetAttribute(k_linearize<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      k_linearize<true><<<g1 - g0, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0, g0);
+      if (d.schur_diag) go(k_linearize<true, true>); else go(k_linearize<true, false>);
     } else {
-      cudaFuncSetAttribute(k_linearize<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      k_linearize<false><<<g1 - g0, RUN_LANES, smem, st>>>(d, sh, dvdc_quirk ? 1 : 0, g0);
+      if (d.schur_diag) go(k_linearize<false, true>); else go(k_linearize<false, false>);
     }
     lc.launches++;
   }

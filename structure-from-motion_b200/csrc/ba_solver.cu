@@ -227,6 +227,9 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   int rc = sfm_setup_problem(ctx, pr, true, &d);
   if (rc != SFMBA_OK) return rc;
   d.huber_delta = opt.huber_delta;
+  if (opt.precond != SFMBA_PRECOND_JACOBI && opt.precond != SFMBA_PRECOND_SCHUR_JACOBI)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "precond is not an sfmba_precond");
+  d.schur_diag = (dense || opt.precond == SFMBA_PRECOND_SCHUR_JACOBI) ? 1 : 0;
   const int n7 = 7 * d.V;
   DenseWork dw;
   memset(&dw, 0, sizeof(dw));

@@ -129,7 +129,7 @@ class Engine:
     # -- options ----------------------------------------------------------------------------------
     def make_options(self, lam=5.0, iterations=3, mode=_capi.MODE_REFERENCE_FIXED, pcg_tol=1e-8, pcg_max_iter=0,
                      dvdc_sign_quirk=True, force_slow_path=False, compute_costs=True, solver=_capi.SOLVER_PCG,
-                     huber_delta=0.0):
+                     huber_delta=0.0, precond=_capi.PRECOND_JACOBI):
         opt = _capi.default_options()
         opt.solver = int(solver)
         opt.lambda_ = float(lam)
@@ -141,6 +141,7 @@ class Engine:
         opt.force_slow_path = 1 if force_slow_path else 0
         opt.compute_costs = 1 if compute_costs else 0
         opt.huber_delta = float(huber_delta)
+        opt.precond = int(precond)
         return opt
 
     @staticmethod

@@ -86,6 +86,33 @@ def test_slow_path_equals_fast_path(engine):
     assert close(p1.pts, p2.pts, 1e-9)
 
 
+@pytest.mark.parametrize('shape,lam', [('small', 5.0), ('ladybug', 5.0), ('ladybug', 1e-2)])
+def test_preconditioners_agree(engine, shape, lam):
+    """sfmba_options.precond changes the PCG preconditioner (7x7 blocks of A + lambda I against the diagonal
+    blocks of the Schur complement), not the system: tightly solved, both give the same parameters, and with
+    the robust loss too (the Schur-diagonal sums carry the weights)."""
+    from sfm_b200 import synthetic, _capi
+    for huber in (0.0, 0.004):
+        p1, _ = synthetic.make_shape(shape)
+        p2, _ = synthetic.make_shape(shape)
+        r1 = engine.ba_solve_host(p1, lam=lam, iterations=2, pcg_tol=1e-13, huber_delta=huber,
+                                  precond=_capi.PRECOND_JACOBI)
+        r2 = engine.ba_solve_host(p2, lam=lam, iterations=2, pcg_tol=1e-13, huber_delta=huber,
+                                  precond=_capi.PRECOND_SCHUR_JACOBI)
+        assert r1.flags == 0 and r2.flags == 0
+        assert close(p1.cams, p2.cams, 1e-10), max_rel(p1.cams, p2.cams)
+        assert close(p1.pts, p2.pts, 1e-10), max_rel(p1.pts, p2.pts)
+        assert abs(r1.final_cost - r2.final_cost) <= 1e-11 * r2.final_cost
+        assert r1.pcg_iterations <= r2.pcg_iterations + 4
+
+
+def test_precond_is_validated(engine):
+    from sfm_b200 import synthetic, _capi
+    prob, _ = synthetic.make_shape('tiny')
+    with pytest.raises(_capi.SfmbaError):
+        engine.ba_solve_host(prob, lam=5.0, iterations=1, precond=7)
+
+
 def test_long_tracks_and_unobserved_points(engine, oracle):
     """Tracks longer than a tile (every camera sees the point), points without observations
     (D = lambda I, ba_processor.py:359) and an empty leading / trailing point."""
