@@ -446,7 +446,14 @@ __device__ __forceinline__ double cam_y_from_rows(const BaDev& d, int cam, int l
 #pragma unroll
       for (int u = 0; u < 8; ++u) a += v[u];
     }
-    for (; k < r1; k += 2) a += d.part12[(size_t)k * MV_ACC + sub];
+    if (k < r1) {                                      // the last (up to seven) rows: loads first, same order of sums
+      double v[7];
+#pragma unroll
+      for (int u = 0; u < 7; ++u) v[u] = k + 2 * u < r1 ? d.part12[(size_t)(k + 2 * u) * MV_ACC + sub] : 0.0;
+#pragma unroll
+      for (int u = 0; u < 7; ++u)
+        if (k + 2 * u < r1) a += v[u];
+    }
   }
   a += __shfl_down_sync(0xffffffffu, a, 16);           // slot 0 + slot 1
   double T[MV_ACC];

@@ -366,14 +366,25 @@ __device__ __forceinline__ double cam_rows_sum64(const BaDev& d, int cam, double
   const double* p = d.part64 + e;
   double a = 0.0;
   int k = r0 + slot;
-  for (; k + 28 < r1; k += 32) {
-    double v[8];
+  // without the Schur-diagonal sums entries 28..55 of every row are zero: seven of a row's sixteen sectors are not read
+  const bool skip = !d.schur_diag && e >= 28 && e < 56;
+  if (!skip) {
+    for (; k + 28 < r1; k += 32) {
+      double v[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(k + 4 * u) * CAM_ACC];
+      for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(k + 4 * u) * CAM_ACC];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) a += v[u];
+      for (int u = 0; u < 8; ++u) a += v[u];
+    }
+    if (k < r1) {                                        // the last (up to seven) rows: loads first, same order of sums
+      double v[7];
+#pragma unroll
+      for (int u = 0; u < 7; ++u) v[u] = k + 4 * u < r1 ? p[(size_t)(k + 4 * u) * CAM_ACC] : 0.0;
+#pragma unroll
+      for (int u = 0; u < 7; ++u)
+        if (k + 4 * u < r1) a += v[u];
+    }
   }
-  for (; k < r1; k += 4) a += p[(size_t)k * CAM_ACC];
   if (slot) sh[slot - 1][e] = a;
   __syncthreads();
   if (slot == 0) a = ((a + sh[0][e]) + sh[1][e]) + sh[2][e];
