@@ -282,6 +282,7 @@ def run_ours(args):
             'config': {'workload': workload_name(args.shape, V, N, m, args.pcg_tol),
                        'parallelism': 'points sharded over %d GPU(s), cameras replicated' % world,
                        'pcg_iterations_per_lm_iteration': pcg_iters / max(1, LM_ITERS * args.steps),
+                       'preconditioner': 'block-Jacobi on A + lambda I (sfmba_options.precond default)',
                        'l2': 'inputs larger than L2 (>1 GB streamed per matvec)'},
             'jacobian_schur_obs_per_sec': (m / (k12_ms * 1e-3)) if k12_ms > 0 else None,
             'final_cost': res.final_cost, 'initial_cost': res.initial_cost,

@@ -72,6 +72,7 @@ void sfmba_default_options(sfmba_options* opt) {
   opt->dvdc_sign_quirk = 1;
   opt->force_slow_path = 0;
   opt->compute_costs = 1;
+  opt->precond = SFMBA_PRECOND_JACOBI;
   opt->lm_lambda_min = 1e-12;
   opt->lm_lambda_max = 1e12;
 }
