@@ -284,7 +284,10 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
       double2 b = make_double2(0.0, 0.0);
       if (lane < nlanes) {
         const int sg = s.lane_seg[lane];
-        const int idx = s.seg_start[sg] + (lane - s.seg_lane0[sg]) * K + k;
+        // the lanes of a segment take its sorted observations round-robin: at trip k they read neighbouring
+        // observations (neighbouring points: fewer shared-memory bank conflicts) and their lengths differ by <= 1
+        const int nl = s.seg_lane0[sg + 1] - s.seg_lane0[sg];
+        const int idx = s.seg_start[sg] + k * nl + (lane - s.seg_lane0[sg]);
         if (idx < s.seg_start[sg + 1]) {
           const uint32_t key = s.key[idx];
           const int pos = (int)(key & 2047u);
