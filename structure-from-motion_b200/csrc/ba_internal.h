@@ -67,7 +67,9 @@ struct Scalars {
   uint32_t ticket_a;     // "last block done" tickets of the multi-CTA PCG kernels
   uint32_t ticket_b;
   double costs[SFMBA_MAX_COST_HISTORY];
+  double alpha_hist[8];  // step lengths of the first PCG_UBUF iterations of the current solve
 };
+constexpr int PCG_UBUF = 8;            // PCG iterations whose per-point u_j are kept for the back-substitution
 
 // One 32-byte load tells a tile CTA everything it needs to start staging its group.
 struct GroupMeta {
@@ -140,6 +142,9 @@ struct BaDev {
   double* camtab;                     // [V][16]
   double* dinv;                       // [6][N] symmetric packing 00 01 02 11 12 22
   double* vj;                         // [3][N] D^-1 e_x
+  double* ubuf;                       // [PCG_UBUF][3][N] u_j = D_j^-1 W_j^T p_i of PCG iteration i < PCG_UBUF: with the step
+                                      // lengths alpha_i (Scalars::alpha_hist) their sum is D^-1 B^T delta_p, so the
+                                      // back-substitution of a short solve needs no pass over the observations
   double* grp_cost;                   // [max(G, cost grid)]
   double* part64;                     // [chunk_bound*SEG_CAP][CAM_ACC] segment rows of the Gram sums
   double* cam_acc;                    // [V][CAM_ACC] (+ 8 trailing doubles: local cost at [V*CAM_ACC])
@@ -215,6 +220,7 @@ void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // p
 void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
                      cudaStream_t st, LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
+void launch_backsub_points(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_model_decrease(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

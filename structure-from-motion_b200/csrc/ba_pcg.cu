@@ -172,6 +172,14 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
     cp_async_wait_all();
     return;
   }
+  // PCG matvec number pcg_iters of this solve (0-based): its u_j = D_j^-1 W_j^T p are kept, written the moment they
+  // are formed.  x = sum alpha_i p_i, so D^-1 B^T delta_p = sum alpha_i u^(i) and the back-substitution of a short
+  // solve is one pass over the points (k_backsub_points)
+  double* ukeep = nullptr;
+  if (!BACKSUB) {
+    const int pcg_it = d.sc->pcg_iters;
+    if (pcg_it < PCG_UBUF) ukeep = d.ubuf + (size_t)pcg_it * 3 * (size_t)d.N + pt0;
+  }
   // stage one chunk: async tables, then gather the camera constants of its segments
   auto stage = [&](int c, bool with_iter) {
     stage_chunk_async(d, c, ci, cs);
@@ -308,6 +316,10 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
           a0 = u[0];
           a1 = u[1];
           a2 = u[2];
+          if (ukeep) {
+#pragma unroll
+            for (int e = 0; e < 3; ++e) ukeep[e * (size_t)d.N + j] = u[e];
+          }
         }
       }
       if (!(BACKSUB && single)) {
@@ -339,6 +351,10 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
         tacc[j] = u[0];
         tacc[pt_cap + j] = u[1];
         tacc[2 * pt_cap + j] = u[2];
+        if (ukeep) {
+#pragma unroll
+          for (int e = 0; e < 3; ++e) ukeep[e * (size_t)d.N + j] = u[e];
+        }
       }
     }
     if (!BACKSUB) __syncthreads();
@@ -668,6 +684,7 @@ __global__ void __launch_bounds__(256) k_pcg_update(BaDev d, int q_grid, double 
   if (newflags) atomicOr(&sc->flags, newflags);
   sc->pq = pq_all;
   sc->alpha = alpha;
+  if (!INIT && it_old < PCG_UBUF) sc->alpha_hist[it_old] = alpha;
   sc->beta = INIT ? 0.0 : rz_new / rz_old;
   sc->rz = rz_new;
   sc->rr = rr;
@@ -675,6 +692,26 @@ __global__ void __launch_bounds__(256) k_pcg_update(BaDev d, int q_grid, double 
   if (d.host_sig)
     *(volatile unsigned long long*)d.host_sig =
         ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
+}
+
+// Back-substitution of a PCG solve of at most PCG_UBUF iterations, pts_j += v_j - D_j^-1 W_j^T delta_p
+// (ba_processor.py:405-406), from what the matvecs left: D^-1 W^T delta_p = sum_i alpha_i u^(i), summed in iteration
+// order.  One thread per point.
+__global__ void __launch_bounds__(256) k_backsub_points(BaDev d) {
+  const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t N = (size_t)d.N;
+  if (j >= N) return;
+  const int iters = d.sc->pcg_iters;
+  double u[3] = {0.0, 0.0, 0.0};
+  for (int i = 0; i < iters && i < PCG_UBUF; ++i) {
+    const double alpha = d.sc->alpha_hist[i];
+    const double* ub = d.ubuf + (size_t)i * 3 * N + j;
+#pragma unroll
+    for (int e = 0; e < 3; ++e) u[e] += alpha * ub[e * N];
+  }
+  double* p = d.pts + 3 * j;
+#pragma unroll
+  for (int e = 0; e < 3; ++e) p[e] = p[e] + (d.vj[e * N + j] - u[e]);
 }
 
 // cams += delta_p; q /= |q|                      (ba_processor.py:383-392)
@@ -834,6 +871,12 @@ void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigne
 
 void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
   k_cam_iter<<<(d.V + 127) / 128, 128, 0, st>>>(d, vec, 0, dvdc_quirk ? 1 : 0);
+  lc.launches++;
+}
+
+void launch_backsub_points(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
+  if (d.N <= 0) return;
+  k_backsub_points<<<(d.N + 255) / 256, 256, 0, st>>>(d);
   lc.launches++;
 }
 

@@ -58,7 +58,7 @@ cudaError_t sfmba_ctx::reserve(int slot, size_t bytes, void** out) {
 namespace {
 
 enum Slot {
-  S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_CAM_ACC, S_ABLK, S_MINV,
+  S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_UBUF, S_CAM_ACC, S_ABLK, S_MINV,
   S_CAMIT, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
   S_CHUNK_INFO, S_REC_B, S_REC_IX, S_REC_W, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
@@ -111,6 +111,7 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
     CARVE(S_GRP_META, d.G + 1, grp_meta);
     CARVE(S_DINV, 6 * N, dinv);
     CARVE(S_VJ, 3 * N, vj);
+    CARVE(S_UBUF, (size_t)PCG_UBUF * 3 * N, ubuf);
     CARVE(S_CAM_ACC, V * CAM_ACC + 8, cam_acc);
     CARVE(S_ABLK, V * 49, ablk);
     CARVE(S_MINV, V * 49, minv);
@@ -160,12 +161,15 @@ struct PhaseTimer {
   // phase timing needs event pairs; to stay asynchronous we record (begin,end) pairs lazily and
   // resolve them after the final synchronisation
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> spans;
-  std::vector<cudaEvent_t> pool;
+  // events come from a pool the context keeps: creating and destroying ~40 of them per solve was host time spent
+  // between two solves, with the GPU idle
   cudaEvent_t get() {
-    cudaEvent_t e;
-    cudaEventCreate(&e);
-    pool.push_back(e);
-    return e;
+    if (ctx->timer_next == ctx->timer_events.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      ctx->timer_events.push_back(e);
+    }
+    return ctx->timer_events[ctx->timer_next++];
   }
   cudaEvent_t begin() {
     cudaEvent_t e = get();
@@ -201,9 +205,8 @@ struct PhaseTimer {
       }
     }
     kspans.clear();
-    for (auto e : pool) cudaEventDestroy(e);
-    pool.clear();
     spans.clear();
+    ctx->timer_next = 0;
   }
 };
 
@@ -267,6 +270,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   d.host_sig = (!multi || peer) ? reinterpret_cast<unsigned long long*>(ctx->pinned) : nullptr;
 
   PhaseTimer pt{ctx, st};
+  ctx->timer_next = 0;                     // (a solve that failed half-way left its events checked out)
   cudaEvent_t t_total = pt.begin();
 
   // scalars (pageable source: the copy is staged by the driver before the call returns)
@@ -386,6 +390,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       launch_cam_rows(d, d.x, quirk, st, lc);
     }
     const int tail_mode = !multi ? 1 : (peer ? 3 : 2);
+    int pcg_finished = -1;                 // iterations of this PCG solve when the host knows the number
     auto launch_iteration = [&]() -> int {
       cudaEvent_t kb = pt.kbegin();
       launch_matvec(d, ts, false, quirk, st, lc);
@@ -446,6 +451,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       }
       if (!done && (rc = wait_for(launched)) != 0) return rc;   // max_iter reached: the kernel sets done itself
       ctx->pcg_hint = finished;
+      pcg_finished = finished;
     } else {
       const int batch = 4;
       int32_t* done_host = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ctx->pinned) + 16);
@@ -474,10 +480,15 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
 
     t0 = pt.begin();
     if (adaptive) launch_lm_model_decrease(d, st, lc);
-    // (the last k_pcg_tail of the solve left camit = rows of x, the back-substitution direction)
     {
       cudaEvent_t kb = pt.kbegin();
-      launch_matvec(d, ts, true, quirk, st, lc);        // back-substitution: pts += v - Dinv B^T dp
+      if (pcg_finished >= 0 && pcg_finished <= PCG_UBUF) {
+        launch_backsub_points(d, st, lc);               // the PCG matvecs have left u_j = Dinv B^T p_i per point
+      } else {
+        // dense solve, NCCL fallback or a long PCG solve: camit holds the rows of x (launch_cam_rows / the last
+        // k_cam_iter of the solve), one tile pass forms pts += v - Dinv B^T dp
+        launch_matvec(d, ts, true, quirk, st, lc);
+      }
       pt.kend("backsub", kb);
     }
     launch_update_cams(d, st, lc);

@@ -141,6 +141,8 @@ int sfmba_destroy(sfmba_ctx* ctx) {
   for (auto& b : ctx->bufs) b.release();
   for (auto& b : ctx->host_stage) b.release();
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  for (auto e : ctx->timer_events) cudaEventDestroy(e);
+  ctx->timer_events.clear();
   ctx->dense_streams.release();
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   if (ctx->io.copy) {

@@ -79,6 +79,8 @@ struct sfmba_ctx {
   sfmba::DenseStreams dense_streams;   // dense-Cholesky look-ahead (dense.cu)
   unsigned pcg_epoch = 0;        // id of the current PCG solve (see host_sig)
   int pcg_hint = 0;              // iterations the previous PCG solve needed
+  std::vector<cudaEvent_t> timer_events;   // phase-timer events, created once and reused by every solve
+  size_t timer_next = 0;
 
   cudaError_t reserve(int slot, size_t bytes, void** out);
 };
