@@ -106,6 +106,21 @@ def test_preconditioners_agree(engine, shape, lam):
         assert r1.pcg_iterations <= r2.pcg_iterations + 4
 
 
+def test_long_pcg_solve_takes_the_tile_back_substitution(engine, oracle):
+    """A PCG solve of more than eight iterations (weak damping, tight tolerance) cannot use the per-point sums the
+    matvecs keep (sfmba: k_backsub_points) and falls back to the tile pass over the observations; both must give
+    the reference's step (ba_processor.py:405-406)."""
+    from sfm_b200 import synthetic
+    prob, _ = synthetic.make_shape('small')
+    b = prob.obs_uv.T.astype(np.float64)
+    cams, pts, costs = oracle.ba_solve(prob.cams, prob.pts, prob.obs_cam, prob.obs_pt, b, 1e-2, 2)
+    res = engine.ba_solve_host(prob, lam=1e-2, iterations=2, pcg_tol=1e-12)
+    assert res.pcg_iterations > 2 * 8
+    assert close(prob.cams, cams, PARAM_TOL), max_rel(prob.cams, cams)
+    assert close(prob.pts, pts, PARAM_TOL), max_rel(prob.pts, pts)
+    assert abs(res.final_cost - costs[-1]) <= COST_RTOL * costs[-1]
+
+
 def test_precond_is_validated(engine):
     from sfm_b200 import synthetic, _capi
     prob, _ = synthetic.make_shape('tiny')
