@@ -34,10 +34,10 @@ LM_ITERS = 3
 LAMBDA = 5.0
 CPU_SAMPLE_SCALE = 0.25
 # ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of ONE k_matvec<0> launch at the full Venice
-# shape on one GPU (profiles/r1_ncu_full_v49_summary.txt: 104.56 MB read + 9.97 MB written); the same for the one
-# k_linearize<0, 0> launch of that capture (155.09 MB read + 132.58 MB written)
-NCU_DRAM_BYTES_PER_MATVEC = {('venice', 1.0, 1): 114.52e6}
-NCU_DRAM_BYTES_PER_LINEARIZE = {('venice', 1.0, 1): 287.67e6}
+# shape on one GPU (profiles/r1_ncu_full_v55_summary.txt, mean of two launches: 104.52 MB read + 19.65 MB written); the same for the one
+# k_linearize<0, 0> launch of that capture (155.09 MB read + 133.70 MB written)
+NCU_DRAM_BYTES_PER_MATVEC = {('venice', 1.0, 1): 124.17e6}
+NCU_DRAM_BYTES_PER_LINEARIZE = {('venice', 1.0, 1): 288.79e6}
 
 
 def _peaks():
@@ -292,13 +292,13 @@ def run_ours(args):
             'roofline': {'kernel': k3_name,
                          'bound': 'hbm', 'achieved': k3_gbs, 'peak': peak, 'unit': 'GB/s', 'frac': k3_gbs / peak,
                          'peak_kind': peak_kind, 'traffic': NCU_DRAM_BYTES_PER_MATVEC.get((args.shape, args.scale, world)),
-                         'traffic_source': 'profiles/r1_ncu_full_v49_summary.txt (k_matvec<0, 0>, one launch)',
+                         'traffic_source': 'profiles/r1_ncu_full_v55_summary.txt (k_matvec<0, 0>, one launch)',
                          'algorithmic_bytes': k3_bytes, 'ms': k3_ms},
             'roofline_jacobian_schur': {'kernel': 'K1+K2 = k_linearize (residuals, Jacobians, point Schur blocks and camera Gram rows in one launch; J never stored)', 'bound': 'hbm',
                                         'achieved': k12_gbs, 'peak': peak, 'unit': 'GB/s', 'frac': k12_gbs / peak,
                                         'algorithmic_bytes': k12_bytes, 'ms': k12_ms,
                                         'traffic': NCU_DRAM_BYTES_PER_LINEARIZE.get((args.shape, args.scale, world)),
-                                        'traffic_source': 'profiles/r1_ncu_full_v49_summary.txt (k_linearize<0, 0>, one launch)'},
+                                        'traffic_source': 'profiles/r1_ncu_full_v55_summary.txt (k_linearize<0, 0>, one launch)'},
             'e2e': {'value': LM_ITERS * e2e_steps / e2e_s, 'unit': 'LM iterations/s', 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'ms_per_step': e2e_s / e2e_steps * 1e3,
                     'kernel_launches_per_step': launches_e2e},
