@@ -44,6 +44,11 @@ def test_struct_layouts_match_header(lib):
     assert ctypes.sizeof(_capi.Problem) == 16 + 7 * 8
     opt = _capi.default_options()
     assert (opt.lambda_, opt.iterations, opt.mode, opt.dvdc_sign_quirk) == (5.0, 3, 0, 1)   # ba_processor.py:24
+    # solver defaults (sfmba_default_options fills the struct on the C side: a wrong field offset would show here)
+    assert (opt.solver, opt.precond, opt.pcg_tol, opt.pcg_max_iter) == (_capi.SOLVER_PCG, _capi.PRECOND_JACOBI, 1e-8, 0)
+    assert (opt.compute_costs, opt.force_slow_path, opt.huber_delta) == (1, 0, 0.0)
+    assert (opt.lm_lambda_min, opt.lm_lambda_max) == (1e-12, 1e12)
+    assert ctypes.sizeof(_capi.Options) == 8 + 4 * 4 + 8 + 4 * 4 + 3 * 8
     assert ctypes.sizeof(_capi.Result) == 3 * 8 + 6 * 4 + 64 * 8 + 6 * 4 + 2 * 4
 
 
