@@ -26,42 +26,7 @@ import sfm_b200                      # noqa: E402
 from sfm_b200 import synthetic       # noqa: E402
 
 
-def tri_problem(M, rng):
-    P = 200
-    K = np.array([[569.0, 0, 640.0], [0, 569.0, 480.0], [0, 0, 1.0]])
-    projs = np.zeros((P, 3, 4))
-    for i in range(P):
-        ang = 0.2 * np.sin(i / 30.0)
-        R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
-        C = np.array([[i * 0.2], [0.0], [0.0]])
-        projs[i] = K @ np.hstack((R.T, -R.T @ C))
-    n = rng.integers(2, 7, M)
-    rowptr = np.zeros(M + 1, dtype=np.int32)
-    rowptr[1:] = np.cumsum(n)
-    first = rng.integers(0, P - 6, M)
-    obs_view = (np.repeat(first, n) + (np.arange(rowptr[-1]) - np.repeat(rowptr[:-1], n))).astype(np.int32)
-    obs_pt = np.repeat(np.arange(M), n)
-    X = np.stack([first * 0.2 + rng.uniform(-2, 2, M), rng.uniform(-2, 2, M), rng.uniform(6, 14, M)], 1)
-    ph = np.einsum('mck,mk->mc', projs[obs_view][:, :, 0:3], X[obs_pt]) + projs[obs_view][:, :, 3]
-    uv = ph[:, 0:2] / ph[:, 2:3] + rng.normal(0, 0.5, (rowptr[-1], 2))
-    return projs, rowptr, obs_view, uv, X + rng.normal(0, 0.05, X.shape)
-
-
-def pnp_problem(P, rng):
-    from scipy.spatial.transform import Rotation
-    n = rng.integers(80, 121, P)
-    rowptr = np.zeros(P + 1, dtype=np.int32)
-    rowptr[1:] = np.cumsum(n)
-    m = int(rowptr[-1])
-    R = Rotation.from_rotvec(rng.normal(0, 0.2, (P, 3))).as_matrix()
-    C = rng.normal(0, 1, (P, 3))
-    pc = np.stack([rng.uniform(-3, 3, m), rng.uniform(-2, 2, m), rng.uniform(5, 15, m)], 1)
-    view = np.repeat(np.arange(P), n)
-    X = np.einsum('mij,mj->mi', R[view], pc) + C[view]
-    xy = pc[:, 0:2] / pc[:, 2:3] + rng.normal(0, 1e-3, (m, 2))
-    rots = np.einsum('pij,pjk->pik', Rotation.from_rotvec(rng.normal(0, 0.01, (P, 3))).as_matrix(), R)
-    locs = C + rng.normal(0, 0.05, (P, 3))
-    return rowptr, xy, X, rots, locs
+tri_problem, pnp_problem = synthetic.tri_problem, synthetic.pnp_problem
 
 
 def timed(fn, reps=3):

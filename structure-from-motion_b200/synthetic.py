@@ -163,3 +163,45 @@ def shard_problem(p: BAProblem, world: int, rank: int) -> BAProblem:
     return BAProblem(cams=p.cams.copy(), pts=p.pts[p0:p1].copy(), obs_uv=p.obs_uv[:, o0:o1].copy(),
                      obs_cam=p.obs_cam[o0:o1].copy(), obs_pt=p.obs_pt[o0:o1] - p0,
                      rowptr=p.rowptr[p0:p1 + 1] - o0, kinv=None if p.kinv is None else p.kinv.copy())
+
+
+# ---- config C3 of BASELINE.json: batched nonlinear triangulation / nonlinear PnP (a18, a19) --------------------
+def tri_problem(M: int, rng, P: int = 200):
+    """M points with 2..6 observations each out of P projections on a slowly turning track.  Returns
+    (projs (P,3,4), rowptr (M+1,) i32, obs_view (m,) i32, uv (m,2) pixels with 0.5 px noise, X0 (M,3) perturbed start)."""
+    K = np.array([[569.0, 0, 640.0], [0, 569.0, 480.0], [0, 0, 1.0]])
+    projs = np.zeros((P, 3, 4))
+    for i in range(P):
+        ang = 0.2 * np.sin(i / 30.0)
+        R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+        C = np.array([[i * 0.2], [0.0], [0.0]])
+        projs[i] = K @ np.hstack((R.T, -R.T @ C))
+    n = rng.integers(2, 7, M)
+    rowptr = np.zeros(M + 1, dtype=np.int32)
+    rowptr[1:] = np.cumsum(n)
+    first = rng.integers(0, P - 6, M)
+    obs_view = (np.repeat(first, n) + (np.arange(rowptr[-1]) - np.repeat(rowptr[:-1], n))).astype(np.int32)
+    obs_pt = np.repeat(np.arange(M), n)
+    X = np.stack([first * 0.2 + rng.uniform(-2, 2, M), rng.uniform(-2, 2, M), rng.uniform(6, 14, M)], 1)
+    ph = np.einsum('mck,mk->mc', projs[obs_view][:, :, 0:3], X[obs_pt]) + projs[obs_view][:, :, 3]
+    uv = ph[:, 0:2] / ph[:, 2:3] + rng.normal(0, 0.5, (rowptr[-1], 2))
+    return projs, rowptr, obs_view, uv, X + rng.normal(0, 0.05, X.shape)
+
+
+def pnp_problem(P: int, rng):
+    """P views with 80..120 observations each.  Returns (rowptr (P+1,) i32, xy (m,2) normalised observations,
+    X (m,3) world points, rots (P,3,3) and locs (P,3): the perturbed starting poses)."""
+    from scipy.spatial.transform import Rotation
+    n = rng.integers(80, 121, P)
+    rowptr = np.zeros(P + 1, dtype=np.int32)
+    rowptr[1:] = np.cumsum(n)
+    m = int(rowptr[-1])
+    R = Rotation.from_rotvec(rng.normal(0, 0.2, (P, 3))).as_matrix()
+    C = rng.normal(0, 1, (P, 3))
+    pc = np.stack([rng.uniform(-3, 3, m), rng.uniform(-2, 2, m), rng.uniform(5, 15, m)], 1)
+    view = np.repeat(np.arange(P), n)
+    X = np.einsum('mij,mj->mi', R[view], pc) + C[view]
+    xy = pc[:, 0:2] / pc[:, 2:3] + rng.normal(0, 1e-3, (m, 2))
+    rots = np.einsum('pij,pjk->pik', Rotation.from_rotvec(rng.normal(0, 0.01, (P, 3))).as_matrix(), R)
+    locs = C + rng.normal(0, 0.05, (P, 3))
+    return rowptr, xy, X, rots, locs
