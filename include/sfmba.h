@@ -161,6 +161,24 @@ SFMBA_API int sfmba_residual_jacobian(sfmba_ctx* ctx, const sfmba_problem* probl
                             double* out_cost, void* stream);
 SFMBA_API int sfmba_ba_cost(sfmba_ctx* ctx, const sfmba_problem* problem, double* host_cost, void* stream);
 
+/* ---- sfmba_ba_cost without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernels and same bits as sfmba_ba_cost, but the scratch they need (camera
+ * table, per-CTA partial sums, flag word) is a fixed file-scope device array (2.1 MB, held by every GPU that
+ * loads the library until the process exits) instead of context workspace, so no ctx is needed and nothing on
+ * the path calls cudaMalloc / cudaFree.  Limit: num_cams <= SFMBA_NOALLOC_MAX_CAMS (any num_pts / num_obs);
+ * more cameras return SFMBA_ERR_UNSUPPORTED with a message in sfmba_last_error(NULL).
+ *   device     CUDA device index (made current); every pointer is a device pointer on it; obs_pt is required
+ *   out_cost   device f64 [1]: sum ||b - f||^2
+ *   out_flags  device u32 [1] or NULL: SFMBA_FLAG_* raised by the kernels (SFMBA_FLAG_BAD_INDEX: an index outside
+ *              its array; that observation is skipped)
+ * Asynchronous on `stream`; the caller synchronises before reading the outputs.  All calls on one device share
+ * the scratch, which keeps the last call's contents (each call clears what must start at zero): calls that
+ * overlap on the GPU -- two streams, or two threads -- race on it and must be serialised by the caller.        */
+#define SFMBA_NOALLOC_MAX_CAMS 16384
+SFMBA_API int sfmba_ba_cost_noalloc(int device, const sfmba_problem* problem, double* out_cost, uint32_t* out_flags,
+                          void* stream);
+
 /* ---- a18: TriangulationProcessor.nonlinear_triangulate (triangulation_processor.py:160-234),
  * batched over points with a CSR of (view, observation) per point.
  *   projs   f64 [P][12] row-major 3x4 projection matrices (K included by the caller)

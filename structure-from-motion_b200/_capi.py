@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get('SFMBA_LIB') or os.path.join(_HERE, 'libsfmba.so')
 
 SFMBA_MAX_COST_HISTORY = 64
+NOALLOC_MAX_CAMS = 16384
 
 OK = 0
 ERR_INVALID_ARG, ERR_CUDA, ERR_NCCL, ERR_NUMERIC, ERR_UNSUPPORTED, ERR_NO_DEVICE = -1, -2, -3, -4, -5, -6
@@ -66,6 +67,7 @@ SYMBOLS = {
     'sfmba_ba_solve_host': (C.c_int, [_vp, C.POINTER(Problem), C.POINTER(Options), C.POINTER(Result)]),
     'sfmba_residual_jacobian': (C.c_int, [_vp, C.POINTER(Problem), C.c_int, _vp, _vp, _vp, _vp, _vp, _vp]),
     'sfmba_ba_cost': (C.c_int, [_vp, C.POINTER(Problem), C.POINTER(_f64), _vp]),
+    'sfmba_ba_cost_noalloc': (C.c_int, [C.c_int, C.POINTER(Problem), _vp, _vp, _vp]),
     'sfmba_triangulate_refine_batched': (C.c_int, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _i32,
                                                    C.POINTER(C.c_uint32), _vp]),
     'sfmba_triangulate_refine_batched_host': (C.c_int, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _i32,

@@ -12,7 +12,7 @@ CSRC = os.path.join(HERE, 'csrc')
 OBJ = os.path.join(HERE, 'build')
 LIB = os.path.join(HERE, 'libsfmba.so')
 SOURCES = ['ba_index.cu', 'ba_linearize.cu', 'ba_schur.cu', 'ba_pcg.cu', 'dense.cu', 'ba_solver.cu', 'refine.cu', 'ransac.cu',
-           'visibility.cu', 'nccl_dl.cu', 'peer_window.cu', 'capi.cu']
+           'visibility.cu', 'noalloc.cu', 'nccl_dl.cu', 'peer_window.cu', 'capi.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden', '--expt-relaxed-constexpr']
 
