@@ -47,7 +47,9 @@ typedef enum {
   SFMBA_ERR_NCCL = -3,
   SFMBA_ERR_NUMERIC = -4,   /* device raised a numeric flag, see sfmba_result.flags              */
   SFMBA_ERR_UNSUPPORTED = -5,
-  SFMBA_ERR_NO_DEVICE = -6
+  SFMBA_ERR_NO_DEVICE = -6,
+  SFMBA_ERR_COMM = -7       /* a peer rank never arrived at an exchange (SFMBA_FLAG_PEER_TIMEOUT): the    */
+                            /* parameters of the failed iteration were not updated                        */
 } sfmba_status;
 
 /* bits of sfmba_result.flags / refine `flags` outputs (device-side error word)                     */
@@ -56,6 +58,7 @@ typedef enum {
 #define SFMBA_FLAG_NONFINITE      4u  /* NaN/Inf in cost or update                                 */
 #define SFMBA_FLAG_PCG_MAXITER    8u  /* PCG stopped on pcg_max_iter, not on pcg_tol               */
 #define SFMBA_FLAG_SINGULAR      16u  /* a 3x3 / 7x7 block was not positive definite               */
+#define SFMBA_FLAG_PEER_TIMEOUT  32u  /* several GPUs: a rank waited 20 s for a peer's partial sums (SFMBA_ERR_COMM) */
 #define SFMBA_FLAG_BAD_INDEX     64u  /* a RANSAC sample index outside [0, n): the call returns INVALID_ARG */
 
 typedef enum { SFMBA_MODE_REFERENCE_FIXED = 0, SFMBA_MODE_ADAPTIVE_LM = 1 } sfmba_mode;

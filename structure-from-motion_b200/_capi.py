@@ -17,8 +17,9 @@ SFMBA_MAX_COST_HISTORY = 64
 NOALLOC_MAX_CAMS = 16384
 
 OK = 0
-ERR_INVALID_ARG, ERR_CUDA, ERR_NCCL, ERR_NUMERIC, ERR_UNSUPPORTED, ERR_NO_DEVICE = -1, -2, -3, -4, -5, -6
+ERR_INVALID_ARG, ERR_CUDA, ERR_NCCL, ERR_NUMERIC, ERR_UNSUPPORTED, ERR_NO_DEVICE, ERR_COMM = -1, -2, -3, -4, -5, -6, -7
 FLAG_QW_NEAR_ZERO, FLAG_DEPTH_ZERO, FLAG_NONFINITE, FLAG_PCG_MAXITER, FLAG_SINGULAR = 1, 2, 4, 8, 16
+FLAG_PEER_TIMEOUT, FLAG_BAD_INDEX = 32, 64
 MODE_REFERENCE_FIXED, MODE_ADAPTIVE_LM = 0, 1
 SOLVER_PCG, SOLVER_DENSE_CHOLESKY = 0, 1
 PRECOND_JACOBI, PRECOND_SCHUR_JACOBI = 0, 1

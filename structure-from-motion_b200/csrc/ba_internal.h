@@ -37,6 +37,7 @@ constexpr int GROUP_PT_CAP = GROUP_WEIGHT / POINT_WEIGHT;   // <= 512 points per
 constexpr int SEG_CAP = 128;        // distinct cameras per chunk
 constexpr int SEG_RUN_STRIDE = SEG_CAP + 2;             // u16 entries per chunk in seg_lane0 (4-byte aligned rows)
 constexpr int CAM_ACC = 64;         // doubles per camera accumulator row: A(28) S(28) g(7) pad(1)
+constexpr int ROW_COMPACT = 36;     // doubles per segment row of the Gram sums without the S entries: A(28) g(7) pad(1)
 constexpr int MV_ACC = 12;          // doubles per matvec row: T[3][3] (c~ d^T), s[3]
 
 // record index word: ptl[0:10) pos[10:21) seg[21:28)
@@ -51,8 +52,9 @@ struct Scalars {
   double lambda;         // current damping (device copy; adaptive mode changes it on device)
   double cost_cur;       // cost at the current linearisation point
   double cost_new;       // cost at the candidate point (adaptive mode)
+  double md_pts;         // point part of the predicted decrease, this rank's points (adjacent to cost_new: one all-reduce)
   double nu;             // LM rejection growth factor
-  double model_decrease; // predicted decrease of the last step (adaptive mode)
+  double model_decrease; // camera part of the predicted decrease of the last step (adaptive mode)
   int32_t pcg_done;
   int32_t pcg_iters;     // iterations of the current PCG solve
   int32_t pcg_iters_total;
@@ -68,6 +70,9 @@ struct Scalars {
   uint32_t ticket_b;
   double costs[SFMBA_MAX_COST_HISTORY];
   double alpha_hist[8];  // step lengths of the first PCG_UBUF iterations of the current solve
+  double beta_hist[8];   // and the direction coefficients (p_i = z_i + beta_i p_(i-1))
+  uint32_t bar_a;        // grid-wide barrier of k_pcg_step (arrival counter, zeroed by the CTA that finishes last)
+  uint32_t pad0;
 };
 constexpr int PCG_UBUF = 8;            // PCG iterations whose per-point u_j are kept for the back-substitution
 
@@ -146,7 +151,8 @@ struct BaDev {
                                       // lengths alpha_i (Scalars::alpha_hist) their sum is D^-1 B^T delta_p, so the
                                       // back-substitution of a short solve needs no pass over the observations
   double* grp_cost;                   // [max(G, cost grid)]
-  double* part64;                     // [chunk_bound*SEG_CAP][CAM_ACC] segment rows of the Gram sums
+  double* grp_exv;                    // [G] sum_j e_x^T D^-1 e_x of the group (adaptive LM only, else null)
+  double* part64;                     // [chunk_bound*SEG_CAP][CAM_ACC or ROW_COMPACT] segment rows of the Gram sums
   double* cam_acc;                    // [V][CAM_ACC] (+ 8 trailing doubles: local cost at [V*CAM_ACC])
   double* ablk;                       // [V][49] A_i + lambda I
   double* minv;                       // [V][49] block-Jacobi inverse of S_ii
@@ -158,7 +164,8 @@ struct BaDev {
   double* r;
   double* z;
   double* p;
-  double* q;                          // [7V] S p
+  double* q;                          // [7V] w = S z of the current iteration
+  double* s;                          // [7V] S p (by recurrence)
   double* gvec;                       // [7V] right-hand side
   double* red_a;                      // [<= 1024] per-block partials of the PCG dot products
   double* red_b;                      // [<= 2048]

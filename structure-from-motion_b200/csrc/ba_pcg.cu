@@ -49,46 +49,33 @@ __device__ __forceinline__ void quat_dRt(const double q2[4], double Q[4][9]) {
   Q[3][6] = x2;        Q[3][7] = y2;        Q[3][8] = 0.0;
 }
 
-// per camera and per matvec: (PCG) p = z + beta p, then E = sum_j p_q[j] Q_j, w = R^T p_C
-__global__ void __launch_bounds__(128) k_cam_iter(BaDev d, const double* __restrict__ vec, int pcg_direction,
-                                                  int dvdc_quirk) {
-  pdl_wait();
-  pdl_trigger();
-  const int cam = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cam >= d.V) return;
-  double dl[7];
-  if (pcg_direction && d.sc->pcg_done) {            // converged: the rows of x, for the back-substitution
-#pragma unroll
-    for (int k = 0; k < 7; ++k) dl[k] = d.x[7 * (size_t)cam + k];
-  } else if (pcg_direction) {
-    const double beta = d.sc->beta;
-#pragma unroll
-    for (int k = 0; k < 7; ++k) {
-      const double v = d.z[7 * (size_t)cam + k] + beta * d.p[7 * (size_t)cam + k];
-      d.p[7 * (size_t)cam + k] = v;
-      dl[k] = v;
-    }
-  } else {
-#pragma unroll
-    for (int k = 0; k < 7; ++k) dl[k] = vec[7 * (size_t)cam + k];
-  }
-  const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
-  double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
+// camit row of one camera from its 7 entries dl of a camera-space vector: E = sum_j dl_q[j] Q_j, w = R^T dl_C
+__device__ __forceinline__ void camit_row(const double* __restrict__ t, const double dl[7], int dvdc_quirk,
+                                          double o[14]) {
+  const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
   double Q[4][9];
   quat_dRt(q2, Q);
-  double* o = d.camit + (size_t)CAMIT_STRIDE * cam;
 #pragma unroll
   for (int e = 0; e < 9; ++e) o[e] = dl[3] * Q[0][e] + dl[4] * Q[1][e] + dl[5] * Q[2][e] + dl[6] * Q[3][e];
-  double w[3];
 #pragma unroll
-  for (int c = 0; c < 3; ++c) w[c] = t[c] * dl[0] + t[3 + c] * dl[1] + t[6 + c] * dl[2];
-  o[9] = w[0];
-  o[10] = w[1];
-  o[11] = w[2];
-  o[12] = dvdc_quirk ? 2.0 * w[2] : 0.0;
+  for (int c = 0; c < 3; ++c) o[9 + c] = t[c] * dl[0] + t[3 + c] * dl[1] + t[6 + c] * dl[2];
+  o[12] = dvdc_quirk ? 2.0 * o[11] : 0.0;
   o[13] = dvdc_quirk ? 1.0 : -1.0;
-  o[14] = 0.0;
-  o[15] = 0.0;
+}
+
+// camit rows of an arbitrary 7V-vector (the direction of the tile back-substitution), one thread per camera
+__global__ void __launch_bounds__(128) k_cam_rows(BaDev d, const double* __restrict__ vec, int dvdc_quirk) {
+  const int cam = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cam >= d.V) return;
+  double dl[7], o[14];
+#pragma unroll
+  for (int k = 0; k < 7; ++k) dl[k] = vec[7 * (size_t)cam + k];
+  camit_row(d.camtab + (size_t)CAMTAB_STRIDE * cam, dl, dvdc_quirk, o);
+  double* dst = d.camit + (size_t)CAMIT_STRIDE * cam;
+#pragma unroll
+  for (int e = 0; e < 14; ++e) dst[e] = o[e];
+  dst[14] = 0.0;
+  dst[15] = 0.0;
 }
 
 // ---- K3: matrix-free implicit-Schur matvec / back-substitution -----------------------------------
@@ -168,7 +155,7 @@ __device__ __forceinline__ void matvec_group(const BaDev& d, const MvShape& sh, 
   // Everything staged so far is constant during the PCG solve, so under a programmatic dependent launch
   // it overlaps the previous kernel's tail; camit and the done flag are that kernel's results.
   pdl_wait();
-  if (!BACKSUB && d.sc->pcg_done) {
+  if ((!BACKSUB && d.sc->pcg_done) || (BACKSUB && (d.sc->flags & FLAG_PEER_TIMEOUT))) {
     cp_async_wait_all();
     return;
   }
@@ -446,37 +433,54 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
   matvec_group<BACKSUB, ROBUST>(d, sh, dvdc_quirk, blockIdx.x, smem);
 }
 
-// y_i from the camera's segment rows, one warp per camera: lane = (row slot, component), two row slots
-// of 16 lanes each take alternate rows with eight loads in flight, slot sums are combined in fixed
-// order.  y_C = -R s, y_q[j] = <Q_j, T>.  Returns y in lanes 0..6 (0 elsewhere).
-__device__ __forceinline__ double cam_y_from_rows(const BaDev& d, int cam, int lane, bool live) {
-  const int sub = lane & 15, slot = lane >> 4;
-  double a = 0.0;
-  if (live && sub < MV_ACC) {
-    const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
-    int k = r0 + slot;
-    for (; k + 14 < r1; k += 16) {                     // rows k, k+2, ..., k+14 of this slot (contiguous rows)
-      double v[8];
+// y_i from the camera's segment rows.  The rows of one camera are contiguous in part12 (camrow_ptr), so the whole warp
+// streams them with 16-byte loads: lane l's t-th load covers the doubles 2 (32 t + l), +1 of the block, i.e. component
+// pair (2 t + l) mod 6 of some row -- three accumulators per lane (t mod 3), six loads in flight, then one fixed-order
+// combination of the 96 lane sums through shared memory (`buf`: 96 double2 per warp).
+// y_C = -R s, y_q[j] = <Q_j, T>.  Returns y in lanes 0..6 (0 elsewhere).
+__device__ __forceinline__ double cam_y_gather(const BaDev& d, int cam, int lane, double2* buf) {
+  const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
+  const double2* src = reinterpret_cast<const double2*>(d.part12 + (size_t)r0 * MV_ACC);
+  const int n2 = (r1 - r0) * (MV_ACC / 2);
+  double2 a0 = make_double2(0.0, 0.0), a1 = a0, a2 = a0;
+  const double2 zero = a0;
+  int e = lane;
+  for (; e + 5 * 32 < n2; e += 6 * 32) {
+    const double2 v0 = __ldcg(src + e), v1 = __ldcg(src + e + 32), v2 = __ldcg(src + e + 64);
+    const double2 v3 = __ldcg(src + e + 96), v4 = __ldcg(src + e + 128), v5 = __ldcg(src + e + 160);
+    a0.x += v0.x; a0.y += v0.y; a1.x += v1.x; a1.y += v1.y; a2.x += v2.x; a2.y += v2.y;
+    a0.x += v3.x; a0.y += v3.y; a1.x += v4.x; a1.y += v4.y; a2.x += v5.x; a2.y += v5.y;
+  }
+  {                                                        // the last (up to five) loads of the lane, same order
+    double2 v[5];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = d.part12[(size_t)(k + 2 * u) * MV_ACC + sub];
+    for (int u = 0; u < 5; ++u) v[u] = e + 32 * u < n2 ? __ldcg(src + e + 32 * u) : zero;
+    a0.x += v[0].x; a0.y += v[0].y; a1.x += v[1].x; a1.y += v[1].y; a2.x += v[2].x; a2.y += v[2].y;
+    a0.x += v[3].x; a0.y += v[3].y; a1.x += v[4].x; a1.y += v[4].y;
+  }
+  __syncwarp();
+  buf[lane] = a0;
+  buf[32 + lane] = a1;
+  buf[64 + lane] = a2;
+  __syncwarp();
+  double tsum = 0.0;
+  if (lane < MV_ACC) {                                     // lane = component: its 16 contributions in (t, l) order
+    const int c = lane >> 1;
 #pragma unroll
-      for (int u = 0; u < 8; ++u) a += v[u];
-    }
-    if (k < r1) {                                      // the last (up to seven) rows: loads first, same order of sums
-      double v[7];
-#pragma unroll
-      for (int u = 0; u < 7; ++u) v[u] = k + 2 * u < r1 ? d.part12[(size_t)(k + 2 * u) * MV_ACC + sub] : 0.0;
-#pragma unroll
-      for (int u = 0; u < 7; ++u)
-        if (k + 2 * u < r1) a += v[u];
+    for (int ph = 0; ph < 3; ++ph) {
+      int l0 = (c - 2 * ph) % 6;
+      if (l0 < 0) l0 += 6;
+      for (int l = l0; l < 32; l += 6) {
+        const double2 v = buf[32 * ph + l];
+        tsum += (lane & 1) ? v.y : v.x;
+      }
     }
   }
-  a += __shfl_down_sync(0xffffffffu, a, 16);           // slot 0 + slot 1
   double T[MV_ACC];
 #pragma unroll
-  for (int e = 0; e < MV_ACC; ++e) T[e] = __shfl_sync(0xffffffffu, a, e);
+  for (int k = 0; k < MV_ACC; ++k) T[k] = __shfl_sync(0xffffffffu, tsum, k);
   double y = 0.0;
-  if (live && lane < 7) {
+  if (lane < 7) {
     const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
     if (lane < 3) {
       y = -(t[3 * lane] * T[9] + t[3 * lane + 1] * T[10] + t[3 * lane + 2] * T[11]);
@@ -488,7 +492,7 @@ __device__ __forceinline__ double cam_y_from_rows(const BaDev& d, int cam, int l
       for (int j = 0; j < 4; ++j) {
         if (j == lane - 3) {
 #pragma unroll
-          for (int e = 0; e < 9; ++e) y += Q[j][e] * T[e];
+          for (int k = 0; k < 9; ++k) y += Q[j][k] * T[k];
         }
       }
     }
@@ -496,24 +500,20 @@ __device__ __forceinline__ double cam_y_from_rows(const BaDev& d, int cam, int l
   return y;
 }
 
-// svec = y only (multi-GPU: all-reduced before k_pcg_tail<2>)
-__global__ void __launch_bounds__(256) k_camsum12(BaDev d) {
+constexpr int VEC_THREADS = 512;                 // vector kernels: one warp per camera
+constexpr int VEC_WARPS = VEC_THREADS / 32;
+
+// svec = y only (several GPUs without peer windows: all-reduced by NCCL before k_pcg_step<2>)
+__global__ void __launch_bounds__(VEC_THREADS) k_camsum12(BaDev d) {
+  __shared__ double2 gat[VEC_WARPS][96];
   if (d.sc->pcg_done) return;
-  const int sub = threadIdx.x & 31;
-  const int cam = blockIdx.x * 8 + (threadIdx.x >> 5);
-  const bool live = cam < d.V;
-  const double y = cam_y_from_rows(d, cam, sub, live);
-  if (live && sub < 7) d.svec[7 * (size_t)cam + sub] = y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
+    const double y = cam_y_gather(d, cam, lane, gat[warp]);
+    if (lane < 7) d.svec[7 * (size_t)cam + lane] = y;
+  }
 }
 
-// The vector part of one PCG iteration in ONE cooperative launch (grid-wide barriers between phases).
-//   MODE 0  init: x = 0, r = g, z = Minv g, rz, gg, p = z, camit(p)
-//   MODE 1  phase 1: y from the segment rows, q = A p - y, p.q            (single GPU)
-//   MODE 2  phase 1: y = svec (already all-reduced), q = A p - y, p.q     (several GPUs, NCCL)
-//   MODE 3  phase 0: this rank's partial y from its rows, stored into every rank's peer window
-//           over NVLink; flags; phase 1: y = sum over ranks in rank order (several GPUs, fused)
-//   phase 2: alpha = rz / p.q;  x += alpha p;  r' = r - alpha q;  z = Minv r';  r'.z, r'.r
-//   phase 3: beta = rz' / rz;  convergence test and host signal;  r = r';  p = z + beta p;  camit(p)
 // Every block sums the per-block partials itself, in block order, so all blocks hold identical scalars.
 __device__ __forceinline__ double all_blocks_sum(const double* __restrict__ partials, int stride, int which,
                                                  double* red) {
@@ -522,19 +522,7 @@ __device__ __forceinline__ double all_blocks_sum(const double* __restrict__ part
   return block_sum(a, red);
 }
 
-
-// ---- the vector part of one PCG iteration: three ordinary launches, no grid-wide barrier --------------
-//   k_pcg_q<MODE>     y per camera, q = A p - y, per-CTA partials of p.q
-//        MODE 1  y from this GPU's segment rows                                   (one GPU)
-//        MODE 2  y = svec, already all-reduced by NCCL                            (fallback)
-//        MODE 3  y = sum over ranks of the peer-window slots, in rank order       (NVLink peers)
-//   k_pcg_ypeer       (MODE 3 only, before k_pcg_q) this rank's partial y -> its slot in every rank's
-//                     window; the CTA that finishes last raises the flags
-//   k_pcg_update<INIT> alpha = rz / p.q; x += alpha p; r -= alpha q; z = Minv r; partials of r.z, r.r;
-//                     the CTA that finishes last sums them: beta, convergence test, host signal
-//   k_cam_iter        p = z + beta p and its camit rows (or, once converged, the rows of x)
-// One warp per camera: lane a < 7 owns entry a of the camera's 7-vectors.  Every CTA sums the per-CTA
-// partials itself, in CTA order, so all CTAs hold identical scalars; nothing spins on this GPU.
+// a[lane][:] . v for the camera's 7x7 block (row-major), v held one entry per lane
 __device__ __forceinline__ double row7_dot(const double* __restrict__ M49, int lane, double v_lane) {
   double a = 0.0;
 #pragma unroll
@@ -545,148 +533,164 @@ __device__ __forceinline__ double row7_dot(const double* __restrict__ M49, int l
   return a;
 }
 
-__global__ void __launch_bounds__(256) k_pcg_ypeer(BaDev d) {
-  pdl_wait();
-  pdl_trigger();
-  Scalars* sc = d.sc;
-  if (sc->pcg_done) return;
-  const PeerWindow& xw = d.xw;
-  const int tid = threadIdx.x, lane = tid & 31;
-  const int gwarp = (blockIdx.x * blockDim.x + tid) >> 5;
-  const int nwarps = (gridDim.x * blockDim.x) >> 5;
-  const unsigned long long seq = *xw.counter() + 1ull;    // advanced by k_pcg_update
-  const int par = (int)(seq & 1ull);
-  for (int cam = gwarp; cam < d.V; cam += nwarps) {
-    const double y = cam_y_from_rows(d, cam, lane, true);
-    if (lane < 7) {
-      const size_t k = 7 * (size_t)cam + lane;
-      for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
-    }
-  }
-  peer_publish(xw, seq, &sc->ticket_a);
+// camit row of a camera whose vector entries sit in lanes 0..6 (every lane computes the row, lanes 0..15 store it)
+__device__ __forceinline__ void warp_camit_row(const BaDev& d, int cam, int lane, double v_lane, int dvdc_quirk) {
+  double dl[7], o[16];
+#pragma unroll
+  for (int k = 0; k < 7; ++k) dl[k] = __shfl_sync(0xffffffffu, v_lane, k);
+  camit_row(d.camtab + (size_t)CAMTAB_STRIDE * cam, dl, dvdc_quirk, o);
+  o[14] = 0.0;
+  o[15] = 0.0;
+  double mine = 0.0;
+#pragma unroll
+  for (int e = 0; e < 16; ++e)
+    if (lane == e) mine = o[e];
+  if (lane < 16) d.camit[(size_t)CAMIT_STRIDE * cam + lane] = mine;
 }
 
+// All CTAs of the grid are resident (the launcher sizes the grid to the SM count): arrive, then spin until everyone
+// has.  The counter is put back to zero by the CTA that finishes the kernel last.  Bounded like the peer wait.
+__device__ __forceinline__ void grid_barrier(uint32_t* counter, Scalars* sc) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(counter, 1u);
+    const unsigned long long t0 = global_timer_ns();
+    unsigned spins = 0;
+    while (*(volatile uint32_t*)counter < gridDim.x) {
+      if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > PEER_TIMEOUT_NS) {
+        atomicOr(&sc->flags, FLAG_PEER_TIMEOUT);
+        break;
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// ---- the vector part of the solve ------------------------------------------------------------------------
+// Preconditioned conjugate gradients in the Chronopoulos-Gear form: the matvec is applied to z = Minv r (k_matvec reads
+// the camit rows of z), and ONE grid-wide reduction per iteration gives both scalars,
+//     w = S z = A z - y,   gamma = r.z,   delta = z.w
+//     beta = gamma / gamma_old,   alpha = gamma / (delta - beta gamma / alpha_old)          (first iteration: 0, gamma / delta)
+//     p = z + beta p;  s = w + beta s (= S p);  x += alpha p;  r -= alpha s;  z = Minv r;  camit rows of the new z
+// -- the iterates of textbook PCG in exact arithmetic.  |r|^2 of the new residual is summed by the CTA that finishes
+// last (ticket), which also decides convergence and signals the host: nothing later in the kernel waits for it.
+// One kernel per iteration, one warp per camera (lane a < 7 owns entry a of the camera's 7-vectors):
+//   phase 0  (MODE 3) this rank's partial y from its rows -> its slot in EVERY rank's peer window over NVLink; flags
+//   phase 1  y (MODE 1: from this GPU's rows; 2: svec, all-reduced by NCCL; 3: the slots of all ranks, in rank order),
+//            w, per-CTA partials of gamma and delta;  grid barrier;  every CTA sums the partials in CTA order
+//   phase 2  the updates above, partial |r|^2, ticket
 template <int MODE>
-__global__ void __launch_bounds__(256) k_pcg_q(BaDev d) {
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, int max_iter, unsigned epoch,
+                                                         int dvdc_quirk) {
   __shared__ double red[32];
+  __shared__ double2 gat[VEC_WARPS][96];
   pdl_wait();
-  pdl_trigger();
   Scalars* sc = d.sc;
   if (sc->pcg_done) return;
-  const int tid = threadIdx.x, lane = tid & 31;
-  const int gwarp = (blockIdx.x * blockDim.x + tid) >> 5;
-  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int gwarp = blockIdx.x * VEC_WARPS + warp, nwarps = gridDim.x * VEC_WARPS;
   const bool l7 = lane < 7;
+  // scalars of the previous iteration: rewritten only by the CTA that finishes this kernel last
+  const double gam_old = sc->rz, alpha_old = sc->alpha, gg = sc->gg;
+  const int it_old = sc->pcg_iters;
   int par = 0;
   if (MODE == 3) {
-    const unsigned long long seq = *d.xw.counter() + 1ull;
+    const PeerWindow& xw = d.xw;
+    const unsigned long long seq = *xw.counter() + 1ull;    // advanced by the CTA that finishes last
     par = (int)(seq & 1ull);
-    peer_wait(d.xw, seq, sc);
+    for (int cam = gwarp; cam < d.V; cam += nwarps) {
+      const double y = cam_y_gather(d, cam, lane, gat[warp]);
+      if (l7) {
+        const size_t k = 7 * (size_t)cam + lane;
+        for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
+      }
+    }
+    peer_publish(xw, seq, &sc->ticket_a);
+    peer_wait(xw, seq, sc);
   }
-  double pq = 0.0;
+  double gam = 0.0, del = 0.0;
   for (int cam = gwarp; cam < d.V; cam += nwarps) {
     const size_t k = 7 * (size_t)cam + lane;
     double y = 0.0;
-    if (MODE == 1) y = cam_y_from_rows(d, cam, lane, true);
+    if (MODE == 1) y = cam_y_gather(d, cam, lane, gat[warp]);
     if (MODE == 2 && l7) y = d.svec[k];
     if (MODE == 3 && l7) {
       for (int w = 0; w < d.xw.world; ++w) y += __ldcg(d.xw.slot(d.xw.rank, par, w) + k);
     }
-    const double pv = l7 ? d.p[k] : 0.0;
-    const double ap = row7_dot(d.ablk + 49 * (size_t)cam, lane, pv);
+    const double zv = l7 ? d.z[k] : 0.0;
+    const double az = row7_dot(d.ablk + 49 * (size_t)cam, lane, zv);
     if (l7) {
-      const double qv = ap - y;
-      d.q[k] = qv;
-      pq += pv * qv;
+      const double wv = az - y;
+      d.q[k] = wv;
+      gam += d.r[k] * zv;
+      del += zv * wv;
     }
   }
-  pq = block_sum(pq, red);
-  if (tid == 0) d.red_a[blockIdx.x] = pq;
-}
-
-// INIT: x = 0, r = g, z = Minv g (then k_cam_iter with beta = 0 makes p = z)
-template <bool INIT, bool PEER>
-__global__ void __launch_bounds__(256) k_pcg_update(BaDev d, int q_grid, double tol, int max_iter, unsigned epoch) {
-  __shared__ double red[32];
-  pdl_wait();
-  pdl_trigger();
-  Scalars* sc = d.sc;
-  if (!INIT && sc->pcg_done) return;
-  const int tid = threadIdx.x, lane = tid & 31;
-  const int gwarp = (blockIdx.x * blockDim.x + tid) >> 5;
-  const int nwarps = (gridDim.x * blockDim.x) >> 5;
-  const bool l7 = lane < 7;
-  const double rz_old = sc->rz, gg_old = sc->gg;          // rewritten by the last CTA only
-  const int it_old = sc->pcg_iters;
-  double alpha = 0.0, pq_all = 1.0;
-  if (!INIT) {
-    double a = 0.0;
-    for (int b = tid; b < q_grid; b += blockDim.x) a += d.red_a[b];
-    pq_all = block_sum(a, red);
-    alpha = rz_old / pq_all;
+  gam = block_sum(gam, red);
+  del = block_sum(del, red);
+  if (tid == 0) {
+    d.red_a[2 * blockIdx.x] = gam;
+    d.red_a[2 * blockIdx.x + 1] = del;
   }
-  double v0 = 0.0, v1 = 0.0;
+  grid_barrier(&sc->bar_a, sc);
+  pdl_trigger();                                   // every CTA of this grid is resident: the next kernel may queue up
+  gam = all_blocks_sum(d.red_a, 2, 0, red);
+  del = all_blocks_sum(d.red_a, 2, 1, red);
+  const double beta = it_old == 0 ? 0.0 : gam / gam_old;
+  const double den = it_old == 0 ? del : del - beta * gam / alpha_old;
+  const double alpha = gam / den;
+  double rr = 0.0;
   for (int cam = gwarp; cam < d.V; cam += nwarps) {
     const size_t k = 7 * (size_t)cam + lane;
     double rn = 0.0;
     if (l7) {
-      if (INIT) {
-        rn = d.gvec[k];
-        d.x[k] = 0.0;
-        d.p[k] = 0.0;
-      } else {
-        d.x[k] += alpha * d.p[k];
-        rn = d.r[k] - alpha * d.q[k];
-      }
-    }
-    const double z = row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
-    if (l7) {
+      const double pv = d.z[k] + beta * d.p[k];
+      const double sv = d.q[k] + beta * d.s[k];
+      d.p[k] = pv;
+      d.s[k] = sv;
+      d.x[k] += alpha * pv;
+      rn = d.r[k] - alpha * sv;
       d.r[k] = rn;
-      d.z[k] = z;
-      v0 += rn * z;
-      v1 += rn * rn;
+      rr += rn * rn;
     }
+    const double zn = row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
+    if (l7) d.z[k] = zn;
+    warp_camit_row(d, cam, lane, zn, dvdc_quirk);
   }
-  v0 = block_sum(v0, red);
-  v1 = block_sum(v1, red);
-  if (tid == 0) {
-    d.red_b[2 * blockIdx.x] = v0;
-    d.red_b[2 * blockIdx.x + 1] = v1;
-  }
+  rr = block_sum(rr, red);
+  if (tid == 0) d.red_b[blockIdx.x] = rr;
   if (!last_cta_arrives(&sc->ticket_b)) return;
   // ---- the last CTA: scalars of the iteration
-  const double rz_new = all_blocks_sum(d.red_b, 2, 0, red);
-  const double rr = all_blocks_sum(d.red_b, 2, 1, red);
+  rr = all_blocks_sum(d.red_b, 1, 0, red);
   if (tid != 0) return;
-  const double gg = INIT ? rr : gg_old;
-  int done = 0, it = 0;
+  const int it = it_old + 1;
+  int done = 0;
   uint32_t newflags = 0;
-  if (INIT) {
-    done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
-    if (!(rr == rr)) newflags |= FLAG_NONFINITE;
-  } else {
-    it = it_old + 1;
-    if (!(pq_all > 0.0) || !(rr == rr)) {              // p.q <= 0 or NaN
-      newflags |= FLAG_NONFINITE;
-      done = 1;
-    }
-    if (rr <= tol * tol * gg) done = 1;
-    if (PEER && (*(volatile uint32_t*)&sc->flags & FLAG_PEER_TIMEOUT)) done = 1;
-    if (!done && it >= max_iter) {
-      newflags |= FLAG_PCG_MAXITER;
-      done = 1;
-    }
-    sc->pcg_iters_total += 1;
-    if (PEER) *d.xw.counter() += 1ull;                  // this exchange is finished on this rank
+  if (!(den > 0.0) || !(gam > 0.0) || !(rr == rr)) {      // breakdown (S is not positive definite) or NaN
+    newflags |= FLAG_NONFINITE;
+    done = 1;
   }
-  sc->gg = gg;
+  if (rr <= tol * tol * gg) done = 1;
+  if (*(volatile uint32_t*)&sc->flags & FLAG_PEER_TIMEOUT) done = 1;
+  if (!done && it >= max_iter) {
+    newflags |= FLAG_PCG_MAXITER;
+    done = 1;
+  }
+  if (MODE == 3) *d.xw.counter() += 1ull;                   // this exchange is finished on this rank
+  sc->bar_a = 0u;
+  sc->pcg_iters_total += 1;
   sc->pcg_iters = it;
   if (newflags) atomicOr(&sc->flags, newflags);
-  sc->pq = pq_all;
+  sc->pq = del;
   sc->alpha = alpha;
-  if (!INIT && it_old < PCG_UBUF) sc->alpha_hist[it_old] = alpha;
-  sc->beta = INIT ? 0.0 : rz_new / rz_old;
-  sc->rz = rz_new;
+  sc->beta = beta;
+  if (it_old < PCG_UBUF) {
+    sc->alpha_hist[it_old] = alpha;
+    sc->beta_hist[it_old] = beta;
+  }
+  sc->rz = gam;
   sc->rr = rr;
   sc->pcg_done = done;
   if (d.host_sig)
@@ -694,20 +698,67 @@ __global__ void __launch_bounds__(256) k_pcg_update(BaDev d, int q_grid, double 
         ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
 }
 
+// x = 0, p = s = 0, r = g, z = Minv g and its camit rows; the CTA that finishes last sets |g|^2 and the iteration state
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_init(BaDev d, unsigned epoch, int dvdc_quirk) {
+  __shared__ double red[32];
+  pdl_wait();
+  pdl_trigger();
+  Scalars* sc = d.sc;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool l7 = lane < 7;
+  double rr = 0.0;
+  for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
+    const size_t k = 7 * (size_t)cam + lane;
+    double rn = 0.0;
+    if (l7) {
+      rn = d.gvec[k];
+      d.x[k] = 0.0;
+      d.p[k] = 0.0;
+      d.s[k] = 0.0;
+      d.r[k] = rn;
+      rr += rn * rn;
+    }
+    const double zn = row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
+    if (l7) d.z[k] = zn;
+    warp_camit_row(d, cam, lane, zn, dvdc_quirk);
+  }
+  rr = block_sum(rr, red);
+  if (tid == 0) d.red_b[blockIdx.x] = rr;
+  if (!last_cta_arrives(&sc->ticket_b)) return;
+  rr = all_blocks_sum(d.red_b, 1, 0, red);
+  if (tid != 0) return;
+  const int done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
+  if (!(rr == rr)) atomicOr(&sc->flags, FLAG_NONFINITE);
+  sc->gg = rr;
+  sc->rr = rr;
+  sc->rz = 0.0;
+  sc->alpha = 0.0;
+  sc->beta = 0.0;
+  sc->pcg_iters = 0;
+  sc->bar_a = 0u;
+  sc->pcg_done = done;
+  if (d.host_sig) *(volatile unsigned long long*)d.host_sig = ((unsigned long long)epoch << 32) | (done ? 1ull : 0ull);
+}
+
 // Back-substitution of a PCG solve of at most PCG_UBUF iterations, pts_j += v_j - D_j^-1 W_j^T delta_p
-// (ba_processor.py:405-406), from what the matvecs left: D^-1 W^T delta_p = sum_i alpha_i u^(i), summed in iteration
-// order.  One thread per point.
+// (ba_processor.py:405-406), from what the matvecs left.  Matvec i was applied to z_i and kept u^(i) = D^-1 W^T z_i;
+// the directions obey p_i = z_i + beta_i p_(i-1) and delta_p = sum alpha_i p_i, so with P_i = u^(i) + beta_i P_(i-1)
+// the wanted D^-1 W^T delta_p is sum_i alpha_i P_i, formed in iteration order.  One thread per point.
 __global__ void __launch_bounds__(256) k_backsub_points(BaDev d) {
   const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t N = (size_t)d.N;
   if (j >= N) return;
+  if (d.sc->flags & FLAG_PEER_TIMEOUT) return;      // incomplete cross-rank sums: the step is not applied
   const int iters = d.sc->pcg_iters;
-  double u[3] = {0.0, 0.0, 0.0};
+  double u[3] = {0.0, 0.0, 0.0}, P[3] = {0.0, 0.0, 0.0};
   for (int i = 0; i < iters && i < PCG_UBUF; ++i) {
-    const double alpha = d.sc->alpha_hist[i];
+    const double alpha = d.sc->alpha_hist[i], beta = d.sc->beta_hist[i];
     const double* ub = d.ubuf + (size_t)i * 3 * N + j;
 #pragma unroll
-    for (int e = 0; e < 3; ++e) u[e] += alpha * ub[e * N];
+    for (int e = 0; e < 3; ++e) {
+      P[e] = ub[e * N] + beta * P[e];
+      u[e] += alpha * P[e];
+    }
   }
   double* p = d.pts + 3 * j;
 #pragma unroll
@@ -718,6 +769,7 @@ __global__ void __launch_bounds__(256) k_backsub_points(BaDev d) {
 __global__ void k_update_cams(BaDev d) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= d.V) return;
+  if (d.sc->flags & FLAG_PEER_TIMEOUT) return;      // incomplete cross-rank sums: the step is not applied
   double* cam = d.cams + 7 * (size_t)c;
   const double* dx = d.x + 7 * (size_t)c;
   double v[7];
@@ -742,17 +794,36 @@ __global__ void k_lm_backup(BaDev d) {
   if (i < (size_t)3 * d.N) d.pts_backup[i] = d.pts[i];
 }
 
-// predicted decrease of the damped Gauss-Newton model, camera part: delta_p . (lambda delta_p + g)
-// (the point part is folded in through the Schur complement: for the exact solve, the model
-// decrease is  delta^T (lambda delta + J^T r)  and J^T r restricted to points is consumed by g)
-__global__ void __launch_bounds__(1024) k_lm_model_decrease(BaDev d) {
+// Predicted decrease of the damped Gauss-Newton model for the step (delta_p, delta_x) that solves
+// (J^T J + lambda I) delta = J^T r:   |r|^2 - |r - J delta|^2 = delta . J^T r + lambda |delta|^2
+//   = delta_p . (g + lambda delta_p)  +  sum_j e_x,j^T D_j^-1 e_x,j  +  lambda |delta_x|^2
+// with g = e_p - B D^-1 e_x the reduced right-hand side (delta_x = D^-1 (e_x - B^T delta_p)).  Runs after the update:
+// delta_x = pts - pts_backup; the e_x^T D^-1 e_x sums come from the linearisation (grp_exv).  The camera part goes to
+// sc->model_decrease, this rank's point part to sc->md_pts (summed over ranks with cost_new).
+__global__ void __launch_bounds__(256) k_lm_model_decrease(BaDev d) {
   __shared__ double red[32];
-  const int n = 7 * d.V;
-  const double lam = d.sc->lambda;
+  Scalars* sc = d.sc;
+  const double lam = sc->lambda;
+  const size_t stride = (size_t)gridDim.x * blockDim.x, t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   double a = 0.0;
-  for (int k = threadIdx.x; k < n; k += blockDim.x) a += d.x[k] * (lam * d.x[k] + d.gvec[k]);
+  for (size_t i = t0; i < (size_t)3 * d.N; i += stride) {
+    const double dx = d.pts[i] - d.pts_backup[i];
+    a += lam * dx * dx;
+  }
+  for (size_t g = t0; g < (size_t)d.G; g += stride) a += d.grp_exv[g];
   a = block_sum(a, red);
-  if (threadIdx.x == 0) d.sc->model_decrease = a;
+  if (threadIdx.x == 0) d.red_a[blockIdx.x] = a;
+  if (!last_cta_arrives(&sc->ticket_a)) return;
+  double b = 0.0;
+  for (int k = threadIdx.x; k < (int)gridDim.x; k += blockDim.x) b += __ldcg(d.red_a + k);
+  b = block_sum(b, red);
+  double c = 0.0;
+  for (int k = threadIdx.x; k < 7 * d.V; k += blockDim.x) c += d.x[k] * (lam * d.x[k] + d.gvec[k]);
+  c = block_sum(c, red);
+  if (threadIdx.x == 0) {
+    sc->md_pts = b;
+    sc->model_decrease = c;
+  }
 }
 
 // accept / reject on device: gain ratio from the actual decrease; Nielsen's lambda update
@@ -768,7 +839,7 @@ __global__ void k_lm_decide(BaDev d, double lam_min, double lam_max) {
   if (i == 0) {
     double lam = sc->lambda;
     if (accept) {
-      const double md = sc->model_decrease;
+      const double md = sc->model_decrease + sc->md_pts;
       double rho = md > 0.0 ? (cur - nw) / md : 1.0;
       double f = 1.0 - (2.0 * rho - 1.0) * (2.0 * rho - 1.0) * (2.0 * rho - 1.0);
       if (f < 1.0 / 3.0) f = 1.0 / 3.0;
@@ -801,16 +872,25 @@ static MvShape matvec_shape(const TileShape& ts, bool backsub, bool robust) {
   return sh;
 }
 
+// grid of the vector kernels: one warp per camera, never more CTAs than SMs (k_pcg_step holds a grid-wide barrier,
+// so all of its CTAs must be resident at once; one 512-thread CTA per SM always is)
 static int vec_grid(const BaDev& d) {
-  int g = (d.V + 7) / 8;                  // one warp per camera
+  static int sms[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int& n = sms[dev & 63];
+  if (n == 0) {
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 1;
+  }
+  int g = (d.V + VEC_WARPS - 1) / VEC_WARPS;
   if (g < 1) g = 1;
-  return g < 1024 ? g : 1024;             // red_a / red_b hold one partial per CTA
+  return g < n ? g : n;
 }
 
 void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
-  launch_pdl(k_pcg_update<true, false>, dim3(vec_grid(d)), dim3(256), 0, st, d, 0, 0.0, 0, epoch);
-  launch_pdl(k_cam_iter, dim3((d.V + 127) / 128), dim3(128), 0, st, d, (const double*)nullptr, 1, dvdc_quirk ? 1 : 0);
-  lc.launches += 2;
+  launch_pdl(k_pcg_init, dim3(vec_grid(d)), dim3(VEC_THREADS), 0, st, d, epoch, dvdc_quirk ? 1 : 0);
+  lc.launches += 1;
 }
 
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
@@ -844,33 +924,27 @@ void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_
 }
 
 void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
-  k_camsum12<<<(d.V + 7) / 8, 256, 0, st>>>(d);
+  k_camsum12<<<vec_grid(d), VEC_THREADS, 0, st>>>(d);
   lc.launches++;
 }
 
-// the vector part of a PCG iteration; from_rows: y from the segment rows (one GPU), else from svec
+// the vector part of a PCG iteration (one launch); mode 1: y from this GPU's rows, 2: from svec, 3: peer windows
 void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
                      cudaStream_t st, LaunchCounter& lc) {
   const int g = vec_grid(d);
+  const int q = dvdc_quirk ? 1 : 0;
   if (mode == 1) {
-    launch_pdl(k_pcg_q<1>, dim3(g), dim3(256), 0, st, d);
+    launch_pdl(k_pcg_step<1>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q);
   } else if (mode == 2) {
-    launch_pdl(k_pcg_q<2>, dim3(g), dim3(256), 0, st, d);
+    launch_pdl(k_pcg_step<2>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q);
   } else {
-    launch_pdl(k_pcg_ypeer, dim3(g), dim3(256), 0, st, d);
-    launch_pdl(k_pcg_q<3>, dim3(g), dim3(256), 0, st, d);
-    lc.launches++;
+    launch_pdl(k_pcg_step<3>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q);
   }
-  if (mode == 3)
-    launch_pdl(k_pcg_update<false, true>, dim3(g), dim3(256), 0, st, d, g, tol, max_iter, epoch);
-  else
-    launch_pdl(k_pcg_update<false, false>, dim3(g), dim3(256), 0, st, d, g, tol, max_iter, epoch);
-  launch_pdl(k_cam_iter, dim3((d.V + 127) / 128), dim3(128), 0, st, d, (const double*)nullptr, 1, dvdc_quirk ? 1 : 0);
-  lc.launches += 3;
+  lc.launches += 1;
 }
 
 void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
-  k_cam_iter<<<(d.V + 127) / 128, 128, 0, st>>>(d, vec, 0, dvdc_quirk ? 1 : 0);
+  k_cam_rows<<<(d.V + 127) / 128, 128, 0, st>>>(d, vec, dvdc_quirk ? 1 : 0);
   lc.launches++;
 }
 
@@ -893,7 +967,10 @@ void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
 }
 
 void launch_lm_model_decrease(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
-  k_lm_model_decrease<<<1, 1024, 0, st>>>(d);
+  size_t g = ((size_t)3 * d.N + 4 * 256 - 1) / (4 * 256);
+  if (g < 1) g = 1;
+  if (g > 592) g = 592;                    // red_a holds one partial per CTA
+  k_lm_model_decrease<<<(unsigned)g, 256, 0, st>>>(d);
   lc.launches++;
 }
 

@@ -17,18 +17,27 @@
 
 namespace sfmba {
 
-constexpr int GRAM = 63;           // A(28) S(28) g(7)
-constexpr int RP_STRIDE = 63;      // odd stride (in doubles): conflict-free simultaneous flushes
+constexpr int SLOT_PLANES = 5;     // slot planes live at once in the point phase (two rounds: 5 + 4 of D(6) e_x(3))
 
-// dynamic shared memory (doubles): Xa[3 pt_cap] | Dv[9][pt_cap] | red[32] | un[max(9 slot_cap, RUN_LANES RP_STRIDE)]
-// then bs | ixs | segc | srun | rowp.   `un` holds the point-pass slots, later the lane sums.
+// Gram sums per lane / per segment row.  SCHUR: A(28) S(28) g(7) = 63, rows of CAM_ACC doubles; otherwise the 28 S
+// entries do not exist: A(28) g(7) = 35, rows of ROW_COMPACT doubles.  Both counts are odd: a lane's flush into
+// shared memory with that stride is conflict-free.
+template <bool SCHUR> struct Gram {
+  static constexpr int N = SCHUR ? 63 : 35;
+  static constexpr int G0 = SCHUR ? 56 : 28;          // first g entry
+  static constexpr int ROW = SCHUR ? CAM_ACC : ROW_COMPACT;
+};
+
+// dynamic shared memory (doubles): Xa[3 pt_cap] | Dv[9][pt_cap] | red[32] | un[max(5 slot_cap, RUN_LANES Gram::N)]
+// then ixs | segc | rpos | srun | rowp.   `un` holds the point-pass slots, later the lane sums.  The observations
+// (rec_b) are read from global memory, lane-transposed and coalesced, one trip ahead.
 struct GramShape {
   int pt_cap, seg_cap, k_cap, slot_cap, un_doubles;
 };
 
 __host__ __device__ inline size_t gram_smem_bytes(const GramShape& s) {
   size_t b = ((size_t)12 * s.pt_cap + 32 + (size_t)s.un_doubles) * 8;
-  b += (size_t)20 * s.k_cap * RUN_LANES;           // bs + ixs
+  b += (size_t)4 * s.k_cap * RUN_LANES;            // ixs
   b += (size_t)8 * ((s.seg_cap + 3) / 4 * 4);      // segc, rpos
   b += (size_t)2 * (SEG_RUN_STRIDE + 6);           // srun
   b += (size_t)4 * (s.pt_cap + 4);                 // rowp
@@ -38,10 +47,12 @@ __host__ __device__ inline size_t gram_smem_bytes(const GramShape& s) {
 // Phase A (K2a, ba_processor.py:355-363): per point D_j = sum J_x^T J_x + lambda I, D_j^-1, v_j = D_j^-1 e_x
 // and the cost; phase B: the camera-side Gram sums.  One launch linearises the whole problem.
 // ROBUST: every observation enters with its Huber weight w = rho'(|r|^2) (J^T W J, J^T W r); the cost is sum rho
-// SCHUR: also the 28 sums of J_p^T Y J_p (diagonal blocks of B D^-1 B^T); without it those entries stay zero
+// SCHUR: also the 28 sums of J_p^T Y J_p (diagonal blocks of B D^-1 B^T)
+// Three CTAs per SM without SCHUR (<= 168 registers, <= 75 KB of shared memory), two with it.
 template <bool ROBUST, bool SCHUR>
-__global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape sh, int dvdc_quirk, int g0) {
+__global__ void __launch_bounds__(RUN_LANES, SCHUR ? 2 : 3) k_linearize(BaDev d, GramShape sh, int dvdc_quirk, int g0) {
   extern __shared__ __align__(16) double smem[];
+  constexpr int GRAM = Gram<SCHUR>::N, RP_STRIDE = Gram<SCHUR>::N, G0 = Gram<SCHUR>::G0, ROW = Gram<SCHUR>::ROW;
   const int pt_cap = sh.pt_cap, slot_cap = sh.slot_cap;
   double* Xa = smem;
   double* Dv = Xa + 3 * pt_cap;
@@ -49,8 +60,8 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
   double* runpart = red + 32;
   double* slots = runpart;
   ChunkStage cs;
-  cs.bs = reinterpret_cast<double2*>(runpart + sh.un_doubles);
-  cs.ixs = reinterpret_cast<uint32_t*>(cs.bs + (size_t)sh.k_cap * RUN_LANES);
+  cs.bs = nullptr;
+  cs.ixs = reinterpret_cast<uint32_t*>(runpart + sh.un_doubles);
   cs.segc = reinterpret_cast<int32_t*>(cs.ixs + (size_t)sh.k_cap * RUN_LANES);
   cs.rpos = cs.segc + (sh.seg_cap + 3) / 4 * 4;
   cs.srun = reinterpret_cast<uint16_t*>(cs.rpos + (sh.seg_cap + 3) / 4 * 4);
@@ -72,93 +83,114 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
   ci.K = gm.K0;
   double cost = 0.0;
   uint32_t flags = 0;
-  // ---- phase A: point blocks
+  // ---- phase A: point blocks, in two rounds over the chunk (planes 0..4, then 5..8: D00 D01 D02 D11 D12 | D22 e_x)
   for (int c = c0; c < c1; ++c) {
     if (c > c0) ci = d.chunk_info[c];
     stage_chunk_async(d, c, ci, cs);
     cp_async_wait_all();
     __syncthreads();
     const int K = ci.K;
+    const double2* gb = d.rec_b + (size_t)c * CHUNK_CAP + tid;
     double R[9], C[3];
     const uint32_t ix_first = cs.ixs[tid];
     if (ix_first != REC_INVALID) load_cam_rc(d.camtab, cs.segc[rec_seg(ix_first)], R, C);
-    // two observations of the lane per trip: their dependent chains (projection, reciprocal, products) interleave
-    auto point_terms = [&](uint32_t ix, double2 b, double out[9], double& cterm, bool& ok) {
+    // J_x of one observation and, in the second round, its residual
+    auto jx_terms = [&](uint32_t ix, double x[3], double y[3], Proj& pr) {
       const int ptl = rec_ptl(ix);
-      const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
-      ok = pr.ok;
-      const double r0 = b.x - pr.u, r1 = b.y - pr.v;
-      const double x0 = (R[0] - pr.u * R[2]) * pr.iw, x1 = (R[3] - pr.u * R[5]) * pr.iw,
-                   x2 = (R[6] - pr.u * R[8]) * pr.iw;
-      const double y0 = (R[1] - pr.v * R[2]) * pr.iw, y1 = (R[4] - pr.v * R[5]) * pr.iw,
-                   y2 = (R[7] - pr.v * R[8]) * pr.iw;
-      double wx0 = x0, wx1 = x1, wx2 = x2, wy0 = y0, wy1 = y1, wy2 = y2;
-      if (ROBUST) {
-        double rho;
-        const double w = huber_weight(r0 * r0 + r1 * r1, d.huber_delta, rho);
-        cterm = rho;
-        wx0 *= w; wx1 *= w; wx2 *= w; wy0 *= w; wy1 *= w; wy2 *= w;
-      } else {
-        cterm = r0 * r0 + r1 * r1;
-      }
-      out[0] = wx0 * x0 + wy0 * y0;
-      out[1] = wx0 * x1 + wy0 * y1;
-      out[2] = wx0 * x2 + wy0 * y2;
-      out[3] = wx1 * x1 + wy1 * y1;
-      out[4] = wx1 * x2 + wy1 * y2;
-      out[5] = wx2 * x2 + wy2 * y2;
-      out[6] = wx0 * r0 + wy0 * r1;
-      out[7] = wx1 * r0 + wy1 * r1;
-      out[8] = wx2 * r0 + wy2 * r1;
+      pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
+      x[0] = (R[0] - pr.u * R[2]) * pr.iw;
+      x[1] = (R[3] - pr.u * R[5]) * pr.iw;
+      x[2] = (R[6] - pr.u * R[8]) * pr.iw;
+      y[0] = (R[1] - pr.v * R[2]) * pr.iw;
+      y[1] = (R[4] - pr.v * R[5]) * pr.iw;
+      y[2] = (R[7] - pr.v * R[8]) * pr.iw;
     };
-    for (int k = 0; k < K; k += 2) {
-      const uint32_t ix_a = cs.ixs[k * RUN_LANES + tid];
-      if (ix_a == REC_INVALID) break;
-      const double2 b_a = cs.bs[k * RUN_LANES + tid];
-      uint32_t ix_b = k + 1 < K ? cs.ixs[(k + 1) * RUN_LANES + tid] : REC_INVALID;
-      const bool two = ix_b != REC_INVALID;
-      const double2 b_b = two ? cs.bs[(k + 1) * RUN_LANES + tid] : b_a;
-      if (!two) ix_b = ix_a;
-      double oa[9], ob[9], ca, cb;
-      bool ok_a, ok_b;
-      point_terms(ix_a, b_a, oa, ca, ok_a);
-      point_terms(ix_b, b_b, ob, cb, ok_b);
-      if (!ok_a || !ok_b) flags |= FLAG_DEPTH_ZERO;
-      cost += ca;
-      double* sa = slots + rec_pos(ix_a);
 #pragma unroll
-      for (int e = 0; e < 9; ++e) sa[e * slot_cap] = oa[e];
-      if (two) {
-        cost += cb;
-        double* sb = slots + rec_pos(ix_b);
-#pragma unroll
-        for (int e = 0; e < 9; ++e) sb[e * slot_cap] = ob[e];
+    for (int round = 0; round < 2; ++round) {
+      // two observations of the lane per trip: their dependent chains (projection, reciprocal, products) interleave
+      double2 nb_a = make_double2(0.0, 0.0), nb_b = nb_a;
+      if (round == 1 || ROBUST) {
+        nb_a = gb[0];
+        if (K > 1) nb_b = gb[RUN_LANES];
       }
-    }
-    __syncthreads();
-    // one work item per (point, component): the slots of a point are summed in observation order
-    // (three components side by side per work item: the row-pointer lookups are paid once for three sums)
-    for (int idx = tid; idx < 3 * np; idx += RUN_LANES) {
-      const int j = idx / 3, e = 3 * (idx - 3 * j);
-      const int lo = max(rowp[j], ci.obs0) - ci.obs0;
-      const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
-      if (lo < hi) {
-        const double* sl = slots + e * slot_cap;
-        double a0 = Dv[e * pt_cap + j], a1 = Dv[(e + 1) * pt_cap + j], a2 = Dv[(e + 2) * pt_cap + j];
-        for (int sidx = lo; sidx < hi; ++sidx) {
-          a0 += sl[sidx];
-          a1 += sl[slot_cap + sidx];
-          a2 += sl[2 * slot_cap + sidx];
+      for (int k = 0; k < K; k += 2) {
+        const uint32_t ix_a = cs.ixs[k * RUN_LANES + tid];
+        if (ix_a == REC_INVALID) break;
+        uint32_t ix_b = k + 1 < K ? cs.ixs[(k + 1) * RUN_LANES + tid] : REC_INVALID;
+        const bool two = ix_b != REC_INVALID;
+        if (!two) ix_b = ix_a;
+        const double2 b_a = nb_a, b_b = two ? nb_b : nb_a;
+        if (round == 1 || ROBUST) {                          // the next trip's observations are on their way
+          if (k + 2 < K) nb_a = gb[(k + 2) * RUN_LANES];
+          if (k + 3 < K) nb_b = gb[(k + 3) * RUN_LANES];
         }
-        Dv[e * pt_cap + j] = a0;
-        Dv[(e + 1) * pt_cap + j] = a1;
-        Dv[(e + 2) * pt_cap + j] = a2;
+        double xa[3], ya[3], xb[3], yb[3];
+        Proj pa, pb;
+        jx_terms(ix_a, xa, ya, pa);
+        jx_terms(ix_b, xb, yb, pb);
+        double wa = 1.0, wb = 1.0;
+        const double ra0 = b_a.x - pa.u, ra1 = b_a.y - pa.v, rb0 = b_b.x - pb.u, rb1 = b_b.y - pb.v;
+        if (ROBUST) {
+          double rho;
+          wa = huber_weight(ra0 * ra0 + ra1 * ra1, d.huber_delta, rho);
+          if (round == 1) cost += rho;
+          wb = huber_weight(rb0 * rb0 + rb1 * rb1, d.huber_delta, rho);
+          if (round == 1 && two) cost += rho;
+        } else if (round == 1) {
+          cost += ra0 * ra0 + ra1 * ra1;
+          if (two) cost += rb0 * rb0 + rb1 * rb1;
+        }
+        auto emit = [&](uint32_t ix, const double x[3], const double y[3], double w, double r0, double r1) {
+          double* sl = slots + rec_pos(ix);
+          const double wx0 = ROBUST ? w * x[0] : x[0], wx1 = ROBUST ? w * x[1] : x[1], wx2 = ROBUST ? w * x[2] : x[2];
+          const double wy0 = ROBUST ? w * y[0] : y[0], wy1 = ROBUST ? w * y[1] : y[1], wy2 = ROBUST ? w * y[2] : y[2];
+          if (round == 0) {
+            sl[0] = wx0 * x[0] + wy0 * y[0];
+            sl[slot_cap] = wx0 * x[1] + wy0 * y[1];
+            sl[2 * slot_cap] = wx0 * x[2] + wy0 * y[2];
+            sl[3 * slot_cap] = wx1 * x[1] + wy1 * y[1];
+            sl[4 * slot_cap] = wx1 * x[2] + wy1 * y[2];
+          } else {
+            sl[0] = wx2 * x[2] + wy2 * y[2];
+            sl[slot_cap] = wx0 * r0 + wy0 * r1;
+            sl[2 * slot_cap] = wx1 * r0 + wy1 * r1;
+            sl[3 * slot_cap] = wx2 * r0 + wy2 * r1;
+          }
+        };
+        if (round == 1 && (!pa.ok || !pb.ok)) flags |= FLAG_DEPTH_ZERO;
+        emit(ix_a, xa, ya, wa, ra0, ra1);
+        if (two) emit(ix_b, xb, yb, wb, rb0, rb1);
       }
+      __syncthreads();
+      // one work item per (point, plane group): the slots of a point are summed in observation order, up to three
+      // planes side by side (the row-pointer lookups are paid once per item).  Round 0: planes {0,1,2} {3,4};
+      // round 1: {5,6} {7,8}
+      for (int idx = tid; idx < 2 * np; idx += RUN_LANES) {
+        const int j = idx >> 1, half = idx & 1;
+        const int lo = max(rowp[j], ci.obs0) - ci.obs0;
+        const int hi = min(rowp[j + 1], ci.obs0 + ci.len) - ci.obs0;
+        if (lo < hi) {
+          const int sp = round == 0 ? 3 * half : 2 * half;                 // first slot plane of the item
+          const int dp = round == 0 ? 3 * half : 5 + 2 * half;             // first Dv plane
+          const bool three = round == 0 && half == 0;
+          const double* sl = slots + sp * slot_cap;
+          double a0 = Dv[dp * pt_cap + j], a1 = Dv[(dp + 1) * pt_cap + j], a2 = three ? Dv[(dp + 2) * pt_cap + j] : 0.0;
+          for (int sidx = lo; sidx < hi; ++sidx) {
+            a0 += sl[sidx];
+            a1 += sl[slot_cap + sidx];
+            if (three) a2 += sl[2 * slot_cap + sidx];
+          }
+          Dv[dp * pt_cap + j] = a0;
+          Dv[(dp + 1) * pt_cap + j] = a1;
+          if (three) Dv[(dp + 2) * pt_cap + j] = a2;
+        }
+      }
+      __syncthreads();
     }
-    __syncthreads();
   }
   cp_async_wait_all();
   __syncthreads();
+  double exv = 0.0;                                    // sum_j e_x^T D^-1 e_x (adaptive LM: point part of the model decrease)
   {
     const double lam = d.sc->lambda;
     const size_t N = (size_t)d.N;
@@ -173,10 +205,11 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
       D[5] += lam;
       if (!sym3_inverse(D, Dinv)) flags |= FLAG_SINGULAR;
       sym3_mul(Dinv, ex, v);
+      exv += ex[0] * v[0] + ex[1] * v[1] + ex[2] * v[2];
       const size_t pt = (size_t)pt0 + j;
 #pragma unroll
       for (int e = 0; e < 6; ++e) {
-        Dv[e * pt_cap + j] = Dinv[e];
+        if (SCHUR) Dv[e * pt_cap + j] = Dinv[e];
         d.dinv[e * N + pt] = Dinv[e];
       }
 #pragma unroll
@@ -188,6 +221,10 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
   }
   cost = block_sum(cost, red);     // (contains the barrier that publishes Dv)
   if (tid == 0) d.grp_cost[grp] = cost;
+  if (d.grp_exv) {                 // adaptive LM only (uniform branch)
+    exv = block_sum(exv, red);
+    if (tid == 0) d.grp_exv[grp] = exv;
+  }
   if (flags) atomicOr(&d.sc->flags, flags);
   // ---- phase B: camera-side Gram sums
   for (int c = c0; c < c1; ++c) {
@@ -198,14 +235,17 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
       __syncthreads();
     }
     const int K = ci.K;
+    const double2* gb = d.rec_b + (size_t)c * CHUNK_CAP + tid;
     double R[9], C[3], q2[4];
     double acc[GRAM];
 #pragma unroll
     for (int e = 0; e < GRAM; ++e) acc[e] = 0.0;
     const uint32_t ix_first = cs.ixs[tid];
     const bool live = ix_first != REC_INVALID;
+    double2 b_next = make_double2(0.0, 0.0);
     if (live) {                                            // one camera per lane
       const int cam = cs.segc[rec_seg(ix_first)];
+      b_next = gb[0];
       load_cam_rc(d.camtab, cam, R, C);
       load_cam_q(d.camtab, cam, q2);
 #pragma unroll
@@ -214,7 +254,8 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
     for (int k = 0; k < K; ++k) {
       const uint32_t ix_cur = cs.ixs[k * RUN_LANES + tid];
       if (ix_cur == REC_INVALID) break;
-      const double2 b_cur = cs.bs[k * RUN_LANES + tid];
+      const double2 b_cur = b_next;
+      if (k + 1 < K) b_next = gb[(k + 1) * RUN_LANES];     // one trip ahead
       const int ptl = rec_ptl(ix_cur);
       const Proj pr = project(R, C, Xa[3 * ptl], Xa[3 * ptl + 1], Xa[3 * ptl + 2]);
       const double iw = pr.iw, u = pr.u, v = pr.v;
@@ -316,7 +357,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
           }
         }
 #pragma unroll
-        for (int a = 0; a < 7; ++a) acc[56 + a] = fma(jw[a], rho0, acc[56 + a]);
+        for (int a = 0; a < 7; ++a) acc[G0 + a] = fma(jw[a], rho0, acc[G0 + a]);
         e = 0;
 #pragma unroll
         for (int a = 0; a < 7; ++a) {
@@ -327,7 +368,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
           }
         }
 #pragma unroll
-        for (int a = 0; a < 7; ++a) acc[56 + a] = fma(jw[7 + a], rho1, acc[56 + a]);
+        for (int a = 0; a < 7; ++a) acc[G0 + a] = fma(jw[7 + a], rho1, acc[G0 + a]);
       }
     }
     if (live) {
@@ -336,7 +377,7 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
       for (int e = 0; e < GRAM; ++e) dst[e] = acc[e];
     }
     __syncthreads();
-    // per segment: sum its lanes in lane order -> one 64-double row
+    // per segment: sum its lanes in lane order -> one row of ROW doubles
     const uint16_t* run0 = cs.srun;
     // one warp per segment, two components per lane: no index arithmetic per element, coalesced rows
     {
@@ -348,9 +389,9 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
           a0 += runpart[rr * RP_STRIDE + lane];
           if (lane + 32 < GRAM) a1 += runpart[rr * RP_STRIDE + 32 + lane];
         }
-        double* row = d.part64 + (size_t)cs.rpos[s] * CAM_ACC;
+        double* row = d.part64 + (size_t)cs.rpos[s] * ROW;
         row[lane] = a0;
-        row[32 + lane] = a1;
+        if (lane + 32 < ROW) row[32 + lane] = a1;
       }
     }
     __syncthreads();
@@ -359,27 +400,27 @@ __global__ void __launch_bounds__(RUN_LANES, 2) k_linearize(BaDev d, GramShape s
 
 // Sum of one camera's (contiguous) segment rows, element e: four row slots (slot = tid >> 6) take rows
 // r0+slot, r0+slot+4, ... with eight loads in flight each and are combined in slot order through shared
-// memory.  One CTA of 256 threads per camera; the result is valid in the threads of slot 0.
+// memory.  One CTA of 256 threads per camera; the result is valid in the threads of slot 0 with e < row length.
+// Rows are CAM_ACC doubles with the Schur-diagonal sums and ROW_COMPACT doubles (A | g) without them.
 __device__ __forceinline__ double cam_rows_sum64(const BaDev& d, int cam, double (*sh)[CAM_ACC]) {
   const int e = threadIdx.x & 63, slot = threadIdx.x >> 6;
   const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
+  const size_t row = d.schur_diag ? CAM_ACC : ROW_COMPACT;
   const double* p = d.part64 + e;
   double a = 0.0;
   int k = r0 + slot;
-  // without the Schur-diagonal sums entries 28..55 of every row are zero: seven of a row's sixteen sectors are not read
-  const bool skip = !d.schur_diag && e >= 28 && e < 56;
-  if (!skip) {
+  if (e < (int)row) {
     for (; k + 28 < r1; k += 32) {
       double v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(k + 4 * u) * CAM_ACC];
+      for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(k + 4 * u) * row];
 #pragma unroll
       for (int u = 0; u < 8; ++u) a += v[u];
     }
     if (k < r1) {                                        // the last (up to seven) rows: loads first, same order of sums
       double v[7];
 #pragma unroll
-      for (int u = 0; u < 7; ++u) v[u] = k + 4 * u < r1 ? p[(size_t)(k + 4 * u) * CAM_ACC] : 0.0;
+      for (int u = 0; u < 7; ++u) v[u] = k + 4 * u < r1 ? p[(size_t)(k + 4 * u) * row] : 0.0;
 #pragma unroll
       for (int u = 0; u < 7; ++u)
         if (k + 4 * u < r1) a += v[u];
@@ -391,12 +432,16 @@ __device__ __forceinline__ double cam_rows_sum64(const BaDev& d, int cam, double
   return a;
 }
 
-// cam_acc[cam][e] = sum over the camera's segment rows
+// position in a cam_acc row (A(28) S(28) g(7) pad) of element e of a segment row
+__device__ __forceinline__ int acc_index(const BaDev& d, int e) { return (d.schur_diag || e < 28) ? e : e + 28; }
+
+// cam_acc[cam][:] = sum over the camera's segment rows
 __global__ void __launch_bounds__(256) k_camsum64(BaDev d) {
   __shared__ double sh[3][CAM_ACC];
   const int cam = blockIdx.x;
   const double a = cam_rows_sum64(d, cam, sh);
-  if (threadIdx.x < CAM_ACC) d.cam_acc[(size_t)cam * CAM_ACC + threadIdx.x] = a;
+  const int row = d.schur_diag ? CAM_ACC : ROW_COMPACT;
+  if ((int)threadIdx.x < row) d.cam_acc[(size_t)cam * CAM_ACC + acc_index(d, threadIdx.x)] = a;
 }
 
 // per camera: A_i + lambda I (full 7x7), block-Jacobi inverse of S_ii, right-hand side g_i
@@ -409,7 +454,7 @@ __global__ void k_cam_blocks(BaDev d) {
   int k = 0;
   for (int a = 0; a < 7; ++a) {
     for (int b = a; b < 7; ++b, ++k) {
-      double va = acc[k], vs = acc[k] - acc[28 + k];
+      double va = acc[k], vs = d.schur_diag ? acc[k] - acc[28 + k] : acc[k];
       if (a == b) {
         va += lam;
         vs += lam;
@@ -438,8 +483,8 @@ void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int 
   sh.pt_cap = (ts.max_group_pts + 1) & ~1;
   sh.seg_cap = ts.max_nseg;
   sh.k_cap = ts.max_k;
-  sh.slot_cap = ((ts.max_chunk_len + 15) & ~15) + 1;   // = 1 mod 16: the 9 slot planes start in different banks
-  const int a = 9 * sh.slot_cap, bb = RUN_LANES * RP_STRIDE;
+  sh.slot_cap = ((ts.max_chunk_len + 15) & ~15) + 1;   // = 1 mod 16: the slot planes start in different banks
+  const int a = SLOT_PLANES * sh.slot_cap, bb = RUN_LANES * (d.schur_diag ? Gram<true>::N : Gram<false>::N);
   sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
   const size_t smem = gram_smem_bytes(sh);
   if (g1 < 0) {
@@ -470,11 +515,12 @@ __global__ void __launch_bounds__(256) k_camsum64_peer(BaDev d) {
   __shared__ double sh[3][CAM_ACC];
   const int cam = blockIdx.x;
   const double a = cam_rows_sum64(d, cam, sh);
-  if (threadIdx.x < CAM_ACC)
-    for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)cam * CAM_ACC + threadIdx.x] = a;
+  const int row = d.schur_diag ? CAM_ACC : ROW_COMPACT;     // only the live entries travel
+  if ((int)threadIdx.x < row)
+    for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)cam * row + threadIdx.x] = a;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     const double c = d.sc->cost_cur;
-    for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)d.V * CAM_ACC] = c;
+    for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[(size_t)d.V * row] = c;
   }
   peer_publish(xw, seq, &d.sc->ticket_a);
 }
@@ -485,12 +531,14 @@ __global__ void __launch_bounds__(256) k_cam_gather_peers(BaDev d, int cost_slot
   const unsigned long long seq = *xw.counter() + 1ull;
   const int par = (int)(seq & 1ull);
   peer_wait(xw, seq, sc);
-  const size_t n = (size_t)d.V * CAM_ACC + 1;
+  const int row = d.schur_diag ? CAM_ACC : ROW_COMPACT;
+  const size_t n = (size_t)d.V * row + 1;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     double a = 0.0;
     for (int w = 0; w < xw.world; ++w) a += __ldcg(xw.slot(xw.rank, par, w) + i);
     if (i + 1 < n) {
-      d.cam_acc[i] = a;
+      const size_t cam = i / row;
+      d.cam_acc[cam * CAM_ACC + acc_index(d, (int)(i - cam * row))] = a;
     } else {
       sc->cost_cur = a;
       if (cost_slot < SFMBA_MAX_COST_HISTORY) sc->costs[cost_slot] = a;
@@ -501,7 +549,7 @@ __global__ void __launch_bounds__(256) k_cam_gather_peers(BaDev d, int cost_slot
 
 void launch_camsum64_peer(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc) {
   k_camsum64_peer<<<d.V, 256, 0, st>>>(d);
-  int g = (int)(((size_t)d.V * CAM_ACC + 256) / 256);
+  int g = (int)(((size_t)d.V * (d.schur_diag ? CAM_ACC : ROW_COMPACT) + 256) / 256);
   if (g > 592) g = 592;
   k_cam_gather_peers<<<g, 256, 0, st>>>(d, cost_slot);
   lc.launches += 2;

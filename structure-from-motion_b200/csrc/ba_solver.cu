@@ -58,8 +58,8 @@ cudaError_t sfmba_ctx::reserve(int slot, size_t bytes, void** out) {
 namespace {
 
 enum Slot {
-  S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_UBUF, S_CAM_ACC, S_ABLK, S_MINV,
-  S_CAMIT, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
+  S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_EXV, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_UBUF, S_CAM_ACC, S_ABLK, S_MINV,
+  S_CAMIT, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
   S_CHUNK_INFO, S_REC_B, S_REC_IX, S_REC_W, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
 };
@@ -122,6 +122,7 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
     CARVE(S_Z, 7 * V, z);
     CARVE(S_P, 7 * V, p);
     CARVE(S_Q, 7 * V, q);
+    CARVE(S_S, 7 * V, s);
     CARVE(S_GVEC, 7 * V, gvec);
     CARVE(S_RED_A, 1024, red_a);
     CARVE(S_RED_B, 2048, red_b);
@@ -230,6 +231,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   int rc = sfm_setup_problem(ctx, pr, true, &d);
   if (rc != SFMBA_OK) return rc;
   d.huber_delta = opt.huber_delta;
+  if (opt.mode == SFMBA_MODE_ADAPTIVE_LM && (rc = carve(ctx, S_GRP_EXV, (size_t)d.G + 1, &d.grp_exv)) != 0) return rc;
   if (opt.precond != SFMBA_PRECOND_JACOBI && opt.precond != SFMBA_PRECOND_SCHUR_JACOBI)
     return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "precond is not an sfmba_precond");
   d.schur_diag = (dense || opt.precond == SFMBA_PRECOND_SCHUR_JACOBI) ? 1 : 0;
@@ -479,14 +481,14 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     pt.end(PH_PCG, t0);
 
     t0 = pt.begin();
-    if (adaptive) launch_lm_model_decrease(d, st, lc);
     {
       cudaEvent_t kb = pt.kbegin();
       if (pcg_finished >= 0 && pcg_finished <= PCG_UBUF) {
         launch_backsub_points(d, st, lc);               // the PCG matvecs have left u_j = Dinv B^T p_i per point
       } else {
-        // dense solve, NCCL fallback or a long PCG solve: camit holds the rows of x (launch_cam_rows / the last
-        // k_cam_iter of the solve), one tile pass forms pts += v - Dinv B^T dp
+        // dense solve, NCCL fallback or a long PCG solve: one tile pass forms pts += v - Dinv B^T dp from the camit
+        // rows of x
+        if (!dense) launch_cam_rows(d, d.x, quirk, st, lc);
         launch_matvec(d, ts, true, quirk, st, lc);
       }
       pt.kend("backsub", kb);
@@ -495,8 +497,9 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     if (adaptive) {
       launch_cam_prepare(d, st, lc);
       launch_cost_tiles(d, ts, nullptr, st, lc);       // -> sc->cost_new
+      launch_lm_model_decrease(d, st, lc);             // -> sc->model_decrease, sc->md_pts (the next word)
       if (multi) {
-        if ((rc = sfm_nccl_allreduce_f64(ctx, &d.sc->cost_new, 1, st)) != 0) return rc;
+        if ((rc = sfm_nccl_allreduce_f64(ctx, &d.sc->cost_new, 2, st)) != 0) return rc;
       }
       launch_lm_decide(d, opt.lm_lambda_min > 0 ? opt.lm_lambda_min : 1e-12,
                        opt.lm_lambda_max > 0 ? opt.lm_lambda_max : 1e12, st, lc);
@@ -553,6 +556,10 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     res->ms_total = pt.acc[PH_TOTAL];
     res->kernel_launches = (int32_t)(ctx->lc.launches - launches0);
   }
+  if (hs->flags & SFMBA_FLAG_PEER_TIMEOUT)
+    return sfm_set_error(ctx, SFMBA_ERR_COMM,
+                         "a peer rank never delivered its partial sums (20 s): the cross-rank sums of that iteration are "
+                         "incomplete and its update was not applied");
   if (hs->flags & (SFMBA_FLAG_QW_NEAR_ZERO | SFMBA_FLAG_NONFINITE | SFMBA_FLAG_DEPTH_ZERO | SFMBA_FLAG_SINGULAR)) {
     char buf[96];
     snprintf(buf, sizeof(buf), "device numeric flags 0x%x", hs->flags);
