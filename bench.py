@@ -162,7 +162,8 @@ def run_ours(args):
     V, N, m = full.num_cams, full.num_pts, full.num_obs
     prob = synthetic.shard_problem(full, world, rank) if world > 1 else full
     opt = eng.make_options(lam=LAMBDA, iterations=LM_ITERS, pcg_tol=args.pcg_tol, compute_costs=True,
-                           pcg_max_iter=args.pcg_max_iter)
+                           pcg_max_iter=args.pcg_max_iter,
+                           matvec_precision={'auto': 0, 'f64': 1, 'f32': 2}[args.matvec])
 
     def barrier():
         if world > 1:
@@ -333,6 +334,8 @@ def main():
     ap.add_argument('--scale', type=float, default=1.0)
     ap.add_argument('--pcg-tol', type=float, default=1e-8)
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--matvec', default='auto', choices=['auto', 'f64', 'f32'],
+                    help='sfmba_options.matvec_precision (auto = the library default)')
     ap.add_argument('--pcg-max-iter', type=int, default=0, help='diagnostic: cap PCG iterations (0 = library default)')
     ap.add_argument('--profile-timed', action='store_true', help='keep per-kernel event timing on inside the timed region')
     args = ap.parse_args()

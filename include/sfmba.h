@@ -72,6 +72,14 @@ typedef enum { SFMBA_SOLVER_PCG = 0, SFMBA_SOLVER_DENSE_CHOLESKY = 1 } sfmba_sol
  * same number of iterations at every damping tried, so JACOBI is the default.  The solution is
  * the same to the PCG tolerance either way.                                                                        */
 typedef enum { SFMBA_PRECOND_JACOBI = 0, SFMBA_PRECOND_SCHUR_JACOBI = 1 } sfmba_precond;
+/* Arithmetic of the implicit-Schur matvec inside PCG (K3).  The linearisation (A, D, the right-hand side, the
+ * preconditioner), every PCG vector and every dot product are FP64 in all modes.
+ *   F64: per-observation arithmetic in FP64.
+ *   F32: per-observation arithmetic in FP32 on group-local coordinates, run sums FP32, everything above them FP64
+ *        (BASELINE.json north_star: "FP32 with FP64 accumulation").  The PCG then solves S (1 + O(1e-7)) dp = g: the
+ *        step differs from the FP64 one by ~1e-7 cond(Minv S) relative.
+ *   AUTO (default): F32 while that bound is harmless, F64 otherwise -- see DESIGN.md section 4 for the rule.          */
+typedef enum { SFMBA_MATVEC_AUTO = 0, SFMBA_MATVEC_F64 = 1, SFMBA_MATVEC_F32 = 2 } sfmba_matvec_precision;
 
 /*
  * One BA problem (this rank's shard when world_size > 1: cameras replicated, points and their
@@ -117,6 +125,8 @@ typedef struct {
                              /* the observation by rho'(s) (IRLS); costs reported are sum rho.  0 = plain   */
                              /* least squares (the reference has no robust loss). */
                              /* PCG solver only.                                                          */
+  int32_t matvec_precision;  /* sfmba_matvec_precision (PCG solver)                                          */
+  int32_t reserved0;
 } sfmba_options;
 
 typedef struct {
@@ -128,12 +138,12 @@ typedef struct {
   int32_t  pcg_iterations;   /* total over all LM iterations                                        */
   uint32_t flags;            /* SFMBA_FLAG_*                                                        */
   int32_t  num_costs;
-  int32_t  reserved0;
+  int32_t  pcg_refine_iterations;  /* FP64 iterations that finished solves begun with the FP32 matvec (AUTO)   */
   double   costs[SFMBA_MAX_COST_HISTORY];  /* cost at the start of iteration k, then the final cost */
   /* device time of the phases of the last call, milliseconds (CUDA events on `stream`)             */
   float    ms_total, ms_index, ms_linearize, ms_camreduce, ms_pcg, ms_update;
   int32_t  kernel_launches;  /* kernels launched by the call                                        */
-  int32_t  reserved1;
+  int32_t  matvec_precision; /* SFMBA_MATVEC_F64 or SFMBA_MATVEC_F32: what the PCG matvecs of the call ran     */
 } sfmba_result;
 
 /* ---- lifetime -------------------------------------------------------------------------------- */

@@ -23,6 +23,7 @@ FLAG_PEER_TIMEOUT, FLAG_BAD_INDEX = 32, 64
 MODE_REFERENCE_FIXED, MODE_ADAPTIVE_LM = 0, 1
 SOLVER_PCG, SOLVER_DENSE_CHOLESKY = 0, 1
 PRECOND_JACOBI, PRECOND_SCHUR_JACOBI = 0, 1
+MATVEC_AUTO, MATVEC_F64, MATVEC_F32 = 0, 1, 2
 SOLVER_PCG = 0
 
 
@@ -42,17 +43,18 @@ class Options(C.Structure):
     _fields_ = [('lambda_', C.c_double), ('iterations', C.c_int32), ('mode', C.c_int32), ('solver', C.c_int32),
                 ('pcg_max_iter', C.c_int32), ('pcg_tol', C.c_double), ('dvdc_sign_quirk', C.c_int32),
                 ('force_slow_path', C.c_int32), ('compute_costs', C.c_int32), ('precond', C.c_int32),
-                ('lm_lambda_min', C.c_double), ('lm_lambda_max', C.c_double), ('huber_delta', C.c_double)]
+                ('lm_lambda_min', C.c_double), ('lm_lambda_max', C.c_double), ('huber_delta', C.c_double),
+                ('matvec_precision', C.c_int32), ('reserved0', C.c_int32)]
 
 
 class Result(C.Structure):
     _fields_ = [('initial_cost', C.c_double), ('final_cost', C.c_double), ('final_lambda', C.c_double),
                 ('iterations_done', C.c_int32), ('iterations_accepted', C.c_int32), ('pcg_iterations', C.c_int32),
-                ('flags', C.c_uint32), ('num_costs', C.c_int32), ('reserved0', C.c_int32),
+                ('flags', C.c_uint32), ('num_costs', C.c_int32), ('pcg_refine_iterations', C.c_int32),
                 ('costs', C.c_double * SFMBA_MAX_COST_HISTORY),
                 ('ms_total', C.c_float), ('ms_index', C.c_float), ('ms_linearize', C.c_float),
                 ('ms_camreduce', C.c_float), ('ms_pcg', C.c_float), ('ms_update', C.c_float),
-                ('kernel_launches', C.c_int32), ('reserved1', C.c_int32)]
+                ('kernel_launches', C.c_int32), ('matvec_precision', C.c_int32)]
 
 
 # every symbol include/sfmba.h declares: name -> (restype, argtypes)

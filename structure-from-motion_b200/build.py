@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 OBJ = os.path.join(HERE, 'build')
 LIB = os.path.join(HERE, 'libsfmba.so')
-SOURCES = ['ba_index.cu', 'ba_linearize.cu', 'ba_schur.cu', 'ba_pcg.cu', 'dense.cu', 'ba_solver.cu', 'refine.cu', 'ransac.cu',
+SOURCES = ['ba_index.cu', 'ba_linearize.cu', 'ba_schur.cu', 'ba_pcg.cu', 'ba_matvec32.cu', 'dense.cu', 'ba_solver.cu', 'refine.cu', 'ransac.cu',
            'visibility.cu', 'noalloc.cu', 'nccl_dl.cu', 'peer_window.cu', 'capi.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden', '--expt-relaxed-constexpr']
@@ -57,12 +57,17 @@ def build_library(force=False, verbose=False):
             if r.returncode != 0:
                 raise RuntimeError('nvcc failed for ' + cmd[-3])
     if jobs or force or _stale(LIB, objs):
-        cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', LIB] + objs + \
+        # link beside the target and rename: a reader (or a snapshot of the tree) never sees a half-written library
+        tmp = LIB + '.tmp%d' % os.getpid()
+        cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs + \
               ['-Xcompiler', '-fPIC', '-lcudart_static', '-ldl', '-lpthread', '-lrt']
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)
+            if os.path.exists(tmp):
+                os.remove(tmp)
             raise RuntimeError('link failed')
+        os.replace(tmp, LIB)
     return LIB
 
 

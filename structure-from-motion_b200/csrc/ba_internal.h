@@ -158,6 +158,11 @@ struct BaDev {
   double* minv;                       // [V][49] block-Jacobi inverse of S_ii
   // PCG
   double* camit;                      // [V][16]
+  // single-precision matvec (ba_matvec32.cu); null when the solve runs the FP64 matvec only
+  float4* xrel;                       // [N] point - origin of its group (first point of the group), FP64 difference stored FP32
+  float* dinv32;                      // [N][8] D^-1 (00 01 02 11 12 22 - -)
+  float* segst;                       // [chunk_bound*SEG_CAP][12] per (chunk, segment): R (9), C - group origin (3)
+  float* camit32;                     // [V][16] FP32 copy of the camit rows
   double* part12;                     // [chunk_bound*SEG_CAP][MV_ACC]
   double* svec;                       // [7V] sum_j W D^-1 W^T p (local; allreduced when world > 1)
   double* x;                          // [7V] solution (delta p)
@@ -221,11 +226,15 @@ void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     
 void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 void launch_matvec(const BaDev& d, const TileShape& ts, bool backsub, bool dvdc_quirk, cudaStream_t st,
                    LaunchCounter& lc);
+void launch_matvec32(const BaDev& d, const TileShape& ts, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);   // FP32 arithmetic
 void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // part12 -> svec (multi-GPU)
 // vector part of one PCG iteration.  mode 1: y from this GPU's rows; 2: y = svec (NCCL all-reduced);
 // 3: partial y exchanged through the peer windows over NVLink inside the kernel
 void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
                      cudaStream_t st, LaunchCounter& lc);
+void launch_pcg_reopen(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
+void launch_pcg_refresh(const BaDev& d, int mode, double tol, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
+                        LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_backsub_points(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);

@@ -533,19 +533,52 @@ __device__ __forceinline__ double row7_dot(const double* __restrict__ M49, int l
   return a;
 }
 
+// the same with the lane's row of the block already in registers
+__device__ __forceinline__ double row7_dot_reg(const double row[7], double v_lane) {
+  double a = 0.0;
+#pragma unroll
+  for (int b = 0; b < 7; ++b) a += row[b] * __shfl_sync(0xffffffffu, v_lane, b);
+  return a;
+}
+
+// two block-wide sums in one exchange (scratch: 64 doubles); results valid in all threads
+__device__ __forceinline__ void block_sum2(double& a, double& b, double* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  a = warp_sum(a);
+  b = warp_sum(b);
+  __syncthreads();
+  if (lane == 0) {
+    scratch[warp] = a;
+    scratch[32 + warp] = b;
+  }
+  __syncthreads();
+  double ta = 0.0, tb = 0.0;
+  for (int w = 0; w < nwarps; ++w) {
+    ta += scratch[w];
+    tb += scratch[32 + w];
+  }
+  a = ta;
+  b = tb;
+}
+
 // camit row of a camera whose vector entries sit in lanes 0..6 (every lane computes the row, lanes 0..15 store it)
-__device__ __forceinline__ void warp_camit_row(const BaDev& d, int cam, int lane, double v_lane, int dvdc_quirk) {
+__device__ __forceinline__ void warp_camit_row(const BaDev& d, int cam, int lane, double v_lane, int dvdc_quirk,
+                                               const double* t_pre = nullptr) {
   double dl[7], o[16];
 #pragma unroll
   for (int k = 0; k < 7; ++k) dl[k] = __shfl_sync(0xffffffffu, v_lane, k);
-  camit_row(d.camtab + (size_t)CAMTAB_STRIDE * cam, dl, dvdc_quirk, o);
+  if (t_pre) camit_row(t_pre, dl, dvdc_quirk, o); else camit_row(d.camtab + (size_t)CAMTAB_STRIDE * cam, dl, dvdc_quirk, o);
   o[14] = 0.0;
   o[15] = 0.0;
   double mine = 0.0;
 #pragma unroll
   for (int e = 0; e < 16; ++e)
     if (lane == e) mine = o[e];
-  if (lane < 16) d.camit[(size_t)CAMIT_STRIDE * cam + lane] = mine;
+  if (lane < 16) {
+    d.camit[(size_t)CAMIT_STRIDE * cam + lane] = mine;
+    if (d.camit32) d.camit32[(size_t)CAMIT_STRIDE * cam + lane] = (float)mine;
+  }
 }
 
 // All CTAs of the grid are resident (the launcher sizes the grid to the SM count): arrive, then spin until everyone
@@ -568,6 +601,44 @@ __device__ __forceinline__ void grid_barrier(uint32_t* counter, Scalars* sc) {
   __syncthreads();
 }
 
+// y of one PCG matvec, by mode.  MODE 3 first exchanges the partial results: every rank's y from its own rows goes
+// straight into its slot of EVERY rank's peer window over NVLink, the CTA that finishes last raises the flags, every CTA
+// waits for the flags of all ranks (this wait is also the grid-wide barrier between the stores and the reads below).
+// Returns the parity of the exchange.
+template <int MODE>
+__device__ __forceinline__ int pcg_exchange_y(const BaDev& d, double2* gat_warp) {
+  if (MODE != 3) return 0;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const PeerWindow& xw = d.xw;
+  const unsigned long long seq = *xw.counter() + 1ull;      // advanced by the CTA that finishes the kernel last
+  const int par = (int)(seq & 1ull);
+  for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
+    const double y = cam_y_gather(d, cam, lane, gat_warp);
+    if (lane < 7) {
+      const size_t k = 7 * (size_t)cam + lane;
+      for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
+    }
+  }
+  peer_publish(xw, seq, &d.sc->ticket_a);
+  peer_wait(xw, seq, d.sc);
+  return par;
+}
+
+// MODE 1: from this GPU's rows; 2: svec, all-reduced by NCCL; 3: the slots of all ranks, summed in rank order
+template <int MODE>
+__device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, int par, double2* gat_warp) {
+  if (MODE == 1) return cam_y_gather(d, cam, lane, gat_warp);
+  double y = 0.0;
+  if (lane < 7) {
+    const size_t k = 7 * (size_t)cam + lane;
+    if (MODE == 2) y = d.svec[k];
+    if (MODE == 3) {
+      for (int w = 0; w < d.xw.world; ++w) y += __ldcg(d.xw.slot(d.xw.rank, par, w) + k);
+    }
+  }
+  return y;
+}
+
 // ---- the vector part of the solve ------------------------------------------------------------------------
 // Preconditioned conjugate gradients in the Chronopoulos-Gear form: the matvec is applied to z = Minv r (k_matvec reads
 // the camit rows of z), and ONE grid-wide reduction per iteration gives both scalars,
@@ -584,43 +655,42 @@ __device__ __forceinline__ void grid_barrier(uint32_t* counter, Scalars* sc) {
 template <int MODE>
 __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, int max_iter, unsigned epoch,
                                                          int dvdc_quirk) {
-  __shared__ double red[32];
+  __shared__ double red[64];
   __shared__ double2 gat[VEC_WARPS][96];
-  pdl_wait();
-  Scalars* sc = d.sc;
-  if (sc->pcg_done) return;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int gwarp = blockIdx.x * VEC_WARPS + warp, nwarps = gridDim.x * VEC_WARPS;
   const bool l7 = lane < 7;
+  // What does not change during the solve is fetched before the wait on the matvec: the lane's rows of A and Minv and the
+  // camera-table row of the warp's first camera (its only one unless V exceeds the grid's warps)
+  double arow[7], mrow[7], trow[16];
+#pragma unroll
+  for (int b = 0; b < 7; ++b) arow[b] = mrow[b] = 0.0;
+#pragma unroll
+  for (int b = 0; b < 16; ++b) trow[b] = 0.0;
+  if (gwarp < d.V) {
+    if (l7) {
+#pragma unroll
+      for (int b = 0; b < 7; ++b) {
+        arow[b] = d.ablk[49 * (size_t)gwarp + lane * 7 + b];
+        mrow[b] = d.minv[49 * (size_t)gwarp + lane * 7 + b];
+      }
+    }
+#pragma unroll
+    for (int b = 0; b < 16; ++b) trow[b] = d.camtab[(size_t)CAMTAB_STRIDE * gwarp + b];
+  }
+  pdl_wait();
+  Scalars* sc = d.sc;
+  if (sc->pcg_done) return;
   // scalars of the previous iteration: rewritten only by the CTA that finishes this kernel last
   const double gam_old = sc->rz, alpha_old = sc->alpha, gg = sc->gg;
   const int it_old = sc->pcg_iters;
-  int par = 0;
-  if (MODE == 3) {
-    const PeerWindow& xw = d.xw;
-    const unsigned long long seq = *xw.counter() + 1ull;    // advanced by the CTA that finishes last
-    par = (int)(seq & 1ull);
-    for (int cam = gwarp; cam < d.V; cam += nwarps) {
-      const double y = cam_y_gather(d, cam, lane, gat[warp]);
-      if (l7) {
-        const size_t k = 7 * (size_t)cam + lane;
-        for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
-      }
-    }
-    peer_publish(xw, seq, &sc->ticket_a);
-    peer_wait(xw, seq, sc);
-  }
+  const int par = pcg_exchange_y<MODE>(d, gat[warp]);
   double gam = 0.0, del = 0.0;
   for (int cam = gwarp; cam < d.V; cam += nwarps) {
     const size_t k = 7 * (size_t)cam + lane;
-    double y = 0.0;
-    if (MODE == 1) y = cam_y_gather(d, cam, lane, gat[warp]);
-    if (MODE == 2 && l7) y = d.svec[k];
-    if (MODE == 3 && l7) {
-      for (int w = 0; w < d.xw.world; ++w) y += __ldcg(d.xw.slot(d.xw.rank, par, w) + k);
-    }
+    const double y = pcg_cam_y<MODE>(d, cam, lane, par, gat[warp]);
     const double zv = l7 ? d.z[k] : 0.0;
-    const double az = row7_dot(d.ablk + 49 * (size_t)cam, lane, zv);
+    const double az = cam == gwarp ? row7_dot_reg(arow, zv) : row7_dot(d.ablk + 49 * (size_t)cam, lane, zv);
     if (l7) {
       const double wv = az - y;
       d.q[k] = wv;
@@ -628,16 +698,19 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, i
       del += zv * wv;
     }
   }
-  gam = block_sum(gam, red);
-  del = block_sum(del, red);
+  block_sum2(gam, del, red);
   if (tid == 0) {
     d.red_a[2 * blockIdx.x] = gam;
     d.red_a[2 * blockIdx.x + 1] = del;
   }
   grid_barrier(&sc->bar_a, sc);
   pdl_trigger();                                   // every CTA of this grid is resident: the next kernel may queue up
-  gam = all_blocks_sum(d.red_a, 2, 0, red);
-  del = all_blocks_sum(d.red_a, 2, 1, red);
+  gam = del = 0.0;
+  for (int b = tid; b < (int)gridDim.x; b += blockDim.x) {
+    gam += __ldcg(d.red_a + 2 * b);
+    del += __ldcg(d.red_a + 2 * b + 1);
+  }
+  block_sum2(gam, del, red);                       // every CTA sums the partials in CTA order: identical scalars
   const double beta = it_old == 0 ? 0.0 : gam / gam_old;
   const double den = it_old == 0 ? del : del - beta * gam / alpha_old;
   const double alpha = gam / den;
@@ -655,9 +728,9 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, i
       d.r[k] = rn;
       rr += rn * rn;
     }
-    const double zn = row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
+    const double zn = cam == gwarp ? row7_dot_reg(mrow, rn) : row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
     if (l7) d.z[k] = zn;
-    warp_camit_row(d, cam, lane, zn, dvdc_quirk);
+    if (cam == gwarp) warp_camit_row(d, cam, lane, zn, dvdc_quirk, trow); else warp_camit_row(d, cam, lane, zn, dvdc_quirk);
   }
   rr = block_sum(rr, red);
   if (tid == 0) d.red_b[blockIdx.x] = rr;
@@ -738,6 +811,65 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_init(BaDev d, unsigned epoc
   sc->bar_a = 0u;
   sc->pcg_done = done;
   if (d.host_sig) *(volatile unsigned long long*)d.host_sig = ((unsigned long long)epoch << 32) | (done ? 1ull : 0ull);
+}
+
+// Restart of a PCG solve from its current x with a freshly computed residual (the matvec before this kernel was applied
+// to x): r = g - (A x - y), z = Minv r and its camit rows, p = s = 0, iteration count 0.  Used to finish in FP64 a
+// solve whose first iterations ran the FP32 matvec: from here on the residual is a true FP64 one.
+template <int MODE>
+__global__ void __launch_bounds__(VEC_THREADS) k_pcg_refresh(BaDev d, double tol, unsigned epoch, int dvdc_quirk) {
+  __shared__ double red[32];
+  __shared__ double2 gat[VEC_WARPS][96];
+  pdl_wait();
+  pdl_trigger();
+  Scalars* sc = d.sc;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool l7 = lane < 7;
+  const int par = pcg_exchange_y<MODE>(d, gat[warp]);
+  double rr = 0.0;
+  for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
+    const size_t k = 7 * (size_t)cam + lane;
+    const double y = pcg_cam_y<MODE>(d, cam, lane, par, gat[warp]);
+    const double xv = l7 ? d.x[k] : 0.0;
+    const double ax = row7_dot(d.ablk + 49 * (size_t)cam, lane, xv);
+    double rn = 0.0;
+    if (l7) {
+      rn = d.gvec[k] - (ax - y);
+      d.r[k] = rn;
+      d.p[k] = 0.0;
+      d.s[k] = 0.0;
+      rr += rn * rn;
+    }
+    const double zn = row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
+    if (l7) d.z[k] = zn;
+    warp_camit_row(d, cam, lane, zn, dvdc_quirk);
+  }
+  rr = block_sum(rr, red);
+  if (tid == 0) d.red_b[blockIdx.x] = rr;
+  if (!last_cta_arrives(&sc->ticket_b)) return;
+  rr = all_blocks_sum(d.red_b, 1, 0, red);
+  if (tid != 0) return;
+  int done = (rr <= tol * tol * sc->gg) ? 1 : 0;
+  if (!(rr == rr)) {
+    atomicOr(&sc->flags, FLAG_NONFINITE);
+    done = 1;
+  }
+  if (*(volatile uint32_t*)&sc->flags & FLAG_PEER_TIMEOUT) done = 1;
+  if (MODE == 3) *d.xw.counter() += 1ull;
+  sc->rr = rr;
+  sc->rz = 0.0;
+  sc->alpha = 0.0;
+  sc->beta = 0.0;
+  sc->pcg_iters = 0;
+  sc->bar_a = 0u;
+  sc->pcg_done = done;
+  if (d.host_sig) *(volatile unsigned long long*)d.host_sig = ((unsigned long long)epoch << 32) | (done ? 1ull : 0ull);
+}
+
+// the solve goes on: the matvec kernels of a finished solve exit at their first instruction
+__global__ void k_pcg_reopen(BaDev d) {
+  d.sc->pcg_done = 0;
+  d.sc->pcg_iters = PCG_UBUF;          // (no u_j is kept from the matvec on x)
 }
 
 // Back-substitution of a PCG solve of at most PCG_UBUF iterations, pts_j += v_j - D_j^-1 W_j^T delta_p
@@ -939,6 +1071,27 @@ void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigne
     launch_pdl(k_pcg_step<2>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q);
   } else {
     launch_pdl(k_pcg_step<3>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q);
+  }
+  lc.launches += 1;
+}
+
+// x keeps its value, the residual is recomputed from it: camit rows of x, matvec on x (the caller's, FP64), refresh
+void launch_pcg_reopen(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
+  k_cam_rows<<<(d.V + 127) / 128, 128, 0, st>>>(d, d.x, dvdc_quirk ? 1 : 0);
+  k_pcg_reopen<<<1, 1, 0, st>>>(d);
+  lc.launches += 2;
+}
+
+void launch_pcg_refresh(const BaDev& d, int mode, double tol, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
+                        LaunchCounter& lc) {
+  const int g = vec_grid(d);
+  const int q = dvdc_quirk ? 1 : 0;
+  if (mode == 1) {
+    launch_pdl(k_pcg_refresh<1>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, epoch, q);
+  } else if (mode == 2) {
+    launch_pdl(k_pcg_refresh<2>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, epoch, q);
+  } else {
+    launch_pdl(k_pcg_refresh<3>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, epoch, q);
   }
   lc.launches += 1;
 }

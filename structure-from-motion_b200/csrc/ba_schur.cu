@@ -207,6 +207,13 @@ __global__ void __launch_bounds__(RUN_LANES, SCHUR ? 2 : 3) k_linearize(BaDev d,
       sym3_mul(Dinv, ex, v);
       exv += ex[0] * v[0] + ex[1] * v[1] + ex[2] * v[2];
       const size_t pt = (size_t)pt0 + j;
+      if (d.xrel) {                                    // FP32 matvec: the point relative to the group's first point, D^-1
+        d.xrel[pt] = make_float4((float)(Xa[3 * j] - Xa[0]), (float)(Xa[3 * j + 1] - Xa[1]),
+                                 (float)(Xa[3 * j + 2] - Xa[2]), 0.f);
+        float4* dg = reinterpret_cast<float4*>(d.dinv32 + 8 * pt);
+        dg[0] = make_float4((float)Dinv[0], (float)Dinv[1], (float)Dinv[2], (float)Dinv[3]);
+        dg[1] = make_float4((float)Dinv[4], (float)Dinv[5], 0.f, 0.f);
+      }
 #pragma unroll
       for (int e = 0; e < 6; ++e) {
         if (SCHUR) Dv[e * pt_cap + j] = Dinv[e];
@@ -250,6 +257,12 @@ __global__ void __launch_bounds__(RUN_LANES, SCHUR ? 2 : 3) k_linearize(BaDev d,
       load_cam_q(d.camtab, cam, q2);
 #pragma unroll
       for (int e = 0; e < 4; ++e) q2[e] *= 2.0;
+      if (d.segst && cs.srun[rec_seg(ix_first)] == tid) {  // first lane of the segment: its FP32 row for the matvec
+        float4* row = reinterpret_cast<float4*>(d.segst + ((size_t)c * SEG_CAP + rec_seg(ix_first)) * 12);
+        row[0] = make_float4((float)R[0], (float)R[1], (float)R[2], (float)R[3]);
+        row[1] = make_float4((float)R[4], (float)R[5], (float)R[6], (float)R[7]);
+        row[2] = make_float4((float)R[8], (float)(C[0] - Xa[0]), (float)(C[1] - Xa[1]), (float)(C[2] - Xa[2]));
+      }
     }
     for (int k = 0; k < K; ++k) {
       const uint32_t ix_cur = cs.ixs[k * RUN_LANES + tid];

@@ -59,7 +59,7 @@ namespace {
 
 enum Slot {
   S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_EXV, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_UBUF, S_CAM_ACC, S_ABLK, S_MINV,
-  S_CAMIT, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
+  S_CAMIT, S_CAMIT32, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
   S_CHUNK_INFO, S_REC_B, S_REC_IX, S_REC_W, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
 };
@@ -256,6 +256,15 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   const int max_iter = opt.pcg_max_iter > 0 ? opt.pcg_max_iter : std::max(200, std::min(4 * n7, 5000));
   const bool quirk = opt.dvdc_sign_quirk != 0;
   const bool fine = opt.force_slow_path != 0;
+  if (opt.matvec_precision < SFMBA_MATVEC_AUTO || opt.matvec_precision > SFMBA_MATVEC_F32)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "matvec_precision is not an sfmba_matvec_precision");
+  // FP32 matvec: PCG solver, plain least squares, peers or one GPU.  AUTO takes it when the requested tolerance is
+  // within its reach (the operator itself is only good to ~1e-7) and falls back to FP64 iterations for slow solves.
+  const bool f32_ok = !dense && opt.huber_delta == 0.0 && !(ctx->world > 1 && ctx->peer_disabled);
+  const bool auto_prec = opt.matvec_precision == SFMBA_MATVEC_AUTO;
+  const bool use_f32 = f32_ok && (opt.matvec_precision == SFMBA_MATVEC_F32 || (auto_prec && tol >= 1e-8));
+  constexpr int F32_SAFE_ITERS = 8;
+  int refine_iters = 0;
   const bool adaptive = opt.mode == SFMBA_MODE_ADAPTIVE_LM;
   const bool multi = ctx->world > 1;
   const int64_t launches0 = ctx->lc.launches;
@@ -306,6 +315,12 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   ts.max_nseg = std::max(hs->max_nseg, 1);
   ts.max_k = std::max(hs->max_k, 1);
   if ((rc = sfm_setup_chunks(ctx, nchunks, &d)) != 0) return rc;
+  if (use_f32 && !(multi && !peer)) {
+    if ((rc = carve(ctx, S_XREL, (size_t)std::max(d.N, 1), &d.xrel)) != 0) return rc;
+    if ((rc = carve(ctx, S_DINV32, (size_t)8 * std::max(d.N, 1), &d.dinv32)) != 0) return rc;
+    if ((rc = carve(ctx, S_SEGST, (size_t)d.chunk_bound * SEG_CAP * 12, &d.segst)) != 0) return rc;
+    if ((rc = carve(ctx, S_CAMIT32, (size_t)d.V * CAMIT_STRIDE, &d.camit32)) != 0) return rc;
+  }
   int32_t *sort_keys = nullptr, *iota = nullptr;
   temp_bytes = index_temp_bytes(d.G, d.chunk_bound, d.V);
   if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_TEMP, temp_bytes, &temp), "cudaMalloc(temp)")) != 0) return rc;
@@ -393,9 +408,11 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     }
     const int tail_mode = !multi ? 1 : (peer ? 3 : 2);
     int pcg_finished = -1;                 // iterations of this PCG solve when the host knows the number
+    bool mv32 = use_f32 && tail_mode != 2; // arithmetic of the matvecs being launched
+    unsigned cur_epoch = pcg_epoch;
     auto launch_iteration = [&]() -> int {
       cudaEvent_t kb = pt.kbegin();
-      launch_matvec(d, ts, false, quirk, st, lc);
+      if (mv32) launch_matvec32(d, ts, quirk, st, lc); else launch_matvec(d, ts, false, quirk, st, lc);
       pt.kend("matvec", kb);
       if (tail_mode == 2) {
         launch_camsum12(d, st, lc);
@@ -403,7 +420,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
         if (r2 != 0) return r2;
       }
       kb = pt.kbegin();
-      launch_pcg_tail(d, tail_mode, tol, max_iter, pcg_epoch, quirk, st, lc);
+      launch_pcg_tail(d, tail_mode, tol, max_iter, cur_epoch, quirk, st, lc);
       pt.kend("pcg_tail", kb);
       return 0;
     };
@@ -422,14 +439,14 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
         long spins = 0;
         for (;;) {
           const unsigned long long w = *sig;
-          if ((unsigned)(w >> 32) == pcg_epoch) {
+          if ((unsigned)(w >> 32) == cur_epoch) {
             finished = (int)((w & 0xffffffffull) >> 1);
             if (w & 1ull) { done = true; return 0; }
             if (finished >= want) return 0;
           }
           if ((++spins & 0x3fff) == 0 && cudaStreamQuery(st) != cudaErrorNotReady) {
             const unsigned long long w2 = *sig;       // stream drained: final state or an error
-            if ((unsigned)(w2 >> 32) == pcg_epoch) {
+            if ((unsigned)(w2 >> 32) == cur_epoch) {
               finished = (int)((w2 & 0xffffffffull) >> 1);
               if (w2 & 1ull) { done = true; return 0; }
               if (finished >= want) return 0;
@@ -439,21 +456,43 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
           }
         }
       };
-      const int hint = std::min(ctx->pcg_hint, max_iter);
-      for (; launched < hint; ++launched)
-        if ((rc = launch_iteration()) != 0) return rc;
-      if (hint > 0 && (rc = wait_for(hint)) != 0) return rc;
-      while (launched < max_iter && !done) {
-        if (launched >= LOOKAHEAD + finished) {
-          if ((rc = wait_for(launched - LOOKAHEAD + 1)) != 0) return rc;
-          if (done) break;
+      auto run = [&](int hint) -> int {
+        for (; launched < hint; ++launched)
+          if ((rc = launch_iteration()) != 0) return rc;
+        if (hint > 0 && (rc = wait_for(hint)) != 0) return rc;
+        while (launched < max_iter && !done) {
+          if (launched >= LOOKAHEAD + finished) {
+            if ((rc = wait_for(launched - LOOKAHEAD + 1)) != 0) return rc;
+            if (done) break;
+          }
+          if ((rc = launch_iteration()) != 0) return rc;
+          ++launched;
         }
-        if ((rc = launch_iteration()) != 0) return rc;
-        ++launched;
-      }
-      if (!done && (rc = wait_for(launched)) != 0) return rc;   // max_iter reached: the kernel sets done itself
+        if (!done && (rc = wait_for(launched)) != 0) return rc;   // max_iter reached: the kernel sets done itself
+        return 0;
+      };
+      if ((rc = run(std::min(ctx->pcg_hint, max_iter))) != 0) return rc;
       ctx->pcg_hint = finished;
       pcg_finished = finished;
+      if (mv32 && auto_prec && finished > F32_SAFE_ITERS && finished < max_iter) {
+        // AUTO: a solve this slow amplifies the 1e-7 operator error of the FP32 matvec too much to accept unseen.  Its
+        // x is the starting point of an FP64 continuation: true residual from one FP64 matvec on x, then FP64 iterations
+        // until that residual meets the tolerance (usually very few)
+        mv32 = false;
+        cur_epoch = ++ctx->pcg_epoch;
+        launch_pcg_reopen(d, quirk, st, lc);
+        cudaEvent_t kb = pt.kbegin();
+        launch_matvec(d, ts, false, quirk, st, lc);
+        pt.kend("matvec64", kb);
+        launch_pcg_refresh(d, tail_mode, tol, cur_epoch, quirk, st, lc);
+        launched = 0;
+        finished = 0;
+        done = false;
+        if ((rc = wait_for(0)) != 0) return rc;              // the refresh itself may find the solve converged
+        if (!done && (rc = run(0)) != 0) return rc;
+        refine_iters += finished;
+        pcg_finished = -1;                                   // x is no longer sum alpha_i p_i of one run: tile back-substitution
+      }
     } else {
       const int batch = 4;
       int32_t* done_host = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ctx->pinned) + 16);
@@ -555,6 +594,8 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     res->ms_update = pt.acc[PH_UPDATE];
     res->ms_total = pt.acc[PH_TOTAL];
     res->kernel_launches = (int32_t)(ctx->lc.launches - launches0);
+    res->pcg_refine_iterations = refine_iters;
+    res->matvec_precision = (use_f32 && d.xrel) ? SFMBA_MATVEC_F32 : SFMBA_MATVEC_F64;
   }
   if (hs->flags & SFMBA_FLAG_PEER_TIMEOUT)
     return sfm_set_error(ctx, SFMBA_ERR_COMM,

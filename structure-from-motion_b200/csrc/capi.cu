@@ -75,6 +75,7 @@ void sfmba_default_options(sfmba_options* opt) {
   opt->precond = SFMBA_PRECOND_JACOBI;
   opt->lm_lambda_min = 1e-12;
   opt->lm_lambda_max = 1e12;
+  opt->matvec_precision = SFMBA_MATVEC_AUTO;
 }
 
 const char* sfmba_last_error(const sfmba_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }

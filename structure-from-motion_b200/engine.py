@@ -73,6 +73,8 @@ class SolveResult:
     costs: list = field(default_factory=list)
     ms: dict = field(default_factory=dict)
     kernel_launches: int = 0
+    pcg_refine_iterations: int = 0
+    matvec_precision: int = 0
 
 
 def _ptr(a):
@@ -129,7 +131,7 @@ class Engine:
     # -- options ----------------------------------------------------------------------------------
     def make_options(self, lam=5.0, iterations=3, mode=_capi.MODE_REFERENCE_FIXED, pcg_tol=1e-8, pcg_max_iter=0,
                      dvdc_sign_quirk=True, force_slow_path=False, compute_costs=True, solver=_capi.SOLVER_PCG,
-                     huber_delta=0.0, precond=_capi.PRECOND_JACOBI):
+                     huber_delta=0.0, precond=_capi.PRECOND_JACOBI, matvec_precision=_capi.MATVEC_AUTO):
         opt = _capi.default_options()
         opt.solver = int(solver)
         opt.lambda_ = float(lam)
@@ -142,6 +144,7 @@ class Engine:
         opt.compute_costs = 1 if compute_costs else 0
         opt.huber_delta = float(huber_delta)
         opt.precond = int(precond)
+        opt.matvec_precision = int(matvec_precision)
         return opt
 
     @staticmethod
@@ -151,7 +154,7 @@ class Engine:
                            [res.costs[i] for i in range(res.num_costs)],
                            dict(total=res.ms_total, index=res.ms_index, linearize=res.ms_linearize,
                                 camreduce=res.ms_camreduce, pcg=res.ms_pcg, update=res.ms_update),
-                           res.kernel_launches)
+                           res.kernel_launches, res.pcg_refine_iterations, res.matvec_precision)
 
     # -- BA: host buffers (the end-to-end path) ---------------------------------------------------
     def _host_problem(self, p: BAProblem) -> _capi.Problem:
