@@ -1,21 +1,23 @@
 #!/usr/bin/env python3
 """bench.py -- BA LM iterations/s at Venice shape (BASELINE.json), 1..8 B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--shape venice]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--shape venice] [--matvec auto|f64|f32]
 
-A "step" is one BaProcessor-style BA call in reference mode (lambda 5, 3 always-accepted LM
-iterations, reduced system solved to pcg_tol) on the synthetic Venice-shaped problem
-(1778 cameras / 993 923 points / 5 001 946 observations); every step starts from the same initial
-parameters (device-to-device restore inside the timed region).
-  value   whole-job LM iterations/s with the problem resident in HBM
-  e2e     the same through sfmba_ba_solve_host (HOST buffers: pinned H2D of every input, D2H of
-          cameras and points inside the timed region)
-  roofline      the implicit-Schur matvec K3 (one PCG iteration of k_pcg_solve), algorithmic bytes / CUDA-event time
-  cpu_baseline  the NumPy/SciPy oracle port timed on this host on a 1/4-scale Venice sample
-With N > 1 (torchrun) the points are sharded by observation count across ranks (strong scaling),
-cameras replicated, NCCL all-reduces the camera-side blocks and the matvec result.
-`--impl reference` times the oracle port (the reference is pure Python and cannot travel; its
-literal code cannot run beyond ~3 k observations) on the host cores.
+A "step" is one BaProcessor-style BA call in reference mode (lambda 5, 3 always-accepted LM iterations, reduced system
+solved to pcg_tol) on the synthetic Venice-shaped problem (1778 cameras / 993 923 points / 5 001 946 observations); every
+step starts from the same initial parameters (device-to-device restore inside the timed region).
+  value             whole-job LM iterations/s with the problem resident in HBM
+  e2e               the same through sfmba_ba_solve_host (HOST buffers: pinned H2D of every input, D2H of cameras and
+                    points inside the timed region)
+  roofline          the implicit-Schur matvec K3 (matvec kernel + k_pcg_step = one PCG iteration), algorithmic bytes over
+                    CUDA-event time; `traffic` only when profiles/r2_ncu_traffic.json was captured from these sources
+  parity_vs_golden  the timed answer against the committed full-size oracle golden (every rank; a mismatch exits 3)
+  c3, ba_weak_damping   (N = 1) BASELINE.json config C3 and the slow-PCG regime, each with its own CPU / parity figures
+  cpu_baseline      the NumPy/SciPy oracle port timed on this host on the full problem (one LM iteration)
+With N > 1 (torchrun) the points are sharded by observation count across ranks (strong scaling), cameras replicated; the
+partial sums cross NVLink through peer windows inside the PCG kernels.
+`--impl reference` times the oracle port (the reference is pure Python and cannot travel; its literal code cannot run beyond
+~3 k observations) on the host cores, on the full problem.
 """
 import argparse
 import json
@@ -32,12 +34,9 @@ sys.path.insert(0, ROOT)
 
 LM_ITERS = 3
 LAMBDA = 5.0
-CPU_SAMPLE_SCALE = 0.25
-# ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of ONE k_matvec<0> launch at the full Venice
-# shape on one GPU (profiles/r1_ncu_full_v55_summary.txt, mean of two launches: 104.52 MB read + 19.65 MB written); the same for the one
-# k_linearize<0, 0> launch of that capture (155.09 MB read + 133.70 MB written)
-NCU_DRAM_BYTES_PER_MATVEC = {('venice', 1.0, 1): 124.17e6}
-NCU_DRAM_BYTES_PER_LINEARIZE = {('venice', 1.0, 1): 288.79e6}
+GOLDEN = os.path.join(ROOT, 'tests', 'golden')
+COST_RTOL, PARAM_TOL = 1e-6, 1e-5            # BASELINE.json north_star: the parity bar
+CPU_BUDGET_S = 150.0                         # wall-clock cap of the CPU legs (repetitions are cut, never the problem)
 
 
 def _peaks():
@@ -46,6 +45,31 @@ def _peaks():
             return float(json.load(f)['hbm_gbs']), 'measured'
     except Exception:
         return 6650.0, 'fallback'
+
+
+def source_sha():
+    """Identity of the kernels: sha256 over the CUDA sources (what an ncu traffic record must have been taken from)."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, 'structure-from-motion_b200', 'csrc')
+    for f in sorted(os.listdir(d)):
+        with open(os.path.join(d, f), 'rb') as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic(kernel, shape, scale, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the newest ncu capture (profiles/ncu_traffic.py writes
+    profiles/r2_ncu_traffic.json).  Only used when that capture was taken from the sources this run is built from."""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'r2_ncu_traffic.json')) as f:
+            rec = json.load(f)
+        if rec.get('source_sha') != source_sha() or rec.get('shape') != shape or float(rec.get('scale', 1.0)) != scale \
+                or int(rec.get('n_gpus', 1)) != world:
+            return None, 'profiles/r2_ncu_traffic.json is from other sources / another shape: not quoted'
+        return rec['kernels'].get(kernel), 'profiles/r2_ncu_traffic.json (%s)' % rec.get('report')
+    except Exception:
+        return None, 'no ncu capture on record'
 
 
 class ClockSampler(threading.Thread):
@@ -79,34 +103,32 @@ class ClockSampler(threading.Thread):
                 'samples': len(sm)}
 
 
-def cpu_baseline(steps=1, warmup=0, shape='venice'):
-    """Oracle port on a bounded sample of the workload, all host threads NumPy/BLAS will use."""
+def cpu_baseline(steps=1, warmup=0, shape='venice', scale=1.0):
+    """The reference's CPU path for this workload: oracle/sfm_oracle.py (NumPy + scipy.sparse port of
+    ba_processor.py:297-406 with the exact dense reduced solve) on the host cores, at the FULL shape.  One timed step is ONE
+    LM iteration; repetitions are cut so that the leg ends within CPU_BUDGET_S (the problem never is)."""
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
     import sfm_oracle as oracle
     from sfm_b200 import synthetic
-    prob, _ = synthetic.make_shape(shape, scale=CPU_SAMPLE_SCALE)
+    prob, _ = synthetic.make_shape(shape, scale=scale)
     b = prob.obs_uv.T.astype(np.float64)
-    V, N, m, _ = synthetic.SHAPES[shape]
     times = []
+    t_start = time.perf_counter()
     for s in range(warmup + steps):
         t0 = time.perf_counter()
         oracle.ba_solve(prob.cams, prob.pts, prob.obs_cam, prob.obs_pt, b, LAMBDA, 1, sparse=True, return_costs=False)
         dt = time.perf_counter() - t0
-        if s >= warmup:
+        if s >= warmup or not times:
             times.append(dt)
+        if time.perf_counter() - t_start + dt > CPU_BUDGET_S:      # the next repetition would not fit
+            break
     per_iter = float(np.mean(times))
-    obs_per_s = prob.num_obs / per_iter
     return {
-        'value': obs_per_s / m,                 # LM iterations/s at full shape, linear extrapolation
-        'unit': 'LM iterations/s',
-        'cores': os.cpu_count(),
-        'kind': 'port',
-        'sample': '%d LM iteration(s) of oracle/sfm_oracle.py (NumPy + scipy.sparse, dense reduced solve) on a '
-                  '%.2f-scale %s problem (%d cams / %d pts / %d obs, %.1f s each); obs/s scaled linearly to the '
-                  'full shape, which favours the CPU (its reduced solve is cubic in cameras)'
-                  % (steps, CPU_SAMPLE_SCALE, shape, prob.num_cams, prob.num_pts, prob.num_obs, per_iter),
-        'obs_per_s': obs_per_s,
-        'ms_per_step': per_iter * 1e3,
+        'value': 1.0 / per_iter, 'unit': 'LM iterations/s', 'cores': os.cpu_count(), 'kind': 'port',
+        'sample': '%d LM iteration(s) of oracle/sfm_oracle.py (NumPy + scipy.sparse, exact dense reduced solve) on the full '
+                  '%s problem (%d cams / %d pts / %d obs), %.1f s each; no extrapolation'
+                  % (len(times), shape, prob.num_cams, prob.num_pts, prob.num_obs, per_iter),
+        'obs_per_s': prob.num_obs / per_iter, 'ms_per_step': per_iter * 1e3, 'steps_run': len(times),
     }
 
 
@@ -119,7 +141,7 @@ def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    base = cpu_baseline(steps=max(1, args.steps), warmup=args.warmup, shape=args.shape)
+    base = cpu_baseline(steps=max(1, args.steps), warmup=args.warmup, shape=args.shape, scale=args.scale)
     from sfm_b200 import synthetic
     V, N, m, _ = synthetic.SHAPES[args.shape]
     line = {
@@ -127,15 +149,112 @@ def run_reference(args):
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': base['ms_per_step'],
         'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
         'config': {'workload': workload_name(args.shape, V, N, m, args.pcg_tol),
-                   'note': 'CPU arm: each timed step is ONE LM iteration of the oracle port (exact reduced solve instead '
-                           'of PCG) on a %.2f-scale sample of the workload; value = LM iterations/s scaled linearly in '
-                           'observations to the full shape' % CPU_SAMPLE_SCALE,
-                   'sample_scale': CPU_SAMPLE_SCALE},
+                   'note': 'CPU arm: each timed step is ONE LM iteration of the oracle port (exact reduced solve instead of '
+                           'PCG) on the full workload; %d of the %d requested steps were run (wall-clock cap %.0f s)'
+                           % (base['steps_run'], args.steps, CPU_BUDGET_S),
+                   'sample_scale': args.scale, 'steps_run': base['steps_run']},
         'cpu_baseline': {k: base[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
         'e2e': {'value': base['value'], 'unit': 'LM iterations/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'jacobian_schur_obs_per_sec': base['obs_per_s'],
     }
     emit(line)
+
+
+def max_rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b) / np.maximum(1.0, np.abs(b)))) if a.size else 0.0
+
+
+def golden_parity(name, cams, pts, final_cost, pt_range=None):
+    """Distance of a finished solve from the committed full-size oracle golden (tests/golden/make_golden_bal.py).
+    pt_range = (p0, p1): this rank holds the points [p0, p1) only."""
+    z = np.load(os.path.join(GOLDEN, name + '.npz'))
+    idx, ref = z['pts_idx'], z['pts_sample']
+    if pt_range is not None:
+        keep = (idx >= pt_range[0]) & (idx < pt_range[1])
+        idx, ref = idx[keep] - pt_range[0], ref[keep]
+    return {'cams_max_rel': max_rel(cams, z['cams']), 'pts_max_rel': max_rel(pts[idx], ref),
+            'cost_rel': abs(final_cost - float(z['costs'][-1])) / float(z['costs'][-1])}
+
+
+def extra_c3(eng):
+    """BASELINE.json config C3 in the same run: 1 M-point nonlinear triangulation (a18) and 10 k-view nonlinear PnP (a19)
+    through the host-buffer entry points (copies inside the time), with the oracle timed on a sample of the same batch."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import sfm_oracle as oracle
+    from sfm_b200 import synthetic
+
+    def best_of(fn, n=2):
+        fn()
+        best = 1e30
+        for _ in range(n):
+            t0 = time.perf_counter()
+            fn()
+            best = min(best, time.perf_counter() - t0)
+        return best
+    out = {}
+    M, it_tri = 1000000, 100
+    projs, rowptr, obs_view, uv, X0 = synthetic.tri_problem(M, np.random.default_rng(3))
+    dt = best_of(lambda: eng.triangulate_refine(projs, rowptr, obs_view, uv, X0, 0.5, it_tri))
+    n_cpu = 300
+    t0 = time.perf_counter()
+    for j in range(n_cpu):
+        o = slice(rowptr[j], rowptr[j + 1])
+        pairs = [np.array([[uv[q, 0]], [uv[q, 1]], [1.0]]) for q in range(o.start, o.stop)]
+        oracle.nonlinear_triangulate(np.append(X0[j], 1.0).reshape(4, 1), projs[obs_view[o]], pairs, 0.5, it_tri)
+    cpu = (time.perf_counter() - t0) / (n_cpu * it_tri)
+    out['triangulation'] = {
+        'workload': '%d points, %d observations, lambda 0.5, %d iterations (triangulation_processor.py:160-234)' % (M, int(rowptr[-1]), it_tri),
+        'seconds': dt, 'value': M * it_tri / dt, 'unit': 'point-iterations/s',
+        'cpu_baseline': {'value': 1.0 / cpu, 'unit': 'point-iterations/s', 'cores': 1, 'kind': 'port',
+                         'sample': 'oracle.nonlinear_triangulate on the first %d points of the batch' % n_cpu},
+        'bound': 'latency / FP64 issue: one thread per point, the whole damped Gauss-Newton loop in registers; the batch '
+                 'moves 48 B per point once (16 MB + 64 MB of observations), far below HBM time'}
+    P, it_pnp = 10000, 300
+    rp, xy, X, rots, locs = synthetic.pnp_problem(P, np.random.default_rng(4))
+    dt = best_of(lambda: eng.pnp_refine(rp, xy, X, rots, locs, 5.0, it_pnp))
+    n_cpu = 8
+    t0 = time.perf_counter()
+    for v in range(n_cpu):
+        o = slice(rp[v], rp[v + 1])
+        n = o.stop - o.start
+        oracle.nonlinear_pnp(np.vstack((xy[o].T, np.ones(n))), np.vstack((X[o].T, np.ones(n))), np.eye(3), rots[v],
+                             locs[v].reshape(3, 1), 5.0, it_pnp)
+    cpu = (time.perf_counter() - t0) / (int(rp[n_cpu]) * it_pnp)
+    out['pnp'] = {
+        'workload': '%d views, %d observations, lambda 5, %d iterations (campose_processor.py:308-459)' % (P, int(rp[-1]), it_pnp),
+        'seconds': dt, 'value': int(rp[-1]) * it_pnp / dt, 'unit': 'observation-iterations/s',
+        'cpu_baseline': {'value': 1.0 / cpu, 'unit': 'observation-iterations/s', 'cores': 1, 'kind': 'port',
+                         'sample': 'oracle.nonlinear_pnp on the first %d views of the batch' % n_cpu},
+        'bound': 'latency / FP64 issue: one warp per view, observations re-read from L1/L2 every iteration'}
+    return out
+
+
+def extra_weak_damping(eng):
+    """The matvec-dominated regime: lambda = 1e-2, exact dv/dC Jacobian, quarter-Venice, 2 LM iterations, default options
+    (the configuration of tests/golden/bal_venice_weak.npz), device-resident."""
+    import torch
+    from sfm_b200 import synthetic
+    z = np.load(os.path.join(GOLDEN, 'bal_venice_weak.npz'))
+    prob, _ = synthetic.make_shape(str(z['shape']), scale=float(z['scale']))
+    t = eng.to_device(prob)
+    c0, p0 = t['cams'].clone(), t['pts'].clone()
+    opt = eng.make_options(lam=float(z['lam']), iterations=int(z['iterations']), dvdc_sign_quirk=bool(z['dvdc_quirk']))
+    best, res = 1e30, None
+    for _ in range(5):
+        t['cams'].copy_(c0)
+        t['pts'].copy_(p0)
+        torch.cuda.synchronize()
+        res = eng.ba_solve_device(t, opt)
+        best = min(best, res.ms['total'])
+    par = golden_parity('bal_venice_weak', t['cams'].cpu().numpy(), t['pts'].cpu().numpy(), res.final_cost)
+    its = int(z['iterations'])
+    return {'workload': 'venice x %.2f (%d cams / %d pts / %d obs), lambda=%g, exact dv/dC, %d LM iterations, default options'
+                        % (float(z['scale']), prob.num_cams, prob.num_pts, prob.num_obs, float(z['lam']), its),
+            'value': its / (best * 1e-3), 'unit': 'LM iterations/s', 'device_ms': best,
+            'pcg_iterations_per_lm_iteration': res.pcg_iterations / its,
+            'pcg_fp64_refine_iterations': res.pcg_refine_iterations,
+            'matvec_precision': {1: 'f64', 2: 'f32'}.get(res.matvec_precision), 'parity_vs_golden': par}
 
 
 def run_ours(args):
@@ -161,6 +280,10 @@ def run_ours(args):
     full, _ = synthetic.make_shape(args.shape, scale=args.scale)
     V, N, m = full.num_cams, full.num_pts, full.num_obs
     prob = synthetic.shard_problem(full, world, rank) if world > 1 else full
+    pt_range = None
+    if world > 1:
+        sb = synthetic.shard_bounds(full.rowptr, world)
+        pt_range = (int(sb[rank]), int(sb[rank + 1]))
     opt = eng.make_options(lam=LAMBDA, iterations=LM_ITERS, pcg_tol=args.pcg_tol, compute_costs=True,
                            pcg_max_iter=args.pcg_max_iter,
                            matvec_precision={'auto': 0, 'f64': 1, 'f32': 2}[args.matvec])
@@ -204,6 +327,18 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
+    # ---- parity of the timed answer: every rank compares its cameras, its points and the global cost with the committed
+    # full-size oracle golden of this exact configuration
+    parity = None
+    golden_name = {'venice': 'bal_venice_ref', 'ladybug': 'bal_ladybug_ref'}.get(args.shape)
+    if golden_name and args.scale == 1.0 and args.pcg_max_iter == 0:
+        par = golden_parity(golden_name, t['cams'].cpu().numpy(), t['pts'].cpu().numpy(), res.final_cost, pt_range)
+        pv = torch.tensor([par['cams_max_rel'], par['pts_max_rel'], par['cost_rel']], dtype=torch.float64, device='cuda')
+        if world > 1:
+            dist.all_reduce(pv, op=dist.ReduceOp.MAX)
+        parity = {'golden': 'tests/golden/%s.npz' % golden_name, 'cams_max_rel': float(pv[0]), 'pts_max_rel': float(pv[1]),
+                  'cost_rel': float(pv[2]), 'ranks_compared': world,
+                  'ok': bool(pv[0] <= PARAM_TOL and pv[1] <= PARAM_TOL and pv[2] <= COST_RTOL)}
     if not args.profile_timed:
         # per-kernel CUDA-event timing adds event records between launches: one extra, untimed step
         eng.profile_enable(True)
@@ -268,7 +403,10 @@ def run_ours(args):
         mv_a_ms, mv_a_n = prof['matvec']
         mv_b_ms, mv_b_n = prof['pcg_tail']
         k3_ms = (mv_a_ms + mv_b_ms) / max(prof_pcg_iters, 1)
-        k3_name = 'K3 implicit-Schur matvec = k_matvec + k_pcg_tail (one PCG iteration, rank 0 shard)'
+        mvk = 'k_matvec32' if res.matvec_precision == 2 else 'k_matvec'
+        k3_name = 'K3 implicit-Schur matvec = %s + k_pcg_step (one PCG iteration, rank 0 shard)' % mvk
+        k3_traffic, k3_src = ncu_traffic(mvk, args.shape, args.scale, world)
+        k12_traffic, k12_src = ncu_traffic('k_linearize', args.shape, args.scale, world)
         k3_gbs = k3_bytes / (k3_ms * 1e-3) / 1e9 if k3_ms > 0 else 0.0
         lin_ms, lin_n = prof['linearize']
         cr_ms, cr_n = 0.0, 1
@@ -284,6 +422,8 @@ def run_ours(args):
                        'parallelism': 'points sharded over %d GPU(s), cameras replicated' % world,
                        'pcg_iterations_per_lm_iteration': pcg_iters / max(1, LM_ITERS * args.steps),
                        'preconditioner': 'block-Jacobi on A + lambda I (sfmba_options.precond default)',
+                       'matvec_precision': {1: 'f64', 2: 'f32'}.get(res.matvec_precision),
+                       'matvec_precision_option': args.matvec,
                        'l2': 'inputs larger than L2 (>1 GB streamed per matvec)'},
             'jacobian_schur_obs_per_sec': (m / (k12_ms * 1e-3)) if k12_ms > 0 else None,
             'final_cost': res.final_cost, 'initial_cost': res.initial_cost,
@@ -292,27 +432,35 @@ def run_ours(args):
                           for k, v in prof.items() if v[1] > 0},
             'roofline': {'kernel': k3_name,
                          'bound': 'hbm', 'achieved': k3_gbs, 'peak': peak, 'unit': 'GB/s', 'frac': k3_gbs / peak,
-                         'peak_kind': peak_kind, 'traffic': NCU_DRAM_BYTES_PER_MATVEC.get((args.shape, args.scale, world)),
-                         'traffic_source': 'profiles/r1_ncu_full_v55_summary.txt (k_matvec<0, 0>, one launch)',
-                         'algorithmic_bytes': k3_bytes, 'ms': k3_ms},
+                         'peak_kind': peak_kind, 'traffic': k3_traffic, 'traffic_source': k3_src,
+                         'algorithmic_bytes': k3_bytes, 'ms': k3_ms,
+                         'matvec_alone': {'ms': mv_a_ms / max(prof_pcg_iters, 1),
+                                          'frac': (k3_bytes / (mv_a_ms / max(prof_pcg_iters, 1) * 1e-3) / 1e9 / peak)
+                                          if mv_a_ms > 0 else None}},
             'roofline_jacobian_schur': {'kernel': 'K1+K2 = k_linearize (residuals, Jacobians, point Schur blocks and camera Gram rows in one launch; J never stored)', 'bound': 'hbm',
                                         'achieved': k12_gbs, 'peak': peak, 'unit': 'GB/s', 'frac': k12_gbs / peak,
                                         'algorithmic_bytes': k12_bytes, 'ms': k12_ms,
-                                        'traffic': NCU_DRAM_BYTES_PER_LINEARIZE.get((args.shape, args.scale, world)),
-                                        'traffic_source': 'profiles/r1_ncu_full_v55_summary.txt (k_linearize<0, 0>, one launch)'},
+                                        'traffic': k12_traffic, 'traffic_source': k12_src},
             'e2e': {'value': LM_ITERS * e2e_steps / e2e_s, 'unit': 'LM iterations/s', 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'ms_per_step': e2e_s / e2e_steps * 1e3,
                     'kernel_launches_per_step': launches_e2e},
             'gpu_launches': launches,
             'clocks': sampler.summary(),
+            'parity_vs_golden': parity,
         }
+        if world == 1 and not args.no_extras:
+            line['c3'] = extra_c3(eng)
+            line['ba_weak_damping'] = extra_weak_damping(eng)
         if world == 1 and not args.no_cpu:
-            base = cpu_baseline(steps=1, warmup=0, shape=args.shape)
+            base = cpu_baseline(steps=1, warmup=0, shape=args.shape, scale=args.scale)
             line['cpu_baseline'] = {k: base[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
         emit(line)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and not parity['ok']:
+        sys.stderr.write('bench.py: the timed answer does not match the oracle golden: %r\n' % (parity,))
+        sys.exit(3)
 
 
 def main():
@@ -334,6 +482,7 @@ def main():
     ap.add_argument('--scale', type=float, default=1.0)
     ap.add_argument('--pcg-tol', type=float, default=1e-8)
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-extras', action='store_true', help='skip the c3 / ba_weak_damping keys (N = 1 only)')
     ap.add_argument('--matvec', default='auto', choices=['auto', 'f64', 'f32'],
                     help='sfmba_options.matvec_precision (auto = the library default)')
     ap.add_argument('--pcg-max-iter', type=int, default=0, help='diagnostic: cap PCG iterations (0 = library default)')

@@ -31,7 +31,7 @@ def main():
             env = dict(os.environ)
             if path != 'default':
                 env['SFMBA_LIB'] = os.path.join(ROOT, path)
-            r = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--no-cpu', '--steps', steps, '--warmup', '3'] + extra,
+            r = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--no-cpu', '--no-extras', '--steps', steps, '--warmup', '3'] + extra,
                                capture_output=True, text=True, env=env)
             if r.returncode != 0:
                 print(json.dumps({'build': name, 'error': r.stderr[-600:]}), flush=True)

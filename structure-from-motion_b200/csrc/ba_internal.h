@@ -163,6 +163,7 @@ struct BaDev {
   float* dinv32;                      // [N][8] D^-1 (00 01 02 11 12 22 - -)
   float* segst;                       // [chunk_bound*SEG_CAP][12] per (chunk, segment): R (9), C - group origin (3)
   float* camit32;                     // [V][16] FP32 copy of the camit rows
+  float* ubuf32;                      // [PCG_UBUF][3][N] the u_j the FP32 matvecs keep (as ubuf)
   double* part12;                     // [chunk_bound*SEG_CAP][MV_ACC]
   double* svec;                       // [7V] sum_j W D^-1 W^T p (local; allreduced when world > 1)
   double* x;                          // [7V] solution (delta p)
@@ -236,7 +237,7 @@ void launch_pcg_reopen(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchC
 void launch_pcg_refresh(const BaDev& d, int mode, double tol, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
                         LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
-void launch_backsub_points(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
+void launch_backsub_points(const BaDev& d, bool from_f32, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_model_decrease(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

@@ -141,10 +141,10 @@ __global__ void __launch_bounds__(RUN_LANES, MV32_MINB) k_matvec32(BaDev d, Mv32
     if (gm.nc > 0) mbar_wait(bar, 0);
     return;
   }
-  double* ukeep = nullptr;
+  float* ukeep = nullptr;                            // u_j of this matvec, kept for the back-substitution (FP32 planes)
   {
     const int pcg_it = d.sc->pcg_iters;
-    if (pcg_it < PCG_UBUF) ukeep = d.ubuf + (size_t)pcg_it * 3 * (size_t)d.N + pt0;
+    if (pcg_it < PCG_UBUF) ukeep = d.ubuf32 + (size_t)pcg_it * 3 * (size_t)d.N + pt0;
   }
   // wait for a chunk's tables
   auto finish_chunk = [&]() {
@@ -269,9 +269,9 @@ __global__ void __launch_bounds__(RUN_LANES, MV32_MINB) k_matvec32(BaDev d, Mv32
         u.w = 0.f;
         a = u;
         if (ukeep) {
-          ukeep[j] = (double)u.x;
-          ukeep[(size_t)d.N + j] = (double)u.y;
-          ukeep[2 * (size_t)d.N + j] = (double)u.z;
+          ukeep[j] = u.x;
+          ukeep[(size_t)d.N + j] = u.y;
+          ukeep[2 * (size_t)d.N + j] = u.z;
         }
       }
       us[j] = a;
@@ -292,9 +292,9 @@ __global__ void __launch_bounds__(RUN_LANES, MV32_MINB) k_matvec32(BaDev d, Mv32
       u.w = 0.f;
       us[j] = u;
       if (ukeep) {
-        ukeep[j] = (double)u.x;
-        ukeep[(size_t)d.N + j] = (double)u.y;
-        ukeep[2 * (size_t)d.N + j] = (double)u.z;
+        ukeep[j] = u.x;
+        ukeep[(size_t)d.N + j] = u.y;
+        ukeep[2 * (size_t)d.N + j] = u.z;
       }
     }
     __syncthreads();

@@ -876,7 +876,8 @@ __global__ void k_pcg_reopen(BaDev d) {
 // (ba_processor.py:405-406), from what the matvecs left.  Matvec i was applied to z_i and kept u^(i) = D^-1 W^T z_i;
 // the directions obey p_i = z_i + beta_i p_(i-1) and delta_p = sum alpha_i p_i, so with P_i = u^(i) + beta_i P_(i-1)
 // the wanted D^-1 W^T delta_p is sum_i alpha_i P_i, formed in iteration order.  One thread per point.
-__global__ void __launch_bounds__(256) k_backsub_points(BaDev d) {
+template <typename UT>
+__global__ void __launch_bounds__(256) k_backsub_points(BaDev d, const UT* __restrict__ ubuf) {
   const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t N = (size_t)d.N;
   if (j >= N) return;
@@ -885,10 +886,10 @@ __global__ void __launch_bounds__(256) k_backsub_points(BaDev d) {
   double u[3] = {0.0, 0.0, 0.0}, P[3] = {0.0, 0.0, 0.0};
   for (int i = 0; i < iters && i < PCG_UBUF; ++i) {
     const double alpha = d.sc->alpha_hist[i], beta = d.sc->beta_hist[i];
-    const double* ub = d.ubuf + (size_t)i * 3 * N + j;
+    const UT* ub = ubuf + (size_t)i * 3 * N + j;
 #pragma unroll
     for (int e = 0; e < 3; ++e) {
-      P[e] = ub[e * N] + beta * P[e];
+      P[e] = (double)ub[e * N] + beta * P[e];
       u[e] += alpha * P[e];
     }
   }
@@ -1101,9 +1102,10 @@ void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStr
   lc.launches++;
 }
 
-void launch_backsub_points(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
+void launch_backsub_points(const BaDev& d, bool from_f32, cudaStream_t st, LaunchCounter& lc) {
   if (d.N <= 0) return;
-  k_backsub_points<<<(d.N + 255) / 256, 256, 0, st>>>(d);
+  if (from_f32) k_backsub_points<float><<<(d.N + 255) / 256, 256, 0, st>>>(d, d.ubuf32);
+  else k_backsub_points<double><<<(d.N + 255) / 256, 256, 0, st>>>(d, d.ubuf);
   lc.launches++;
 }
 

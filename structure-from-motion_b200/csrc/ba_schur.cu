@@ -497,7 +497,8 @@ void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int 
   sh.seg_cap = ts.max_nseg;
   sh.k_cap = ts.max_k;
   sh.slot_cap = ((ts.max_chunk_len + 15) & ~15) + 1;   // = 1 mod 16: the slot planes start in different banks
-  const int a = SLOT_PLANES * sh.slot_cap, bb = RUN_LANES * (d.schur_diag ? Gram<true>::N : Gram<false>::N);
+  const int a = SLOT_PLANES * sh.slot_cap;
+  const int bb = RUN_LANES * (d.schur_diag ? Gram<true>::N : Gram<false>::N);
   sh.un_doubles = ((a > bb ? a : bb) + 1) & ~1;
   const size_t smem = gram_smem_bytes(sh);
   if (g1 < 0) {

@@ -59,7 +59,7 @@ namespace {
 
 enum Slot {
   S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_EXV, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_UBUF, S_CAM_ACC, S_ABLK, S_MINV,
-  S_CAMIT, S_CAMIT32, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
+  S_CAMIT, S_CAMIT32, S_UBUF32, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
   S_CHUNK_INFO, S_REC_B, S_REC_IX, S_REC_W, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
 };
@@ -320,6 +320,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     if ((rc = carve(ctx, S_DINV32, (size_t)8 * std::max(d.N, 1), &d.dinv32)) != 0) return rc;
     if ((rc = carve(ctx, S_SEGST, (size_t)d.chunk_bound * SEG_CAP * 12, &d.segst)) != 0) return rc;
     if ((rc = carve(ctx, S_CAMIT32, (size_t)d.V * CAMIT_STRIDE, &d.camit32)) != 0) return rc;
+    if ((rc = carve(ctx, S_UBUF32, (size_t)PCG_UBUF * 3 * std::max(d.N, 1), &d.ubuf32)) != 0) return rc;
   }
   int32_t *sort_keys = nullptr, *iota = nullptr;
   temp_bytes = index_temp_bytes(d.G, d.chunk_bound, d.V);
@@ -523,7 +524,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     {
       cudaEvent_t kb = pt.kbegin();
       if (pcg_finished >= 0 && pcg_finished <= PCG_UBUF) {
-        launch_backsub_points(d, st, lc);               // the PCG matvecs have left u_j = Dinv B^T p_i per point
+        launch_backsub_points(d, mv32, st, lc);             // the PCG matvecs have left u_j = Dinv B^T p_i per point
       } else {
         // dense solve, NCCL fallback or a long PCG solve: one tile pass forms pts += v - Dinv B^T dp from the camit
         // rows of x

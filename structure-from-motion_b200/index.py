@@ -48,7 +48,30 @@ def build_visibility_host(diag_rows, num_pts: int):
     return obs_pt, obs_cam, obs_key, rowptr
 
 
-def problem_from_tracks(views, tri_pts, key_tracker, engine=None, use_gpu_index: bool = False) -> BAProblem:
+def key_xy(view) -> np.ndarray:
+    """(n_keys, 2) float32 pixel coordinates of a view's key points (cv2.KeyPoint.pt is float32), built once per view
+    and kept on the view object: every later bundle adjustment gathers from it instead of touching the key objects."""
+    keys = view.key_pts
+    cached = getattr(view, '_sfmba_key_xy', None)
+    if cached is not None and cached[0] is keys and cached[1].shape[0] == len(keys):
+        return cached[1]
+    xy = None
+    try:                                                   # cv2.KeyPoint lists convert in one C call
+        import cv2
+        if len(keys) and isinstance(keys[0], cv2.KeyPoint):
+            xy = np.asarray(cv2.KeyPoint_convert(keys), dtype=np.float32).reshape(-1, 2)
+    except Exception:
+        xy = None
+    if xy is None:
+        xy = np.array([kp.pt for kp in keys], dtype=np.float32).reshape(-1, 2)
+    try:
+        view._sfmba_key_xy = (keys, xy)
+    except Exception:
+        pass
+    return xy
+
+
+def problem_from_tracks(views, tri_pts, key_tracker, engine=None, use_gpu_index: bool = True) -> BAProblem:
     """Pack the reference's objects into a BAProblem (ba_processor.py:285-294, 309-342).
 
     views[i] needs .rot (3,3), .loc (3,1), .k (3,3), .key_pts[k].pt; tri_pts is the (4,N) TriPt
@@ -72,10 +95,7 @@ def problem_from_tracks(views, tri_pts, key_tracker, engine=None, use_gpu_index:
     for i, view in enumerate(views):
         sel = np.flatnonzero(obs_cam == i)
         if sel.size:
-            keys = view.key_pts
-            ks = obs_key[sel]
-            uv[0, sel] = [keys[k].pt[0] for k in ks]
-            uv[1, sel] = [keys[k].pt[1] for k in ks]
+            uv[:, sel] = key_xy(view)[obs_key[sel]].T          # one gather per view (ba_processor.py:336-338)
     pts = np.ascontiguousarray(np.asarray(tri_pts, dtype=float)[0:3, :].T)
     return BAProblem(cams=cams, pts=pts, obs_uv=uv, obs_cam=obs_cam, obs_pt=obs_pt, rowptr=rowptr, kinv=kinv,
                      obs_key=obs_key)

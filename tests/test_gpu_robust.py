@@ -53,7 +53,10 @@ def test_adaptive_lm_with_huber_rejects_outliers(engine, oracle):
     prob_h, truth, bad = _with_outliers('small', 0.1, 5)
     prob_l, _, _ = _with_outliers('small', 0.1, 5)
     prob_big, _, _ = _with_outliers('small', 0.1, 5)
-    kw = dict(lam=1e-3, iterations=25, mode=_capi.MODE_ADAPTIVE_LM, dvdc_sign_quirk=False)
+    # (FP64 matvec in all three: the Huber solves always run it, and 25 adaptive iterations would otherwise compare the
+    # FP32 matvec of the plain solve with the FP64 one of the huge-delta solve instead of the two losses)
+    kw = dict(lam=1e-3, iterations=25, mode=_capi.MODE_ADAPTIVE_LM, dvdc_sign_quirk=False,
+              matvec_precision=_capi.MATVEC_F64)
     rh = engine.ba_solve_host(prob_h, huber_delta=0.002, **kw)
     rl = engine.ba_solve_host(prob_l, **kw)
     rb = engine.ba_solve_host(prob_big, huber_delta=1e6, **kw)
