@@ -172,6 +172,11 @@ SFMBA_API int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* problem, 
 SFMBA_API int sfmba_residual_jacobian(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk,
                             float* out_r, float* out_jp, float* out_jx, double* out_r64,
                             double* out_cost, void* stream);
+/* the same blocks in full precision: out_r64 f64 [2][m], out_jp64 f64 [14][m], out_jx64 f64 [6][m] (any may be NULL) --
+ * what CamposeProcessor.construct_jacobian_matrix hands to callers that build their own normal equations.
+ * Both variants synchronise and report bad indices (SFMBA_ERR_INVALID_ARG) and zero depths (SFMBA_ERR_NUMERIC).   */
+SFMBA_API int sfmba_residual_jacobian_f64(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk,
+                                double* out_r64, double* out_jp64, double* out_jx64, double* out_cost, void* stream);
 SFMBA_API int sfmba_ba_cost(sfmba_ctx* ctx, const sfmba_problem* problem, double* host_cost, void* stream);
 
 /* ---- sfmba_ba_cost without any allocation.  No counterpart in the reference: added

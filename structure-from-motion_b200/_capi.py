@@ -69,6 +69,7 @@ SYMBOLS = {
     'sfmba_ba_solve': (C.c_int, [_vp, C.POINTER(Problem), C.POINTER(Options), C.POINTER(Result), _vp]),
     'sfmba_ba_solve_host': (C.c_int, [_vp, C.POINTER(Problem), C.POINTER(Options), C.POINTER(Result)]),
     'sfmba_residual_jacobian': (C.c_int, [_vp, C.POINTER(Problem), C.c_int, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'sfmba_residual_jacobian_f64': (C.c_int, [_vp, C.POINTER(Problem), C.c_int, _vp, _vp, _vp, _vp, _vp]),
     'sfmba_ba_cost': (C.c_int, [_vp, C.POINTER(Problem), C.POINTER(_f64), _vp]),
     'sfmba_ba_cost_noalloc': (C.c_int, [C.c_int, C.POINTER(Problem), _vp, _vp, _vp]),
     'sfmba_triangulate_refine_batched': (C.c_int, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _f64, _i32,

@@ -23,6 +23,7 @@ import math
 
 import numpy as np
 
+from . import _capi
 from .engine import get_engine
 from .index import problem_from_tracks
 from .utils import quaternion_to_rotation_unchecked, verify_rotation_mat
@@ -68,6 +69,15 @@ class BaProcessor:
         init_pts = prob.pts.copy()
         self.last_result = self.engine.ba_solve_host(prob, lam=self.damping_factor, iterations=self.iteration,
                                                      pcg_tol=self.pcg_tol, dvdc_sign_quirk=self.dvdc_sign_quirk)
+        if self.last_result.flags & _capi.FLAG_PCG_MAXITER:
+            # The reference solves the reduced system exactly (ba_processor.py:382).  A PCG solve that stopped on its
+            # iteration cap is not that: redo the call from the same start with the direct (dense Cholesky) solver -- at
+            # most 7 * filter_size unknowns here.
+            prob.cams[...] = init_cams
+            prob.pts[...] = init_pts
+            self.last_result = self.engine.ba_solve_host(prob, lam=self.damping_factor, iterations=self.iteration,
+                                                         dvdc_sign_quirk=self.dvdc_sign_quirk,
+                                                         solver=_capi.SOLVER_DENSE_CHOLESKY)
         # Write back.  The quaternion is renormalised in f64 on the host before R is rebuilt so the
         # result passes the reference's one-sided 1e-8 validity check (utils.py:101-105).
         for i in range(view_num):

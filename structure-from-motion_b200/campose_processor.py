@@ -190,5 +190,5 @@ class CamposeProcessor:
         prob = BAProblem(cams=np.concatenate([np.asarray(loc, dtype=float).reshape(3), q])[None, :],
                          pts=x[None, :], obs_uv=np.zeros((2, 1), dtype=np.float32), obs_cam=np.zeros(1, dtype=np.int32),
                          obs_pt=np.zeros(1, dtype=np.int32), rowptr=np.array([0, 1], dtype=np.int32))
-        _, jp, _, _, _ = self.engine.residual_jacobian(prob, dvdc_sign_quirk, want_r64=False)
-        return jp[0].astype(np.float64)
+        _, jp, _, _ = self.engine.residual_jacobian_f64(prob, dvdc_sign_quirk)
+        return jp[0]

@@ -103,6 +103,7 @@ constexpr int PEER_HEADER_BYTES = 256;
 struct PeerWindow {
   int world, rank;
   unsigned long long cap;             // doubles per (parity, rank) slot
+  unsigned long long timeout_ns;      // how long a rank waits for a peer's flag before it gives up (SFMBA_ERR_COMM)
   char* base[MAX_PEERS];              // window of every rank in this rank's address space
   __host__ __device__ unsigned long long* flags(int r) const { return reinterpret_cast<unsigned long long*>(base[r]); }
   __host__ __device__ unsigned long long* counter() const { return flags(rank) + 2 * MAX_PEERS; }
@@ -175,6 +176,7 @@ struct BaDev {
   double* gvec;                       // [7V] right-hand side
   double* red_a;                      // [<= 1024] per-block partials of the PCG dot products
   double* red_b;                      // [<= 2048]
+  double* cam_rr;                     // [V] |g_i|^2 per camera (k_cam_finish)
   double* cams_backup;                // [V][7]  adaptive mode
   double* pts_backup;                 // [N][3]
   Scalars* sc;
@@ -211,7 +213,7 @@ void launch_cam_prepare(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_cost_tiles(const BaDev& d, const TileShape& ts, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc);
 void launch_cost(const BaDev& d, double* out_cost_dev, cudaStream_t st, LaunchCounter& lc);   // index-free
 void launch_k1(const BaDev& d, bool dvdc_quirk, float* out_r, float* out_jp, float* out_jx, double* out_r64,
-               double* out_cost, cudaStream_t st, LaunchCounter& lc);
+               double* out_jp64, double* out_jx64, double* out_cost, cudaStream_t st, LaunchCounter& lc);
 
 // ---- camera-side reduction (ba_schur.cu) --------------------------------------------------------
 // fused linearisation: point blocks (D^-1, v, cost -> sc->costs[cost_slot]) + camera-side Gram rows
@@ -222,6 +224,10 @@ void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 // several GPUs with peer windows: segment rows -> every rank's window -> cam_acc and cost summed over ranks
 void launch_camsum64_peer(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc);       // part64 -> cam_acc
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
+// PCG solver: camera sums (this GPU's rows, or all ranks' through the peer windows), blocks and the PCG start in one
+// kernel per camera
+void launch_cam_finish(const BaDev& d, bool peer, int cost_slot, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
+                       LaunchCounter& lc);
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
 void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);

@@ -160,7 +160,8 @@ __global__ void __launch_bounds__(256) k_cost(BaDev d) {
 // K1 alone (sfmba_residual_jacobian): SoA outputs, f32 (and optional f64 residuals)
 __global__ void __launch_bounds__(256) k_residual_jacobian(BaDev d, int dvdc_quirk, float* __restrict__ out_r,
                                                            float* __restrict__ out_jp, float* __restrict__ out_jx,
-                                                           double* __restrict__ out_r64) {
+                                                           double* __restrict__ out_r64, double* __restrict__ out_jp64,
+                                                           double* __restrict__ out_jx64) {
   __shared__ double red[32];
   double cost = 0.0;
   uint32_t flags = 0;
@@ -190,6 +191,14 @@ __global__ void __launch_bounds__(256) k_residual_jacobian(BaDev d, int dvdc_qui
     if (out_jx) {
 #pragma unroll
       for (int e = 0; e < 6; ++e) out_jx[e * m + o] = (float)Jx[e];
+    }
+    if (out_jp64) {
+#pragma unroll
+      for (int e = 0; e < 14; ++e) out_jp64[e * m + o] = Jp[e];
+    }
+    if (out_jx64) {
+#pragma unroll
+      for (int e = 0; e < 6; ++e) out_jx64[e * m + o] = Jx[e];
     }
   }
   cost = block_sum(cost, red);
@@ -239,9 +248,9 @@ void launch_cost(const BaDev& d, double* out_cost_dev, cudaStream_t st, LaunchCo
 }
 
 void launch_k1(const BaDev& d, bool dvdc_quirk, float* out_r, float* out_jp, float* out_jx, double* out_r64,
-               double* out_cost, cudaStream_t st, LaunchCounter& lc) {
+               double* out_jp64, double* out_jx64, double* out_cost, cudaStream_t st, LaunchCounter& lc) {
   const int g = cost_grid(d);
-  k_residual_jacobian<<<g, 256, 0, st>>>(d, dvdc_quirk ? 1 : 0, out_r, out_jp, out_jx, out_r64);
+  k_residual_jacobian<<<g, 256, 0, st>>>(d, dvdc_quirk ? 1 : 0, out_r, out_jp, out_jx, out_r64, out_jp64, out_jx64);
   k_sum_cost<<<1, 1024, 0, st>>>(d.grp_cost, g, nullptr, -1, out_cost);
   lc.launches += 2;
 }

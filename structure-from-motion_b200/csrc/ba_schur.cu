@@ -488,6 +488,208 @@ __global__ void k_cam_blocks(BaDev d) {
   for (int a = 0; a < 7; ++a) d.gvec[7 * cam + a] = acc[56 + a];
 }
 
+__global__ void k_camsum64_peer(BaDev d);
+
+// ---- camera finish, fused (PCG solver): segment rows (or the ranks' window slots) -> cam_acc -> A_i + lambda I, the
+// block-Jacobi inverse, the right-hand side -> the start of the PCG solve for this camera (x = 0, r = g, z = Minv g and
+// its camit rows, p = s = 0) -> |g|^2 by the CTA that finishes last: what k_camsum64 (or k_cam_gather_peers),
+// k_cam_blocks and k_pcg_init do in three launches.  One WARP per camera: lane e holds elements e and e + 32 of the
+// camera's sums; every lane factors the 7x7 block (Cholesky, from values fetched by shuffles) and lane c < 7 solves for
+// column c of the inverse, so the 7x7 work is seven-fold parallel and lives in registers.
+constexpr int FIN_WARPS = 8;
+
+template <bool PEER>
+__global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost_slot, unsigned epoch, int dvdc_quirk) {
+  __shared__ double red[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  Scalars* sc = d.sc;
+  const bool schur = d.schur_diag != 0;
+  const int row = schur ? CAM_ACC : ROW_COMPACT;
+  const bool hi = lane + 32 < row;
+  int par = 0;
+  if (PEER) {
+    const unsigned long long seq = *d.xw.counter() + 1ull;    // advanced by the CTA that finishes last
+    par = (int)(seq & 1ull);
+    peer_wait(d.xw, seq, sc);
+    if (blockIdx.x == 0 && tid == 0) {
+      double c = 0.0;
+      for (int w = 0; w < d.xw.world; ++w) c += __ldcg(d.xw.slot(d.xw.rank, par, w) + (size_t)d.V * row);
+      sc->cost_cur = c;
+      if (cost_slot < SFMBA_MAX_COST_HISTORY) sc->costs[cost_slot] = c;
+    }
+  }
+  const double lam = sc->lambda;
+  double rr = 0.0;
+  for (int cam = blockIdx.x * FIN_WARPS + warp; cam < d.V; cam += gridDim.x * FIN_WARPS) {
+    double a0 = 0.0, a1 = 0.0;                       // elements lane, lane + 32 of the camera's row sum
+    if (PEER) {
+      const size_t base = (size_t)cam * row + lane;
+      for (int w = 0; w < d.xw.world; ++w) {
+        const double* sl = d.xw.slot(d.xw.rank, par, w) + base;
+        a0 += __ldcg(sl);
+        if (hi) a1 += __ldcg(sl + 32);
+      }
+    } else {
+      const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
+      const double* p = d.part64 + lane;
+      for (int k = r0; k < r1; k += 8) {             // eight rows in flight, summed in row order
+        double v[8], w[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const bool ok = k + u < r1;
+          v[u] = ok ? p[(size_t)(k + u) * row] : 0.0;
+          w[u] = (ok && hi) ? p[(size_t)(k + u) * row + 32] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          a0 += v[u];
+          a1 += w[u];
+        }
+      }
+    }
+    d.cam_acc[(size_t)cam * CAM_ACC + acc_index(d, lane)] = a0;
+    if (hi) d.cam_acc[(size_t)cam * CAM_ACC + acc_index(d, lane + 32)] = a1;
+    // element e of the row (compile-time e) in every lane
+    auto get = [&](int e) { return e < 32 ? __shfl_sync(0xffffffffu, a0, e) : __shfl_sync(0xffffffffu, a1, e - 32); };
+    // S_ii = A + lambda I - (Schur-diagonal sums), packed upper triangle k(a, b) = a (15 - a) / 2 + b - a, a <= b
+    double S[28];
+#pragma unroll
+    for (int k = 0; k < 28; ++k) {
+      S[k] = get(k);
+      if (schur) S[k] -= get(28 + k);
+    }
+#pragma unroll
+    for (int a = 0; a < 7; ++a) S[a * (15 - a) / 2] += lam;
+    // Cholesky S = L L^T, L[i][j] (j <= i) stored at S-index k(j, i): L overwrites the packed triangle column by column
+    bool ok = true;
+    double L[28];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+      double dj = S[j * (15 - j) / 2];
+#pragma unroll
+      for (int k = 0; k < j; ++k) dj -= L[k * (15 - k) / 2 + j - k] * L[k * (15 - k) / 2 + j - k];
+      if (!(dj > 0.0)) ok = false;
+      const double ljj = sqrt(dj);
+      const double inv = 1.0 / ljj;
+      L[j * (15 - j) / 2] = ljj;
+#pragma unroll
+      for (int i = j + 1; i < 7; ++i) {
+        double v = S[j * (15 - j) / 2 + i - j];
+#pragma unroll
+        for (int k = 0; k < j; ++k) v -= L[k * (15 - k) / 2 + i - k] * L[k * (15 - k) / 2 + j - k];
+        L[j * (15 - j) / 2 + i - j] = v * inv;          // L[i][j]
+      }
+    }
+    if (!ok && lane == 0) atomicOr(&sc->flags, FLAG_SINGULAR);
+    // lane c < 7: column c of S^-1 (L y = e_c, L^T x = y)
+    const int c = lane < 7 ? lane : 0;
+    double y[7], x[7];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+      double v = (i == c) ? 1.0 : 0.0;
+#pragma unroll
+      for (int j = 0; j < i; ++j) v -= L[j * (15 - j) / 2 + i - j] * y[j];
+      y[i] = v / L[i * (15 - i) / 2];
+    }
+#pragma unroll
+    for (int i = 6; i >= 0; --i) {
+      double v = y[i];
+#pragma unroll
+      for (int j = i + 1; j < 7; ++j) v -= L[i * (15 - i) / 2 + j - i] * x[j];
+      x[i] = v / L[i * (15 - i) / 2];
+    }
+    // right-hand side g and z = Minv g (row c of the symmetric inverse is x)
+    const int g0 = schur ? 56 : 28;
+    double g[7], zc = 0.0;
+#pragma unroll
+    for (int bb = 0; bb < 7; ++bb) {
+      g[bb] = schur ? get(56 + bb) : get(28 + bb);
+      zc += x[bb] * g[bb];
+    }
+    (void)g0;
+    double gc = 0.0;
+#pragma unroll
+    for (int bb = 0; bb < 7; ++bb)
+      if (bb == c) gc = g[bb];
+    // A_i + lambda I, row c: entry (c, b) sits at packed index k(min, max) of a0
+    double arow[7];
+#pragma unroll
+    for (int bb = 0; bb < 7; ++bb) {
+      const int lo = c < bb ? c : bb, hh = c < bb ? bb : c;
+      arow[bb] = __shfl_sync(0xffffffffu, a0, lo * (15 - lo) / 2 + hh - lo) + (bb == c ? lam : 0.0);
+    }
+    // camit row of z: every lane needs all of z
+    double zl[7], o[16];
+#pragma unroll
+    for (int bb = 0; bb < 7; ++bb) zl[bb] = __shfl_sync(0xffffffffu, zc, bb);
+    camit_row(d.camtab + (size_t)CAMTAB_STRIDE * cam, zl, dvdc_quirk, o);
+    o[14] = 0.0;
+    o[15] = 0.0;
+    double mine = 0.0;
+#pragma unroll
+    for (int e = 0; e < 16; ++e)
+      if (lane == e) mine = o[e];
+    if (lane < 16) {
+      d.camit[(size_t)CAMIT_STRIDE * cam + lane] = mine;
+      if (d.camit32) d.camit32[(size_t)CAMIT_STRIDE * cam + lane] = (float)mine;
+    }
+    if (lane < 7) {
+      double* ao = d.ablk + (size_t)cam * 49 + 7 * lane;
+      double* mo = d.minv + (size_t)cam * 49 + 7 * lane;
+#pragma unroll
+      for (int bb = 0; bb < 7; ++bb) {
+        ao[bb] = arow[bb];
+        mo[bb] = x[bb];
+      }
+      const size_t k7 = 7 * (size_t)cam + lane;
+      d.gvec[k7] = gc;
+      d.x[k7] = 0.0;
+      d.p[k7] = 0.0;
+      d.s[k7] = 0.0;
+      d.r[k7] = gc;
+      d.z[k7] = zc;
+      rr += gc * gc;
+    }
+  }
+  rr = block_sum(rr, red);
+  if (tid == 0) d.red_b[blockIdx.x] = rr;
+  if (!last_cta_arrives(&sc->ticket_b)) return;
+  // ---- the last CTA: |g|^2 in CTA order, the iteration state
+  double a = 0.0;
+  for (int k = tid; k < (int)gridDim.x; k += blockDim.x) a += __ldcg(d.red_b + k);
+  a = block_sum(a, red);
+  if (tid != 0) return;
+  if (PEER) *d.xw.counter() += 1ull;                     // every CTA has read its slots
+  const int done = (a == 0.0 || !(a == a)) ? 1 : 0;
+  if (!(a == a)) atomicOr(&sc->flags, FLAG_NONFINITE);
+  sc->gg = a;
+  sc->rr = a;
+  sc->rz = 0.0;
+  sc->alpha = 0.0;
+  sc->beta = 0.0;
+  sc->pcg_iters = 0;
+  sc->bar_a = 0u;
+  sc->pcg_done = done;
+  if (d.host_sig) *(volatile unsigned long long*)d.host_sig = ((unsigned long long)epoch << 32) | (done ? 1ull : 0ull);
+}
+
+static int fin_grid(const BaDev& d) {
+  int g = (d.V + FIN_WARPS - 1) / FIN_WARPS;
+  return g < 1 ? 1 : (g > 2048 ? 2048 : g);           // red_b holds one partial per CTA
+}
+
+void launch_cam_finish(const BaDev& d, bool peer, int cost_slot, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
+                       LaunchCounter& lc) {
+  if (peer) {
+    k_camsum64_peer<<<d.V, 256, 0, st>>>(d);
+    k_cam_finish<true><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0);
+    lc.launches += 2;
+  } else {
+    k_cam_finish<false><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0);
+    lc.launches++;
+  }
+}
+
 // Linearises the groups [g0, g1) (g1 < 0: all).  The host-buffer solve calls it once per upload range, so the
 // first linearisation overlaps the arrival of the later points; sum_cost closes the last range.
 void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int cost_slot, cudaStream_t st,

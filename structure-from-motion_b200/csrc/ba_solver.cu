@@ -59,7 +59,7 @@ namespace {
 
 enum Slot {
   S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_EXV, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_UBUF, S_CAM_ACC, S_ABLK, S_MINV,
-  S_CAMIT, S_CAMIT32, S_UBUF32, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
+  S_CAMIT, S_CAMIT32, S_UBUF32, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAM_RR, S_CAMS_BAK, S_PTS_BAK,
   S_CHUNK_INFO, S_REC_B, S_REC_IX, S_REC_W, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
 };
@@ -126,6 +126,7 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
     CARVE(S_GVEC, 7 * V, gvec);
     CARVE(S_RED_A, 1024, red_a);
     CARVE(S_RED_B, 2048, red_b);
+    CARVE(S_CAM_RR, V, cam_rr);
     CARVE(S_CAMS_BAK, 7 * V, cams_backup);
     CARVE(S_PTS_BAK, 3 * N, pts_backup);
     CARVE(S_CAMROW_PTR, V + 1, camrow_ptr);
@@ -366,25 +367,31 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     pt.end(PH_LINEARIZE, t0);
 
     t0 = pt.begin();
-    if (peer) {
-      launch_camsum64_peer(d, cost_slot, st, lc);
-    } else {
-      launch_camsum64(d, st, lc);
-    }
-    if (multi && !peer) {
-      // one message: the camera accumulators plus this rank's cost in the trailing slot
-      cudaMemcpyAsync(d.cam_acc + (size_t)d.V * CAM_ACC, &d.sc->cost_cur, sizeof(double),
-                      cudaMemcpyDeviceToDevice, st);
-      if ((rc = sfm_nccl_allreduce_f64(ctx, d.cam_acc, (size_t)d.V * CAM_ACC + 1, st)) != 0) return rc;
-      cudaMemcpyAsync(&d.sc->cost_cur, d.cam_acc + (size_t)d.V * CAM_ACC, sizeof(double),
-                      cudaMemcpyDeviceToDevice, st);
-      if (cost_slot < SFMBA_MAX_COST_HISTORY)
-        cudaMemcpyAsync(&d.sc->costs[cost_slot], d.cam_acc + (size_t)d.V * CAM_ACC, sizeof(double),
-                        cudaMemcpyDeviceToDevice, st);
-    }
-    launch_cam_blocks(d, st, lc);
     const unsigned pcg_epoch = ++ctx->pcg_epoch;
-    if (!dense) launch_pcg_init(d, pcg_epoch, quirk, st, lc);
+    static const bool fused_finish = !(getenv("SFMBA_FUSED_FINISH") && atoi(getenv("SFMBA_FUSED_FINISH")) == 0);
+    if (fused_finish && !dense && (!multi || peer)) {
+      // PCG on one GPU or over peer windows: camera sums, blocks and the start of the PCG solve in one kernel per camera
+      launch_cam_finish(d, peer, cost_slot, pcg_epoch, quirk, st, lc);
+    } else {
+      if (peer) {
+        launch_camsum64_peer(d, cost_slot, st, lc);
+      } else {
+        launch_camsum64(d, st, lc);
+      }
+      if (multi && !peer) {
+        // one message: the camera accumulators plus this rank's cost in the trailing slot
+        cudaMemcpyAsync(d.cam_acc + (size_t)d.V * CAM_ACC, &d.sc->cost_cur, sizeof(double),
+                        cudaMemcpyDeviceToDevice, st);
+        if ((rc = sfm_nccl_allreduce_f64(ctx, d.cam_acc, (size_t)d.V * CAM_ACC + 1, st)) != 0) return rc;
+        cudaMemcpyAsync(&d.sc->cost_cur, d.cam_acc + (size_t)d.V * CAM_ACC, sizeof(double),
+                        cudaMemcpyDeviceToDevice, st);
+        if (cost_slot < SFMBA_MAX_COST_HISTORY)
+          cudaMemcpyAsync(&d.sc->costs[cost_slot], d.cam_acc + (size_t)d.V * CAM_ACC, sizeof(double),
+                          cudaMemcpyDeviceToDevice, st);
+      }
+      launch_cam_blocks(d, st, lc);
+      if (!dense) launch_pcg_init(d, pcg_epoch, quirk, st, lc);
+    }
     pt.end(PH_CAMREDUCE, t0);
 
     // ---- PCG.  Kernels of an already-converged solve exit at their first instruction, so launching
@@ -548,6 +555,10 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     ++cost_slot;
   }
 
+  if (ranged) {
+    // (with zero iterations nothing above has waited for the points of the later upload ranges)
+    for (int r = 0; r < io->num_ranges; ++r) cudaStreamWaitEvent(st, io->ev_range_pts[r], 0);
+  }
   if (io) {
     // parameters are final: their download runs on the copy stream beside the final cost pass
     cudaEventRecord(io->ev_final, st);

@@ -282,8 +282,11 @@ int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   return rc;
 }
 
-int sfmba_residual_jacobian(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk, float* out_r,
-                            float* out_jp, float* out_jx, double* out_r64, double* out_cost, void* stream) {
+namespace {
+// K1 alone; reads the device flag word back (one synchronisation) so that bad indices and zero depths are reported
+int residual_jacobian_impl(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk, float* out_r, float* out_jp,
+                           float* out_jx, double* out_r64, double* out_jp64, double* out_jx64, double* out_cost,
+                           void* stream) {
   if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
   cudaSetDevice(ctx->device);
   cudaStream_t st = (cudaStream_t)stream;
@@ -292,8 +295,33 @@ int sfmba_residual_jacobian(sfmba_ctx* ctx, const sfmba_problem* problem, int dv
   if (rc) return rc;
   cudaMemsetAsync(d.sc, 0, sizeof(Scalars), st);
   launch_cam_prepare(d, st, ctx->lc);
-  launch_k1(d, dvdc_sign_quirk != 0, out_r, out_jp, out_jx, out_r64, out_cost, st, ctx->lc);
-  return sfm_check_cuda(ctx, cudaGetLastError(), "k1 launch");
+  launch_k1(d, dvdc_sign_quirk != 0, out_r, out_jp, out_jx, out_r64, out_jp64, out_jx64, out_cost, st, ctx->lc);
+  uint32_t* pin_flags = reinterpret_cast<uint32_t*>(ctx->pinned);
+  cudaMemcpyAsync(pin_flags, &d.sc->flags, sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+  if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "k1 sync")) != 0) return rc;
+  if ((rc = sfm_check_cuda(ctx, cudaGetLastError(), "k1 launch")) != 0) return rc;
+  if (*pin_flags & SFMBA_FLAG_BAD_INDEX)
+    return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG,
+                         "obs_cam / obs_pt has an index outside its array (the outputs of those observations were not written)");
+  if (*pin_flags & (SFMBA_FLAG_DEPTH_ZERO | SFMBA_FLAG_QW_NEAR_ZERO | SFMBA_FLAG_NONFINITE)) {
+    char buf[64];
+    snprintf(buf, sizeof(buf), "device numeric flags 0x%x", *pin_flags);
+    return sfm_set_error(ctx, SFMBA_ERR_NUMERIC, buf);
+  }
+  return SFMBA_OK;
+}
+}  // namespace
+
+int sfmba_residual_jacobian(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk, float* out_r,
+                            float* out_jp, float* out_jx, double* out_r64, double* out_cost, void* stream) {
+  return residual_jacobian_impl(ctx, problem, dvdc_sign_quirk, out_r, out_jp, out_jx, out_r64, nullptr, nullptr, out_cost,
+                                stream);
+}
+
+int sfmba_residual_jacobian_f64(sfmba_ctx* ctx, const sfmba_problem* problem, int dvdc_sign_quirk, double* out_r64,
+                                double* out_jp64, double* out_jx64, double* out_cost, void* stream) {
+  return residual_jacobian_impl(ctx, problem, dvdc_sign_quirk, nullptr, nullptr, nullptr, out_r64, out_jp64, out_jx64,
+                                out_cost, stream);
 }
 
 int sfmba_ba_cost(sfmba_ctx* ctx, const sfmba_problem* problem, double* host_cost, void* stream) {

@@ -62,7 +62,7 @@ __device__ __forceinline__ void peer_wait(const PeerWindow& xw, unsigned long lo
     const unsigned long long t0 = global_timer_ns();
     unsigned spins = 0;
     while (ld_acquire_sys(f) < seq) {
-      if ((++spins & 0x3ffu) == 0 && global_timer_ns() - t0 > PEER_TIMEOUT_NS) {
+      if ((++spins & 0x3ffu) == 0 && global_timer_ns() - t0 > xw.timeout_ns) {
         atomicOr(&sc->flags, FLAG_PEER_TIMEOUT);
         break;
       }

@@ -118,6 +118,12 @@ int sfm_peer_setup(sfmba_ctx* ctx, size_t doubles_cap, cudaStream_t st) {
   ctx->peer.world = W;
   ctx->peer.rank = ctx->rank;
   ctx->peer.cap = cap;
+  {
+    // 20 s by default; SFMBA_PEER_TIMEOUT_MS shortens it (tests of the failure path)
+    const char* ms = getenv("SFMBA_PEER_TIMEOUT_MS");
+    const long long v = ms ? atoll(ms) : 0;
+    ctx->peer.timeout_ns = (v > 0 ? (unsigned long long)v : 20000ull) * 1000000ull;
+  }
   for (int r = 0; r < MAX_PEERS; ++r)
     ctx->peer.base[r] = r == ctx->rank ? reinterpret_cast<char*>(ctx->peer_local)
                                        : reinterpret_cast<char*>(r < W ? ctx->peer_mapped[r] : nullptr);

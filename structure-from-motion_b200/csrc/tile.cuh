@@ -104,4 +104,36 @@ __device__ __forceinline__ void stage_chunk_async(const BaDev& d, int c, const C
   }
 }
 
+// ---- per-camera rows of a camera-space vector (shared by the PCG kernels and the fused camera finish) -------------
+// Q[j][3 c + k] = d R[k][c] / d q_j for q2 = 2 (w,x,y,z)        (campose_processor.py:636-702)
+__device__ __forceinline__ void quat_dRt(const double q2[4], double Q[4][9]) {
+  const double w2 = q2[0], x2 = q2[1], y2 = q2[2], z2 = q2[3];
+  Q[0][0] = 0.0;       Q[0][1] = z2;        Q[0][2] = -y2;
+  Q[0][3] = -z2;       Q[0][4] = 0.0;       Q[0][5] = x2;
+  Q[0][6] = y2;        Q[0][7] = -x2;       Q[0][8] = 0.0;
+  Q[1][0] = 0.0;       Q[1][1] = y2;        Q[1][2] = z2;
+  Q[1][3] = y2;        Q[1][4] = -2.0 * x2; Q[1][5] = w2;
+  Q[1][6] = z2;        Q[1][7] = -w2;       Q[1][8] = -2.0 * x2;
+  Q[2][0] = -2.0 * y2; Q[2][1] = x2;        Q[2][2] = -w2;
+  Q[2][3] = x2;        Q[2][4] = 0.0;       Q[2][5] = z2;
+  Q[2][6] = w2;        Q[2][7] = z2;        Q[2][8] = -2.0 * y2;
+  Q[3][0] = -2.0 * z2; Q[3][1] = w2;        Q[3][2] = x2;
+  Q[3][3] = -w2;       Q[3][4] = -2.0 * z2; Q[3][5] = y2;
+  Q[3][6] = x2;        Q[3][7] = y2;        Q[3][8] = 0.0;
+}
+
+// camit row of one camera from its 7 entries dl of a camera-space vector: E = sum_j dl_q[j] Q_j, w = R^T dl_C
+__device__ __forceinline__ void camit_row(const double* __restrict__ t, const double dl[7], int dvdc_quirk,
+                                          double o[14]) {
+  const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
+  double Q[4][9];
+  quat_dRt(q2, Q);
+#pragma unroll
+  for (int e = 0; e < 9; ++e) o[e] = dl[3] * Q[0][e] + dl[4] * Q[1][e] + dl[5] * Q[2][e] + dl[6] * Q[3][e];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) o[9 + c] = t[c] * dl[0] + t[3 + c] * dl[1] + t[6 + c] * dl[2];
+  o[12] = dvdc_quirk ? 2.0 * o[11] : 0.0;
+  o[13] = dvdc_quirk ? 1.0 : -1.0;
+}
+
 }  // namespace sfmba

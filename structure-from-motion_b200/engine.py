@@ -244,6 +244,24 @@ class Engine:
         r64_h = r64[:, :m].t().cpu().numpy() if want_r64 else None
         return r_h, jp_h, jx_h, r64_h, float(cost.item())
 
+    def residual_jacobian_f64(self, p: BAProblem, dvdc_sign_quirk=True):
+        """K1 alone in full precision.  Returns (r (m,2), Jp (m,2,7), Jx (m,2,3), cost), all float64."""
+        import torch
+        t = self.to_device(p)
+        dev = torch.device('cuda', self.device)
+        m = p.num_obs
+        r = torch.empty((2, max(m, 1)), dtype=torch.float64, device=dev)
+        jp = torch.empty((14, max(m, 1)), dtype=torch.float64, device=dev)
+        jx = torch.empty((6, max(m, 1)), dtype=torch.float64, device=dev)
+        cost = torch.zeros(1, dtype=torch.float64, device=dev)
+        cp = self._dev_problem(t)
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        rc = self.lib.sfmba_residual_jacobian_f64(self.ctx, C.byref(cp), 1 if dvdc_sign_quirk else 0, r.data_ptr(),
+                                                  jp.data_ptr(), jx.data_ptr(), cost.data_ptr(), C.c_void_p(st))
+        _capi.check(rc, self.ctx)
+        return (r[:, :m].t().cpu().numpy(), jp[:, :m].t().reshape(m, 2, 7).cpu().numpy(),
+                jx[:, :m].t().reshape(m, 2, 3).cpu().numpy(), float(cost.item()))
+
     def ba_cost(self, p: BAProblem) -> float:
         import torch
         t = self.to_device(p)

@@ -54,3 +54,54 @@ def test_two_rank_solve_matches_single_gpu(engine, tmp_path):
         assert abs(float(o['cost']) - res.final_cost) <= 1e-9 * res.final_cost
         assert abs(float(o['c0']) - res.costs[0]) <= 1e-9 * res.costs[0]
     assert np.max(np.abs(np.concatenate([o['pts'] for o in out]) - full.pts)) < 1e-8
+
+
+TIMEOUT_WORKER = r'''
+import os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+sys.path.insert(0, %(root)r)
+import sfm_b200
+from sfm_b200 import _capi, synthetic
+rank, world = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
+torch.cuda.set_device(rank)
+dist.init_process_group('nccl', device_id=torch.device('cuda', rank))
+buf = torch.zeros(128, dtype=torch.uint8, device='cuda')
+if rank == 0:
+    buf.copy_(torch.frombuffer(bytearray(sfm_b200.Engine.nccl_unique_id()), dtype=torch.uint8))
+dist.broadcast(buf, 0)
+eng = sfm_b200.Engine(device=rank, world_size=world, rank=rank, nccl_unique_id=bytes(buf.cpu().numpy().tobytes()))
+full, _ = synthetic.make_shape('small')
+sh = synthetic.shard_problem(full, world, rank)
+eng.ba_solve_host(sh, lam=5.0, iterations=1)            # both ranks: the peer windows get mapped
+dist.barrier()
+out = 'skipped'
+if rank == 0:                                           # rank 1 never enters the second solve
+    before = sh.cams.copy()
+    try:
+        eng.ba_solve_host(sh, lam=5.0, iterations=2)
+        out = 'returned OK'
+    except _capi.SfmbaError as e:
+        out = 'code %%d unchanged %%s' %% (e.code, bool(np.array_equal(before, sh.cams)))
+open(os.path.join(%(out)r, 'timeout%%d.txt' %% rank), 'w').write(out)
+dist.barrier()
+os._exit(0)                                             # the windows are out of step now: no orderly teardown
+'''
+
+
+def test_missing_peer_is_reported_as_comm_error(engine, tmp_path):
+    """A rank whose peer never arrives at an exchange gives up after the timeout, returns SFMBA_ERR_COMM (not SFMBA_OK
+    with corrupted sums) and leaves the cameras of the failed iteration untouched."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs 2 GPUs')
+    from sfm_b200 import _capi
+    script = tmp_path / 'worker_timeout.py'
+    script.write_text(TIMEOUT_WORKER % dict(root=ROOT, out=str(tmp_path)))
+    env = dict(os.environ, MASTER_ADDR='127.0.0.1', SFMBA_PEER_TIMEOUT_MS='1500')
+    subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2',
+                    '--master-addr', '127.0.0.1', '--master-port', '29534', str(script)], check=True, env=env,
+                   timeout=300)
+    got = (tmp_path / 'timeout0.txt').read_text()
+    assert got == 'code %d unchanged True' % _capi.ERR_COMM, got
