@@ -363,8 +363,14 @@ def run_ours(args):
     hp = sfm_b200.BAProblem(cams=pin['cams'].numpy(), pts=pin['pts'].numpy(), obs_uv=pin['obs_uv'].numpy(),
                             obs_cam=pin['obs_cam'].numpy(), obs_pt=pin['obs_pt'].numpy(), rowptr=pin['rowptr'].numpy())
     assert hp.cams.ctypes.data == pin['cams'].data_ptr()
+    up_keys = ['cams', 'pts', 'obs_uv', 'obs_cam', 'rowptr']                 # obs_pt is not uploaded
+    if V <= 65536 and not args.cam_i32:
+        # half-width camera indices on the bus (SFMBA_PROBLEM_CAM_U16): prepared once, like the other pinned inputs
+        pin['obs_cam16'] = pinned_like(prob.obs_cam.astype(np.uint16))
+        hp.obs_cam16 = pin['obs_cam16'].numpy()
+        up_keys[3] = 'obs_cam16'
     cams_h0, pts_h0 = prob.cams.copy(), prob.pts.copy()
-    h2d = sum(getattr(hp, k).nbytes for k in ('cams', 'pts', 'obs_uv', 'obs_cam', 'rowptr'))   # obs_pt is not uploaded
+    h2d = sum(getattr(hp, k).nbytes for k in up_keys)
     d2h = hp.cams.nbytes + hp.pts.nbytes
     e2e_steps = max(1, min(args.steps, 5))
     for _ in range(min(args.warmup, 2)):
@@ -443,7 +449,8 @@ def run_ours(args):
                                         'traffic': k12_traffic, 'traffic_source': k12_src},
             'e2e': {'value': LM_ITERS * e2e_steps / e2e_s, 'unit': 'LM iterations/s', 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'ms_per_step': e2e_s / e2e_steps * 1e3,
-                    'kernel_launches_per_step': launches_e2e},
+                    'kernel_launches_per_step': launches_e2e, 'obs_cam_wire_format': 'u16' if 'obs_cam16' in up_keys else 'i32',
+                    'pcie_gbs_if_serial': (h2d + d2h) / (e2e_s / e2e_steps) / 1e9},
             'gpu_launches': launches,
             'clocks': sampler.summary(),
             'parity_vs_golden': parity,
@@ -482,6 +489,7 @@ def main():
     ap.add_argument('--scale', type=float, default=1.0)
     ap.add_argument('--pcg-tol', type=float, default=1e-8)
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--cam-i32', action='store_true', help='e2e: upload obs_cam as int32 instead of uint16')
     ap.add_argument('--no-extras', action='store_true', help='skip the c3 / ba_weak_damping keys (N = 1 only)')
     ap.add_argument('--matvec', default='auto', choices=['auto', 'f64', 'f32'],
                     help='sfmba_options.matvec_precision (auto = the library default)')

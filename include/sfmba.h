@@ -86,14 +86,18 @@ typedef enum { SFMBA_MATVEC_AUTO = 0, SFMBA_MATVEC_F64 = 1, SFMBA_MATVEC_F32 = 2
  * observations partitioned by point).  Replaces the packing at ba_processor.py:285-294 and the
  * per-observation gathers at ba_processor.py:309-342.
  */
+/* sfmba_problem.flags.  CAM_U16 (sfmba_ba_solve_host only): obs_cam points to uint16_t[m] instead of int32_t[m]
+ * (num_cams <= 65536) -- half the bytes of the largest index array on the bus; widened on the device, bit-exact.   */
+#define SFMBA_PROBLEM_CAM_U16 1
+
 typedef struct {
   int32_t num_cams;          /* V                                                                   */
   int32_t num_pts;           /* N (local)                                                           */
   int32_t num_obs;           /* m (local)                                                           */
-  int32_t reserved0;
+  int32_t flags;             /* SFMBA_PROBLEM_* bits, 0 = the plain layout below                    */
   const float*   obs_uv;     /* f32 [2][m] SoA: all u then all v.  Pixel coordinates when cam_kinv  */
                              /* is given (cv2.KeyPoint.pt is float32), else already normalised      */
-  const int32_t* obs_cam;    /* i32 [m] camera index of each observation                            */
+  const int32_t* obs_cam;    /* i32 [m] camera index of each observation (u16 [m] with SFMBA_PROBLEM_CAM_U16) */
   const int32_t* obs_pt;     /* i32 [m] point index, non-decreasing (point-major order).  Read only */
                              /* by sfmba_residual_jacobian / sfmba_ba_cost; the solve derives it   */
                              /* from pt_rowptr and accepts NULL                                    */

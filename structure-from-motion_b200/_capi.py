@@ -24,6 +24,7 @@ MODE_REFERENCE_FIXED, MODE_ADAPTIVE_LM = 0, 1
 SOLVER_PCG, SOLVER_DENSE_CHOLESKY = 0, 1
 PRECOND_JACOBI, PRECOND_SCHUR_JACOBI = 0, 1
 MATVEC_AUTO, MATVEC_F64, MATVEC_F32 = 0, 1, 2
+PROBLEM_CAM_U16 = 1
 SOLVER_PCG = 0
 
 
@@ -34,7 +35,7 @@ class SfmbaError(RuntimeError):
 
 
 class Problem(C.Structure):
-    _fields_ = [('num_cams', C.c_int32), ('num_pts', C.c_int32), ('num_obs', C.c_int32), ('reserved0', C.c_int32),
+    _fields_ = [('num_cams', C.c_int32), ('num_pts', C.c_int32), ('num_obs', C.c_int32), ('flags', C.c_int32),
                 ('obs_uv', C.c_void_p), ('obs_cam', C.c_void_p), ('obs_pt', C.c_void_p), ('pt_rowptr', C.c_void_p),
                 ('cam_kinv', C.c_void_p), ('cams', C.c_void_p), ('pts', C.c_void_p)]
 

@@ -335,6 +335,28 @@ __global__ void k_cam_rowptr(const int32_t* __restrict__ sorted_cam, int n, int 
   out[c] = lo;
 }
 
+__global__ void k_widen_u16(const uint16_t* __restrict__ in, int32_t* __restrict__ out, size_t n) {
+  // eight indices per thread: one 16-byte load, two 16-byte stores
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (i + 8 <= n) {
+    const uint4 v = *reinterpret_cast<const uint4*>(in + i);
+    int4 a, b;
+    a.x = v.x & 0xffff; a.y = v.x >> 16; a.z = v.y & 0xffff; a.w = v.y >> 16;
+    b.x = v.z & 0xffff; b.y = v.z >> 16; b.z = v.w & 0xffff; b.w = v.w >> 16;
+    *reinterpret_cast<int4*>(out + i) = a;
+    *reinterpret_cast<int4*>(out + i + 4) = b;
+  } else {
+    for (size_t k = i; k < n; ++k) out[k] = in[k];
+  }
+}
+
+void launch_widen_u16(const uint16_t* in, int32_t* out, size_t n, cudaStream_t st, LaunchCounter& lc) {
+  if (n == 0) return;
+  const size_t threads = (n + 7) / 8;
+  k_widen_u16<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(in, out, n);
+  lc.launches++;
+}
+
 static int bits_for(int n) {   // bits needed to represent values in [0, n]
   int b = 1;
   while ((1ll << b) <= (long long)n) ++b;

@@ -103,6 +103,8 @@ constexpr int PEER_HEADER_BYTES = 256;
 struct PeerWindow {
   int world, rank;
   unsigned long long cap;             // doubles per (parity, rank) slot
+  unsigned long long ll_cam;          // doubles from the start of a slot to the flag-in-data area of the camera sums
+  unsigned long long ll_y;            // ... and of the PCG matvec result
   unsigned long long timeout_ns;      // how long a rank waits for a peer's flag before it gives up (SFMBA_ERR_COMM)
   char* base[MAX_PEERS];              // window of every rank in this rank's address space
   __host__ __device__ unsigned long long* flags(int r) const { return reinterpret_cast<unsigned long long*>(base[r]); }
@@ -205,6 +207,8 @@ void launch_chunk_build(const BaDev& d, int g0, int g1, cudaStream_t st, LaunchC
 // phase 2b: camera -> segment-row CSR over all chunks
 void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_bytes, int32_t* sort_keys_out,
                         int32_t* iota, cudaStream_t st, LaunchCounter& lc);
+
+void launch_widen_u16(const uint16_t* in, int32_t* out, size_t n, cudaStream_t st, LaunchCounter& lc);
 
 // ---- linearisation (ba_linearize.cu) ------------------------------------------------------------
 void launch_cam_prepare(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

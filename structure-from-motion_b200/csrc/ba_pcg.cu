@@ -570,39 +570,30 @@ __device__ __forceinline__ void grid_barrier(uint32_t* counter, Scalars* sc) {
   __syncthreads();
 }
 
-// y of one PCG matvec, by mode.  MODE 3 first exchanges the partial results: every rank's y from its own rows goes
-// straight into its slot of EVERY rank's peer window over NVLink, the CTA that finishes last raises the flags, every CTA
-// waits for the flags of all ranks (this wait is also the grid-wide barrier between the stores and the reads below).
-// Returns the parity of the exchange.
+// y of one PCG matvec, by mode.
+//   MODE 1  from this GPU's segment rows
+//   MODE 2  svec, all-reduced by NCCL
+//   MODE 3  peer windows over NVLink, flag-in-data ("LL") protocol: the warp that owns a camera gathers this rank's partial
+//           y, stores each double as one 16-byte word {lo, seq, hi, seq} into its slot of EVERY rank's window, then reads
+//           the same camera's words of all ranks from its own window, spinning until both sequence tags match, and adds
+//           them in rank order -- every rank gets bit-identical sums.  No fence, no ticket, no separate flag, no grid-wide
+//           wait: a warp waits only for the seven numbers it needs.  Two parities: a rank can reach exchange s + 2 only
+//           after every peer has finished reading exchange s (they send s + 1 after that).
 template <int MODE>
-__device__ __forceinline__ int pcg_exchange_y(const BaDev& d, double2* gat_warp) {
-  if (MODE != 3) return 0;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const PeerWindow& xw = d.xw;
-  const unsigned long long seq = *xw.counter() + 1ull;      // advanced by the CTA that finishes the kernel last
-  const int par = (int)(seq & 1ull);
-  for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
-    const double y = cam_y_gather(d, cam, lane, gat_warp);
+__device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, double2* gat_warp) {
+  if (MODE == 2) return lane < 7 ? d.svec[7 * (size_t)cam + lane] : 0.0;
+  double y = cam_y_gather(d, cam, lane, gat_warp);
+  if (MODE == 3) {
+    const PeerWindow& xw = d.xw;
+    const unsigned long long seq64 = *xw.counter() + 1ull;    // advanced by the CTA that finishes the kernel last
+    const unsigned seq = (unsigned)seq64;
+    const int par = (int)(seq64 & 1ull);
     if (lane < 7) {
-      const size_t k = 7 * (size_t)cam + lane;
-      for (int w = 0; w < xw.world; ++w) xw.slot(w, par, xw.rank)[k] = y;
-    }
-  }
-  peer_publish(xw, seq, &d.sc->ticket_a);
-  peer_wait(xw, seq, d.sc);
-  return par;
-}
-
-// MODE 1: from this GPU's rows; 2: svec, all-reduced by NCCL; 3: the slots of all ranks, summed in rank order
-template <int MODE>
-__device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, int par, double2* gat_warp) {
-  if (MODE == 1) return cam_y_gather(d, cam, lane, gat_warp);
-  double y = 0.0;
-  if (lane < 7) {
-    const size_t k = 7 * (size_t)cam + lane;
-    if (MODE == 2) y = d.svec[k];
-    if (MODE == 3) {
-      for (int w = 0; w < d.xw.world; ++w) y += __ldcg(d.xw.slot(d.xw.rank, par, w) + k);
+      const size_t k2 = 2 * (7 * (size_t)cam + lane);
+      for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(d.xw, w, par, xw.rank, d.xw.ll_y) + k2, y, seq);
+      double a = 0.0;
+      for (int w = 0; w < xw.world; ++w) a += ll_load(ll_slot(d.xw, xw.rank, par, w, d.xw.ll_y) + k2, seq, xw.timeout_ns, d.sc);
+      y = a;
     }
   }
   return y;
@@ -653,11 +644,10 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, i
   // scalars of the previous iteration: rewritten only by the CTA that finishes this kernel last
   const double gam_old = sc->rz, alpha_old = sc->alpha, gg = sc->gg;
   const int it_old = sc->pcg_iters;
-  const int par = pcg_exchange_y<MODE>(d, gat[warp]);
   double gam = 0.0, del = 0.0;
   for (int cam = gwarp; cam < d.V; cam += nwarps) {
     const size_t k = 7 * (size_t)cam + lane;
-    const double y = pcg_cam_y<MODE>(d, cam, lane, par, gat[warp]);
+    const double y = pcg_cam_y<MODE>(d, cam, lane, gat[warp]);
     const double zv = l7 ? d.z[k] : 0.0;
     const double az = cam == gwarp ? row7_dot_reg(arow, zv) : row7_dot(d.ablk + 49 * (size_t)cam, lane, zv);
     if (l7) {
@@ -794,11 +784,10 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_refresh(BaDev d, double tol
   Scalars* sc = d.sc;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool l7 = lane < 7;
-  const int par = pcg_exchange_y<MODE>(d, gat[warp]);
   double rr = 0.0;
   for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
     const size_t k = 7 * (size_t)cam + lane;
-    const double y = pcg_cam_y<MODE>(d, cam, lane, par, gat[warp]);
+    const double y = pcg_cam_y<MODE>(d, cam, lane, gat[warp]);
     const double xv = l7 ? d.x[k] : 0.0;
     const double ax = row7_dot(d.ablk + 49 * (size_t)cam, lane, xv);
     double rn = 0.0;

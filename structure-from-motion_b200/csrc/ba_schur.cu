@@ -507,13 +507,19 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
   const int row = schur ? CAM_ACC : ROW_COMPACT;
   const bool hi = lane + 32 < row;
   int par = 0;
+  unsigned seq = 0;
   if (PEER) {
-    const unsigned long long seq = *d.xw.counter() + 1ull;    // advanced by the CTA that finishes last
-    par = (int)(seq & 1ull);
-    peer_wait(d.xw, seq, sc);
+    // several GPUs: this rank's sums go out as flag-in-data words and every rank's words of the same camera come back in
+    // the same warp (peer.cuh); the cost travels as one more entry behind the cameras
+    const unsigned long long seq64 = *d.xw.counter() + 1ull;  // advanced by the CTA that finishes last
+    seq = (unsigned)seq64;
+    par = (int)(seq64 & 1ull);
     if (blockIdx.x == 0 && tid == 0) {
+      const PeerWindow& xw = d.xw;
+      const size_t k2 = 2 * (size_t)d.V * row;
+      for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_cam) + k2, sc->cost_cur, seq);
       double c = 0.0;
-      for (int w = 0; w < d.xw.world; ++w) c += __ldcg(d.xw.slot(d.xw.rank, par, w) + (size_t)d.V * row);
+      for (int w = 0; w < xw.world; ++w) c += ll_load(ll_slot(xw, xw.rank, par, w, xw.ll_cam) + k2, seq, xw.timeout_ns, sc);
       sc->cost_cur = c;
       if (cost_slot < SFMBA_MAX_COST_HISTORY) sc->costs[cost_slot] = c;
     }
@@ -522,14 +528,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
   double rr = 0.0;
   for (int cam = blockIdx.x * FIN_WARPS + warp; cam < d.V; cam += gridDim.x * FIN_WARPS) {
     double a0 = 0.0, a1 = 0.0;                       // elements lane, lane + 32 of the camera's row sum
-    if (PEER) {
-      const size_t base = (size_t)cam * row + lane;
-      for (int w = 0; w < d.xw.world; ++w) {
-        const double* sl = d.xw.slot(d.xw.rank, par, w) + base;
-        a0 += __ldcg(sl);
-        if (hi) a1 += __ldcg(sl + 32);
-      }
-    } else {
+    {
       const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
       const double* p = d.part64 + lane;
       for (int k = r0; k < r1; k += 8) {             // eight rows in flight, summed in row order
@@ -546,6 +545,23 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
           a1 += w[u];
         }
       }
+    }
+    if (PEER) {
+      const PeerWindow& xw = d.xw;
+      const size_t k2 = 2 * ((size_t)cam * row + lane);
+      for (int w = 0; w < xw.world; ++w) {
+        double* dst = ll_slot(xw, w, par, xw.rank, xw.ll_cam) + k2;
+        ll_store(dst, a0, seq);
+        if (hi) ll_store(dst + 64, a1, seq);
+      }
+      double s0 = 0.0, s1 = 0.0;
+      for (int w = 0; w < xw.world; ++w) {
+        const double* src = ll_slot(xw, xw.rank, par, w, xw.ll_cam) + k2;
+        s0 += ll_load(src, seq, xw.timeout_ns, sc);
+        if (hi) s1 += ll_load(src + 64, seq, xw.timeout_ns, sc);
+      }
+      a0 = s0;
+      a1 = s1;
     }
     d.cam_acc[(size_t)cam * CAM_ACC + acc_index(d, lane)] = a0;
     if (hi) d.cam_acc[(size_t)cam * CAM_ACC + acc_index(d, lane + 32)] = a1;
@@ -681,9 +697,8 @@ static int fin_grid(const BaDev& d) {
 void launch_cam_finish(const BaDev& d, bool peer, int cost_slot, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
                        LaunchCounter& lc) {
   if (peer) {
-    k_camsum64_peer<<<d.V, 256, 0, st>>>(d);
     k_cam_finish<true><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0);
-    lc.launches += 2;
+    lc.launches++;
   } else {
     k_cam_finish<false><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0);
     lc.launches++;

@@ -274,8 +274,14 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   // several GPUs: map the peer windows (first solve, or more cameras than before); NCCL otherwise
   memset(&d.xw, 0, sizeof(d.xw));
   if (multi) {
-    if ((rc = sfm_peer_setup(ctx, (size_t)d.V * CAM_ACC + 64, st)) != 0) return rc;
+    // a slot: plain doubles of the camera-sum exchange of the unfused path (+ the cost), then the flag-in-data areas
+    // (16 bytes per entry) of the camera sums (+ the cost) and of the PCG matvec result
+    const size_t ll_cam = ((size_t)d.V * CAM_ACC + 64 + 1) & ~(size_t)1;
+    const size_t ll_y = ll_cam + 2 * ((size_t)d.V * CAM_ACC + 2);
+    if ((rc = sfm_peer_setup(ctx, ll_y + 2 * (size_t)n7 + 16, st)) != 0) return rc;
     d.xw = ctx->peer;
+    d.xw.ll_cam = ll_cam;
+    d.xw.ll_y = ll_y;
   }
   const bool peer = multi && d.xw.world == ctx->world;
   // PCG progress word in pinned memory: polled by the host when the ranks need no matched collectives

@@ -164,6 +164,8 @@ int sfmba_destroy(sfmba_ctx* ctx) {
 int sfmba_ba_solve(sfmba_ctx* ctx, const sfmba_problem* problem, const sfmba_options* opt, sfmba_result* result,
                    void* stream) {
   if (!ctx) return sfm_set_error(nullptr, SFMBA_ERR_INVALID_ARG, "null ctx");
+  if (problem && problem->flags != 0)
+    return sfm_set_error(ctx, SFMBA_ERR_UNSUPPORTED, "sfmba_problem.flags: the compact layouts are for sfmba_ba_solve_host");
   cudaSetDevice(ctx->device);
   return sfm_ba_solve_device(ctx, problem, opt, result, (cudaStream_t)stream, nullptr);
 }
@@ -193,7 +195,18 @@ int sfmba_ba_solve_host(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   // pt_rowptr[j] + 2 j >= 1024 g, ba_index.cu) so that the record build and the first linearisation of a range run
   // while the later ranges are still on the bus.
   if ((rc = stage_in(ctx, 3, pr->pt_rowptr, N + 1, &d_row, io.copy))) return rc;
-  if ((rc = stage_in(ctx, 1, pr->obs_cam, m, &d_cam, io.copy))) return rc;
+  if (pr->flags & SFMBA_PROBLEM_CAM_U16) {
+    // half-width camera indices on the bus, widened on the device behind the copy
+    if (pr->num_cams > 65536) return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG, "SFMBA_PROBLEM_CAM_U16 needs num_cams <= 65536");
+    uint16_t* d_cam16;
+    if ((rc = stage_in(ctx, 8, reinterpret_cast<const uint16_t*>(pr->obs_cam), m, &d_cam16, io.copy))) return rc;
+    cudaError_t e = ctx->host_stage[1].reserve(std::max<size_t>(16, m * sizeof(int32_t)));
+    if (e != cudaSuccess) return sfm_check_cuda(ctx, e, "cudaMalloc(stage)");
+    d_cam = ctx->host_stage[1].as<int32_t>();
+    launch_widen_u16(d_cam16, d_cam, m, io.copy, ctx->lc);
+  } else {
+    if ((rc = stage_in(ctx, 1, pr->obs_cam, m, &d_cam, io.copy))) return rc;
+  }
   cudaEventRecord(io.ev_index, io.copy);
   if (pr->cam_kinv && (rc = stage_in(ctx, 4, pr->cam_kinv, 9 * V, &d_kinv, io.copy))) return rc;
   if ((rc = stage_in(ctx, 5, pr->cams, 7 * V, &d_cams, io.copy))) return rc;

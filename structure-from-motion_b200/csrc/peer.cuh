@@ -71,4 +71,35 @@ __device__ __forceinline__ void peer_wait(const PeerWindow& xw, unsigned long lo
   __syncthreads();
 }
 
+// ---- flag-in-data ("LL") exchange: every double travels as one 16-byte word {lo, seq, hi, seq}; the reader spins until
+// both sequence tags match.  No fence, no ticket, no separate flag: a reader waits only for the numbers it needs.
+__device__ __forceinline__ void ll_store(double* slot16, double v, unsigned seq) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(slot16), "r"((unsigned)b), "r"(seq),
+               "r"((unsigned)(b >> 32)), "r"(seq)
+               : "memory");
+}
+__device__ __forceinline__ double ll_load(const double* slot16, unsigned seq, unsigned long long timeout_ns, Scalars* sc) {
+  unsigned lo, f0, hi, f1;
+  unsigned spins = 0;
+  unsigned long long t0 = 0;
+  for (;;) {
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(f0), "=r"(hi), "=r"(f1) : "l"(slot16) : "memory");
+    if (f0 == seq && f1 == seq) break;
+    if ((++spins & 0xffu) == 0) {
+      const unsigned long long now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > timeout_ns) {
+        atomicOr(&sc->flags, FLAG_PEER_TIMEOUT);
+        break;
+      }
+    }
+  }
+  return __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
+}
+// a flag-in-data area of a window slot (offset in doubles from the slot's start); element k at 16 k bytes
+__device__ __forceinline__ double* ll_slot(const PeerWindow& xw, int window, int parity, int writer, unsigned long long off) {
+  return xw.slot(window, parity, writer) + off;
+}
+
 }  // namespace sfmba

@@ -28,6 +28,7 @@ class BAProblem:
     rowptr: np.ndarray
     kinv: np.ndarray | None = None
     obs_key: np.ndarray | None = None      # key-point index of each observation (bookkeeping only)
+    obs_cam16: np.ndarray | None = None    # obs_cam as uint16 (V <= 65536): the host-buffer solve uploads this instead
 
     def __post_init__(self):
         self.cams = np.ascontiguousarray(self.cams, dtype=np.float64).reshape(-1, 7)
@@ -163,6 +164,11 @@ class Engine:
         cp.obs_uv, cp.obs_cam, cp.obs_pt = _ptr(p.obs_uv), _ptr(p.obs_cam), _ptr(p.obs_pt)
         cp.pt_rowptr, cp.cam_kinv = _ptr(p.rowptr), _ptr(p.kinv)
         cp.cams, cp.pts = _ptr(p.cams), _ptr(p.pts)
+        if p.obs_cam16 is not None:
+            if p.obs_cam16.dtype != np.uint16 or p.obs_cam16.shape != p.obs_cam.shape or not p.obs_cam16.flags.c_contiguous:
+                raise ValueError('obs_cam16 must be a contiguous uint16 copy of obs_cam')
+            cp.obs_cam = _ptr(p.obs_cam16)
+            cp.flags = _capi.PROBLEM_CAM_U16
         return cp
 
     def ba_solve_host(self, p: BAProblem, opt: _capi.Options | None = None, **kw) -> SolveResult:

@@ -224,3 +224,24 @@ def test_c_abi_rejects_bad_indices(engine):
     assert engine.ba_cost(good) > 0.0
     res = engine.ba_solve_host(good, lam=5.0, iterations=1)
     assert res.final_cost > 0.0 and not np.array_equal(good.cams, ref.cams)
+
+
+def test_u16_camera_indices_give_identical_bits(engine):
+    """SFMBA_PROBLEM_CAM_U16: the host-buffer solve uploads obs_cam as uint16 and widens it on the device."""
+    from sfm_b200 import synthetic
+    p1, _ = synthetic.make_shape('ladybug')
+    p2, _ = synthetic.make_shape('ladybug')
+    p2.obs_cam16 = p2.obs_cam.astype(np.uint16)
+    r1 = engine.ba_solve_host(p1, lam=5.0, iterations=2)
+    r2 = engine.ba_solve_host(p2, lam=5.0, iterations=2)
+    assert np.array_equal(p1.cams, p2.cams) and np.array_equal(p1.pts, p2.pts)
+    assert r1.costs == r2.costs
+    t = engine.to_device(p2)
+    cp = engine._dev_problem(t)
+    cp.flags = 1
+    import ctypes as C
+    from sfm_b200 import _capi
+    res = _capi.Result()
+    opt = engine.make_options()
+    rc = engine.lib.sfmba_ba_solve(engine.ctx, C.byref(cp), C.byref(opt), C.byref(res), None)
+    assert rc == _capi.ERR_UNSUPPORTED                    # the compact layout is a host-buffer wire format

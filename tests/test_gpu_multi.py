@@ -80,7 +80,8 @@ out = 'skipped'
 if rank == 0:                                           # rank 1 never enters the second solve
     before = sh.cams.copy()
     try:
-        eng.ba_solve_host(sh, lam=5.0, iterations=2)
+        # (no final cost: that one number is all-reduced by NCCL, which has its own way of dealing with a dead peer)
+        eng.ba_solve_host(sh, lam=5.0, iterations=2, compute_costs=False)
         out = 'returned OK'
     except _capi.SfmbaError as e:
         out = 'code %%d unchanged %%s' %% (e.code, bool(np.array_equal(before, sh.cams)))
