@@ -150,11 +150,23 @@ __global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chu
   }
 }
 
-__global__ void k_finish_scan(BaDev d) {
+__global__ void k_finish_scan(BaDev d, IndexStats* host_stats, unsigned epoch) {
   // grp_chunk holds the exclusive scan of grp_nchunk over [0, G); close it
   const int total = d.G > 0 ? d.grp_chunk[d.G - 1] + d.grp_nchunk[d.G - 1] : 0;
   d.grp_chunk[d.G] = total;
   d.sc->num_chunks = total;
+  if (host_stats) {
+    // what the host needs to size the chunk arrays and the tiles' shared memory, straight into pinned host memory: the
+    // host spins on the epoch word instead of synchronising the stream
+    host_stats->num_chunks = total;
+    host_stats->max_chunk_len = d.sc->max_chunk_len;
+    host_stats->max_group_pts = d.sc->max_group_pts;
+    host_stats->max_nseg = d.sc->max_nseg;
+    host_stats->max_k = d.sc->max_k;
+    host_stats->flags = d.sc->flags;
+    __threadfence_system();
+    *(volatile unsigned*)&host_stats->epoch = epoch;
+  }
 }
 
 struct BuildSmem {
@@ -373,8 +385,8 @@ size_t index_temp_bytes(int G, int chunk_bound, int V) {
 }
 
 // phase 1: groups and chunk counts (the host then reads sc->num_chunks and the shape statistics)
-void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, cudaStream_t st,
-                        LaunchCounter& lc) {
+void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, IndexStats* host_stats,
+                        unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
   k_validate_index<<<(d.N + 1 + 255) / 256, 256, 0, st>>>(d);
   k_group_bounds<<<(d.G + 1 + 255) / 256, 256, 0, st>>>(d);
   lc.launches += 2;
@@ -383,7 +395,7 @@ void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t tem
     cub::DeviceScan::ExclusiveSum(temp, temp_bytes, d.grp_nchunk, d.grp_chunk, d.G, st);
     lc.launches += 2;
   }
-  k_finish_scan<<<1, 1, 0, st>>>(d);
+  k_finish_scan<<<1, 1, 0, st>>>(d, host_stats, epoch);
   lc.launches++;
 }
 

@@ -186,6 +186,13 @@ struct BaDev {
   PeerWindow xw;                      // NVLink peer exchange window (world > 1 and peers mapped), else world = 0
 };
 
+// index statistics of one solve as the device hands them to the host (pinned memory)
+struct IndexStats {
+  unsigned epoch;                     // written last: the record belongs to this solve
+  int32_t num_chunks, max_chunk_len, max_group_pts, max_nseg, max_k;
+  uint32_t flags;
+};
+
 struct LaunchCounter {
   int64_t launches = 0;
 };
@@ -200,8 +207,8 @@ struct TileShape {                    // from the index statistics; sizes dynami
 // ---- index (ba_index.cu) ------------------------------------------------------------------------
 size_t index_temp_bytes(int G, int chunk_bound, int V);
 // phase 1: groups + chunk counts + shape statistics in sc (host reads them back once)
-void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, cudaStream_t st,
-                        LaunchCounter& lc);
+void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, IndexStats* host_stats,
+                        unsigned epoch, cudaStream_t st, LaunchCounter& lc);
 // phase 2a: records and run / segment tables of the groups [g0, g1) (needs obs_uv of their observations only)
 void launch_chunk_build(const BaDev& d, int g0, int g1, cudaStream_t st, LaunchCounter& lc);
 // phase 2b: camera -> segment-row CSR over all chunks
@@ -246,6 +253,7 @@ void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigne
 void launch_pcg_reopen(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 void launch_pcg_refresh(const BaDev& d, int mode, double tol, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
                         LaunchCounter& lc);
+void launch_peer_sum_scalars(const BaDev& d, double* vals, int n, cudaStream_t st, LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_backsub_points(const BaDev& d, bool from_f32, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);

@@ -1055,6 +1055,29 @@ void launch_pcg_refresh(const BaDev& d, int mode, double tol, unsigned epoch, bo
   lc.launches += 1;
 }
 
+// Sum of n <= 32 device scalars over the ranks through the peer windows (flag-in-data words in the PCG area): what the
+// cost of a candidate step and the final cost need.  One warp; every rank ends with the same bits.
+__global__ void k_peer_sum_scalars(BaDev d, double* vals, int n) {
+  const PeerWindow& xw = d.xw;
+  const unsigned long long seq64 = *xw.counter() + 1ull;
+  const unsigned seq = (unsigned)seq64;
+  const int par = (int)(seq64 & 1ull), i = threadIdx.x;
+  if (i < n) {
+    const double v = vals[i];
+    for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_y) + 2 * i, v, seq);
+    double a = 0.0;
+    for (int w = 0; w < xw.world; ++w) a += ll_load(ll_slot(xw, xw.rank, par, w, xw.ll_y) + 2 * i, seq, xw.timeout_ns, d.sc);
+    vals[i] = a;
+  }
+  __syncwarp();
+  if (i == 0) *xw.counter() = seq64;
+}
+
+void launch_peer_sum_scalars(const BaDev& d, double* vals, int n, cudaStream_t st, LaunchCounter& lc) {
+  k_peer_sum_scalars<<<1, 32, 0, st>>>(d, vals, n);
+  lc.launches++;
+}
+
 void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
   k_cam_rows<<<(d.V + 127) / 128, 128, 0, st>>>(d, vec, dvdc_quirk ? 1 : 0);
   lc.launches++;

@@ -309,18 +309,30 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   size_t temp_bytes = index_temp_bytes(d.G, 1, d.V);
   if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_TEMP, temp_bytes, &temp), "cudaMalloc(temp)")) != 0) return rc;
   if (io) cudaStreamWaitEvent(st, io->ev_index, 0);
-  launch_index_count(d, fine, temp, temp_bytes, st, lc);
-  cudaMemcpyAsync(hs, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, st);
-  if ((rc = sfm_check_cuda(ctx, cudaStreamSynchronize(st), "index count")) != 0) return rc;
-  const int nchunks = hs->num_chunks;
-  if ((hs->flags & SFMBA_FLAG_BAD_INDEX) || nchunks < 0 || nchunks > chunk_upper)
+  volatile IndexStats* ist = reinterpret_cast<volatile IndexStats*>(reinterpret_cast<char*>(ctx->pinned) + 32);
+  const unsigned idx_epoch = ++ctx->pcg_epoch;
+  launch_index_count(d, fine, temp, temp_bytes, const_cast<IndexStats*>(ist), idx_epoch, st, lc);
+  {
+    // the counting kernels' last act is to write the statistics into pinned memory: spin on their epoch word (a stream
+    // synchronisation costs several times the latency); the stream is only queried to notice a failed launch
+    long spins = 0;
+    while (ist->epoch != idx_epoch) {
+      if ((++spins & 0x3fff) == 0 && cudaStreamQuery(st) != cudaErrorNotReady) {
+        if (ist->epoch == idx_epoch) break;
+        rc = sfm_check_cuda(ctx, cudaGetLastError(), "index count");
+        return rc ? rc : sfm_set_error(ctx, SFMBA_ERR_CUDA, "index count made no progress");
+      }
+    }
+  }
+  const int nchunks = ist->num_chunks;
+  if ((ist->flags & SFMBA_FLAG_BAD_INDEX) || nchunks < 0 || nchunks > chunk_upper)
     return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG,
                          "pt_rowptr is not a CSR over [0, num_obs] or obs_cam has an index outside [0, num_cams)");
   TileShape ts;
-  ts.max_chunk_len = std::max(hs->max_chunk_len, 1);
-  ts.max_group_pts = std::max(hs->max_group_pts, 1);
-  ts.max_nseg = std::max(hs->max_nseg, 1);
-  ts.max_k = std::max(hs->max_k, 1);
+  ts.max_chunk_len = std::max((int)ist->max_chunk_len, 1);
+  ts.max_group_pts = std::max((int)ist->max_group_pts, 1);
+  ts.max_nseg = std::max((int)ist->max_nseg, 1);
+  ts.max_k = std::max((int)ist->max_k, 1);
   if ((rc = sfm_setup_chunks(ctx, nchunks, &d)) != 0) return rc;
   if (use_f32 && !(multi && !peer)) {
     if ((rc = carve(ctx, S_XREL, (size_t)std::max(d.N, 1), &d.xrel)) != 0) return rc;
@@ -552,7 +564,8 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       launch_cost_tiles(d, ts, nullptr, st, lc);       // -> sc->cost_new
       launch_lm_model_decrease(d, st, lc);             // -> sc->model_decrease, sc->md_pts (the next word)
       if (multi) {
-        if ((rc = sfm_nccl_allreduce_f64(ctx, &d.sc->cost_new, 2, st)) != 0) return rc;
+        if (peer) launch_peer_sum_scalars(d, &d.sc->cost_new, 2, st, lc);
+        else if ((rc = sfm_nccl_allreduce_f64(ctx, &d.sc->cost_new, 2, st)) != 0) return rc;
       }
       launch_lm_decide(d, opt.lm_lambda_min > 0 ? opt.lm_lambda_min : 1e-12,
                        opt.lm_lambda_max > 0 ? opt.lm_lambda_max : 1e12, st, lc);
@@ -579,7 +592,8 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     cudaEvent_t kb = pt.kbegin();
     launch_cost_tiles(d, ts, final_cost_dev, st, lc);
     pt.kend("cost", kb);
-    if (multi && (rc = sfm_nccl_allreduce_f64(ctx, final_cost_dev, 1, st)) != 0) return rc;
+    if (peer) launch_peer_sum_scalars(d, final_cost_dev, 1, st, lc);
+    else if (multi && (rc = sfm_nccl_allreduce_f64(ctx, final_cost_dev, 1, st)) != 0) return rc;
   }
   pt.end(PH_TOTAL, t_total);
 
