@@ -144,7 +144,8 @@ typedef struct {
   int32_t  num_costs;
   int32_t  pcg_refine_iterations;  /* FP64 iterations that finished solves begun with the FP32 matvec (AUTO)   */
   double   costs[SFMBA_MAX_COST_HISTORY];  /* cost at the start of iteration k, then the final cost */
-  /* device time of the phases of the last call, milliseconds (CUDA events on `stream`)             */
+  /* device time of the call (ms_total, always) and of its phases (after sfmba_profile_enable(ctx, 2), else 0),
+   * milliseconds, CUDA events on `stream`                                                           */
   float    ms_total, ms_index, ms_linearize, ms_camreduce, ms_pcg, ms_update;
   int32_t  kernel_launches;  /* kernels launched by the call                                        */
   int32_t  matvec_precision; /* SFMBA_MATVEC_F64 or SFMBA_MATVEC_F32: what the PCG matvecs of the call ran     */
@@ -299,7 +300,9 @@ SFMBA_API int sfmba_build_visibility(sfmba_ctx* ctx, int32_t num_views, int32_t 
 /* device time (ms) and launch count of named kernels accumulated since the last reset; names:
  * "linearize", "matvec", "pcg_tail", "backsub", "cost"                                            */
 SFMBA_API int sfmba_profile_reset(sfmba_ctx* ctx);
-SFMBA_API int sfmba_profile_enable(sfmba_ctx* ctx, int enable);    /* per-kernel event timing (adds syncs)    */
+/* enable: bit 0 = per-kernel event timing (records between the launches: the kernels no longer overlap), bit 1 = the
+ * per-phase times of sfmba_result.ms_* (ms_total is always measured).  Both off by default.                          */
+SFMBA_API int sfmba_profile_enable(sfmba_ctx* ctx, int enable);
 SFMBA_API int sfmba_profile_get(sfmba_ctx* ctx, const char* name, double* ms_total, int64_t* launches);
 SFMBA_API int64_t sfmba_total_launches(const sfmba_ctx* ctx);
 

@@ -23,6 +23,7 @@ def main():
     import torch
     names = sys.argv[1:] or ['bal_venice_ref', 'bal_venice_weak', 'bal_ladybug_ref']
     eng = sfm_b200.Engine(device=0)
+    eng.profile_enable(False, phases=True)
     for name in names:
         z = np.load(os.path.join(ROOT, 'tests', 'golden', name + '.npz'))
         prob, _ = synthetic.make_shape(str(z['shape']), scale=float(z['scale']))

@@ -173,12 +173,16 @@ struct PhaseTimer {
     }
     return ctx->timer_events[ctx->timer_next++];
   }
-  cudaEvent_t begin() {
+  // phase spans are recorded only on request (sfmba_profile_enable): ~40 event records and as many elapsed-time queries
+  // per solve are host time a tight loop of solves would pay for numbers nobody reads.  The total is always timed.
+  cudaEvent_t begin(bool always = false) {
+    if (!always && !ctx->phase_timing && !ctx->profile) return nullptr;
     cudaEvent_t e = get();
     cudaEventRecord(e, st);
     return e;
   }
   void end(int phase, cudaEvent_t b) {
+    if (!b) return;
     cudaEvent_t e = get();
     cudaEventRecord(e, st);
     spans.push_back({phase, {b, e}});
@@ -186,7 +190,7 @@ struct PhaseTimer {
   // named per-kernel spans, recorded only when ctx->profile is on (sfmba_profile_enable)
   struct KSpan { const char* name; cudaEvent_t b, e; };
   std::vector<KSpan> kspans;
-  cudaEvent_t kbegin() { return ctx->profile ? begin() : nullptr; }
+  cudaEvent_t kbegin() { return ctx->profile ? begin(true) : nullptr; }
   void kend(const char* name, cudaEvent_t b) {
     if (!ctx->profile) return;
     cudaEvent_t e = get();
@@ -289,7 +293,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
 
   PhaseTimer pt{ctx, st};
   ctx->timer_next = 0;                     // (a solve that failed half-way left its events checked out)
-  cudaEvent_t t_total = pt.begin();
+  cudaEvent_t t_total = pt.begin(true);
 
   // scalars (pageable source: the copy is staged by the driver before the call returns)
   Scalars h0;

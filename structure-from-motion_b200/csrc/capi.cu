@@ -737,7 +737,8 @@ int sfmba_profile_reset(sfmba_ctx* ctx) {
 
 int sfmba_profile_enable(sfmba_ctx* ctx, int enable) {
   if (!ctx) return SFMBA_ERR_INVALID_ARG;
-  ctx->profile = enable != 0;
+  ctx->profile = (enable & 1) != 0;
+  ctx->phase_timing = (enable & 2) != 0;
   return SFMBA_OK;
 }
 

@@ -65,7 +65,8 @@ struct sfmba_ctx {
     return e;
   }
   // profiling
-  bool profile = false;
+  bool profile = false;          // per-kernel spans (event records between the launches)
+  bool phase_timing = false;     // per-phase spans of sfmba_result.ms_*
   std::map<std::string, ProfileEntry> prof;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   cudaEvent_t phase_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

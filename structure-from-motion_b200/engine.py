@@ -419,8 +419,10 @@ class Engine:
                 rowptr.cpu().numpy())
 
     # -- profiling ---------------------------------------------------------------------------------
-    def profile_enable(self, on=True):
-        self.lib.sfmba_profile_enable(self.ctx, 1 if on else 0)
+    def profile_enable(self, on=True, phases=None):
+        """on: per-kernel spans (serialises the launches); phases: the per-phase times of SolveResult.ms (default: as on)."""
+        ph = on if phases is None else phases
+        self.lib.sfmba_profile_enable(self.ctx, (1 if on else 0) | (2 if ph else 0))
 
     def profile_reset(self):
         self.lib.sfmba_profile_reset(self.ctx)
