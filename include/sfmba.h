@@ -149,6 +149,8 @@ typedef struct {
   float    ms_total, ms_index, ms_linearize, ms_camreduce, ms_pcg, ms_update;
   int32_t  kernel_launches;  /* kernels launched by the call                                        */
   int32_t  matvec_precision; /* SFMBA_MATVEC_F64 or SFMBA_MATVEC_F32: what the PCG matvecs of the call ran     */
+  int32_t  relinearized;     /* AUTO: LM iterations redone from an FP64 linearisation (slow PCG after an FP32 one) */
+  int32_t  reserved1;
 } sfmba_result;
 
 /* ---- lifetime -------------------------------------------------------------------------------- */

@@ -43,7 +43,7 @@ def main():
             print(json.dumps({
                 'case': name, 'mode': mname, 'ran': {1: 'f64', 2: 'f32'}.get(res.matvec_precision), 'device_ms': round(best, 4),
                 'pcg_ms': round(res.ms['pcg'], 4), 'pcg_iterations': res.pcg_iterations,
-                'refine_iterations': res.pcg_refine_iterations, 'flags': res.flags,
+                'refine_iterations': res.pcg_refine_iterations, 'relinearized': res.relinearized, 'flags': res.flags,
                 'cams_vs_oracle': max_rel(cams, z['cams']), 'pts_vs_oracle': max_rel(pts[z['pts_idx']], z['pts_sample']),
                 'cost_vs_oracle': abs(res.final_cost - float(z['costs'][-1])) / float(z['costs'][-1])}), flush=True)
     eng.close()

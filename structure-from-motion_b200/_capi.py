@@ -55,7 +55,8 @@ class Result(C.Structure):
                 ('costs', C.c_double * SFMBA_MAX_COST_HISTORY),
                 ('ms_total', C.c_float), ('ms_index', C.c_float), ('ms_linearize', C.c_float),
                 ('ms_camreduce', C.c_float), ('ms_pcg', C.c_float), ('ms_update', C.c_float),
-                ('kernel_launches', C.c_int32), ('matvec_precision', C.c_int32)]
+                ('kernel_launches', C.c_int32), ('matvec_precision', C.c_int32),
+                ('relinearized', C.c_int32), ('reserved1', C.c_int32)]
 
 
 # every symbol include/sfmba.h declares: name -> (restype, argtypes)

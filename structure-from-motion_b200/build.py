@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 OBJ = os.path.join(HERE, 'build')
 LIB = os.path.join(HERE, 'libsfmba.so')
-SOURCES = ['ba_index.cu', 'ba_linearize.cu', 'ba_schur.cu', 'ba_pcg.cu', 'ba_matvec32.cu', 'dense.cu', 'ba_solver.cu', 'refine.cu', 'ransac.cu',
+SOURCES = ['ba_index.cu', 'ba_linearize.cu', 'ba_schur.cu', 'ba_linearize32.cu', 'ba_pcg.cu', 'ba_matvec32.cu', 'dense.cu', 'ba_solver.cu', 'refine.cu', 'ransac.cu',
            'visibility.cu', 'noalloc.cu', 'nccl_dl.cu', 'peer_window.cu', 'capi.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden', '--expt-relaxed-constexpr']

@@ -38,6 +38,9 @@ constexpr int SEG_CAP = 128;        // distinct cameras per chunk
 constexpr int SEG_RUN_STRIDE = SEG_CAP + 2;             // u16 entries per chunk in seg_lane0 (4-byte aligned rows)
 constexpr int CAM_ACC = 64;         // doubles per camera accumulator row: A(28) S(28) g(7) pad(1)
 constexpr int ROW_COMPACT = 36;     // doubles per segment row of the Gram sums without the S entries: A(28) g(7) pad(1)
+constexpr int MV_ROW32 = 16;        // floats per segment row of the FP32 matvec: 12 sums + pad = 64 bytes (two whole sectors)
+constexpr int ROW_F32 = 40;         // floats per segment row of the FP32 linearisation: A(28) g(7) pad(5) = 160 bytes, whole
+                                    // 32-byte sectors (144-byte rows made neighbouring CTAs share sectors: slower to sum)
 constexpr int MV_ACC = 12;          // doubles per matvec row: T[3][3] (c~ d^T), s[3]
 
 // record index word: ptl[0:10) pos[10:21) seg[21:28)
@@ -166,6 +169,8 @@ struct BaDev {
   float* dinv32;                      // [N][8] D^-1 (00 01 02 11 12 22 - -)
   float* segst;                       // [chunk_bound*SEG_CAP][12] per (chunk, segment): R (9), C - group origin (3)
   float* camit32;                     // [V][16] FP32 copy of the camit rows
+  float* part64f;                     // [chunk_bound*SEG_CAP][ROW_F32] segment rows of the FP32 linearisation
+  float* part12f;                     // [chunk_bound*SEG_CAP][MV_ROW32] segment rows of the FP32 matvec
   float* ubuf32;                      // [PCG_UBUF][3][N] the u_j the FP32 matvecs keep (as ubuf)
   double* part12;                     // [chunk_bound*SEG_CAP][MV_ACC]
   double* svec;                       // [7V] sum_j W D^-1 W^T p (local; allreduced when world > 1)
@@ -230,6 +235,9 @@ void launch_k1(const BaDev& d, bool dvdc_quirk, float* out_r, float* out_jp, flo
 // fused linearisation: point blocks (D^-1, v, cost -> sc->costs[cost_slot]) + camera-side Gram rows
 void launch_linearize(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int cost_slot, cudaStream_t st,
                       LaunchCounter& lc, int g0 = 0, int g1 = -1, bool sum_cost = true);
+// the same with FP32 Jacobian arithmetic (ba_linearize32.cu); plain least squares without the Schur-diagonal sums only
+void launch_linearize32(const BaDev& d, const TileShape& ts, bool dvdc_quirk, int cost_slot, cudaStream_t st,
+                        LaunchCounter& lc, int g0 = 0, int g1 = -1, bool sum_cost = true);
 void launch_sum_cost(const BaDev& d, int cost_slot, cudaStream_t st, LaunchCounter& lc);
 void launch_camsum64(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 // several GPUs with peer windows: segment rows -> every rank's window -> cam_acc and cost summed over ranks
@@ -237,8 +245,8 @@ void launch_camsum64_peer(const BaDev& d, int cost_slot, cudaStream_t st, Launch
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 // PCG solver: camera sums (this GPU's rows, or all ranks' through the peer windows), blocks and the PCG start in one
 // kernel per camera
-void launch_cam_finish(const BaDev& d, bool peer, int cost_slot, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
-                       LaunchCounter& lc);
+void launch_cam_finish(const BaDev& d, bool peer, bool rows_f32, int cost_slot, unsigned epoch, bool dvdc_quirk,
+                       cudaStream_t st, LaunchCounter& lc);
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
 void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
@@ -248,7 +256,7 @@ void launch_matvec32(const BaDev& d, const TileShape& ts, bool dvdc_quirk, cudaS
 void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // part12 -> svec (multi-GPU)
 // vector part of one PCG iteration.  mode 1: y from this GPU's rows; 2: y = svec (NCCL all-reduced);
 // 3: partial y exchanged through the peer windows over NVLink inside the kernel
-void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
+void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk, bool rows_f32,
                      cudaStream_t st, LaunchCounter& lc);
 void launch_pcg_reopen(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 void launch_pcg_refresh(const BaDev& d, int mode, double tol, unsigned epoch, bool dvdc_quirk, cudaStream_t st,

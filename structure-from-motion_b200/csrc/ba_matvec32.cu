@@ -355,23 +355,23 @@ __global__ void __launch_bounds__(RUN_LANES, MV32_MINB) k_matvec32(BaDev d, Mv32
       for (int e = 0; e < MV_ACC; ++e) dst[e] = acc[e];
     }
     __syncthreads();
-    // one thread per (segment, component): its runs are added in lane order, in FP64; consecutive threads write
-    // consecutive doubles of a row
+    // one thread per (segment, component): its runs are added in lane order; consecutive threads write consecutive
+    // floats of a row (the per-camera sums over the rows are FP64, cam_y_gather32)
     for (int i = tid; i < ci.nseg * MV_ACC; i += RUN_LANES) {
       const int s = i / MV_ACC, e = i - s * MV_ACC;
       const int ra = srun[s], rb = srun[s + 1];
-      double a = 0.0;
+      float a = 0.f;
       for (int rr = ra; rr < rb; rr += 4) {                  // up to four loads in flight, sums in lane order
         const int n = rb - rr;
         const float* q = flush + rr * MV32_STRIDE + e;
         const float v0 = q[0], v1 = n > 1 ? q[MV32_STRIDE] : 0.f, v2 = n > 2 ? q[2 * MV32_STRIDE] : 0.f;
         const float v3 = n > 3 ? q[3 * MV32_STRIDE] : 0.f;
-        a += (double)v0;
-        a += (double)v1;
-        a += (double)v2;
-        a += (double)v3;
+        a += v0;
+        a += v1;
+        a += v2;
+        a += v3;
       }
-      d.part12[(size_t)rpos[s] * MV_ACC + e] = a;
+      d.part12f[(size_t)rpos[s] * MV_ROW32 + e] = a;
     }
     __syncthreads();
   }

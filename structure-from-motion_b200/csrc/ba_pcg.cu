@@ -402,6 +402,33 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
   matvec_group<BACKSUB, ROBUST>(d, sh, dvdc_quirk, blockIdx.x, smem);
 }
 
+// y_i of a camera from the 12 sums over its segment rows (component c in lane c): y_C = -R s, y_q[j] = <Q_j, T>.
+// Returns y in lanes 0..6 (0 elsewhere).
+__device__ __forceinline__ double cam_y_from_sums(const BaDev& d, int cam, int lane, double tsum) {
+  double T[MV_ACC];
+#pragma unroll
+  for (int k = 0; k < MV_ACC; ++k) T[k] = __shfl_sync(0xffffffffu, tsum, k);
+  double y = 0.0;
+  if (lane < 7) {
+    const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
+    if (lane < 3) {
+      y = -(t[3 * lane] * T[9] + t[3 * lane + 1] * T[10] + t[3 * lane + 2] * T[11]);
+    } else {
+      const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
+      double Q[4][9];
+      quat_dRt(q2, Q);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (j == lane - 3) {
+#pragma unroll
+          for (int k = 0; k < 9; ++k) y += Q[j][k] * T[k];
+        }
+      }
+    }
+  }
+  return y;
+}
+
 // y_i from the camera's segment rows.  The rows of one camera are contiguous in part12 (camrow_ptr), so the whole warp
 // streams them with 16-byte loads: lane l's t-th load covers the doubles 2 (32 t + l), +1 of the block, i.e. component
 // pair (2 t + l) mod 6 of some row -- three accumulators per lane (t mod 3), six loads in flight, then one fixed-order
@@ -445,28 +472,43 @@ __device__ __forceinline__ double cam_y_gather(const BaDev& d, int cam, int lane
       }
     }
   }
-  double T[MV_ACC];
-#pragma unroll
-  for (int k = 0; k < MV_ACC; ++k) T[k] = __shfl_sync(0xffffffffu, tsum, k);
-  double y = 0.0;
-  if (lane < 7) {
-    const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
-    if (lane < 3) {
-      y = -(t[3 * lane] * T[9] + t[3 * lane + 1] * T[10] + t[3 * lane + 2] * T[11]);
-    } else {
-      const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
-      double Q[4][9];
-      quat_dRt(q2, Q);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (j == lane - 3) {
-#pragma unroll
-          for (int k = 0; k < 9; ++k) y += Q[j][k] * T[k];
-        }
-      }
-    }
+  return cam_y_from_sums(d, cam, lane, tsum);
+}
+
+// The same for the FP32 segment rows the FP32 matvec writes (MV_ROW32 = 16 floats = four 16-byte words per row, the
+// last one padding): lane l always reads word l mod 4 of some row, eight rows per warp-load, six loads in flight; FP32
+// sums inside a lane (about a dozen terms), FP64 across the lanes in a fixed order.
+__device__ __forceinline__ double cam_y_gather32(const BaDev& d, int cam, int lane, double2* buf) {
+  const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
+  const float4* src = reinterpret_cast<const float4*>(d.part12f + (size_t)r0 * MV_ROW32);
+  const int n4 = (r1 - r0) * (MV_ROW32 / 4);
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 a0 = zero;
+  auto add = [](float4& a, const float4 v) { a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w; };
+  int e = lane;
+  for (; e + 5 * 32 < n4; e += 6 * 32) {
+    const float4 v0 = __ldcg(src + e), v1 = __ldcg(src + e + 32), v2 = __ldcg(src + e + 64);
+    const float4 v3 = __ldcg(src + e + 96), v4 = __ldcg(src + e + 128), v5 = __ldcg(src + e + 160);
+    add(a0, v0); add(a0, v1); add(a0, v2); add(a0, v3); add(a0, v4); add(a0, v5);
   }
-  return y;
+  {
+    float4 v[5];
+#pragma unroll
+    for (int u = 0; u < 5; ++u) v[u] = e + 32 * u < n4 ? __ldcg(src + e + 32 * u) : zero;
+    add(a0, v[0]); add(a0, v[1]); add(a0, v[2]); add(a0, v[3]); add(a0, v[4]);
+  }
+  float4* bf = reinterpret_cast<float4*>(buf);               // [32] float4
+  __syncwarp();
+  bf[lane] = a0;
+  __syncwarp();
+  double tsum = 0.0;
+  if (lane < MV_ACC) {                                     // lane = component: word lane / 4 lives in lanes = it mod 4
+    const int q = lane >> 2, j = lane & 3;
+    const float* f = reinterpret_cast<const float*>(bf);
+#pragma unroll
+    for (int l = 0; l < 8; ++l) tsum += (double)f[(4 * l + q) * 4 + j];
+  }
+  return cam_y_from_sums(d, cam, lane, tsum);
 }
 
 constexpr int VEC_THREADS = 512;                 // vector kernels: one warp per camera
@@ -580,9 +622,9 @@ __device__ __forceinline__ void grid_barrier(uint32_t* counter, Scalars* sc) {
 //           wait: a warp waits only for the seven numbers it needs.  Two parities: a rank can reach exchange s + 2 only
 //           after every peer has finished reading exchange s (they send s + 1 after that).
 template <int MODE>
-__device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, double2* gat_warp) {
+__device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, double2* gat_warp, int rows_f32) {
   if (MODE == 2) return lane < 7 ? d.svec[7 * (size_t)cam + lane] : 0.0;
-  double y = cam_y_gather(d, cam, lane, gat_warp);
+  double y = rows_f32 ? cam_y_gather32(d, cam, lane, gat_warp) : cam_y_gather(d, cam, lane, gat_warp);
   if (MODE == 3) {
     const PeerWindow& xw = d.xw;
     const unsigned long long seq64 = *xw.counter() + 1ull;    // advanced by the CTA that finishes the kernel last
@@ -614,7 +656,7 @@ __device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, d
 //   phase 2  the updates above, partial |r|^2, ticket
 template <int MODE>
 __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, int max_iter, unsigned epoch,
-                                                         int dvdc_quirk) {
+                                                         int dvdc_quirk, int rows_f32) {
   __shared__ double red[64];
   __shared__ double2 gat[VEC_WARPS][96];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -647,7 +689,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, i
   double gam = 0.0, del = 0.0;
   for (int cam = gwarp; cam < d.V; cam += nwarps) {
     const size_t k = 7 * (size_t)cam + lane;
-    const double y = pcg_cam_y<MODE>(d, cam, lane, gat[warp]);
+    const double y = pcg_cam_y<MODE>(d, cam, lane, gat[warp], rows_f32);
     const double zv = l7 ? d.z[k] : 0.0;
     const double az = cam == gwarp ? row7_dot_reg(arow, zv) : row7_dot(d.ablk + 49 * (size_t)cam, lane, zv);
     if (l7) {
@@ -777,6 +819,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_init(BaDev d, unsigned epoc
 // solve whose first iterations ran the FP32 matvec: from here on the residual is a true FP64 one.
 template <int MODE>
 __global__ void __launch_bounds__(VEC_THREADS) k_pcg_refresh(BaDev d, double tol, unsigned epoch, int dvdc_quirk) {
+  const int rows_f32 = 0;                            // (the matvec before a refresh is the FP64 one)
   __shared__ double red[32];
   __shared__ double2 gat[VEC_WARPS][96];
   pdl_wait();
@@ -787,7 +830,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_refresh(BaDev d, double tol
   double rr = 0.0;
   for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
     const size_t k = 7 * (size_t)cam + lane;
-    const double y = pcg_cam_y<MODE>(d, cam, lane, gat[warp]);
+    const double y = pcg_cam_y<MODE>(d, cam, lane, gat[warp], rows_f32);
     const double xv = l7 ? d.x[k] : 0.0;
     const double ax = row7_dot(d.ablk + 49 * (size_t)cam, lane, xv);
     double rn = 0.0;
@@ -1020,16 +1063,17 @@ void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
 }
 
 // the vector part of a PCG iteration (one launch); mode 1: y from this GPU's rows, 2: from svec, 3: peer windows
-void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk,
+void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk, bool rows_f32,
                      cudaStream_t st, LaunchCounter& lc) {
+  const int rf = rows_f32 ? 1 : 0;
   const int g = vec_grid(d);
   const int q = dvdc_quirk ? 1 : 0;
   if (mode == 1) {
-    launch_pdl(k_pcg_step<1>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q);
+    launch_pdl(k_pcg_step<1>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
   } else if (mode == 2) {
-    launch_pdl(k_pcg_step<2>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q);
+    launch_pdl(k_pcg_step<2>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
   } else {
-    launch_pdl(k_pcg_step<3>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q);
+    launch_pdl(k_pcg_step<3>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
   }
   lc.launches += 1;
 }

@@ -499,7 +499,8 @@ __global__ void k_camsum64_peer(BaDev d);
 constexpr int FIN_WARPS = 8;
 
 template <bool PEER>
-__global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost_slot, unsigned epoch, int dvdc_quirk) {
+__global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost_slot, unsigned epoch, int dvdc_quirk,
+                                                              int rows_f32) {
   __shared__ double red[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   Scalars* sc = d.sc;
@@ -531,18 +532,48 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
     {
       const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
       const double* p = d.part64 + lane;
-      for (int k = r0; k < r1; k += 8) {             // eight rows in flight, summed in row order
-        double v[8], w[8];
+      const float* pf = d.part64f + lane;            // rows of the FP32 linearisation (ROW_F32 floats each)
+      if (rows_f32) {
+        // software-pipelined: the loads of the next eight rows are issued before the previous eight are converted and
+        // added (a conversion placed between two loads would hold the later load back: in-order issue)
+        float vf[8], wf[8];
+        auto load8 = [&](int k, float (&a)[8], float (&b)[8]) {
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const bool ok = k + u < r1;
-          v[u] = ok ? p[(size_t)(k + u) * row] : 0.0;
-          w[u] = (ok && hi) ? p[(size_t)(k + u) * row + 32] : 0.0;
+          for (int u = 0; u < 8; ++u) {
+            const bool ok = k + u < r1;
+            a[u] = ok ? __ldcg(pf + (size_t)(k + u) * ROW_F32) : 0.f;
+            b[u] = (ok && hi) ? __ldcg(pf + (size_t)(k + u) * ROW_F32 + 32) : 0.f;
+          }
+        };
+        load8(r0, vf, wf);
+        for (int k = r0; k < r1; k += 8) {
+          float nv[8], nw[8];
+          load8(k + 8, nv, nw);                        // (past the end: all zeros, no loads)
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            a0 += (double)vf[u];
+            a1 += (double)wf[u];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            vf[u] = nv[u];
+            wf[u] = nw[u];
+          }
         }
+      } else {
+        for (int k = r0; k < r1; k += 8) {             // eight rows in flight, summed in row order
+          double v[8], w[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          a0 += v[u];
-          a1 += w[u];
+          for (int u = 0; u < 8; ++u) {
+            const bool ok = k + u < r1;
+            v[u] = ok ? p[(size_t)(k + u) * row] : 0.0;
+            w[u] = (ok && hi) ? p[(size_t)(k + u) * row + 32] : 0.0;
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            a0 += v[u];
+            a1 += w[u];
+          }
         }
       }
     }
@@ -694,13 +725,14 @@ static int fin_grid(const BaDev& d) {
   return g < 1 ? 1 : (g > 2048 ? 2048 : g);           // red_b holds one partial per CTA
 }
 
-void launch_cam_finish(const BaDev& d, bool peer, int cost_slot, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
-                       LaunchCounter& lc) {
+void launch_cam_finish(const BaDev& d, bool peer, bool rows_f32, int cost_slot, unsigned epoch, bool dvdc_quirk,
+                       cudaStream_t st, LaunchCounter& lc) {
+  const int rf = rows_f32 ? 1 : 0;
   if (peer) {
-    k_cam_finish<true><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0);
+    k_cam_finish<true><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0, rf);
     lc.launches++;
   } else {
-    k_cam_finish<false><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0);
+    k_cam_finish<false><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0, rf);
     lc.launches++;
   }
 }

@@ -59,7 +59,7 @@ namespace {
 
 enum Slot {
   S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_EXV, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_UBUF, S_CAM_ACC, S_ABLK, S_MINV,
-  S_CAMIT, S_CAMIT32, S_UBUF32, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAM_RR, S_CAMS_BAK, S_PTS_BAK,
+  S_CAMIT, S_CAMIT32, S_UBUF32, S_PART12F, S_PART64F, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAM_RR, S_CAMS_BAK, S_PTS_BAK,
   S_CHUNK_INFO, S_REC_B, S_REC_IX, S_REC_W, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
 };
@@ -269,6 +269,11 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   const bool auto_prec = opt.matvec_precision == SFMBA_MATVEC_AUTO;
   const bool use_f32 = f32_ok && (opt.matvec_precision == SFMBA_MATVEC_F32 || (auto_prec && tol >= 1e-8));
   constexpr int F32_SAFE_ITERS = 8;
+  // FP32 Jacobian arithmetic in the linearisation (ba_linearize32.cu): where the FP32 matvec runs, no Schur-diagonal sums
+  static const int lin32_env = getenv("SFMBA_LIN32") ? atoi(getenv("SFMBA_LIN32")) : -1;
+  int relinearized = 0;
+  int f32_cond = 0;     // what the previous PCG solve OF THIS CALL said about the reduced system: 1 = converged fast, -1 = slow,
+                        // 0 = none yet (the first linearisation of a call is FP64: the result never depends on earlier calls)
   int refine_iters = 0;
   const bool adaptive = opt.mode == SFMBA_MODE_ADAPTIVE_LM;
   const bool multi = ctx->world > 1;
@@ -343,6 +348,8 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     if ((rc = carve(ctx, S_DINV32, (size_t)8 * std::max(d.N, 1), &d.dinv32)) != 0) return rc;
     if ((rc = carve(ctx, S_SEGST, (size_t)d.chunk_bound * SEG_CAP * 12, &d.segst)) != 0) return rc;
     if ((rc = carve(ctx, S_CAMIT32, (size_t)d.V * CAMIT_STRIDE, &d.camit32)) != 0) return rc;
+    if ((rc = carve(ctx, S_PART64F, (size_t)d.chunk_bound * SEG_CAP * ROW_F32, &d.part64f)) != 0) return rc;
+    if ((rc = carve(ctx, S_PART12F, (size_t)d.chunk_bound * SEG_CAP * MV_ROW32, &d.part12f)) != 0) return rc;
     if ((rc = carve(ctx, S_UBUF32, (size_t)PCG_UBUF * 3 * std::max(d.N, 1), &d.ubuf32)) != 0) return rc;
   }
   int32_t *sort_keys = nullptr, *iota = nullptr;
@@ -369,31 +376,44 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     for (int r = 0; r < io->num_ranges; ++r) cudaStreamWaitEvent(st, io->ev_range_pts[r], 0);   // (the backup reads every point)
   }
 
+  static const bool fused_finish = !(getenv("SFMBA_FUSED_FINISH") && atoi(getenv("SFMBA_FUSED_FINISH")) == 0);
+  // the FP32 linearisation writes FP32 segment rows, which only the fused camera finish reads
+  const bool lin32_ok = use_f32 && d.xrel != nullptr && opt.precond == SFMBA_PRECOND_JACOBI && fused_finish && (!multi || peer);
   int cost_slot = 0;
   for (int it = 0; it < opt.iterations; ++it) {
     t0 = pt.begin();
     if (adaptive) launch_lm_backup(d, st, lc);
+    // FP32 Jacobian arithmetic in this linearisation?  F32: always.  AUTO: from the second LM iteration of a call on, when
+    // the previous iteration's PCG solve showed a well-conditioned reduced system (it converged within F32_SAFE_ITERS
+    // iterations); if this iteration's solve then turns out slow after all, the iteration is redone from an FP64
+    // linearisation (the parameters are still untouched).
+    bool lin32 = lin32_ok && (lin32_env >= 0 ? lin32_env != 0
+                                             : (opt.matvec_precision == SFMBA_MATVEC_F32 || (auto_prec && f32_cond > 0)));
+    int pcg_finished = -1;                 // iterations of this PCG solve when the host knows the number
+    bool mv32 = false;                     // arithmetic of the matvecs being launched
+   for (int attempt = 0;; ++attempt) {
+    if (attempt > 0) t0 = pt.begin();
     launch_cam_prepare(d, st, lc);
     if (it == 0 && ranged) {
       // first linearisation of a host-buffer solve: range by range, behind the upload of the points
       for (int r = 0; r < io->num_ranges; ++r) {
         cudaStreamWaitEvent(st, io->ev_range_pts[r], 0);
-        launch_linearize(d, ts, quirk, cost_slot, st, lc, io->range_grp[r], io->range_grp[r + 1],
-                         r + 1 == io->num_ranges);
+        if (lin32) launch_linearize32(d, ts, quirk, cost_slot, st, lc, io->range_grp[r], io->range_grp[r + 1], r + 1 == io->num_ranges);
+        else launch_linearize(d, ts, quirk, cost_slot, st, lc, io->range_grp[r], io->range_grp[r + 1],
+                              r + 1 == io->num_ranges);
       }
     } else {
       cudaEvent_t kb = pt.kbegin();
-      launch_linearize(d, ts, quirk, cost_slot, st, lc);
+      if (lin32) launch_linearize32(d, ts, quirk, cost_slot, st, lc); else launch_linearize(d, ts, quirk, cost_slot, st, lc);
       pt.kend("linearize", kb);
     }
     pt.end(PH_LINEARIZE, t0);
 
     t0 = pt.begin();
     const unsigned pcg_epoch = ++ctx->pcg_epoch;
-    static const bool fused_finish = !(getenv("SFMBA_FUSED_FINISH") && atoi(getenv("SFMBA_FUSED_FINISH")) == 0);
     if (fused_finish && !dense && (!multi || peer)) {
       // PCG on one GPU or over peer windows: camera sums, blocks and the start of the PCG solve in one kernel per camera
-      launch_cam_finish(d, peer, cost_slot, pcg_epoch, quirk, st, lc);
+      launch_cam_finish(d, peer, lin32, cost_slot, pcg_epoch, quirk, st, lc);
     } else {
       if (peer) {
         launch_camsum64_peer(d, cost_slot, st, lc);
@@ -437,8 +457,9 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       launch_cam_rows(d, d.x, quirk, st, lc);
     }
     const int tail_mode = !multi ? 1 : (peer ? 3 : 2);
-    int pcg_finished = -1;                 // iterations of this PCG solve when the host knows the number
-    bool mv32 = use_f32 && tail_mode != 2; // arithmetic of the matvecs being launched
+    int pcg_count = -1;                    // iterations of the solve's first run (before any FP64 continuation)
+    pcg_finished = -1;
+    mv32 = use_f32 && tail_mode != 2;
     unsigned cur_epoch = pcg_epoch;
     auto launch_iteration = [&]() -> int {
       cudaEvent_t kb = pt.kbegin();
@@ -450,7 +471,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
         if (r2 != 0) return r2;
       }
       kb = pt.kbegin();
-      launch_pcg_tail(d, tail_mode, tol, max_iter, cur_epoch, quirk, st, lc);
+      launch_pcg_tail(d, tail_mode, tol, max_iter, cur_epoch, quirk, mv32, st, lc);
       pt.kend("pcg_tail", kb);
       return 0;
     };
@@ -504,6 +525,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       if ((rc = run(std::min(ctx->pcg_hint, max_iter))) != 0) return rc;
       ctx->pcg_hint = finished;
       pcg_finished = finished;
+      pcg_count = finished;
       if (mv32 && auto_prec && finished > F32_SAFE_ITERS && finished < max_iter) {
         // AUTO: a solve this slow amplifies the 1e-7 operator error of the FP32 matvec too much to accept unseen.  Its
         // x is the starting point of an FP64 continuation: true residual from one FP64 matvec on x, then FP64 iterations
@@ -548,6 +570,14 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       }
     }
     pt.end(PH_PCG, t0);
+    if (pcg_count >= 0) f32_cond = pcg_count <= F32_SAFE_ITERS ? 1 : -1;
+    if (lin32 && auto_prec && lin32_env < 0 && pcg_count > F32_SAFE_ITERS && attempt == 0) {
+      lin32 = false;                       // mispredicted: this reduced system is not one to perturb by 1e-7
+      ++relinearized;
+      continue;
+    }
+    break;
+   }
 
     t0 = pt.begin();
     {
@@ -631,6 +661,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     res->ms_total = pt.acc[PH_TOTAL];
     res->kernel_launches = (int32_t)(ctx->lc.launches - launches0);
     res->pcg_refine_iterations = refine_iters;
+    res->relinearized = relinearized;
     res->matvec_precision = (use_f32 && d.xrel) ? SFMBA_MATVEC_F32 : SFMBA_MATVEC_F64;
   }
   if (hs->flags & SFMBA_FLAG_PEER_TIMEOUT)

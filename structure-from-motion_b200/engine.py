@@ -76,6 +76,7 @@ class SolveResult:
     kernel_launches: int = 0
     pcg_refine_iterations: int = 0
     matvec_precision: int = 0
+    relinearized: int = 0
 
 
 def _ptr(a):
@@ -155,7 +156,7 @@ class Engine:
                            [res.costs[i] for i in range(res.num_costs)],
                            dict(total=res.ms_total, index=res.ms_index, linearize=res.ms_linearize,
                                 camreduce=res.ms_camreduce, pcg=res.ms_pcg, update=res.ms_update),
-                           res.kernel_launches, res.pcg_refine_iterations, res.matvec_precision)
+                           res.kernel_launches, res.pcg_refine_iterations, res.matvec_precision, res.relinearized)
 
     # -- BA: host buffers (the end-to-end path) ---------------------------------------------------
     def _host_problem(self, p: BAProblem) -> _capi.Problem:

@@ -80,10 +80,20 @@ def test_slow_path_equals_fast_path(engine):
     from sfm_b200 import synthetic
     p1, _ = synthetic.make_shape('small')
     p2, _ = synthetic.make_shape('small')
-    engine.ba_solve_host(p1, lam=5.0, iterations=2)
-    engine.ba_solve_host(p2, lam=5.0, iterations=2, force_slow_path=True)
+    from sfm_b200 import _capi
+    # FP64 arithmetic: the two paths differ only in the order of their sums
+    engine.ba_solve_host(p1, lam=5.0, iterations=2, matvec_precision=_capi.MATVEC_F64)
+    engine.ba_solve_host(p2, lam=5.0, iterations=2, force_slow_path=True, matvec_precision=_capi.MATVEC_F64)
     assert close(p1.cams, p2.cams, 1e-9)
     assert close(p1.pts, p2.pts, 1e-9)
+    # default (AUTO) and all-FP32 arithmetic: FP32 sums in another order agree to FP32 accuracy, far inside the parity bar
+    for prec in (_capi.MATVEC_AUTO, _capi.MATVEC_F32):
+        q1, _ = synthetic.make_shape('small')
+        q2, _ = synthetic.make_shape('small')
+        engine.ba_solve_host(q1, lam=5.0, iterations=2, matvec_precision=prec)
+        engine.ba_solve_host(q2, lam=5.0, iterations=2, force_slow_path=True, matvec_precision=prec)
+        assert close(q1.cams, q2.cams, 1e-6) and close(q1.pts, q2.pts, 1e-6)
+        assert close(q1.cams, p1.cams, 1e-5)               # (and it is the FP64 answer to the parity bar)
 
 
 @pytest.mark.parametrize('shape,lam', [('small', 5.0), ('ladybug', 5.0), ('ladybug', 1e-2)])
@@ -245,3 +255,26 @@ def test_u16_camera_indices_give_identical_bits(engine):
     opt = engine.make_options()
     rc = engine.lib.sfmba_ba_solve(engine.ctx, C.byref(cp), C.byref(opt), C.byref(res), None)
     assert rc == _capi.ERR_UNSUPPORTED                    # the compact layout is a host-buffer wire format
+
+
+def test_precision_modes_against_oracle(engine, oracle):
+    """sfmba_options.matvec_precision: F64, AUTO (the default: FP32 matvec, FP32 Jacobian arithmetic from the second LM
+    iteration on while the PCG solves stay fast) and F32 all meet the parity bar on a well-damped problem; F64 sits
+    orders of magnitude inside it.  AUTO falls back to FP64 by itself where PCG is slow (lambda = 1e-3)."""
+    from sfm_b200 import _capi, synthetic
+    base, _ = synthetic.make_shape('ladybug')
+    b = base.obs_uv.T.astype(np.float64)
+    cams, pts, costs = oracle.ba_solve(base.cams, base.pts, base.obs_cam, base.obs_pt, b, 5.0, 3)
+    for prec, tol in ((_capi.MATVEC_F64, 1e-8), (_capi.MATVEC_AUTO, PARAM_TOL), (_capi.MATVEC_F32, PARAM_TOL)):
+        p, _ = synthetic.make_shape('ladybug')
+        res = engine.ba_solve_host(p, lam=5.0, iterations=3, matvec_precision=prec)
+        assert close(p.cams, cams, tol) and close(p.pts, pts, tol), (prec, max_rel(p.cams, cams))
+        assert abs(res.final_cost - costs[-1]) <= COST_RTOL * costs[-1]
+        assert res.matvec_precision == (_capi.MATVEC_F64 if prec == _capi.MATVEC_F64 else _capi.MATVEC_F32)
+    # weak damping, exact Jacobian: slow PCG.  AUTO must land where FP64 lands
+    cams, pts, costs = oracle.ba_solve(base.cams, base.pts, base.obs_cam, base.obs_pt, b, 1e-3, 3, dvdc_quirk=False)
+    p, _ = synthetic.make_shape('ladybug')
+    res = engine.ba_solve_host(p, lam=1e-3, iterations=3, dvdc_sign_quirk=False)
+    assert close(p.cams, cams, PARAM_TOL) and close(p.pts, pts, PARAM_TOL), max_rel(p.cams, cams)
+    assert abs(res.final_cost - costs[-1]) <= COST_RTOL * costs[-1]
+    assert res.pcg_iterations > 3 * 8                     # really the slow regime

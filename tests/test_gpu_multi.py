@@ -28,8 +28,12 @@ dist.broadcast(buf, 0)
 eng = sfm_b200.Engine(device=rank, world_size=world, rank=rank, nccl_unique_id=bytes(buf.cpu().numpy().tobytes()))
 full, _ = synthetic.make_shape('ladybug')
 sh = synthetic.shard_problem(full, world, rank)
-res = eng.ba_solve_host(sh, lam=5.0, iterations=3)
-np.savez(os.path.join(%(out)r, 'rank%%d.npz' %% rank), cams=sh.cams, pts=sh.pts, cost=res.final_cost, c0=res.costs[0])
+from sfm_b200 import _capi
+res = eng.ba_solve_host(sh, lam=5.0, iterations=3, matvec_precision=_capi.MATVEC_F64)
+sh2 = synthetic.shard_problem(full, world, rank)
+res2 = eng.ba_solve_host(sh2, lam=5.0, iterations=3)              # default precision (AUTO)
+np.savez(os.path.join(%(out)r, 'rank%%d.npz' %% rank), cams=sh.cams, pts=sh.pts, cost=res.final_cost, c0=res.costs[0],
+         cams_auto=sh2.cams, pts_auto=sh2.pts, cost_auto=res2.final_cost)
 eng.close()
 dist.destroy_process_group()
 '''
@@ -47,13 +51,21 @@ def test_two_rank_solve_matches_single_gpu(engine, tmp_path):
                     '--master-addr', '127.0.0.1', '--master-port', '29533', str(script)], check=True, env=env,
                    timeout=600)
     full, _ = synthetic.make_shape('ladybug')
-    res = engine.ba_solve_host(full, lam=5.0, iterations=3)
+    from sfm_b200 import _capi
+    full_auto, _ = synthetic.make_shape('ladybug')
+    res_auto = engine.ba_solve_host(full_auto, lam=5.0, iterations=3)
+    res = engine.ba_solve_host(full, lam=5.0, iterations=3, matvec_precision=_capi.MATVEC_F64)
     out = [np.load(tmp_path / ('rank%d.npz' % r)) for r in range(2)]
     for o in out:
         assert np.max(np.abs(o['cams'] - full.cams)) < 1e-9
         assert abs(float(o['cost']) - res.final_cost) <= 1e-9 * res.final_cost
         assert abs(float(o['c0']) - res.costs[0]) <= 1e-9 * res.costs[0]
     assert np.max(np.abs(np.concatenate([o['pts'] for o in out]) - full.pts)) < 1e-8
+    # default precision: FP32 sums over another partition of the points agree to FP32 accuracy
+    for o in out:
+        assert np.max(np.abs(o['cams_auto'] - full_auto.cams)) < 1e-6
+        assert abs(float(o['cost_auto']) - res_auto.final_cost) <= 1e-6 * res_auto.final_cost
+    assert np.max(np.abs(np.concatenate([o['pts_auto'] for o in out]) - full_auto.pts)) < 1e-6
 
 
 TIMEOUT_WORKER = r'''

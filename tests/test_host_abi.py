@@ -49,7 +49,7 @@ def test_struct_layouts_match_header(lib):
     assert (opt.compute_costs, opt.force_slow_path, opt.huber_delta) == (1, 0, 0.0)
     assert (opt.lm_lambda_min, opt.lm_lambda_max) == (1e-12, 1e12)
     assert ctypes.sizeof(_capi.Options) == 8 + 4 * 4 + 8 + 4 * 4 + 3 * 8 + 2 * 4
-    assert ctypes.sizeof(_capi.Result) == 3 * 8 + 6 * 4 + 64 * 8 + 6 * 4 + 2 * 4
+    assert ctypes.sizeof(_capi.Result) == 3 * 8 + 6 * 4 + 64 * 8 + 6 * 4 + 4 * 4
 
 
 def test_no_cpu_fallback_without_gpu():
