@@ -300,7 +300,7 @@ SFMBA_API int sfmba_build_visibility(sfmba_ctx* ctx, int32_t num_views, int32_t 
 
 /* ---- introspection used by bench.py ---------------------------------------------------------- */
 /* device time (ms) and launch count of named kernels accumulated since the last reset; names:
- * "linearize", "matvec", "pcg_tail", "backsub", "cost"                                            */
+ * "linearize", "linearize32", "matvec", "pcg_tail", "backsub", "cost"                                            */
 SFMBA_API int sfmba_profile_reset(sfmba_ctx* ctx);
 /* enable: bit 0 = per-kernel event timing (records between the launches: the kernels no longer overlap), bit 1 = the
  * per-phase times of sfmba_result.ms_* (ms_total is always measured).  Both off by default.                          */

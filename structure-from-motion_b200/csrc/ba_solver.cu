@@ -405,7 +405,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     } else {
       cudaEvent_t kb = pt.kbegin();
       if (lin32) launch_linearize32(d, ts, quirk, cost_slot, st, lc); else launch_linearize(d, ts, quirk, cost_slot, st, lc);
-      pt.kend("linearize", kb);
+      pt.kend(lin32 ? "linearize32" : "linearize", kb);
     }
     pt.end(PH_LINEARIZE, t0);
 
