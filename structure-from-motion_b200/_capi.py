@@ -45,7 +45,7 @@ class Options(C.Structure):
                 ('pcg_max_iter', C.c_int32), ('pcg_tol', C.c_double), ('dvdc_sign_quirk', C.c_int32),
                 ('force_slow_path', C.c_int32), ('compute_costs', C.c_int32), ('precond', C.c_int32),
                 ('lm_lambda_min', C.c_double), ('lm_lambda_max', C.c_double), ('huber_delta', C.c_double),
-                ('matvec_precision', C.c_int32), ('reserved0', C.c_int32)]
+                ('matvec_precision', C.c_int32), ('reuse_index', C.c_int32)]
 
 
 class Result(C.Structure):

@@ -319,9 +319,16 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if ((rc = sfm_check_cuda(ctx, ctx->reserve(S_TEMP, temp_bytes, &temp), "cudaMalloc(temp)")) != 0) return rc;
   if (io) cudaStreamWaitEvent(st, io->ev_index, 0);
   volatile IndexStats* ist = reinterpret_cast<volatile IndexStats*>(reinterpret_cast<char*>(ctx->pinned) + 32);
+  // sfmba_options.reuse_index: the caller vouches that the structure and the observations are those of the previous
+  // device-buffer solve on this context; the index (groups, chunks, records, camera rows) is then still in the workspace
+  IndexCache& ic = ctx->index_cache;
+  const bool reuse = opt.reuse_index != 0 && !io && ic.valid && ic.V == d.V && ic.N == d.N && ic.m == d.m &&
+                     ic.obs_uv == d.obs_uv && ic.obs_cam == d.obs_cam && ic.rowptr == d.rowptr && ic.kinv == d.kinv &&
+                     ic.fine == (fine ? 1 : 0);
+  ic.valid = false;
   const unsigned idx_epoch = ++ctx->pcg_epoch;
-  launch_index_count(d, fine, temp, temp_bytes, const_cast<IndexStats*>(ist), idx_epoch, st, lc);
-  {
+  if (!reuse) launch_index_count(d, fine, temp, temp_bytes, const_cast<IndexStats*>(ist), idx_epoch, st, lc);
+  if (!reuse) {
     // the counting kernels' last act is to write the statistics into pinned memory: spin on their epoch word (a stream
     // synchronisation costs several times the latency); the stream is only queried to notice a failed launch
     long spins = 0;
@@ -333,15 +340,19 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       }
     }
   }
-  const int nchunks = ist->num_chunks;
-  if ((ist->flags & SFMBA_FLAG_BAD_INDEX) || nchunks < 0 || nchunks > chunk_upper)
+  const int nchunks = reuse ? ic.nchunks : ist->num_chunks;
+  if (!reuse && ((ist->flags & SFMBA_FLAG_BAD_INDEX) || nchunks < 0 || nchunks > chunk_upper))
     return sfm_set_error(ctx, SFMBA_ERR_INVALID_ARG,
                          "pt_rowptr is not a CSR over [0, num_obs] or obs_cam has an index outside [0, num_cams)");
   TileShape ts;
-  ts.max_chunk_len = std::max((int)ist->max_chunk_len, 1);
-  ts.max_group_pts = std::max((int)ist->max_group_pts, 1);
-  ts.max_nseg = std::max((int)ist->max_nseg, 1);
-  ts.max_k = std::max((int)ist->max_k, 1);
+  if (reuse) {
+    ts = ic.ts;
+  } else {
+    ts.max_chunk_len = std::max((int)ist->max_chunk_len, 1);
+    ts.max_group_pts = std::max((int)ist->max_group_pts, 1);
+    ts.max_nseg = std::max((int)ist->max_nseg, 1);
+    ts.max_k = std::max((int)ist->max_k, 1);
+  }
   if ((rc = sfm_setup_chunks(ctx, nchunks, &d)) != 0) return rc;
   if (use_f32 && !(multi && !peer)) {
     if ((rc = carve(ctx, S_XREL, (size_t)std::max(d.N, 1), &d.xrel)) != 0) return rc;
@@ -359,7 +370,9 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   if ((rc = carve(ctx, S_IOTA, (size_t)d.chunk_bound * SEG_CAP, &iota)) != 0) return rc;
   d.rowpos = iota;   // the identity permutation fed to the sort; overwritten with the inverse permutation after it
   const bool ranged = io && io->num_ranges > 1 && io->range_grp[io->num_ranges] == d.G;
-  if (ranged) {
+  if (reuse) {
+    // nothing to build
+  } else if (ranged) {
     // records of a range are built as soon as its observations have arrived
     for (int r = 0; r < io->num_ranges; ++r) {
       cudaStreamWaitEvent(st, io->ev_range_obs[r], 0);
@@ -369,7 +382,15 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     if (io) cudaStreamWaitEvent(st, io->ev_obs, 0);
     launch_chunk_build(d, 0, d.G, st, lc);
   }
-  launch_index_build(d, nchunks, temp, temp_bytes, sort_keys, iota, st, lc);
+  if (!reuse) launch_index_build(d, nchunks, temp, temp_bytes, sort_keys, iota, st, lc);
+  if (!io) {                               // (host-buffer solves index their own staging copies)
+    ic.V = d.V; ic.N = d.N; ic.m = d.m;
+    ic.obs_uv = d.obs_uv; ic.obs_cam = d.obs_cam; ic.rowptr = d.rowptr; ic.kinv = d.kinv;
+    ic.fine = fine ? 1 : 0;
+    ic.nchunks = nchunks;
+    ic.ts = ts;
+    ic.valid = true;
+  }
   pt.end(PH_INDEX, t0);
   if (io) cudaStreamWaitEvent(st, io->ev_params, 0);      // ranged: the cameras; otherwise cameras and points
   if (ranged && adaptive) {

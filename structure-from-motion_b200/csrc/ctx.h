@@ -44,6 +44,14 @@ struct SolveIo {
   cudaEvent_t ev_range_pts[MAX_RANGES] = {};
 };
 
+// what the workspace's index was built from (sfmba_options.reuse_index)
+struct IndexCache {
+  bool valid = false;
+  int V = 0, N = 0, m = 0, fine = 0, nchunks = 0;
+  const void *obs_uv = nullptr, *obs_cam = nullptr, *rowptr = nullptr, *kinv = nullptr;
+  sfmba::TileShape ts;
+};
+
 struct sfmba_ctx {
   int device = 0;
   int world = 1;
@@ -78,6 +86,7 @@ struct sfmba_ctx {
   cudaStream_t own_stream = nullptr;
   SolveIo io;                    // copy stream and events of the host-buffer entry point
   sfmba::DenseStreams dense_streams;   // dense-Cholesky look-ahead (dense.cu)
+  IndexCache index_cache;
   unsigned pcg_epoch = 0;        // id of the current PCG solve (see host_sig)
   int pcg_hint = 0;              // iterations the previous PCG solve needed
   std::vector<cudaEvent_t> timer_events;   // phase-timer events, created once and reused by every solve

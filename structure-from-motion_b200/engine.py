@@ -133,7 +133,7 @@ class Engine:
     # -- options ----------------------------------------------------------------------------------
     def make_options(self, lam=5.0, iterations=3, mode=_capi.MODE_REFERENCE_FIXED, pcg_tol=1e-8, pcg_max_iter=0,
                      dvdc_sign_quirk=True, force_slow_path=False, compute_costs=True, solver=_capi.SOLVER_PCG,
-                     huber_delta=0.0, precond=_capi.PRECOND_JACOBI, matvec_precision=_capi.MATVEC_AUTO):
+                     huber_delta=0.0, precond=_capi.PRECOND_JACOBI, matvec_precision=_capi.MATVEC_AUTO, reuse_index=False):
         opt = _capi.default_options()
         opt.solver = int(solver)
         opt.lambda_ = float(lam)
@@ -147,6 +147,7 @@ class Engine:
         opt.huber_delta = float(huber_delta)
         opt.precond = int(precond)
         opt.matvec_precision = int(matvec_precision)
+        opt.reuse_index = 1 if reuse_index else 0
         return opt
 
     @staticmethod

@@ -278,3 +278,25 @@ def test_precision_modes_against_oracle(engine, oracle):
     assert close(p.cams, cams, PARAM_TOL) and close(p.pts, pts, PARAM_TOL), max_rel(p.cams, cams)
     assert abs(res.final_cost - costs[-1]) <= COST_RTOL * costs[-1]
     assert res.pcg_iterations > 3 * 8                     # really the slow regime
+
+
+def test_reuse_index_gives_identical_bits(engine):
+    """sfmba_options.reuse_index: the second solve of the same device buffers skips the index build; a changed structure is
+    noticed where the library can notice it (sizes, pointers) and rebuilt."""
+    from sfm_b200 import synthetic
+    p, _ = synthetic.make_shape('ladybug')
+    t = engine.to_device(p)
+    c0, x0 = t['cams'].clone(), t['pts'].clone()
+    r1 = engine.ba_solve_device(t, lam=5.0, iterations=2)
+    a1, b1 = t['cams'].clone(), t['pts'].clone()
+    t['cams'].copy_(c0)
+    t['pts'].copy_(x0)
+    r2 = engine.ba_solve_device(t, lam=5.0, iterations=2, reuse_index=True)
+    assert r2.kernel_launches < r1.kernel_launches                      # no counting, sorting or record kernels
+    assert bool((t['cams'] == a1).all()) and bool((t['pts'] == b1).all()) and r1.costs == r2.costs
+    q, _ = synthetic.make_shape('small')                               # another problem: the flag must not reuse anything
+    tq = engine.to_device(q)
+    rq = engine.ba_solve_device(tq, lam=5.0, iterations=2, reuse_index=True)
+    q2, _ = synthetic.make_shape('small')
+    rq2 = engine.ba_solve_host(q2, lam=5.0, iterations=2)
+    assert rq.costs == rq2.costs and np.array_equal(tq['cams'].cpu().numpy(), q2.cams)
