@@ -32,21 +32,28 @@ from sfm_b200 import _capi
 res = eng.ba_solve_host(sh, lam=5.0, iterations=3, matvec_precision=_capi.MATVEC_F64)
 sh2 = synthetic.shard_problem(full, world, rank)
 res2 = eng.ba_solve_host(sh2, lam=5.0, iterations=3)              # default precision (AUTO)
+sh3 = synthetic.shard_problem(full, world, rank)                  # adaptive LM: the cost of every candidate step and the
+res3 = eng.ba_solve_host(sh3, lam=1e-2, iterations=6, mode=_capi.MODE_ADAPTIVE_LM, dvdc_sign_quirk=False,  # model decrease
+                         matvec_precision=_capi.MATVEC_F64)       # are summed over the ranks
 np.savez(os.path.join(%(out)r, 'rank%%d.npz' %% rank), cams=sh.cams, pts=sh.pts, cost=res.final_cost, c0=res.costs[0],
-         cams_auto=sh2.cams, pts_auto=sh2.pts, cost_auto=res2.final_cost)
+         cams_auto=sh2.cams, pts_auto=sh2.pts, cost_auto=res2.final_cost,
+         cams_lm=sh3.cams, cost_lm=res3.final_cost, lam_lm=res3.final_lambda, acc_lm=res3.iterations_accepted)
 eng.close()
 dist.destroy_process_group()
 '''
 
 
-def test_two_rank_solve_matches_single_gpu(engine, tmp_path):
+@pytest.mark.parametrize('peer', ['1', '0'])
+def test_two_rank_solve_matches_single_gpu(engine, tmp_path, peer):
+    """peer = '1': partial sums through the CUDA-IPC peer windows (flag-in-data words inside the solver's kernels);
+    peer = '0' (SFMBA_PEER=0): the NCCL all-reduce fallback."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip('needs 2 GPUs')
     from sfm_b200 import synthetic
     script = tmp_path / 'worker.py'
     script.write_text(WORKER % dict(root=ROOT, out=str(tmp_path)))
-    env = dict(os.environ, MASTER_ADDR='127.0.0.1')
+    env = dict(os.environ, MASTER_ADDR='127.0.0.1', SFMBA_PEER=peer)
     subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2',
                     '--master-addr', '127.0.0.1', '--master-port', '29533', str(script)], check=True, env=env,
                    timeout=600)
@@ -66,6 +73,15 @@ def test_two_rank_solve_matches_single_gpu(engine, tmp_path):
         assert np.max(np.abs(o['cams_auto'] - full_auto.cams)) < 1e-6
         assert abs(float(o['cost_auto']) - res_auto.final_cost) <= 1e-6 * res_auto.final_cost
     assert np.max(np.abs(np.concatenate([o['pts_auto'] for o in out]) - full_auto.pts)) < 1e-6
+    # adaptive LM: same accept / reject decisions, same damping, same answer
+    full_lm, _ = synthetic.make_shape('ladybug')
+    res_lm = engine.ba_solve_host(full_lm, lam=1e-2, iterations=6, mode=_capi.MODE_ADAPTIVE_LM, dvdc_sign_quirk=False,
+                                  matvec_precision=_capi.MATVEC_F64)
+    for o in out:
+        assert int(o['acc_lm']) == res_lm.iterations_accepted
+        assert abs(float(o['lam_lm']) - res_lm.final_lambda) <= 1e-6 * res_lm.final_lambda
+        assert abs(float(o['cost_lm']) - res_lm.final_cost) <= 1e-8 * res_lm.final_cost
+        assert np.max(np.abs(o['cams_lm'] - full_lm.cams)) < 1e-7
 
 
 TIMEOUT_WORKER = r'''
