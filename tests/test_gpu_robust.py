@@ -69,3 +69,42 @@ def test_adaptive_lm_with_huber_rejects_outliers(engine, oracle):
         r, _, _ = oracle.residual_jacobian(p.cams, p.pts, p.obs_cam, p.obs_pt, b, want_jac=False)
         return float(np.sqrt(np.mean(np.sum(r[~bad] ** 2, axis=1))))
     assert clean_rms(prob_h) < 0.7 * clean_rms(prob_l), (clean_rms(prob_h), clean_rms(prob_l))
+
+
+def test_adaptive_lm_gain_ratio_and_damping_match_a_numpy_lm(engine, oracle):
+    """The device-side LM bookkeeping (k_lm_model_decrease, k_lm_decide): predicted decrease delta . J^T r + lambda |delta|^2
+    over cameras AND points, gain ratio, Nielsen's damping update, accept / reject -- replayed in NumPy on the oracle's
+    normal equations with the exact reduced solve.  Same accepted steps, same final damping, same cost."""
+    from sfm_b200 import _capi, synthetic
+    prob, _ = synthetic.make_shape('small')
+    b = prob.obs_uv.T.astype(np.float64)
+    oc, op = prob.obs_cam.astype(np.int64), prob.obs_pt.astype(np.int64)
+    cams, pts = prob.cams.copy(), prob.pts.copy()
+    V, N = cams.shape[0], pts.shape[0]
+    lam, nu, accepted, iters = 1e-2, 2.0, 0, 6
+    for _ in range(iters):
+        ne = oracle.ba_normal_equations(cams, pts, oc, op, b, lam, dvdc_quirk=False)
+        S, g = oracle._reduced_system_dense(ne, oc, op, V)
+        dp = np.linalg.solve(S, g).reshape(V, 7)
+        bt_dp = oracle._segment_sum(np.einsum('mij,mi->mj', ne['W'], dp[oc]), op, N)
+        dx = np.einsum('nij,nj->ni', ne['Dinv'], ne['e_x'] - bt_dp)
+        pred = float(np.sum(dp * ne['e_p']) + np.sum(dx * ne['e_x']) + lam * (np.sum(dp * dp) + np.sum(dx * dx)))
+        c2 = cams + dp
+        c2[:, 3:7] /= np.sqrt(np.sum(np.square(c2[:, 3:7]), axis=1, keepdims=True))
+        p2 = pts + dx
+        new = oracle.ba_cost(c2, p2, oc, op, b)
+        if new < ne['cost']:
+            rho = (ne['cost'] - new) / pred if pred > 0 else 1.0
+            lam *= max(1.0 / 3.0, 1.0 - (2.0 * rho - 1.0) ** 3)
+            nu = 2.0
+            cams, pts = c2, p2
+            accepted += 1
+        else:
+            lam *= nu
+            nu *= 2.0
+    res = engine.ba_solve_host(prob, lam=1e-2, iterations=iters, mode=_capi.MODE_ADAPTIVE_LM, dvdc_sign_quirk=False,
+                               pcg_tol=1e-13)
+    assert res.iterations_accepted == accepted
+    assert abs(res.final_lambda - lam) <= 1e-6 * lam, (res.final_lambda, lam)
+    assert close(prob.cams, cams, 1e-7) and close(prob.pts, pts, 1e-7)
+    assert abs(res.final_cost - oracle.ba_cost(cams, pts, oc, op, b)) <= 1e-8 * res.final_cost
