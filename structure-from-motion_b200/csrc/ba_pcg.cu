@@ -621,22 +621,38 @@ __device__ __forceinline__ void grid_barrier(uint32_t* counter, Scalars* sc) {
 //           them in rank order -- every rank gets bit-identical sums.  No fence, no ticket, no separate flag, no grid-wide
 //           wait: a warp waits only for the seven numbers it needs.  Two parities: a rank can reach exchange s + 2 only
 //           after every peer has finished reading exchange s (they send s + 1 after that).
+// MODE 3, first half: the warp gathers this rank's partial y of ALL its cameras and sends them off (the words of the later
+// cameras are under way while the first ones are being waited for)
+template <int MODE>
+__device__ __forceinline__ void pcg_push_y(const BaDev& d, double2* gat_warp, int rows_f32) {
+  if (MODE != 3) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const PeerWindow& xw = d.xw;
+  const unsigned long long seq64 = *xw.counter() + 1ull;      // advanced by the CTA that finishes the kernel last
+  const unsigned seq = (unsigned)seq64;
+  const int par = (int)(seq64 & 1ull);
+  for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
+    const double y = rows_f32 ? cam_y_gather32(d, cam, lane, gat_warp) : cam_y_gather(d, cam, lane, gat_warp);
+    if (lane < 7) {
+      const size_t k2 = 2 * (7 * (size_t)cam + lane);
+      for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_y) + k2, y, seq);
+    }
+  }
+}
+
+// y of one camera (lanes 0..6).  MODE 1: from this GPU's rows; 2: svec; 3: the words of all ranks, in rank order
 template <int MODE>
 __device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, double2* gat_warp, int rows_f32) {
   if (MODE == 2) return lane < 7 ? d.svec[7 * (size_t)cam + lane] : 0.0;
-  double y = rows_f32 ? cam_y_gather32(d, cam, lane, gat_warp) : cam_y_gather(d, cam, lane, gat_warp);
-  if (MODE == 3) {
-    const PeerWindow& xw = d.xw;
-    const unsigned long long seq64 = *xw.counter() + 1ull;    // advanced by the CTA that finishes the kernel last
-    const unsigned seq = (unsigned)seq64;
-    const int par = (int)(seq64 & 1ull);
-    if (lane < 7) {
-      const size_t k2 = 2 * (7 * (size_t)cam + lane);
-      for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(d.xw, w, par, xw.rank, d.xw.ll_y) + k2, y, seq);
-      double a = 0.0;
-      for (int w = 0; w < xw.world; ++w) a += ll_load(ll_slot(d.xw, xw.rank, par, w, d.xw.ll_y) + k2, seq, xw.timeout_ns, d.sc);
-      y = a;
-    }
+  if (MODE == 1) return rows_f32 ? cam_y_gather32(d, cam, lane, gat_warp) : cam_y_gather(d, cam, lane, gat_warp);
+  double y = 0.0;
+  const PeerWindow& xw = d.xw;
+  const unsigned long long seq64 = *xw.counter() + 1ull;
+  const unsigned seq = (unsigned)seq64;
+  const int par = (int)(seq64 & 1ull);
+  if (lane < 7) {
+    const size_t k2 = 2 * (7 * (size_t)cam + lane);
+    for (int w = 0; w < xw.world; ++w) y += ll_load(ll_slot(xw, xw.rank, par, w, xw.ll_y) + k2, seq, xw.timeout_ns, d.sc);
   }
   return y;
 }
@@ -686,6 +702,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, i
   // scalars of the previous iteration: rewritten only by the CTA that finishes this kernel last
   const double gam_old = sc->rz, alpha_old = sc->alpha, gg = sc->gg;
   const int it_old = sc->pcg_iters;
+  pcg_push_y<MODE>(d, gat[warp], rows_f32);
   double gam = 0.0, del = 0.0;
   for (int cam = gwarp; cam < d.V; cam += nwarps) {
     const size_t k = 7 * (size_t)cam + lane;
@@ -827,6 +844,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_refresh(BaDev d, double tol
   Scalars* sc = d.sc;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const bool l7 = lane < 7;
+  pcg_push_y<MODE>(d, gat[warp], rows_f32);
   double rr = 0.0;
   for (int cam = blockIdx.x * VEC_WARPS + warp; cam < d.V; cam += gridDim.x * VEC_WARPS) {
     const size_t k = 7 * (size_t)cam + lane;
