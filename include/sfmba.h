@@ -72,13 +72,18 @@ typedef enum { SFMBA_SOLVER_PCG = 0, SFMBA_SOLVER_DENSE_CHOLESKY = 1 } sfmba_sol
  * same number of iterations at every damping tried, so JACOBI is the default.  The solution is
  * the same to the PCG tolerance either way.                                                                        */
 typedef enum { SFMBA_PRECOND_JACOBI = 0, SFMBA_PRECOND_SCHUR_JACOBI = 1 } sfmba_precond;
-/* Arithmetic of the implicit-Schur matvec inside PCG (K3).  The linearisation (A, D, the right-hand side, the
- * preconditioner), every PCG vector and every dot product are FP64 in all modes.
- *   F64: per-observation arithmetic in FP64.
- *   F32: per-observation arithmetic in FP32 on group-local coordinates, run sums FP32, everything above them FP64
- *        (BASELINE.json north_star: "FP32 with FP64 accumulation").  The PCG then solves S (1 + O(1e-7)) dp = g: the
- *        step differs from the FP64 one by ~1e-7 cond(Minv S) relative.
- *   AUTO (default): F32 while that bound is harmless, F64 otherwise -- see DESIGN.md section 4 for the rule.          */
+/* Arithmetic of the per-observation work (the name is historical: it started with the PCG matvec K3 and now also governs
+ * the Jacobian arithmetic of the linearisation K1 + K2).  The normal equations (A, D, the right-hand side, the
+ * preconditioner), every PCG vector and dot product, the cost and the LM bookkeeping are FP64 in all modes.
+ *   F64:  everything FP64.
+ *   F32:  the matvec runs in FP32 on group-local coordinates (FP32 run sums, FP64 above them); the linearisation keeps
+ *         the projection, the residual and the cost in FP64 and builds the Jacobian blocks and their products in FP32
+ *         (BASELINE.json north_star: "FP32 with FP64 accumulation").  The reduced system is perturbed by ~1e-7 relative:
+ *         the step moves by ~1e-7 cond(Minv S).  Plain least squares with the A + lambda I preconditioner only.
+ *   AUTO (default): FP32 matvec when pcg_tol >= 1e-8, a solve that needs more than 8 iterations is finished in FP64 from
+ *         a true FP64 residual; FP32 Jacobians from the second LM iteration of a call on while the previous solve was
+ *         that fast, and an iteration whose solve turns out slow is redone from an FP64 linearisation.  Depends on
+ *         nothing but the call itself (bit-reproducible).  DESIGN.md section 4 has the measured distances.            */
 typedef enum { SFMBA_MATVEC_AUTO = 0, SFMBA_MATVEC_F64 = 1, SFMBA_MATVEC_F32 = 2 } sfmba_matvec_precision;
 
 /*

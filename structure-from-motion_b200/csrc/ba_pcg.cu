@@ -670,9 +670,11 @@ __device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, d
 //   phase 1  y (MODE 1: from this GPU's rows; 2: svec, all-reduced by NCCL; 3: the slots of all ranks, in rank order),
 //            w, per-CTA partials of gamma and delta;  grid barrier;  every CTA sums the partials in CTA order
 //   phase 2  the updates above, partial |r|^2, ticket
-template <int MODE>
-__global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, int max_iter, unsigned epoch,
-                                                         int dvdc_quirk, int rows_f32) {
+// WIDE: more cameras than one grid of 1-CTA-per-SM warps (V > 16 x SMs, e.g. the Final shape): compiled for two CTAs per SM
+// (64 registers: the per-warp constants are then read where they are used instead of being fetched ahead)
+template <int MODE, bool WIDE>
+__global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d, double tol, int max_iter, unsigned epoch,
+                                                                        int dvdc_quirk, int rows_f32) {
   __shared__ double red[64];
   __shared__ double2 gat[VEC_WARPS][96];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -685,7 +687,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, i
   for (int b = 0; b < 7; ++b) arow[b] = mrow[b] = 0.0;
 #pragma unroll
   for (int b = 0; b < 16; ++b) trow[b] = 0.0;
-  if (gwarp < d.V) {
+  if (!WIDE && gwarp < d.V) {
     if (l7) {
 #pragma unroll
       for (int b = 0; b < 7; ++b) {
@@ -708,7 +710,7 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, i
     const size_t k = 7 * (size_t)cam + lane;
     const double y = pcg_cam_y<MODE>(d, cam, lane, gat[warp], rows_f32);
     const double zv = l7 ? d.z[k] : 0.0;
-    const double az = cam == gwarp ? row7_dot_reg(arow, zv) : row7_dot(d.ablk + 49 * (size_t)cam, lane, zv);
+    const double az = (!WIDE && cam == gwarp) ? row7_dot_reg(arow, zv) : row7_dot(d.ablk + 49 * (size_t)cam, lane, zv);
     if (l7) {
       const double wv = az - y;
       d.q[k] = wv;
@@ -746,9 +748,9 @@ __global__ void __launch_bounds__(VEC_THREADS) k_pcg_step(BaDev d, double tol, i
       d.r[k] = rn;
       rr += rn * rn;
     }
-    const double zn = cam == gwarp ? row7_dot_reg(mrow, rn) : row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
+    const double zn = (!WIDE && cam == gwarp) ? row7_dot_reg(mrow, rn) : row7_dot(d.minv + 49 * (size_t)cam, lane, rn);
     if (l7) d.z[k] = zn;
-    if (cam == gwarp) warp_camit_row(d, cam, lane, zn, dvdc_quirk, trow); else warp_camit_row(d, cam, lane, zn, dvdc_quirk);
+    if (!WIDE && cam == gwarp) warp_camit_row(d, cam, lane, zn, dvdc_quirk, trow); else warp_camit_row(d, cam, lane, zn, dvdc_quirk);
   }
   rr = block_sum(rr, red);
   if (tid == 0) d.red_b[blockIdx.x] = rr;
@@ -1084,14 +1086,21 @@ void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
 void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk, bool rows_f32,
                      cudaStream_t st, LaunchCounter& lc) {
   const int rf = rows_f32 ? 1 : 0;
-  const int g = vec_grid(d);
   const int q = dvdc_quirk ? 1 : 0;
-  if (mode == 1) {
-    launch_pdl(k_pcg_step<1>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
-  } else if (mode == 2) {
-    launch_pdl(k_pcg_step<2>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+  const int g1 = vec_grid(d);                          // <= SM count
+  const bool wide = (d.V + VEC_WARPS - 1) / VEC_WARPS > g1;      // more cameras than that grid has warps
+  if (!wide) {
+    if (mode == 1) launch_pdl(k_pcg_step<1, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    else if (mode == 2) launch_pdl(k_pcg_step<2, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    else launch_pdl(k_pcg_step<3, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
   } else {
-    launch_pdl(k_pcg_step<3>, dim3(g), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    // two CTAs per SM are resident at 64 registers: twice the warps, still every CTA of the grid on the chip (the kernel
+    // holds a grid-wide barrier)
+    int g2 = (d.V + VEC_WARPS - 1) / VEC_WARPS;
+    if (g2 > 2 * g1) g2 = 2 * g1;
+    if (mode == 1) launch_pdl(k_pcg_step<1, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    else if (mode == 2) launch_pdl(k_pcg_step<2, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    else launch_pdl(k_pcg_step<3, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
   }
   lc.launches += 1;
 }
