@@ -183,7 +183,6 @@ struct BaDev {
   double* gvec;                       // [7V] right-hand side
   double* red_a;                      // [<= 1024] per-block partials of the PCG dot products
   double* red_b;                      // [<= 2048]
-  double* cam_rr;                     // [V] |g_i|^2 per camera (k_cam_finish)
   double* cams_backup;                // [V][7]  adaptive mode
   double* pts_backup;                 // [N][3]
   Scalars* sc;

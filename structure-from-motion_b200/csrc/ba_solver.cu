@@ -59,7 +59,7 @@ namespace {
 
 enum Slot {
   S_SCALARS = 0, S_CAMTAB, S_GRP_COST, S_GRP_EXV, S_GRP_PT, S_GRP_NCHUNK, S_GRP_K, S_GRP_CHUNK, S_GRP_META, S_DINV, S_VJ, S_UBUF, S_CAM_ACC, S_ABLK, S_MINV,
-  S_CAMIT, S_CAMIT32, S_UBUF32, S_PART12F, S_PART64F, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAM_RR, S_CAMS_BAK, S_PTS_BAK,
+  S_CAMIT, S_CAMIT32, S_UBUF32, S_PART12F, S_PART64F, S_XREL, S_DINV32, S_SEGST, S_SVEC, S_X, S_R, S_Z, S_P, S_Q, S_S, S_GVEC, S_RED_A, S_RED_B, S_CAMS_BAK, S_PTS_BAK,
   S_CHUNK_INFO, S_REC_B, S_REC_IX, S_REC_W, S_SEG_CAM, S_SEG_LANE0, S_CAMROW_PTR, S_CAMROW_IDX, S_PART64, S_PART12,
   S_TEMP, S_SORT_KEYS, S_IOTA, S_DENSE, S_DENSE_LINV, S_DENSE_VEC, S_COUNT
 };
@@ -126,7 +126,6 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
     CARVE(S_GVEC, 7 * V, gvec);
     CARVE(S_RED_A, 1024, red_a);
     CARVE(S_RED_B, 2048, red_b);
-    CARVE(S_CAM_RR, V, cam_rr);
     CARVE(S_CAMS_BAK, 7 * V, cams_backup);
     CARVE(S_PTS_BAK, 3 * N, pts_backup);
     CARVE(S_CAMROW_PTR, V + 1, camrow_ptr);
