@@ -442,7 +442,12 @@ def run_ours(args):
         mvk = 'k_matvec32' if res.matvec_precision == 2 else 'k_matvec'
         k3_name = 'K3 implicit-Schur matvec = %s + k_pcg_step (one PCG iteration, rank 0 shard)' % mvk
         k3_traffic, k3_src = ncu_traffic(mvk, args.shape, args.scale, world)
-        k12_traffic, k12_src = ncu_traffic('k_linearize', args.shape, args.scale, world)
+        t64, k12_src = ncu_traffic('k_linearize', args.shape, args.scale, world)
+        t32, _ = ncu_traffic('k_linearize32', args.shape, args.scale, world)
+        n64, n32 = prof['linearize'][1], prof['linearize32'][1]
+        k12_traffic = None                           # mean DRAM bytes per launch over the step's FP64 and FP32-Jacobian launches
+        if (n64 == 0 or t64 is not None) and (n32 == 0 or t32 is not None) and n64 + n32 > 0:
+            k12_traffic = ((t64 or 0.0) * n64 + (t32 or 0.0) * n32) / (n64 + n32)
         k3_gbs = k3_bytes / (k3_ms * 1e-3) / 1e9 if k3_ms > 0 else 0.0
         lin_ms = prof['linearize'][0] + prof['linearize32'][0]          # k_linearize (FP64) and k_linearize32 launches
         lin_n = prof['linearize'][1] + prof['linearize32'][1]

@@ -27,14 +27,14 @@ def main():
     acc = {}
     for r in rows[2:]:
         name = r[ix['Kernel Name']]
-        key = next((k for k in ('k_matvec32', 'k_matvec', 'k_linearize', 'k_pcg_step') if k in name), None)
+        key = next((k for k in ('k_matvec32', 'k_matvec', 'k_linearize32', 'k_linearize', 'k_pcg_step') if k in name), None)
         if key is None:
             continue
         tot = 0.0
         for m in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
             tot += float(r[ix[m]].replace(',', '')) * scale_of[units[ix[m]]]
         dur = float(r[ix['gpu__time_duration.sum']].replace(',', ''))
-        if key in ('k_matvec32', 'k_matvec') and dur < 40.0:
+        if (key in ('k_matvec32', 'k_matvec') and dur < 40.0) or (key == 'k_pcg_step' and dur < 10.0):
             continue                                    # a launch past convergence (exits at its first instruction)
         acc.setdefault(key, []).append(tot)
     import bench
