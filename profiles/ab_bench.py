@@ -3,7 +3,7 @@
 
     python profiles/ab_bench.py [--steps 10] [--extra "--shape venice"] name=path/to/lib.so ...
 
-`name=default` stands for the in-tree build.  Rows go to stdout as JSON lines (kept under profiles/ when quoted)."""
+`name=default` stands for the in-tree build; `name=lib.so:VAR=VALUE[:VAR=VALUE]` also sets environment switches.  Rows go to stdout as JSON lines (kept under profiles/ when quoted)."""
 import json
 import os
 import subprocess
@@ -29,6 +29,9 @@ def main():
     for _ in range(reps):
         for name, path in libs:
             env = dict(os.environ)
+            path, *sets = path.split(':')
+            for kv in sets:
+                env[kv.split('=', 1)[0]] = kv.split('=', 1)[1]
             if path != 'default':
                 env['SFMBA_LIB'] = os.path.join(ROOT, path)
             r = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--no-cpu', '--no-extras', '--steps', steps, '--warmup', '3'] + extra,

@@ -357,6 +357,9 @@ __global__ void __launch_bounds__(RUN_LANES, MV32_MINB) k_matvec32(BaDev d, Mv32
     __syncthreads();
     // one thread per (segment, component): its runs are added in lane order; consecutive threads write consecutive
     // floats of a row (the per-camera sums over the rows are FP64, cam_y_gather32)
+    // -- the padding floats 12..15 are written too (zeros, by the threads of components 8..11): a row is two whole
+    // 32-byte sectors, so L2 never holds a partially written sector that the reader's load would first have to complete
+    // from DRAM
     for (int i = tid; i < ci.nseg * MV_ACC; i += RUN_LANES) {
       const int s = i / MV_ACC, e = i - s * MV_ACC;
       const int ra = srun[s], rb = srun[s + 1];
@@ -371,7 +374,9 @@ __global__ void __launch_bounds__(RUN_LANES, MV32_MINB) k_matvec32(BaDev d, Mv32
         a += v2;
         a += v3;
       }
-      d.part12f[(size_t)rpos[s] * MV_ROW32 + e] = a;
+      float* row = d.part12f + (size_t)rpos[s] * MV_ROW32;
+      row[e] = a;
+      if (e >= 8) row[e + 4] = 0.f;
     }
     __syncthreads();
   }

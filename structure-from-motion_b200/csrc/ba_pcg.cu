@@ -404,29 +404,35 @@ __global__ void __launch_bounds__(RUN_LANES, 4) k_matvec(BaDev d, MvShape sh, in
 
 // y_i of a camera from the 12 sums over its segment rows (component c in lane c): y_C = -R s, y_q[j] = <Q_j, T>.
 // Returns y in lanes 0..6 (0 elsewhere).
-__device__ __forceinline__ double cam_y_from_sums(const BaDev& d, int cam, int lane, double tsum) {
+__device__ __forceinline__ double cam_y_from_sums(const double* t, int lane, double tsum) {
   double T[MV_ACC];
 #pragma unroll
   for (int k = 0; k < MV_ACC; ++k) T[k] = __shfl_sync(0xffffffffu, tsum, k);
   double y = 0.0;
   if (lane < 7) {
-    const double* t = d.camtab + (size_t)CAMTAB_STRIDE * cam;
     if (lane < 3) {
       y = -(t[3 * lane] * T[9] + t[3 * lane + 1] * T[10] + t[3 * lane + 2] * T[11]);
     } else {
       const double q2[4] = {2.0 * t[12], 2.0 * t[13], 2.0 * t[14], 2.0 * t[15]};
       double Q[4][9];
       quat_dRt(q2, Q);
+      // all four products with constant indices and a select at the end: indexing Q by the lane would put the table in
+      // local memory (288 bytes per thread, stored and re-read through L1 / L2 -- it was a fifth of k_pcg_step)
+      double yq[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (j == lane - 3) {
+        double a = 0.0;
 #pragma unroll
-          for (int k = 0; k < 9; ++k) y += Q[j][k] * T[k];
-        }
+        for (int k = 0; k < 9; ++k) a += Q[j][k] * T[k];
+        yq[j] = a;
       }
+      y = lane == 3 ? yq[0] : (lane == 4 ? yq[1] : (lane == 5 ? yq[2] : yq[3]));
     }
   }
   return y;
+}
+__device__ __forceinline__ double cam_y_from_sums(const BaDev& d, int cam, int lane, double tsum) {
+  return cam_y_from_sums(d.camtab + (size_t)CAMTAB_STRIDE * cam, lane, tsum);
 }
 
 // y_i from the camera's segment rows.  The rows of one camera are contiguous in part12 (camrow_ptr), so the whole warp
@@ -434,8 +440,7 @@ __device__ __forceinline__ double cam_y_from_sums(const BaDev& d, int cam, int l
 // pair (2 t + l) mod 6 of some row -- three accumulators per lane (t mod 3), six loads in flight, then one fixed-order
 // combination of the 96 lane sums through shared memory (`buf`: 96 double2 per warp).
 // y_C = -R s, y_q[j] = <Q_j, T>.  Returns y in lanes 0..6 (0 elsewhere).
-__device__ __forceinline__ double cam_y_gather(const BaDev& d, int cam, int lane, double2* buf) {
-  const int r0 = d.camrow_ptr[cam], r1 = d.camrow_ptr[cam + 1];
+__device__ __forceinline__ double cam_y_gather(const BaDev& d, int r0, int r1, const double* t, int lane, double2* buf) {
   const double2* src = reinterpret_cast<const double2*>(d.part12 + (size_t)r0 * MV_ACC);
   const int n2 = (r1 - r0) * (MV_ACC / 2);
   double2 a0 = make_double2(0.0, 0.0), a1 = a0, a2 = a0;
@@ -472,7 +477,10 @@ __device__ __forceinline__ double cam_y_gather(const BaDev& d, int cam, int lane
       }
     }
   }
-  return cam_y_from_sums(d, cam, lane, tsum);
+  return cam_y_from_sums(t, lane, tsum);
+}
+__device__ __forceinline__ double cam_y_gather(const BaDev& d, int cam, int lane, double2* buf) {
+  return cam_y_gather(d, d.camrow_ptr[cam], d.camrow_ptr[cam + 1], d.camtab + (size_t)CAMTAB_STRIDE * cam, lane, buf);
 }
 
 // The same for the FP32 segment rows the FP32 matvec writes (MV_ROW32 = 16 floats = four 16-byte words per row, the
@@ -509,6 +517,68 @@ __device__ __forceinline__ double cam_y_gather32(const BaDev& d, int cam, int la
     for (int l = 0; l < 8; ++l) tsum += (double)f[(4 * l + q) * 4 + j];
   }
   return cam_y_from_sums(d, cam, lane, tsum);
+}
+
+#ifdef SFMBA_STEP_TRACE
+// profiling build only (profiles/step_trace.py): thread 0 of every CTA stamps the phases of the last k_pcg_step launch
+__device__ unsigned long long g_step_trace[2][256][16];
+#define STEP_STAMP(i)                                                    \
+  do {                                                                   \
+    if (threadIdx.x == 0 && blockIdx.x < 256) {                          \
+      g_step_trace[0][blockIdx.x][i] = global_timer_ns();                \
+      g_step_trace[1][blockIdx.x][i] = (unsigned long long)clock64();    \
+    }                                                                    \
+  } while (0)
+#else
+#define STEP_STAMP(i) do {} while (0)
+#endif
+
+// FP32 rows again, for a warp that owns ONE camera and has registers to spare (k_pcg_step1): three lanes per row (the
+// padding word is not read), ten rows per warp-load, GATHER_DEPTH loads of a lane in flight -- the gather is a chain of
+// L2 round trips, and this makes it a quarter as long.  FP32 sums inside a lane (two accumulators), FP64 across lanes in
+// a fixed order.  Row range and camera-table row come from the caller (fetched before the wait on the matvec).
+constexpr int GATHER_DEPTH = 16;
+__device__ __forceinline__ double cam_y_gather32_deep(const BaDev& d, int r0, int r1, const double* t, int lane,
+                                                      double2* buf) {
+  const int nrow = r1 - r0;
+  const int sub = lane / 3, word = lane - 3 * sub;
+  const float4* mine = reinterpret_cast<const float4*>(d.part12f + (size_t)r0 * MV_ROW32) + 4 * sub + word;
+  const int lim = lane < 30 ? nrow - sub : 0;                // this lane reads rows sub + 10 j while 10 j < lim
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 a0 = zero, a1 = zero;
+  auto add = [](float4& a, const float4 v) { a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w; };
+  for (int base = 0; base < nrow; base += 10 * GATHER_DEPTH) {
+    float4 v[GATHER_DEPTH];
+#pragma unroll
+    for (int u = 0; u < GATHER_DEPTH; ++u) v[u] = base + 10 * u < lim ? __ldcg(mine + 4 * (base + 10 * u)) : zero;
+#pragma unroll
+    for (int u = 0; u < GATHER_DEPTH; u += 2) {
+      add(a0, v[u]);
+      add(a1, v[u + 1]);
+    }
+#ifdef SFMBA_STEP_TRACE
+    if (base == 0 && threadIdx.x == 0 && blockIdx.x < 256) {
+      g_step_trace[1][blockIdx.x][13] = a0.x + a1.x != 12345.f ? (unsigned long long)clock64() : 0ull;
+      g_step_trace[1][blockIdx.x][12] = (unsigned long long)nrow;
+    }
+#endif
+  }
+  add(a0, a1);
+  float4* bf = reinterpret_cast<float4*>(buf);               // [32] float4
+  __syncwarp();
+  bf[lane] = a0;
+  __syncwarp();
+  double tsum = 0.0;
+  if (lane < MV_ACC) {                                     // lane = component: word lane / 4 lives in lanes = it mod 3
+    const int q = lane >> 2, j = lane & 3;
+    const float* f = reinterpret_cast<const float*>(bf);
+#pragma unroll
+    for (int g = 0; g < 10; ++g) tsum += (double)f[(3 * g + q) * 4 + j];
+  }
+#ifdef SFMBA_STEP_TRACE
+  if (threadIdx.x == 0 && blockIdx.x < 256) g_step_trace[1][blockIdx.x][14] = tsum != 12345.0 ? (unsigned long long)clock64() : 0ull;
+#endif
+  return cam_y_from_sums(t, lane, tsum);
 }
 
 constexpr int VEC_THREADS = 512;                 // vector kernels: one warp per camera
@@ -680,6 +750,7 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int gwarp = blockIdx.x * VEC_WARPS + warp, nwarps = gridDim.x * VEC_WARPS;
   const bool l7 = lane < 7;
+  STEP_STAMP(0);
   // What does not change during the solve is fetched before the wait on the matvec: the lane's rows of A and Minv and the
   // camera-table row of the warp's first camera (its only one unless V exceeds the grid's warps)
   double arow[7], mrow[7], trow[16];
@@ -698,13 +769,16 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
 #pragma unroll
     for (int b = 0; b < 16; ++b) trow[b] = d.camtab[(size_t)CAMTAB_STRIDE * gwarp + b];
   }
+  STEP_STAMP(1);
   pdl_wait();
+  STEP_STAMP(2);
   Scalars* sc = d.sc;
   if (sc->pcg_done) return;
   // scalars of the previous iteration: rewritten only by the CTA that finishes this kernel last
   const double gam_old = sc->rz, alpha_old = sc->alpha, gg = sc->gg;
   const int it_old = sc->pcg_iters;
   pcg_push_y<MODE>(d, gat[warp], rows_f32);
+  STEP_STAMP(3);
   double gam = 0.0, del = 0.0;
   for (int cam = gwarp; cam < d.V; cam += nwarps) {
     const size_t k = 7 * (size_t)cam + lane;
@@ -718,12 +792,15 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
       del += zv * wv;
     }
   }
+  STEP_STAMP(4);
   block_sum2(gam, del, red);
+  STEP_STAMP(5);
   if (tid == 0) {
     d.red_a[2 * blockIdx.x] = gam;
     d.red_a[2 * blockIdx.x + 1] = del;
   }
   grid_barrier(&sc->bar_a, sc);
+  STEP_STAMP(6);
   pdl_trigger();                                   // every CTA of this grid is resident: the next kernel may queue up
   gam = del = 0.0;
   for (int b = tid; b < (int)gridDim.x; b += blockDim.x) {
@@ -734,6 +811,7 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
   const double beta = it_old == 0 ? 0.0 : gam / gam_old;
   const double den = it_old == 0 ? del : del - beta * gam / alpha_old;
   const double alpha = gam / den;
+  STEP_STAMP(7);
   double rr = 0.0;
   for (int cam = gwarp; cam < d.V; cam += nwarps) {
     const size_t k = 7 * (size_t)cam + lane;
@@ -752,9 +830,13 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
     if (l7) d.z[k] = zn;
     if (!WIDE && cam == gwarp) warp_camit_row(d, cam, lane, zn, dvdc_quirk, trow); else warp_camit_row(d, cam, lane, zn, dvdc_quirk);
   }
+  STEP_STAMP(8);
   rr = block_sum(rr, red);
   if (tid == 0) d.red_b[blockIdx.x] = rr;
-  if (!last_cta_arrives(&sc->ticket_b)) return;
+  STEP_STAMP(9);
+  const bool last_cta = last_cta_arrives(&sc->ticket_b);
+  STEP_STAMP(10);
+  if (!last_cta) return;
   // ---- the last CTA: scalars of the iteration
   rr = all_blocks_sum(d.red_b, 1, 0, red);
   if (tid != 0) return;
@@ -789,6 +871,178 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
   if (d.host_sig)
     *(volatile unsigned long long*)d.host_sig =
         ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
+  STEP_STAMP(11);
+}
+
+// The same iteration for the usual case of one camera per warp (V <= 16 x the grid; MODE 1 or 3), arranged so that as
+// little as possible sits on the chain of dependent memory round trips that this latency-bound kernel is:
+//   * before the wait on the matvec: the camera's row range, its blocks A and Minv and its camera-table row (shared
+//     memory, so no registers are held through the gather);
+//   * right after it: the camera's entries of z, r, p, s, x and the scalars -- in flight during the gather;
+//   * the gather of the FP32 rows with GATHER_DEPTH loads per lane in flight (cam_y_gather32_deep);
+//   * the updates use the registers loaded above: no loads after the grid-wide sum.
+// (Tried and dropped: the grid-wide sum as a flag-in-data exchange, every CTA polling every CTA's tagged partials -- 12 500
+// polling threads on a few L2 lines delayed the stores they were waiting for: 5 us from the last partial to alpha instead
+// of 2.6 us with the arrival counter.  Prefetches before the wait to warm the address translations: no gain.)
+// The arithmetic (and the order of every sum) is that of k_pcg_step, except inside cam_y_gather32_deep.
+template <int MODE>
+__global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double tol, int max_iter, unsigned epoch,
+                                                              int dvdc_quirk, int rows_f32) {
+  __shared__ double red[64];
+  __shared__ double2 gat[VEC_WARPS][96];
+  __shared__ double s_a[VEC_WARPS][49], s_m[VEC_WARPS][49], s_t[VEC_WARPS][16];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int cam = blockIdx.x * VEC_WARPS + warp;
+  const bool has = cam < d.V, l7 = has && lane < 7;
+  const size_t k = 7 * (size_t)(has ? cam : 0) + (lane < 7 ? lane : 0);
+  STEP_STAMP(0);
+  int r0 = 0, r1 = 0;
+  if (has) {
+    r0 = d.camrow_ptr[cam];
+    r1 = d.camrow_ptr[cam + 1];
+    const double* A = d.ablk + 49 * (size_t)cam;
+    const double* M = d.minv + 49 * (size_t)cam;
+    s_a[warp][lane] = A[lane];
+    s_m[warp][lane] = M[lane];
+    if (lane < 17) {
+      s_a[warp][32 + lane] = A[32 + lane];
+      s_m[warp][32 + lane] = M[32 + lane];
+    }
+    if (lane < 16) s_t[warp][lane] = d.camtab[(size_t)CAMTAB_STRIDE * cam + lane];
+  }
+  __syncwarp();
+  STEP_STAMP(1);
+  pdl_wait();
+  STEP_STAMP(2);
+  Scalars* sc = d.sc;
+  // the previous iteration's state of this camera and the scalars (rewritten only by the CTA that finishes this kernel
+  // last): issued here, needed after the gather
+  double zv = 0.0, rv = 0.0, pv = 0.0, sv = 0.0, xv = 0.0;
+  if (l7) {
+    zv = __ldcg(d.z + k);
+    rv = __ldcg(d.r + k);
+    pv = __ldcg(d.p + k);
+    sv = __ldcg(d.s + k);
+    xv = __ldcg(d.x + k);
+  }
+  const int done_before = *(volatile int32_t*)&sc->pcg_done;
+  const double gam_old = sc->rz, alpha_old = sc->alpha, gg = sc->gg;
+  const int it_old = sc->pcg_iters;
+  unsigned long long xseq = 0ull;
+  if (MODE == 3) xseq = *d.xw.counter() + 1ull;               // advanced by the CTA that finishes the kernel last
+  double y = 0.0;
+  if (has)
+    y = rows_f32 ? cam_y_gather32_deep(d, r0, r1, s_t[warp], lane, gat[warp])
+                 : cam_y_gather(d, r0, r1, s_t[warp], lane, gat[warp]);
+  if (done_before) return;                                   // (the same in every thread of the grid)
+  STEP_STAMP(3);
+  if (MODE == 3 && l7) {
+    // this rank's partial y into the camera's words of EVERY rank's window, then the words of all ranks, in rank order
+    const PeerWindow& xw = d.xw;
+    const unsigned seq = (unsigned)xseq;
+    const int par = (int)(xseq & 1ull);
+    const size_t k2 = 2 * k;
+    for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_y) + k2, y, seq);
+    y = 0.0;
+    for (int w = 0; w < xw.world; ++w) y += ll_load(ll_slot(xw, xw.rank, par, w, xw.ll_y) + k2, seq, xw.timeout_ns, sc);
+  }
+  double gam = 0.0, del = 0.0, wv = 0.0;
+  {
+    double az = 0.0;
+#pragma unroll
+    for (int b = 0; b < 7; ++b) {
+      const double zb = __shfl_sync(0xffffffffu, zv, b);
+      if (lane < 7) az += s_a[warp][lane * 7 + b] * zb;
+    }
+    if (l7) {
+      wv = az - y;
+      gam = rv * zv;
+      del = zv * wv;
+    }
+  }
+  STEP_STAMP(4);
+  block_sum2(gam, del, red);
+  STEP_STAMP(5);
+  if (tid == 0) {
+    d.red_a[2 * blockIdx.x] = gam;
+    d.red_a[2 * blockIdx.x + 1] = del;
+  }
+  grid_barrier(&sc->bar_a, sc);
+  STEP_STAMP(6);
+  pdl_trigger();                                   // every CTA of this grid is resident: the next kernel may queue up
+  gam = del = 0.0;
+  if (tid < (int)gridDim.x) {
+    gam = __ldcg(d.red_a + 2 * tid);
+    del = __ldcg(d.red_a + 2 * tid + 1);
+  }
+  block_sum2(gam, del, red);                       // every CTA sums the partials in CTA order: identical scalars
+  const double beta = it_old == 0 ? 0.0 : gam / gam_old;
+  const double den = it_old == 0 ? del : del - beta * gam / alpha_old;
+  const double alpha = gam / den;
+  STEP_STAMP(7);
+  double rr = 0.0, rn = 0.0;
+  if (l7) {
+    const double pn = zv + beta * pv;
+    const double sn = wv + beta * sv;
+    d.p[k] = pn;
+    d.s[k] = sn;
+    d.x[k] = xv + alpha * pn;
+    rn = rv - alpha * sn;
+    d.r[k] = rn;
+    rr = rn * rn;
+  }
+  if (has) {
+    double zn = 0.0;
+#pragma unroll
+    for (int b = 0; b < 7; ++b) {
+      const double rb = __shfl_sync(0xffffffffu, rn, b);
+      if (lane < 7) zn += s_m[warp][lane * 7 + b] * rb;
+    }
+    if (l7) d.z[k] = zn;
+    warp_camit_row(d, cam, lane, zn, dvdc_quirk, s_t[warp]);
+  }
+  STEP_STAMP(8);
+  rr = block_sum(rr, red);
+  if (tid == 0) d.red_b[blockIdx.x] = rr;
+  STEP_STAMP(9);
+  const bool last_cta = last_cta_arrives(&sc->ticket_b);
+  STEP_STAMP(10);
+  if (!last_cta) return;
+  // ---- the last CTA: scalars of the iteration
+  rr = all_blocks_sum(d.red_b, 1, 0, red);
+  if (tid != 0) return;
+  const int it = it_old + 1;
+  int done = 0;
+  uint32_t newflags = 0;
+  if (!(den > 0.0) || !(gam > 0.0) || !(rr == rr)) {      // breakdown (S is not positive definite) or NaN
+    newflags |= FLAG_NONFINITE;
+    done = 1;
+  }
+  if (rr <= tol * tol * gg) done = 1;
+  if (*(volatile uint32_t*)&sc->flags & FLAG_PEER_TIMEOUT) done = 1;
+  if (!done && it >= max_iter) {
+    newflags |= FLAG_PCG_MAXITER;
+    done = 1;
+  }
+  if (MODE == 3) *d.xw.counter() += 1ull;                   // this exchange is finished on this rank
+  sc->bar_a = 0u;
+  sc->pcg_iters_total += 1;
+  sc->pcg_iters = it;
+  if (newflags) atomicOr(&sc->flags, newflags);
+  sc->pq = del;
+  sc->alpha = alpha;
+  sc->beta = beta;
+  if (it_old < PCG_UBUF) {
+    sc->alpha_hist[it_old] = alpha;
+    sc->beta_hist[it_old] = beta;
+  }
+  sc->rz = gam;
+  sc->rr = rr;
+  sc->pcg_done = done;
+  if (d.host_sig)
+    *(volatile unsigned long long*)d.host_sig =
+        ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
+  STEP_STAMP(11);
 }
 
 // x = 0, p = s = 0, r = g, z = Minv g and its camit rows; the CTA that finishes last sets |g|^2 and the iteration state
@@ -1088,8 +1342,13 @@ void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigne
   const int rf = rows_f32 ? 1 : 0;
   const int q = dvdc_quirk ? 1 : 0;
   const int g1 = vec_grid(d);                          // <= SM count
+  static const bool step1_enabled = !(getenv("SFMBA_STEP1") && atoi(getenv("SFMBA_STEP1")) == 0);   // (A/B switch)
   const bool wide = (d.V + VEC_WARPS - 1) / VEC_WARPS > g1;      // more cameras than that grid has warps
-  if (!wide) {
+  if (!wide && mode != 2 && step1_enabled) {
+    // one camera per warp: the latency-trimmed kernel
+    if (mode == 1) launch_pdl(k_pcg_step1<1>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    else launch_pdl(k_pcg_step1<3>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+  } else if (!wide) {
     if (mode == 1) launch_pdl(k_pcg_step<1, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
     else if (mode == 2) launch_pdl(k_pcg_step<2, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
     else launch_pdl(k_pcg_step<3, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
@@ -1189,3 +1448,9 @@ void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream
 }
 
 }  // namespace sfmba
+
+#ifdef SFMBA_STEP_TRACE
+extern "C" __attribute__((visibility("default"))) int sfmba_debug_step_trace(unsigned long long* out_host) {
+  return (int)cudaMemcpyFromSymbol(out_host, sfmba::g_step_trace, sizeof(sfmba::g_step_trace));
+}
+#endif

@@ -599,52 +599,63 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
     // element e of the row (compile-time e) in every lane
     auto get = [&](int e) { return e < 32 ? __shfl_sync(0xffffffffu, a0, e) : __shfl_sync(0xffffffffu, a1, e - 32); };
     // S_ii = A + lambda I - (Schur-diagonal sums), packed upper triangle k(a, b) = a (15 - a) / 2 + b - a, a <= b
+    // (static_for: every index below is a compile-time constant, so S and L live in registers)
     double S[28];
-#pragma unroll
-    for (int k = 0; k < 28; ++k) {
+    static_for<0, 28>([&](auto K) {
+      constexpr int k = K;
       S[k] = get(k);
       if (schur) S[k] -= get(28 + k);
-    }
-#pragma unroll
-    for (int a = 0; a < 7; ++a) S[a * (15 - a) / 2] += lam;
+    });
+    static_for<0, 7>([&](auto A) {
+      constexpr int a = A;
+      S[a * (15 - a) / 2] += lam;
+    });
     // Cholesky S = L L^T, L[i][j] (j <= i) stored at S-index k(j, i): L overwrites the packed triangle column by column
     bool ok = true;
     double L[28];
-#pragma unroll
-    for (int j = 0; j < 7; ++j) {
+    static_for<0, 7>([&](auto J) {
+      constexpr int j = J;
       double dj = S[j * (15 - j) / 2];
-#pragma unroll
-      for (int k = 0; k < j; ++k) dj -= L[k * (15 - k) / 2 + j - k] * L[k * (15 - k) / 2 + j - k];
+      static_for<0, j>([&](auto K) {
+        constexpr int k = K;
+        dj -= L[k * (15 - k) / 2 + j - k] * L[k * (15 - k) / 2 + j - k];
+      });
       if (!(dj > 0.0)) ok = false;
       const double ljj = sqrt(dj);
       const double inv = 1.0 / ljj;
       L[j * (15 - j) / 2] = ljj;
-#pragma unroll
-      for (int i = j + 1; i < 7; ++i) {
+      static_for<j + 1, 7>([&](auto I) {
+        constexpr int i = I;
         double v = S[j * (15 - j) / 2 + i - j];
-#pragma unroll
-        for (int k = 0; k < j; ++k) v -= L[k * (15 - k) / 2 + i - k] * L[k * (15 - k) / 2 + j - k];
+        static_for<0, j>([&](auto K) {
+          constexpr int k = K;
+          v -= L[k * (15 - k) / 2 + i - k] * L[k * (15 - k) / 2 + j - k];
+        });
         L[j * (15 - j) / 2 + i - j] = v * inv;          // L[i][j]
-      }
-    }
+      });
+    });
     if (!ok && lane == 0) atomicOr(&sc->flags, FLAG_SINGULAR);
     // lane c < 7: column c of S^-1 (L y = e_c, L^T x = y)
     const int c = lane < 7 ? lane : 0;
     double y[7], x[7];
-#pragma unroll
-    for (int i = 0; i < 7; ++i) {
+    static_for<0, 7>([&](auto I) {
+      constexpr int i = I;
       double v = (i == c) ? 1.0 : 0.0;
-#pragma unroll
-      for (int j = 0; j < i; ++j) v -= L[j * (15 - j) / 2 + i - j] * y[j];
+      static_for<0, i>([&](auto J) {
+        constexpr int j = J;
+        v -= L[j * (15 - j) / 2 + i - j] * y[j];
+      });
       y[i] = v / L[i * (15 - i) / 2];
-    }
-#pragma unroll
-    for (int i = 6; i >= 0; --i) {
+    });
+    static_for<0, 7>([&](auto R) {
+      constexpr int i = 6 - R;
       double v = y[i];
-#pragma unroll
-      for (int j = i + 1; j < 7; ++j) v -= L[i * (15 - i) / 2 + j - i] * x[j];
+      static_for<i + 1, 7>([&](auto J) {
+        constexpr int j = J;
+        v -= L[i * (15 - i) / 2 + j - i] * x[j];
+      });
       x[i] = v / L[i * (15 - i) / 2];
-    }
+    });
     // right-hand side g and z = Minv g (row c of the symmetric inverse is x)
     const int g0 = schur ? 56 : 28;
     double g[7], zc = 0.0;

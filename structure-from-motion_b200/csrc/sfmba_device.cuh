@@ -7,9 +7,21 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 #include "ba_internal.h"
 
 namespace sfmba {
+
+// f(integral_constant<int, I>) for I = BEGIN .. END - 1: loop bodies whose array indices MUST be compile-time constants
+// (small register arrays; `#pragma unroll` is only a request, and a loop nest it declines puts the array in local memory)
+template <int BEGIN, int END, typename F>
+__device__ __forceinline__ void static_for(F&& f) {
+  if constexpr (BEGIN < END) {
+    f(std::integral_constant<int, BEGIN>{});
+    static_for<BEGIN + 1, END>(f);
+  }
+}
 
 constexpr uint32_t FLAG_QW_NEAR_ZERO = 1u;
 constexpr uint32_t FLAG_DEPTH_ZERO = 2u;
