@@ -244,8 +244,8 @@ void launch_camsum64_peer(const BaDev& d, int cost_slot, cudaStream_t st, Launch
 void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc);     // ablk, minv, gvec
 // PCG solver: camera sums (this GPU's rows, or all ranks' through the peer windows), blocks and the PCG start in one
 // kernel per camera
-void launch_cam_finish(const BaDev& d, bool peer, bool rows_f32, int cost_slot, unsigned epoch, bool dvdc_quirk,
-                       cudaStream_t st, LaunchCounter& lc);
+void launch_cam_finish(const BaDev& d, bool peer, bool rows_f32, bool sum_cost, int cost_slot, unsigned epoch,
+                       bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 
 // ---- PCG (ba_pcg.cu) -----------------------------------------------------------------------------
 void launch_pcg_init(const BaDev& d, unsigned epoch, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);

@@ -11,23 +11,13 @@
 
 namespace sfmba {
 
-// camtab row = R(q) row-major, C, qj = R->q (the Jacobian's quaternion, campose_processor.py:464)
+// camtab row = R(q) row-major, C, qj = R->q (cam_table_row, tile.cuh)
 __global__ void k_cam_prepare(BaDev d) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= d.V) return;
   const double* cam = d.cams + 7 * (size_t)c;
-  double q[4] = {cam[3], cam[4], cam[5], cam[6]};
-  double R[9], qj[4];
-  quat_to_rot(q, R);                              // ba_processor.py:323 (q as stored, not renormalised)
-  if (!rot_to_quat(R, qj)) atomicOr(&d.sc->flags, FLAG_QW_NEAR_ZERO);
-  double* t = d.camtab + (size_t)CAMTAB_STRIDE * c;
-#pragma unroll
-  for (int i = 0; i < 9; ++i) t[i] = R[i];
-  t[9] = cam[0];
-  t[10] = cam[1];
-  t[11] = cam[2];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) t[12 + i] = qj[i];
+  const double v[7] = {cam[0], cam[1], cam[2], cam[3], cam[4], cam[5], cam[6]};
+  cam_table_row(d, c, v);
 }
 
 // ---- cost over the solve's index: sum ||b - f||^2 per group (ba_processor.py:346-349,376) ------------

@@ -1173,7 +1173,7 @@ __global__ void __launch_bounds__(256) k_backsub_points(BaDev d, const UT* __res
   for (int e = 0; e < 3; ++e) p[e] = p[e] + (d.vj[e * N + j] - u[e]);
 }
 
-// cams += delta_p; q /= |q|                      (ba_processor.py:383-392)
+// cams += delta_p; q /= |q|                      (ba_processor.py:383-392); and the camera-table row of the result
 __global__ void k_update_cams(BaDev d) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= d.V) return;
@@ -1193,6 +1193,7 @@ __global__ void k_update_cams(BaDev d) {
     bad |= !(v[k] == v[k]);
   }
   if (bad) atomicOr(&d.sc->flags, FLAG_NONFINITE);
+  cam_table_row(d, c, v);                           // the table row of the new parameters (no k_cam_prepare launch)
 }
 
 // ---- adaptive LM (extension; the reference has fixed lambda and no accept/reject) -----------------

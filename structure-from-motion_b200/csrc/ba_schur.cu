@@ -500,10 +500,23 @@ constexpr int FIN_WARPS = 8;
 
 template <bool PEER>
 __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost_slot, unsigned epoch, int dvdc_quirk,
-                                                              int rows_f32) {
+                                                              int rows_f32, int cost_partials) {
   __shared__ double red[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   Scalars* sc = d.sc;
+  if (cost_partials > 0 && blockIdx.x == 0) {
+    // the cost of this linearisation point: the per-group partials of the linearisation, summed in a fixed order (what
+    // k_sum_cost did in a launch of its own)
+    double a = 0.0;
+    for (int i = tid; i < cost_partials; i += 32 * FIN_WARPS) a += __ldcg(d.grp_cost + i);
+    a = block_sum(a, red);
+    if (tid == 0) {
+      sc->cost_cur = a;
+      if (cost_slot < SFMBA_MAX_COST_HISTORY) sc->costs[cost_slot] = a;
+      if (!(a == a) || isinf(a)) atomicOr(&sc->flags, FLAG_NONFINITE);
+    }
+    __syncthreads();
+  }
   const bool schur = d.schur_diag != 0;
   const int row = schur ? CAM_ACC : ROW_COMPACT;
   const bool hi = lane + 32 < row;
@@ -736,14 +749,15 @@ static int fin_grid(const BaDev& d) {
   return g < 1 ? 1 : (g > 2048 ? 2048 : g);           // red_b holds one partial per CTA
 }
 
-void launch_cam_finish(const BaDev& d, bool peer, bool rows_f32, int cost_slot, unsigned epoch, bool dvdc_quirk,
-                       cudaStream_t st, LaunchCounter& lc) {
+void launch_cam_finish(const BaDev& d, bool peer, bool rows_f32, bool sum_cost, int cost_slot, unsigned epoch,
+                       bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc) {
   const int rf = rows_f32 ? 1 : 0;
+  const int cp = sum_cost ? d.G : 0;                   // the linearisation left one cost partial per group
   if (peer) {
-    k_cam_finish<true><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0, rf);
+    k_cam_finish<true><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0, rf, cp);
     lc.launches++;
   } else {
-    k_cam_finish<false><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0, rf);
+    k_cam_finish<false><<<fin_grid(d), 32 * FIN_WARPS, 0, st>>>(d, cost_slot, epoch, dvdc_quirk ? 1 : 0, rf, cp);
     lc.launches++;
   }
 }

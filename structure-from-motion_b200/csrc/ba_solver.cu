@@ -400,6 +400,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   // the FP32 linearisation writes FP32 segment rows, which only the fused camera finish reads
   const bool lin32_ok = use_f32 && d.xrel != nullptr && opt.precond == SFMBA_PRECOND_JACOBI && fused_finish && (!multi || peer);
   int cost_slot = 0;
+  bool camtab_fresh = false;              // camtab holds the rows of the current cameras (k_update_cams leaves them so)
   for (int it = 0; it < opt.iterations; ++it) {
     t0 = pt.begin();
     if (adaptive) launch_lm_backup(d, st, lc);
@@ -413,18 +414,22 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     bool mv32 = false;                     // arithmetic of the matvecs being launched
    for (int attempt = 0;; ++attempt) {
     if (attempt > 0) t0 = pt.begin();
-    launch_cam_prepare(d, st, lc);
+    if (!camtab_fresh) launch_cam_prepare(d, st, lc);
+    camtab_fresh = true;
+    // (the fused camera finish also sums the cost partials of the linearisation: no k_sum_cost launch)
+    const bool finish_sums_cost = fused_finish && !dense && (!multi || peer);
     if (it == 0 && ranged) {
       // first linearisation of a host-buffer solve: range by range, behind the upload of the points
       for (int r = 0; r < io->num_ranges; ++r) {
         cudaStreamWaitEvent(st, io->ev_range_pts[r], 0);
-        if (lin32) launch_linearize32(d, ts, quirk, cost_slot, st, lc, io->range_grp[r], io->range_grp[r + 1], r + 1 == io->num_ranges);
-        else launch_linearize(d, ts, quirk, cost_slot, st, lc, io->range_grp[r], io->range_grp[r + 1],
-                              r + 1 == io->num_ranges);
+        const bool close = r + 1 == io->num_ranges && !finish_sums_cost;
+        if (lin32) launch_linearize32(d, ts, quirk, cost_slot, st, lc, io->range_grp[r], io->range_grp[r + 1], close);
+        else launch_linearize(d, ts, quirk, cost_slot, st, lc, io->range_grp[r], io->range_grp[r + 1], close);
       }
     } else {
       cudaEvent_t kb = pt.kbegin();
-      if (lin32) launch_linearize32(d, ts, quirk, cost_slot, st, lc); else launch_linearize(d, ts, quirk, cost_slot, st, lc);
+      if (lin32) launch_linearize32(d, ts, quirk, cost_slot, st, lc, 0, -1, !finish_sums_cost);
+      else launch_linearize(d, ts, quirk, cost_slot, st, lc, 0, -1, !finish_sums_cost);
       pt.kend(lin32 ? "linearize32" : "linearize", kb);
     }
     pt.end(PH_LINEARIZE, t0);
@@ -433,7 +438,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     const unsigned pcg_epoch = ++ctx->pcg_epoch;
     if (fused_finish && !dense && (!multi || peer)) {
       // PCG on one GPU or over peer windows: camera sums, blocks and the start of the PCG solve in one kernel per camera
-      launch_cam_finish(d, peer, lin32, cost_slot, pcg_epoch, quirk, st, lc);
+      launch_cam_finish(d, peer, lin32, true, cost_slot, pcg_epoch, quirk, st, lc);
     } else {
       if (peer) {
         launch_camsum64_peer(d, cost_slot, st, lc);
@@ -612,9 +617,8 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       }
       pt.kend("backsub", kb);
     }
-    launch_update_cams(d, st, lc);
+    launch_update_cams(d, st, lc);                      // (and their camtab rows)
     if (adaptive) {
-      launch_cam_prepare(d, st, lc);
       launch_cost_tiles(d, ts, nullptr, st, lc);       // -> sc->cost_new
       launch_lm_model_decrease(d, st, lc);             // -> sc->model_decrease, sc->md_pts (the next word)
       if (multi) {
@@ -623,6 +627,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       }
       launch_lm_decide(d, opt.lm_lambda_min > 0 ? opt.lm_lambda_min : 1e-12,
                        opt.lm_lambda_max > 0 ? opt.lm_lambda_max : 1e12, st, lc);
+      camtab_fresh = false;                            // a rejected step puts the old cameras back
     }
     pt.end(PH_UPDATE, t0);
     ++cost_slot;
@@ -642,7 +647,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   // final cost
   double* final_cost_dev = d.cam_acc + (size_t)d.V * CAM_ACC + 1;
   if (opt.compute_costs || adaptive) {
-    launch_cam_prepare(d, st, lc);
+    if (!camtab_fresh) launch_cam_prepare(d, st, lc);
     cudaEvent_t kb = pt.kbegin();
     launch_cost_tiles(d, ts, final_cost_dev, st, lc);
     pt.kend("cost", kb);

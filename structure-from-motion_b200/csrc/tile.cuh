@@ -104,6 +104,23 @@ __device__ __forceinline__ void stage_chunk_async(const BaDev& d, int c, const C
   }
 }
 
+// camtab row of camera c from its parameters (C, q): R(q) row-major, C, qj = R -> q (the Jacobian's quaternion,
+// campose_processor.py:464)
+__device__ __forceinline__ void cam_table_row(const BaDev& d, int c, const double cam[7]) {
+  double q[4] = {cam[3], cam[4], cam[5], cam[6]};
+  double R[9], qj[4];
+  quat_to_rot(q, R);                              // ba_processor.py:323 (q as stored, not renormalised)
+  if (!rot_to_quat(R, qj)) atomicOr(&d.sc->flags, FLAG_QW_NEAR_ZERO);
+  double* t = d.camtab + (size_t)CAMTAB_STRIDE * c;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) t[i] = R[i];
+  t[9] = cam[0];
+  t[10] = cam[1];
+  t[11] = cam[2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) t[12 + i] = qj[i];
+}
+
 // ---- per-camera rows of a camera-space vector (shared by the PCG kernels and the fused camera finish) -------------
 // Q[j][3 c + k] = d R[k][c] / d q_j for q2 = 2 (w,x,y,z)        (campose_processor.py:636-702)
 __device__ __forceinline__ void quat_dRt(const double q2[4], double Q[4][9]) {
