@@ -262,7 +262,7 @@ void launch_pcg_refresh(const BaDev& d, int mode, double tol, unsigned epoch, bo
                         LaunchCounter& lc);
 void launch_peer_sum_scalars(const BaDev& d, double* vals, int n, cudaStream_t st, LaunchCounter& lc);
 void launch_update_cams(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
-void launch_backsub_points(const BaDev& d, bool from_f32, cudaStream_t st, LaunchCounter& lc);
+void launch_backsub_points(const BaDev& d, bool from_f32, int iters, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_decide(const BaDev& d, double lam_min, double lam_max, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_backup(const BaDev& d, cudaStream_t st, LaunchCounter& lc);
 void launch_lm_model_decrease(const BaDev& d, cudaStream_t st, LaunchCounter& lc);

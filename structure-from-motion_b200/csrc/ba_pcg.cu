@@ -1151,14 +1151,40 @@ __global__ void k_pcg_reopen(BaDev d) {
 // (ba_processor.py:405-406), from what the matvecs left.  Matvec i was applied to z_i and kept u^(i) = D^-1 W^T z_i;
 // the directions obey p_i = z_i + beta_i p_(i-1) and delta_p = sum alpha_i p_i, so with P_i = u^(i) + beta_i P_(i-1)
 // the wanted D^-1 W^T delta_p is sum_i alpha_i P_i, formed in iteration order.  One thread per point.
-template <typename UT>
+// NIT > 0: the number of PCG iterations, known to the host when it launches (it has read the solve's last signal) -- the
+// loads of all iterations are then issued before the first is used; NIT = 0 reads the count from the device scalars.
+template <typename UT, int NIT>
 __global__ void __launch_bounds__(256) k_backsub_points(BaDev d, const UT* __restrict__ ubuf) {
   const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t N = (size_t)d.N;
   if (j >= N) return;
+  double u[3] = {0.0, 0.0, 0.0}, P[3] = {0.0, 0.0, 0.0};
+  double* p = d.pts + 3 * j;
+  if (NIT > 0) {
+    UT ub[NIT > 0 ? NIT : 1][3];
+#pragma unroll
+    for (int i = 0; i < NIT; ++i)
+#pragma unroll
+      for (int e = 0; e < 3; ++e) ub[i][e] = __ldcs(ubuf + ((size_t)i * 3 + e) * N + j);
+    const double v0 = __ldcs(d.vj + j), v1 = __ldcs(d.vj + N + j), v2 = __ldcs(d.vj + 2 * N + j);
+    const double p0 = p[0], p1 = p[1], p2 = p[2];
+    if (d.sc->flags & FLAG_PEER_TIMEOUT) return;    // incomplete cross-rank sums: the step is not applied
+#pragma unroll
+    for (int i = 0; i < NIT; ++i) {
+      const double alpha = d.sc->alpha_hist[i], beta = d.sc->beta_hist[i];
+#pragma unroll
+      for (int e = 0; e < 3; ++e) {
+        P[e] = (double)ub[i][e] + beta * P[e];
+        u[e] += alpha * P[e];
+      }
+    }
+    p[0] = p0 + (v0 - u[0]);
+    p[1] = p1 + (v1 - u[1]);
+    p[2] = p2 + (v2 - u[2]);
+    return;
+  }
   if (d.sc->flags & FLAG_PEER_TIMEOUT) return;      // incomplete cross-rank sums: the step is not applied
   const int iters = d.sc->pcg_iters;
-  double u[3] = {0.0, 0.0, 0.0}, P[3] = {0.0, 0.0, 0.0};
   for (int i = 0; i < iters && i < PCG_UBUF; ++i) {
     const double alpha = d.sc->alpha_hist[i], beta = d.sc->beta_hist[i];
     const UT* ub = ubuf + (size_t)i * 3 * N + j;
@@ -1168,7 +1194,6 @@ __global__ void __launch_bounds__(256) k_backsub_points(BaDev d, const UT* __res
       u[e] += alpha * P[e];
     }
   }
-  double* p = d.pts + 3 * j;
 #pragma unroll
   for (int e = 0; e < 3; ++e) p[e] = p[e] + (d.vj[e * N + j] - u[e]);
 }
@@ -1414,10 +1439,28 @@ void launch_cam_rows(const BaDev& d, const double* vec, bool dvdc_quirk, cudaStr
   lc.launches++;
 }
 
-void launch_backsub_points(const BaDev& d, bool from_f32, cudaStream_t st, LaunchCounter& lc) {
+template <typename UT>
+static void backsub_dispatch(const BaDev& d, const UT* ubuf, int iters, cudaStream_t st) {
+  const dim3 g((unsigned)((d.N + 255) / 256)), b(256);
+  switch (iters) {
+    case 1: k_backsub_points<UT, 1><<<g, b, 0, st>>>(d, ubuf); break;
+    case 2: k_backsub_points<UT, 2><<<g, b, 0, st>>>(d, ubuf); break;
+    case 3: k_backsub_points<UT, 3><<<g, b, 0, st>>>(d, ubuf); break;
+    case 4: k_backsub_points<UT, 4><<<g, b, 0, st>>>(d, ubuf); break;
+    case 5: k_backsub_points<UT, 5><<<g, b, 0, st>>>(d, ubuf); break;
+    case 6: k_backsub_points<UT, 6><<<g, b, 0, st>>>(d, ubuf); break;
+    case 7: k_backsub_points<UT, 7><<<g, b, 0, st>>>(d, ubuf); break;
+    case 8: k_backsub_points<UT, 8><<<g, b, 0, st>>>(d, ubuf); break;
+    default: k_backsub_points<UT, 0><<<g, b, 0, st>>>(d, ubuf); break;
+  }
+}
+
+// `iters`: PCG iterations of the solve as the host read them from its last signal (1..PCG_UBUF), or 0 = ask the device
+void launch_backsub_points(const BaDev& d, bool from_f32, int iters, cudaStream_t st, LaunchCounter& lc) {
   if (d.N <= 0) return;
-  if (from_f32) k_backsub_points<float><<<(d.N + 255) / 256, 256, 0, st>>>(d, d.ubuf32);
-  else k_backsub_points<double><<<(d.N + 255) / 256, 256, 0, st>>>(d, d.ubuf);
+  static_assert(PCG_UBUF == 8, "backsub_dispatch lists the iteration counts 1..PCG_UBUF");
+  if (from_f32) backsub_dispatch<float>(d, d.ubuf32, iters, st);
+  else backsub_dispatch<double>(d, d.ubuf, iters, st);
   lc.launches++;
 }
 

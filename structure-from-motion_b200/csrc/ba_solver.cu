@@ -608,7 +608,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
     {
       cudaEvent_t kb = pt.kbegin();
       if (pcg_finished >= 0 && pcg_finished <= PCG_UBUF) {
-        launch_backsub_points(d, mv32, st, lc);             // the PCG matvecs have left u_j = Dinv B^T p_i per point
+        launch_backsub_points(d, mv32, pcg_finished, st, lc);             // the PCG matvecs have left u_j = Dinv B^T p_i per point
       } else {
         // dense solve, NCCL fallback or a long PCG solve: one tile pass forms pts += v - Dinv B^T dp from the camit
         // rows of x
