@@ -22,18 +22,36 @@ NAMES = ['entry', 'prefetch issued', 'pdl_wait', 'push (mode 3)', 'y / w / dots 
          'partials + alpha', 'update loop', 'block_sum + red_b', 'ticket', 'last CTA']
 
 shape = sys.argv[1] if len(sys.argv) > 1 else 'venice'
-eng = sfm_b200.Engine(device=0)
+world = int(os.environ.get('WORLD_SIZE', '1'))
+rank = int(os.environ.get('RANK', '0'))
+local = int(os.environ.get('LOCAL_RANK', '0'))
+nccl_id = None
+if world > 1:                        # under torchrun: points sharded over the ranks, the exchange inside the kernel
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    b = torch.zeros(128, dtype=torch.uint8, device='cuda')
+    if rank == 0:
+        b.copy_(torch.frombuffer(bytearray(sfm_b200.Engine.nccl_unique_id()), dtype=torch.uint8))
+    dist.broadcast(b, 0)
+    nccl_id = bytes(b.cpu().numpy().tobytes())
+eng = sfm_b200.Engine(device=local, world_size=world, rank=rank, nccl_unique_id=nccl_id)
 prob, _ = synthetic.make_shape(shape)
+if world > 1:
+    prob = synthetic.shard_problem(prob, world, rank)
 t = eng.to_device(prob)
 c0, p0 = t['cams'].clone(), t['pts'].clone()
 for _ in range(3):
     t['cams'].copy_(c0)
     t['pts'].copy_(p0)
     res = eng.ba_solve_device(t, lam=5.0, iterations=3, compute_costs=False)
+if rank != 0:
+    eng.close()
+    sys.exit(0)
 buf = np.zeros((2, 256, 16), dtype=np.uint64)
 rc = eng.lib.sfmba_debug_step_trace(buf.ctypes.data_as(C.c_void_p))
 assert rc == 0, rc
-import torch                         # noqa: E402
 mhz = 1965.0
 g, c = buf[0].astype(np.int64), buf[1].astype(np.int64)
 n = int((g[:, 0] > 0).sum())

@@ -722,7 +722,7 @@ __device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, d
   const int par = (int)(seq64 & 1ull);
   if (lane < 7) {
     const size_t k2 = 2 * (7 * (size_t)cam + lane);
-    for (int w = 0; w < xw.world; ++w) y += ll_load(ll_slot(xw, xw.rank, par, w, xw.ll_y) + k2, seq, xw.timeout_ns, d.sc);
+    y = ll_sum_ranks(ll_slot(xw, xw.rank, par, 0, xw.ll_y) + k2, xw.cap, xw.world, seq, xw.timeout_ns, d.sc);
   }
   return y;
 }
@@ -943,8 +943,7 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
     const int par = (int)(xseq & 1ull);
     const size_t k2 = 2 * k;
     for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_y) + k2, y, seq);
-    y = 0.0;
-    for (int w = 0; w < xw.world; ++w) y += ll_load(ll_slot(xw, xw.rank, par, w, xw.ll_y) + k2, seq, xw.timeout_ns, sc);
+    y = ll_sum_ranks(ll_slot(xw, xw.rank, par, 0, xw.ll_y) + k2, xw.cap, xw.world, seq, xw.timeout_ns, sc);
   }
   double gam = 0.0, del = 0.0, wv = 0.0;
   {
@@ -1421,9 +1420,7 @@ __global__ void k_peer_sum_scalars(BaDev d, double* vals, int n) {
   if (i < n) {
     const double v = vals[i];
     for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_y) + 2 * i, v, seq);
-    double a = 0.0;
-    for (int w = 0; w < xw.world; ++w) a += ll_load(ll_slot(xw, xw.rank, par, w, xw.ll_y) + 2 * i, seq, xw.timeout_ns, d.sc);
-    vals[i] = a;
+    vals[i] = ll_sum_ranks(ll_slot(xw, xw.rank, par, 0, xw.ll_y) + 2 * i, xw.cap, xw.world, seq, xw.timeout_ns, d.sc);
   }
   __syncwarp();
   if (i == 0) *xw.counter() = seq64;

@@ -532,8 +532,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
       const PeerWindow& xw = d.xw;
       const size_t k2 = 2 * (size_t)d.V * row;
       for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_cam) + k2, sc->cost_cur, seq);
-      double c = 0.0;
-      for (int w = 0; w < xw.world; ++w) c += ll_load(ll_slot(xw, xw.rank, par, w, xw.ll_cam) + k2, seq, xw.timeout_ns, sc);
+      const double c = ll_sum_ranks(ll_slot(xw, xw.rank, par, 0, xw.ll_cam) + k2, xw.cap, xw.world, seq, xw.timeout_ns, sc);
       sc->cost_cur = c;
       if (cost_slot < SFMBA_MAX_COST_HISTORY) sc->costs[cost_slot] = c;
     }
@@ -598,14 +597,9 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
         ll_store(dst, a0, seq);
         if (hi) ll_store(dst + 64, a1, seq);
       }
-      double s0 = 0.0, s1 = 0.0;
-      for (int w = 0; w < xw.world; ++w) {
-        const double* src = ll_slot(xw, xw.rank, par, w, xw.ll_cam) + k2;
-        s0 += ll_load(src, seq, xw.timeout_ns, sc);
-        if (hi) s1 += ll_load(src + 64, seq, xw.timeout_ns, sc);
-      }
-      a0 = s0;
-      a1 = s1;
+      const double* src = ll_slot(xw, xw.rank, par, 0, xw.ll_cam) + k2;
+      a0 = ll_sum_ranks(src, xw.cap, xw.world, seq, xw.timeout_ns, sc);
+      a1 = hi ? ll_sum_ranks(src + 64, xw.cap, xw.world, seq, xw.timeout_ns, sc) : 0.0;
     }
     d.cam_acc[(size_t)cam * CAM_ACC + acc_index(d, lane)] = a0;
     if (hi) d.cam_acc[(size_t)cam * CAM_ACC + acc_index(d, lane + 32)] = a1;

@@ -97,6 +97,37 @@ __device__ __forceinline__ double ll_load(const double* slot16, unsigned seq, un
   }
   return __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
 }
+// Sum over the ranks' words of one number, in rank order (all ranks get the same bits).  The loads of all ranks' words go
+// out together and only the words whose tags do not match yet are waited for: a loop of ll_load pays one L2 round trip per
+// rank even when every word has long arrived.  `first` = the number's word in writer 0's slot of this rank's window,
+// `writer_stride` = doubles between the slots of consecutive writers (PeerWindow::cap).
+__device__ __forceinline__ double ll_sum_ranks(const double* first, unsigned long long writer_stride, int world, unsigned seq,
+                                               unsigned long long timeout_ns, Scalars* sc) {
+  unsigned lo[MAX_PEERS], hi[MAX_PEERS];
+  unsigned missing = 0;
+#pragma unroll
+  for (int w = 0; w < MAX_PEERS; ++w) {
+    lo[w] = hi[w] = 0u;
+    if (w < world) {
+      unsigned f0, f1;
+      asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(lo[w]), "=r"(f0), "=r"(hi[w]), "=r"(f1)
+                   : "l"(first + (size_t)w * writer_stride)
+                   : "memory");
+      if (f0 != seq || f1 != seq) missing |= 1u << w;
+    }
+  }
+  double sum = 0.0;
+#pragma unroll
+  for (int w = 0; w < MAX_PEERS; ++w) {
+    if (w < world) {
+      double v = __longlong_as_double((long long)(((unsigned long long)hi[w] << 32) | lo[w]));
+      if (missing & (1u << w)) v = ll_load(first + (size_t)w * writer_stride, seq, timeout_ns, sc);
+      sum += v;
+    }
+  }
+  return sum;
+}
 // a flag-in-data area of a window slot (offset in doubles from the slot's start); element k at 16 k bytes
 __device__ __forceinline__ double* ll_slot(const PeerWindow& xw, int window, int parity, int writer, unsigned long long off) {
   return xw.slot(window, parity, writer) + off;
