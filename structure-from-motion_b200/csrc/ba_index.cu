@@ -30,21 +30,29 @@ __global__ void k_validate_index(BaDev d) {
   if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(&d.sc->flags, FLAG_BAD_INDEX);
 }
 
-// group g owns the points j with rowptr[j] + POINT_WEIGHT * j in [g W, (g+1) W)
-__global__ void k_group_bounds(BaDev d) {
-  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+// group g owns the points j with rowptr[j] + POINT_WEIGHT * j in [g W, (g+1) W).  One warp per group: 32 probes per round
+// cut the range 33-fold (four dependent rounds for a million points instead of twenty bisection steps)
+__global__ void __launch_bounds__(256) k_group_bounds(BaDev d) {
+  const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (g > d.G) return;
   if (g == d.G) {
-    d.grp_pt[g] = d.N;
+    if (lane == 0) d.grp_pt[g] = d.N;
     return;
   }
   const long long target = (long long)g * GROUP_WEIGHT;
   int lo = 0, hi = d.N;   // first j in [0,N] with weight prefix >= target
   while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if ((long long)d.rowptr[mid] + (long long)POINT_WEIGHT * mid < target) lo = mid + 1; else hi = mid;
+    const long long span = hi - lo;
+    const int p = lo + (int)(((long long)(lane + 1) * span) / 33);           // lo <= p < hi, non-decreasing in the lane
+    const bool below = (long long)d.rowptr[p] + (long long)POINT_WEIGHT * p < target;
+    const unsigned m = __ballot_sync(0xffffffffu, below);
+    const int c = __popc(m);                                                 // the predicate is monotone: lanes 0..c-1
+    const int p_last_below = __shfl_sync(0xffffffffu, p, c > 0 ? c - 1 : 0);
+    const int p_first_not = __shfl_sync(0xffffffffu, p, c < 32 ? c : 31);
+    if (c > 0) lo = p_last_below + 1;
+    if (c < 32) hi = p_first_not;
   }
-  d.grp_pt[g] = lo;
+  if (lane == 0) d.grp_pt[g] = lo;
 }
 
 // Cameras of one group are counted in a small open-addressing table: only groups with <= SEG_CAP distinct
@@ -150,9 +158,7 @@ __global__ void __launch_bounds__(RUN_LANES) k_group_count(BaDev d, int fine_chu
   }
 }
 
-__global__ void k_finish_scan(BaDev d, IndexStats* host_stats, unsigned epoch) {
-  // grp_chunk holds the exclusive scan of grp_nchunk over [0, G); close it
-  const int total = d.G > 0 ? d.grp_chunk[d.G - 1] + d.grp_nchunk[d.G - 1] : 0;
+__device__ __forceinline__ void finish_scan(const BaDev& d, int total, IndexStats* host_stats, unsigned epoch) {
   d.grp_chunk[d.G] = total;
   d.sc->num_chunks = total;
   if (host_stats) {
@@ -167,6 +173,31 @@ __global__ void k_finish_scan(BaDev d, IndexStats* host_stats, unsigned epoch) {
     __threadfence_system();
     *(volatile unsigned*)&host_stats->epoch = epoch;
   }
+}
+
+// (after cub's device scan) grp_chunk holds the exclusive scan of grp_nchunk over [0, G); close it
+__global__ void k_finish_scan(BaDev d, IndexStats* host_stats, unsigned epoch) {
+  const int total = d.G > 0 ? d.grp_chunk[d.G - 1] + d.grp_nchunk[d.G - 1] : 0;
+  finish_scan(d, total, host_stats, epoch);
+}
+
+// the same in one launch for the usual group counts: one CTA scans grp_nchunk tile by tile, then closes the scan
+constexpr int SCAN1_THREADS = 1024;
+constexpr int SCAN1_MAX_GROUPS = 64 * SCAN1_THREADS;
+__global__ void __launch_bounds__(SCAN1_THREADS) k_scan_chunks(BaDev d, IndexStats* host_stats, unsigned epoch) {
+  using Scan = cub::BlockScan<int, SCAN1_THREADS>;
+  __shared__ typename Scan::TempStorage tmp;
+  int carry = 0;
+  for (int base = 0; base < d.G; base += SCAN1_THREADS) {
+    const int i = base + threadIdx.x;
+    const int v = i < d.G ? d.grp_nchunk[i] : 0;
+    int ex, tot;
+    Scan(tmp).ExclusiveSum(v, ex, tot);
+    if (i < d.G) d.grp_chunk[i] = carry + ex;
+    carry += tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) finish_scan(d, carry, host_stats, epoch);
 }
 
 struct BuildSmem {
@@ -329,10 +360,17 @@ __global__ void k_iota(int32_t* v, int n) {
   if (i < n) v[i] = i;
 }
 
-// rowpos[slot] = position of (chunk, segment) slot in the camera-sorted order
-__global__ void k_rowpos(const int32_t* __restrict__ sorted_slot, int n, int32_t* __restrict__ rowpos) {
+// rowpos[slot] = position of (chunk, segment) slot in the camera-sorted order; camrow_ptr[c] = first sorted row whose
+// camera is >= c, written where the sorted camera changes (cameras without rows included)
+__global__ void k_rowpos_camptr(const int32_t* __restrict__ sorted_slot, const int32_t* __restrict__ sorted_cam, int n, int V,
+                                int32_t* __restrict__ rowpos, int32_t* __restrict__ camrow_ptr) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < n) rowpos[sorted_slot[k]] = k;
+  if (k >= n) return;
+  rowpos[sorted_slot[k]] = k;
+  const int cam = sorted_cam[k], prev = k > 0 ? sorted_cam[k - 1] : -1;      // ascending, <= V (V = unused slot)
+  for (int c = prev + 1; c <= cam; ++c) camrow_ptr[c] = k;
+  if (k == n - 1)
+    for (int c = cam + 1; c <= V; ++c) camrow_ptr[c] = n;
 }
 
 // camrow_ptr[c] = first sorted row whose camera is >= c
@@ -388,15 +426,20 @@ size_t index_temp_bytes(int G, int chunk_bound, int V) {
 void launch_index_count(const BaDev& d, bool fine_chunks, void* temp, size_t temp_bytes, IndexStats* host_stats,
                         unsigned epoch, cudaStream_t st, LaunchCounter& lc) {
   k_validate_index<<<(d.N + 1 + 255) / 256, 256, 0, st>>>(d);
-  k_group_bounds<<<(d.G + 1 + 255) / 256, 256, 0, st>>>(d);
+  k_group_bounds<<<(unsigned)(((size_t)(d.G + 1) * 32 + 255) / 256), 256, 0, st>>>(d);
   lc.launches += 2;
   if (d.G > 0) {
     k_group_count<<<d.G, RUN_LANES, 0, st>>>(d, fine_chunks ? 1 : 0);
-    cub::DeviceScan::ExclusiveSum(temp, temp_bytes, d.grp_nchunk, d.grp_chunk, d.G, st);
-    lc.launches += 2;
+    lc.launches++;
   }
-  k_finish_scan<<<1, 1, 0, st>>>(d, host_stats, epoch);
-  lc.launches++;
+  if (d.G <= SCAN1_MAX_GROUPS) {
+    k_scan_chunks<<<1, SCAN1_THREADS, 0, st>>>(d, host_stats, epoch);
+    lc.launches++;
+  } else {
+    cub::DeviceScan::ExclusiveSum(temp, temp_bytes, d.grp_nchunk, d.grp_chunk, d.G, st);
+    k_finish_scan<<<1, 1, 0, st>>>(d, host_stats, epoch);
+    lc.launches += 3;
+  }
 }
 
 // phase 2: records, tables and the camera CSR (chunk arrays allocated for `nchunks`)
@@ -414,11 +457,13 @@ void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_byt
     k_iota<<<(n + 255) / 256, 256, 0, st>>>(iota, n);
     cub::DeviceRadixSort::SortPairs(temp, temp_bytes, (const int32_t*)d.seg_cam, sort_keys_out, (const int32_t*)iota,
                                     d.camrow_idx, n, 0, bits_for(d.V), st);
-    k_rowpos<<<(n + 255) / 256, 256, 0, st>>>(d.camrow_idx, n, d.rowpos);     // (iota's buffer: free after the sort)
+    // (rowpos is iota's buffer: free after the sort)
+    k_rowpos_camptr<<<(n + 255) / 256, 256, 0, st>>>(d.camrow_idx, sort_keys_out, n, d.V, d.rowpos, d.camrow_ptr);
     lc.launches += 5;
+  } else {
+    k_cam_rowptr<<<(d.V + 1 + 255) / 256, 256, 0, st>>>(sort_keys_out, n, d.V, d.camrow_ptr);   // no rows: all zeros
+    lc.launches++;
   }
-  k_cam_rowptr<<<(d.V + 1 + 255) / 256, 256, 0, st>>>(sort_keys_out, n, d.V, d.camrow_ptr);
-  lc.launches++;
 }
 
 }  // namespace sfmba
