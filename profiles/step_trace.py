@@ -76,4 +76,24 @@ if c[:, 13].max() > 0:
     print('  fit: %.3f us + %.4f us per row (%.2f us per 160-row batch)' % (b, k, 160 * k))
 last = np.argmax(g[:, 11])
 print('last CTA tail: %.2f us' % ((c[last, 11] - c[last, 10]) / mhz))
+
+# ---- the fused camera finish (k_cam_finish), same build
+if hasattr(eng.lib, 'sfmba_debug_fin_trace') or True:
+    try:
+        fb = np.zeros((2, 512, 8), dtype=np.uint64)
+        eng2 = None
+        rc = C.CDLL(sfm_b200._capi.LIB_PATH).sfmba_debug_fin_trace(fb.ctypes.data_as(C.c_void_p))
+        fg, fc = fb[0].astype(np.int64), fb[1].astype(np.int64)
+        nf = int((fg[:, 0] > 0).sum())
+        fg, fc = fg[:nf], fc[:nf]
+        names = ['entry', 'cost sum / scalars', 'row gather', 'Cholesky', 'inverse columns', 'rhs, rows, stores', 'block_sum + ticket']
+        t0 = fg[:, 0].min()
+        print('k_cam_finish: %d CTAs, span %.2f us' % (nf, (fg[:, :7].max() - t0) / 1e3))
+        for i in range(1, 7):
+            dt = (fc[:, i] - fc[:, i - 1]) / mhz
+            at = (fg[:, i] - t0) / 1e3
+            print('%-22s  dt median %6.2f  max %6.2f us   | reached at (global) median %6.2f  max %6.2f us' %
+                  (names[i], np.median(dt), dt.max(), np.median(at), at.max()))
+    except AttributeError:
+        pass
 eng.close()

@@ -498,17 +498,45 @@ __global__ void k_camsum64_peer(BaDev d);
 // column c of the inverse, so the 7x7 work is seven-fold parallel and lives in registers.
 constexpr int FIN_WARPS = 8;
 
+#ifdef SFMBA_STEP_TRACE
+// profiling build only (profiles/step_trace.py): warp 0 of every CTA stamps the phases of the last k_cam_finish launch
+__device__ unsigned long long g_fin_trace[2][512][8];
+#define FIN_STAMP(i)                                                     \
+  do {                                                                   \
+    if (threadIdx.x == 0 && blockIdx.x < 512) {                          \
+      g_fin_trace[0][blockIdx.x][i] = global_timer_ns();                 \
+      g_fin_trace[1][blockIdx.x][i] = (unsigned long long)clock64();     \
+    }                                                                    \
+  } while (0)
+#else
+#define FIN_STAMP(i) do {} while (0)
+#endif
+
 template <bool PEER>
 __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost_slot, unsigned epoch, int dvdc_quirk,
                                                               int rows_f32, int cost_partials) {
   __shared__ double red[32];
+  __shared__ float4 fin_buf[FIN_WARPS][5 * 32];      // lane sums of the FP32 row gather
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   Scalars* sc = d.sc;
-  if (cost_partials > 0 && blockIdx.x == 0) {
+  FIN_STAMP(0);
+  // (the CTA with the fewest cameras does the extra work)
+  const bool cost_cta = blockIdx.x == gridDim.x - 1;
+  if (cost_partials > 0 && cost_cta) {
     // the cost of this linearisation point: the per-group partials of the linearisation, summed in a fixed order (what
-    // k_sum_cost did in a launch of its own)
+    // k_sum_cost did in a launch of its own); four loads in flight per thread
     double a = 0.0;
-    for (int i = tid; i < cost_partials; i += 32 * FIN_WARPS) a += __ldcg(d.grp_cost + i);
+    constexpr int T = 32 * FIN_WARPS;
+    int i = tid;
+    for (; i + 3 * T < cost_partials; i += 4 * T) {
+      const double v0 = __ldcg(d.grp_cost + i), v1 = __ldcg(d.grp_cost + i + T), v2 = __ldcg(d.grp_cost + i + 2 * T);
+      const double v3 = __ldcg(d.grp_cost + i + 3 * T);
+      a += v0;
+      a += v1;
+      a += v2;
+      a += v3;
+    }
+    for (; i < cost_partials; i += T) a += __ldcg(d.grp_cost + i);
     a = block_sum(a, red);
     if (tid == 0) {
       sc->cost_cur = a;
@@ -528,7 +556,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
     const unsigned long long seq64 = *d.xw.counter() + 1ull;  // advanced by the CTA that finishes last
     seq = (unsigned)seq64;
     par = (int)(seq64 & 1ull);
-    if (blockIdx.x == 0 && tid == 0) {
+    if (cost_cta && tid == 0) {
       const PeerWindow& xw = d.xw;
       const size_t k2 = 2 * (size_t)d.V * row;
       for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_cam) + k2, sc->cost_cur, seq);
@@ -539,6 +567,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
   }
   const double lam = sc->lambda;
   double rr = 0.0;
+  FIN_STAMP(1);
   for (int cam = blockIdx.x * FIN_WARPS + warp; cam < d.V; cam += gridDim.x * FIN_WARPS) {
     double a0 = 0.0, a1 = 0.0;                       // elements lane, lane + 32 of the camera's row sum
     {
@@ -546,32 +575,50 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
       const double* p = d.part64 + lane;
       const float* pf = d.part64f + lane;            // rows of the FP32 linearisation (ROW_F32 floats each)
       if (rows_f32) {
-        // software-pipelined: the loads of the next eight rows are issued before the previous eight are converted and
-        // added (a conversion placed between two loads would hold the later load back: in-order issue)
-        float vf[8], wf[8];
-        auto load8 = [&](int k, float (&a)[8], float (&b)[8]) {
+        // The camera's rows are contiguous: the warp streams them as 16-byte words, ten loads per lane in flight.  Word
+        // i = 32 t + lane of the stream holds floats 4 (i mod 10) .. + 3 of some row, and i mod 10 = (lane + 2 t) mod 10
+        // repeats with t mod 5: five FP32 accumulators per lane (a handful of terms each), combined across lanes in FP64
+        // in a fixed order through shared memory.  (The earlier form -- scalar loads, eight rows at a time -- was a chain
+        // of fifteen L2 round trips for a typical camera: 11 of the kernel's 21 us.)
+        const float4* src = reinterpret_cast<const float4*>(d.part64f + (size_t)r0 * ROW_F32);
+        const int n4 = (r1 - r0) * (ROW_F32 / 4);
+        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 acc[5] = {zero, zero, zero, zero, zero};
+        for (int base = 0; base < n4; base += 320) {
+          float4 v[10];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const bool ok = k + u < r1;
-            a[u] = ok ? __ldcg(pf + (size_t)(k + u) * ROW_F32) : 0.f;
-            b[u] = (ok && hi) ? __ldcg(pf + (size_t)(k + u) * ROW_F32 + 32) : 0.f;
-          }
-        };
-        load8(r0, vf, wf);
-        for (int k = r0; k < r1; k += 8) {
-          float nv[8], nw[8];
-          load8(k + 8, nv, nw);                        // (past the end: all zeros, no loads)
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            a0 += (double)vf[u];
-            a1 += (double)wf[u];
+          for (int u = 0; u < 10; ++u) {
+            const int i = base + 32 * u + lane;
+            v[u] = i < n4 ? __ldcg(src + i) : zero;
           }
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            vf[u] = nv[u];
-            wf[u] = nw[u];
+          for (int u = 0; u < 10; ++u) {
+            acc[u % 5].x += v[u].x;
+            acc[u % 5].y += v[u].y;
+            acc[u % 5].z += v[u].z;
+            acc[u % 5].w += v[u].w;
           }
         }
+        float4* fb = fin_buf[warp];
+        __syncwarp();
+#pragma unroll
+        for (int ph = 0; ph < 5; ++ph) fb[ph * 32 + lane] = acc[ph];
+        __syncwarp();
+        const float* ff = reinterpret_cast<const float*>(fb);
+        auto element = [&](int e) {                    // lanes (cg - 2 ph) mod 10, + 10, ... of phase ph hold column group cg
+          const int cg = e >> 2, j = e & 3;
+          double sum = 0.0;
+#pragma unroll
+          for (int ph = 0; ph < 5; ++ph) {
+            int l0 = (cg - 2 * ph) % 10;
+            if (l0 < 0) l0 += 10;
+            for (int l = l0; l < 32; l += 10) sum += (double)ff[(ph * 32 + l) * 4 + j];
+          }
+          return sum;
+        };
+        a0 = element(lane);
+        a1 = lane < 8 ? element(32 + lane) : 0.0;
+        __syncwarp();
       } else {
         for (int k = r0; k < r1; k += 8) {             // eight rows in flight, summed in row order
           double v[8], w[8];
@@ -589,6 +636,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
         }
       }
     }
+    if (a0 != 12345.0) FIN_STAMP(2);
     if (PEER) {
       const PeerWindow& xw = d.xw;
       const size_t k2 = 2 * ((size_t)cam * row + lane);
@@ -641,6 +689,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
         L[j * (15 - j) / 2 + i - j] = v * inv;          // L[i][j]
       });
     });
+    if (L[27] != 12345.0) FIN_STAMP(3);
     if (!ok && lane == 0) atomicOr(&sc->flags, FLAG_SINGULAR);
     // lane c < 7: column c of S^-1 (L y = e_c, L^T x = y)
     const int c = lane < 7 ? lane : 0;
@@ -663,6 +712,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
       });
       x[i] = v / L[i * (15 - i) / 2];
     });
+    if (x[0] != 12345.0) FIN_STAMP(4);
     // right-hand side g and z = Minv g (row c of the symmetric inverse is x)
     const int g0 = schur ? 56 : 28;
     double g[7], zc = 0.0;
@@ -716,9 +766,12 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
       rr += gc * gc;
     }
   }
+  FIN_STAMP(5);
   rr = block_sum(rr, red);
   if (tid == 0) d.red_b[blockIdx.x] = rr;
-  if (!last_cta_arrives(&sc->ticket_b)) return;
+  const bool fin_last = last_cta_arrives(&sc->ticket_b);
+  FIN_STAMP(6);
+  if (!fin_last) return;
   // ---- the last CTA: |g|^2 in CTA order, the iteration state
   double a = 0.0;
   for (int k = tid; k < (int)gridDim.x; k += blockDim.x) a += __ldcg(d.red_b + k);
@@ -736,6 +789,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
   sc->bar_a = 0u;
   sc->pcg_done = done;
   if (d.host_sig) *(volatile unsigned long long*)d.host_sig = ((unsigned long long)epoch << 32) | (done ? 1ull : 0ull);
+  FIN_STAMP(7);
 }
 
 static int fin_grid(const BaDev& d) {
@@ -848,3 +902,9 @@ void launch_cam_blocks(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
 }
 
 }  // namespace sfmba
+
+#ifdef SFMBA_STEP_TRACE
+extern "C" __attribute__((visibility("default"))) int sfmba_debug_fin_trace(unsigned long long* out_host) {
+  return (int)cudaMemcpyFromSymbol(out_host, sfmba::g_fin_trace, sizeof(sfmba::g_fin_trace));
+}
+#endif
