@@ -18,8 +18,8 @@ sys.path.insert(0, ROOT)
 import sfm_b200                      # noqa: E402
 from sfm_b200 import synthetic       # noqa: E402
 
-NAMES = ['entry', 'prefetch issued', 'pdl_wait', 'push (mode 3)', 'y / w / dots loop', 'block_sum2', 'grid barrier',
-         'partials + alpha', 'update loop', 'block_sum + red_b', 'ticket', 'last CTA']
+NAMES = ['entry', 'prefetch issued', 'pdl_wait', 'gather', 'exchange (mode 3), w, dots', 'block sums', 'grid barrier',
+         'partials + alpha', 'update']
 
 shape = sys.argv[1] if len(sys.argv) > 1 else 'venice'
 world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -58,8 +58,8 @@ n = int((g[:, 0] > 0).sum())
 g, c = g[:n], c[:n]
 print('%d CTAs, %d PCG iterations in the solve' % (n, res.pcg_iterations))
 t_first = g[:, 0].min()
-print('launch span on the global timer: first entry -> last stamp %.2f us' % ((g[:, :11].max() - t_first) / 1e3))
-for i in range(1, 11):
+print('launch span on the global timer: first entry -> last stamp %.2f us' % ((g[:, :9].max() - t_first) / 1e3))
+for i in range(1, 9):
     dt = (c[:, i] - c[:, i - 1]) / mhz
     at = (g[:, i] - t_first) / 1e3
     print('%-22s  dt median %6.2f  max %6.2f us   | reached at (global) median %6.2f  max %6.2f us' %
@@ -74,8 +74,7 @@ if c[:, 13].max() > 0:
     A = np.vstack([rows, np.ones_like(rows)]).T.astype(float)
     k, b = np.linalg.lstsq(A, total, rcond=None)[0]
     print('  fit: %.3f us + %.4f us per row (%.2f us per 160-row batch)' % (b, k, 160 * k))
-last = np.argmax(g[:, 11])
-print('last CTA tail: %.2f us' % ((c[last, 11] - c[last, 10]) / mhz))
+print('scalars written by CTA 0 %.2f us after its update' % ((c[0, 11] - c[0, 8]) / mhz))
 
 # ---- the fused camera finish (k_cam_finish), same build
 if hasattr(eng.lib, 'sfmba_debug_fin_trace') or True:

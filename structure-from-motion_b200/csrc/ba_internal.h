@@ -181,7 +181,7 @@ struct BaDev {
   double* q;                          // [7V] w = S z of the current iteration
   double* s;                          // [7V] S p (by recurrence)
   double* gvec;                       // [7V] right-hand side
-  double* red_a;                      // [<= 1024] per-block partials of the PCG dot products
+  double* red_a;                      // [<= 2048] per-block partials of the PCG dot products (eight per CTA in k_pcg_step1)
   double* red_b;                      // [<= 2048]
   double* cams_backup;                // [V][7]  adaptive mode
   double* pts_backup;                 // [N][3]

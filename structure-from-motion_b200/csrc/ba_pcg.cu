@@ -643,6 +643,30 @@ __device__ __forceinline__ void block_sum2(double& a, double& b, double* scratch
   b = tb;
 }
 
+// NS block-wide sums in one exchange (scratch: NS * 32 + NS doubles); results valid in all threads.  Same order as
+// block_sum2 for each of them (xor tree inside a warp, then the warps in order).
+template <int NS>
+__device__ __forceinline__ void block_sum_n(double (&v)[NS], double* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int i = 0; i < NS; ++i) v[i] = warp_sum(v[i]);
+  __syncthreads();
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < NS; ++i) scratch[i * 32 + warp] = v[i];
+  }
+  __syncthreads();
+  if (threadIdx.x < NS) {                          // one thread per sum: the warps in order
+    double t = 0.0;
+    for (int w = 0; w < nwarps; ++w) t += scratch[threadIdx.x * 32 + w];
+    scratch[NS * 32 + threadIdx.x] = t;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < NS; ++i) v[i] = scratch[NS * 32 + i];
+}
+
 // camit row of a camera whose vector entries sit in lanes 0..6 (every lane computes the row, lanes 0..15 store it)
 __device__ __forceinline__ void warp_camit_row(const BaDev& d, int cam, int lane, double v_lane, int dvdc_quirk,
                                                const double* t_pre = nullptr) {
@@ -672,6 +696,25 @@ __device__ __forceinline__ void grid_barrier(uint32_t* counter, Scalars* sc) {
     const unsigned long long t0 = global_timer_ns();
     unsigned spins = 0;
     while (*(volatile uint32_t*)counter < gridDim.x) {
+      if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > PEER_TIMEOUT_NS) {
+        atomicOr(&sc->flags, FLAG_PEER_TIMEOUT);
+        break;
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// The same with a running arrival count: wait until `target` CTAs have arrived since the counter was last zero.
+__device__ __forceinline__ void grid_barrier_gen(uint32_t* counter, uint32_t target, Scalars* sc) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(counter, 1u);
+    const unsigned long long t0 = global_timer_ns();
+    unsigned spins = 0;
+    while (*(volatile uint32_t*)counter < target) {
       if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > PEER_TIMEOUT_NS) {
         atomicOr(&sc->flags, FLAG_PEER_TIMEOUT);
         break;
@@ -885,10 +928,11 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
 // polling threads on a few L2 lines delayed the stores they were waiting for: 5 us from the last partial to alpha instead
 // of 2.6 us with the arrival counter.  Prefetches before the wait to warm the address translations: no gain.)
 // The arithmetic (and the order of every sum) is that of k_pcg_step, except inside cam_y_gather32_deep.
+constexpr int STEP_SUMS = 8;
 template <int MODE>
 __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double tol, int max_iter, unsigned epoch,
                                                               int dvdc_quirk, int rows_f32) {
-  __shared__ double red[64];
+  __shared__ double red[STEP_SUMS * 32 + STEP_SUMS];
   __shared__ double2 gat[VEC_WARPS][96];
   __shared__ double s_a[VEC_WARPS][49], s_m[VEC_WARPS][49], s_t[VEC_WARPS][16];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -945,7 +989,12 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
     for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_y) + k2, y, seq);
     y = ll_sum_ranks(ll_slot(xw, xw.rank, par, 0, xw.ll_y) + k2, xw.cap, xw.world, seq, xw.timeout_ns, sc);
   }
-  double gam = 0.0, del = 0.0, wv = 0.0;
+  // the sums of the iteration, all through ONE grid-wide reduction: gamma = r.z, delta = z.w, and what gives |r_new|^2
+  // without a second one (below): r.r, r.w, r.s, w.w, w.s, s.s with s the previous direction image
+  double wv = 0.0;
+  double sums[STEP_SUMS];
+#pragma unroll
+  for (int i = 0; i < STEP_SUMS; ++i) sums[i] = 0.0;
   {
     double az = 0.0;
 #pragma unroll
@@ -955,31 +1004,34 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
     }
     if (l7) {
       wv = az - y;
-      gam = rv * zv;
-      del = zv * wv;
+      sums[0] = rv * zv;
+      sums[1] = zv * wv;
+      sums[2] = rv * rv;
+      sums[3] = rv * wv;
+      sums[4] = rv * sv;
+      sums[5] = wv * wv;
+      sums[6] = wv * sv;
+      sums[7] = sv * sv;
     }
   }
   STEP_STAMP(4);
-  block_sum2(gam, del, red);
+  block_sum_n<STEP_SUMS>(sums, red);
   STEP_STAMP(5);
-  if (tid == 0) {
-    d.red_a[2 * blockIdx.x] = gam;
-    d.red_a[2 * blockIdx.x + 1] = del;
-  }
-  grid_barrier(&sc->bar_a, sc);
+  if (tid < STEP_SUMS) d.red_a[STEP_SUMS * blockIdx.x + tid] = red[STEP_SUMS * 32 + tid];     // (block_sum_n leaves the totals there)
+  // grid-wide barrier by generation: the arrival counter is zero when a PCG solve starts (k_cam_finish, k_pcg_init,
+  // k_pcg_refresh) and every iteration of the solve adds the grid to it, so nobody has to put it back
+  grid_barrier_gen(&sc->bar_a, (uint32_t)gridDim.x * (uint32_t)(it_old + 1), sc);
   STEP_STAMP(6);
   pdl_trigger();                                   // every CTA of this grid is resident: the next kernel may queue up
-  gam = del = 0.0;
-  if (tid < (int)gridDim.x) {
-    gam = __ldcg(d.red_a + 2 * tid);
-    del = __ldcg(d.red_a + 2 * tid + 1);
-  }
-  block_sum2(gam, del, red);                       // every CTA sums the partials in CTA order: identical scalars
+#pragma unroll
+  for (int i = 0; i < STEP_SUMS; ++i) sums[i] = tid < (int)gridDim.x ? __ldcg(d.red_a + STEP_SUMS * tid + i) : 0.0;
+  block_sum_n<STEP_SUMS>(sums, red);               // every CTA sums the partials in CTA order: identical scalars
+  const double gam = sums[0], del = sums[1];
   const double beta = it_old == 0 ? 0.0 : gam / gam_old;
   const double den = it_old == 0 ? del : del - beta * gam / alpha_old;
   const double alpha = gam / den;
   STEP_STAMP(7);
-  double rr = 0.0, rn = 0.0;
+  double rn = 0.0;
   if (l7) {
     const double pn = zv + beta * pv;
     const double sn = wv + beta * sv;
@@ -988,7 +1040,6 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
     d.x[k] = xv + alpha * pn;
     rn = rv - alpha * sn;
     d.r[k] = rn;
-    rr = rn * rn;
   }
   if (has) {
     double zn = 0.0;
@@ -1001,30 +1052,27 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
     warp_camit_row(d, cam, lane, zn, dvdc_quirk, s_t[warp]);
   }
   STEP_STAMP(8);
-  rr = block_sum(rr, red);
-  if (tid == 0) d.red_b[blockIdx.x] = rr;
-  STEP_STAMP(9);
-  const bool last_cta = last_cta_arrives(&sc->ticket_b);
-  STEP_STAMP(10);
-  if (!last_cta) return;
-  // ---- the last CTA: scalars of the iteration
-  rr = all_blocks_sum(d.red_b, 1, 0, red);
-  if (tid != 0) return;
+  if (blockIdx.x != 0 || tid != 0) return;
+  // ---- one thread: scalars of the iteration.  |r_new|^2 from the sums above (r_new = r - alpha s_new, s_new = w + beta s):
+  // no second grid-wide reduction, nobody waits for a last CTA.  The r.r it starts from is summed afresh every iteration,
+  // so the rounding of this formula (a few ulp of r.r) does not accumulate; a value that small against r.r is converged.
+  const double rs_new = sums[3] + beta * sums[4];
+  const double ss_new = sums[5] + 2.0 * beta * sums[6] + beta * beta * sums[7];
+  const double rr_new = sums[2] - 2.0 * alpha * rs_new + alpha * alpha * ss_new;
   const int it = it_old + 1;
   int done = 0;
   uint32_t newflags = 0;
-  if (!(den > 0.0) || !(gam > 0.0) || !(rr == rr)) {      // breakdown (S is not positive definite) or NaN
+  if (!(den > 0.0) || !(gam > 0.0) || !(rr_new == rr_new)) {      // breakdown (S is not positive definite) or NaN
     newflags |= FLAG_NONFINITE;
     done = 1;
   }
-  if (rr <= tol * tol * gg) done = 1;
+  if (rr_new <= tol * tol * gg) done = 1;
   if (*(volatile uint32_t*)&sc->flags & FLAG_PEER_TIMEOUT) done = 1;
   if (!done && it >= max_iter) {
     newflags |= FLAG_PCG_MAXITER;
     done = 1;
   }
-  if (MODE == 3) *d.xw.counter() += 1ull;                   // this exchange is finished on this rank
-  sc->bar_a = 0u;
+  if (MODE == 3) *d.xw.counter() += 1ull;                   // every CTA has read its words of this exchange (barrier)
   sc->pcg_iters_total += 1;
   sc->pcg_iters = it;
   if (newflags) atomicOr(&sc->flags, newflags);
@@ -1036,7 +1084,7 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
     sc->beta_hist[it_old] = beta;
   }
   sc->rz = gam;
-  sc->rr = rr;
+  sc->rr = rr_new > 0.0 ? rr_new : 0.0;
   sc->pcg_done = done;
   if (d.host_sig)
     *(volatile unsigned long long*)d.host_sig =

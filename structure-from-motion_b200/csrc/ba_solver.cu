@@ -124,7 +124,7 @@ int sfm_setup_problem(sfmba_ctx* ctx, const sfmba_problem* pr, bool full, BaDev*
     CARVE(S_Q, 7 * V, q);
     CARVE(S_S, 7 * V, s);
     CARVE(S_GVEC, 7 * V, gvec);
-    CARVE(S_RED_A, 1024, red_a);
+    CARVE(S_RED_A, 2048, red_a);
     CARVE(S_RED_B, 2048, red_b);
     CARVE(S_CAMS_BAK, 7 * V, cams_backup);
     CARVE(S_PTS_BAK, 3 * N, pts_backup);
