@@ -81,9 +81,11 @@ typedef enum { SFMBA_PRECOND_JACOBI = 0, SFMBA_PRECOND_SCHUR_JACOBI = 1 } sfmba_
  *         (BASELINE.json north_star: "FP32 with FP64 accumulation").  The reduced system is perturbed by ~1e-7 relative:
  *         the step moves by ~1e-7 cond(Minv S).  Plain least squares with the A + lambda I preconditioner only.
  *   AUTO (default): FP32 matvec when pcg_tol >= 1e-8, a solve that needs more than 8 iterations is finished in FP64 from
- *         a true FP64 residual; FP32 Jacobians from the second LM iteration of a call on while the previous solve was
- *         that fast, and an iteration whose solve turns out slow is redone from an FP64 linearisation.  Depends on
- *         nothing but the call itself (bit-reproducible).  DESIGN.md section 4 has the measured distances.            */
+ *         a true FP64 residual; FP32 Jacobians as long as no PCG solve of the call has been that slow.  A solve on an
+ *         FP32 linearisation is watched: the device gives it up when its convergence rate predicts more than 8
+ *         iterations (or the host sees it take them), the LM iteration is redone from an FP64 linearisation
+ *         (sfmba_result.relinearized counts these) and the rest of the call stays FP64.  Depends on nothing but the
+ *         call itself (bit-reproducible).  DESIGN.md section 4 has the measured distances.                            */
 typedef enum { SFMBA_MATVEC_AUTO = 0, SFMBA_MATVEC_F64 = 1, SFMBA_MATVEC_F32 = 2 } sfmba_matvec_precision;
 
 /*

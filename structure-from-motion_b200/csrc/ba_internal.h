@@ -256,7 +256,7 @@ void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc);   // p
 // vector part of one PCG iteration.  mode 1: y from this GPU's rows; 2: y = svec (NCCL all-reduced);
 // 3: partial y exchanged through the peer windows over NVLink inside the kernel
 void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk, bool rows_f32,
-                     cudaStream_t st, LaunchCounter& lc);
+                     bool abort_slow, cudaStream_t st, LaunchCounter& lc);
 void launch_pcg_reopen(const BaDev& d, bool dvdc_quirk, cudaStream_t st, LaunchCounter& lc);
 void launch_pcg_refresh(const BaDev& d, int mode, double tol, unsigned epoch, bool dvdc_quirk, cudaStream_t st,
                         LaunchCounter& lc);

@@ -770,6 +770,22 @@ __device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, d
   return y;
 }
 
+// What the host reads from pinned memory after every iteration: (epoch, slow, iteration, done) in one 8-byte store.
+__device__ __forceinline__ unsigned long long pcg_signal(unsigned epoch, int it, int done, bool slow) {
+  return ((unsigned long long)epoch << 32) | (slow ? 0x80000000ull : 0ull) | ((unsigned long long)(unsigned)it << 1) |
+         (done ? 1ull : 0ull);
+}
+// A solve being tried on an FP32 linearisation (abort_slow) is given up as soon as its convergence rate says it will need
+// more than PCG_FAST_ITERS iterations -- |r|^2 has to fall from |g|^2 to tol^2 |g|^2 within them, i.e. by 1e-2 per
+// iteration on average at the default tolerance: the host then redoes the LM iteration from an FP64 linearisation.  The decision is taken
+// on the device (every rank takes the same one from the same numbers) and stops the solve like convergence does, so ranks
+// need not agree on how many iterations they have queued.
+constexpr int PCG_FAST_ITERS = 8;
+__device__ __forceinline__ bool pcg_slow(int abort_slow, int done, int it, double rr, double gg, double tol) {
+  return abort_slow && !done && it >= 2 && it <= PCG_FAST_ITERS &&
+         rr > gg * exp10(2.0 * log10(tol) * (double)it / (double)PCG_FAST_ITERS);
+}
+
 // ---- the vector part of the solve ------------------------------------------------------------------------
 // Preconditioned conjugate gradients in the Chronopoulos-Gear form: the matvec is applied to z = Minv r (k_matvec reads
 // the camit rows of z), and ONE grid-wide reduction per iteration gives both scalars,
@@ -787,7 +803,7 @@ __device__ __forceinline__ double pcg_cam_y(const BaDev& d, int cam, int lane, d
 // (64 registers: the per-warp constants are then read where they are used instead of being fetched ahead)
 template <int MODE, bool WIDE>
 __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d, double tol, int max_iter, unsigned epoch,
-                                                                        int dvdc_quirk, int rows_f32) {
+                                                                        int dvdc_quirk, int rows_f32, int abort_slow) {
   __shared__ double red[64];
   __shared__ double2 gat[VEC_WARPS][96];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -896,6 +912,8 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
     newflags |= FLAG_PCG_MAXITER;
     done = 1;
   }
+  const bool slow = pcg_slow(abort_slow, done, it, rr, gg, tol);
+  if (slow) done = 1;
   if (MODE == 3) *d.xw.counter() += 1ull;                   // this exchange is finished on this rank
   sc->bar_a = 0u;
   sc->pcg_iters_total += 1;
@@ -911,9 +929,7 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
   sc->rz = gam;
   sc->rr = rr;
   sc->pcg_done = done;
-  if (d.host_sig)
-    *(volatile unsigned long long*)d.host_sig =
-        ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
+  if (d.host_sig) *(volatile unsigned long long*)d.host_sig = pcg_signal(epoch, it, done, slow);
   STEP_STAMP(11);
 }
 
@@ -931,7 +947,7 @@ __global__ void __launch_bounds__(VEC_THREADS, WIDE ? 2 : 1) k_pcg_step(BaDev d,
 constexpr int STEP_SUMS = 8;
 template <int MODE>
 __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double tol, int max_iter, unsigned epoch,
-                                                              int dvdc_quirk, int rows_f32) {
+                                                              int dvdc_quirk, int rows_f32, int abort_slow) {
   __shared__ double red[STEP_SUMS * 32 + STEP_SUMS];
   __shared__ double2 gat[VEC_WARPS][96];
   __shared__ double s_a[VEC_WARPS][49], s_m[VEC_WARPS][49], s_t[VEC_WARPS][16];
@@ -1072,6 +1088,8 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
     newflags |= FLAG_PCG_MAXITER;
     done = 1;
   }
+  const bool slow = pcg_slow(abort_slow, done, it, rr_new, gg, tol);
+  if (slow) done = 1;
   if (MODE == 3) *d.xw.counter() += 1ull;                   // every CTA has read its words of this exchange (barrier)
   sc->pcg_iters_total += 1;
   sc->pcg_iters = it;
@@ -1086,9 +1104,7 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
   sc->rz = gam;
   sc->rr = rr_new > 0.0 ? rr_new : 0.0;
   sc->pcg_done = done;
-  if (d.host_sig)
-    *(volatile unsigned long long*)d.host_sig =
-        ((unsigned long long)epoch << 32) | ((unsigned long long)(unsigned)it << 1) | (done ? 1ull : 0ull);
+  if (d.host_sig) *(volatile unsigned long long*)d.host_sig = pcg_signal(epoch, it, done, slow);
   STEP_STAMP(11);
 }
 
@@ -1411,28 +1427,29 @@ void launch_camsum12(const BaDev& d, cudaStream_t st, LaunchCounter& lc) {
 
 // the vector part of a PCG iteration (one launch); mode 1: y from this GPU's rows, 2: from svec, 3: peer windows
 void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigned epoch, bool dvdc_quirk, bool rows_f32,
-                     cudaStream_t st, LaunchCounter& lc) {
+                     bool abort_slow, cudaStream_t st, LaunchCounter& lc) {
   const int rf = rows_f32 ? 1 : 0;
+  const int ab = abort_slow ? 1 : 0;
   const int q = dvdc_quirk ? 1 : 0;
   const int g1 = vec_grid(d);                          // <= SM count
   static const bool step1_enabled = !(getenv("SFMBA_STEP1") && atoi(getenv("SFMBA_STEP1")) == 0);   // (A/B switch)
   const bool wide = (d.V + VEC_WARPS - 1) / VEC_WARPS > g1;      // more cameras than that grid has warps
   if (!wide && mode != 2 && step1_enabled) {
     // one camera per warp: the latency-trimmed kernel
-    if (mode == 1) launch_pdl(k_pcg_step1<1>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
-    else launch_pdl(k_pcg_step1<3>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    if (mode == 1) launch_pdl(k_pcg_step1<1>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
+    else launch_pdl(k_pcg_step1<3>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
   } else if (!wide) {
-    if (mode == 1) launch_pdl(k_pcg_step<1, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
-    else if (mode == 2) launch_pdl(k_pcg_step<2, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
-    else launch_pdl(k_pcg_step<3, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    if (mode == 1) launch_pdl(k_pcg_step<1, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
+    else if (mode == 2) launch_pdl(k_pcg_step<2, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
+    else launch_pdl(k_pcg_step<3, false>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
   } else {
     // two CTAs per SM are resident at 64 registers: twice the warps, still every CTA of the grid on the chip (the kernel
     // holds a grid-wide barrier)
     int g2 = (d.V + VEC_WARPS - 1) / VEC_WARPS;
     if (g2 > 2 * g1) g2 = 2 * g1;
-    if (mode == 1) launch_pdl(k_pcg_step<1, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
-    else if (mode == 2) launch_pdl(k_pcg_step<2, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
-    else launch_pdl(k_pcg_step<3, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf);
+    if (mode == 1) launch_pdl(k_pcg_step<1, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
+    else if (mode == 2) launch_pdl(k_pcg_step<2, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
+    else launch_pdl(k_pcg_step<3, true>, dim3(g2), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
   }
   lc.launches += 1;
 }

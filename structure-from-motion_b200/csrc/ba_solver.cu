@@ -272,7 +272,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   static const int lin32_env = getenv("SFMBA_LIN32") ? atoi(getenv("SFMBA_LIN32")) : -1;
   int relinearized = 0;
   int f32_cond = 0;     // what the previous PCG solve OF THIS CALL said about the reduced system: 1 = converged fast, -1 = slow,
-                        // 0 = none yet (the first linearisation of a call is FP64: the result never depends on earlier calls)
+                        // 0 = none yet (nothing is carried over from earlier calls: the result never depends on them)
   int refine_iters = 0;
   const bool adaptive = opt.mode == SFMBA_MODE_ADAPTIVE_LM;
   const bool multi = ctx->world > 1;
@@ -404,12 +404,13 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
   for (int it = 0; it < opt.iterations; ++it) {
     t0 = pt.begin();
     if (adaptive) launch_lm_backup(d, st, lc);
-    // FP32 Jacobian arithmetic in this linearisation?  F32: always.  AUTO: from the second LM iteration of a call on, when
-    // the previous iteration's PCG solve showed a well-conditioned reduced system (it converged within F32_SAFE_ITERS
-    // iterations); if this iteration's solve then turns out slow after all, the iteration is redone from an FP64
-    // linearisation (the parameters are still untouched).
+    // FP32 Jacobian arithmetic in this linearisation?  F32: always.  AUTO: unless a PCG solve of this call has shown an
+    // ill-conditioned reduced system (more than F32_SAFE_ITERS iterations).  The solve on an FP32 linearisation is watched:
+    // the device gives it up as soon as its convergence rate predicts more than F32_SAFE_ITERS iterations (pcg_slow,
+    // ba_pcg.cu) or, failing that, the host sees it take that many -- the LM iteration is then redone from an FP64
+    // linearisation (the parameters are still untouched) and the rest of the call stays FP64.
     bool lin32 = lin32_ok && (lin32_env >= 0 ? lin32_env != 0
-                                             : (opt.matvec_precision == SFMBA_MATVEC_F32 || (auto_prec && f32_cond > 0)));
+                                             : (opt.matvec_precision == SFMBA_MATVEC_F32 || (auto_prec && f32_cond >= 0)));
     int pcg_finished = -1;                 // iterations of this PCG solve when the host knows the number
     bool mv32 = false;                     // arithmetic of the matvecs being launched
    for (int attempt = 0;; ++attempt) {
@@ -482,6 +483,8 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       launch_cam_rows(d, d.x, quirk, st, lc);
     }
     const int tail_mode = !multi ? 1 : (peer ? 3 : 2);
+    // a solve on an FP32 linearisation that AUTO chose is on probation (see above)
+    const bool watch_solve = lin32 && auto_prec && lin32_env < 0 && attempt == 0;
     int pcg_count = -1;                    // iterations of the solve's first run (before any FP64 continuation)
     pcg_finished = -1;
     mv32 = use_f32 && tail_mode != 2;
@@ -496,7 +499,7 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
         if (r2 != 0) return r2;
       }
       kb = pt.kbegin();
-      launch_pcg_tail(d, tail_mode, tol, max_iter, cur_epoch, quirk, mv32, st, lc);
+      launch_pcg_tail(d, tail_mode, tol, max_iter, cur_epoch, quirk, mv32, watch_solve, st, lc);
       pt.kend("pcg_tail", kb);
       return 0;
     };
@@ -509,22 +512,22 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
       static const int LOOKAHEAD = getenv("SFMBA_LOOKAHEAD") ? std::max(1, atoi(getenv("SFMBA_LOOKAHEAD"))) : 2;
       volatile unsigned long long* sig = reinterpret_cast<volatile unsigned long long*>(ctx->pinned);
       int launched = 0, finished = 0;
-      bool done = false;
+      bool done = false, gave_up = false;    // gave_up: the device stopped a solve it predicts to be slow (abort_slow)
       // wait until iteration `want` (1-based) has finished or the solve is done; updates finished/done
       auto wait_for = [&](int want) -> int {
         long spins = 0;
         for (;;) {
           const unsigned long long w = *sig;
           if ((unsigned)(w >> 32) == cur_epoch) {
-            finished = (int)((w & 0xffffffffull) >> 1);
-            if (w & 1ull) { done = true; return 0; }
+            finished = (int)((w & 0x7fffffffull) >> 1);
+            if (w & 1ull) { done = true; gave_up = (w & 0x80000000ull) != 0; return 0; }
             if (finished >= want) return 0;
           }
           if ((++spins & 0x3fff) == 0 && cudaStreamQuery(st) != cudaErrorNotReady) {
             const unsigned long long w2 = *sig;       // stream drained: final state or an error
             if ((unsigned)(w2 >> 32) == cur_epoch) {
-              finished = (int)((w2 & 0xffffffffull) >> 1);
-              if (w2 & 1ull) { done = true; return 0; }
+              finished = (int)((w2 & 0x7fffffffull) >> 1);
+              if (w2 & 1ull) { done = true; gave_up = (w2 & 0x80000000ull) != 0; return 0; }
               if (finished >= want) return 0;
             }
             int r2 = sfm_check_cuda(ctx, cudaGetLastError(), "pcg kernels");
@@ -548,10 +551,16 @@ int sfm_ba_solve_device(sfmba_ctx* ctx, const sfmba_problem* pr, const sfmba_opt
         return 0;
       };
       if ((rc = run(std::min(ctx->pcg_hint, max_iter))) != 0) return rc;
+      if (gave_up) {
+        // (the hint for the next solve stays what it was)
+        pcg_count = F32_SAFE_ITERS + 1;                      // counts as a slow solve below
+        pcg_finished = -1;
+      } else {
       ctx->pcg_hint = finished;
       pcg_finished = finished;
       pcg_count = finished;
-      if (mv32 && auto_prec && finished > F32_SAFE_ITERS && finished < max_iter) {
+      }
+      if (!gave_up && mv32 && auto_prec && finished > F32_SAFE_ITERS && finished < max_iter && !watch_solve) {
         // AUTO: a solve this slow amplifies the 1e-7 operator error of the FP32 matvec too much to accept unseen.  Its
         // x is the starting point of an FP64 continuation: true residual from one FP64 matvec on x, then FP64 iterations
         // until that residual meets the tolerance (usually very few)
