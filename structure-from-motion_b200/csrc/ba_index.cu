@@ -183,17 +183,28 @@ __global__ void k_finish_scan(BaDev d, IndexStats* host_stats, unsigned epoch) {
 
 // the same in one launch for the usual group counts: one CTA scans grp_nchunk tile by tile, then closes the scan
 constexpr int SCAN1_THREADS = 1024;
-constexpr int SCAN1_MAX_GROUPS = 64 * SCAN1_THREADS;
+constexpr int SCAN1_ITEMS = 8;                       // consecutive groups per thread: one tile covers 8192 groups
+constexpr int SCAN1_MAX_GROUPS = 64 * SCAN1_THREADS * SCAN1_ITEMS;
 __global__ void __launch_bounds__(SCAN1_THREADS) k_scan_chunks(BaDev d, IndexStats* host_stats, unsigned epoch) {
   using Scan = cub::BlockScan<int, SCAN1_THREADS>;
   __shared__ typename Scan::TempStorage tmp;
   int carry = 0;
-  for (int base = 0; base < d.G; base += SCAN1_THREADS) {
-    const int i = base + threadIdx.x;
-    const int v = i < d.G ? d.grp_nchunk[i] : 0;
+  for (int base = 0; base < d.G; base += SCAN1_THREADS * SCAN1_ITEMS) {
+    const int i0 = base + threadIdx.x * SCAN1_ITEMS;
+    int v[SCAN1_ITEMS], mine = 0;
+#pragma unroll
+    for (int u = 0; u < SCAN1_ITEMS; ++u) {
+      v[u] = i0 + u < d.G ? d.grp_nchunk[i0 + u] : 0;
+      mine += v[u];
+    }
     int ex, tot;
-    Scan(tmp).ExclusiveSum(v, ex, tot);
-    if (i < d.G) d.grp_chunk[i] = carry + ex;
+    Scan(tmp).ExclusiveSum(mine, ex, tot);
+    int run = carry + ex;
+#pragma unroll
+    for (int u = 0; u < SCAN1_ITEMS; ++u) {
+      if (i0 + u < d.G) d.grp_chunk[i0 + u] = run;
+      run += v[u];
+    }
     carry += tot;
     __syncthreads();
   }
@@ -291,6 +302,8 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
     }
     if (tid == 0) s.seg_start[nseg] = len;
     for (int sidx = nseg + tid; sidx < SEG_CAP; sidx += RUN_LANES) d.seg_cam[(size_t)c * SEG_CAP + sidx] = d.V;
+    // the identity permutation the camera sort of the rows starts from (rowpos is that buffer until the sort is done)
+    for (int sidx = tid; sidx < SEG_CAP; sidx += RUN_LANES) d.rowpos[(size_t)c * SEG_CAP + sidx] = c * SEG_CAP + sidx;
     __syncthreads();
     // lanes per segment -> first lane of each segment
     const int nl = tid < nseg ? (s.seg_start[tid + 1] - s.seg_start[tid] + K - 1) / K : 0;
@@ -353,11 +366,6 @@ __global__ void __launch_bounds__(RUN_LANES) k_chunk_build(BaDev d, int cam_bits
     }
     __syncthreads();
   }
-}
-
-__global__ void k_iota(int32_t* v, int n) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) v[i] = i;
 }
 
 // rowpos[slot] = position of (chunk, segment) slot in the camera-sorted order; camrow_ptr[c] = first sorted row whose
@@ -454,12 +462,12 @@ void launch_index_build(const BaDev& d, int nchunks, void* temp, size_t temp_byt
                         int32_t* iota, cudaStream_t st, LaunchCounter& lc) {
   const int n = nchunks * SEG_CAP;
   if (n > 0) {
-    k_iota<<<(n + 255) / 256, 256, 0, st>>>(iota, n);
+    // (iota = d.rowpos: filled by k_chunk_build)
     cub::DeviceRadixSort::SortPairs(temp, temp_bytes, (const int32_t*)d.seg_cam, sort_keys_out, (const int32_t*)iota,
                                     d.camrow_idx, n, 0, bits_for(d.V), st);
     // (rowpos is iota's buffer: free after the sort)
     k_rowpos_camptr<<<(n + 255) / 256, 256, 0, st>>>(d.camrow_idx, sort_keys_out, n, d.V, d.rowpos, d.camrow_ptr);
-    lc.launches += 5;
+    lc.launches += 4;
   } else {
     k_cam_rowptr<<<(d.V + 1 + 255) / 256, 256, 0, st>>>(sort_keys_out, n, d.V, d.camrow_ptr);   // no rows: all zeros
     lc.launches++;
