@@ -46,9 +46,11 @@ for _ in range(3):
     t['cams'].copy_(c0)
     t['pts'].copy_(p0)
     res = eng.ba_solve_device(t, lam=5.0, iterations=3, compute_costs=False)
-if rank != 0:
-    eng.close()
-    sys.exit(0)
+if rank != 0:                        # the other ranks report into their own file (TRACE_ALL_RANKS=dir)
+    if not os.environ.get('TRACE_ALL_RANKS'):
+        eng.close()
+        sys.exit(0)
+    sys.stdout = open(os.path.join(os.environ['TRACE_ALL_RANKS'], 'step_trace_rank%d.txt' % rank), 'w')
 buf = np.zeros((2, 256, 16), dtype=np.uint64)
 rc = eng.lib.sfmba_debug_step_trace(buf.ctypes.data_as(C.c_void_p))
 assert rc == 0, rc
@@ -57,6 +59,8 @@ g, c = buf[0].astype(np.int64), buf[1].astype(np.int64)
 n = int((g[:, 0] > 0).sum())
 g, c = g[:n], c[:n]
 print('%d CTAs, %d PCG iterations in the solve' % (n, res.pcg_iterations))
+if os.environ.get('TRACE_ALL_RANKS'):
+    np.save(os.path.join(os.environ['TRACE_ALL_RANKS'], 'step_trace_raw_rank%d.npy' % rank), buf)
 t_first = g[:, 0].min()
 print('launch span on the global timer: first entry -> last stamp %.2f us' % ((g[:, :9].max() - t_first) / 1e3))
 for i in range(1, 9):

@@ -1003,6 +1003,7 @@ __global__ void __launch_bounds__(VEC_THREADS, 1) k_pcg_step1(BaDev d, double to
     const int par = (int)(xseq & 1ull);
     const size_t k2 = 2 * k;
     for (int w = 0; w < xw.world; ++w) ll_store(ll_slot(xw, w, par, xw.rank, xw.ll_y) + k2, y, seq);
+    ll_flush();
     y = ll_sum_ranks(ll_slot(xw, xw.rank, par, 0, xw.ll_y) + k2, xw.cap, xw.world, seq, xw.timeout_ns, sc);
   }
   // the sums of the iteration, all through ONE grid-wide reduction: gamma = r.z, delta = z.w, and what gives |r_new|^2

@@ -645,6 +645,7 @@ __global__ void __launch_bounds__(32 * FIN_WARPS) k_cam_finish(BaDev d, int cost
         ll_store(dst, a0, seq);
         if (hi) ll_store(dst + 64, a1, seq);
       }
+      ll_flush();
       const double* src = ll_slot(xw, xw.rank, par, 0, xw.ll_cam) + k2;
       a0 = ll_sum_ranks(src, xw.cap, xw.world, seq, xw.timeout_ns, sc);
       a1 = hi ? ll_sum_ranks(src + 64, xw.cap, xw.world, seq, xw.timeout_ns, sc) : 0.0;

@@ -71,6 +71,20 @@ __device__ __forceinline__ void peer_wait(const PeerWindow& xw, unsigned long lo
   __syncthreads();
 }
 
+// After a warp's words have been stored: push them out (SFMBA_LL_FENCE 1 = membar.sys by the storing lanes).
+#ifndef SFMBA_LL_FENCE
+#define SFMBA_LL_FENCE 0
+#endif
+__device__ __forceinline__ void ll_flush() {
+#if SFMBA_LL_FENCE == 1
+  __threadfence_system();
+#elif SFMBA_LL_FENCE == 2
+  __threadfence();
+#endif
+}
+#ifndef SFMBA_LL_SLEEP
+#define SFMBA_LL_SLEEP 0
+#endif
 // ---- flag-in-data ("LL") exchange: every double travels as one 16-byte word {lo, seq, hi, seq}; the reader spins until
 // both sequence tags match.  No fence, no ticket, no separate flag: a reader waits only for the numbers it needs.
 __device__ __forceinline__ void ll_store(double* slot16, double v, unsigned seq) {
@@ -86,6 +100,9 @@ __device__ __forceinline__ double ll_load(const double* slot16, unsigned seq, un
   for (;;) {
     asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(f0), "=r"(hi), "=r"(f1) : "l"(slot16) : "memory");
     if (f0 == seq && f1 == seq) break;
+#if SFMBA_LL_SLEEP > 0
+    __nanosleep(SFMBA_LL_SLEEP);     // thousands of lanes poll: back off, or the polling loads delay the very stores they wait for
+#endif
     if ((++spins & 0xffu) == 0) {
       const unsigned long long now = global_timer_ns();
       if (t0 == 0) t0 = now;
