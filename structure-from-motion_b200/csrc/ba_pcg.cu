@@ -1435,8 +1435,11 @@ void launch_pcg_tail(const BaDev& d, int mode, double tol, int max_iter, unsigne
   const int g1 = vec_grid(d);                          // <= SM count
   static const bool step1_enabled = !(getenv("SFMBA_STEP1") && atoi(getenv("SFMBA_STEP1")) == 0);   // (A/B switch)
   const bool wide = (d.V + VEC_WARPS - 1) / VEC_WARPS > g1;      // more cameras than that grid has warps
-  if (!wide && mode != 2 && step1_enabled) {
-    // one camera per warp: the latency-trimmed kernel
+  static const bool step1_peer = getenv("SFMBA_STEP1_PEER") && atoi(getenv("SFMBA_STEP1_PEER")) != 0;
+  if (!wide && step1_enabled && (mode == 1 || (mode == 3 && step1_peer))) {
+    // one camera per warp on one GPU: the latency-trimmed kernel.  With the peer exchange inside it measured SLOWER than
+    // k_pcg_step<3> (4 GPUs, same box: 33 against 26 us between the matvecs, profiles/r2_ab32_*), so several GPUs keep
+    // the older kernel unless SFMBA_STEP1_PEER=1
     if (mode == 1) launch_pdl(k_pcg_step1<1>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
     else launch_pdl(k_pcg_step1<3>, dim3(g1), dim3(VEC_THREADS), 0, st, d, tol, max_iter, epoch, q, rf, ab);
   } else if (!wide) {
